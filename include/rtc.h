@@ -1,0 +1,205 @@
+/*
+ * rtc.h — C ABI of the B200-native `Camera::render` hot path.
+ *
+ * One shared library (librtc_b200.so), C linkage, plain pointers and sizes, no
+ * exceptions across the boundary, `int` status + rtc_last_error().  The caller owns
+ * every buffer; descriptors are copied during the call.  The reference
+ * (joedane/raytracer-challenge, crate `ch1`) has no FFI/plugin interface: the
+ * boundary replaced is the Rust method
+ *     pub fn render(&self, w:&World) -> Canvas          src/camera.rs:116
+ * and its siblings render_async (src/camera.rs:144) / render_async1 (:128).
+ * Each entry point below cites the reference code whose work it takes over.
+ * INTEGRATION.md shows the Rust `extern "C"` block + `flatten()` shim that binds them.
+ *
+ * All matrices are 4x4 row-major f64 (src/transform.rs:23-27); only the affine 3x4
+ * part is used by the path (src/transform.rs:107-128).
+ *
+ * There is NO CPU fallback behind this ABI: without a CUDA device every compute
+ * entry point returns RTC_ERR_NO_DEVICE.
+ */
+#ifndef RTC_B200_H
+#define RTC_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define RTC_ABI_VERSION 1
+
+/* status codes */
+enum {
+    RTC_OK = 0,
+    RTC_ERR_INVALID_ARG = 1,  /* null pointer, bad enum, bad size */
+    RTC_ERR_UNSUPPORTED = 2,  /* e.g. material with neither colour nor pattern (the reference
+                                 panics: src/material.rs:331), samples >= 2 (rand::thread_rng,
+                                 src/camera.rs:84-92) */
+    RTC_ERR_NO_DEVICE = 3,    /* no CUDA device / driver: the path never falls back to the CPU */
+    RTC_ERR_CUDA = 4,         /* a CUDA runtime call failed; see rtc_last_error() */
+    RTC_ERR_NO_SCENE = 5,     /* rtc_render* before rtc_scene_upload */
+    RTC_ERR_NCCL = 6
+};
+
+/* src/shape.rs:281 (Sphere), :405 (Plane), :500 (Cube) */
+enum { RTC_SHAPE_SPHERE = 0, RTC_SHAPE_PLANE = 1, RTC_SHAPE_CUBE = 2 };
+
+/* src/material.rs:48 Test, :72 Stripe, :106 Gradient, :138 Ring, :173 Checker, :208 Grid */
+enum {
+    RTC_PATTERN_NONE = 0,
+    RTC_PATTERN_TEST = 1,
+    RTC_PATTERN_STRIPE = 2,
+    RTC_PATTERN_GRADIENT = 3,
+    RTC_PATTERN_RING = 4,
+    RTC_PATTERN_CHECKER = 5,
+    RTC_PATTERN_GRID = 6
+};
+
+/* One `Box<dyn Shape>` of World.shapes (src/shape.rs:633-637), flattened:
+ *   inv     = Shape::get_transform_inverse()            src/shape.rs:30
+ *   inv_t   = Shape::get_transform_inverse_transpose()  src/shape.rs:32   (read verbatim; the
+ *             stale value left by Plane/Cube::set_transform, :446-449, is kept as is)
+ *   world_id= Shape::get_world_id()                     src/shape.rs:21   (u8, wraps at 256)
+ *   material fields                                     src/material.rs:244-254
+ *   pattern: kind + Pattern::get_transform_inverse() + its two colours  src/material.rs:33-242
+ *            (GRID: pat_a = base colour, pat_b = grid colour)
+ */
+typedef struct rtc_shape {
+    int32_t kind;
+    int32_t world_id;
+    double inv[16];
+    double inv_t[16];
+    int32_t has_color;
+    int32_t pattern_kind;
+    double color[3];
+    double ambient;
+    double diffuse;
+    double specular;
+    double shininess;
+    double reflective;
+    double transparency;
+    double refractive_index;
+    double pat_inv[16];
+    double pat_a[3];
+    double pat_b[3];
+} rtc_shape;
+
+/* World.light (src/shape.rs:635, src/material.rs:10-14): a single point light. */
+typedef struct rtc_light {
+    double intensity[3];
+    double position[3];
+} rtc_light;
+
+/* Camera (src/camera.rs:16-27): the derived fields computed by Camera::new (:39-58) and
+ * the private view_transform_inv (:25).  samples = antialiasing_samples: 1 = one centre
+ * sample, 0 = the deterministic 2x2 supersample (:96-113 with an empty resample loop). */
+typedef struct rtc_camera {
+    uint32_t hsize;
+    uint32_t vsize;
+    double half_width;
+    double half_height;
+    double pixel_size;
+    double view_inv[16];
+    uint32_t samples;
+    uint32_t reserved;
+} rtc_camera;
+
+enum { RTC_PRECISION_F64_PARITY = 0, RTC_PRECISION_F32_FAST = 1 };
+/* RTC_RECT_REFERENCE_RENDER reproduces Camera::render's loop bounds, which skip the last row
+ * and the last column (src/camera.rs:120-121); RTC_RECT_FULL is render_async's (:149). */
+enum { RTC_RECT_REFERENCE_RENDER = 0, RTC_RECT_FULL = 1 };
+/* F64_RGB is Canvas.pixels' layout: row-major y*width+x, 3 x f64 (src/canvas.rs:17-22,43-51).
+ * U8_RGB applies Color::scale's truncate-then-clamp rule (src/color.rs:100-114). */
+enum { RTC_OUT_F64_RGB = 0, RTC_OUT_F32_RGB = 1, RTC_OUT_U8_RGB = 2 };
+
+typedef struct rtc_render_opts {
+    int32_t precision;   /* RTC_PRECISION_* */
+    int32_t rect;        /* RTC_RECT_* */
+    int32_t max_depth;   /* Camera::MAX_REFLECTIONS = 5 (src/camera.rs:31); 0..RTC_MAX_DEPTH */
+    int32_t out_format;  /* RTC_OUT_* */
+    /* Row-tile sharding (rtc_render_device only; rtc_render shards over the context's GPUs
+     * itself).  Tile k = rows [k*tile_rows, (k+1)*tile_rows) belongs to shard k % shard_count.
+     * shard_count <= 1 renders the whole frame. */
+    int32_t shard_index;
+    int32_t shard_count;
+    int32_t tile_rows;
+    int32_t reserved;
+} rtc_render_opts;
+
+#define RTC_MAX_DEPTH 8
+
+/* Work counters of one render ("ray" = one World::intersect call, src/shape.rs:677). */
+typedef struct rtc_stats {
+    uint64_t rays;
+    uint64_t primary_hits;
+    uint64_t shaded_hits;
+    uint64_t shadow_rays;
+    uint64_t kernel_launches;
+    double h2d_ms;
+    double kernel_ms;
+    double gather_ms;
+    double d2h_ms;
+    double total_ms; /* host wall clock of the whole call */
+} rtc_stats;
+
+typedef struct rtc_context rtc_context;
+
+/* ABI version of the loaded library (== RTC_ABI_VERSION). */
+int rtc_abi_version(void);
+
+/* Message for the last non-RTC_OK status returned on this thread. */
+const char* rtc_last_error(void);
+
+/* Number of visible CUDA devices (0 when there is no driver/device). */
+int rtc_device_count(void);
+
+/* A context owns streams, the device scene, frame buffers and pinned staging for the GPUs in
+ * device_ids (n_gpus >= 1; NULL device_ids = devices 0..n_gpus-1).  It amortises set-up over
+ * frames (the reference re-renders per GIF frame: src/lua.rs:34-41).  One thread at a time
+ * per context; different contexts may be used concurrently (Camera::render takes &self,
+ * &World and both are Sync: src/shape.rs:17, src/material.rs:33). */
+int rtc_context_create(const int* device_ids, int n_gpus, rtc_context** out_ctx);
+void rtc_context_destroy(rtc_context* ctx);
+
+/* Scene flattening pass: takes World.shapes in add_shape order (src/shape.rs:661-667) and
+ * World.light, and packs them into structure-of-arrays device buffers on every GPU of the
+ * context.  Replaces what World::intersect (src/shape.rs:677-683) reads per ray. */
+int rtc_scene_upload(rtc_context* ctx, const rtc_light* light, const rtc_shape* shapes, size_t n_shapes);
+
+/* Camera::render / render_async (src/camera.rs:116-160): renders the uploaded scene into the
+ * caller's HOST buffers.  out_rgb: hsize*vsize*3 elements of opts->out_format, row-major
+ * y*hsize+x (Canvas.pixels, src/canvas.rs:43-46); pixels outside the rect are 0 (src/canvas.rs:37-41).
+ * out_hit_mask (nullable): hsize*vsize bytes, bit k set when sub-sample k's primary ray hit
+ * a shape (World::color_at's Some/None, src/shape.rs:704-709).  stats nullable. */
+int rtc_render(rtc_context* ctx, const rtc_camera* cam, const rtc_render_opts* opts, void* out_rgb,
+               uint8_t* out_hit_mask, rtc_stats* stats);
+
+/* Rows of the frame owned by a shard under opts' tiling (the compact buffer height). */
+int rtc_shard_rows(const rtc_camera* cam, const rtc_render_opts* opts);
+
+/* Same render, DEVICE buffers on the context's first GPU, enqueued on `stream`
+ * (a cudaStream_t; NULL = the context's own stream, synchronised before returning).
+ * With shard_count > 1, d_out_rgb / d_out_hit_mask are the shard's compact buffers:
+ * rtc_shard_rows() rows of hsize pixels, owned tiles stacked in frame order.
+ * Counters and kernel_ms in `stats` are only filled when stream == NULL. */
+int rtc_render_device(rtc_context* ctx, const rtc_camera* cam, const rtc_render_opts* opts,
+                      void* d_out_rgb, uint8_t* d_out_hit_mask, void* stream, rtc_stats* stats);
+
+/* De-interleave: d_gathered holds shard_count compact shard buffers back to back, each padded
+ * to `shard_stride_rows` rows (e.g. the output of an NCCL all-gather / gather of
+ * rtc_render_device results); writes the assembled frame (hsize*vsize pixels of out_format)
+ * to d_frame.  `elem_kind` is RTC_OUT_* or -1 for the 1-byte hit mask. */
+int rtc_assemble_device(rtc_context* ctx, const rtc_camera* cam, const rtc_render_opts* opts,
+                        const void* d_gathered, int shard_stride_rows, int elem_kind, void* d_frame,
+                        void* stream);
+
+/* Register-resident FMA micro-benchmark on the context's first GPU: measured non-tensor peak
+ * of the FP32 (precision = RTC_PRECISION_F32_FAST) or FP64 pipe in TFLOP/s (FMA = 2 flops),
+ * used as the roofline denominator beside the formula peak. */
+int rtc_measure_peak_tflops(rtc_context* ctx, int precision, double* out_tflops);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* RTC_B200_H */
