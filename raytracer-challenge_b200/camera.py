@@ -1,0 +1,192 @@
+"""Host-side mirror of ``Camera`` (``src/camera.rs:16-162``) and ``Canvas`` (``src/canvas.rs``),
+plus ``Renderer``: the thin owner of an ``rtc_context`` through which ``camera.render(world)``
+reaches the CUDA kernels.  ``Camera.render`` / ``render_async`` are the drop-in entry points;
+everything they compute happens on the GPU behind the C ABI (no CPU fallback).
+"""
+import ctypes as C
+import math
+
+import numpy as np
+
+from . import ffi
+from .transform import Matrix
+
+
+class Canvas:
+    """src/canvas.rs:16-51: ``pixels`` is row-major ``y*width+x``, 3 x f64 per pixel."""
+
+    def __init__(self, w, h, pixels=None, hit_mask=None, stats=None):
+        self.width, self.height = w, h
+        self.pixels = pixels if pixels is not None else np.zeros((h, w, 3), dtype=np.float64)
+        self.hit_mask = hit_mask
+        self.stats = stats
+        self.gamma = 1.0
+
+    def write_pixel(self, x, y, c):
+        self.pixels[y, x] = tuple(c)
+
+    def get_pixel(self, x, y):
+        from .scene import Color
+        p = self.pixels[y, x]
+        return Color(p[0], p[1], p[2])
+
+    def to_u8(self):
+        """Color::scale's 8-bit rule: ``clamp((c*255.0) as i32, 0, 255)`` — truncation toward
+        zero, saturating, NaN -> 0 (src/color.rs:100-114)."""
+        v = self.pixels.astype(np.float64) * 255.0
+        v = np.nan_to_num(v, nan=0.0, posinf=3e9, neginf=-3e9)
+        return np.clip(np.trunc(v), 0, 255).astype(np.uint8)
+
+    def write_to_file_simple(self, file_name):
+        """PPM P3, one image row per line (src/canvas.rs:86-109)."""
+        u8 = self.to_u8()
+        with open(file_name, "w") as f:
+            f.write(f"P3\n{self.width} {self.height}\n255\n")
+            for row in u8:
+                f.write(" ".join(str(int(v)) for v in row.reshape(-1)))
+                f.write("\n")
+
+
+class Renderer:
+    """Owns one ``rtc_context`` (streams, device scene, frame buffers).  Not thread-safe per
+    instance; create one per thread for concurrent renders (include/rtc.h)."""
+
+    def __init__(self, devices=None):
+        self._lib = ffi.lib()
+        self._ctx = C.c_void_p()
+        if devices is None:
+            devices = [0]
+        ids = (C.c_int * len(devices))(*devices)
+        ffi.check(self._lib.rtc_context_create(ids, len(devices), C.byref(self._ctx)))
+        self.devices = list(devices)
+        self._world_key = None
+
+    def close(self):
+        if self._ctx:
+            self._lib.rtc_context_destroy(self._ctx)
+            self._ctx = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    @property
+    def handle(self):
+        return self._ctx
+
+    def upload(self, world):
+        light, shapes, n = world.flatten()
+        ffi.check(self._lib.rtc_scene_upload(self._ctx, C.byref(light), shapes, n))
+
+    def upload_flat(self, light, shapes, n):
+        ffi.check(self._lib.rtc_scene_upload(self._ctx, C.byref(light), shapes, n))
+
+    @staticmethod
+    def make_opts(precision=ffi.PRECISION_F64_PARITY, rect=ffi.RECT_FULL, max_depth=5,
+                  out_format=ffi.OUT_F64_RGB, shard_index=0, shard_count=1, tile_rows=16):
+        o = ffi.RtcRenderOpts()
+        o.precision, o.rect, o.max_depth, o.out_format = precision, rect, max_depth, out_format
+        o.shard_index, o.shard_count, o.tile_rows = shard_index, shard_count, tile_rows
+        return o
+
+    def render(self, cam_desc, opts, want_mask=True, out=None):
+        """rtc_render into host numpy buffers.  Returns (rgb, hit_mask, stats)."""
+        h, w = cam_desc.vsize, cam_desc.hsize
+        dt = {ffi.OUT_F64_RGB: np.float64, ffi.OUT_F32_RGB: np.float32, ffi.OUT_U8_RGB: np.uint8}[opts.out_format]
+        rgb = out if out is not None else np.empty((h, w, 3), dtype=dt)
+        assert rgb.dtype == dt and rgb.flags["C_CONTIGUOUS"] and rgb.size == h * w * 3
+        mask = np.empty((h, w), dtype=np.uint8) if want_mask else None
+        stats = ffi.RtcStats()
+        ffi.check(self._lib.rtc_render(
+            self._ctx, C.byref(cam_desc), C.byref(opts), rgb.ctypes.data_as(C.c_void_p),
+            mask.ctypes.data_as(C.c_void_p) if mask is not None else None, C.byref(stats)))
+        return rgb, mask, stats
+
+    def render_device(self, cam_desc, opts, d_rgb, d_mask=None, stream=None, stats=None):
+        """rtc_render_device: d_rgb / d_mask are raw device pointers (ints)."""
+        ffi.check(self._lib.rtc_render_device(
+            self._ctx, C.byref(cam_desc), C.byref(opts), C.c_void_p(d_rgb),
+            C.c_void_p(d_mask) if d_mask else None, C.c_void_p(stream) if stream else None,
+            C.byref(stats) if stats is not None else None))
+
+    def assemble_device(self, cam_desc, opts, d_gathered, shard_stride_rows, elem_kind, d_frame, stream=None):
+        ffi.check(self._lib.rtc_assemble_device(
+            self._ctx, C.byref(cam_desc), C.byref(opts), C.c_void_p(d_gathered), shard_stride_rows,
+            elem_kind, C.c_void_p(d_frame), C.c_void_p(stream) if stream else None))
+
+    def shard_rows(self, cam_desc, opts):
+        return self._lib.rtc_shard_rows(C.byref(cam_desc), C.byref(opts))
+
+    def measure_peak_tflops(self, precision):
+        v = C.c_double()
+        ffi.check(self._lib.rtc_measure_peak_tflops(self._ctx, precision, C.byref(v)))
+        return v.value
+
+
+_default_renderer = None
+
+
+def default_renderer():
+    global _default_renderer
+    if _default_renderer is None:
+        _default_renderer = Renderer([0])
+    return _default_renderer
+
+
+class Camera:
+    """src/camera.rs:16-58."""
+    MAX_REFLECTIONS = 5  # :31
+
+    def __init__(self, hsize, vsize, fov):
+        self.hsize, self.vsize, self.fov = int(hsize), int(vsize), float(fov)
+        half_view = math.tan(self.fov / 2.0)
+        aspect = float(self.hsize) / float(self.vsize)
+        if aspect < 1.0:
+            self.half_height = half_view
+            self.half_width = half_view * aspect
+        else:
+            self.half_width = half_view
+            self.half_height = half_view / aspect
+        self.pixel_size = (self.half_width * 2.) / float(self.hsize)
+        self.view_transform_inv = Matrix.identity()
+        self.antialiasing_samples = 1
+
+    @staticmethod
+    def new(hsize, vsize, fov):
+        return Camera(hsize, vsize, fov)
+
+    @staticmethod
+    def new_with_transform(hsize, vsize, fov, m):  # :33-37
+        c = Camera(hsize, vsize, fov)
+        c.view_transform_inv = m.inverse()
+        return c
+
+    def set_samples(self, n):  # :60
+        self.antialiasing_samples = int(n)
+
+    def flatten(self):
+        d = ffi.RtcCamera()
+        d.hsize, d.vsize = self.hsize, self.vsize
+        d.half_width, d.half_height, d.pixel_size = self.half_width, self.half_height, self.pixel_size
+        d.view_inv[:] = self.view_transform_inv.to_row_major()
+        d.samples = self.antialiasing_samples
+        return d
+
+    def _render(self, world, rect, precision, renderer, max_depth):
+        r = renderer or default_renderer()
+        r.upload(world)
+        opts = Renderer.make_opts(precision=precision, rect=rect, max_depth=max_depth)
+        rgb, mask, stats = r.render(self.flatten(), opts)
+        return Canvas(self.hsize, self.vsize, rgb, mask, stats)
+
+    def render(self, world, precision=ffi.PRECISION_F64_PARITY, renderer=None, max_depth=MAX_REFLECTIONS):
+        """Camera::render (:116-126) — including its loop bounds: last row/column stay black."""
+        return self._render(world, ffi.RECT_REFERENCE_RENDER, precision, renderer, max_depth)
+
+    def render_async(self, world, precision=ffi.PRECISION_F64_PARITY, renderer=None, max_depth=MAX_REFLECTIONS):
+        """Camera::render_async (:144-160) — the full image."""
+        return self._render(world, ffi.RECT_FULL, precision, renderer, max_depth)
+
+    render_async1 = render_async  # :128-142

@@ -1,0 +1,471 @@
+// F64 PARITY kernel — compiled with -fmad=false (see __graft_entry__.build) so that no a*b+c is
+// contracted: Rust never fuses, and the hit/miss mask has to be bit-exact.
+// f64 '/' and sqrt() are IEEE-rounded in CUDA by construction.
+//
+// One thread per pixel sample.  The reference's recursion
+//   World::color_at -> shade_hit -> reflected_color / refracted_color -> color_at ...
+// (src/shape.rs:685-766) becomes an explicit per-thread stack of at most max_depth frames,
+// evaluated in the reference's post-order so every colour is combined with the same operations
+// in the same order.
+#include "rtc_common.h"
+
+namespace rtc {
+namespace {
+
+constexpr double kEps = 0.00000001;  // Vector::EPSILON, src/vec.rs:16
+constexpr int kBlockX = 16, kBlockY = 8, kThreads = kBlockX * kBlockY;
+
+struct V3 { double x, y, z; };
+__device__ __forceinline__ V3 mk(double x, double y, double z) { V3 v; v.x = x; v.y = y; v.z = z; return v; }
+__device__ __forceinline__ V3 add(V3 a, V3 b) { return mk(a.x + b.x, a.y + b.y, a.z + b.z); }
+__device__ __forceinline__ V3 sub(V3 a, V3 b) { return mk(a.x - b.x, a.y - b.y, a.z - b.z); }
+__device__ __forceinline__ V3 mul(V3 a, double m) { return mk(a.x * m, a.y * m, a.z * m); }
+__device__ __forceinline__ V3 mulc(V3 a, V3 b) { return mk(a.x * b.x, a.y * b.y, a.z * b.z); }
+__device__ __forceinline__ V3 neg(V3 a) { return mk(-a.x, -a.y, -a.z); }
+__device__ __forceinline__ double dot(V3 a, V3 b) { return a.x * b.x + a.y * b.y + a.z * b.z; }   // src/vec.rs:78
+__device__ __forceinline__ V3 normalize(V3 a) {                                                    // src/vec.rs:65-76
+    double m = sqrt(a.x * a.x + a.y * a.y + a.z * a.z);
+    return mk(a.x / m, a.y / m, a.z / m);
+}
+__device__ __forceinline__ V3 reflect(V3 v, V3 n) { return sub(v, mul(n, 2. * dot(v, n))); }       // src/vec.rs:106
+// Matrix::transform_point / transform_vector, src/transform.rs:107-128 (sums left to right)
+__device__ __forceinline__ V3 xpoint(const double* m, V3 p) {
+    return mk(m[0] * p.x + m[1] * p.y + m[2] * p.z + m[3], m[4] * p.x + m[5] * p.y + m[6] * p.z + m[7],
+              m[8] * p.x + m[9] * p.y + m[10] * p.z + m[11]);
+}
+__device__ __forceinline__ V3 xvec3(const double* m9, V3 p) {
+    return mk(m9[0] * p.x + m9[1] * p.y + m9[2] * p.z, m9[3] * p.x + m9[4] * p.y + m9[5] * p.z,
+              m9[6] * p.x + m9[7] * p.y + m9[8] * p.z);
+}
+
+struct Streams {  // intersect streams, in shared memory when they fit, else global
+    const double2* sph; const int32_t* sph_index; int ns;
+    const double2* pl;  const int32_t* pl_index;  int np;
+};
+
+// Shape::intersect + Sphere::intersect_local (src/shape.rs:23-26, 361-375)
+__device__ __forceinline__ bool sphere_roots(const double2* r, V3 o, V3 d, double& t1, double& t2) {
+    double2 a0 = r[0], a1 = r[1], b0 = r[2], b1 = r[3], c0 = r[4], c1 = r[5];
+    double ox = a0.x * o.x + a0.y * o.y + a1.x * o.z + a1.y;
+    double oy = b0.x * o.x + b0.y * o.y + b1.x * o.z + b1.y;
+    double oz = c0.x * o.x + c0.y * o.y + c1.x * o.z + c1.y;
+    double dx = a0.x * d.x + a0.y * d.y + a1.x * d.z;
+    double dy = b0.x * d.x + b0.y * d.y + b1.x * d.z;
+    double dz = c0.x * d.x + c0.y * d.y + c1.x * d.z;
+    double a = dx * dx + dy * dy + dz * dz;
+    double b = 2. * (dx * ox + dy * oy + dz * oz);
+    double c = (ox * ox + oy * oy + oz * oz) - 1.;
+    double disc = (b * b) - 4. * a * c;
+    if (disc < 0.) return false;
+    double s = sqrt(disc);
+    t1 = (-b - s) / (2. * a);
+    t2 = (-b + s) / (2. * a);
+    return true;
+}
+// Plane::intersect_local (src/shape.rs:462-471)
+__device__ __forceinline__ bool plane_root(const double2* r, V3 o, V3 d, double& t) {
+    double2 b0 = r[0], b1 = r[1];
+    double dy = b0.x * d.x + b0.y * d.y + b1.x * d.z;
+    if (fabs(dy) < kEps) return false;
+    double oy = b0.x * o.x + b0.y * o.y + b1.x * o.z + b1.y;
+    t = -oy / dy;
+    return true;
+}
+
+// World::intersect + Intersections::get_hit (src/shape.rs:677-683, 195-232): the hit is the
+// smallest t >= 0; among equal t the earlier shape (then t1 before t2) wins — the order the
+// reference's stable insertion sort leaves them in.
+__device__ __forceinline__ void take(double t, int idx, double& best_t, int& best_idx) {
+    if (t >= 0.0 && (t < best_t || (t == best_t && idx < best_idx))) { best_t = t; best_idx = idx; }
+}
+__device__ __noinline__ void intersect_world(const Streams& S, V3 o, V3 d, double& best_t, int& best_idx) {
+    best_t = __longlong_as_double(0x7ff0000000000000LL);
+    best_idx = 0x7fffffff;
+    for (int i = 0; i < S.np; ++i) {
+        double t;
+        if (plane_root(S.pl + 2 * i, o, d, t)) take(t, S.pl_index[i], best_t, best_idx);
+    }
+    for (int i = 0; i < S.ns; ++i) {
+        double t1, t2;
+        if (sphere_roots(S.sph + 6 * i, o, d, t1, t2)) {
+            int idx = S.sph_index[i];
+            if (t1 >= 0.0) take(t1, idx, best_t, best_idx);
+            else take(t2, idx, best_t, best_idx);
+        }
+    }
+    if (best_idx == 0x7fffffff) best_idx = -1;
+}
+
+// Intersection::compute_refractive (src/shape.rs:115-141) without materialising the list.
+// Every list entry before the hit has t < 0.  Containers are toggled by world_id, so after the
+// negative entries the container list holds, per id with an ODD number of negative entries, that
+// id's LAST entry, ordered by list position (t, shape index, root).  n1 = refractive index of the
+// last container; then the hit toggles its own id and n2 = the last container after that.
+struct Cont { double t; int ord; int idx; int id; };  // ord = 2*shape_index + root
+__device__ __forceinline__ bool later(const Cont& a, const Cont& b) { return a.t > b.t || (a.t == b.t && a.ord > b.ord); }
+__device__ __forceinline__ void offer(Cont e, Cont& top1, Cont& top2) {
+    if (top1.idx >= 0 && e.id == top1.id) { if (later(e, top1)) top1 = e; return; }
+    if (top2.idx >= 0 && e.id == top2.id) {
+        if (later(e, top2)) top2 = e;
+        if (top1.idx < 0 || later(top2, top1)) { Cont s = top1; top1 = top2; top2 = s; }
+        return;
+    }
+    if (top1.idx < 0 || later(e, top1)) { top2 = top1; top1 = e; }
+    else if (top2.idx < 0 || later(e, top2)) top2 = e;
+}
+__device__ __noinline__ void compute_refractive(const Streams& S, const DevScene64& sc, V3 o, V3 d, int hit_idx,
+                                                double& n1, double& n2) {
+    unsigned parity[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) parity[k] = 0u;
+    // pass A: parity of the number of negative-t entries per world_id
+    for (int i = 0; i < S.np; ++i) {
+        double t;
+        if (plane_root(S.pl + 2 * i, o, d, t) && t < 0.0) {
+            int id = sc.rec[S.pl_index[i]].world_id & 255;
+            parity[id >> 5] ^= 1u << (id & 31);
+        }
+    }
+    for (int i = 0; i < S.ns; ++i) {
+        double t1, t2;
+        if (sphere_roots(S.sph + 6 * i, o, d, t1, t2)) {
+            int id = sc.rec[S.sph_index[i]].world_id & 255;
+            if (t1 < 0.0) parity[id >> 5] ^= 1u << (id & 31);
+            if (t2 < 0.0) parity[id >> 5] ^= 1u << (id & 31);
+        }
+    }
+    // pass B: the last two containers
+    Cont top1, top2;
+    top1.idx = -1; top2.idx = -1; top1.t = top2.t = 0.0; top1.ord = top2.ord = 0; top1.id = top2.id = -1;
+    for (int i = 0; i < S.np; ++i) {
+        double t;
+        if (plane_root(S.pl + 2 * i, o, d, t) && t < 0.0) {
+            int idx = S.pl_index[i];
+            int id = sc.rec[idx].world_id & 255;
+            if ((parity[id >> 5] >> (id & 31)) & 1u) { Cont e; e.t = t; e.ord = 2 * idx; e.idx = idx; e.id = id; offer(e, top1, top2); }
+        }
+    }
+    for (int i = 0; i < S.ns; ++i) {
+        double t1, t2;
+        if (sphere_roots(S.sph + 6 * i, o, d, t1, t2)) {
+            int idx = S.sph_index[i];
+            int id = sc.rec[idx].world_id & 255;
+            if ((parity[id >> 5] >> (id & 31)) & 1u) {
+                if (t1 < 0.0) { Cont e; e.t = t1; e.ord = 2 * idx; e.idx = idx; e.id = id; offer(e, top1, top2); }
+                if (t2 < 0.0) { Cont e; e.t = t2; e.ord = 2 * idx + 1; e.idx = idx; e.id = id; offer(e, top1, top2); }
+            }
+        }
+    }
+    n1 = top1.idx >= 0 ? sc.rec[top1.idx].refractive_index : 1.0;
+    int hid = sc.rec[hit_idx].world_id & 255;
+    bool hit_is_container = (parity[hid >> 5] >> (hid & 31)) & 1u;
+    if (hit_is_container) {
+        if (top1.idx >= 0 && top1.id == hid) n2 = top2.idx >= 0 ? sc.rec[top2.idx].refractive_index : 1.0;
+        else n2 = top1.idx >= 0 ? sc.rec[top1.idx].refractive_index : 1.0;
+    } else {
+        n2 = sc.rec[hit_idx].refractive_index;
+    }
+}
+
+// Pattern::pattern_at for the six patterns (src/material.rs:67-69,97-103,133-135,163-170,198-205,233-241)
+__device__ __forceinline__ V3 pattern_at(const ShadeRec64& r, V3 p) {
+    V3 a = mk(r.pat_a[0], r.pat_a[1], r.pat_a[2]), b = mk(r.pat_b[0], r.pat_b[1], r.pat_b[2]);
+    switch (r.pattern_kind) {
+        case RTC_PATTERN_TEST: return p;
+        case RTC_PATTERN_STRIPE: return fmod(floor(p.x), 2.0) == 0. ? a : b;
+        case RTC_PATTERN_GRADIENT: return add(a, mul(sub(b, a), p.x - floor(p.x)));
+        case RTC_PATTERN_RING: return fmod(floor(sqrt(p.x * p.x + p.y * p.y)), 2.0) == 0.0 ? a : b;
+        case RTC_PATTERN_CHECKER: return fmod(floor(p.x) + floor(p.y) + floor(p.z), 2.0) == 0.0 ? a : b;
+        default: /* GRID: a = base, b = grid lines */
+            return (fabs(p.x - floor(p.x)) < 0.01 || fabs(p.z - floor(p.z)) < 0.01) ? b : a;
+    }
+}
+
+// Material::lighting (src/material.rs:319-361); `point` is over_point (src/shape.rs:688)
+__device__ __forceinline__ V3 lighting(const ShadeRec64& r, V3 light_pos, V3 light_int, V3 point, V3 eye, V3 normal,
+                                       bool in_shadow) {
+    V3 base;
+    if (r.pattern_kind != RTC_PATTERN_NONE) {
+        V3 object_point = xpoint(r.inv, point);            // src/material.rs:41-45
+        V3 pattern_point = xpoint(r.pat_inv, object_point);
+        base = pattern_at(r, pattern_point);
+    } else {
+        base = mk(r.color[0], r.color[1], r.color[2]);
+    }
+    V3 effective = mulc(base, light_int);
+    V3 lightv = normalize(sub(light_pos, point));
+    V3 ambient = mul(effective, r.ambient);
+    if (in_shadow) return ambient;
+    double ldn = dot(lightv, normal);
+    V3 diffuse = mk(0., 0., 0.), specular = mk(0., 0., 0.);
+    if (!(ldn < 0.)) {
+        diffuse = mul(effective, r.diffuse * ldn);
+        V3 rv = reflect(neg(lightv), normal);
+        double rde = dot(rv, eye);
+        if (!(rde <= 0.)) {
+            double factor = pow(rde, r.shininess);
+            specular = mul(light_int, r.specular * factor);
+        }
+    }
+    return add(add(ambient, diffuse), specular);
+}
+
+struct Frame {  // one suspended shade_hit (src/shape.rs:685-700)
+    V3 surface;
+    V3 refl;            // reflected_color once its subtree is done
+    V3 ro, rd;          // pending refraction ray
+    double k_refl, k_transp, reflectance;
+    unsigned char both, has_refr, waiting_refr;
+};
+
+// thread -> sample mapping: a warp covers an 8x4 patch of the sample grid, a block 16x8.
+__device__ __forceinline__ void thread_sample(int& sx, int& sy) {
+    int w = threadIdx.x >> 5, l = threadIdx.x & 31;
+    sx = blockIdx.x * kBlockX + (w & 1) * 8 + (l & 7);
+    sy = blockIdx.y * kBlockY + (w >> 1) * 4 + (l >> 3);
+}
+
+template <bool kInSmem>
+__global__ void __launch_bounds__(kThreads)
+render_f64_kernel(DevScene64 sc, CamParams cam, double* __restrict__ out_f64, float* __restrict__ out_f32,
+                  uint8_t* __restrict__ out_u8, uint8_t* __restrict__ out_hit, Counters* __restrict__ counters) {
+    extern __shared__ double2 smem[];
+    Streams S;
+    S.ns = sc.n_spheres; S.np = sc.n_planes;
+    if (kInSmem) {
+        // stage the intersect streams: coalesced 16-byte loads, one pass per block
+        double2* s_sph = smem;
+        double2* s_pl = s_sph + 6 * sc.n_spheres;
+        int32_t* s_si = reinterpret_cast<int32_t*>(s_pl + 2 * sc.n_planes);
+        int32_t* s_pi = s_si + sc.n_spheres;
+        for (int i = threadIdx.x; i < 6 * sc.n_spheres; i += kThreads) s_sph[i] = sc.sph_rows[i];
+        for (int i = threadIdx.x; i < 2 * sc.n_planes; i += kThreads) s_pl[i] = sc.pl_rows[i];
+        for (int i = threadIdx.x; i < sc.n_spheres; i += kThreads) s_si[i] = sc.sph_index[i];
+        for (int i = threadIdx.x; i < sc.n_planes; i += kThreads) s_pi[i] = sc.pl_index[i];
+        __syncthreads();
+        S.sph = s_sph; S.pl = s_pl; S.sph_index = s_si; S.pl_index = s_pi;
+    } else {
+        S.sph = sc.sph_rows; S.pl = sc.pl_rows; S.sph_index = sc.sph_index; S.pl_index = sc.pl_index;
+    }
+
+    const int ss = cam.samples == 1 ? 1 : 2;  // samples per pixel edge
+    int sx, sy;
+    thread_sample(sx, sy);
+    const int px = sx / ss, pr = sy / ss;     // pixel x, compact shard row
+    const bool in_image = px < (int)cam.hsize && pr < cam.shard_rows;
+    int py = 0;
+    if (in_image) py = cam.shard_count > 1 ? shard_row_to_frame_row(pr, cam.tile_rows, cam.shard_index, cam.shard_count) : pr;
+    const bool active = in_image && px < (int)cam.xlim && py < (int)cam.ylim;
+
+    V3 result = mk(0., 0., 0.);
+    bool primary_hit = false;
+    unsigned n_rays = 0, n_shadow = 0, n_shaded = 0;
+
+    if (active) {
+        // Camera::ray_for_pixel_offset (src/camera.rs:64-76)
+        double xo = ss == 1 ? 0.5 : ((sx & 1) ? 0.75 : 0.25);
+        double yo = ss == 1 ? 0.5 : ((sy & 1) ? 0.75 : 0.25);
+        double xoffset = ((double)px + xo) * cam.pixel_size;
+        double yoffset = ((double)py + yo) * cam.pixel_size;
+        double world_x = cam.half_width - xoffset;
+        double world_y = cam.half_height - yoffset;
+        V3 pixel = xpoint(cam.vinv, mk(world_x, world_y, -1.));
+        V3 origin = xpoint(cam.vinv, mk(0., 0., 0.));
+        V3 ro = origin, rd = normalize(sub(pixel, origin));
+
+        const V3 light_pos = mk(sc.light_pos[0], sc.light_pos[1], sc.light_pos[2]);
+        const V3 light_int = mk(sc.light_int[0], sc.light_int[1], sc.light_int[2]);
+        Frame stack[RTC_MAX_DEPTH];
+        int level = 0;
+        int remaining = cam.max_depth;
+        bool first = true;
+        for (;;) {
+            // ---- World::color_at(ray, remaining)  (src/shape.rs:702-710) ----
+            V3 color;
+            bool descended = false;
+            double t; int idx;
+            ++n_rays;
+            intersect_world(S, ro, rd, t, idx);
+            if (first) { primary_hit = idx >= 0; first = false; }
+            if (idx < 0) {
+                color = mk(0., 0., 0.);  // background_color, src/shape.rs:652
+            } else {
+                const ShadeRec64& rec = sc.rec[idx];
+                // Intersection::compute_vectors + CachedVectors::new (src/shape.rs:144-152, 75-96)
+                V3 point = add(ro, mul(rd, t));
+                V3 eyev = neg(rd);
+                V3 lp = xpoint(rec.inv, point);                                    // Shape::normal_at :34-40
+                V3 ln = rec.kind == RTC_SHAPE_PLANE ? mk(0., 1., 0.) : lp;
+                V3 normal = normalize(xvec3(rec.invt, ln));
+                double n1 = 1.0, n2 = 1.0;
+                if (rec.transparency != 0.0) compute_refractive(S, sc, ro, rd, idx, n1, n2);
+                bool inside = dot(normal, eyev) < 0.0;
+                if (inside) normal = neg(normal);
+                V3 over_point = add(point, mul(normal, kEps));
+                V3 under_point = sub(point, mul(normal, kEps));
+                V3 reflectv = reflect(rd, normal);
+                // World::is_shadowed_by_light (src/shape.rs:716-727)
+                V3 v = sub(light_pos, over_point);
+                double distance = sqrt(v.x * v.x + v.y * v.y + v.z * v.z);
+                V3 sdir = normalize(v);
+                double st; int sidx;
+                ++n_rays; ++n_shadow; ++n_shaded;
+                intersect_world(S, over_point, sdir, st, sidx);
+                bool shadowed = sidx >= 0 && st < distance;
+                V3 surface = lighting(rec, light_pos, light_int, over_point, eyev, normal, shadowed);
+                // shade_hit's children (src/shape.rs:689-699, 729-766)
+                bool want_refl = remaining != 0 && !(rec.reflective <= 0.);
+                bool want_refr = false;
+                V3 fo = mk(0., 0., 0.), fd = mk(0., 0., 0.);
+                if (remaining != 0 && rec.transparency != 0.0) {
+                    double n_ratio = n1 / n2;
+                    double cos_i = dot(eyev, normal);
+                    double sin2_t = (n_ratio * n_ratio) * (1.0 - (cos_i * cos_i));
+                    if (!(sin2_t > 1.0)) {
+                        double cos_t = sqrt(1.0 - sin2_t);
+                        fd = sub(mul(normal, n_ratio * cos_i - cos_t), mul(eyev, n_ratio));
+                        fo = under_point;
+                        want_refr = true;
+                    }
+                }
+                bool both = rec.reflective > 0.0 && rec.transparency > 0.0;
+                double reflectance = 0.0;
+                if (both) {  // World::reflectance, src/shape.rs:768-781
+                    double cs = dot(eyev, normal);
+                    bool tir = false;
+                    if (n1 > n2) {
+                        double n = n1 / n2;
+                        double sin2_t = (n * n) * (1.0 - (cs * cs));
+                        if (sin2_t > 1.0) tir = true;
+                        else cs = sqrt(1.0 - sin2_t);
+                    }
+                    if (tir) reflectance = 1.0;
+                    else {
+                        double q = (n1 - n2) / (n1 + n2);
+                        double r0 = q * q;
+                        double m = 1.0 - cs;
+                        double m2 = m * m;
+                        double m4 = m2 * m2;
+                        reflectance = r0 + (1.0 - r0) * (m4 * m);
+                    }
+                }
+                if (!want_refl && !want_refr) {
+                    // both children are BLACK; surface + 0 is surface
+                    if (both) {
+                        V3 z = mk(0., 0., 0.);
+                        color = add(surface, add(mul(z, reflectance), mul(z, 1.0 - reflectance)));
+                    } else {
+                        color = surface;
+                    }
+                } else {
+                    Frame& f = stack[level];
+                    f.surface = surface;
+                    f.refl = mk(0., 0., 0.);
+                    f.k_refl = rec.reflective; f.k_transp = rec.transparency; f.reflectance = reflectance;
+                    f.both = both; f.has_refr = want_refr; f.ro = fo; f.rd = fd;
+                    if (want_refl) { f.waiting_refr = 0; ro = over_point; rd = reflectv; }
+                    else { f.waiting_refr = 1; ro = fo; rd = fd; }
+                    ++level; --remaining;
+                    descended = true;
+                }
+            }
+            if (descended) continue;
+            // ---- return `color` to the suspended callers ----
+            bool resumed = false;
+            while (level > 0) {
+                Frame& f = stack[level - 1];
+                if (!f.waiting_refr) {
+                    f.refl = mul(color, f.k_refl);                   // reflected_color, :736
+                    if (f.has_refr) {
+                        f.waiting_refr = 1;
+                        ro = f.ro; rd = f.rd;
+                        resumed = true;
+                        break;
+                    }
+                    V3 z = mk(0., 0., 0.);
+                    color = f.both ? add(f.surface, add(mul(f.refl, f.reflectance), mul(z, 1.0 - f.reflectance)))
+                                   : add(add(f.surface, f.refl), z);
+                } else {
+                    V3 refr = mul(color, f.k_transp);               // refracted_color, :765
+                    color = f.both ? add(f.surface, add(mul(f.refl, f.reflectance), mul(refr, 1.0 - f.reflectance)))
+                                   : add(add(f.surface, f.refl), refr);
+                }
+                --level; ++remaining;
+            }
+            if (resumed) continue;
+            result = color;
+            break;
+        }
+    }
+
+    // ---- combine sub-samples (Camera::render_pixel, src/camera.rs:96-113; Color::average_over) ----
+    unsigned hit_bits = primary_hit ? 1u : 0u;
+    if (ss == 2) {
+        const unsigned full = 0xffffffffu;
+        int l = threadIdx.x & 31;
+        double r1 = __shfl_sync(full, result.x, l + 1), g1 = __shfl_sync(full, result.y, l + 1), b1 = __shfl_sync(full, result.z, l + 1);
+        double r2 = __shfl_sync(full, result.x, l + 8), g2 = __shfl_sync(full, result.y, l + 8), b2 = __shfl_sync(full, result.z, l + 8);
+        double r3 = __shfl_sync(full, result.x, l + 9), g3 = __shfl_sync(full, result.y, l + 9), b3 = __shfl_sync(full, result.z, l + 9);
+        unsigned h1 = __shfl_sync(full, hit_bits, l + 1), h2 = __shfl_sync(full, hit_bits, l + 8), h3 = __shfl_sync(full, hit_bits, l + 9);
+        double reds = 0., greens = 0., blues = 0.;
+        reds += result.x; greens += result.y; blues += result.z;
+        reds += r1; greens += g1; blues += b1;
+        reds += r2; greens += g2; blues += b2;
+        reds += r3; greens += g3; blues += b3;
+        result = mk(reds / 4.0, greens / 4.0, blues / 4.0);
+        hit_bits = hit_bits | (h1 << 1) | (h2 << 2) | (h3 << 3);
+    }
+    const bool writer = in_image && (ss == 1 || (((sx | sy) & 1) == 0));
+    if (writer) {
+        size_t p = (size_t)pr * cam.hsize + px;
+        if (cam.out_format == RTC_OUT_F64_RGB) {
+            out_f64[3 * p + 0] = result.x; out_f64[3 * p + 1] = result.y; out_f64[3 * p + 2] = result.z;
+        } else if (cam.out_format == RTC_OUT_F32_RGB) {
+            out_f32[3 * p + 0] = (float)result.x; out_f32[3 * p + 1] = (float)result.y; out_f32[3 * p + 2] = (float)result.z;
+        } else {
+            // Color::scale: clamp((c*255.0) as i32, 0, 255)  (src/color.rs:100-114)
+            double c3[3] = {result.x, result.y, result.z};
+#pragma unroll
+            for (int k = 0; k < 3; ++k) {
+                double s = c3[k] * 255.0;
+                int q = s != s ? 0 : (s >= 2147483647.0 ? 2147483647 : (s <= -2147483648.0 ? (-2147483647 - 1) : (int)s));
+                out_u8[3 * p + k] = (uint8_t)(q < 0 ? 0 : (q > 255 ? 255 : q));
+            }
+        }
+        if (out_hit) out_hit[p] = (uint8_t)hit_bits;
+    }
+    if (counters) {
+        const unsigned full = 0xffffffffu;
+        unsigned r = __reduce_add_sync(full, n_rays), s = __reduce_add_sync(full, n_shadow);
+        unsigned h = __reduce_add_sync(full, n_shaded), ph = __reduce_add_sync(full, primary_hit ? 1u : 0u);
+        if ((threadIdx.x & 31) == 0) {
+            atomicAdd(&counters->rays, (unsigned long long)r);
+            atomicAdd(&counters->shadow_rays, (unsigned long long)s);
+            atomicAdd(&counters->shaded_hits, (unsigned long long)h);
+            atomicAdd(&counters->primary_hits, (unsigned long long)ph);
+        }
+    }
+}
+
+}  // namespace
+
+cudaError_t launch_render_f64(const DevScene64& scene, const CamParams& cam, void* d_rgb, uint8_t* d_hit,
+                              Counters* d_counters, cudaStream_t stream) {
+    const int ss = cam.samples == 1 ? 1 : 2;
+    dim3 grid((cam.hsize * ss + kBlockX - 1) / kBlockX, (cam.shard_rows * ss + kBlockY - 1) / kBlockY);
+    if (grid.x == 0 || grid.y == 0) return cudaSuccess;
+    double* o64 = cam.out_format == RTC_OUT_F64_RGB ? (double*)d_rgb : nullptr;
+    float* o32 = cam.out_format == RTC_OUT_F32_RGB ? (float*)d_rgb : nullptr;
+    uint8_t* o8 = cam.out_format == RTC_OUT_U8_RGB ? (uint8_t*)d_rgb : nullptr;
+    size_t smem = (size_t)scene.n_spheres * (6 * 16 + 4) + (size_t)scene.n_planes * (2 * 16 + 4) + 16;
+    if (smem <= 200 * 1024) {
+        cudaError_t e = cudaFuncSetAttribute(render_f64_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) return e;
+        render_f64_kernel<true><<<grid, kThreads, smem, stream>>>(scene, cam, o64, o32, o8, d_hit, d_counters);
+    } else {
+        render_f64_kernel<false><<<grid, kThreads, 0, stream>>>(scene, cam, o64, o32, o8, d_hit, d_counters);
+    }
+    return cudaGetLastError();
+}
+
+}  // namespace rtc

@@ -1,0 +1,566 @@
+// C ABI of include/rtc.h: context management, the scene-flattening pass (AoS rtc_shape[] ->
+// device SoA intersect streams + shading records), render dispatch over the context's GPUs,
+// row-tile de-interleave, and the FMA peak micro-benchmark.
+// No CPU path exists here: every compute entry point needs a CUDA device.
+#include <algorithm>
+#include <chrono>
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <thread>
+#include <vector>
+#include "rtc_common.h"
+
+using namespace rtc;
+
+namespace {
+
+thread_local std::string g_err;
+
+int fail(int code, const std::string& msg) {
+    g_err = msg;
+    return code;
+}
+#define CUDA_TRY(expr)                                                                              \
+    do {                                                                                            \
+        cudaError_t _e = (expr);                                                                    \
+        if (_e != cudaSuccess)                                                                      \
+            return fail(RTC_ERR_CUDA, std::string(#expr) + ": " + cudaGetErrorString(_e));          \
+    } while (0)
+
+template <typename T>
+struct DevBuf {
+    T* p = nullptr;
+    size_t cap = 0;  // elements
+    cudaError_t ensure(size_t n) {
+        if (n <= cap) return cudaSuccess;
+        if (p) cudaFree(p);
+        p = nullptr;
+        cap = 0;
+        cudaError_t e = cudaMalloc(&p, std::max<size_t>(n, 1) * sizeof(T));
+        if (e == cudaSuccess) cap = n;
+        return e;
+    }
+    void release() {
+        if (p) cudaFree(p);
+        p = nullptr;
+        cap = 0;
+    }
+};
+
+struct DeviceState {
+    int dev = 0;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev_k0 = nullptr, ev_k1 = nullptr, ev_c1 = nullptr;
+    // scene
+    DevBuf<double2> sph64, pl64;
+    DevBuf<float4> sph32, pl32;
+    DevBuf<int32_t> sph_index, pl_index;
+    DevBuf<ShadeRec64> rec64;
+    DevBuf<ShadeRec32> rec32;
+    DevScene64 s64{};
+    DevScene32 s32{};
+    // frame
+    DevBuf<unsigned char> rgb;
+    DevBuf<unsigned char> hit;
+    DevBuf<Counters> counters;
+};
+
+size_t elem_size(int out_format) {
+    return out_format == RTC_OUT_F64_RGB ? 8 : (out_format == RTC_OUT_F32_RGB ? 4 : 1);
+}
+
+}  // namespace
+
+struct rtc_context {
+    std::vector<DeviceState> devs;
+    bool has_scene = false;
+    // pinned staging for D2H (full frame), grown on demand
+    unsigned char* pinned_rgb = nullptr;
+    size_t pinned_rgb_cap = 0;
+    unsigned char* pinned_hit = nullptr;
+    size_t pinned_hit_cap = 0;
+    Counters* pinned_counters = nullptr;  // one per device
+};
+
+namespace {
+
+int ensure_pinned(unsigned char** p, size_t* cap, size_t n) {
+    if (n <= *cap) return RTC_OK;
+    if (*p) cudaFreeHost(*p);
+    *p = nullptr;
+    *cap = 0;
+    CUDA_TRY(cudaMallocHost((void**)p, n));
+    *cap = n;
+    return RTC_OK;
+}
+
+int validate_opts(const rtc_camera* cam, const rtc_render_opts* o) {
+    if (!cam || !o) return fail(RTC_ERR_INVALID_ARG, "null camera or opts");
+    if (cam->hsize == 0 || cam->vsize == 0) return fail(RTC_ERR_INVALID_ARG, "empty image");
+    if ((uint64_t)cam->hsize * cam->vsize > (1ull << 31)) return fail(RTC_ERR_INVALID_ARG, "image too large");
+    if (cam->samples > 1)
+        return fail(RTC_ERR_UNSUPPORTED,
+                    "antialiasing_samples >= 2 draws from rand::thread_rng in the reference (src/camera.rs:84-92); "
+                    "only 1 and 0 (deterministic 2x2) are reproducible");
+    if (o->precision != RTC_PRECISION_F64_PARITY && o->precision != RTC_PRECISION_F32_FAST)
+        return fail(RTC_ERR_INVALID_ARG, "bad precision");
+    if (o->rect != RTC_RECT_REFERENCE_RENDER && o->rect != RTC_RECT_FULL) return fail(RTC_ERR_INVALID_ARG, "bad rect");
+    if (o->max_depth < 0 || o->max_depth > RTC_MAX_DEPTH) return fail(RTC_ERR_INVALID_ARG, "max_depth out of range");
+    if (o->out_format < RTC_OUT_F64_RGB || o->out_format > RTC_OUT_U8_RGB) return fail(RTC_ERR_INVALID_ARG, "bad out_format");
+    if (o->shard_count > 1 && (o->shard_index < 0 || o->shard_index >= o->shard_count || o->tile_rows <= 0))
+        return fail(RTC_ERR_INVALID_ARG, "bad shard spec");
+    return RTC_OK;
+}
+
+CamParams make_cam(const rtc_camera* cam, const rtc_render_opts* o, int shard_index, int shard_count, int tile_rows) {
+    CamParams c{};
+    c.hsize = cam->hsize;
+    c.vsize = cam->vsize;
+    c.half_width = cam->half_width;
+    c.half_height = cam->half_height;
+    c.pixel_size = cam->pixel_size;
+    for (int i = 0; i < 12; ++i) c.vinv[i] = cam->view_inv[i];
+    c.samples = cam->samples;
+    // Camera::render loops 0..vsize-1 x 0..hsize-1 (src/camera.rs:120-121)
+    c.xlim = o->rect == RTC_RECT_REFERENCE_RENDER ? cam->hsize - 1 : cam->hsize;
+    c.ylim = o->rect == RTC_RECT_REFERENCE_RENDER ? cam->vsize - 1 : cam->vsize;
+    c.max_depth = o->max_depth;
+    c.shard_index = shard_count > 1 ? shard_index : 0;
+    c.shard_count = shard_count > 1 ? shard_count : 1;
+    c.tile_rows = tile_rows > 0 ? tile_rows : 16;
+    c.shard_rows = shard_num_rows((int)cam->vsize, c.tile_rows, c.shard_index, c.shard_count);
+    c.out_format = o->out_format;
+    return c;
+}
+
+// ---- scene flattening ---------------------------------------------------------------------------
+struct HostScene {
+    std::vector<double2> sph64, pl64;
+    std::vector<float4> sph32, pl32;
+    std::vector<int32_t> sph_index, pl_index;
+    std::vector<ShadeRec64> rec64;
+    std::vector<ShadeRec32> rec32;
+    int ids_unique = 1;
+};
+
+void mul34(const double* a, const double* b, double* out) {  // (a as 3x4 affine) * (b as 3x4 affine)
+    for (int r = 0; r < 3; ++r)
+        for (int c = 0; c < 4; ++c) {
+            double s = 0.0;
+            for (int k = 0; k < 3; ++k) s += a[4 * r + k] * b[4 * k + c];
+            if (c == 3) s += a[4 * r + 3];
+            out[4 * r + c] = s;
+        }
+}
+
+int flatten(const rtc_shape* shapes, size_t n, HostScene& hs) {
+    bool seen[256] = {false};
+    hs.rec64.resize(n);
+    hs.rec32.resize(n);
+    for (size_t i = 0; i < n; ++i) {
+        const rtc_shape& s = shapes[i];
+        if (s.kind == RTC_SHAPE_CUBE)
+            return fail(RTC_ERR_UNSUPPORTED, "shape " + std::to_string(i) + ": Cube (src/shape.rs:500-630) is not on the device path yet");
+        if (s.kind != RTC_SHAPE_SPHERE && s.kind != RTC_SHAPE_PLANE)
+            return fail(RTC_ERR_INVALID_ARG, "shape " + std::to_string(i) + ": bad kind");
+        if (s.pattern_kind < RTC_PATTERN_NONE || s.pattern_kind > RTC_PATTERN_GRID)
+            return fail(RTC_ERR_INVALID_ARG, "shape " + std::to_string(i) + ": bad pattern kind");
+        if (s.pattern_kind == RTC_PATTERN_NONE && !s.has_color)
+            return fail(RTC_ERR_UNSUPPORTED, "shape " + std::to_string(i) +
+                                                 ": material has neither colour nor pattern (the reference panics, src/material.rs:331)");
+        int id = s.world_id & 255;
+        if (seen[id]) hs.ids_unique = 0;
+        seen[id] = true;
+
+        ShadeRec64& r = hs.rec64[i];
+        std::memset(&r, 0, sizeof r);
+        for (int k = 0; k < 12; ++k) r.inv[k] = s.inv[k];
+        for (int rr = 0; rr < 3; ++rr)
+            for (int cc = 0; cc < 3; ++cc) r.invt[3 * rr + cc] = s.inv_t[4 * rr + cc];
+        for (int k = 0; k < 3; ++k) { r.color[k] = s.color[k]; r.pat_a[k] = s.pat_a[k]; r.pat_b[k] = s.pat_b[k]; }
+        r.ambient = s.ambient; r.diffuse = s.diffuse; r.specular = s.specular; r.shininess = s.shininess;
+        r.reflective = s.reflective; r.transparency = s.transparency; r.refractive_index = s.refractive_index;
+        for (int k = 0; k < 12; ++k) r.pat_inv[k] = s.pat_inv[k];
+        r.kind = s.kind; r.world_id = id; r.pattern_kind = s.pattern_kind;
+
+        ShadeRec32& q = hs.rec32[i];
+        std::memset(&q, 0, sizeof q);
+        for (int k = 0; k < 12; ++k) q.inv[k] = (float)s.inv[k];
+        for (int k = 0; k < 9; ++k) q.invt[k] = (float)r.invt[k];
+        for (int k = 0; k < 3; ++k) { q.color[k] = (float)s.color[k]; q.pat_a[k] = (float)s.pat_a[k]; q.pat_b[k] = (float)s.pat_b[k]; }
+        q.ambient = (float)s.ambient; q.diffuse = (float)s.diffuse; q.specular = (float)s.specular; q.shininess = (float)s.shininess;
+        q.reflective = (float)s.reflective; q.transparency = (float)s.transparency; q.refractive_index = (float)s.refractive_index;
+        double comb[12];
+        mul34(s.pat_inv, s.inv, comb);  // world point -> pattern space in one apply (fast mode only)
+        for (int k = 0; k < 12; ++k) q.pat_inv[k] = (float)comb[k];
+        q.kind = s.kind; q.world_id = id; q.pattern_kind = s.pattern_kind;
+
+        if (s.kind == RTC_SHAPE_SPHERE) {
+            for (int rr = 0; rr < 3; ++rr) {
+                hs.sph64.push_back(make_double2(s.inv[4 * rr + 0], s.inv[4 * rr + 1]));
+                hs.sph64.push_back(make_double2(s.inv[4 * rr + 2], s.inv[4 * rr + 3]));
+                hs.sph32.push_back(make_float4((float)s.inv[4 * rr + 0], (float)s.inv[4 * rr + 1], (float)s.inv[4 * rr + 2], (float)s.inv[4 * rr + 3]));
+            }
+            hs.sph_index.push_back((int32_t)i);
+        } else {
+            hs.pl64.push_back(make_double2(s.inv[4], s.inv[5]));
+            hs.pl64.push_back(make_double2(s.inv[6], s.inv[7]));
+            hs.pl32.push_back(make_float4((float)s.inv[4], (float)s.inv[5], (float)s.inv[6], (float)s.inv[7]));
+            hs.pl_index.push_back((int32_t)i);
+        }
+    }
+    return RTC_OK;
+}
+
+template <typename T>
+cudaError_t upload(DevBuf<T>& b, const std::vector<T>& v, cudaStream_t st) {
+    cudaError_t e = b.ensure(v.size());
+    if (e != cudaSuccess || v.empty()) return e;
+    return cudaMemcpyAsync(b.p, v.data(), v.size() * sizeof(T), cudaMemcpyHostToDevice, st);
+}
+
+}  // namespace
+
+// ---- de-interleave kernel (rtc_assemble_device) --------------------------------------------------
+namespace {
+template <typename U>
+__global__ void assemble_rows_kernel(const U* __restrict__ gathered, U* __restrict__ frame, int vsize, size_t row_units,
+                                     int tile_rows, int shard_count, size_t shard_stride_units) {
+    int y = blockIdx.y;
+    if (y >= vsize) return;
+    int k = y / tile_rows;              // frame tile
+    int shard = k % shard_count;
+    int local_tile = k / shard_count;
+    int compact_row = local_tile * tile_rows + (y - k * tile_rows);
+    const U* src = gathered + (size_t)shard * shard_stride_units + (size_t)compact_row * row_units;
+    U* dst = frame + (size_t)y * row_units;
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < row_units; i += (size_t)gridDim.x * blockDim.x) dst[i] = src[i];
+}
+
+// ---- FMA peak micro-benchmark --------------------------------------------------------------------
+template <typename T>
+__global__ void __launch_bounds__(256) fma_peak_kernel(T* out, int iters, T seed) {
+    T a0 = seed + (T)threadIdx.x, a1 = a0 + (T)1, a2 = a0 + (T)2, a3 = a0 + (T)3, a4 = a0 + (T)4, a5 = a0 + (T)5, a6 = a0 + (T)6, a7 = a0 + (T)7;
+    const T m = (T)0.999, c = (T)0.001;
+    for (int i = 0; i < iters; ++i) {
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+            a0 = fma(a0, m, c); a1 = fma(a1, m, c); a2 = fma(a2, m, c); a3 = fma(a3, m, c);
+            a4 = fma(a4, m, c); a5 = fma(a5, m, c); a6 = fma(a6, m, c); a7 = fma(a7, m, c);
+        }
+    }
+    T s = ((a0 + a1) + (a2 + a3)) + ((a4 + a5) + (a6 + a7));
+    if (s == (T)-12345.678) out[0] = s;  // never true: keeps the chains alive
+}
+
+template <typename T>
+int run_peak(DeviceState& d, double* out_tflops) {
+    T* dummy = nullptr;
+    CUDA_TRY(cudaMalloc(&dummy, sizeof(T)));
+    int sms = 0;
+    CUDA_TRY(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, d.dev));
+    const int blocks = sms * 8, iters = 4096;
+    cudaEvent_t e0, e1;
+    CUDA_TRY(cudaEventCreate(&e0));
+    CUDA_TRY(cudaEventCreate(&e1));
+    float best = 1e30f;
+    for (int rep = 0; rep < 5; ++rep) {
+        CUDA_TRY(cudaEventRecord(e0, d.stream));
+        fma_peak_kernel<T><<<blocks, 256, 0, d.stream>>>(dummy, iters, (T)1.0);
+        CUDA_TRY(cudaEventRecord(e1, d.stream));
+        CUDA_TRY(cudaEventSynchronize(e1));
+        float ms = 0.f;
+        CUDA_TRY(cudaEventElapsedTime(&ms, e0, e1));
+        if (rep > 0) best = std::min(best, ms);
+    }
+    CUDA_TRY(cudaGetLastError());
+    double flops = 2.0 * 64.0 * (double)iters * 256.0 * (double)blocks;
+    *out_tflops = flops / ((double)best * 1e-3) / 1e12;
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+    cudaFree(dummy);
+    return RTC_OK;
+}
+
+void parallel_copy(unsigned char* dst, const unsigned char* src, size_t n) {
+    const size_t kMin = 8u << 20;
+    unsigned hw = std::thread::hardware_concurrency();
+    int nt = (int)std::min<size_t>(std::max(1u, std::min(hw, 16u)), n / kMin + 1);
+    if (nt <= 1) { std::memcpy(dst, src, n); return; }
+    std::vector<std::thread> pool;
+    size_t chunk = (n + nt - 1) / nt;
+    chunk = (chunk + 4095) & ~(size_t)4095;
+    for (int t = 0; t < nt; ++t) {
+        size_t b = (size_t)t * chunk;
+        if (b >= n) break;
+        size_t e = std::min(n, b + chunk);
+        pool.emplace_back([=] { std::memcpy(dst + b, src + b, e - b); });
+    }
+    for (auto& th : pool) th.join();
+}
+
+int launch_on(DeviceState& d, const CamParams& cp, int precision, void* d_rgb, uint8_t* d_hit, Counters* d_counters,
+              cudaStream_t st) {
+    cudaError_t e = precision == RTC_PRECISION_F64_PARITY ? launch_render_f64(d.s64, cp, d_rgb, d_hit, d_counters, st)
+                                                          : launch_render_f32(d.s32, cp, d_rgb, d_hit, d_counters, st);
+    if (e != cudaSuccess) return fail(RTC_ERR_CUDA, std::string("kernel launch: ") + cudaGetErrorString(e));
+    return RTC_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int rtc_abi_version(void) { return RTC_ABI_VERSION; }
+
+const char* rtc_last_error(void) { return g_err.c_str(); }
+
+int rtc_device_count(void) {
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) {
+        cudaGetLastError();
+        return 0;
+    }
+    return n;
+}
+
+int rtc_context_create(const int* device_ids, int n_gpus, rtc_context** out_ctx) {
+    if (!out_ctx || n_gpus < 1) return fail(RTC_ERR_INVALID_ARG, "rtc_context_create: bad arguments");
+    *out_ctx = nullptr;
+    int avail = rtc_device_count();
+    if (avail == 0) return fail(RTC_ERR_NO_DEVICE, "no CUDA device available (there is no CPU fallback)");
+    rtc_context* ctx = new rtc_context();
+    ctx->devs.resize(n_gpus);
+    for (int g = 0; g < n_gpus; ++g) {
+        DeviceState& d = ctx->devs[g];
+        d.dev = device_ids ? device_ids[g] : g;
+        if (d.dev < 0 || d.dev >= avail) {
+            delete ctx;
+            return fail(RTC_ERR_INVALID_ARG, "device id out of range");
+        }
+        cudaError_t e = cudaSetDevice(d.dev);
+        if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&d.stream, cudaStreamNonBlocking);
+        if (e == cudaSuccess) e = cudaEventCreate(&d.ev_k0);
+        if (e == cudaSuccess) e = cudaEventCreate(&d.ev_k1);
+        if (e == cudaSuccess) e = cudaEventCreate(&d.ev_c1);
+        if (e == cudaSuccess) e = d.counters.ensure(1);
+        if (e != cudaSuccess) {
+            std::string m = cudaGetErrorString(e);
+            rtc_context_destroy(ctx);
+            return fail(RTC_ERR_CUDA, "rtc_context_create: " + m);
+        }
+    }
+    cudaError_t e = cudaMallocHost((void**)&ctx->pinned_counters, sizeof(Counters) * n_gpus);
+    if (e != cudaSuccess) {
+        rtc_context_destroy(ctx);
+        return fail(RTC_ERR_CUDA, std::string("rtc_context_create: ") + cudaGetErrorString(e));
+    }
+    *out_ctx = ctx;
+    return RTC_OK;
+}
+
+void rtc_context_destroy(rtc_context* ctx) {
+    if (!ctx) return;
+    for (DeviceState& d : ctx->devs) {
+        cudaSetDevice(d.dev);
+        if (d.stream) cudaStreamSynchronize(d.stream);
+        d.sph64.release(); d.pl64.release(); d.sph32.release(); d.pl32.release();
+        d.sph_index.release(); d.pl_index.release(); d.rec64.release(); d.rec32.release();
+        d.rgb.release(); d.hit.release(); d.counters.release();
+        if (d.ev_k0) cudaEventDestroy(d.ev_k0);
+        if (d.ev_k1) cudaEventDestroy(d.ev_k1);
+        if (d.ev_c1) cudaEventDestroy(d.ev_c1);
+        if (d.stream) cudaStreamDestroy(d.stream);
+    }
+    if (ctx->pinned_rgb) cudaFreeHost(ctx->pinned_rgb);
+    if (ctx->pinned_hit) cudaFreeHost(ctx->pinned_hit);
+    if (ctx->pinned_counters) cudaFreeHost(ctx->pinned_counters);
+    delete ctx;
+}
+
+int rtc_scene_upload(rtc_context* ctx, const rtc_light* light, const rtc_shape* shapes, size_t n_shapes) {
+    if (!ctx || !light || (!shapes && n_shapes)) return fail(RTC_ERR_INVALID_ARG, "rtc_scene_upload: null argument");
+    HostScene hs;
+    int rc = flatten(shapes, n_shapes, hs);
+    if (rc != RTC_OK) return rc;
+    for (DeviceState& d : ctx->devs) {
+        CUDA_TRY(cudaSetDevice(d.dev));
+        CUDA_TRY(upload(d.sph64, hs.sph64, d.stream));
+        CUDA_TRY(upload(d.pl64, hs.pl64, d.stream));
+        CUDA_TRY(upload(d.sph32, hs.sph32, d.stream));
+        CUDA_TRY(upload(d.pl32, hs.pl32, d.stream));
+        CUDA_TRY(upload(d.sph_index, hs.sph_index, d.stream));
+        CUDA_TRY(upload(d.pl_index, hs.pl_index, d.stream));
+        CUDA_TRY(upload(d.rec64, hs.rec64, d.stream));
+        CUDA_TRY(upload(d.rec32, hs.rec32, d.stream));
+        d.s64.n_shapes = d.s32.n_shapes = (int)n_shapes;
+        d.s64.n_spheres = d.s32.n_spheres = (int)hs.sph_index.size();
+        d.s64.n_planes = d.s32.n_planes = (int)hs.pl_index.size();
+        d.s64.ids_unique = d.s32.ids_unique = hs.ids_unique;
+        d.s64.sph_rows = d.sph64.p; d.s64.pl_rows = d.pl64.p; d.s64.sph_index = d.sph_index.p; d.s64.pl_index = d.pl_index.p;
+        d.s64.rec = d.rec64.p;
+        d.s32.sph_rows = d.sph32.p; d.s32.pl_rows = d.pl32.p; d.s32.sph_index = d.sph_index.p; d.s32.pl_index = d.pl_index.p;
+        d.s32.rec = d.rec32.p;
+        for (int k = 0; k < 3; ++k) {
+            d.s64.light_pos[k] = light->position[k]; d.s64.light_int[k] = light->intensity[k];
+            d.s32.light_pos[k] = (float)light->position[k]; d.s32.light_int[k] = (float)light->intensity[k];
+        }
+        // the host vectors die at return: finish the copies now
+        CUDA_TRY(cudaStreamSynchronize(d.stream));
+    }
+    ctx->has_scene = true;
+    return RTC_OK;
+}
+
+int rtc_shard_rows(const rtc_camera* cam, const rtc_render_opts* opts) {
+    if (!cam || !opts) return -1;
+    if (opts->shard_count <= 1) return (int)cam->vsize;
+    return shard_num_rows((int)cam->vsize, opts->tile_rows > 0 ? opts->tile_rows : 16, opts->shard_index, opts->shard_count);
+}
+
+int rtc_render_device(rtc_context* ctx, const rtc_camera* cam, const rtc_render_opts* opts, void* d_out_rgb,
+                      uint8_t* d_out_hit_mask, void* stream, rtc_stats* stats) {
+    if (!ctx || !d_out_rgb) return fail(RTC_ERR_INVALID_ARG, "rtc_render_device: null argument");
+    int rc = validate_opts(cam, opts);
+    if (rc != RTC_OK) return rc;
+    if (!ctx->has_scene) return fail(RTC_ERR_NO_SCENE, "rtc_render_device before rtc_scene_upload");
+    DeviceState& d = ctx->devs[0];
+    CUDA_TRY(cudaSetDevice(d.dev));
+    CamParams cp = make_cam(cam, opts, opts->shard_index, opts->shard_count, opts->tile_rows);
+    if (stream) {
+        return launch_on(d, cp, opts->precision, d_out_rgb, d_out_hit_mask, nullptr, (cudaStream_t)stream);
+    }
+    auto t0 = std::chrono::steady_clock::now();
+    CUDA_TRY(cudaMemsetAsync(d.counters.p, 0, sizeof(Counters), d.stream));
+    CUDA_TRY(cudaEventRecord(d.ev_k0, d.stream));
+    rc = launch_on(d, cp, opts->precision, d_out_rgb, d_out_hit_mask, d.counters.p, d.stream);
+    if (rc != RTC_OK) return rc;
+    CUDA_TRY(cudaEventRecord(d.ev_k1, d.stream));
+    CUDA_TRY(cudaMemcpyAsync(&ctx->pinned_counters[0], d.counters.p, sizeof(Counters), cudaMemcpyDeviceToHost, d.stream));
+    CUDA_TRY(cudaStreamSynchronize(d.stream));
+    if (stats) {
+        std::memset(stats, 0, sizeof *stats);
+        float ms = 0.f;
+        CUDA_TRY(cudaEventElapsedTime(&ms, d.ev_k0, d.ev_k1));
+        const Counters& c = ctx->pinned_counters[0];
+        stats->rays = c.rays; stats->primary_hits = c.primary_hits; stats->shaded_hits = c.shaded_hits; stats->shadow_rays = c.shadow_rays;
+        stats->kernel_launches = 1;
+        stats->kernel_ms = ms;
+        stats->total_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+    }
+    return RTC_OK;
+}
+
+int rtc_assemble_device(rtc_context* ctx, const rtc_camera* cam, const rtc_render_opts* opts, const void* d_gathered,
+                        int shard_stride_rows, int elem_kind, void* d_frame, void* stream) {
+    if (!ctx || !cam || !opts || !d_gathered || !d_frame) return fail(RTC_ERR_INVALID_ARG, "rtc_assemble_device: null argument");
+    if (opts->shard_count < 1 || opts->tile_rows <= 0 || shard_stride_rows <= 0) return fail(RTC_ERR_INVALID_ARG, "rtc_assemble_device: bad shard spec");
+    DeviceState& d = ctx->devs[0];
+    CUDA_TRY(cudaSetDevice(d.dev));
+    cudaStream_t st = stream ? (cudaStream_t)stream : d.stream;
+    size_t row_bytes = elem_kind < 0 ? (size_t)cam->hsize : (size_t)cam->hsize * 3 * elem_size(elem_kind);
+    size_t stride_bytes = row_bytes * (size_t)shard_stride_rows;
+    dim3 grid(8, cam->vsize);
+    bool a16 = row_bytes % 16 == 0 && ((uintptr_t)d_gathered % 16 == 0) && ((uintptr_t)d_frame % 16 == 0);
+    bool a4 = row_bytes % 4 == 0 && ((uintptr_t)d_gathered % 4 == 0) && ((uintptr_t)d_frame % 4 == 0);
+    if (a16)
+        assemble_rows_kernel<uint4><<<grid, 256, 0, st>>>((const uint4*)d_gathered, (uint4*)d_frame, (int)cam->vsize, row_bytes / 16,
+                                                          opts->tile_rows, opts->shard_count, stride_bytes / 16);
+    else if (a4)
+        assemble_rows_kernel<uint32_t><<<grid, 256, 0, st>>>((const uint32_t*)d_gathered, (uint32_t*)d_frame, (int)cam->vsize,
+                                                             row_bytes / 4, opts->tile_rows, opts->shard_count, stride_bytes / 4);
+    else
+        assemble_rows_kernel<unsigned char><<<grid, 256, 0, st>>>((const unsigned char*)d_gathered, (unsigned char*)d_frame,
+                                                                  (int)cam->vsize, row_bytes, opts->tile_rows, opts->shard_count, stride_bytes);
+    CUDA_TRY(cudaGetLastError());
+    if (!stream) CUDA_TRY(cudaStreamSynchronize(st));
+    return RTC_OK;
+}
+
+int rtc_measure_peak_tflops(rtc_context* ctx, int precision, double* out_tflops) {
+    if (!ctx || !out_tflops) return fail(RTC_ERR_INVALID_ARG, "rtc_measure_peak_tflops: null argument");
+    DeviceState& d = ctx->devs[0];
+    CUDA_TRY(cudaSetDevice(d.dev));
+    return precision == RTC_PRECISION_F64_PARITY ? run_peak<double>(d, out_tflops) : run_peak<float>(d, out_tflops);
+}
+
+}  // extern "C"
+
+// ---- rtc_render: host buffers in, host buffers out ------------------------------------------------
+extern "C" int rtc_render(rtc_context* ctx, const rtc_camera* cam, const rtc_render_opts* opts, void* out_rgb,
+                          uint8_t* out_hit_mask, rtc_stats* stats) {
+    if (!ctx || !out_rgb) return fail(RTC_ERR_INVALID_ARG, "rtc_render: null argument");
+    int rc = validate_opts(cam, opts);
+    if (rc != RTC_OK) return rc;
+    if (!ctx->has_scene) return fail(RTC_ERR_NO_SCENE, "rtc_render before rtc_scene_upload");
+    auto t0 = std::chrono::steady_clock::now();
+    const int G = (int)ctx->devs.size();
+    const int tile_rows = opts->tile_rows > 0 ? opts->tile_rows : 16;
+    const size_t px_bytes = 3 * elem_size(opts->out_format);
+    const size_t row_bytes = (size_t)cam->hsize * px_bytes;
+    const size_t frame_bytes = row_bytes * cam->vsize;
+    const size_t mask_bytes = (size_t)cam->hsize * cam->vsize;
+    rc = ensure_pinned(&ctx->pinned_rgb, &ctx->pinned_rgb_cap, frame_bytes);
+    if (rc != RTC_OK) return rc;
+    if (out_hit_mask) {
+        rc = ensure_pinned(&ctx->pinned_hit, &ctx->pinned_hit_cap, mask_bytes);
+        if (rc != RTC_OK) return rc;
+    }
+    // Interleaved row tiles: tile k -> GPU k % G.  Every GPU renders its tiles into a compact
+    // buffer and copies each tile straight to its rows of the pinned frame over its own PCIe link.
+    for (int g = 0; g < G; ++g) {
+        DeviceState& d = ctx->devs[g];
+        CUDA_TRY(cudaSetDevice(d.dev));
+        CamParams cp = make_cam(cam, opts, g, G, tile_rows);
+        CUDA_TRY(d.rgb.ensure((size_t)cp.shard_rows * row_bytes));
+        if (out_hit_mask) CUDA_TRY(d.hit.ensure((size_t)cp.shard_rows * cam->hsize));
+        CUDA_TRY(cudaMemsetAsync(d.counters.p, 0, sizeof(Counters), d.stream));
+        CUDA_TRY(cudaEventRecord(d.ev_k0, d.stream));
+        rc = launch_on(d, cp, opts->precision, d.rgb.p, out_hit_mask ? d.hit.p : nullptr, d.counters.p, d.stream);
+        if (rc != RTC_OK) return rc;
+        CUDA_TRY(cudaEventRecord(d.ev_k1, d.stream));
+        if (G == 1) {
+            CUDA_TRY(cudaMemcpyAsync(ctx->pinned_rgb, d.rgb.p, frame_bytes, cudaMemcpyDeviceToHost, d.stream));
+            if (out_hit_mask) CUDA_TRY(cudaMemcpyAsync(ctx->pinned_hit, d.hit.p, mask_bytes, cudaMemcpyDeviceToHost, d.stream));
+        } else {
+            int n_tiles = ((int)cam->vsize + tile_rows - 1) / tile_rows;
+            int compact_row = 0;
+            for (int t = g; t < n_tiles; t += G) {
+                int r0 = t * tile_rows, r1 = std::min((int)cam->vsize, r0 + tile_rows);
+                CUDA_TRY(cudaMemcpyAsync(ctx->pinned_rgb + (size_t)r0 * row_bytes, d.rgb.p + (size_t)compact_row * row_bytes,
+                                         (size_t)(r1 - r0) * row_bytes, cudaMemcpyDeviceToHost, d.stream));
+                if (out_hit_mask)
+                    CUDA_TRY(cudaMemcpyAsync(ctx->pinned_hit + (size_t)r0 * cam->hsize, d.hit.p + (size_t)compact_row * cam->hsize,
+                                             (size_t)(r1 - r0) * cam->hsize, cudaMemcpyDeviceToHost, d.stream));
+                compact_row += r1 - r0;
+            }
+        }
+        CUDA_TRY(cudaMemcpyAsync(&ctx->pinned_counters[g], d.counters.p, sizeof(Counters), cudaMemcpyDeviceToHost, d.stream));
+        CUDA_TRY(cudaEventRecord(d.ev_c1, d.stream));
+    }
+    rtc_stats st;
+    std::memset(&st, 0, sizeof st);
+    for (int g = 0; g < G; ++g) {
+        DeviceState& d = ctx->devs[g];
+        CUDA_TRY(cudaSetDevice(d.dev));
+        CUDA_TRY(cudaStreamSynchronize(d.stream));
+        float k_ms = 0.f, c_ms = 0.f;
+        CUDA_TRY(cudaEventElapsedTime(&k_ms, d.ev_k0, d.ev_k1));
+        CUDA_TRY(cudaEventElapsedTime(&c_ms, d.ev_k1, d.ev_c1));
+        st.kernel_ms = std::max(st.kernel_ms, (double)k_ms);
+        st.d2h_ms = std::max(st.d2h_ms, (double)c_ms);
+        const Counters& c = ctx->pinned_counters[g];
+        st.rays += c.rays; st.primary_hits += c.primary_hits; st.shaded_hits += c.shaded_hits; st.shadow_rays += c.shadow_rays;
+        st.kernel_launches += 1;
+    }
+    auto t1 = std::chrono::steady_clock::now();
+    parallel_copy((unsigned char*)out_rgb, ctx->pinned_rgb, frame_bytes);
+    if (out_hit_mask) parallel_copy(out_hit_mask, ctx->pinned_hit, mask_bytes);
+    auto t2 = std::chrono::steady_clock::now();
+    st.d2h_ms += std::chrono::duration<double, std::milli>(t2 - t1).count();
+    st.total_ms = std::chrono::duration<double, std::milli>(t2 - t0).count();
+    if (stats) *stats = st;
+    return RTC_OK;
+}

@@ -1,0 +1,116 @@
+// Shared between the C-ABI translation unit (rtc_api.cu) and the kernel translation units
+// (render_f64.cu: parity mode, built with -fmad=false; render_f32.cu: fast mode).
+//
+// Device scene layout ("scene flattening pass", north-star item 1).  World.shapes arrives as an
+// AoS of rtc_shape (include/rtc.h); rtc_scene_upload splits it into
+//   * INTERSECT STREAMS (structure of arrays, one entry per sphere / per plane, in add_shape
+//     order): exactly what the brute-force World::intersect loop (src/shape.rs:677-683) reads for
+//     every ray.  All lanes of a warp walk these arrays in lock step, so they are staged into
+//     shared memory per block with 16-byte vector loads and read back as broadcasts.
+//       spheres: 3 rows x (m0 m1 m2 m3) of the inverse transform  -> 6 x double2 / 3 x float4
+//       planes : row 1 of the inverse only (the plane test uses just o'.y and d'.y,
+//                src/shape.rs:462-471)                             -> 2 x double2 / 1 x float4
+//   * SHADING RECORDS (one 16-byte-aligned record per shape, original order): inverse,
+//     inverse-transpose 3x3, material scalars, pattern.  Gathered by individual lanes at hit time
+//     (one record per hit), so they stay in global memory behind L1/L2.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include "../../include/rtc.h"
+
+namespace rtc {
+
+// ---- f64 (parity) layout ----------------------------------------------------------------------
+struct __align__(16) ShadeRec64 {
+    double inv[12];     // rows 0..2 of Shape::get_transform_inverse()            (src/shape.rs:30)
+    double invt[9];     // upper-left 3x3 of get_transform_inverse_transpose()    (src/shape.rs:32)
+    double color[3];    // Material.color                                         (src/material.rs:246)
+    double ambient, diffuse, specular, shininess;
+    double reflective, transparency, refractive_index;
+    double pat_inv[12]; // Pattern::get_transform_inverse()                       (src/material.rs:37)
+    double pat_a[3], pat_b[3];
+    int32_t kind;         // RTC_SHAPE_*
+    int32_t world_id;     // u8 in the reference (src/shape.rs:287)
+    int32_t pattern_kind; // RTC_PATTERN_*
+    int32_t pad;
+};
+
+struct DevScene64 {
+    int n_shapes, n_spheres, n_planes, ids_unique;
+    const double2* sph_rows;   // [n_spheres][6]: r0.xy r0.zw r1.xy r1.zw r2.xy r2.zw
+    const int32_t* sph_index;  // [n_spheres] original shape index
+    const double2* pl_rows;    // [n_planes][2]: r1.xy r1.zw
+    const int32_t* pl_index;   // [n_planes]
+    const ShadeRec64* rec;     // [n_shapes]
+    double light_pos[3];
+    double light_int[3];
+};
+
+// ---- f32 (fast) layout ------------------------------------------------------------------------
+struct __align__(16) ShadeRec32 {
+    float inv[12];
+    float invt[9];
+    float color[3];
+    float ambient, diffuse, specular, shininess;
+    float reflective, transparency, refractive_index;
+    float pat_inv[12];  // pattern_inv * shape_inv pre-multiplied on the host (one apply per lookup)
+    float pat_a[3], pat_b[3];
+    int32_t kind, world_id, pattern_kind, flags;
+};
+
+struct DevScene32 {
+    int n_shapes, n_spheres, n_planes, ids_unique;
+    const float4* sph_rows;    // [n_spheres][3]
+    const int32_t* sph_index;
+    const float4* pl_rows;     // [n_planes]
+    const int32_t* pl_index;
+    const ShadeRec32* rec;
+    float light_pos[3];
+    float light_int[3];
+};
+
+// ---- per-launch parameters --------------------------------------------------------------------
+struct CamParams {
+    uint32_t hsize, vsize;
+    double half_width, half_height, pixel_size;
+    double vinv[12];  // rows 0..2 of view_transform_inv (src/camera.rs:25)
+    uint32_t samples; // 1 or 0 (= deterministic 2x2)
+    uint32_t xlim, ylim;  // rect: pixels with x >= xlim or y >= ylim are written black
+    int32_t max_depth;
+    // row-tile sharding: tile k (rows [k*tile_rows, ...)) belongs to shard k % shard_count
+    int32_t shard_index, shard_count, tile_rows;
+    int32_t shard_rows;   // rows in this shard's compact buffer
+    int32_t out_format;   // RTC_OUT_*
+};
+
+struct Counters {
+    unsigned long long rays, primary_hits, shaded_hits, shadow_rays;
+};
+
+// Map a compact shard row to the frame row (tiles stacked in frame order).
+__host__ __device__ inline int shard_row_to_frame_row(int r, int tile_rows, int shard_index, int shard_count) {
+    int t = r / tile_rows;                 // shard-local tile
+    int in = r - t * tile_rows;
+    return (t * shard_count + shard_index) * tile_rows + in;
+}
+
+// Rows owned by `shard_index` in a frame of vsize rows.
+__host__ __device__ inline int shard_num_rows(int vsize, int tile_rows, int shard_index, int shard_count) {
+    if (shard_count <= 1) return vsize;
+    int n_tiles = (vsize + tile_rows - 1) / tile_rows;
+    int rows = 0;
+    for (int t = shard_index; t < n_tiles; t += shard_count) {
+        int r0 = t * tile_rows;
+        int r1 = r0 + tile_rows < vsize ? r0 + tile_rows : vsize;
+        rows += r1 - r0;
+    }
+    return rows;
+}
+
+// kernel launchers implemented in the kernel TUs
+cudaError_t launch_render_f64(const DevScene64& scene, const CamParams& cam, void* d_rgb, uint8_t* d_hit,
+                              Counters* d_counters, cudaStream_t stream);
+cudaError_t launch_render_f32(const DevScene32& scene, const CamParams& cam, void* d_rgb, uint8_t* d_hit,
+                              Counters* d_counters, cudaStream_t stream);
+
+}  // namespace rtc
