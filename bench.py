@@ -1,0 +1,335 @@
+#!/usr/bin/env python
+"""bench.py — Mrays/s and ms/frame of the Camera::render hot path on the 4K reflect/refract scene.
+
+  python bench.py --gpus N --steps K --warmup W            (N>1: launched by torchrun, one rank per GPU)
+  python bench.py --impl reference ...                     (the reference's CPU path: the oracle port)
+
+A "step" is one frame: config C3 of BASELINE.json — the chapter-11 reflect/refract room
+(jamis.yml) at 3840x2160, 1 sample per pixel, recursion depth 5 — rendered by the f32 fast kernel
+(the f64 parity kernel is timed beside it and reported under "f64").  A "ray" is one
+World::intersect call (primary + reflected + refracted + shadow); the per-frame ray
+count is deterministic and taken from the f64 parity kernel, whose counters the GPU tests pin to
+the oracle's.  Prints ONE JSON line on rank 0.
+"""
+import argparse
+import ctypes as C
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+WORKLOAD = "C3: reflect-refract room (jamis.yml, 13 shapes), 3840x2160, 1 spp, depth 5"
+W, H, DEPTH = 3840, 2160, 5
+N_SPHERES, N_PLANES = 7, 6
+FLOP_PER_RAY = 54 * N_SPHERES + 13 * N_PLANES   # algorithmic flops per World::intersect
+FLOP_PER_SHADED_HIT = 150
+FP32_FORMULA_PEAK = 148 * 128 * 2 * 1.965e9 / 1e12  # TFLOP/s, non-tensor, at clocks.max.sm
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons DURING the timed region (B200_PROFILING.md recipe)."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index=0):
+        self.rows, self.proc, self.gpu = [], None, gpu_index
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-lms", "100", "-i", str(self.gpu)], stdout=subprocess.PIPE, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append((time.time(), [c.strip() for c in line.split(",")]))
+
+    def stop(self, t0, t1):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        rows = [r for t, r in self.rows if t0 - 0.05 <= t <= t1 + 0.15 and len(r) >= 9] or [r for _, r in self.rows if len(r) >= 9]
+        if not rows:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["no samples"]}
+        sm = sorted(float(r[1]) for r in rows)
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = sorted({n for r in rows for n, v in zip(names, r[5:9]) if v.lower().startswith("active")})
+        return {"sm_mhz": sm[len(sm) // 2], "sm_max_mhz": float(rows[0][2]), "reasons": reasons, "samples": len(rows),
+                "power_w_max": max(float(r[3]) for r in rows)}
+
+
+def measured_peaks():
+    try:
+        return json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        return {}
+
+
+def cpu_info():
+    model = "unknown"
+    try:
+        for line in open("/proc/cpuinfo"):
+            if line.startswith("model name"):
+                model = line.split(":", 1)[1].strip()
+                break
+    except Exception:
+        pass
+    return model, os.cpu_count() or 1
+
+
+def oracle_sample(threads, target_seconds=12.0):
+    """Times the oracle (the CPU restatement of the reference's Camera::render path) on a bounded
+    sample of the SAME workload: a pixel lattice of the 4K frame sized to ~target_seconds of CPU work."""
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import numpy as np
+    import orc
+    import rtc_b200 as rtc
+    world = rtc.scenes.reflect_refract_scene()
+    cam = rtc.scenes.reflect_refract_camera(W, H)
+    ow = orc.OracleWorld(world)
+    # calibrate on a coarse lattice, then size the real sample
+    idx = orc.lattice(W, H, step=64, n_random=0)
+    _, _, c0 = ow.render(cam, threads=threads, pixels=idx)
+    rate = c0.rays / max(c0.seconds, 1e-6)
+    rays_per_px = c0.rays / idx.size
+    n_px = int(min(W * H, max(idx.size, rate * target_seconds / rays_per_px)))
+    step = max(1, int((W * H / n_px) ** 0.5))
+    idx = orc.lattice(W, H, step=step, n_random=0)
+    _, _, c = ow.render(cam, threads=threads, pixels=idx)
+    return {"mrays_per_s": c.rays / c.seconds / 1e6, "rays": int(c.rays), "pixels": int(idx.size), "seconds": c.seconds,
+            "ms_per_frame_extrapolated": (W * H / idx.size) * c.seconds * 1e3,
+            "sample": f"every {step}th pixel in x and y of the {W}x{H} frame ({idx.size} px, {c.rays} rays, {c.seconds:.1f} s)"}
+
+
+def run_reference(args):
+    """--impl reference: the reference's own CPU implementation of the path.  The Rust crate cannot
+    be built here (no cargo/rustc), so this is the oracle port — a line-by-line C++
+    restatement pinned by the reference's unit-test known answers — on all host threads
+    (= Camera::render_async's rayon pool, src/camera.rs:144-160)."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return 0
+    model, cores = cpu_info()
+    per_step = max(1.0, min(15.0, 150.0 / max(1, args.steps + args.warmup)))
+    for _ in range(args.warmup):
+        oracle_sample(cores, per_step)
+    runs = [oracle_sample(cores, per_step) for _ in range(args.steps)]
+    rays = sum(r["rays"] for r in runs)
+    secs = sum(r["seconds"] for r in runs)
+    value = rays / secs / 1e6
+    line = {
+        "impl": "reference", "metric": "Mrays/s", "value": value, "unit": "Mrays/s", "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": secs / max(1, args.steps) * 1e3,
+        "ms_per_frame_extrapolated": sum(r["ms_per_frame_extrapolated"] for r in runs) / len(runs),
+        "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": WORKLOAD, "timing": "host wall clock around Camera::render_pixel over a pixel lattice"},
+        "cpu_baseline": {"value": value, "unit": "Mrays/s", "cores": cores, "kind": "port", "cpu": model,
+                         "sample": runs[-1]["sample"]},
+        "e2e": {"value": value, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+    return 0
+
+
+def run_gpu(args):
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+    import rtc_b200 as rtc
+    from rtc_b200 import ffi
+
+    rank = int(os.environ.get("RANK", "0"))
+    world_size = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    N = world_size
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device (the render path has no CPU fallback)")
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if N > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    r = rtc.Renderer([local_rank])
+    world = rtc.scenes.reflect_refract_scene()
+    cam = rtc.scenes.reflect_refract_camera(W, H)
+    flat = world.flatten()
+    camd = cam.flatten()
+    r.upload_flat(*flat)
+    TILE = 16
+    mk = lambda prec, fmt: rtc.Renderer.make_opts(precision=prec, rect=ffi.RECT_FULL, max_depth=DEPTH, out_format=fmt,
+                                                  shard_index=rank, shard_count=N, tile_rows=TILE)
+    o32 = mk(ffi.PRECISION_F32_FAST, ffi.OUT_F32_RGB)
+    o64 = mk(ffi.PRECISION_F64_PARITY, ffi.OUT_F64_RGB)
+    o0 = rtc.Renderer.make_opts(shard_index=0, shard_count=N, tile_rows=TILE)
+    stride_rows = r.shard_rows(camd, o0)          # shard 0 owns the most rows
+    my_rows = r.shard_rows(camd, o32)
+    d32 = torch.zeros((stride_rows, W, 3), dtype=torch.float32, device=dev)
+    d64 = torch.zeros((stride_rows, W, 3), dtype=torch.float64, device=dev)
+    g32 = torch.empty((N, stride_rows, W, 3), dtype=torch.float32, device=dev) if (N > 1 and rank == 0) else None
+    g64 = torch.empty((N, stride_rows, W, 3), dtype=torch.float64, device=dev) if (N > 1 and rank == 0) else None
+    f32 = torch.empty((H, W, 3), dtype=torch.float32, device=dev) if (N > 1 and rank == 0) else None
+    f64 = torch.empty((H, W, 3), dtype=torch.float64, device=dev) if (N > 1 and rank == 0) else None
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)  # > 126 MB L2
+    stream = torch.cuda.current_stream().cuda_stream
+
+    def sync_all():
+        if N > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def frame(opts, shard, gathered, full, fmt):
+        """One frame: render this rank's interleaved row tiles, NCCL-gather to rank 0, de-interleave."""
+        r.render_device(camd, opts, shard.data_ptr(), None, stream)
+        if N > 1:
+            dist.gather(shard, [gathered[i] for i in range(N)] if rank == 0 else None, dst=0)
+            if rank == 0:
+                r.assemble_device(camd, opts, gathered.data_ptr(), stride_rows, fmt, full.data_ptr(), stream)
+
+    def timed(fn, steps, warmup):
+        for _ in range(warmup):
+            fn()
+        sync_all()
+        ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
+        t0 = time.time()
+        for a, b in ev:
+            flush.zero_()            # L2 flush between timed iterations, outside the event pair
+            a.record()
+            fn()
+            b.record()
+        sync_all()
+        t1 = time.time()
+        ms = torch.tensor([a.elapsed_time(b) for a, b in ev], dtype=torch.float64, device=dev)
+        if N > 1:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)   # max over ranks, per step
+        return ms.cpu().numpy(), t0, t1
+
+    # deterministic work counts of the frame, from the f64 parity kernel's counters (== the oracle's)
+    st = ffi.RtcStats()
+    r.render_device(camd, o64, d64.data_ptr(), None, None, st)
+    counts = torch.tensor([st.rays, st.shaded_hits, st.shadow_rays, st.primary_hits], dtype=torch.float64, device=dev)
+    st32 = ffi.RtcStats()
+    r.render_device(camd, o32, d32.data_ptr(), None, None, st32)
+    counts32 = torch.tensor([st32.rays], dtype=torch.float64, device=dev)
+    if N > 1:
+        dist.all_reduce(counts)
+        dist.all_reduce(counts32)
+    rays, shaded = float(counts[0]), float(counts[1])
+    flops = rays * FLOP_PER_RAY + shaded * FLOP_PER_SHADED_HIT
+
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+    ms32, t0, t1 = timed(lambda: frame(o32, d32, g32, f32, ffi.OUT_F32_RGB), args.steps, max(3, args.warmup))
+    clocks = sampler.stop(t0, t1) if rank == 0 else None
+    total_ms = float(ms32.sum())
+    ms_per_step = total_ms / args.steps
+    value = rays * args.steps / (total_ms * 1e-3) / 1e6
+    # kernel alone (this rank's shard), for the roofline
+    k32, _, _ = timed(lambda: r.render_device(camd, o32, d32.data_ptr(), None, stream), args.steps, 3)
+    kernel_ms = float(k32.mean())
+    n64 = max(1, min(args.steps, 5))
+    ms64, _, _ = timed(lambda: frame(o64, d64, g64, f64, ffi.OUT_F64_RGB), n64, 3)
+    k64, _, _ = timed(lambda: r.render_device(camd, o64, d64.data_ptr(), None, stream), n64, 3)
+
+    # ---- e2e: the public API with HOST buffers: scene H2D + render + Canvas (f64) D2H every step ----
+    oe = rtc.Renderer.make_opts(precision=ffi.PRECISION_F32_FAST, rect=ffi.RECT_FULL, max_depth=DEPTH, out_format=ffi.OUT_F64_RGB)
+    h2d = C.sizeof(ffi.RtcShape) * flat[2] + C.sizeof(ffi.RtcLight) + C.sizeof(ffi.RtcCamera)
+    e2e_steps = max(1, min(args.steps, 10))
+    if N == 1:
+        host = np.zeros((H, W, 3), dtype=np.float64)
+
+        def e2e_step():
+            r.upload_flat(*flat)
+            r.render(camd, oe, want_mask=False, out=host)
+        d2h = host.nbytes
+    else:
+        oeN = mk(ffi.PRECISION_F32_FAST, ffi.OUT_F64_RGB)
+        host_t = torch.empty((H, W, 3), dtype=torch.float64).pin_memory() if rank == 0 else None
+
+        def e2e_step():
+            r.upload_flat(*flat)
+            frame(oeN, d64, g64, f64, ffi.OUT_F64_RGB)
+            if rank == 0:
+                host_t.copy_(f64, non_blocking=True)
+            torch.cuda.synchronize()
+        d2h = H * W * 3 * 8
+    for _ in range(2):
+        e2e_step()
+    sync_all()
+    e2e_times = []
+    for _ in range(e2e_steps):
+        sync_all()
+        a = time.perf_counter()
+        e2e_step()
+        torch.cuda.synchronize()
+        e2e_times.append(time.perf_counter() - a)
+    e2e_t = torch.tensor(e2e_times, dtype=torch.float64, device=dev)
+    if N > 1:
+        dist.all_reduce(e2e_t, op=dist.ReduceOp.MAX)
+    e2e_ms = float(e2e_t.mean()) * 1e3
+
+    if rank == 0:
+        peaks = measured_peaks()
+        p32 = r.measure_peak_tflops(ffi.PRECISION_F32_FAST)
+        p64 = r.measure_peak_tflops(ffi.PRECISION_F64_PARITY)
+        my_share = my_rows / H
+        achieved = flops * my_share / (kernel_ms * 1e-3) / 1e12
+        line = {
+            "metric": "Mrays/s", "value": value, "unit": "Mrays/s", "n_gpus": N, "steps": args.steps, "warmup": max(3, args.warmup),
+            "ms_per_step": ms_per_step, "ms_per_frame": ms_per_step, "higher_is_better": True, "scaling": "strong",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": WORKLOAD, "rays_per_frame": int(rays), "rays_per_frame_f32_kernel": int(counts32[0]),
+                       "shaded_hits_per_frame": int(shaded), "l2": "256 MB buffer rewritten between timed iterations (outside the events)",
+                       "parallelism": f"interleaved {TILE}-row tiles over {N} GPU(s)" + (", NCCL gather to rank 0 + de-interleave" if N > 1 else ""),
+                       "timing": "CUDA events per step on the launch stream, max over ranks"},
+            "roofline": {"bound": "fp32_non_tensor", "achieved": achieved, "peak": p32, "unit": "TFLOP/s", "frac": achieved / p32,
+                         "traffic": None, "peak_source": "FFMA micro-benchmark on this GPU in this run (rtc_measure_peak_tflops)",
+                         "peak_formula": FP32_FORMULA_PEAK, "frac_of_formula": achieved / FP32_FORMULA_PEAK,
+                         "algorithmic_gflop_per_frame": flops / 1e9, "kernel_ms": kernel_ms, "kernel": "render_f32_kernel",
+                         "hbm_gbs_measured_peak": peaks.get("hbm_gbs")},
+            "f64": {"ms_per_frame": float(ms64.mean()), "mrays_per_s": rays / (float(ms64.mean()) * 1e-3) / 1e6,
+                    "kernel_ms": float(k64.mean()), "tflops_algorithmic": flops * my_share / (float(k64.mean()) * 1e-3) / 1e12,
+                    "peak_dfma_tflops_measured": p64},
+            "e2e": {"value": rays / (e2e_ms * 1e-3) / 1e6, "unit": "Mrays/s", "ms_per_frame": e2e_ms, "h2d_bytes_per_step": int(h2d),
+                    "d2h_bytes_per_step": int(d2h), "steps": e2e_steps,
+                    "path": "rtc_scene_upload + rtc_render (f32 fast, F64_RGB Canvas layout) into a host buffer" if N == 1 else
+                            "rtc_scene_upload + rtc_render_device shards + NCCL gather + de-interleave + D2H on rank 0"},
+            "gpu_launches": args.steps * (1 if N == 1 else 2),
+            "clocks": clocks,
+        }
+        if N == 1 and not args.no_cpu_baseline:
+            model, cores = cpu_info()
+            s = oracle_sample(cores, 12.0)
+            line["cpu_baseline"] = {"value": s["mrays_per_s"], "unit": "Mrays/s", "cores": cores, "kind": "port", "cpu": model,
+                                    "sample": s["sample"], "ms_per_frame_extrapolated": s["ms_per_frame_extrapolated"]}
+        print(json.dumps(line), flush=True)
+    if N > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    return 0
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        return run_reference(args)
+    return run_gpu(args)
+
+
+if __name__ == "__main__":
+    sys.exit(main())

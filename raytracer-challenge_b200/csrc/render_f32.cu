@@ -1,7 +1,491 @@
-// F32 FAST kernel — placeholder translation unit until the fast path lands (next commit).
+// F32 FAST kernel (compiled with --use_fast_math; FMA contraction on).
+//
+// Same path as render_f64.cu — ray_for_pixel, World::intersect over every shape, hit selection,
+// prepare_computations, Phong lighting with a shadow ray, reflection + refraction with Schlick
+// (src/camera.rs:64-114, src/shape.rs:677-781, src/material.rs:319-361) — re-designed for
+// throughput instead of bit parity:
+//   * shape tests are done in WORLD space (planes as n.x+w, similarity-transformed spheres as
+//     centre/radius; only genuinely affine spheres go through their inverse), so the brute-force
+//     loop is almost pure FFMA;
+//   * the recursion is unrolled into path weights: every factor the reference multiplies a child
+//     colour by (reflectiveness, transparency, Schlick reflectance; src/shape.rs:692-699,736,765)
+//     is a scalar, so colour = sum over tree nodes of (path weight x surface colour) and a node
+//     needs no frame — only pending refraction rays sit on a small per-lane stack;
+//   * persistent warps: each lane is a little state machine doing exactly ONE World::intersect per
+//     loop iteration (a radiance ray or the shadow ray of its pending hit), and lanes that run out
+//     of rays pull the next pixel from the warp's batch with a ballot/popc rank, so reflected,
+//     refracted and shadow rays of different pixels share the same brute-force loop instead of
+//     idling each other (north-star item 2);
+//   * EPSILON: the reference offsets over_point/under_point by 1e-8, below f32 resolution
+//     (SURVEY.md F4).  Fast mode uses kEps32 = 1e-4 (the book's value) for the same purpose.
 #include "rtc_common.h"
+
 namespace rtc {
-cudaError_t launch_render_f32(const DevScene32&, const CamParams&, void*, uint8_t*, Counters*, cudaStream_t) {
-    return cudaErrorNotSupported;
+namespace {
+
+constexpr float kEps32 = 1e-4f;
+constexpr float kPlaneEps = 1e-8f;  // abs(d.y) < EPSILON -> parallel (src/shape.rs:463)
+constexpr int kThreads = 128;
+constexpr int kBatch = 128;         // pixels a warp claims per atomic: one 16x8 tile
+constexpr int kTileX = 16, kTileY = 8;
+constexpr int kMaxStack = RTC_MAX_DEPTH;
+
+struct F3 { float x, y, z; };
+__device__ __forceinline__ F3 mk(float x, float y, float z) { F3 v; v.x = x; v.y = y; v.z = z; return v; }
+__device__ __forceinline__ F3 operator+(F3 a, F3 b) { return mk(a.x + b.x, a.y + b.y, a.z + b.z); }
+__device__ __forceinline__ F3 operator-(F3 a, F3 b) { return mk(a.x - b.x, a.y - b.y, a.z - b.z); }
+__device__ __forceinline__ F3 operator*(F3 a, float m) { return mk(a.x * m, a.y * m, a.z * m); }
+__device__ __forceinline__ F3 operator*(F3 a, F3 b) { return mk(a.x * b.x, a.y * b.y, a.z * b.z); }
+__device__ __forceinline__ float dot(F3 a, F3 b) { return fmaf(a.z, b.z, fmaf(a.y, b.y, a.x * b.x)); }
+__device__ __forceinline__ F3 fma3(F3 a, float m, F3 c) { return mk(fmaf(a.x, m, c.x), fmaf(a.y, m, c.y), fmaf(a.z, m, c.z)); }
+__device__ __forceinline__ F3 xyz(float4 v) { return mk(v.x, v.y, v.z); }
+__device__ __forceinline__ float row4(float4 r, F3 p) { return fmaf(r.z, p.z, fmaf(r.y, p.y, fmaf(r.x, p.x, r.w))); }
+__device__ __forceinline__ float row3(float4 r, F3 p) { return fmaf(r.z, p.z, fmaf(r.y, p.y, r.x * p.x)); }
+
+struct Streams32 {
+    const float4* planes; const int32_t* pl_index; int np;
+    const float4* usph;   const int32_t* us_index; int nu;
+    const float4* gsph;   const int32_t* gs_index; int ng;
+};
+
+// World::intersect + get_hit for one ray: nearest t in [0, best_t).  best_t comes in as the
+// upper bound (+inf for radiance rays, 1 for shadow rays whose direction is light - point, which
+// is the reference's `h.t < distance` in units of the unnormalised direction, src/shape.rs:716-727).
+// `hit` is a position in the concatenated stream order planes | uniform spheres | general spheres.
+__device__ __forceinline__ void intersect32(const Streams32& S, F3 o, F3 d, float& best_t, int& hit) {
+    hit = -1;
+    const float a = dot(d, d);
+    const float inv_a = __frcp_rn(a);
+#pragma unroll 2
+    for (int i = 0; i < S.np; ++i) {                     // Plane::intersect_local, src/shape.rs:462-471
+        float4 pl = S.planes[i];
+        float dy = row3(pl, d);
+        float oy = row4(pl, o);
+        float t = -oy * __frcp_rn(dy);
+        if (fabsf(dy) >= kPlaneEps && t >= 0.f && t < best_t) { best_t = t; hit = i; }
+    }
+#pragma unroll 2
+    for (int i = 0; i < S.nu; ++i) {                     // Sphere::intersect_local, src/shape.rs:361-375
+        float4 sp = S.usph[i];
+        F3 L = mk(o.x - sp.x, o.y - sp.y, o.z - sp.z);
+        float b = dot(d, L);                             // half of the reference's b
+        float c = fmaf(L.z, L.z, fmaf(L.y, L.y, fmaf(L.x, L.x, -sp.w)));
+        float disc = fmaf(b, b, -a * c);
+        float s = sqrtf(fmaxf(disc, 0.f));
+        float t1 = (-b - s) * inv_a, t2 = (s - b) * inv_a;
+        float t = t1 >= 0.f ? t1 : t2;
+        if (disc >= 0.f && t >= 0.f && t < best_t) { best_t = t; hit = S.np + i; }
+    }
+    for (int i = 0; i < S.ng; ++i) {                     // Shape::intersect: ray.transform(inverse) first
+        float4 r0 = S.gsph[3 * i], r1 = S.gsph[3 * i + 1], r2 = S.gsph[3 * i + 2];
+        F3 lo = mk(row4(r0, o), row4(r1, o), row4(r2, o));
+        F3 ld = mk(row3(r0, d), row3(r1, d), row3(r2, d));
+        float la = dot(ld, ld), b = dot(ld, lo), c = dot(lo, lo) - 1.f;
+        float disc = fmaf(b, b, -la * c);
+        float s = sqrtf(fmaxf(disc, 0.f));
+        float inv = __frcp_rn(la);
+        float t1 = (-b - s) * inv, t2 = (s - b) * inv;
+        float t = t1 >= 0.f ? t1 : t2;
+        if (disc >= 0.f && t >= 0.f && t < best_t) { best_t = t; hit = S.np + S.nu + i; }
+    }
 }
+
+__device__ __forceinline__ int stream_to_shape(const Streams32& S, int pos) {
+    if (pos < S.np) return S.pl_index[pos];
+    pos -= S.np;
+    if (pos < S.nu) return S.us_index[pos];
+    return S.gs_index[pos - S.nu];
+}
+
+// Intersection::compute_refractive (src/shape.rs:115-141), list-free, as in render_f64.cu:
+// containers = per world_id with an odd number of negative-t entries, that id's last entry.
+struct Cont32 { float t; int ord; int idx; int id; };
+__device__ __forceinline__ bool later32(const Cont32& a, const Cont32& b) { return a.t > b.t || (a.t == b.t && a.ord > b.ord); }
+__device__ __forceinline__ void offer32(Cont32 e, Cont32& top1, Cont32& top2) {
+    if (top1.idx >= 0 && e.id == top1.id) { if (later32(e, top1)) top1 = e; return; }
+    if (top2.idx >= 0 && e.id == top2.id) {
+        if (later32(e, top2)) top2 = e;
+        if (top1.idx < 0 || later32(top2, top1)) { Cont32 s = top1; top1 = top2; top2 = s; }
+        return;
+    }
+    if (top1.idx < 0 || later32(e, top1)) { top2 = top1; top1 = e; }
+    else if (top2.idx < 0 || later32(e, top2)) top2 = e;
+}
+
+// Calls f(t, shape_index, root) for every list entry of the ray with t < 0.
+template <typename F>
+__device__ __forceinline__ void for_each_negative(const Streams32& S, F3 o, F3 d, F f) {
+    const float a = dot(d, d);
+    const float inv_a = __frcp_rn(a);
+    for (int i = 0; i < S.np; ++i) {
+        float4 pl = S.planes[i];
+        float dy = row3(pl, d), oy = row4(pl, o);
+        float t = -oy * __frcp_rn(dy);
+        if (fabsf(dy) >= kPlaneEps && t < 0.f) f(t, S.pl_index[i], 0);
+    }
+    for (int i = 0; i < S.nu; ++i) {
+        float4 sp = S.usph[i];
+        F3 L = mk(o.x - sp.x, o.y - sp.y, o.z - sp.z);
+        float b = dot(d, L);
+        float c = fmaf(L.z, L.z, fmaf(L.y, L.y, fmaf(L.x, L.x, -sp.w)));
+        float disc = fmaf(b, b, -a * c);
+        if (disc >= 0.f) {
+            float s = sqrtf(disc);
+            float t1 = (-b - s) * inv_a, t2 = (s - b) * inv_a;
+            if (t1 < 0.f) f(t1, S.us_index[i], 0);
+            if (t2 < 0.f) f(t2, S.us_index[i], 1);
+        }
+    }
+    for (int i = 0; i < S.ng; ++i) {
+        float4 r0 = S.gsph[3 * i], r1 = S.gsph[3 * i + 1], r2 = S.gsph[3 * i + 2];
+        F3 lo = mk(row4(r0, o), row4(r1, o), row4(r2, o));
+        F3 ld = mk(row3(r0, d), row3(r1, d), row3(r2, d));
+        float la = dot(ld, ld), b = dot(ld, lo), c = dot(lo, lo) - 1.f;
+        float disc = fmaf(b, b, -la * c);
+        if (disc >= 0.f) {
+            float s = sqrtf(disc), inv = __frcp_rn(la);
+            float t1 = (-b - s) * inv, t2 = (s - b) * inv;
+            if (t1 < 0.f) f(t1, S.gs_index[i], 0);
+            if (t2 < 0.f) f(t2, S.gs_index[i], 1);
+        }
+    }
+}
+
+__device__ __noinline__ void compute_refractive32(const Streams32& S, const ShadeRec32* rec, F3 o, F3 d, int hit_idx,
+                                                  float& n1, float& n2) {
+    unsigned parity[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) parity[k] = 0u;
+    for_each_negative(S, o, d, [&](float, int idx, int) {
+        int id = __float_as_int(rec[idx].pa.w) & 255;
+        parity[id >> 5] ^= 1u << (id & 31);
+    });
+    Cont32 top1, top2;
+    top1.idx = -1; top2.idx = -1; top1.t = top2.t = 0.f; top1.ord = top2.ord = 0; top1.id = top2.id = -1;
+    for_each_negative(S, o, d, [&](float t, int idx, int root) {
+        int id = __float_as_int(rec[idx].pa.w) & 255;
+        if ((parity[id >> 5] >> (id & 31)) & 1u) {
+            Cont32 e; e.t = t; e.ord = 2 * idx + root; e.idx = idx; e.id = id;
+            offer32(e, top1, top2);
+        }
+    });
+    n1 = top1.idx >= 0 ? rec[top1.idx].tr_ri.y : 1.0f;
+    int hid = __float_as_int(rec[hit_idx].pa.w) & 255;
+    bool hit_is_container = (parity[hid >> 5] >> (hid & 31)) & 1u;
+    if (hit_is_container) {
+        if (top1.idx >= 0 && top1.id == hid) n2 = top2.idx >= 0 ? rec[top2.idx].tr_ri.y : 1.0f;
+        else n2 = top1.idx >= 0 ? rec[top1.idx].tr_ri.y : 1.0f;
+    } else {
+        n2 = rec[hit_idx].tr_ri.y;
+    }
+}
+
+// Pattern::pattern_at (src/material.rs:67-69,97-103,133-135,163-170,198-205,233-241)
+__device__ __forceinline__ F3 pattern_at32(int kind, F3 a, F3 b, F3 p) {
+    switch (kind) {
+        case RTC_PATTERN_TEST: return p;
+        case RTC_PATTERN_STRIPE: return fmodf(floorf(p.x), 2.0f) == 0.f ? a : b;
+        case RTC_PATTERN_GRADIENT: return fma3(b - a, p.x - floorf(p.x), a);
+        case RTC_PATTERN_RING: return fmodf(floorf(sqrtf(fmaf(p.x, p.x, p.y * p.y))), 2.0f) == 0.f ? a : b;
+        case RTC_PATTERN_CHECKER: return fmodf(floorf(p.x) + floorf(p.y) + floorf(p.z), 2.0f) == 0.f ? a : b;
+        default: return (fabsf(p.x - floorf(p.x)) < 0.01f || fabsf(p.z - floorf(p.z)) < 0.01f) ? b : a;
+    }
+}
+
+
+enum { ST_IDLE = 0, ST_RADIANCE = 1, ST_SHADOW = 2, ST_DEAD = 3 };
+
+template <bool kSmem>
+__global__ void __launch_bounds__(kThreads, 4)
+render_f32_kernel(DevScene32 sc, CamParams cam, void* __restrict__ out_rgb, uint8_t* __restrict__ out_hit,
+                  Counters* __restrict__ counters, unsigned* __restrict__ work) {
+    extern __shared__ float4 smem4[];
+    Streams32 S;
+    S.np = sc.n_planes; S.nu = sc.n_usph; S.ng = sc.n_gsph;
+    const ShadeRec32* R = sc.rec;
+    if (kSmem) {
+        // stage the intersect streams and the shading records: coalesced 16-byte loads
+        float4* s_pl = smem4;
+        float4* s_us = s_pl + S.np;
+        float4* s_gs = s_us + S.nu;
+        float4* s_rec = s_gs + 3 * S.ng;
+        const int rec4 = (int)(sizeof(ShadeRec32) / 16) * sc.n_shapes;
+        int32_t* s_pi = reinterpret_cast<int32_t*>(s_rec + rec4);
+        int32_t* s_ui = s_pi + S.np;
+        int32_t* s_gi = s_ui + S.nu;
+        for (int i = threadIdx.x; i < S.np; i += kThreads) { s_pl[i] = sc.planes[i]; s_pi[i] = sc.pl_index[i]; }
+        for (int i = threadIdx.x; i < S.nu; i += kThreads) { s_us[i] = sc.usph[i]; s_ui[i] = sc.us_index[i]; }
+        for (int i = threadIdx.x; i < 3 * S.ng; i += kThreads) s_gs[i] = sc.gsph[i];
+        for (int i = threadIdx.x; i < S.ng; i += kThreads) s_gi[i] = sc.gs_index[i];
+        const float4* g_rec = reinterpret_cast<const float4*>(sc.rec);
+        for (int i = threadIdx.x; i < rec4; i += kThreads) s_rec[i] = g_rec[i];
+        __syncthreads();
+        S.planes = s_pl; S.usph = s_us; S.gsph = s_gs; S.pl_index = s_pi; S.us_index = s_ui; S.gs_index = s_gi;
+        R = reinterpret_cast<const ShadeRec32*>(s_rec);
+    } else {
+        S.planes = sc.planes; S.usph = sc.usph; S.gsph = sc.gsph;
+        S.pl_index = sc.pl_index; S.us_index = sc.us_index; S.gs_index = sc.gs_index;
+    }
+
+    const unsigned full = 0xffffffffu;
+    const int lane = threadIdx.x & 31;
+    const unsigned lt_mask = (1u << lane) - 1u;
+    const int tiles_x = ((int)cam.hsize + kTileX - 1) / kTileX;
+    const int tiles_y = (cam.shard_rows + kTileY - 1) / kTileY;
+    const unsigned total_tiles = (unsigned)(tiles_x * tiles_y);
+    const int n_sub = cam.samples == 1 ? 1 : 4;
+    const float w0 = cam.samples == 1 ? 1.0f : 0.25f;
+    const F3 light_pos = mk(sc.light_pos[0], sc.light_pos[1], sc.light_pos[2]);
+    const F3 light_int = mk(sc.light_int[0], sc.light_int[1], sc.light_int[2]);
+    const F3 cam_origin = mk((float)cam.vinv[3], (float)cam.vinv[7], (float)cam.vinv[11]);  // Vinv * (0,0,0)
+
+    // warp-uniform work state
+    unsigned wtile = 0;
+    int wnext = kBatch;
+    bool exhausted = false;
+    // lane state
+    int st = ST_IDLE;
+    F3 ro = mk(0, 0, 0), rd = mk(0, 0, 1);   // current radiance ray
+    float rw = 0.f;                            // its path weight
+    int remaining = 0;
+    bool is_primary = false;
+    F3 hp = mk(0, 0, 0), hn = mk(0, 1, 0);   // pending hit: over_point, normal
+    int hidx = 0;
+    float hn1 = 1.f, hn2 = 1.f;
+    bool have = false;                         // owns a pixel
+    int px = 0, pr = 0, py = 0, sub = 0;
+    F3 acc = mk(0, 0, 0);
+    unsigned hitbits = 0;
+    float4 stk_a[kMaxStack], stk_b[kMaxStack];  // pending refraction rays: (o, w), (d, remaining)
+    int sp = 0;
+    unsigned n_rays = 0, n_shadow = 0, n_shaded = 0, n_phits = 0;
+
+    for (;;) {
+        // ------------------------------------------------------------------ refill idle lanes
+        if (st == ST_IDLE && sp > 0) {
+            --sp;
+            float4 a = stk_a[sp], b = stk_b[sp];
+            ro = xyz(a); rw = a.w; rd = xyz(b); remaining = __float_as_int(b.w);
+            is_primary = false;
+            st = ST_RADIANCE;
+        }
+        if (st == ST_IDLE && have && sub + 1 < n_sub) ++sub;  // next sub-sample of the same pixel
+        else if (st == ST_IDLE && have) {
+            // pixel finished: Canvas::write_pixel (src/canvas.rs:43-46)
+            size_t p = (size_t)pr * cam.hsize + px;
+            if (cam.out_format == RTC_OUT_F64_RGB) {
+                double* o = (double*)out_rgb + 3 * p;
+                o[0] = (double)acc.x; o[1] = (double)acc.y; o[2] = (double)acc.z;
+            } else if (cam.out_format == RTC_OUT_F32_RGB) {
+                float* o = (float*)out_rgb + 3 * p;
+                o[0] = acc.x; o[1] = acc.y; o[2] = acc.z;
+            } else {
+                uint8_t* o = (uint8_t*)out_rgb + 3 * p;  // Color::scale, src/color.rs:100-114
+                float c3[3] = {acc.x, acc.y, acc.z};
+#pragma unroll
+                for (int k = 0; k < 3; ++k) {
+                    float s = c3[k] * 255.0f;
+                    int q = s != s ? 0 : (s >= 2147483520.0f ? 2147483647 : (s <= -2147483648.0f ? (-2147483647 - 1) : (int)s));
+                    o[k] = (uint8_t)(q < 0 ? 0 : (q > 255 ? 255 : q));
+                }
+            }
+            if (out_hit) out_hit[p] = (uint8_t)hitbits;
+            have = false;
+        }
+        // lanes without a pixel claim the next ones of the warp's tile (ballot/popc rank)
+        for (;;) {
+            bool need = st == ST_IDLE && !have;
+            unsigned m = __ballot_sync(full, need);
+            if (m == 0u || exhausted) break;
+            if (wnext >= kBatch) {
+                unsigned t = 0;
+                if (lane == 0) t = atomicAdd(work, 1u);
+                wtile = __shfl_sync(full, t, 0);
+                wnext = 0;
+                if (wtile >= total_tiles) { exhausted = true; break; }
+            }
+            int rank = __popc(m & lt_mask);
+            int take = min(__popc(m), kBatch - wnext);
+            if (need && rank < take) {
+                int k = wnext + rank;
+                int tx = (int)(wtile % (unsigned)tiles_x), ty = (int)(wtile / (unsigned)tiles_x);
+                px = tx * kTileX + (k & (kTileX - 1));
+                pr = ty * kTileY + (k >> 4);
+                if (px < (int)cam.hsize && pr < cam.shard_rows) {
+                    py = cam.shard_count > 1 ? shard_row_to_frame_row(pr, cam.tile_rows, cam.shard_index, cam.shard_count) : pr;
+                    have = true; sub = 0; acc = mk(0, 0, 0); hitbits = 0;
+                    if (!(px < (int)cam.xlim && py < (int)cam.ylim)) sub = n_sub;  // outside the rect: stays black
+                }
+            }
+            wnext += take;
+        }
+        if (st == ST_IDLE && have && sub < n_sub) {
+            // Camera::ray_for_pixel_offset (src/camera.rs:64-76); the pixel position in f64, once per sample
+            double xo = n_sub == 1 ? 0.5 : ((sub & 1) ? 0.75 : 0.25);
+            double yo = n_sub == 1 ? 0.5 : ((sub & 2) ? 0.75 : 0.25);
+            double wx = cam.half_width - ((double)px + xo) * cam.pixel_size;
+            double wy = cam.half_height - ((double)py + yo) * cam.pixel_size;
+            F3 dir = mk((float)(cam.vinv[0] * wx + cam.vinv[1] * wy - cam.vinv[2]),
+                        (float)(cam.vinv[4] * wx + cam.vinv[5] * wy - cam.vinv[6]),
+                        (float)(cam.vinv[8] * wx + cam.vinv[9] * wy - cam.vinv[10]));
+            rd = dir * rsqrtf(dot(dir, dir));
+            ro = cam_origin; rw = w0; remaining = cam.max_depth; is_primary = true;
+            st = ST_RADIANCE;
+        }
+        if (st == ST_IDLE && !have && exhausted) st = ST_DEAD;
+        if (!__any_sync(full, st != ST_DEAD)) break;
+        if (st == ST_IDLE) continue;  // e.g. a pixel outside the rect: finalise it next round
+
+        // ------------------------------------------------------------------ one World::intersect per lane
+        F3 io, id;
+        float tmax;
+        if (st == ST_SHADOW) { io = hp; id = light_pos - hp; tmax = 1.0f; }   // is_shadowed_by_light, src/shape.rs:716-727
+        else { io = ro; id = rd; tmax = __int_as_float(0x7f800000); }
+        int hit = -1;
+        if (st != ST_DEAD) { intersect32(S, io, id, tmax, hit); ++n_rays; }
+
+        if (st == ST_RADIANCE) {
+            // ---- World::color_at: hit or background (src/shape.rs:702-710) ----
+            if (is_primary && hit >= 0) { hitbits |= 1u << sub; ++n_phits; }
+            if (hit < 0) {
+                st = ST_IDLE;
+            } else {
+                const int idx = stream_to_shape(S, hit);
+                const ShadeRec32& rec = R[idx];
+                const float4 tr = rec.tr_ri;
+                const int geom = __float_as_int(tr.w);
+                F3 p = fma3(rd, tmax, ro);                       // Ray::position
+                F3 n;
+                if (geom == GEOM_PLANE) n = xyz(rec.g0);
+                else if (geom == GEOM_USPHERE) { float4 g = rec.g0; n = (p - xyz(g)) * g.w; }
+                else {                                            // Shape::normal_at, src/shape.rs:34-40
+                    F3 lp = mk(row4(rec.g0, p), row4(rec.g1, p), row4(rec.g2, p));
+                    F3 wn = mk(row3(rec.t0, lp), row3(rec.t1, lp), row3(rec.t2, lp));
+                    n = wn * rsqrtf(dot(wn, wn));
+                }
+                hn1 = 1.f; hn2 = 1.f;
+                if (tr.x != 0.f) compute_refractive32(S, R, ro, rd, idx, hn1, hn2);
+                if (dot(n, rd) > 0.f) n = mk(-n.x, -n.y, -n.z);  // inside: normal . eyev < 0  (src/shape.rs:77-78)
+                hn = n;
+                hp = fma3(n, kEps32, p);                         // over_point
+                hidx = idx;
+                st = ST_SHADOW;
+            }
+        } else if (st == ST_SHADOW) {
+            // ---- shade_hit (src/shape.rs:685-700) with Material::lighting (src/material.rs:319-361) ----
+            ++n_shadow; ++n_shaded;
+            const bool shadowed = hit >= 0;
+            const ShadeRec32& rec = R[hidx];
+            const float4 ca = rec.col_amb, ds = rec.dif_spec, tr = rec.tr_ri;
+            const int pkind = __float_as_int(tr.z);
+            F3 base = xyz(ca);
+            if (pkind != RTC_PATTERN_NONE) {
+                F3 pp = mk(row4(rec.p0, hp), row4(rec.p1, hp), row4(rec.p2, hp));
+                base = pattern_at32(pkind, xyz(rec.pa), xyz(rec.pb), pp);
+            }
+            const F3 eff = base * light_int;
+            F3 surface = eff * ca.w;                                   // ambient
+            const F3 eye = mk(-rd.x, -rd.y, -rd.z);
+            if (!shadowed) {
+                F3 lv = light_pos - hp;
+                lv = lv * rsqrtf(dot(lv, lv));
+                float ldn = dot(lv, hn);
+                if (ldn >= 0.f) {
+                    surface = fma3(eff, ds.x * ldn, surface);          // diffuse
+                    F3 rv = fma3(hn, 2.f * ldn, mk(-lv.x, -lv.y, -lv.z));  // (-lightv).reflect(normal)
+                    float rde = dot(rv, eye);
+                    if (rde > 0.f) surface = fma3(light_int, ds.y * __powf(rde, ds.z), surface);
+                }
+            }
+            acc = fma3(surface, rw, acc);
+            // children (src/shape.rs:689-699, 729-781) as weighted rays
+            const float k_refl = ds.w, k_tr = tr.x;
+            const bool both = k_refl > 0.f && k_tr > 0.f;
+            const float cos_i = dot(eye, hn);
+            float refl_w = rw * k_refl, refr_w = rw * k_tr;
+            if (both) {                                                // World::reflectance (Schlick)
+                float cs = cos_i, refl = 0.f;
+                bool tir = false;
+                if (hn1 > hn2) {
+                    float nn = hn1 / hn2;
+                    float sin2_t = nn * nn * (1.f - cs * cs);
+                    if (sin2_t > 1.f) tir = true; else cs = sqrtf(1.f - sin2_t);
+                }
+                if (tir) refl = 1.f;
+                else {
+                    float q = (hn1 - hn2) / (hn1 + hn2), r0 = q * q, m = 1.f - cs, m2 = m * m;
+                    refl = fmaf(1.f - r0, m2 * m2 * m, r0);
+                }
+                refl_w *= refl; refr_w *= 1.f - refl;
+            }
+            const bool want_refl = remaining != 0 && k_refl > 0.f;
+            bool want_refr = false;
+            F3 fo = mk(0, 0, 0), fd = mk(0, 0, 1);
+            if (remaining != 0 && k_tr != 0.f) {                       // refracted_color
+                float ratio = hn1 / hn2;
+                float sin2_t = ratio * ratio * (1.f - cos_i * cos_i);
+                if (!(sin2_t > 1.f)) {
+                    float cos_t = sqrtf(1.f - sin2_t);
+                    fd = fma3(hn, ratio * cos_i - cos_t, eye * (-ratio));
+                    fo = fma3(hn, -2.f * kEps32, hp);                  // under_point
+                    want_refr = true;
+                }
+            }
+            is_primary = false;
+            if (want_refl) {
+                if (want_refr && sp < kMaxStack) {
+                    stk_a[sp] = make_float4(fo.x, fo.y, fo.z, refr_w);
+                    stk_b[sp] = make_float4(fd.x, fd.y, fd.z, __int_as_float(remaining - 1));
+                    ++sp;
+                }
+                float dn = dot(rd, hn);
+                rd = fma3(hn, -2.f * dn, rd);                          // reflectv = d.reflect(n)
+                ro = hp; rw = refl_w; --remaining;
+                st = ST_RADIANCE;
+            } else if (want_refr) {
+                ro = fo; rd = fd; rw = refr_w; --remaining;
+                st = ST_RADIANCE;
+            } else {
+                st = ST_IDLE;
+            }
+        }
+    }
+
+    if (counters) {
+        unsigned r = __reduce_add_sync(full, n_rays), s = __reduce_add_sync(full, n_shadow);
+        unsigned h = __reduce_add_sync(full, n_shaded), ph = __reduce_add_sync(full, n_phits);
+        if (lane == 0) {
+            atomicAdd(&counters->rays, (unsigned long long)r);
+            atomicAdd(&counters->shadow_rays, (unsigned long long)s);
+            atomicAdd(&counters->shaded_hits, (unsigned long long)h);
+            atomicAdd(&counters->primary_hits, (unsigned long long)ph);
+        }
+    }
+}
+
+}  // namespace
+
+cudaError_t launch_render_f32(const DevScene32& scene, const CamParams& cam, void* d_rgb, uint8_t* d_hit,
+                              Counters* d_counters, unsigned* d_work, cudaStream_t stream) {
+    if (cam.shard_rows <= 0) return cudaSuccess;
+    cudaError_t e = cudaMemsetAsync(d_work, 0, sizeof(unsigned), stream);
+    if (e != cudaSuccess) return e;
+    int dev = 0, sms = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    size_t smem = (size_t)(scene.n_planes + scene.n_usph + 3 * scene.n_gsph) * 16 + (size_t)scene.n_shapes * (sizeof(ShadeRec32) + 4) + 16;
+    const int tiles = ((cam.hsize + kTileX - 1) / kTileX) * ((cam.shard_rows + kTileY - 1) / kTileY);
+    int blocks_per_sm = 0;
+    if (smem <= 48 * 1024) {
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks_per_sm, render_f32_kernel<true>, kThreads, smem);
+        int grid = max(1, min(sms * max(blocks_per_sm, 1), (tiles + 3) / 4));
+        render_f32_kernel<true><<<grid, kThreads, smem, stream>>>(scene, cam, d_rgb, d_hit, d_counters, d_work);
+    } else {
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks_per_sm, render_f32_kernel<false>, kThreads, 0);
+        int grid = max(1, min(sms * max(blocks_per_sm, 1), (tiles + 3) / 4));
+        render_f32_kernel<false><<<grid, kThreads, 0, stream>>>(scene, cam, d_rgb, d_hit, d_counters, d_work);
+    }
+    return cudaGetLastError();
+}
+
 }  // namespace rtc

@@ -55,8 +55,8 @@ struct DeviceState {
     cudaEvent_t ev_k0 = nullptr, ev_k1 = nullptr, ev_c1 = nullptr;
     // scene
     DevBuf<double2> sph64, pl64;
-    DevBuf<float4> sph32, pl32;
-    DevBuf<int32_t> sph_index, pl_index;
+    DevBuf<float4> pl32, us32, gs32;
+    DevBuf<int32_t> sph_index, pl_index, us_index, gs_index;
     DevBuf<ShadeRec64> rec64;
     DevBuf<ShadeRec32> rec32;
     DevScene64 s64{};
@@ -65,6 +65,7 @@ struct DeviceState {
     DevBuf<unsigned char> rgb;
     DevBuf<unsigned char> hit;
     DevBuf<Counters> counters;
+    DevBuf<unsigned> work;  // tile counter of the persistent f32 kernel
 };
 
 size_t elem_size(int out_format) {
@@ -138,12 +139,18 @@ CamParams make_cam(const rtc_camera* cam, const rtc_render_opts* o, int shard_in
 // ---- scene flattening ---------------------------------------------------------------------------
 struct HostScene {
     std::vector<double2> sph64, pl64;
-    std::vector<float4> sph32, pl32;
-    std::vector<int32_t> sph_index, pl_index;
+    std::vector<float4> pl32, us32, gs32;
+    std::vector<int32_t> sph_index, pl_index, us_index, gs_index;
     std::vector<ShadeRec64> rec64;
     std::vector<ShadeRec32> rec32;
     int ids_unique = 1;
 };
+
+inline float __int_as_float_host(int v) {
+    float f;
+    std::memcpy(&f, &v, 4);
+    return f;
+}
 
 void mul34(const double* a, const double* b, double* out) {  // (a as 3x4 affine) * (b as 3x4 affine)
     for (int r = 0; r < 3; ++r)
@@ -187,29 +194,66 @@ int flatten(const rtc_shape* shapes, size_t n, HostScene& hs) {
 
         ShadeRec32& q = hs.rec32[i];
         std::memset(&q, 0, sizeof q);
-        for (int k = 0; k < 12; ++k) q.inv[k] = (float)s.inv[k];
-        for (int k = 0; k < 9; ++k) q.invt[k] = (float)r.invt[k];
-        for (int k = 0; k < 3; ++k) { q.color[k] = (float)s.color[k]; q.pat_a[k] = (float)s.pat_a[k]; q.pat_b[k] = (float)s.pat_b[k]; }
-        q.ambient = (float)s.ambient; q.diffuse = (float)s.diffuse; q.specular = (float)s.specular; q.shininess = (float)s.shininess;
-        q.reflective = (float)s.reflective; q.transparency = (float)s.transparency; q.refractive_index = (float)s.refractive_index;
+        q.col_amb = make_float4((float)s.color[0], (float)s.color[1], (float)s.color[2], (float)s.ambient);
+        q.dif_spec = make_float4((float)s.diffuse, (float)s.specular, (float)s.shininess, (float)s.reflective);
         double comb[12];
         mul34(s.pat_inv, s.inv, comb);  // world point -> pattern space in one apply (fast mode only)
-        for (int k = 0; k < 12; ++k) q.pat_inv[k] = (float)comb[k];
-        q.kind = s.kind; q.world_id = id; q.pattern_kind = s.pattern_kind;
-
+        q.p0 = make_float4((float)comb[0], (float)comb[1], (float)comb[2], (float)comb[3]);
+        q.p1 = make_float4((float)comb[4], (float)comb[5], (float)comb[6], (float)comb[7]);
+        q.p2 = make_float4((float)comb[8], (float)comb[9], (float)comb[10], (float)comb[11]);
+        q.pa = make_float4((float)s.pat_a[0], (float)s.pat_a[1], (float)s.pat_a[2], __int_as_float_host(id));
+        q.pb = make_float4((float)s.pat_b[0], (float)s.pat_b[1], (float)s.pat_b[2], 0.f);
+        int geom;
         if (s.kind == RTC_SHAPE_SPHERE) {
             for (int rr = 0; rr < 3; ++rr) {
                 hs.sph64.push_back(make_double2(s.inv[4 * rr + 0], s.inv[4 * rr + 1]));
                 hs.sph64.push_back(make_double2(s.inv[4 * rr + 2], s.inv[4 * rr + 3]));
-                hs.sph32.push_back(make_float4((float)s.inv[4 * rr + 0], (float)s.inv[4 * rr + 1], (float)s.inv[4 * rr + 2], (float)s.inv[4 * rr + 3]));
             }
             hs.sph_index.push_back((int32_t)i);
+            // similarity test: M^T M == k I  (M = upper 3x3 of the inverse)  ->  world-space sphere
+            const double* m = s.inv;
+            double g[3][3];
+            for (int a2 = 0; a2 < 3; ++a2)
+                for (int b2 = 0; b2 < 3; ++b2) g[a2][b2] = m[a2] * m[b2] + m[4 + a2] * m[4 + b2] + m[8 + a2] * m[8 + b2];
+            double k2 = (g[0][0] + g[1][1] + g[2][2]) / 3.0;
+            double dev = 0.0;
+            for (int a2 = 0; a2 < 3; ++a2)
+                for (int b2 = 0; b2 < 3; ++b2) dev = std::max(dev, std::fabs(g[a2][b2] - (a2 == b2 ? k2 : 0.0)));
+            // the stored inverse-transpose must also be the true one (Sphere keeps it in sync, src/shape.rs:319-322)
+            double devt = 0.0;
+            for (int a2 = 0; a2 < 3; ++a2)
+                for (int b2 = 0; b2 < 3; ++b2) devt = std::max(devt, std::fabs(s.inv_t[4 * a2 + b2] - s.inv[4 * b2 + a2]));
+            if (k2 > 0.0 && dev <= 1e-12 * k2 && devt <= 1e-12 * std::sqrt(k2)) {
+                geom = GEOM_USPHERE;
+                double r2 = 1.0 / k2, c3[3];
+                for (int a2 = 0; a2 < 3; ++a2) c3[a2] = -r2 * (m[a2] * m[3] + m[4 + a2] * m[7] + m[8 + a2] * m[11]);
+                hs.us32.push_back(make_float4((float)c3[0], (float)c3[1], (float)c3[2], (float)r2));
+                hs.us_index.push_back((int32_t)i);
+                q.g0 = make_float4((float)c3[0], (float)c3[1], (float)c3[2], (float)std::sqrt(k2));
+            } else {
+                geom = GEOM_GSPHERE;
+                for (int rr = 0; rr < 3; ++rr) {
+                    float4 row = make_float4((float)m[4 * rr], (float)m[4 * rr + 1], (float)m[4 * rr + 2], (float)m[4 * rr + 3]);
+                    hs.gs32.push_back(row);
+                    (rr == 0 ? q.g0 : rr == 1 ? q.g1 : q.g2) = row;
+                    float4 trow = make_float4((float)s.inv_t[4 * rr], (float)s.inv_t[4 * rr + 1], (float)s.inv_t[4 * rr + 2], 0.f);
+                    (rr == 0 ? q.t0 : rr == 1 ? q.t1 : q.t2) = trow;
+                }
+                hs.gs_index.push_back((int32_t)i);
+            }
         } else {
+            geom = GEOM_PLANE;
             hs.pl64.push_back(make_double2(s.inv[4], s.inv[5]));
             hs.pl64.push_back(make_double2(s.inv[6], s.inv[7]));
             hs.pl32.push_back(make_float4((float)s.inv[4], (float)s.inv[5], (float)s.inv[6], (float)s.inv[7]));
             hs.pl_index.push_back((int32_t)i);
+            // world normal = normalize(stored inverse-transpose * (0,1,0))  (src/shape.rs:34-40, 481)
+            double nx = s.inv_t[1], ny = s.inv_t[5], nz = s.inv_t[9];
+            double nm = std::sqrt(nx * nx + ny * ny + nz * nz);
+            q.g0 = make_float4((float)(nx / nm), (float)(ny / nm), (float)(nz / nm), 0.f);
         }
+        q.tr_ri = make_float4((float)s.transparency, (float)s.refractive_index, __int_as_float_host(s.pattern_kind),
+                              __int_as_float_host(geom));
     }
     return RTC_OK;
 }
@@ -304,7 +348,7 @@ void parallel_copy(unsigned char* dst, const unsigned char* src, size_t n) {
 int launch_on(DeviceState& d, const CamParams& cp, int precision, void* d_rgb, uint8_t* d_hit, Counters* d_counters,
               cudaStream_t st) {
     cudaError_t e = precision == RTC_PRECISION_F64_PARITY ? launch_render_f64(d.s64, cp, d_rgb, d_hit, d_counters, st)
-                                                          : launch_render_f32(d.s32, cp, d_rgb, d_hit, d_counters, st);
+                                                          : launch_render_f32(d.s32, cp, d_rgb, d_hit, d_counters, d.work.p, st);
     if (e != cudaSuccess) return fail(RTC_ERR_CUDA, std::string("kernel launch: ") + cudaGetErrorString(e));
     return RTC_OK;
 }
@@ -346,6 +390,7 @@ int rtc_context_create(const int* device_ids, int n_gpus, rtc_context** out_ctx)
         if (e == cudaSuccess) e = cudaEventCreate(&d.ev_k1);
         if (e == cudaSuccess) e = cudaEventCreate(&d.ev_c1);
         if (e == cudaSuccess) e = d.counters.ensure(1);
+        if (e == cudaSuccess) e = d.work.ensure(1);
         if (e != cudaSuccess) {
             std::string m = cudaGetErrorString(e);
             rtc_context_destroy(ctx);
@@ -366,9 +411,9 @@ void rtc_context_destroy(rtc_context* ctx) {
     for (DeviceState& d : ctx->devs) {
         cudaSetDevice(d.dev);
         if (d.stream) cudaStreamSynchronize(d.stream);
-        d.sph64.release(); d.pl64.release(); d.sph32.release(); d.pl32.release();
+        d.sph64.release(); d.pl64.release(); d.pl32.release(); d.us32.release(); d.gs32.release(); d.us_index.release(); d.gs_index.release();
         d.sph_index.release(); d.pl_index.release(); d.rec64.release(); d.rec32.release();
-        d.rgb.release(); d.hit.release(); d.counters.release();
+        d.rgb.release(); d.hit.release(); d.counters.release(); d.work.release();
         if (d.ev_k0) cudaEventDestroy(d.ev_k0);
         if (d.ev_k1) cudaEventDestroy(d.ev_k1);
         if (d.ev_c1) cudaEventDestroy(d.ev_c1);
@@ -389,19 +434,25 @@ int rtc_scene_upload(rtc_context* ctx, const rtc_light* light, const rtc_shape* 
         CUDA_TRY(cudaSetDevice(d.dev));
         CUDA_TRY(upload(d.sph64, hs.sph64, d.stream));
         CUDA_TRY(upload(d.pl64, hs.pl64, d.stream));
-        CUDA_TRY(upload(d.sph32, hs.sph32, d.stream));
         CUDA_TRY(upload(d.pl32, hs.pl32, d.stream));
+        CUDA_TRY(upload(d.us32, hs.us32, d.stream));
+        CUDA_TRY(upload(d.gs32, hs.gs32, d.stream));
+        CUDA_TRY(upload(d.us_index, hs.us_index, d.stream));
+        CUDA_TRY(upload(d.gs_index, hs.gs_index, d.stream));
         CUDA_TRY(upload(d.sph_index, hs.sph_index, d.stream));
         CUDA_TRY(upload(d.pl_index, hs.pl_index, d.stream));
         CUDA_TRY(upload(d.rec64, hs.rec64, d.stream));
         CUDA_TRY(upload(d.rec32, hs.rec32, d.stream));
         d.s64.n_shapes = d.s32.n_shapes = (int)n_shapes;
-        d.s64.n_spheres = d.s32.n_spheres = (int)hs.sph_index.size();
+        d.s64.n_spheres = (int)hs.sph_index.size();
+        d.s32.n_usph = (int)hs.us_index.size();
+        d.s32.n_gsph = (int)hs.gs_index.size();
         d.s64.n_planes = d.s32.n_planes = (int)hs.pl_index.size();
         d.s64.ids_unique = d.s32.ids_unique = hs.ids_unique;
         d.s64.sph_rows = d.sph64.p; d.s64.pl_rows = d.pl64.p; d.s64.sph_index = d.sph_index.p; d.s64.pl_index = d.pl_index.p;
         d.s64.rec = d.rec64.p;
-        d.s32.sph_rows = d.sph32.p; d.s32.pl_rows = d.pl32.p; d.s32.sph_index = d.sph_index.p; d.s32.pl_index = d.pl_index.p;
+        d.s32.planes = d.pl32.p; d.s32.pl_index = d.pl_index.p; d.s32.usph = d.us32.p; d.s32.us_index = d.us_index.p;
+        d.s32.gsph = d.gs32.p; d.s32.gs_index = d.gs_index.p;
         d.s32.rec = d.rec32.p;
         for (int k = 0; k < 3; ++k) {
             d.s64.light_pos[k] = light->position[k]; d.s64.light_int[k] = light->intensity[k];

@@ -47,24 +47,33 @@ struct DevScene64 {
 };
 
 // ---- f32 (fast) layout ------------------------------------------------------------------------
+// Fast mode re-derives each shape test in WORLD space so that almost every instruction is an FFMA:
+//   planes          (nx, ny, nz, w) = row 1 of the inverse: o'.y = n.o + w, d'.y = n.d
+//   uniform spheres (cx, cy, cz, r^2): spheres whose transform is a similarity (uniform scale +
+//                   rotation + translation) are ordinary world-space spheres
+//   general spheres 3 rows of the inverse (any affine transform), tested in object space
+// Geometry kinds of a shading record:
+enum { GEOM_PLANE = 0, GEOM_USPHERE = 1, GEOM_GSPHERE = 2 };
+
 struct __align__(16) ShadeRec32 {
-    float inv[12];
-    float invt[9];
-    float color[3];
-    float ambient, diffuse, specular, shininess;
-    float reflective, transparency, refractive_index;
-    float pat_inv[12];  // pattern_inv * shape_inv pre-multiplied on the host (one apply per lookup)
-    float pat_a[3], pat_b[3];
-    int32_t kind, world_id, pattern_kind, flags;
+    float4 g0, g1, g2;  // plane: g0.xyz = unit world normal | usphere: g0 = (c, 1/r) | gsphere: inverse rows
+    float4 t0, t1, t2;  // gsphere: rows of the stored inverse-transpose 3x3
+    float4 col_amb;     // colour rgb, ambient
+    float4 dif_spec;    // diffuse, specular, shininess, reflective
+    float4 tr_ri;       // transparency, refractive_index, (int) pattern_kind, (int) geom kind
+    float4 p0, p1, p2;  // world -> pattern space (pattern_inv * shape_inv), rows
+    float4 pa, pb;      // pattern colours a, b ; pa.w = (int) world_id
 };
 
 struct DevScene32 {
-    int n_shapes, n_spheres, n_planes, ids_unique;
-    const float4* sph_rows;    // [n_spheres][3]
-    const int32_t* sph_index;
-    const float4* pl_rows;     // [n_planes]
-    const int32_t* pl_index;
-    const ShadeRec32* rec;
+    int n_shapes, n_planes, n_usph, n_gsph, ids_unique;
+    const float4* planes;      // [n_planes]
+    const int32_t* pl_index;   // original shape index
+    const float4* usph;        // [n_usph]
+    const int32_t* us_index;
+    const float4* gsph;        // [n_gsph][3]
+    const int32_t* gs_index;
+    const ShadeRec32* rec;     // [n_shapes]
     float light_pos[3];
     float light_int[3];
 };
@@ -111,6 +120,6 @@ __host__ __device__ inline int shard_num_rows(int vsize, int tile_rows, int shar
 cudaError_t launch_render_f64(const DevScene64& scene, const CamParams& cam, void* d_rgb, uint8_t* d_hit,
                               Counters* d_counters, cudaStream_t stream);
 cudaError_t launch_render_f32(const DevScene32& scene, const CamParams& cam, void* d_rgb, uint8_t* d_hit,
-                              Counters* d_counters, cudaStream_t stream);
+                              Counters* d_counters, unsigned* d_work, cudaStream_t stream);
 
 }  // namespace rtc

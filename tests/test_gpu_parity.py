@@ -1,0 +1,239 @@
+"""GPU parity tests proper: the CUDA path, called through the C ABI, against the oracle on the
+same inputs.  f64 parity mode: hit/miss mask bit-exact, |delta| <= 1e-9 per channel (north star).
+f32 fast mode: within 1/255 after the reference's truncating 8-bit rule on >= 99.9 % of pixels."""
+import math
+import os
+import random
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+TOL64 = 1e-9
+NCPU = os.cpu_count() or 1
+
+
+def _check64(rtc, orc, renderer, world, cam, rect=None, max_depth=5, flat=None):
+    rect = rtc.ffi.RECT_FULL if rect is None else rect
+    if flat is not None:
+        renderer.upload_flat(*flat)
+        ow = orc.OracleWorld(flat=flat)
+    else:
+        renderer.upload(world)
+        ow = orc.OracleWorld(world)
+    want, want_hit, cnt = ow.render(cam, rect=rect, max_depth=max_depth, threads=NCPU)
+    opts = rtc.Renderer.make_opts(precision=rtc.ffi.PRECISION_F64_PARITY, rect=rect, max_depth=max_depth)
+    got, hit, stats = renderer.render(cam.flatten(), opts)
+    assert np.array_equal(hit, want_hit), f"hit mask differs at {np.argwhere(hit != want_hit)[:5]}"
+    err = np.abs(got - want).max()
+    assert err <= TOL64, f"max |delta| = {err} at {np.unravel_index(np.abs(got - want).argmax(), got.shape)}"
+    assert stats.rays == cnt.rays and stats.shadow_rays == cnt.shadow_rays and stats.shaded_hits == cnt.shaded_hits
+    return got, want, stats
+
+
+def test_render1_kat_through_the_c_abi(rtc, orc, renderer):
+    """src/camera.rs:216-231: default world 11x11, pixel (5,5) = (0.38066, 0.47583, 0.2855)."""
+    world = rtc.World.default()
+    cam = rtc.Camera.new_with_transform(11, 11, math.pi / 2.,
+                                        rtc.Matrix.make_view_transform((0., 0., -5.), (0., 0., 0.), (0., 1., 0.)))
+    c = cam.render(world, renderer=renderer)
+    p = c.get_pixel(5, 5)
+    assert abs(p.red - 0.38066) < 1e-4 and abs(p.green - 0.47583) < 1e-4 and abs(p.blue - 0.2855) < 1e-4
+    assert (c.pixels[10, :] == 0).all() and (c.pixels[:, 10] == 0).all()  # Camera::render's loop bounds
+    assert c.hit_mask[5, 5] == 1 and c.hit_mask[0, 0] == 0
+    _check64(rtc, orc, renderer, world, cam, rect=rtc.ffi.RECT_REFERENCE_RENDER)
+    _check64(rtc, orc, renderer, world, cam, rect=rtc.ffi.RECT_FULL)
+
+
+@pytest.mark.parametrize("rect", [0, 1])
+def test_c1_reflect_refract_320x160(rtc, orc, renderer, rect):
+    world = rtc.scenes.reflect_refract_scene()
+    cam = rtc.scenes.reflect_refract_camera(320, 160)
+    got, want, stats = _check64(rtc, orc, renderer, world, cam, rect=rect)
+    if rect == 1:
+        assert stats.rays == 650692 and stats.primary_hits == 320 * 160
+
+
+@pytest.mark.parametrize("depth", [0, 1, 2, 3, 5, 8])
+def test_depth_limits(rtc, orc, renderer, depth):
+    world = rtc.scenes.reflect_refract_scene()
+    cam = rtc.scenes.reflect_refract_camera(96, 48)
+    _check64(rtc, orc, renderer, world, cam, max_depth=depth)
+
+
+def test_supersample_2x2(rtc, orc, renderer):
+    """antialiasing_samples = 0: the deterministic 4-sample path of render_pixel (src/camera.rs:96-113)."""
+    world = rtc.scenes.reflect_refract_scene()
+    cam = rtc.scenes.reflect_refract_camera(160, 80, samples=0)
+    got, want, stats = _check64(rtc, orc, renderer, world, cam)
+    assert stats.primary_hits == 160 * 80 * 4
+
+
+@pytest.mark.parametrize("size", [(1, 1), (2, 2), (7, 3), (33, 17), (129, 65)])
+def test_ragged_sizes(rtc, orc, renderer, size):
+    world = rtc.scenes.reflect_refract_scene()
+    for samples in (1, 0):
+        cam = rtc.scenes.reflect_refract_camera(size[0], size[1], samples=samples)
+        for rect in (0, 1):
+            _check64(rtc, orc, renderer, world, cam, rect=rect)
+
+
+def test_bench_scene(rtc, orc, renderer):
+    world, cam = rtc.scenes.bench_scene()
+    _check64(rtc, orc, renderer, world, cam)
+
+
+def _random_world(rtc, seed, n=24):
+    rnd = random.Random(seed)
+    w = rtc.World(rtc.Light(rtc.Color(rnd.uniform(0.5, 1), rnd.uniform(0.5, 1), rnd.uniform(0.5, 1)),
+                            (rnd.uniform(-8, 8), rnd.uniform(4, 10), rnd.uniform(-8, 8))))
+    pats = [rtc.TestPattern, rtc.StripePattern, rtc.GradientPattern, rtc.RingPattern, rtc.CheckerPattern, rtc.GridPattern]
+
+    def material():
+        m = rtc.Material(color=rtc.Color(rnd.random(), rnd.random(), rnd.random()), ambient=rnd.uniform(0, 0.3),
+                         diffuse=rnd.uniform(0.2, 0.9), specular=rnd.uniform(0, 0.9), shininess=rnd.uniform(1, 300))
+        k = rnd.random()
+        if k < 0.3:
+            m.reflectiveness = rnd.uniform(0.1, 0.9)
+        elif k < 0.55:
+            m.reflectiveness, m.transparency, m.refractive_index = rnd.uniform(0.1, 0.9), rnd.uniform(0.1, 1.0), rnd.uniform(1.0, 2.5)
+        elif k < 0.7:
+            m.transparency, m.refractive_index = rnd.uniform(0.1, 1.0), rnd.uniform(1.0, 2.5)
+        if rnd.random() < 0.5:
+            p = rnd.choice(pats)(rtc.Color(rnd.random(), rnd.random(), rnd.random()), rtc.Color(rnd.random(), rnd.random(), rnd.random()))
+            p.set_transform(rtc.Matrix.identity().scaling(rnd.uniform(0.2, 1), rnd.uniform(0.2, 1), rnd.uniform(0.2, 1))
+                            .rotation_y(rnd.uniform(0, 3)).translation(rnd.uniform(-1, 1), 0, 0))
+            m.set_pattern(p)
+        return m
+
+    w.add_shape(rtc.Plane(rtc.Matrix.identity().translation(0, -1, 0), material()))
+    if rnd.random() < 0.5:
+        w.add_shape(rtc.Plane(rtc.Matrix.identity().rotation_x(math.pi / 2).translation(0, 0, 12), material()))
+    for _ in range(n):
+        m = rtc.Matrix.identity().scaling(rnd.uniform(0.3, 1.5), rnd.uniform(0.3, 1.5), rnd.uniform(0.3, 1.5))
+        m = m.rotation_z(rnd.uniform(0, 3)).rotation_x(rnd.uniform(0, 3)).shearing(rnd.uniform(-.3, .3), 0, 0, rnd.uniform(-.3, .3), 0, 0)
+        m = m.translation(rnd.uniform(-5, 5), rnd.uniform(-0.5, 4), rnd.uniform(-2, 8))
+        w.add_shape(rtc.Sphere(m, material()))
+    # nested glass spheres (containers in compute_refractive, src/shape.rs:115-141)
+    for r, ri in ((2.0, 1.5), (1.4, 2.0), (0.8, 1.2)):
+        w.add_shape(rtc.Sphere(rtc.Matrix.identity().scaling(r, r, r).translation(0, 1.2, 3),
+                               rtc.Material(color=rtc.Color(0.1, 0.1, 0.1), diffuse=0.2, reflectiveness=0.5, transparency=0.9, refractive_index=ri)))
+    cam = rtc.Camera.new_with_transform(120, 90, 1.0, rtc.Matrix.make_view_transform((0, 2.0, -9.0), (0, 1, 3), (0, 1, 0)))
+    return w, cam
+
+
+@pytest.mark.parametrize("seed", [1, 2, 3, 4, 5, 6])
+def test_random_worlds_all_patterns_nested_glass(rtc, orc, renderer, seed):
+    w, cam = _random_world(rtc, seed)
+    _check64(rtc, orc, renderer, w, cam)
+
+
+def test_camera_inside_glass_and_behind_planes(rtc, orc, renderer):
+    """Rays that start inside shapes: negative-t entries count as containers."""
+    w, _ = _random_world(rtc, 9, n=6)
+    cam = rtc.Camera.new_with_transform(80, 60, 1.3, rtc.Matrix.make_view_transform((0.2, 1.3, 2.6), (0, 1.0, 8), (0, 1, 0)))
+    _check64(rtc, orc, renderer, w, cam)
+
+
+def test_aliased_world_ids(rtc, orc, renderer):
+    """More than 255 shapes: world_id wraps (src/shape.rs:661-667, u8) and compute_refractive
+    matches containers by id, so shapes alias.  The device path reproduces that."""
+    rnd = random.Random(5)
+    w = rtc.World(rtc.Light(rtc.Color(1, 1, 1), (-5, 8, -6)))
+    w.add_shape(rtc.Plane(rtc.Matrix.identity(), rtc.Material(reflectiveness=0.3, transparency=0.5, refractive_index=1.3)))
+    for i in range(300):
+        r = rnd.uniform(0.2, 0.9)
+        glass = i % 3 == 0
+        mat = rtc.Material(color=rtc.Color(rnd.random(), rnd.random(), rnd.random()),
+                           transparency=0.9 if glass else 0.0, reflectiveness=0.6 if glass else 0.0,
+                           refractive_index=rnd.uniform(1.1, 2.0))
+        w.add_shape(rtc.Sphere(rtc.Matrix.identity().scaling(r, r, r).translation(rnd.uniform(-4, 4), rnd.uniform(0.2, 3), rnd.uniform(-1, 6)), mat))
+    assert len({s.world_id for s in w.shapes}) < len(w.shapes)
+    cam = rtc.Camera.new_with_transform(96, 64, 1.1, rtc.Matrix.make_view_transform((0, 1.5, -3.0), (0, 1, 3), (0, 1, 0)))
+    _check64(rtc, orc, renderer, w, cam)
+
+
+def test_output_formats(rtc, orc, renderer):
+    world = rtc.scenes.reflect_refract_scene()
+    cam = rtc.scenes.reflect_refract_camera(160, 80)
+    renderer.upload(world)
+    d = cam.flatten()
+    f64, _, _ = renderer.render(d, rtc.Renderer.make_opts(out_format=rtc.ffi.OUT_F64_RGB))
+    f32, _, _ = renderer.render(d, rtc.Renderer.make_opts(out_format=rtc.ffi.OUT_F32_RGB))
+    u8, _, _ = renderer.render(d, rtc.Renderer.make_opts(out_format=rtc.ffi.OUT_U8_RGB))
+    assert np.array_equal(f32, f64.astype(np.float32))
+    assert np.array_equal(u8, orc.quantize_u8(f64))  # Color::scale, src/color.rs:100-114
+
+
+def test_unsupported_inputs_are_errors_not_fallbacks(rtc, renderer):
+    w = rtc.World.default()
+    w.add_shape(rtc.Cube())
+    with pytest.raises(rtc.ffi.RtcError) as e:
+        renderer.upload(w)
+    assert e.value.code == rtc.ffi.RTC_ERR_UNSUPPORTED
+    w2 = rtc.World.default()
+    w2.shapes[0].material.color = None
+    with pytest.raises(rtc.ffi.RtcError):
+        renderer.upload(w2)
+    renderer.upload(rtc.World.default())
+    cam = rtc.Camera.new(16, 16, 1.0)
+    cam.set_samples(4)
+    with pytest.raises(rtc.ffi.RtcError) as e:
+        renderer.render(cam.flatten(), rtc.Renderer.make_opts())
+    assert e.value.code == rtc.ffi.RTC_ERR_UNSUPPORTED
+    fresh = rtc.Renderer([0])
+    with pytest.raises(rtc.ffi.RtcError) as e:
+        fresh.render(rtc.Camera.new(4, 4, 1.0).flatten(), rtc.Renderer.make_opts())
+    assert e.value.code == rtc.ffi.RTC_ERR_NO_SCENE
+
+
+# ---- f32 fast mode ---------------------------------------------------------------------------------
+def _check32(rtc, orc, renderer, world, cam, rect=1, max_depth=5, min_ok=0.999, ray_tol=0.002):
+    renderer.upload(world)
+    want, want_hit, cnt = orc.OracleWorld(world).render(cam, rect=rect, max_depth=max_depth, threads=NCPU)
+    opts = rtc.Renderer.make_opts(precision=rtc.ffi.PRECISION_F32_FAST, rect=rect, max_depth=max_depth,
+                                  out_format=rtc.ffi.OUT_F32_RGB)
+    got, hit, stats = renderer.render(cam.flatten(), opts)
+    assert np.isfinite(got).all()
+    q_got = orc.quantize_u8(got.astype(np.float64)).astype(int)   # Color::scale, src/color.rs:100-114
+    q_want = orc.quantize_u8(want).astype(int)
+    ok = (np.abs(q_got - q_want).max(axis=2) <= 1).mean()
+    assert ok >= min_ok, f"only {ok:.5f} of pixels within 1/255"
+    mask_mismatch = int((hit != want_hit).sum())
+    assert abs(int(stats.rays) - int(cnt.rays)) <= ray_tol * cnt.rays, (stats.rays, cnt.rays)
+    return ok, mask_mismatch, stats
+
+
+@pytest.mark.parametrize("size,samples", [((320, 160), 1), ((400, 200), 1), ((160, 80), 0), ((33, 17), 1)])
+def test_f32_reflect_refract(rtc, orc, renderer, size, samples):
+    world = rtc.scenes.reflect_refract_scene()
+    cam = rtc.scenes.reflect_refract_camera(size[0], size[1], samples=samples)
+    ok, mm, stats = _check32(rtc, orc, renderer, world, cam)
+    assert mm == 0  # closed room: every primary ray hits in both precisions
+
+
+def test_f32_reference_rect_and_formats(rtc, orc, renderer):
+    world = rtc.scenes.reflect_refract_scene()
+    cam = rtc.scenes.reflect_refract_camera(96, 48)
+    renderer.upload(world)
+    d = cam.flatten()
+    mk = lambda fmt: rtc.Renderer.make_opts(precision=rtc.ffi.PRECISION_F32_FAST, rect=rtc.ffi.RECT_REFERENCE_RENDER, out_format=fmt)
+    f32, hit, _ = renderer.render(d, mk(rtc.ffi.OUT_F32_RGB))
+    f64, _, _ = renderer.render(d, mk(rtc.ffi.OUT_F64_RGB))
+    u8, _, _ = renderer.render(d, mk(rtc.ffi.OUT_U8_RGB))
+    assert (f32[47, :] == 0).all() and (f32[:, 95] == 0).all() and (hit[47, :] == 0).all()
+    assert np.array_equal(f64, f32.astype(np.float64))
+    assert np.abs(u8.astype(int) - orc.quantize_u8(f64).astype(int)).max() <= 1
+
+
+def test_f32_bench_scene(rtc, orc, renderer):
+    world, cam = rtc.scenes.bench_scene()
+    _check32(rtc, orc, renderer, world, cam)
+
+
+@pytest.mark.parametrize("seed", [1, 2, 3])
+def test_f32_random_worlds(rtc, orc, renderer, seed):
+    """General affine spheres, all six patterns, nested glass: f32 is held to a looser bar here
+    (pattern edges and grazing refraction amplify rounding); the 99.9 % bar is for the named scenes."""
+    w, cam = _random_world(rtc, seed)
+    _check32(rtc, orc, renderer, w, cam, min_ok=0.98, ray_tol=0.02)
