@@ -26,8 +26,8 @@ namespace {
 constexpr float kEps32 = 1e-4f;
 constexpr float kPlaneEps = 1e-8f;  // abs(d.y) < EPSILON -> parallel (src/shape.rs:463)
 constexpr int kThreads = 128;
-constexpr int kBatch = 128;         // pixels a warp claims per atomic: one 16x8 tile
-constexpr int kTileX = 16, kTileY = 8;
+constexpr int kTileX = 8, kTileY = 4;
+constexpr int kBatch = kTileX * kTileY;  // pixels a warp claims per atomic: one 8x4 tile
 constexpr int kMaxStack = RTC_MAX_DEPTH;
 
 struct F3 { float x, y, z; };
@@ -56,7 +56,7 @@ __device__ __forceinline__ void intersect32(const Streams32& S, F3 o, F3 d, floa
     hit = -1;
     const float a = dot(d, d);
     const float inv_a = __frcp_rn(a);
-#pragma unroll 2
+#pragma unroll 3
     for (int i = 0; i < S.np; ++i) {                     // Plane::intersect_local, src/shape.rs:462-471
         float4 pl = S.planes[i];
         float dy = row3(pl, d);
@@ -64,17 +64,19 @@ __device__ __forceinline__ void intersect32(const Streams32& S, F3 o, F3 d, floa
         float t = -oy * __frcp_rn(dy);
         if (fabsf(dy) >= kPlaneEps && t >= 0.f && t < best_t) { best_t = t; hit = i; }
     }
-#pragma unroll 2
+#pragma unroll 4
     for (int i = 0; i < S.nu; ++i) {                     // Sphere::intersect_local, src/shape.rs:361-375
         float4 sp = S.usph[i];
         F3 L = mk(o.x - sp.x, o.y - sp.y, o.z - sp.z);
         float b = dot(d, L);                             // half of the reference's b
         float c = fmaf(L.z, L.z, fmaf(L.y, L.y, fmaf(L.x, L.x, -sp.w)));
         float disc = fmaf(b, b, -a * c);
-        float s = sqrtf(fmaxf(disc, 0.f));
-        float t1 = (-b - s) * inv_a, t2 = (s - b) * inv_a;
-        float t = t1 >= 0.f ? t1 : t2;
-        if (disc >= 0.f && t >= 0.f && t < best_t) { best_t = t; hit = S.np + i; }
+        if (disc >= 0.f) {                               // most rays miss most spheres: skip the roots
+            float s = sqrtf(disc);
+            float t1 = (-b - s) * inv_a, t2 = (s - b) * inv_a;
+            float t = t1 >= 0.f ? t1 : t2;
+            if (t >= 0.f && t < best_t) { best_t = t; hit = S.np + i; }
+        }
     }
     for (int i = 0; i < S.ng; ++i) {                     // Shape::intersect: ray.transform(inverse) first
         float4 r0 = S.gsph[3 * i], r1 = S.gsph[3 * i + 1], r2 = S.gsph[3 * i + 2];
@@ -112,7 +114,8 @@ __device__ __forceinline__ void offer32(Cont32 e, Cont32& top1, Cont32& top2) {
     else if (top2.idx < 0 || later32(e, top2)) top2 = e;
 }
 
-// Calls f(t, shape_index, root) for every list entry of the ray with t < 0.
+// Calls f(t, shape_index, root, single) for every list entry of the ray with t < 0; `single` says the
+// shape has exactly one negative entry (it contains the ray origin).
 template <typename F>
 __device__ __forceinline__ void for_each_negative(const Streams32& S, F3 o, F3 d, F f) {
     const float a = dot(d, d);
@@ -121,7 +124,7 @@ __device__ __forceinline__ void for_each_negative(const Streams32& S, F3 o, F3 d
         float4 pl = S.planes[i];
         float dy = row3(pl, d), oy = row4(pl, o);
         float t = -oy * __frcp_rn(dy);
-        if (fabsf(dy) >= kPlaneEps && t < 0.f) f(t, S.pl_index[i], 0);
+        if (fabsf(dy) >= kPlaneEps && t < 0.f) f(t, S.pl_index[i], 0, true);
     }
     for (int i = 0; i < S.nu; ++i) {
         float4 sp = S.usph[i];
@@ -132,8 +135,8 @@ __device__ __forceinline__ void for_each_negative(const Streams32& S, F3 o, F3 d
         if (disc >= 0.f) {
             float s = sqrtf(disc);
             float t1 = (-b - s) * inv_a, t2 = (s - b) * inv_a;
-            if (t1 < 0.f) f(t1, S.us_index[i], 0);
-            if (t2 < 0.f) f(t2, S.us_index[i], 1);
+            if (t1 < 0.f) f(t1, S.us_index[i], 0, !(t2 < 0.f));
+            if (t2 < 0.f) f(t2, S.us_index[i], 1, false);
         }
     }
     for (int i = 0; i < S.ng; ++i) {
@@ -145,8 +148,8 @@ __device__ __forceinline__ void for_each_negative(const Streams32& S, F3 o, F3 d
         if (disc >= 0.f) {
             float s = sqrtf(disc), inv = __frcp_rn(la);
             float t1 = (-b - s) * inv, t2 = (s - b) * inv;
-            if (t1 < 0.f) f(t1, S.gs_index[i], 0);
-            if (t2 < 0.f) f(t2, S.gs_index[i], 1);
+            if (t1 < 0.f) f(t1, S.gs_index[i], 0, !(t2 < 0.f));
+            if (t2 < 0.f) f(t2, S.gs_index[i], 1, false);
         }
     }
 }
@@ -156,13 +159,13 @@ __device__ __noinline__ void compute_refractive32(const Streams32& S, const Shad
     unsigned parity[8];
 #pragma unroll
     for (int k = 0; k < 8; ++k) parity[k] = 0u;
-    for_each_negative(S, o, d, [&](float, int idx, int) {
+    for_each_negative(S, o, d, [&](float, int idx, int, bool) {
         int id = __float_as_int(rec[idx].pa.w) & 255;
         parity[id >> 5] ^= 1u << (id & 31);
     });
     Cont32 top1, top2;
     top1.idx = -1; top2.idx = -1; top1.t = top2.t = 0.f; top1.ord = top2.ord = 0; top1.id = top2.id = -1;
-    for_each_negative(S, o, d, [&](float t, int idx, int root) {
+    for_each_negative(S, o, d, [&](float t, int idx, int root, bool) {
         int id = __float_as_int(rec[idx].pa.w) & 255;
         if ((parity[id >> 5] >> (id & 31)) & 1u) {
             Cont32 e; e.t = t; e.ord = 2 * idx + root; e.idx = idx; e.id = id;
@@ -193,38 +196,119 @@ __device__ __forceinline__ F3 pattern_at32(int kind, F3 a, F3 b, F3 p) {
 }
 
 
-enum { ST_IDLE = 0, ST_RADIANCE = 1, ST_SHADOW = 2, ST_DEAD = 3 };
+// World::is_shadowed_by_light (src/shape.rs:716-727) as an ANY-hit test.  The reference takes the
+// nearest hit of the shadow ray and asks `h.t < distance`; that is true iff some shape has a root
+// in [0, distance).  With d = light - p the question is "a root in [0,1)", which for
+// a plane is a sign change of f(t) = n.(p + t d) + w between t=0 and t=1, and for a sphere needs
+// no square root: f(0) f(1) < 0 (one root inside) or both roots inside.  f(1) depends only on the
+// light and is precomputed per shape (plL / usL, staged beside the streams).
+__device__ __forceinline__ bool shadow32(const Streams32& S, const float* __restrict__ plL, const float* __restrict__ usL,
+                                         F3 o, F3 d) {
+    bool hit = false;
+    const float a = dot(d, d);
+#pragma unroll 3
+    for (int i = 0; i < S.np; ++i) {
+        float4 pl = S.planes[i];
+        float f0 = row4(pl, o);
+        hit |= (f0 * plL[i] < 0.f) || f0 == 0.f;
+    }
+#pragma unroll 4
+    for (int i = 0; i < S.nu; ++i) {
+        float4 sp = S.usph[i];
+        F3 L = mk(o.x - sp.x, o.y - sp.y, o.z - sp.z);
+        float f0 = fmaf(L.z, L.z, fmaf(L.y, L.y, fmaf(L.x, L.x, -sp.w)));
+        float f1 = usL[i];
+        float b = dot(d, L);
+        float disc = fmaf(b, b, -a * f0);
+        bool both_in = disc >= 0.f && f0 >= 0.f && f1 >= 0.f && b < 0.f && -b < a;
+        hit |= (f0 * f1 < 0.f) || both_in;
+    }
+    if (S.ng > 0) {  // genuinely affine spheres: nearest-root test in object space
+        for (int i = 0; i < S.ng; ++i) {
+            float4 r0 = S.gsph[3 * i], r1 = S.gsph[3 * i + 1], r2 = S.gsph[3 * i + 2];
+            F3 lo = mk(row4(r0, o), row4(r1, o), row4(r2, o));
+            F3 ld = mk(row3(r0, d), row3(r1, d), row3(r2, d));
+            float la = dot(ld, ld), b = dot(ld, lo), c = dot(lo, lo) - 1.f;
+            float disc = fmaf(b, b, -la * c);
+            if (disc >= 0.f) {
+                float s = sqrtf(disc), inv = __frcp_rn(la);
+                float t1 = (-b - s) * inv, t2 = (s - b) * inv;
+                float t = t1 >= 0.f ? t1 : t2;
+                hit |= t >= 0.f && t < 1.f;
+            }
+        }
+    }
+    return hit;
+}
+
+// compute_refractive when every world_id is unique (<= 255 shapes): a shape is a container iff it
+// has exactly one negative-t entry (plane: t < 0; sphere: t1 < 0 <= t2), so one pass that keeps the
+// last two containers by (t, shape index) is enough.
+__device__ __noinline__ void compute_refractive32_unique(const Streams32& S, const ShadeRec32* rec, F3 o, F3 d, int hit_idx,
+                                                         float& n1, float& n2) {
+    float t1st = -__int_as_float(0x7f800000), t2nd = t1st;
+    int i1st = -1, i2nd = -1;
+    bool hit_is_container = false;
+    for_each_negative(S, o, d, [&](float t, int idx, int, bool single) {
+        if (!single) return;  // both roots negative: entered and left again -> not a container
+        if (idx == hit_idx) hit_is_container = true;
+        if (t > t1st || (t == t1st && idx > i1st)) { t2nd = t1st; i2nd = i1st; t1st = t; i1st = idx; }
+        else if (t > t2nd || (t == t2nd && idx > i2nd)) { t2nd = t; i2nd = idx; }
+    });
+    n1 = i1st >= 0 ? rec[i1st].tr_ri.y : 1.0f;
+    if (hit_is_container) {
+        if (i1st == hit_idx) n2 = i2nd >= 0 ? rec[i2nd].tr_ri.y : 1.0f;
+        else n2 = i1st >= 0 ? rec[i1st].tr_ri.y : 1.0f;
+    } else {
+        n2 = rec[hit_idx].tr_ri.y;
+    }
+}
 
 template <bool kSmem>
-__global__ void __launch_bounds__(kThreads, 4)
+__global__ void __launch_bounds__(kThreads, 5)
 render_f32_kernel(DevScene32 sc, CamParams cam, void* __restrict__ out_rgb, uint8_t* __restrict__ out_hit,
                   Counters* __restrict__ counters, unsigned* __restrict__ work) {
     extern __shared__ float4 smem4[];
     Streams32 S;
     S.np = sc.n_planes; S.nu = sc.n_usph; S.ng = sc.n_gsph;
     const ShadeRec32* R = sc.rec;
-    if (kSmem) {
-        // stage the intersect streams and the shading records: coalesced 16-byte loads
+    const float* plL;  // f(1) of the shadow test per plane / per uniform sphere (depends on the light only)
+    const float* usL;
+    const F3 light_pos = mk(sc.light_pos[0], sc.light_pos[1], sc.light_pos[2]);
+    const F3 light_int = mk(sc.light_int[0], sc.light_int[1], sc.light_int[2]);
+    {
+        // stage the intersect streams (and, when small, the shading records): coalesced 16-byte loads
         float4* s_pl = smem4;
         float4* s_us = s_pl + S.np;
         float4* s_gs = s_us + S.nu;
         float4* s_rec = s_gs + 3 * S.ng;
-        const int rec4 = (int)(sizeof(ShadeRec32) / 16) * sc.n_shapes;
+        const int rec4 = kSmem ? (int)(sizeof(ShadeRec32) / 16) * sc.n_shapes : 0;
         int32_t* s_pi = reinterpret_cast<int32_t*>(s_rec + rec4);
         int32_t* s_ui = s_pi + S.np;
         int32_t* s_gi = s_ui + S.nu;
-        for (int i = threadIdx.x; i < S.np; i += kThreads) { s_pl[i] = sc.planes[i]; s_pi[i] = sc.pl_index[i]; }
-        for (int i = threadIdx.x; i < S.nu; i += kThreads) { s_us[i] = sc.usph[i]; s_ui[i] = sc.us_index[i]; }
+        float* s_plL = reinterpret_cast<float*>(s_gi + S.ng);
+        float* s_usL = s_plL + S.np;
+        for (int i = threadIdx.x; i < S.np; i += kThreads) {
+            float4 p = sc.planes[i];
+            s_pl[i] = p; s_pi[i] = sc.pl_index[i];
+            s_plL[i] = row4(p, light_pos);
+        }
+        for (int i = threadIdx.x; i < S.nu; i += kThreads) {
+            float4 p = sc.usph[i];
+            s_us[i] = p; s_ui[i] = sc.us_index[i];
+            F3 L = mk(light_pos.x - p.x, light_pos.y - p.y, light_pos.z - p.z);
+            s_usL[i] = dot(L, L) - p.w;
+        }
         for (int i = threadIdx.x; i < 3 * S.ng; i += kThreads) s_gs[i] = sc.gsph[i];
         for (int i = threadIdx.x; i < S.ng; i += kThreads) s_gi[i] = sc.gs_index[i];
-        const float4* g_rec = reinterpret_cast<const float4*>(sc.rec);
-        for (int i = threadIdx.x; i < rec4; i += kThreads) s_rec[i] = g_rec[i];
+        if (kSmem) {
+            const float4* g_rec = reinterpret_cast<const float4*>(sc.rec);
+            for (int i = threadIdx.x; i < rec4; i += kThreads) s_rec[i] = g_rec[i];
+            R = reinterpret_cast<const ShadeRec32*>(s_rec);
+        }
         __syncthreads();
         S.planes = s_pl; S.usph = s_us; S.gsph = s_gs; S.pl_index = s_pi; S.us_index = s_ui; S.gs_index = s_gi;
-        R = reinterpret_cast<const ShadeRec32*>(s_rec);
-    } else {
-        S.planes = sc.planes; S.usph = sc.usph; S.gsph = sc.gsph;
-        S.pl_index = sc.pl_index; S.us_index = sc.us_index; S.gs_index = sc.gs_index;
+        plL = s_plL; usL = s_usL;
     }
 
     const unsigned full = 0xffffffffu;
@@ -235,66 +319,61 @@ render_f32_kernel(DevScene32 sc, CamParams cam, void* __restrict__ out_rgb, uint
     const unsigned total_tiles = (unsigned)(tiles_x * tiles_y);
     const int n_sub = cam.samples == 1 ? 1 : 4;
     const float w0 = cam.samples == 1 ? 1.0f : 0.25f;
-    const F3 light_pos = mk(sc.light_pos[0], sc.light_pos[1], sc.light_pos[2]);
-    const F3 light_int = mk(sc.light_int[0], sc.light_int[1], sc.light_int[2]);
     const F3 cam_origin = mk((float)cam.vinv[3], (float)cam.vinv[7], (float)cam.vinv[11]);  // Vinv * (0,0,0)
+    const bool ids_unique = sc.ids_unique != 0;
 
-    // warp-uniform work state
-    unsigned wtile = 0;
+    unsigned wtile = 0;       // warp-uniform: the tile being handed out, next pixel in it
     int wnext = kBatch;
     bool exhausted = false;
-    // lane state
-    int st = ST_IDLE;
-    F3 ro = mk(0, 0, 0), rd = mk(0, 0, 1);   // current radiance ray
-    float rw = 0.f;                            // its path weight
+    bool has_ray = false, dead = false;
+    F3 ro = mk(0, 0, 0), rd = mk(0, 0, 1);
+    float rw = 0.f;
     int remaining = 0;
     bool is_primary = false;
-    F3 hp = mk(0, 0, 0), hn = mk(0, 1, 0);   // pending hit: over_point, normal
-    int hidx = 0;
-    float hn1 = 1.f, hn2 = 1.f;
-    bool have = false;                         // owns a pixel
+    bool have = false;
     int px = 0, pr = 0, py = 0, sub = 0;
     F3 acc = mk(0, 0, 0);
     unsigned hitbits = 0;
     float4 stk_a[kMaxStack], stk_b[kMaxStack];  // pending refraction rays: (o, w), (d, remaining)
     int sp = 0;
-    unsigned n_rays = 0, n_shadow = 0, n_shaded = 0, n_phits = 0;
+    unsigned n_rays = 0, n_shaded = 0, n_phits = 0;
 
     for (;;) {
-        // ------------------------------------------------------------------ refill idle lanes
-        if (st == ST_IDLE && sp > 0) {
+        // ---------------------------------------------------------------- refill lanes without a ray
+        if (!has_ray && sp > 0) {
             --sp;
             float4 a = stk_a[sp], b = stk_b[sp];
             ro = xyz(a); rw = a.w; rd = xyz(b); remaining = __float_as_int(b.w);
-            is_primary = false;
-            st = ST_RADIANCE;
+            is_primary = false; has_ray = true;
         }
-        if (st == ST_IDLE && have && sub + 1 < n_sub) ++sub;  // next sub-sample of the same pixel
-        else if (st == ST_IDLE && have) {
-            // pixel finished: Canvas::write_pixel (src/canvas.rs:43-46)
-            size_t p = (size_t)pr * cam.hsize + px;
-            if (cam.out_format == RTC_OUT_F64_RGB) {
-                double* o = (double*)out_rgb + 3 * p;
-                o[0] = (double)acc.x; o[1] = (double)acc.y; o[2] = (double)acc.z;
-            } else if (cam.out_format == RTC_OUT_F32_RGB) {
-                float* o = (float*)out_rgb + 3 * p;
-                o[0] = acc.x; o[1] = acc.y; o[2] = acc.z;
-            } else {
-                uint8_t* o = (uint8_t*)out_rgb + 3 * p;  // Color::scale, src/color.rs:100-114
-                float c3[3] = {acc.x, acc.y, acc.z};
+        if (!has_ray && have) {
+            if (sub + 1 < n_sub) ++sub;   // next sub-sample of the same pixel
+            else {
+                // pixel finished: Canvas::write_pixel (src/canvas.rs:43-46)
+                size_t p = (size_t)pr * cam.hsize + px;
+                if (cam.out_format == RTC_OUT_F64_RGB) {
+                    double* o = (double*)out_rgb + 3 * p;
+                    o[0] = (double)acc.x; o[1] = (double)acc.y; o[2] = (double)acc.z;
+                } else if (cam.out_format == RTC_OUT_F32_RGB) {
+                    float* o = (float*)out_rgb + 3 * p;
+                    o[0] = acc.x; o[1] = acc.y; o[2] = acc.z;
+                } else {
+                    uint8_t* o = (uint8_t*)out_rgb + 3 * p;  // Color::scale, src/color.rs:100-114
+                    float c3[3] = {acc.x, acc.y, acc.z};
 #pragma unroll
-                for (int k = 0; k < 3; ++k) {
-                    float s = c3[k] * 255.0f;
-                    int q = s != s ? 0 : (s >= 2147483520.0f ? 2147483647 : (s <= -2147483648.0f ? (-2147483647 - 1) : (int)s));
-                    o[k] = (uint8_t)(q < 0 ? 0 : (q > 255 ? 255 : q));
+                    for (int k = 0; k < 3; ++k) {
+                        float s = c3[k] * 255.0f;
+                        int q = s != s ? 0 : (s >= 2147483520.0f ? 2147483647 : (s <= -2147483648.0f ? (-2147483647 - 1) : (int)s));
+                        o[k] = (uint8_t)(q < 0 ? 0 : (q > 255 ? 255 : q));
+                    }
                 }
+                if (out_hit) out_hit[p] = (uint8_t)hitbits;
+                have = false;
             }
-            if (out_hit) out_hit[p] = (uint8_t)hitbits;
-            have = false;
         }
-        // lanes without a pixel claim the next ones of the warp's tile (ballot/popc rank)
+        // lanes without a pixel claim the next ones of the warp's tile (ballot + popc rank)
         for (;;) {
-            bool need = st == ST_IDLE && !have;
+            bool need = !has_ray && !have && !dead;
             unsigned m = __ballot_sync(full, need);
             if (m == 0u || exhausted) break;
             if (wnext >= kBatch) {
@@ -310,7 +389,7 @@ render_f32_kernel(DevScene32 sc, CamParams cam, void* __restrict__ out_rgb, uint
                 int k = wnext + rank;
                 int tx = (int)(wtile % (unsigned)tiles_x), ty = (int)(wtile / (unsigned)tiles_x);
                 px = tx * kTileX + (k & (kTileX - 1));
-                pr = ty * kTileY + (k >> 4);
+                pr = ty * kTileY + k / kTileX;
                 if (px < (int)cam.hsize && pr < cam.shard_rows) {
                     py = cam.shard_count > 1 ? shard_row_to_frame_row(pr, cam.tile_rows, cam.shard_index, cam.shard_count) : pr;
                     have = true; sub = 0; acc = mk(0, 0, 0); hitbits = 0;
@@ -319,8 +398,8 @@ render_f32_kernel(DevScene32 sc, CamParams cam, void* __restrict__ out_rgb, uint
             }
             wnext += take;
         }
-        if (st == ST_IDLE && have && sub < n_sub) {
-            // Camera::ray_for_pixel_offset (src/camera.rs:64-76); the pixel position in f64, once per sample
+        if (!has_ray && have && sub < n_sub) {
+            // Camera::ray_for_pixel_offset (src/camera.rs:64-76); pixel position in f64, once per sample
             double xo = n_sub == 1 ? 0.5 : ((sub & 1) ? 0.75 : 0.25);
             double yo = n_sub == 1 ? 0.5 : ((sub & 2) ? 0.75 : 0.25);
             double wx = cam.half_width - ((double)px + xo) * cam.pixel_size;
@@ -329,52 +408,50 @@ render_f32_kernel(DevScene32 sc, CamParams cam, void* __restrict__ out_rgb, uint
                         (float)(cam.vinv[4] * wx + cam.vinv[5] * wy - cam.vinv[6]),
                         (float)(cam.vinv[8] * wx + cam.vinv[9] * wy - cam.vinv[10]));
             rd = dir * rsqrtf(dot(dir, dir));
-            ro = cam_origin; rw = w0; remaining = cam.max_depth; is_primary = true;
-            st = ST_RADIANCE;
+            ro = cam_origin; rw = w0; remaining = cam.max_depth; is_primary = true; has_ray = true;
         }
-        if (st == ST_IDLE && !have && exhausted) st = ST_DEAD;
-        if (!__any_sync(full, st != ST_DEAD)) break;
-        if (st == ST_IDLE) continue;  // e.g. a pixel outside the rect: finalise it next round
+        if (!has_ray && !have && exhausted) dead = true;
+        if (__all_sync(full, dead)) break;
 
-        // ------------------------------------------------------------------ one World::intersect per lane
-        F3 io, id;
-        float tmax;
-        if (st == ST_SHADOW) { io = hp; id = light_pos - hp; tmax = 1.0f; }   // is_shadowed_by_light, src/shape.rs:716-727
-        else { io = ro; id = rd; tmax = __int_as_float(0x7f800000); }
+        // ---------------------------------------------------------------- phase A: World::intersect, radiance rays
+        float t = __int_as_float(0x7f800000);
         int hit = -1;
-        if (st != ST_DEAD) { intersect32(S, io, id, tmax, hit); ++n_rays; }
+        if (has_ray) { intersect32(S, ro, rd, t, hit); ++n_rays; }
+        if (has_ray && is_primary && hit >= 0) { hitbits |= 1u << sub; ++n_phits; }
+        if (hit < 0) has_ray = false;   // World::color_at -> background_color (black), src/shape.rs:708
 
-        if (st == ST_RADIANCE) {
-            // ---- World::color_at: hit or background (src/shape.rs:702-710) ----
-            if (is_primary && hit >= 0) { hitbits |= 1u << sub; ++n_phits; }
-            if (hit < 0) {
-                st = ST_IDLE;
-            } else {
-                const int idx = stream_to_shape(S, hit);
-                const ShadeRec32& rec = R[idx];
-                const float4 tr = rec.tr_ri;
-                const int geom = __float_as_int(tr.w);
-                F3 p = fma3(rd, tmax, ro);                       // Ray::position
-                F3 n;
-                if (geom == GEOM_PLANE) n = xyz(rec.g0);
-                else if (geom == GEOM_USPHERE) { float4 g = rec.g0; n = (p - xyz(g)) * g.w; }
-                else {                                            // Shape::normal_at, src/shape.rs:34-40
-                    F3 lp = mk(row4(rec.g0, p), row4(rec.g1, p), row4(rec.g2, p));
-                    F3 wn = mk(row3(rec.t0, lp), row3(rec.t1, lp), row3(rec.t2, lp));
-                    n = wn * rsqrtf(dot(wn, wn));
-                }
-                hn1 = 1.f; hn2 = 1.f;
-                if (tr.x != 0.f) compute_refractive32(S, R, ro, rd, idx, hn1, hn2);
-                if (dot(n, rd) > 0.f) n = mk(-n.x, -n.y, -n.z);  // inside: normal . eyev < 0  (src/shape.rs:77-78)
-                hn = n;
-                hp = fma3(n, kEps32, p);                         // over_point
-                hidx = idx;
-                st = ST_SHADOW;
+        // ---------------------------------------------------------------- phase B: prepare_computations
+        F3 hp = mk(0, 0, 0), hn = mk(0, 1, 0);
+        float hn1 = 1.f, hn2 = 1.f;
+        int hidx = 0;
+        if (hit >= 0) {
+            hidx = stream_to_shape(S, hit);
+            const ShadeRec32& rec = R[hidx];
+            const float4 tr = rec.tr_ri;
+            const int geom = __float_as_int(tr.w);
+            F3 p = fma3(rd, t, ro);                              // Ray::position
+            if (geom == GEOM_PLANE) hn = xyz(rec.g0);
+            else if (geom == GEOM_USPHERE) { float4 g = rec.g0; hn = (p - xyz(g)) * g.w; }
+            else {                                                // Shape::normal_at, src/shape.rs:34-40
+                F3 lp = mk(row4(rec.g0, p), row4(rec.g1, p), row4(rec.g2, p));
+                F3 wn = mk(row3(rec.t0, lp), row3(rec.t1, lp), row3(rec.t2, lp));
+                hn = wn * rsqrtf(dot(wn, wn));
             }
-        } else if (st == ST_SHADOW) {
-            // ---- shade_hit (src/shape.rs:685-700) with Material::lighting (src/material.rs:319-361) ----
-            ++n_shadow; ++n_shaded;
-            const bool shadowed = hit >= 0;
+            if (tr.x != 0.f) {                                    // Intersection::compute_refractive
+                if (ids_unique) compute_refractive32_unique(S, R, ro, rd, hidx, hn1, hn2);
+                else compute_refractive32(S, R, ro, rd, hidx, hn1, hn2);
+            }
+            if (dot(hn, rd) > 0.f) hn = mk(-hn.x, -hn.y, -hn.z);  // inside: normal . eyev < 0 (src/shape.rs:77-78)
+            hp = fma3(hn, kEps32, p);                             // over_point
+        }
+
+        // ---------------------------------------------------------------- phase C: is_shadowed (any-hit)
+        bool shadowed = false;
+        if (hit >= 0) { shadowed = shadow32(S, plL, usL, hp, light_pos - hp); ++n_rays; ++n_shaded; }
+
+        // ---------------------------------------------------------------- phase D: shade_hit
+        if (hit >= 0) {
+            // Material::lighting (src/material.rs:319-361) at over_point
             const ShadeRec32& rec = R[hidx];
             const float4 ca = rec.col_amb, ds = rec.dif_spec, tr = rec.tr_ri;
             const int pkind = __float_as_int(tr.z);
@@ -441,22 +518,19 @@ render_f32_kernel(DevScene32 sc, CamParams cam, void* __restrict__ out_rgb, uint
                 float dn = dot(rd, hn);
                 rd = fma3(hn, -2.f * dn, rd);                          // reflectv = d.reflect(n)
                 ro = hp; rw = refl_w; --remaining;
-                st = ST_RADIANCE;
             } else if (want_refr) {
                 ro = fo; rd = fd; rw = refr_w; --remaining;
-                st = ST_RADIANCE;
             } else {
-                st = ST_IDLE;
+                has_ray = false;
             }
         }
     }
 
     if (counters) {
-        unsigned r = __reduce_add_sync(full, n_rays), s = __reduce_add_sync(full, n_shadow);
-        unsigned h = __reduce_add_sync(full, n_shaded), ph = __reduce_add_sync(full, n_phits);
+        unsigned r = __reduce_add_sync(full, n_rays), h = __reduce_add_sync(full, n_shaded), ph = __reduce_add_sync(full, n_phits);
         if (lane == 0) {
             atomicAdd(&counters->rays, (unsigned long long)r);
-            atomicAdd(&counters->shadow_rays, (unsigned long long)s);
+            atomicAdd(&counters->shadow_rays, (unsigned long long)h);
             atomicAdd(&counters->shaded_hits, (unsigned long long)h);
             atomicAdd(&counters->primary_hits, (unsigned long long)ph);
         }
@@ -473,17 +547,24 @@ cudaError_t launch_render_f32(const DevScene32& scene, const CamParams& cam, voi
     int dev = 0, sms = 0;
     cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-    size_t smem = (size_t)(scene.n_planes + scene.n_usph + 3 * scene.n_gsph) * 16 + (size_t)scene.n_shapes * (sizeof(ShadeRec32) + 4) + 16;
+    const size_t streams = (size_t)(scene.n_planes + scene.n_usph + 3 * scene.n_gsph) * 16 +
+                           (size_t)(scene.n_planes + scene.n_usph + scene.n_gsph) * 4 + (size_t)(scene.n_planes + scene.n_usph) * 4 + 16;
+    const size_t recs = (size_t)scene.n_shapes * sizeof(ShadeRec32);
     const int tiles = ((cam.hsize + kTileX - 1) / kTileX) * ((cam.shard_rows + kTileY - 1) / kTileY);
+    const int warps = kThreads / 32;
     int blocks_per_sm = 0;
-    if (smem <= 48 * 1024) {
+    if (streams + recs <= 40 * 1024) {
+        size_t smem = streams + recs;
         cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks_per_sm, render_f32_kernel<true>, kThreads, smem);
-        int grid = max(1, min(sms * max(blocks_per_sm, 1), (tiles + 3) / 4));
+        int grid = max(1, min(sms * max(blocks_per_sm, 1), (tiles + warps - 1) / warps));
         render_f32_kernel<true><<<grid, kThreads, smem, stream>>>(scene, cam, d_rgb, d_hit, d_counters, d_work);
     } else {
-        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks_per_sm, render_f32_kernel<false>, kThreads, 0);
-        int grid = max(1, min(sms * max(blocks_per_sm, 1), (tiles + 3) / 4));
-        render_f32_kernel<false><<<grid, kThreads, 0, stream>>>(scene, cam, d_rgb, d_hit, d_counters, d_work);
+        if (streams > 200 * 1024) return cudaErrorInvalidConfiguration;  // TODO(C4): tiled streaming of big scenes
+        e = cudaFuncSetAttribute(render_f32_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)streams);
+        if (e != cudaSuccess) return e;
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks_per_sm, render_f32_kernel<false>, kThreads, streams);
+        int grid = max(1, min(sms * max(blocks_per_sm, 1), (tiles + warps - 1) / warps));
+        render_f32_kernel<false><<<grid, kThreads, streams, stream>>>(scene, cam, d_rgb, d_hit, d_counters, d_work);
     }
     return cudaGetLastError();
 }
