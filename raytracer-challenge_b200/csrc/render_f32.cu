@@ -40,6 +40,7 @@ __device__ __forceinline__ float dot(F3 a, F3 b) { return fmaf(a.z, b.z, fmaf(a.
 __device__ __forceinline__ F3 fma3(F3 a, float m, F3 c) { return mk(fmaf(a.x, m, c.x), fmaf(a.y, m, c.y), fmaf(a.z, m, c.z)); }
 __device__ __forceinline__ F3 xyz(float4 v) { return mk(v.x, v.y, v.z); }
 __device__ __forceinline__ float row4(float4 r, F3 p) { return fmaf(r.z, p.z, fmaf(r.y, p.y, fmaf(r.x, p.x, r.w))); }
+__device__ __forceinline__ float rcp(float x) { float r; asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }  // MUFU.RCP
 __device__ __forceinline__ float row3(float4 r, F3 p) { return fmaf(r.z, p.z, fmaf(r.y, p.y, r.x * p.x)); }
 
 struct Streams32 {
@@ -55,14 +56,14 @@ struct Streams32 {
 __device__ __forceinline__ void intersect32(const Streams32& S, F3 o, F3 d, float& best_t, int& hit) {
     hit = -1;
     const float a = dot(d, d);
-    const float inv_a = __frcp_rn(a);
+    const float inv_a = rcp(a);
 #pragma unroll 3
     for (int i = 0; i < S.np; ++i) {                     // Plane::intersect_local, src/shape.rs:462-471
         float4 pl = S.planes[i];
         float dy = row3(pl, d);
         float oy = row4(pl, o);
-        float t = -oy * __frcp_rn(dy);
-        if (fabsf(dy) >= kPlaneEps && t >= 0.f && t < best_t) { best_t = t; hit = i; }
+        float t = -oy * rcp(dy);
+        if (t >= 0.f && t < best_t) { best_t = t; hit = i; }  // dy ~ 0 -> t = +-inf or NaN: never taken
     }
 #pragma unroll 4
     for (int i = 0; i < S.nu; ++i) {                     // Sphere::intersect_local, src/shape.rs:361-375
@@ -85,7 +86,7 @@ __device__ __forceinline__ void intersect32(const Streams32& S, F3 o, F3 d, floa
         float la = dot(ld, ld), b = dot(ld, lo), c = dot(lo, lo) - 1.f;
         float disc = fmaf(b, b, -la * c);
         float s = sqrtf(fmaxf(disc, 0.f));
-        float inv = __frcp_rn(la);
+        float inv = rcp(la);
         float t1 = (-b - s) * inv, t2 = (s - b) * inv;
         float t = t1 >= 0.f ? t1 : t2;
         if (disc >= 0.f && t >= 0.f && t < best_t) { best_t = t; hit = S.np + S.nu + i; }
@@ -119,12 +120,12 @@ __device__ __forceinline__ void offer32(Cont32 e, Cont32& top1, Cont32& top2) {
 template <typename F>
 __device__ __forceinline__ void for_each_negative(const Streams32& S, F3 o, F3 d, F f) {
     const float a = dot(d, d);
-    const float inv_a = __frcp_rn(a);
+    const float inv_a = rcp(a);
     for (int i = 0; i < S.np; ++i) {
         float4 pl = S.planes[i];
         float dy = row3(pl, d), oy = row4(pl, o);
-        float t = -oy * __frcp_rn(dy);
-        if (fabsf(dy) >= kPlaneEps && t < 0.f) f(t, S.pl_index[i], 0, true);
+        float t = -oy * rcp(dy);
+        if (t < 0.f) f(t, S.pl_index[i], 0, true);
     }
     for (int i = 0; i < S.nu; ++i) {
         float4 sp = S.usph[i];
@@ -146,7 +147,7 @@ __device__ __forceinline__ void for_each_negative(const Streams32& S, F3 o, F3 d
         float la = dot(ld, ld), b = dot(ld, lo), c = dot(lo, lo) - 1.f;
         float disc = fmaf(b, b, -la * c);
         if (disc >= 0.f) {
-            float s = sqrtf(disc), inv = __frcp_rn(la);
+            float s = sqrtf(disc), inv = rcp(la);
             float t1 = (-b - s) * inv, t2 = (s - b) * inv;
             if (t1 < 0.f) f(t1, S.gs_index[i], 0, !(t2 < 0.f));
             if (t2 < 0.f) f(t2, S.gs_index[i], 1, false);
@@ -183,14 +184,17 @@ __device__ __noinline__ void compute_refractive32(const Streams32& S, const Shad
     }
 }
 
+// floor(x) % 2.0 == 0.0 (Rust % = fmod): is the integer-valued float v even?
+__device__ __forceinline__ bool is_even(float v) { float h = v * 0.5f; return h == floorf(h); }
+
 // Pattern::pattern_at (src/material.rs:67-69,97-103,133-135,163-170,198-205,233-241)
 __device__ __forceinline__ F3 pattern_at32(int kind, F3 a, F3 b, F3 p) {
     switch (kind) {
         case RTC_PATTERN_TEST: return p;
-        case RTC_PATTERN_STRIPE: return fmodf(floorf(p.x), 2.0f) == 0.f ? a : b;
+        case RTC_PATTERN_STRIPE: return is_even(floorf(p.x)) ? a : b;
         case RTC_PATTERN_GRADIENT: return fma3(b - a, p.x - floorf(p.x), a);
-        case RTC_PATTERN_RING: return fmodf(floorf(sqrtf(fmaf(p.x, p.x, p.y * p.y))), 2.0f) == 0.f ? a : b;
-        case RTC_PATTERN_CHECKER: return fmodf(floorf(p.x) + floorf(p.y) + floorf(p.z), 2.0f) == 0.f ? a : b;
+        case RTC_PATTERN_RING: return is_even(floorf(sqrtf(fmaf(p.x, p.x, p.y * p.y)))) ? a : b;
+        case RTC_PATTERN_CHECKER: return is_even(floorf(p.x) + floorf(p.y) + floorf(p.z)) ? a : b;
         default: return (fabsf(p.x - floorf(p.x)) < 0.01f || fabsf(p.z - floorf(p.z)) < 0.01f) ? b : a;
     }
 }
@@ -206,22 +210,24 @@ __device__ __forceinline__ bool shadow32(const Streams32& S, const float* __rest
                                          F3 o, F3 d) {
     bool hit = false;
     const float a = dot(d, d);
+    const float inv_a = rcp(a);
 #pragma unroll 3
     for (int i = 0; i < S.np; ++i) {
         float4 pl = S.planes[i];
         float f0 = row4(pl, o);
-        hit |= (f0 * plL[i] < 0.f) || f0 == 0.f;
+        hit |= f0 * plL[i] <= 0.f;                     // f(0) and f(1) on opposite sides
     }
 #pragma unroll 4
     for (int i = 0; i < S.nu; ++i) {
         float4 sp = S.usph[i];
         F3 L = mk(o.x - sp.x, o.y - sp.y, o.z - sp.z);
         float f0 = fmaf(L.z, L.z, fmaf(L.y, L.y, fmaf(L.x, L.x, -sp.w)));
-        float f1 = usL[i];
         float b = dot(d, L);
-        float disc = fmaf(b, b, -a * f0);
-        bool both_in = disc >= 0.f && f0 >= 0.f && f1 >= 0.f && b < 0.f && -b < a;
-        hit |= (f0 * f1 < 0.f) || both_in;
+        // f(t) = a t^2 + 2 b t + f0 is convex: its minimum over [0,1] is at clamp(-b/a); a root lies
+        // in [0,1] iff that minimum is <= 0 and the segment is not entirely inside (max(f0,f1) >= 0)
+        float tc = __saturatef(-b * inv_a);
+        float fmin = fmaf(tc, fmaf(a, tc, b + b), f0);
+        hit |= fmin <= 0.f && fmaxf(f0, usL[i]) >= 0.f;
     }
     if (S.ng > 0) {  // genuinely affine spheres: nearest-root test in object space
         for (int i = 0; i < S.ng; ++i) {
@@ -231,7 +237,7 @@ __device__ __forceinline__ bool shadow32(const Streams32& S, const float* __rest
             float la = dot(ld, ld), b = dot(ld, lo), c = dot(lo, lo) - 1.f;
             float disc = fmaf(b, b, -la * c);
             if (disc >= 0.f) {
-                float s = sqrtf(disc), inv = __frcp_rn(la);
+                float s = sqrtf(disc), inv = rcp(la);
                 float t1 = (-b - s) * inv, t2 = (s - b) * inv;
                 float t = t1 >= 0.f ? t1 : t2;
                 hit |= t >= 0.f && t < 1.f;
