@@ -57,7 +57,7 @@ __device__ __forceinline__ void intersect32(const Streams32& S, F3 o, F3 d, floa
     hit = -1;
     const float a = dot(d, d);
     const float inv_a = rcp(a);
-#pragma unroll 3
+#pragma unroll 2
     for (int i = 0; i < S.np; ++i) {                     // Plane::intersect_local, src/shape.rs:462-471
         float4 pl = S.planes[i];
         float dy = row3(pl, d);
@@ -65,7 +65,7 @@ __device__ __forceinline__ void intersect32(const Streams32& S, F3 o, F3 d, floa
         float t = -oy * rcp(dy);
         if (t >= 0.f && t < best_t) { best_t = t; hit = i; }  // dy ~ 0 -> t = +-inf or NaN: never taken
     }
-#pragma unroll 4
+#pragma unroll 2
     for (int i = 0; i < S.nu; ++i) {                     // Sphere::intersect_local, src/shape.rs:361-375
         float4 sp = S.usph[i];
         F3 L = mk(o.x - sp.x, o.y - sp.y, o.z - sp.z);
@@ -211,13 +211,13 @@ __device__ __forceinline__ bool shadow32(const Streams32& S, const float* __rest
     bool hit = false;
     const float a = dot(d, d);
     const float inv_a = rcp(a);
-#pragma unroll 3
+#pragma unroll 2
     for (int i = 0; i < S.np; ++i) {
         float4 pl = S.planes[i];
         float f0 = row4(pl, o);
         hit |= f0 * plL[i] <= 0.f;                     // f(0) and f(1) on opposite sides
     }
-#pragma unroll 4
+#pragma unroll 2
     for (int i = 0; i < S.nu; ++i) {
         float4 sp = S.usph[i];
         F3 L = mk(o.x - sp.x, o.y - sp.y, o.z - sp.z);
@@ -252,25 +252,50 @@ __device__ __forceinline__ bool shadow32(const Streams32& S, const float* __rest
 // last two containers by (t, shape index) is enough.
 __device__ __noinline__ void compute_refractive32_unique(const Streams32& S, const ShadeRec32* rec, F3 o, F3 d, int hit_idx,
                                                          float& n1, float& n2) {
-    float t1st = -__int_as_float(0x7f800000), t2nd = t1st;
+    const float ninf = -__int_as_float(0x7f800000);
+    float t1st = ninf, t2nd = ninf;
     int i1st = -1, i2nd = -1;
     bool hit_is_container = false;
-    for_each_negative(S, o, d, [&](float t, int idx, int, bool single) {
-        if (!single) return;  // both roots negative: entered and left again -> not a container
-        if (idx == hit_idx) hit_is_container = true;
+    auto offer = [&](float t, int idx) {
+        hit_is_container |= idx == hit_idx;
         if (t > t1st || (t == t1st && idx > i1st)) { t2nd = t1st; i2nd = i1st; t1st = t; i1st = idx; }
         else if (t > t2nd || (t == t2nd && idx > i2nd)) { t2nd = t; i2nd = idx; }
-    });
-    n1 = i1st >= 0 ? rec[i1st].tr_ri.y : 1.0f;
-    if (hit_is_container) {
-        if (i1st == hit_idx) n2 = i2nd >= 0 ? rec[i2nd].tr_ri.y : 1.0f;
-        else n2 = i1st >= 0 ? rec[i1st].tr_ri.y : 1.0f;
-    } else {
-        n2 = rec[hit_idx].tr_ri.y;
+    };
+    const float a = dot(d, d);
+#pragma unroll 1
+    for (int i = 0; i < S.np; ++i) {           // a plane behind the origin (t < 0) counts as a container
+        float4 pl = S.planes[i];
+        float t = -row4(pl, o) * rcp(row3(pl, d));
+        if (t < 0.f) offer(t, S.pl_index[i]);
     }
+#pragma unroll 1
+    for (int i = 0; i < S.nu; ++i) {           // t1 < 0 <= t2  <=>  the origin is inside the sphere (c < 0)
+        float4 sp = S.usph[i];
+        F3 L = mk(o.x - sp.x, o.y - sp.y, o.z - sp.z);
+        float c = fmaf(L.z, L.z, fmaf(L.y, L.y, fmaf(L.x, L.x, -sp.w)));
+        if (c < 0.f) {
+            float b = dot(d, L);
+            offer((-b - sqrtf(fmaf(b, b, -a * c))) * rcp(a), S.us_index[i]);
+        }
+    }
+#pragma unroll 1
+    for (int i = 0; i < S.ng; ++i) {
+        float4 r0 = S.gsph[3 * i], r1 = S.gsph[3 * i + 1], r2 = S.gsph[3 * i + 2];
+        F3 lo = mk(row4(r0, o), row4(r1, o), row4(r2, o));
+        float c = dot(lo, lo) - 1.f;
+        if (c < 0.f) {
+            F3 ld = mk(row3(r0, d), row3(r1, d), row3(r2, d));
+            float la = dot(ld, ld), b = dot(ld, lo);
+            offer((-b - sqrtf(fmaf(b, b, -la * c))) * rcp(la), S.gs_index[i]);
+        }
+    }
+    n1 = i1st >= 0 ? rec[i1st].tr_ri.y : 1.0f;
+    if (i1st == hit_idx) n2 = i2nd >= 0 ? rec[i2nd].tr_ri.y : 1.0f;
+    else if (hit_is_container) n2 = i1st >= 0 ? rec[i1st].tr_ri.y : 1.0f;
+    else n2 = rec[hit_idx].tr_ri.y;
 }
 
-template <bool kSmem>
+template <bool kSmem, bool kUnique>
 __global__ void __launch_bounds__(kThreads, 5)
 render_f32_kernel(DevScene32 sc, CamParams cam, void* __restrict__ out_rgb, uint8_t* __restrict__ out_hit,
                   Counters* __restrict__ counters, unsigned* __restrict__ work) {
@@ -326,7 +351,6 @@ render_f32_kernel(DevScene32 sc, CamParams cam, void* __restrict__ out_rgb, uint
     const int n_sub = cam.samples == 1 ? 1 : 4;
     const float w0 = cam.samples == 1 ? 1.0f : 0.25f;
     const F3 cam_origin = mk((float)cam.vinv[3], (float)cam.vinv[7], (float)cam.vinv[11]);  // Vinv * (0,0,0)
-    const bool ids_unique = sc.ids_unique != 0;
 
     unsigned wtile = 0;       // warp-uniform: the tile being handed out, next pixel in it
     int wnext = kBatch;
@@ -444,7 +468,7 @@ render_f32_kernel(DevScene32 sc, CamParams cam, void* __restrict__ out_rgb, uint
                 hn = wn * rsqrtf(dot(wn, wn));
             }
             if (tr.x != 0.f) {                                    // Intersection::compute_refractive
-                if (ids_unique) compute_refractive32_unique(S, R, ro, rd, hidx, hn1, hn2);
+                if (kUnique) compute_refractive32_unique(S, R, ro, rd, hidx, hn1, hn2);
                 else compute_refractive32(S, R, ro, rd, hidx, hn1, hn2);
             }
             if (dot(hn, rd) > 0.f) hn = mk(-hn.x, -hn.y, -hn.z);  // inside: normal . eyev < 0 (src/shape.rs:77-78)
@@ -558,20 +582,22 @@ cudaError_t launch_render_f32(const DevScene32& scene, const CamParams& cam, voi
     const size_t recs = (size_t)scene.n_shapes * sizeof(ShadeRec32);
     const int tiles = ((cam.hsize + kTileX - 1) / kTileX) * ((cam.shard_rows + kTileY - 1) / kTileY);
     const int warps = kThreads / 32;
-    int blocks_per_sm = 0;
-    if (streams + recs <= 40 * 1024) {
-        size_t smem = streams + recs;
-        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks_per_sm, render_f32_kernel<true>, kThreads, smem);
+    const bool small = streams + recs <= 40 * 1024;
+    if (!small && streams > 200 * 1024) return cudaErrorInvalidConfiguration;  // TODO(C4): tiled streaming of big scenes
+    const size_t smem = small ? streams + recs : streams;
+    auto launch = [&](auto kernel) -> cudaError_t {
+        cudaError_t er = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (er != cudaSuccess) return er;
+        int blocks_per_sm = 0;
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks_per_sm, kernel, kThreads, smem);
         int grid = max(1, min(sms * max(blocks_per_sm, 1), (tiles + warps - 1) / warps));
-        render_f32_kernel<true><<<grid, kThreads, smem, stream>>>(scene, cam, d_rgb, d_hit, d_counters, d_work);
-    } else {
-        if (streams > 200 * 1024) return cudaErrorInvalidConfiguration;  // TODO(C4): tiled streaming of big scenes
-        e = cudaFuncSetAttribute(render_f32_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)streams);
-        if (e != cudaSuccess) return e;
-        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks_per_sm, render_f32_kernel<false>, kThreads, streams);
-        int grid = max(1, min(sms * max(blocks_per_sm, 1), (tiles + warps - 1) / warps));
-        render_f32_kernel<false><<<grid, kThreads, streams, stream>>>(scene, cam, d_rgb, d_hit, d_counters, d_work);
-    }
+        kernel<<<grid, kThreads, smem, stream>>>(scene, cam, d_rgb, d_hit, d_counters, d_work);
+        return cudaSuccess;
+    };
+    const bool uniq = scene.ids_unique != 0;
+    if (small) e = uniq ? launch(render_f32_kernel<true, true>) : launch(render_f32_kernel<true, false>);
+    else e = uniq ? launch(render_f32_kernel<false, true>) : launch(render_f32_kernel<false, false>);
+    if (e != cudaSuccess) return e;
     return cudaGetLastError();
 }
 
