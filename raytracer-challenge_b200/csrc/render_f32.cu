@@ -207,28 +207,39 @@ __device__ __forceinline__ F3 pattern_at32(int kind, F3 a, F3 b, F3 p) {
 // no square root: f(0) f(1) < 0 (one root inside) or both roots inside.  f(1) depends only on the
 // light and is precomputed per shape (plL / usL, staged beside the streams).
 __device__ __forceinline__ bool shadow32(const Streams32& S, const float* __restrict__ plL, const float* __restrict__ usL,
-                                         F3 o, F3 d) {
-    bool hit = false;
+                                         bool light_inside, F3 o, F3 d) {
+    // every test is reduced to "g <= 0" and the g's are min-accumulated: FMNMX instead of predicates
+    float g = 1.0f;
     const float a = dot(d, d);
     const float inv_a = rcp(a);
 #pragma unroll 2
     for (int i = 0; i < S.np; ++i) {
         float4 pl = S.planes[i];
-        float f0 = row4(pl, o);
-        hit |= f0 * plL[i] <= 0.f;                     // f(0) and f(1) on opposite sides
+        g = fminf(g, row4(pl, o) * plL[i]);            // f(0) f(1) <= 0: the two ends on opposite sides
     }
+    if (!light_inside) {
 #pragma unroll 2
-    for (int i = 0; i < S.nu; ++i) {
-        float4 sp = S.usph[i];
-        F3 L = mk(o.x - sp.x, o.y - sp.y, o.z - sp.z);
-        float f0 = fmaf(L.z, L.z, fmaf(L.y, L.y, fmaf(L.x, L.x, -sp.w)));
-        float b = dot(d, L);
-        // f(t) = a t^2 + 2 b t + f0 is convex: its minimum over [0,1] is at clamp(-b/a); a root lies
-        // in [0,1] iff that minimum is <= 0 and the segment is not entirely inside (max(f0,f1) >= 0)
-        float tc = __saturatef(-b * inv_a);
-        float fmin = fmaf(tc, fmaf(a, tc, b + b), f0);
-        hit |= fmin <= 0.f && fmaxf(f0, usL[i]) >= 0.f;
+        for (int i = 0; i < S.nu; ++i) {
+            float4 sp = S.usph[i];
+            F3 L = mk(o.x - sp.x, o.y - sp.y, o.z - sp.z);
+            float f0 = fmaf(L.z, L.z, fmaf(L.y, L.y, fmaf(L.x, L.x, -sp.w)));
+            float b = dot(d, L);
+            // f(t) = a t^2 + 2 b t + f0 is convex: its minimum over [0,1] is at clamp(-b/a, 0, 1)
+            float tc = __saturatef(-b * inv_a);
+            g = fminf(g, fmaf(tc, fmaf(a, tc, b + b), f0));
+        }
+    } else {  // the light sits inside some sphere: a segment entirely inside it (f0 < 0 and f1 < 0) has no root
+        for (int i = 0; i < S.nu; ++i) {
+            float4 sp = S.usph[i];
+            F3 L = mk(o.x - sp.x, o.y - sp.y, o.z - sp.z);
+            float f0 = fmaf(L.z, L.z, fmaf(L.y, L.y, fmaf(L.x, L.x, -sp.w)));
+            float b = dot(d, L);
+            float tc = __saturatef(-b * inv_a);
+            float fmin = fmaf(tc, fmaf(a, tc, b + b), f0);
+            g = fminf(g, fmaxf(fmin, -fmaxf(f0, usL[i])));
+        }
     }
+    bool hit = g <= 0.f;
     if (S.ng > 0) {  // genuinely affine spheres: nearest-root test in object space
         for (int i = 0; i < S.ng; ++i) {
             float4 r0 = S.gsph[3 * i], r1 = S.gsph[3 * i + 1], r2 = S.gsph[3 * i + 2];
@@ -250,6 +261,27 @@ __device__ __forceinline__ bool shadow32(const Streams32& S, const float* __rest
 // compute_refractive when every world_id is unique (<= 255 shapes): a shape is a container iff it
 // has exactly one negative-t entry (plane: t < 0; sphere: t1 < 0 <= t2), so one pass that keeps the
 // last two containers by (t, shape index) is enough.
+// Fast path of compute_refractive: only shapes whose refractive index is not 1.0 ("gset", stream
+// positions) can make n1/n2 differ from (1.0, ri(hit)): if the ray origin is inside none of them
+// (no negative single entry), every container has ri 1.0, so n1 = 1 and n2 = ri(hit) either way.
+__device__ __forceinline__ bool origin_in_gset(const Streams32& S, const int32_t* gset, int n_gset, F3 o, F3 d) {
+    bool any = false;
+    for (int k = 0; k < n_gset; ++k) {
+        int pos = gset[k];
+        if (pos < S.np) { float4 pl = S.planes[pos]; any |= row4(pl, o) * row3(pl, d) > 0.f; }      // t = -oy/dy < 0
+        else if (pos < S.np + S.nu) {
+            float4 sp = S.usph[pos - S.np];
+            F3 L = mk(o.x - sp.x, o.y - sp.y, o.z - sp.z);
+            any |= fmaf(L.z, L.z, fmaf(L.y, L.y, fmaf(L.x, L.x, -sp.w))) < 0.f;                      // origin inside
+        } else {
+            const float4* r = S.gsph + 3 * (pos - S.np - S.nu);
+            F3 lo = mk(row4(r[0], o), row4(r[1], o), row4(r[2], o));
+            any |= dot(lo, lo) < 1.f;
+        }
+    }
+    return any;
+}
+
 __device__ __noinline__ void compute_refractive32_unique(const Streams32& S, const ShadeRec32* rec, F3 o, F3 d, int hit_idx,
                                                          float& n1, float& n2) {
     const float ninf = -__int_as_float(0x7f800000);
@@ -305,6 +337,9 @@ render_f32_kernel(DevScene32 sc, CamParams cam, void* __restrict__ out_rgb, uint
     const ShadeRec32* R = sc.rec;
     const float* plL;  // f(1) of the shadow test per plane / per uniform sphere (depends on the light only)
     const float* usL;
+    const int32_t* gset;
+    const int n_gset = sc.n_gset;
+    int light_inside_local = 0;
     const F3 light_pos = mk(sc.light_pos[0], sc.light_pos[1], sc.light_pos[2]);
     const F3 light_int = mk(sc.light_int[0], sc.light_int[1], sc.light_int[2]);
     {
@@ -319,6 +354,8 @@ render_f32_kernel(DevScene32 sc, CamParams cam, void* __restrict__ out_rgb, uint
         int32_t* s_gi = s_ui + S.nu;
         float* s_plL = reinterpret_cast<float*>(s_gi + S.ng);
         float* s_usL = s_plL + S.np;
+        int32_t* s_gset = reinterpret_cast<int32_t*>(s_usL + S.nu);
+        for (int i = threadIdx.x; i < sc.n_gset && i < 16; i += kThreads) s_gset[i] = sc.gset[i];
         for (int i = threadIdx.x; i < S.np; i += kThreads) {
             float4 p = sc.planes[i];
             s_pl[i] = p; s_pi[i] = sc.pl_index[i];
@@ -329,6 +366,7 @@ render_f32_kernel(DevScene32 sc, CamParams cam, void* __restrict__ out_rgb, uint
             s_us[i] = p; s_ui[i] = sc.us_index[i];
             F3 L = mk(light_pos.x - p.x, light_pos.y - p.y, light_pos.z - p.z);
             s_usL[i] = dot(L, L) - p.w;
+            if (s_usL[i] < 0.f) light_inside_local = 1;
         }
         for (int i = threadIdx.x; i < 3 * S.ng; i += kThreads) s_gs[i] = sc.gsph[i];
         for (int i = threadIdx.x; i < S.ng; i += kThreads) s_gi[i] = sc.gs_index[i];
@@ -337,11 +375,12 @@ render_f32_kernel(DevScene32 sc, CamParams cam, void* __restrict__ out_rgb, uint
             for (int i = threadIdx.x; i < rec4; i += kThreads) s_rec[i] = g_rec[i];
             R = reinterpret_cast<const ShadeRec32*>(s_rec);
         }
-        __syncthreads();
+        light_inside_local = __syncthreads_or(light_inside_local);
         S.planes = s_pl; S.usph = s_us; S.gsph = s_gs; S.pl_index = s_pi; S.us_index = s_ui; S.gs_index = s_gi;
-        plL = s_plL; usL = s_usL;
+        plL = s_plL; usL = s_usL; gset = s_gset;
     }
 
+    const bool light_inside = light_inside_local != 0;
     const unsigned full = 0xffffffffu;
     const int lane = threadIdx.x & 31;
     const unsigned lt_mask = (1u << lane) - 1u;
@@ -351,6 +390,13 @@ render_f32_kernel(DevScene32 sc, CamParams cam, void* __restrict__ out_rgb, uint
     const int n_sub = cam.samples == 1 ? 1 : 4;
     const float w0 = cam.samples == 1 ? 1.0f : 0.25f;
     const F3 cam_origin = mk((float)cam.vinv[3], (float)cam.vinv[7], (float)cam.vinv[11]);  // Vinv * (0,0,0)
+    // Camera::ray_for_pixel_offset (src/camera.rs:64-76): pixel - origin = Vinv3 * (wx, wy, -1) with
+    // wx = half_width - (x + xo) ps, wy = half_height - (y + yo) ps  ==  cam_dx (x+xo) + cam_dy (y+yo) + cam_d0
+    const F3 cam_dx = mk((float)(-cam.pixel_size * cam.vinv[0]), (float)(-cam.pixel_size * cam.vinv[4]), (float)(-cam.pixel_size * cam.vinv[8]));
+    const F3 cam_dy = mk((float)(-cam.pixel_size * cam.vinv[1]), (float)(-cam.pixel_size * cam.vinv[5]), (float)(-cam.pixel_size * cam.vinv[9]));
+    const F3 cam_d0 = mk((float)(cam.half_width * cam.vinv[0] + cam.half_height * cam.vinv[1] - cam.vinv[2]),
+                         (float)(cam.half_width * cam.vinv[4] + cam.half_height * cam.vinv[5] - cam.vinv[6]),
+                         (float)(cam.half_width * cam.vinv[8] + cam.half_height * cam.vinv[9] - cam.vinv[10]));
 
     unsigned wtile = 0;       // warp-uniform: the tile being handed out, next pixel in it
     int wnext = kBatch;
@@ -429,14 +475,9 @@ render_f32_kernel(DevScene32 sc, CamParams cam, void* __restrict__ out_rgb, uint
             wnext += take;
         }
         if (!has_ray && have && sub < n_sub) {
-            // Camera::ray_for_pixel_offset (src/camera.rs:64-76); pixel position in f64, once per sample
-            double xo = n_sub == 1 ? 0.5 : ((sub & 1) ? 0.75 : 0.25);
-            double yo = n_sub == 1 ? 0.5 : ((sub & 2) ? 0.75 : 0.25);
-            double wx = cam.half_width - ((double)px + xo) * cam.pixel_size;
-            double wy = cam.half_height - ((double)py + yo) * cam.pixel_size;
-            F3 dir = mk((float)(cam.vinv[0] * wx + cam.vinv[1] * wy - cam.vinv[2]),
-                        (float)(cam.vinv[4] * wx + cam.vinv[5] * wy - cam.vinv[6]),
-                        (float)(cam.vinv[8] * wx + cam.vinv[9] * wy - cam.vinv[10]));
+            float fx = (float)px + (n_sub == 1 ? 0.5f : ((sub & 1) ? 0.75f : 0.25f));
+            float fy = (float)py + (n_sub == 1 ? 0.5f : ((sub & 2) ? 0.75f : 0.25f));
+            F3 dir = fma3(cam_dx, fx, fma3(cam_dy, fy, cam_d0));
             rd = dir * rsqrtf(dot(dir, dir));
             ro = cam_origin; rw = w0; remaining = cam.max_depth; is_primary = true; has_ray = true;
         }
@@ -468,7 +509,8 @@ render_f32_kernel(DevScene32 sc, CamParams cam, void* __restrict__ out_rgb, uint
                 hn = wn * rsqrtf(dot(wn, wn));
             }
             if (tr.x != 0.f) {                                    // Intersection::compute_refractive
-                if (kUnique) compute_refractive32_unique(S, R, ro, rd, hidx, hn1, hn2);
+                if (kUnique && n_gset <= 16 && !origin_in_gset(S, gset, n_gset, ro, rd)) { hn1 = 1.f; hn2 = tr.y; }
+                else if (kUnique) compute_refractive32_unique(S, R, ro, rd, hidx, hn1, hn2);
                 else compute_refractive32(S, R, ro, rd, hidx, hn1, hn2);
             }
             if (dot(hn, rd) > 0.f) hn = mk(-hn.x, -hn.y, -hn.z);  // inside: normal . eyev < 0 (src/shape.rs:77-78)
@@ -477,7 +519,7 @@ render_f32_kernel(DevScene32 sc, CamParams cam, void* __restrict__ out_rgb, uint
 
         // ---------------------------------------------------------------- phase C: is_shadowed (any-hit)
         bool shadowed = false;
-        if (hit >= 0) { shadowed = shadow32(S, plL, usL, hp, light_pos - hp); ++n_rays; ++n_shaded; }
+        if (hit >= 0) { shadowed = shadow32(S, plL, usL, light_inside, hp, light_pos - hp); ++n_rays; ++n_shaded; }
 
         // ---------------------------------------------------------------- phase D: shade_hit
         if (hit >= 0) {
@@ -578,7 +620,7 @@ cudaError_t launch_render_f32(const DevScene32& scene, const CamParams& cam, voi
     cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
     const size_t streams = (size_t)(scene.n_planes + scene.n_usph + 3 * scene.n_gsph) * 16 +
-                           (size_t)(scene.n_planes + scene.n_usph + scene.n_gsph) * 4 + (size_t)(scene.n_planes + scene.n_usph) * 4 + 16;
+                           (size_t)(scene.n_planes + scene.n_usph + scene.n_gsph) * 4 + (size_t)(scene.n_planes + scene.n_usph) * 4 + 16 * 4 + 16;
     const size_t recs = (size_t)scene.n_shapes * sizeof(ShadeRec32);
     const int tiles = ((cam.hsize + kTileX - 1) / kTileX) * ((cam.shard_rows + kTileY - 1) / kTileY);
     const int warps = kThreads / 32;

@@ -56,7 +56,7 @@ struct DeviceState {
     // scene
     DevBuf<double2> sph64, pl64;
     DevBuf<float4> pl32, us32, gs32;
-    DevBuf<int32_t> sph_index, pl_index, us_index, gs_index;
+    DevBuf<int32_t> sph_index, pl_index, us_index, gs_index, gset;
     DevBuf<ShadeRec64> rec64;
     DevBuf<ShadeRec32> rec32;
     DevScene64 s64{};
@@ -140,7 +140,7 @@ CamParams make_cam(const rtc_camera* cam, const rtc_render_opts* o, int shard_in
 struct HostScene {
     std::vector<double2> sph64, pl64;
     std::vector<float4> pl32, us32, gs32;
-    std::vector<int32_t> sph_index, pl_index, us_index, gs_index;
+    std::vector<int32_t> sph_index, pl_index, us_index, gs_index, gset;
     std::vector<ShadeRec64> rec64;
     std::vector<ShadeRec32> rec32;
     int ids_unique = 1;
@@ -255,6 +255,12 @@ int flatten(const rtc_shape* shapes, size_t n, HostScene& hs) {
         q.tr_ri = make_float4((float)s.transparency, (float)s.refractive_index, __int_as_float_host(s.pattern_kind),
                               __int_as_float_host(geom));
     }
+    // stream positions (planes | uniform spheres | general spheres) of the shapes whose refractive
+    // index is not 1.0: the only ones that can change n1/n2 (fast path of compute_refractive)
+    const int np = (int)hs.pl_index.size(), nu = (int)hs.us_index.size();
+    for (int k = 0; k < np; ++k) if (shapes[hs.pl_index[k]].refractive_index != 1.0) hs.gset.push_back(k);
+    for (int k = 0; k < nu; ++k) if (shapes[hs.us_index[k]].refractive_index != 1.0) hs.gset.push_back(np + k);
+    for (int k = 0; k < (int)hs.gs_index.size(); ++k) if (shapes[hs.gs_index[k]].refractive_index != 1.0) hs.gset.push_back(np + nu + k);
     return RTC_OK;
 }
 
@@ -411,7 +417,7 @@ void rtc_context_destroy(rtc_context* ctx) {
     for (DeviceState& d : ctx->devs) {
         cudaSetDevice(d.dev);
         if (d.stream) cudaStreamSynchronize(d.stream);
-        d.sph64.release(); d.pl64.release(); d.pl32.release(); d.us32.release(); d.gs32.release(); d.us_index.release(); d.gs_index.release();
+        d.sph64.release(); d.pl64.release(); d.pl32.release(); d.us32.release(); d.gs32.release(); d.us_index.release(); d.gs_index.release(); d.gset.release();
         d.sph_index.release(); d.pl_index.release(); d.rec64.release(); d.rec32.release();
         d.rgb.release(); d.hit.release(); d.counters.release(); d.work.release();
         if (d.ev_k0) cudaEventDestroy(d.ev_k0);
@@ -439,6 +445,7 @@ int rtc_scene_upload(rtc_context* ctx, const rtc_light* light, const rtc_shape* 
         CUDA_TRY(upload(d.gs32, hs.gs32, d.stream));
         CUDA_TRY(upload(d.us_index, hs.us_index, d.stream));
         CUDA_TRY(upload(d.gs_index, hs.gs_index, d.stream));
+        CUDA_TRY(upload(d.gset, hs.gset, d.stream));
         CUDA_TRY(upload(d.sph_index, hs.sph_index, d.stream));
         CUDA_TRY(upload(d.pl_index, hs.pl_index, d.stream));
         CUDA_TRY(upload(d.rec64, hs.rec64, d.stream));
@@ -453,6 +460,7 @@ int rtc_scene_upload(rtc_context* ctx, const rtc_light* light, const rtc_shape* 
         d.s64.rec = d.rec64.p;
         d.s32.planes = d.pl32.p; d.s32.pl_index = d.pl_index.p; d.s32.usph = d.us32.p; d.s32.us_index = d.us_index.p;
         d.s32.gsph = d.gs32.p; d.s32.gs_index = d.gs_index.p;
+        d.s32.gset = d.gset.p; d.s32.n_gset = (int)hs.gset.size();
         d.s32.rec = d.rec32.p;
         for (int k = 0; k < 3; ++k) {
             d.s64.light_pos[k] = light->position[k]; d.s64.light_int[k] = light->intensity[k];

@@ -74,6 +74,8 @@ struct DevScene32 {
     const float4* gsph;        // [n_gsph][3]
     const int32_t* gs_index;
     const ShadeRec32* rec;     // [n_shapes]
+    const int32_t* gset;       // stream positions of the shapes with refractive_index != 1.0
+    int n_gset;
     float light_pos[3];
     float light_int[3];
 };
