@@ -327,8 +327,11 @@ __device__ __noinline__ void compute_refractive32_unique(const Streams32& S, con
     else n2 = rec[hit_idx].tr_ri.y;
 }
 
+#ifndef RTC_F32_MIN_BLOCKS
+#define RTC_F32_MIN_BLOCKS 6
+#endif
 template <bool kSmem, bool kUnique>
-__global__ void __launch_bounds__(kThreads, 5)
+__global__ void __launch_bounds__(kThreads, RTC_F32_MIN_BLOCKS)
 render_f32_kernel(DevScene32 sc, CamParams cam, void* __restrict__ out_rgb, uint8_t* __restrict__ out_hit,
                   Counters* __restrict__ counters, unsigned* __restrict__ work) {
     extern __shared__ float4 smem4[];
