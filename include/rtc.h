@@ -124,8 +124,17 @@ typedef struct rtc_render_opts {
     int32_t shard_index;
     int32_t shard_count;
     int32_t tile_rows;
-    int32_t reserved;
+    int32_t flags;       /* RTC_OPT_* bits */
 } rtc_render_opts;
+
+/* rtc_render_device only: the destination buffers are FULL frames (hsize*vsize pixels) and the
+ * shard's rows are written at their frame positions instead of into a compact shard buffer.
+ * With a peer-mapped frame of another GPU (rtc_ipc_open) this is the fused render + gather:
+ * finished pixels travel over NVLink as the kernel produces them, no collective afterwards. */
+#define RTC_OPT_DST_FULL_FRAME 1
+/* f32 fast mode: use the general kernel (shared-memory streams, any shape count) even when the
+ * scene fits the constant-bank small-scene kernel.  For testing one against the other. */
+#define RTC_OPT_F32_GENERAL_KERNEL 2
 
 #define RTC_MAX_DEPTH 8
 
@@ -193,6 +202,18 @@ int rtc_render_device(rtc_context* ctx, const rtc_camera* cam, const rtc_render_
 int rtc_assemble_device(rtc_context* ctx, const rtc_camera* cam, const rtc_render_opts* opts,
                         const void* d_gathered, int shard_stride_rows, int elem_kind, void* d_frame,
                         void* stream);
+
+/* Cross-process peer access to a device buffer (one process per GPU, torchrun style).
+ * rtc_ipc_export: fills `handle` (RTC_IPC_HANDLE_BYTES bytes, = cudaIpcMemHandle_t) for the
+ * allocation containing d_ptr and the byte offset of d_ptr inside it; the bytes can be sent to
+ * another process by any transport.  rtc_ipc_open maps that allocation into this process on the
+ * context's first GPU (enabling peer access) and returns the device pointer corresponding to
+ * d_ptr; rtc_ipc_close unmaps it.  Replaces nothing in the reference (it has no multi-device
+ * path): this is the NVLink side of the multi-GPU framebuffer assembly. */
+#define RTC_IPC_HANDLE_BYTES 64
+int rtc_ipc_export(rtc_context* ctx, const void* d_ptr, void* handle, uint64_t* offset);
+int rtc_ipc_open(rtc_context* ctx, const void* handle, uint64_t offset, void** out_d_ptr);
+int rtc_ipc_close(rtc_context* ctx, void* d_ptr, uint64_t offset);
 
 /* Register-resident FMA micro-benchmark on the context's first GPU: measured non-tensor peak
  * of the FP32 (precision = RTC_PRECISION_F32_FAST) or FP64 pipe in TFLOP/s (FMA = 2 flops),

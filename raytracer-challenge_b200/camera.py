@@ -85,10 +85,10 @@ class Renderer:
 
     @staticmethod
     def make_opts(precision=ffi.PRECISION_F64_PARITY, rect=ffi.RECT_FULL, max_depth=5,
-                  out_format=ffi.OUT_F64_RGB, shard_index=0, shard_count=1, tile_rows=16):
+                  out_format=ffi.OUT_F64_RGB, shard_index=0, shard_count=1, tile_rows=16, flags=0):
         o = ffi.RtcRenderOpts()
         o.precision, o.rect, o.max_depth, o.out_format = precision, rect, max_depth, out_format
-        o.shard_index, o.shard_count, o.tile_rows = shard_index, shard_count, tile_rows
+        o.shard_index, o.shard_count, o.tile_rows, o.flags = shard_index, shard_count, tile_rows, flags
         return o
 
     def render(self, cam_desc, opts, want_mask=True, out=None):
@@ -115,6 +115,23 @@ class Renderer:
         ffi.check(self._lib.rtc_assemble_device(
             self._ctx, C.byref(cam_desc), C.byref(opts), C.c_void_p(d_gathered), shard_stride_rows,
             elem_kind, C.c_void_p(d_frame), C.c_void_p(stream) if stream else None))
+
+    def ipc_export(self, d_ptr):
+        """-> (handle bytes, offset) for the allocation containing device pointer d_ptr."""
+        h = (C.c_ubyte * ffi.IPC_HANDLE_BYTES)()
+        off = C.c_uint64()
+        ffi.check(self._lib.rtc_ipc_export(self._ctx, C.c_void_p(d_ptr), h, C.byref(off)))
+        return bytes(h), off.value
+
+    def ipc_open(self, handle, offset):
+        """Map a peer process's buffer; -> device pointer (int) valid in this process."""
+        h = (C.c_ubyte * ffi.IPC_HANDLE_BYTES).from_buffer_copy(handle)
+        out = C.c_void_p()
+        ffi.check(self._lib.rtc_ipc_open(self._ctx, h, offset, C.byref(out)))
+        return out.value
+
+    def ipc_close(self, d_ptr, offset):
+        ffi.check(self._lib.rtc_ipc_close(self._ctx, C.c_void_p(d_ptr), offset))
 
     def shard_rows(self, cam_desc, opts):
         return self._lib.rtc_shard_rows(C.byref(cam_desc), C.byref(opts))

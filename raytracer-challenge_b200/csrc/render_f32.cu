@@ -429,7 +429,7 @@ render_f32_kernel(DevScene32 sc, CamParams cam, void* __restrict__ out_rgb, uint
             if (sub + 1 < n_sub) ++sub;   // next sub-sample of the same pixel
             else {
                 // pixel finished: Canvas::write_pixel (src/canvas.rs:43-46)
-                size_t p = (size_t)pr * cam.hsize + px;
+                size_t p = (size_t)(cam.dst_full ? py : pr) * cam.hsize + px;
                 if (cam.out_format == RTC_OUT_F64_RGB) {
                     double* o = (double*)out_rgb + 3 * p;
                     o[0] = (double)acc.x; o[1] = (double)acc.y; o[2] = (double)acc.z;

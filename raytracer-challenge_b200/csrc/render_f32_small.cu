@@ -1,0 +1,435 @@
+// F32 FAST kernel, small-scene variant (<= 16 planes, <= 48 similarity-transformed spheres, no
+// genuinely affine sphere, light outside every sphere): the path configs C1/C2/C3/C5 of BASELINE.json take.  Same algorithm as render_f32.cu —
+// ray_for_pixel, World::intersect over every shape, hit selection, prepare_computations, Phong
+// lighting with a shadow ray, reflection + refraction with Schlick, as path weights
+// (src/camera.rs:64-114, src/shape.rs:677-781, src/material.rs:319-361) — but built so that the
+// brute-force loops issue almost nothing except FP32 math:
+//   * the intersect streams travel as a __grid_constant__ kernel parameter, i.e. they live in
+//     constant bank 0, and the loops are fully unrolled in groups of four with a warp-uniform exit
+//     per group: every plane / sphere coefficient is a c[0x0][imm] operand of the FFMA/FADD that
+//     uses it — no load instruction, no address arithmetic, no loop counter;
+//   * hit selection is ONE unsigned min per candidate root: for t >= 0 the IEEE bit pattern orders
+//     like the value, negative and NaN roots compare above +inf, so
+//         best = min(best, (bits(t) & ~mask) + stream_position)
+//     keeps the nearest non-negative root together with its shape in a single register (the low
+//     6 mantissa bits carry the position: t is truncated by <= 2^-17 relative); there is no branch
+//     on the discriminant (sqrt of a negative discriminant is NaN, which loses the min);
+//   * shadow rays are any-hit tests reduced to "min over shapes of g <= 0" (SURVEY.md A4);
+//   * persistent warps, one pixel per lane, lanes refill from the warp's 8x4 tile by ballot rank;
+//     pending refraction rays sit on a small per-lane stack (north-star item 2).
+// EPSILON: kEps32 = 1e-4 instead of the reference's 1e-8 (below f32 resolution).
+#include "rtc_common.h"
+
+namespace rtc {
+namespace {
+
+constexpr float kEps32 = 1e-4f;
+constexpr int kThreads = 128;
+constexpr int kTileX = 8, kTileY = 4;
+constexpr int kBatch = kTileX * kTileY;
+constexpr int kMaxStack = RTC_MAX_DEPTH;
+constexpr unsigned kInfBits = 0x7f800000u;
+
+struct F3 { float x, y, z; };
+__device__ __forceinline__ F3 mk(float x, float y, float z) { F3 v; v.x = x; v.y = y; v.z = z; return v; }
+__device__ __forceinline__ F3 operator+(F3 a, F3 b) { return mk(a.x + b.x, a.y + b.y, a.z + b.z); }
+__device__ __forceinline__ F3 operator-(F3 a, F3 b) { return mk(a.x - b.x, a.y - b.y, a.z - b.z); }
+__device__ __forceinline__ F3 operator*(F3 a, float m) { return mk(a.x * m, a.y * m, a.z * m); }
+__device__ __forceinline__ F3 operator*(F3 a, F3 b) { return mk(a.x * b.x, a.y * b.y, a.z * b.z); }
+__device__ __forceinline__ float dot(F3 a, F3 b) { return fmaf(a.z, b.z, fmaf(a.y, b.y, a.x * b.x)); }
+__device__ __forceinline__ F3 fma3(F3 a, float m, F3 c) { return mk(fmaf(a.x, m, c.x), fmaf(a.y, m, c.y), fmaf(a.z, m, c.z)); }
+__device__ __forceinline__ F3 xyz(float4 v) { return mk(v.x, v.y, v.z); }
+__device__ __forceinline__ float row4(float4 r, F3 p) { return fmaf(r.z, p.z, fmaf(r.y, p.y, fmaf(r.x, p.x, r.w))); }
+__device__ __forceinline__ float row3(float4 r, F3 p) { return fmaf(r.z, p.z, fmaf(r.y, p.y, r.x * p.x)); }
+__device__ __forceinline__ float rcp(float x) { float r; asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
+__device__ __forceinline__ float sqrt_nan(float x) { float r; asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }  // NaN for x < 0
+__device__ __forceinline__ bool is_even(float v) { float h = v * 0.5f; return h == floorf(h); }
+
+// Stream positions are fixed at compile time: planes occupy [0, 16), spheres [16, 64) — so the
+// position a candidate carries in the low kIdxBits bits of its key is an immediate.
+constexpr int kIdxBits = 6;
+constexpr unsigned kMask = (1u << kIdxBits) - 1u;
+
+// One sphere against a unit-length radiance ray (Sphere::intersect_local, src/shape.rs:361-375, with
+// a = d.d = 1 and b halved).  Only one root can be the hit: t1 when the origin is outside (c > 0),
+// t2 when it is inside (c < 0; then t1 < 0 < t2)  ->  t = -b - copysign(s, c).
+__device__ __forceinline__ unsigned offer_sphere(unsigned best, const float4 sp, F3 o, F3 d, unsigned pos) {
+    F3 L = mk(o.x - sp.x, o.y - sp.y, o.z - sp.z);
+    float b = dot(d, L);
+    float c = fmaf(L.z, L.z, fmaf(L.y, L.y, fmaf(L.x, L.x, -sp.w)));
+    float s = sqrt_nan(fmaf(b, b, -c));                   // NaN when the ray misses: loses the min
+    float ss = __uint_as_float(__float_as_uint(s) | (__float_as_uint(c) & 0x80000000u));
+    return min(best, (__float_as_uint(-b - ss) & ~kMask) + pos);
+}
+
+// World::intersect + Intersections::get_hit for a unit-length ray: nearest root in [0, +inf).
+// Returns the packed key; >= kInfBits means "no hit".
+__device__ __forceinline__ unsigned intersect_small(const SmallParams& P, F3 o, F3 d) {
+    unsigned best = kInfBits;
+#pragma unroll
+    for (int g = 0; g < kSmallMaxPlanes / 4; ++g) {
+        if (g >= P.npg) break;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {                     // Plane::intersect_local, src/shape.rs:462-471
+            float t = -row4(P.planes[4 * g + j], o) * rcp(row3(P.planes_d[4 * g + j], d));  // parallel: +-inf / NaN
+            best = min(best, (__float_as_uint(t) & ~kMask) + (unsigned)(4 * g + j));
+        }
+    }
+#pragma unroll
+    for (int g = 0; g < kSmallMaxUsph / 4; ++g) {
+        if (g >= P.nug) break;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) best = offer_sphere(best, P.usph[4 * g + j], o, d, (unsigned)(kSmallMaxPlanes + 4 * g + j));
+    }
+    return best;
+}
+
+// World::is_shadowed_by_light (src/shape.rs:716-727) as an any-hit test over the segment
+// o -> light (d = light - o): some shape has a root in [0, 1)  <=>  min over shapes of g <= 0.
+//   plane : f(0) f(1) <= 0; f(1) depends on the light only and is folded into the coefficients
+//   sphere: f(t) = a t^2 + 2 b t + f0 is convex, its minimum over [0,1] is at clamp(-b/a, 0, 1)
+__device__ __forceinline__ bool shadow_small(const SmallParams& P, F3 o, F3 d) {
+    float g = 1.0f;
+#pragma unroll
+    for (int k = 0; k < kSmallMaxPlanes / 4; ++k) {
+        if (k >= P.npg) break;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) g = fminf(g, row4(P.splanes[4 * k + j], o));
+    }
+    const float a = dot(d, d);
+    const float nhia = -0.5f * rcp(a);
+    const F3 d2 = mk(d.x + d.x, d.y + d.y, d.z + d.z);
+#pragma unroll
+    for (int k = 0; k < kSmallMaxUsph / 4; ++k) {
+        if (k >= P.nug) break;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const float4 sp = P.usph_s[4 * k + j];
+            F3 L = mk(o.x - sp.x, o.y - sp.y, o.z - sp.z);
+            float f0 = fmaf(L.z, L.z, fmaf(L.y, L.y, fmaf(L.x, L.x, -sp.w)));
+            float b2 = dot(d2, L);                        // f(t) = a t^2 + b2 t + f0
+            float tc = __saturatef(b2 * nhia);
+            g = fminf(g, fmaf(tc, fmaf(a, tc, b2), f0));
+        }
+    }
+    return g <= 0.f;
+}
+
+// Intersection::compute_refractive (src/shape.rs:115-141) in its list-free form (SURVEY.md A6;
+// world_ids are unique on this path): a shape is a container iff it has exactly one negative-t
+// entry (plane: t < 0; sphere: origin inside), containers are ordered by (t, stream position), and
+//   n1 = ri(last container)            n2 = hit is a container ? ri(last container other than it) : ri(hit)
+// Negative floats order in reverse as unsigned, so bits(t) ^ 0x80000000 turns "latest negative t"
+// into an unsigned min as well; ties go to the later position via (mask - pos).
+__device__ __noinline__ void compute_refractive_small(const SmallParams& P, const SmallRec32* __restrict__ R, F3 o, F3 d,
+                                                      int hit_pos, float& n1, float& n2) {
+    unsigned top1 = 0xffffffffu, top2 = 0xffffffffu;   // smallest / second smallest key
+    auto offer = [&](float t, int pos) {               // only called with t < 0
+        unsigned k = ((__float_as_uint(t) ^ 0x80000000u) & ~kMask) + (kMask - (unsigned)pos);
+        top2 = min(top2, max(top1, k));
+        top1 = min(top1, k);
+    };
+    bool hit_is_container = false;
+#pragma unroll 1
+    for (int i = 0; i < P.np; ++i) {                   // a plane behind the origin counts as a container
+        float4 pl = P.planes[i];
+        float t = -row4(pl, o) * rcp(row3(pl, d));
+        if (t < 0.f) offer(t, i);
+    }
+#pragma unroll 1
+    for (int i = 0; i < P.nu; ++i) {                   // t1 < 0 <= t2  <=>  the origin is inside (c < 0)
+        float4 sp = P.usph[i];
+        F3 L = mk(o.x - sp.x, o.y - sp.y, o.z - sp.z);
+        float c = fmaf(L.z, L.z, fmaf(L.y, L.y, fmaf(L.x, L.x, -sp.w)));
+        if (c < 0.f) {
+            float b = dot(d, L);
+            offer(-b - sqrtf(fmaf(b, b, -c)), kSmallMaxPlanes + i);
+            hit_is_container |= kSmallMaxPlanes + i == hit_pos;
+        }
+    }
+    const int p1 = top1 == 0xffffffffu ? -1 : (int)(kMask - (top1 & kMask));
+    const int p2 = top2 == 0xffffffffu ? -1 : (int)(kMask - (top2 & kMask));
+    n1 = p1 >= 0 ? R[p1].tr_ri.y : 1.0f;
+    if (p1 == hit_pos) n2 = p2 >= 0 ? R[p2].tr_ri.y : 1.0f;
+    else if (hit_is_container) n2 = n1;
+    else n2 = R[hit_pos].tr_ri.y;
+}
+
+// Pattern::pattern_at for the rarely used kinds (src/material.rs:67-69,133-135,163-170,233-241)
+__device__ __noinline__ F3 pattern_rare(int kind, F3 a, F3 b, F3 p) {
+    switch (kind) {
+        case RTC_PATTERN_TEST: return p;
+        case RTC_PATTERN_GRADIENT: return fma3(b - a, p.x - floorf(p.x), a);
+        case RTC_PATTERN_RING: return is_even(floorf(sqrtf(fmaf(p.x, p.x, p.y * p.y)))) ? a : b;
+        default: return (fabsf(p.x - floorf(p.x)) < 0.01f || fabsf(p.z - floorf(p.z)) < 0.01f) ? b : a;
+    }
+}
+
+#ifndef RTC_F32S_MIN_BLOCKS
+#define RTC_F32S_MIN_BLOCKS 6
+#endif
+
+template <int kFmt>
+__global__ void __launch_bounds__(kThreads, RTC_F32S_MIN_BLOCKS)
+render_f32_small_kernel(const __grid_constant__ SmallParams P, void* __restrict__ out_rgb, uint8_t* __restrict__ out_hit,
+                        Counters* __restrict__ counters, unsigned* __restrict__ work) {
+    extern __shared__ float4 smem4[];
+    SmallRec32* R = reinterpret_cast<SmallRec32*>(smem4);
+    {   // stage the shading records (indexed by stream position): coalesced 16-byte loads
+        constexpr int kRec4 = (int)(sizeof(SmallRec32) / 16);
+        const float4* g_rec = reinterpret_cast<const float4*>(P.rec);
+        for (int i = threadIdx.x; i < kRec4 * P.np; i += kThreads) smem4[i] = g_rec[i];
+        for (int i = threadIdx.x; i < kRec4 * P.nu; i += kThreads) smem4[kRec4 * kSmallMaxPlanes + i] = g_rec[kRec4 * kSmallMaxPlanes + i];
+        __syncthreads();
+    }
+    const F3 light_pos = mk(P.light_pos[0], P.light_pos[1], P.light_pos[2]);
+    const F3 light_int = mk(P.light_int[0], P.light_int[1], P.light_int[2]);
+    const unsigned full = 0xffffffffu;
+    const int lane = threadIdx.x & 31;
+    const unsigned lt_mask = (1u << lane) - 1u;
+    const int n_sub = P.n_sub;
+    const float w0 = n_sub == 1 ? 1.0f : 0.25f;
+
+    // warp-uniform tile cursor
+    int wnext = kBatch;        // next pixel of the current tile
+    int wtx = 0, wty = 0;      // tile origin (pixels / compact rows)
+    bool exhausted = false;
+    // per-lane path state
+    bool has_ray = false, have = false, primary = false;
+    F3 ro = mk(0.f, 0.f, 0.f), rd = mk(0.f, 0.f, 1.f);
+    float rw = 0.f;
+    int remaining = 0;
+    int px = 0, pr = 0, py = 0, sub = 0;
+    F3 acc = mk(0.f, 0.f, 0.f);
+    unsigned hitbits = 0;
+    float4 stk_a[kMaxStack], stk_b[kMaxStack];  // pending refraction rays: (o, weight), (d, remaining)
+    int sp = 0;
+    unsigned n_rad = 0, n_hits = 0, n_phits = 0;
+
+    for (;;) {
+        // ------------------------------------------------------------ lanes without a ray
+        if (!has_ray && sp == 0 && have) {
+            if (sub + 1 < n_sub) ++sub;
+            else {                                            // Canvas::write_pixel (src/canvas.rs:43-46)
+                size_t p = (size_t)(P.dst_full ? py : pr) * (size_t)P.hsize + (size_t)px;
+                if (kFmt == RTC_OUT_F64_RGB) {
+                    double* o = (double*)out_rgb + 3 * p;
+                    o[0] = (double)acc.x; o[1] = (double)acc.y; o[2] = (double)acc.z;
+                } else if (kFmt == RTC_OUT_F32_RGB) {
+                    float* o = (float*)out_rgb + 3 * p;
+                    o[0] = acc.x; o[1] = acc.y; o[2] = acc.z;
+                } else {                                      // Color::scale, src/color.rs:100-114
+                    uint8_t* o = (uint8_t*)out_rgb + 3 * p;
+                    float c3[3] = {acc.x, acc.y, acc.z};
+#pragma unroll
+                    for (int k = 0; k < 3; ++k) {
+                        float s = c3[k] * 255.0f;
+                        int q = s != s ? 0 : (s >= 2147483520.0f ? 2147483647 : (s <= -2147483648.0f ? (-2147483647 - 1) : (int)s));
+                        o[k] = (uint8_t)(q < 0 ? 0 : (q > 255 ? 255 : q));
+                    }
+                }
+                if (out_hit) out_hit[p] = (uint8_t)hitbits;
+                have = false;
+            }
+        }
+        // lanes without a pixel claim the next ones of the warp's tile (ballot + popc rank)
+        for (;;) {
+            const bool need = !has_ray && sp == 0 && !have;
+            const unsigned m = __ballot_sync(full, need);
+            if (m == 0u || exhausted) break;
+            if (wnext >= kBatch) {
+                unsigned t = 0;
+                if (lane == 0) t = atomicAdd(work, 1u);
+                t = __shfl_sync(full, t, 0);
+                if (t >= (unsigned)P.total_tiles) { exhausted = true; break; }
+                const int ty = (int)(t / (unsigned)P.tiles_x);
+                wtx = ((int)t - ty * P.tiles_x) * kTileX;
+                wty = ty * kTileY;
+                wnext = 0;
+            }
+            const int rank = __popc(m & lt_mask);
+            const int take = min(__popc(m), kBatch - wnext);
+            if (need && rank < take) {
+                const int k = wnext + rank;
+                px = wtx + (k & (kTileX - 1));
+                pr = wty + (k >> 3);
+                if (px < P.hsize && pr < P.shard_rows) {
+                    py = P.shard_count > 1 ? shard_row_to_frame_row(pr, P.tile_rows, P.shard_index, P.shard_count) : pr;
+                    have = true; sub = 0; acc = mk(0.f, 0.f, 0.f); hitbits = 0;
+                    if (!(px < P.xlim && py < P.ylim)) sub = n_sub;   // outside the rect: stays black
+                }
+            }
+            wnext += take;
+        }
+        if (!has_ray) {
+            if (sp > 0) {                                     // next pending refraction ray of this pixel
+                --sp;
+                const float4 a = stk_a[sp], b = stk_b[sp];
+                ro = xyz(a); rw = a.w; rd = xyz(b); remaining = __float_as_int(b.w);
+                primary = false; has_ray = true;
+            } else if (have && sub < n_sub) {                 // Camera::ray_for_pixel_offset (src/camera.rs:64-76)
+                const float fx = (float)px + (n_sub == 1 ? 0.5f : ((sub & 1) ? 0.75f : 0.25f));
+                const float fy = (float)py + (n_sub == 1 ? 0.5f : ((sub & 2) ? 0.75f : 0.25f));
+                F3 dir = mk(fmaf(P.cam_dx[0], fx, fmaf(P.cam_dy[0], fy, P.cam_d0[0])),
+                            fmaf(P.cam_dx[1], fx, fmaf(P.cam_dy[1], fy, P.cam_d0[1])),
+                            fmaf(P.cam_dx[2], fx, fmaf(P.cam_dy[2], fy, P.cam_d0[2])));
+                rd = dir * rsqrtf(dot(dir, dir));
+                ro = mk(P.cam_o[0], P.cam_o[1], P.cam_o[2]);
+                rw = w0; remaining = P.max_depth; primary = true; has_ray = true;
+            }
+        }
+        if (__all_sync(full, !has_ray && !have && exhausted)) break;
+
+        // ------------------------------------------------------------ phase A: World::intersect (all lanes, idle ones trace a dummy)
+        const unsigned key = intersect_small(P, ro, rd);
+        const bool hit = has_ray && key < kInfBits;
+        n_rad += has_ray ? 1u : 0u;
+        n_hits += hit ? 1u : 0u;
+        if (hit && primary) { hitbits |= 1u << sub; ++n_phits; }
+        has_ray = hit;                                        // miss: World::color_at -> black (src/shape.rs:708)
+
+        // ------------------------------------------------------------ phase B: prepare_computations (src/shape.rs:75-96,144-152)
+        const int hpos = hit ? (int)(key & kMask) : 0;
+        const float t = __uint_as_float((key & ~kMask) | ((kMask + 1u) >> 1));   // centre of the truncation interval
+        const SmallRec32& rec = R[hpos];
+        const float4 tr = rec.tr_ri;
+        F3 p = fma3(rd, hit ? t : 0.f, ro);                   // Ray::position
+        F3 hn;
+        {
+            const float4 nr = rec.nrm;                        // plane: constant normal; sphere: (p - c) / r
+            hn = mk(fmaf(p.x, nr.w, nr.x), fmaf(p.y, nr.w, nr.y), fmaf(p.z, nr.w, nr.z));
+            // p carries t's truncation error (<= 2^-18 relative), so |hn| is only ~1e-4 from 1; the
+            // reflected / refracted directions must stay unit length (the sphere test assumes a = 1)
+            hn = hn * rsqrtf(dot(hn, hn));
+        }
+        float hn1 = 1.f, hn2 = tr.y;
+        if (hit && tr.x != 0.f) {                             // Intersection::compute_refractive
+            bool inside_glass = P.n_glass < 0;                // fast test unavailable -> general form
+#pragma unroll
+            for (int k = 0; k < kSmallMaxGlass; ++k) {
+                if (k >= P.n_glass) break;
+                const float4 sp4 = P.glass[k];
+                F3 L = mk(ro.x - sp4.x, ro.y - sp4.y, ro.z - sp4.z);
+                inside_glass |= fmaf(L.z, L.z, fmaf(L.y, L.y, fmaf(L.x, L.x, -sp4.w))) < 0.f;
+            }
+            // origin inside no shape with ri != 1: every container has ri 1.0 -> n1 = 1, n2 = ri(hit)
+            if (inside_glass) compute_refractive_small(P, R, ro, rd, hpos, hn1, hn2);
+        }
+        const float dn = dot(rd, hn);
+        if (dn > 0.f) hn = mk(-hn.x, -hn.y, -hn.z);           // inside: normal . eyev < 0
+        const float cos_i = fabsf(dn);                        // eyev . normal after the flip
+        const F3 hp = fma3(hn, kEps32, p);                    // over_point
+
+        // ------------------------------------------------------------ phase C: is_shadowed (all lanes)
+        const F3 lv0 = light_pos - hp;
+        const bool shadowed = shadow_small(P, hp, lv0);
+
+        // ------------------------------------------------------------ phase D: shade_hit
+        if (hit) {
+            const float4 ca = rec.col_amb, ds = rec.dif_spec;
+            const int pkind = __float_as_int(tr.z);
+            F3 base = xyz(ca);
+            if (pkind != RTC_PATTERN_NONE) {                  // Pattern::pattern_at_shape at over_point
+                const F3 pp = mk(row4(rec.p0, hp), row4(rec.p1, hp), row4(rec.p2, hp));
+                const float4 pa = rec.pa, pb = rec.pb;
+                if (pkind == RTC_PATTERN_STRIPE || pkind == RTC_PATTERN_CHECKER) {
+                    // stripe: floor(x) % 2 ; checker: (floor x + floor y + floor z) % 2   (pb.w = 0 / 1)
+                    const float s = fmaf(pb.w, floorf(pp.y) + floorf(pp.z), floorf(pp.x));
+                    base = is_even(s) ? xyz(pa) : xyz(pb);
+                } else base = pattern_rare(pkind, xyz(pa), xyz(pb), pp);
+            }
+            const F3 eff = base * light_int;                  // Material::lighting, src/material.rs:319-361
+            F3 surface = eff * ca.w;
+            if (!shadowed) {
+                const F3 lv = lv0 * rsqrtf(dot(lv0, lv0));
+                const float ldn = dot(lv, hn);
+                if (ldn >= 0.f) {
+                    surface = fma3(eff, ds.x * ldn, surface);
+                    // reflect(-lightv, n) . eye  with eye = -rd:  (2 ldn n - lv) . (-rd)
+                    const float rde = fmaf(2.f * ldn, cos_i, dot(lv, rd));
+                    if (rde > 0.f) surface = fma3(light_int, ds.y * __powf(rde, ds.z), surface);
+                }
+            }
+            acc = fma3(surface, rw, acc);
+            // children (src/shape.rs:689-699, 729-781) as weighted rays
+            const float k_refl = ds.w, k_tr = tr.x;
+            float refl_w = rw * k_refl, refr_w = rw * k_tr;
+            const float ratio = hn1 * rcp(hn2);
+            const float sin2_t = ratio * ratio * fmaf(-cos_i, cos_i, 1.f);
+            if (k_refl > 0.f && k_tr > 0.f) {                 // World::reflectance (Schlick), src/shape.rs:768-781
+                float refl = 1.f;                             // total internal reflection
+                float cs = cos_i;
+                bool tir = false;
+                if (hn1 > hn2) { if (sin2_t > 1.f) tir = true; else cs = sqrtf(1.f - sin2_t); }
+                if (!tir) {
+                    const float q = (hn1 - hn2) * rcp(hn1 + hn2), r0 = q * q, m = 1.f - cs, m2 = m * m;
+                    refl = fmaf(1.f - r0, m2 * m2 * m, r0);
+                }
+                refl_w *= refl; refr_w *= 1.f - refl;
+            }
+            const bool want_refl = remaining != 0 && k_refl > 0.f;
+            const bool want_refr = remaining != 0 && k_tr != 0.f && !(sin2_t > 1.f);   // refracted_color, :751-766
+            F3 fo = mk(0.f, 0.f, 0.f), fd = mk(0.f, 0.f, 1.f);
+            if (want_refr) {
+                const float cos_t = sqrtf(1.f - sin2_t);
+                fd = fma3(hn, ratio * cos_i - cos_t, rd * ratio);   // n (r cos_i - cos_t) - eyev r
+                fo = fma3(hn, -2.f * kEps32, hp);                   // under_point
+            }
+            primary = false;
+            --remaining;
+            if (want_refl) {
+                if (want_refr && sp < kMaxStack) {
+                    stk_a[sp] = make_float4(fo.x, fo.y, fo.z, refr_w);
+                    stk_b[sp] = make_float4(fd.x, fd.y, fd.z, __int_as_float(remaining));
+                    ++sp;
+                }
+                rd = fma3(hn, 2.f * cos_i, rd);                     // reflectv = d.reflect(n); d . n = -cos_i
+                ro = hp; rw = refl_w;
+            } else if (want_refr) {
+                ro = fo; rd = fd; rw = refr_w;
+            } else {
+                has_ray = false;
+            }
+        }
+    }
+
+    if (counters) {
+        // every shaded hit casts exactly one shadow ray: rays = radiance rays + shaded hits
+        const unsigned r = __reduce_add_sync(full, n_rad), h = __reduce_add_sync(full, n_hits), ph = __reduce_add_sync(full, n_phits);
+        if (lane == 0) {
+            atomicAdd(&counters->rays, (unsigned long long)r + h);
+            atomicAdd(&counters->shadow_rays, (unsigned long long)h);
+            atomicAdd(&counters->shaded_hits, (unsigned long long)h);
+            atomicAdd(&counters->primary_hits, (unsigned long long)ph);
+        }
+    }
+}
+
+}  // namespace
+
+cudaError_t launch_render_f32_small(const SmallParams& P, int out_format, void* d_rgb, uint8_t* d_hit, Counters* d_counters,
+                                    unsigned* d_work, cudaStream_t stream) {
+    if (P.shard_rows <= 0) return cudaSuccess;
+    cudaError_t e = cudaMemsetAsync(d_work, 0, sizeof(unsigned), stream);
+    if (e != cudaSuccess) return e;
+    int dev = 0, sms = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    const size_t smem = (size_t)(kSmallMaxPlanes + P.nu) * sizeof(SmallRec32) + 16;
+    const int warps = kThreads / 32;
+    auto launch = [&](auto kernel) -> cudaError_t {
+        int blocks_per_sm = 0;
+        cudaError_t er = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks_per_sm, kernel, kThreads, smem);
+        if (er != cudaSuccess) return er;
+        const int grid = max(1, min(sms * max(blocks_per_sm, 1), (P.total_tiles + warps - 1) / warps));
+        kernel<<<grid, kThreads, smem, stream>>>(P, d_rgb, d_hit, d_counters, d_work);
+        return cudaGetLastError();
+    };
+    switch (out_format) {
+        case RTC_OUT_F64_RGB: return launch(render_f32_small_kernel<RTC_OUT_F64_RGB>);
+        case RTC_OUT_F32_RGB: return launch(render_f32_small_kernel<RTC_OUT_F32_RGB>);
+        default:              return launch(render_f32_small_kernel<RTC_OUT_U8_RGB>);
+    }
+}
+
+}  // namespace rtc

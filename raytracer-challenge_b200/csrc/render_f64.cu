@@ -417,7 +417,7 @@ render_f64_kernel(DevScene64 sc, CamParams cam, double* __restrict__ out_f64, fl
     }
     const bool writer = in_image && (ss == 1 || (((sx | sy) & 1) == 0));
     if (writer) {
-        size_t p = (size_t)pr * cam.hsize + px;
+        size_t p = (size_t)(cam.dst_full ? py : pr) * cam.hsize + px;
         if (cam.out_format == RTC_OUT_F64_RGB) {
             out_f64[3 * p + 0] = result.x; out_f64[3 * p + 1] = result.y; out_f64[3 * p + 2] = result.z;
         } else if (cam.out_format == RTC_OUT_F32_RGB) {

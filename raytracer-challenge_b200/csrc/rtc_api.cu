@@ -6,6 +6,7 @@
 #include <chrono>
 #include <cmath>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <string>
 #include <thread>
@@ -59,6 +60,9 @@ struct DeviceState {
     DevBuf<int32_t> sph_index, pl_index, us_index, gs_index, gset;
     DevBuf<ShadeRec64> rec64;
     DevBuf<ShadeRec32> rec32;
+    DevBuf<SmallRec32> srec;   // small-scene shading records, by stream position
+    SmallParams small{};       // scene part of the small-scene kernel parameter (camera part filled per launch)
+    bool small_ok = false;
     DevScene64 s64{};
     DevScene32 s32{};
     // frame
@@ -67,6 +71,26 @@ struct DeviceState {
     DevBuf<Counters> counters;
     DevBuf<unsigned> work;  // tile counter of the persistent f32 kernel
 };
+
+// Allocation base of a device pointer (cuMemGetAddressRange, fetched through the runtime so that the
+// library does not link libcuda directly).
+typedef unsigned long long CUdeviceptr_v;
+int cuMemGetAddressRange_shim(void** base, size_t* size, const void* ptr) {
+    typedef int (*fn_t)(CUdeviceptr_v*, size_t*, CUdeviceptr_v);
+    static fn_t fn = nullptr;
+    if (!fn) {
+        void* f = nullptr;
+        cudaDriverEntryPointQueryResult qr;
+        if (cudaGetDriverEntryPoint("cuMemGetAddressRange", &f, cudaEnableDefault, &qr) != cudaSuccess || !f) return -1;
+        fn = (fn_t)f;
+    }
+    CUdeviceptr_v b = 0;
+    size_t sz = 0;
+    int rc = fn(&b, &sz, (CUdeviceptr_v)(uintptr_t)ptr);
+    *base = (void*)(uintptr_t)b;
+    *size = sz;
+    return rc;
+}
 
 size_t elem_size(int out_format) {
     return out_format == RTC_OUT_F64_RGB ? 8 : (out_format == RTC_OUT_F32_RGB ? 4 : 1);
@@ -133,6 +157,7 @@ CamParams make_cam(const rtc_camera* cam, const rtc_render_opts* o, int shard_in
     c.tile_rows = tile_rows > 0 ? tile_rows : 16;
     c.shard_rows = shard_num_rows((int)cam->vsize, c.tile_rows, c.shard_index, c.shard_count);
     c.out_format = o->out_format;
+    c.dst_full = 0;
     return c;
 }
 
@@ -144,6 +169,10 @@ struct HostScene {
     std::vector<ShadeRec64> rec64;
     std::vector<ShadeRec32> rec32;
     int ids_unique = 1;
+    // small-scene form (render_f32_small.cu)
+    bool small_ok = false;
+    SmallParams small{};
+    std::vector<SmallRec32> srec;
 };
 
 inline float __int_as_float_host(int v) {
@@ -162,7 +191,7 @@ void mul34(const double* a, const double* b, double* out) {  // (a as 3x4 affine
         }
 }
 
-int flatten(const rtc_shape* shapes, size_t n, HostScene& hs) {
+int flatten(const rtc_light* light, const rtc_shape* shapes, size_t n, HostScene& hs) {
     bool seen[256] = {false};
     hs.rec64.resize(n);
     hs.rec32.resize(n);
@@ -261,6 +290,61 @@ int flatten(const rtc_shape* shapes, size_t n, HostScene& hs) {
     for (int k = 0; k < np; ++k) if (shapes[hs.pl_index[k]].refractive_index != 1.0) hs.gset.push_back(k);
     for (int k = 0; k < nu; ++k) if (shapes[hs.us_index[k]].refractive_index != 1.0) hs.gset.push_back(np + k);
     for (int k = 0; k < (int)hs.gs_index.size(); ++k) if (shapes[hs.gs_index[k]].refractive_index != 1.0) hs.gset.push_back(np + nu + k);
+
+    // ---- small-scene form: constant-bank streams + records by stream position ----
+    SmallParams& sp = hs.small;
+    std::memset(&sp, 0, sizeof sp);
+    bool ok = np <= kSmallMaxPlanes && nu <= kSmallMaxUsph && hs.gs_index.empty() && hs.ids_unique && np + nu > 0;
+    const double lp[3] = {light->position[0], light->position[1], light->position[2]};
+    for (int k = 0; ok && k < nu; ++k) {   // light inside a sphere: the convex-minimum shadow test does not apply
+        const float4& u = hs.us32[k];
+        double dx = lp[0] - u.x, dy = lp[1] - u.y, dz = lp[2] - u.z;
+        if (dx * dx + dy * dy + dz * dz - u.w <= 0.0) ok = false;
+    }
+    if (ok) {
+        for (int k = 0; k < kSmallMaxPlanes; ++k) sp.planes[k] = sp.planes_d[k] = sp.splanes[k] = make_float4(0.f, 0.f, 0.f, 1.f);
+        for (int k = 0; k < kSmallMaxUsph; ++k) sp.usph[k] = sp.usph_s[k] = make_float4(0.f, 0.f, 0.f, -1.f);
+        hs.srec.assign(kSmallMaxShapes, SmallRec32{});
+        sp.np = np; sp.nu = nu; sp.npg = (np + 3) / 4; sp.nug = (nu + 3) / 4;
+        int n_glass = 0;
+        auto fill_common = [&](SmallRec32& r, const rtc_shape& s, const ShadeRec32& q) {
+            r.col_amb = q.col_amb; r.dif_spec = q.dif_spec;
+            r.tr_ri = make_float4((float)s.transparency, (float)s.refractive_index, __int_as_float_host(s.pattern_kind), 0.f);
+            r.p0 = q.p0; r.p1 = q.p1; r.p2 = q.p2;
+            r.pa = make_float4(q.pa.x, q.pa.y, q.pa.z, 0.f);
+            r.pb = make_float4(q.pb.x, q.pb.y, q.pb.z, s.pattern_kind == RTC_PATTERN_CHECKER ? 1.f : 0.f);
+        };
+        for (int k = 0; k < np; ++k) {
+            const int i = hs.pl_index[k];
+            const float4 pl = hs.pl32[k];
+            sp.planes[k] = sp.planes_d[k] = pl;
+            // f(1) = n.light + w: fold it into the coefficients so that the shadow test is splane.(o,1) <= 0
+            const double f1 = shapes[i].inv[4] * lp[0] + shapes[i].inv[5] * lp[1] + shapes[i].inv[6] * lp[2] + shapes[i].inv[7];
+            const double sc = f1 / (std::fabs(f1) > 0.0 ? std::fabs(f1) : 1.0);   // sign only: keeps the magnitudes of the plane
+            sp.splanes[k] = make_float4((float)(shapes[i].inv[4] * sc), (float)(shapes[i].inv[5] * sc), (float)(shapes[i].inv[6] * sc),
+                                        (float)(shapes[i].inv[7] * sc));
+            SmallRec32& r = hs.srec[k];
+            const float4 g0 = hs.rec32[i].g0;
+            r.nrm = make_float4(g0.x, g0.y, g0.z, 0.f);
+            fill_common(r, shapes[i], hs.rec32[i]);
+            if (shapes[i].refractive_index != 1.0) n_glass = -1000;   // a glass plane: no fast n1/n2 test
+        }
+        for (int k = 0; k < nu; ++k) {
+            const int i = hs.us_index[k];
+            sp.usph[k] = sp.usph_s[k] = hs.us32[k];
+            SmallRec32& r = hs.srec[kSmallMaxPlanes + k];
+            const float4 g0 = hs.rec32[i].g0;   // (c, 1/r)
+            r.nrm = make_float4(-g0.x * g0.w, -g0.y * g0.w, -g0.z * g0.w, g0.w);
+            fill_common(r, shapes[i], hs.rec32[i]);
+            if (shapes[i].refractive_index != 1.0) {
+                if (n_glass >= 0 && n_glass < kSmallMaxGlass) sp.glass[n_glass] = hs.us32[k];
+                ++n_glass;
+            }
+        }
+        sp.n_glass = (n_glass < 0 || n_glass > kSmallMaxGlass) ? -1 : n_glass;
+        for (int k = 0; k < 3; ++k) { sp.light_pos[k] = (float)light->position[k]; sp.light_int[k] = (float)light->intensity[k]; }
+    }
+    hs.small_ok = ok;
     return RTC_OK;
 }
 
@@ -351,10 +435,33 @@ void parallel_copy(unsigned char* dst, const unsigned char* src, size_t n) {
     for (auto& th : pool) th.join();
 }
 
-int launch_on(DeviceState& d, const CamParams& cp, int precision, void* d_rgb, uint8_t* d_hit, Counters* d_counters,
+// Camera part of the small-scene kernel parameter: Camera::ray_for_pixel_offset (src/camera.rs:64-76) reduced to
+//   dir = normalize(cam_dx (x + xo) + cam_dy (y + yo) + cam_d0),   origin = Vinv * (0,0,0)
+void fill_small_camera(SmallParams& P, const CamParams& cam) {
+    const double* v = cam.vinv;
+    for (int k = 0; k < 3; ++k) {
+        P.cam_o[k] = (float)v[4 * k + 3];
+        P.cam_dx[k] = (float)(-cam.pixel_size * v[4 * k + 0]);
+        P.cam_dy[k] = (float)(-cam.pixel_size * v[4 * k + 1]);
+        P.cam_d0[k] = (float)(cam.half_width * v[4 * k + 0] + cam.half_height * v[4 * k + 1] - v[4 * k + 2]);
+    }
+    P.hsize = (int)cam.hsize; P.shard_rows = cam.shard_rows; P.xlim = (int)cam.xlim; P.ylim = (int)cam.ylim;
+    P.shard_index = cam.shard_index; P.shard_count = cam.shard_count; P.tile_rows = cam.tile_rows; P.dst_full = cam.dst_full;
+    P.n_sub = cam.samples == 1 ? 1 : 4;
+    P.max_depth = cam.max_depth;
+    P.tiles_x = ((int)cam.hsize + 7) / 8;
+    P.total_tiles = P.tiles_x * ((cam.shard_rows + 3) / 4);
+}
+
+int launch_on(DeviceState& d, const CamParams& cp, int precision, int flags, void* d_rgb, uint8_t* d_hit, Counters* d_counters,
               cudaStream_t st) {
-    cudaError_t e = precision == RTC_PRECISION_F64_PARITY ? launch_render_f64(d.s64, cp, d_rgb, d_hit, d_counters, st)
-                                                          : launch_render_f32(d.s32, cp, d_rgb, d_hit, d_counters, d.work.p, st);
+    cudaError_t e;
+    if (precision == RTC_PRECISION_F64_PARITY) e = launch_render_f64(d.s64, cp, d_rgb, d_hit, d_counters, st);
+    else if (d.small_ok && !(flags & RTC_OPT_F32_GENERAL_KERNEL)) {
+        SmallParams P = d.small;
+        fill_small_camera(P, cp);
+        e = launch_render_f32_small(P, cp.out_format, d_rgb, d_hit, d_counters, d.work.p, st);
+    } else e = launch_render_f32(d.s32, cp, d_rgb, d_hit, d_counters, d.work.p, st);
     if (e != cudaSuccess) return fail(RTC_ERR_CUDA, std::string("kernel launch: ") + cudaGetErrorString(e));
     return RTC_OK;
 }
@@ -418,7 +525,7 @@ void rtc_context_destroy(rtc_context* ctx) {
         cudaSetDevice(d.dev);
         if (d.stream) cudaStreamSynchronize(d.stream);
         d.sph64.release(); d.pl64.release(); d.pl32.release(); d.us32.release(); d.gs32.release(); d.us_index.release(); d.gs_index.release(); d.gset.release();
-        d.sph_index.release(); d.pl_index.release(); d.rec64.release(); d.rec32.release();
+        d.sph_index.release(); d.pl_index.release(); d.rec64.release(); d.rec32.release(); d.srec.release();
         d.rgb.release(); d.hit.release(); d.counters.release(); d.work.release();
         if (d.ev_k0) cudaEventDestroy(d.ev_k0);
         if (d.ev_k1) cudaEventDestroy(d.ev_k1);
@@ -434,7 +541,7 @@ void rtc_context_destroy(rtc_context* ctx) {
 int rtc_scene_upload(rtc_context* ctx, const rtc_light* light, const rtc_shape* shapes, size_t n_shapes) {
     if (!ctx || !light || (!shapes && n_shapes)) return fail(RTC_ERR_INVALID_ARG, "rtc_scene_upload: null argument");
     HostScene hs;
-    int rc = flatten(shapes, n_shapes, hs);
+    int rc = flatten(light, shapes, n_shapes, hs);
     if (rc != RTC_OK) return rc;
     for (DeviceState& d : ctx->devs) {
         CUDA_TRY(cudaSetDevice(d.dev));
@@ -450,6 +557,12 @@ int rtc_scene_upload(rtc_context* ctx, const rtc_light* light, const rtc_shape* 
         CUDA_TRY(upload(d.pl_index, hs.pl_index, d.stream));
         CUDA_TRY(upload(d.rec64, hs.rec64, d.stream));
         CUDA_TRY(upload(d.rec32, hs.rec32, d.stream));
+        d.small_ok = hs.small_ok;
+        if (hs.small_ok) {
+            CUDA_TRY(upload(d.srec, hs.srec, d.stream));
+            d.small = hs.small;
+            d.small.rec = d.srec.p;
+        }
         d.s64.n_shapes = d.s32.n_shapes = (int)n_shapes;
         d.s64.n_spheres = (int)hs.sph_index.size();
         d.s32.n_usph = (int)hs.us_index.size();
@@ -488,13 +601,14 @@ int rtc_render_device(rtc_context* ctx, const rtc_camera* cam, const rtc_render_
     DeviceState& d = ctx->devs[0];
     CUDA_TRY(cudaSetDevice(d.dev));
     CamParams cp = make_cam(cam, opts, opts->shard_index, opts->shard_count, opts->tile_rows);
+    cp.dst_full = (opts->flags & RTC_OPT_DST_FULL_FRAME) ? 1 : 0;
     if (stream) {
-        return launch_on(d, cp, opts->precision, d_out_rgb, d_out_hit_mask, nullptr, (cudaStream_t)stream);
+        return launch_on(d, cp, opts->precision, opts->flags, d_out_rgb, d_out_hit_mask, nullptr, (cudaStream_t)stream);
     }
     auto t0 = std::chrono::steady_clock::now();
     CUDA_TRY(cudaMemsetAsync(d.counters.p, 0, sizeof(Counters), d.stream));
     CUDA_TRY(cudaEventRecord(d.ev_k0, d.stream));
-    rc = launch_on(d, cp, opts->precision, d_out_rgb, d_out_hit_mask, d.counters.p, d.stream);
+    rc = launch_on(d, cp, opts->precision, opts->flags, d_out_rgb, d_out_hit_mask, d.counters.p, d.stream);
     if (rc != RTC_OK) return rc;
     CUDA_TRY(cudaEventRecord(d.ev_k1, d.stream));
     CUDA_TRY(cudaMemcpyAsync(&ctx->pinned_counters[0], d.counters.p, sizeof(Counters), cudaMemcpyDeviceToHost, d.stream));
@@ -538,6 +652,45 @@ int rtc_assemble_device(rtc_context* ctx, const rtc_camera* cam, const rtc_rende
     return RTC_OK;
 }
 
+int rtc_ipc_export(rtc_context* ctx, const void* d_ptr, void* handle, uint64_t* offset) {
+    if (!ctx || !d_ptr || !handle || !offset) return fail(RTC_ERR_INVALID_ARG, "rtc_ipc_export: null argument");
+    static_assert(sizeof(cudaIpcMemHandle_t) == RTC_IPC_HANDLE_BYTES, "handle size");
+    CUDA_TRY(cudaSetDevice(ctx->devs[0].dev));
+    CUdeviceptr_v base = 0;  // allocation base: the handle always refers to the start of the allocation
+    {
+        cudaPointerAttributes at;
+        CUDA_TRY(cudaPointerGetAttributes(&at, d_ptr));
+        if (at.type != cudaMemoryTypeDevice) return fail(RTC_ERR_INVALID_ARG, "rtc_ipc_export: not a device pointer");
+        void* b = nullptr;
+        size_t sz = 0;
+        if (cuMemGetAddressRange_shim(&b, &sz, d_ptr) != 0) return fail(RTC_ERR_CUDA, "rtc_ipc_export: cannot find the allocation base");
+        base = (CUdeviceptr_v)(uintptr_t)b;
+    }
+    cudaIpcMemHandle_t h;
+    CUDA_TRY(cudaIpcGetMemHandle(&h, (void*)(uintptr_t)base));
+    std::memcpy(handle, &h, sizeof h);
+    *offset = (uint64_t)((uintptr_t)d_ptr - (uintptr_t)base);
+    return RTC_OK;
+}
+
+int rtc_ipc_open(rtc_context* ctx, const void* handle, uint64_t offset, void** out_d_ptr) {
+    if (!ctx || !handle || !out_d_ptr) return fail(RTC_ERR_INVALID_ARG, "rtc_ipc_open: null argument");
+    CUDA_TRY(cudaSetDevice(ctx->devs[0].dev));
+    cudaIpcMemHandle_t h;
+    std::memcpy(&h, handle, sizeof h);
+    void* base = nullptr;
+    CUDA_TRY(cudaIpcOpenMemHandle(&base, h, cudaIpcMemLazyEnablePeerAccess));
+    *out_d_ptr = (char*)base + offset;
+    return RTC_OK;
+}
+
+int rtc_ipc_close(rtc_context* ctx, void* d_ptr, uint64_t offset) {
+    if (!ctx || !d_ptr) return fail(RTC_ERR_INVALID_ARG, "rtc_ipc_close: null argument");
+    CUDA_TRY(cudaSetDevice(ctx->devs[0].dev));
+    CUDA_TRY(cudaIpcCloseMemHandle((char*)d_ptr - offset));
+    return RTC_OK;
+}
+
 int rtc_measure_peak_tflops(rtc_context* ctx, int precision, double* out_tflops) {
     if (!ctx || !out_tflops) return fail(RTC_ERR_INVALID_ARG, "rtc_measure_peak_tflops: null argument");
     DeviceState& d = ctx->devs[0];
@@ -577,7 +730,7 @@ extern "C" int rtc_render(rtc_context* ctx, const rtc_camera* cam, const rtc_ren
         if (out_hit_mask) CUDA_TRY(d.hit.ensure((size_t)cp.shard_rows * cam->hsize));
         CUDA_TRY(cudaMemsetAsync(d.counters.p, 0, sizeof(Counters), d.stream));
         CUDA_TRY(cudaEventRecord(d.ev_k0, d.stream));
-        rc = launch_on(d, cp, opts->precision, d.rgb.p, out_hit_mask ? d.hit.p : nullptr, d.counters.p, d.stream);
+        rc = launch_on(d, cp, opts->precision, opts->flags, d.rgb.p, out_hit_mask ? d.hit.p : nullptr, d.counters.p, d.stream);
         if (rc != RTC_OK) return rc;
         CUDA_TRY(cudaEventRecord(d.ev_k1, d.stream));
         if (G == 1) {

@@ -80,6 +80,42 @@ struct DevScene32 {
     float light_int[3];
 };
 
+// ---- f32 small-scene layout (render_f32_small.cu) ------------------------------------------------
+// Scenes with <= 16 planes and <= 48 spheres, all of them similarity-transformed, travel to the kernel
+// as a __grid_constant__ parameter: the intersect streams sit in constant bank 0 and every
+// coefficient is a direct c[0x0][imm] operand of the FP32 instruction that uses it.
+constexpr int kSmallMaxPlanes = 16, kSmallMaxUsph = 48, kSmallMaxShapes = 64, kSmallMaxGlass = 8;
+
+struct __align__(16) SmallRec32 {   // shading record, indexed by stream position
+    float4 nrm;       // world normal n = p * nrm.w + nrm.xyz   (plane: w = 0, xyz = n; sphere: w = 1/r, xyz = -c/r)
+    float4 col_amb;   // colour rgb, ambient
+    float4 dif_spec;  // diffuse, specular, shininess, reflective
+    float4 tr_ri;     // transparency, refractive_index, (int) pattern_kind, unused
+    float4 p0, p1, p2;  // world -> pattern space rows (pattern_inv * shape_inv)
+    float4 pa, pb;    // pattern colours; pb.w = 1 for CHECKER, 0 for STRIPE
+};
+
+struct SmallParams {
+    // Stream positions: plane i -> i, sphere i -> 16 + i.  Arrays that two different loops read are
+    // stored twice so that each copy has a single use and stays a direct constant operand.
+    float4 planes[kSmallMaxPlanes];    // (nx, ny, nz, w) = row 1 of the inverse; padding (0,0,0,1): t = -inf
+    float4 planes_d[kSmallMaxPlanes];  // same rows again (the n.d use)
+    float4 splanes[kSmallMaxPlanes];   // planes * f(light): shadow test g = splane . (o,1); padding (0,0,0,1)
+    float4 usph[kSmallMaxUsph];        // (cx, cy, cz, r^2); padding (0,0,0,-1): never hit
+    float4 usph_s[kSmallMaxUsph];      // same again (the shadow loop's copy)
+    float4 glass[kSmallMaxGlass];      // the spheres with refractive_index != 1
+    int npg, nug;                      // plane / sphere groups of four
+    int np, nu;
+    int n_glass;                       // -1: fast n1/n2 test unavailable (a glass plane, or more than 8 glass spheres)
+    int pad0;
+    const SmallRec32* rec;             // [64] by stream position (global, staged to shared memory per block)
+    float light_pos[3], light_int[3];
+    float cam_o[3], cam_dx[3], cam_dy[3], cam_d0[3];   // ray dir = normalize(cam_dx (x+xo) + cam_dy (y+yo) + cam_d0)
+    int hsize, shard_rows, xlim, ylim;
+    int shard_index, shard_count, tile_rows, dst_full;
+    int n_sub, max_depth, tiles_x, total_tiles;
+};
+
 // ---- per-launch parameters --------------------------------------------------------------------
 struct CamParams {
     uint32_t hsize, vsize;
@@ -92,6 +128,7 @@ struct CamParams {
     int32_t shard_index, shard_count, tile_rows;
     int32_t shard_rows;   // rows in this shard's compact buffer
     int32_t out_format;   // RTC_OUT_*
+    int32_t dst_full;     // 1: the destination is a full frame (rows at their frame positions), not the compact shard buffer
 };
 
 struct Counters {
@@ -123,5 +160,8 @@ cudaError_t launch_render_f64(const DevScene64& scene, const CamParams& cam, voi
                               Counters* d_counters, cudaStream_t stream);
 cudaError_t launch_render_f32(const DevScene32& scene, const CamParams& cam, void* d_rgb, uint8_t* d_hit,
                               Counters* d_counters, unsigned* d_work, cudaStream_t stream);
+
+cudaError_t launch_render_f32_small(const SmallParams& P, int out_format, void* d_rgb, uint8_t* d_hit, Counters* d_counters,
+                                    unsigned* d_work, cudaStream_t stream);
 
 }  // namespace rtc

@@ -18,6 +18,9 @@ PRECISION_F64_PARITY, PRECISION_F32_FAST = 0, 1
 RECT_REFERENCE_RENDER, RECT_FULL = 0, 1
 OUT_F64_RGB, OUT_F32_RGB, OUT_U8_RGB = 0, 1, 2
 RTC_MAX_DEPTH = 8
+OPT_DST_FULL_FRAME = 1
+OPT_F32_GENERAL_KERNEL = 2
+IPC_HANDLE_BYTES = 64
 
 
 class RtcShape(C.Structure):
@@ -49,7 +52,7 @@ class RtcCamera(C.Structure):
 class RtcRenderOpts(C.Structure):
     _fields_ = [
         ("precision", C.c_int32), ("rect", C.c_int32), ("max_depth", C.c_int32), ("out_format", C.c_int32),
-        ("shard_index", C.c_int32), ("shard_count", C.c_int32), ("tile_rows", C.c_int32), ("reserved", C.c_int32),
+        ("shard_index", C.c_int32), ("shard_count", C.c_int32), ("tile_rows", C.c_int32), ("flags", C.c_int32),
     ]
 
 
@@ -80,6 +83,9 @@ EXPORTS = [
                                     C.c_void_p, C.c_void_p, C.POINTER(RtcStats)]),
     ("rtc_assemble_device", C.c_int, [C.c_void_p, C.POINTER(RtcCamera), C.POINTER(RtcRenderOpts), C.c_void_p,
                                       C.c_int, C.c_int, C.c_void_p, C.c_void_p]),
+    ("rtc_ipc_export", C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.POINTER(C.c_uint64)]),
+    ("rtc_ipc_open", C.c_int, [C.c_void_p, C.c_void_p, C.c_uint64, C.POINTER(C.c_void_p)]),
+    ("rtc_ipc_close", C.c_int, [C.c_void_p, C.c_void_p, C.c_uint64]),
     ("rtc_measure_peak_tflops", C.c_int, [C.c_void_p, C.c_int, C.POINTER(C.c_double)]),
 ]
 

@@ -188,11 +188,13 @@ def test_unsupported_inputs_are_errors_not_fallbacks(rtc, renderer):
 
 
 # ---- f32 fast mode ---------------------------------------------------------------------------------
-def _check32(rtc, orc, renderer, world, cam, rect=1, max_depth=5, min_ok=0.999, ray_tol=0.002):
+def _check32(rtc, orc, renderer, world, cam, rect=1, max_depth=5, min_ok=0.999, ray_tol=0.002, general=False):
+    """general=True forces the general f32 kernel (render_f32.cu); otherwise scenes that fit take the
+    constant-bank small-scene kernel (render_f32_small.cu)."""
     renderer.upload(world)
     want, want_hit, cnt = orc.OracleWorld(world).render(cam, rect=rect, max_depth=max_depth, threads=NCPU)
     opts = rtc.Renderer.make_opts(precision=rtc.ffi.PRECISION_F32_FAST, rect=rect, max_depth=max_depth,
-                                  out_format=rtc.ffi.OUT_F32_RGB)
+                                  out_format=rtc.ffi.OUT_F32_RGB, flags=rtc.ffi.OPT_F32_GENERAL_KERNEL if general else 0)
     got, hit, stats = renderer.render(cam.flatten(), opts)
     assert np.isfinite(got).all()
     q_got = orc.quantize_u8(got.astype(np.float64)).astype(int)   # Color::scale, src/color.rs:100-114
@@ -204,12 +206,79 @@ def _check32(rtc, orc, renderer, world, cam, rect=1, max_depth=5, min_ok=0.999, 
     return ok, mask_mismatch, stats
 
 
-@pytest.mark.parametrize("size,samples", [((320, 160), 1), ((400, 200), 1), ((160, 80), 0), ((33, 17), 1)])
-def test_f32_reflect_refract(rtc, orc, renderer, size, samples):
+@pytest.mark.parametrize("general", [False, True])
+@pytest.mark.parametrize("size,samples", [((320, 160), 1), ((400, 200), 1), ((160, 80), 0), ((33, 17), 1), ((1, 1), 1), ((9, 5), 0)])
+def test_f32_reflect_refract(rtc, orc, renderer, size, samples, general):
     world = rtc.scenes.reflect_refract_scene()
     cam = rtc.scenes.reflect_refract_camera(size[0], size[1], samples=samples)
-    ok, mm, stats = _check32(rtc, orc, renderer, world, cam)
+    ok, mm, stats = _check32(rtc, orc, renderer, world, cam, general=general, min_ok=0.999 if size[0] * size[1] >= 1000 else 0.97)
     assert mm == 0  # closed room: every primary ray hits in both precisions
+
+
+@pytest.mark.parametrize("general", [False, True])
+@pytest.mark.parametrize("depth", [0, 1, 3, 8])
+def test_f32_depth_limits(rtc, orc, renderer, depth, general):
+    world = rtc.scenes.reflect_refract_scene()
+    cam = rtc.scenes.reflect_refract_camera(200, 100)
+    _check32(rtc, orc, renderer, world, cam, max_depth=depth, general=general)
+
+
+def test_f32_c2_full_hd(rtc, orc, renderer):
+    """Config C2: the reflect/refract room at 1920x1080, f32 fast mode vs the oracle (all host threads)."""
+    world = rtc.scenes.reflect_refract_scene()
+    cam = rtc.scenes.reflect_refract_camera(1920, 1080)
+    ok, mm, stats = _check32(rtc, orc, renderer, world, cam)
+    assert mm == 0
+
+
+def _glass_world(rtc, n_glass, glass_plane=False):
+    """Uniform spheres only (small-scene kernel), nested and overlapping glass, optional glass plane."""
+    rnd = random.Random(100 + n_glass)
+    w = rtc.World(rtc.Light(rtc.Color(1, 1, 1), (-6, 9, -7)))
+    floor = rtc.Material(specular=0.0, reflectiveness=0.2, pattern=rtc.CheckerPattern(rtc.Color(0.3, 0.3, 0.3), rtc.Color(0.7, 0.7, 0.7)))
+    w.add_shape(rtc.Plane(rtc.Matrix.identity().translation(0, -1, 0), floor))
+    w.add_shape(rtc.Plane(rtc.Matrix.identity().rotation_x(math.pi / 2).translation(0, 0, 14),
+                          rtc.Material(color=rtc.Color(0.5, 0.6, 0.7), specular=0.1)))
+    if glass_plane:
+        w.add_shape(rtc.Plane(rtc.Matrix.identity().translation(0, -0.5, 0),
+                              rtc.Material(color=rtc.Color(0.05, 0.1, 0.1), diffuse=0.2, reflectiveness=0.3, transparency=0.8, refractive_index=1.33)))
+    for r, ri in ((2.0, 1.5), (1.4, 2.0), (0.8, 1.2)):   # src/shape.rs:1269-1304 style nesting
+        w.add_shape(rtc.Sphere(rtc.Matrix.identity().scaling(r, r, r).translation(0, 1.2, 3),
+                               rtc.Material(color=rtc.Color(0.1, 0.1, 0.1), diffuse=0.2, reflectiveness=0.5, transparency=0.9, refractive_index=ri)))
+    for i in range(n_glass):
+        r = rnd.uniform(0.4, 0.9)
+        w.add_shape(rtc.Sphere(rtc.Matrix.identity().scaling(r, r, r).translation(rnd.uniform(-4, 4), rnd.uniform(0, 2), rnd.uniform(0, 7)),
+                               rtc.Material(color=rtc.Color(rnd.random() * 0.3, rnd.random() * 0.3, rnd.random() * 0.3), diffuse=0.3,
+                                            reflectiveness=0.6, transparency=0.8, refractive_index=rnd.uniform(1.1, 2.0))))
+    for i in range(8):
+        r = rnd.uniform(0.3, 0.8)
+        w.add_shape(rtc.Sphere(rtc.Matrix.identity().scaling(r, r, r).translation(rnd.uniform(-5, 5), rnd.uniform(-0.5, 3), rnd.uniform(-1, 9)),
+                               rtc.Material(color=rtc.Color(rnd.random(), rnd.random(), rnd.random()), reflectiveness=rnd.choice([0, 0, 0.5]))))
+    cam = rtc.Camera.new_with_transform(240, 160, 1.0, rtc.Matrix.make_view_transform((0, 2.0, -7.0), (0, 1, 3), (0, 1, 0)))
+    return w, cam
+
+
+@pytest.mark.parametrize("general", [False, True])
+@pytest.mark.parametrize("n_glass,glass_plane", [(2, False), (12, False), (3, True)])
+def test_f32_nested_glass_small_scene(rtc, orc, renderer, n_glass, glass_plane, general):
+    """compute_refractive in both f32 kernels: fast n1/n2 test (<= 8 glass spheres), its overflow
+    (> 8) and a glass plane (fast test unavailable)."""
+    w, cam = _glass_world(rtc, n_glass, glass_plane)
+    _check32(rtc, orc, renderer, w, cam, min_ok=0.995, ray_tol=0.01, general=general)
+
+
+def test_f32_camera_inside_glass(rtc, orc, renderer):
+    w, _ = _glass_world(rtc, 2)
+    cam = rtc.Camera.new_with_transform(160, 120, 1.3, rtc.Matrix.make_view_transform((0.2, 1.3, 2.6), (0, 1.0, 8), (0, 1, 0)))
+    _check32(rtc, orc, renderer, w, cam, min_ok=0.99, ray_tol=0.01)
+
+
+def test_f32_light_inside_sphere_takes_general_kernel(rtc, orc, renderer):
+    """A light inside a (glass) sphere disqualifies the small-scene kernel's shadow test; the general
+    kernel's light_inside variant must give the same image as the oracle."""
+    w, cam = _glass_world(rtc, 2)
+    w.light = rtc.Light(rtc.Color(1, 1, 1), (0, 1.2, 3))   # centre of the nested glass spheres
+    _check32(rtc, orc, renderer, w, cam, min_ok=0.99, ray_tol=0.01)
 
 
 def test_f32_reference_rect_and_formats(rtc, orc, renderer):
@@ -218,6 +287,13 @@ def test_f32_reference_rect_and_formats(rtc, orc, renderer):
     renderer.upload(world)
     d = cam.flatten()
     mk = lambda fmt: rtc.Renderer.make_opts(precision=rtc.ffi.PRECISION_F32_FAST, rect=rtc.ffi.RECT_REFERENCE_RENDER, out_format=fmt)
+    _f32_formats(rtc, orc, renderer, d, mk)
+    mk = lambda fmt: rtc.Renderer.make_opts(precision=rtc.ffi.PRECISION_F32_FAST, rect=rtc.ffi.RECT_REFERENCE_RENDER, out_format=fmt,
+                                            flags=rtc.ffi.OPT_F32_GENERAL_KERNEL)
+    _f32_formats(rtc, orc, renderer, d, mk)
+
+
+def _f32_formats(rtc, orc, renderer, d, mk):
     f32, hit, _ = renderer.render(d, mk(rtc.ffi.OUT_F32_RGB))
     f64, _, _ = renderer.render(d, mk(rtc.ffi.OUT_F64_RGB))
     u8, _, _ = renderer.render(d, mk(rtc.ffi.OUT_U8_RGB))
@@ -226,9 +302,10 @@ def test_f32_reference_rect_and_formats(rtc, orc, renderer):
     assert np.abs(u8.astype(int) - orc.quantize_u8(f64).astype(int)).max() <= 1
 
 
-def test_f32_bench_scene(rtc, orc, renderer):
+@pytest.mark.parametrize("general", [False, True])
+def test_f32_bench_scene(rtc, orc, renderer, general):
     world, cam = rtc.scenes.bench_scene()
-    _check32(rtc, orc, renderer, world, cam)
+    _check32(rtc, orc, renderer, world, cam, general=general)
 
 
 @pytest.mark.parametrize("seed", [1, 2, 3])
@@ -237,3 +314,44 @@ def test_f32_random_worlds(rtc, orc, renderer, seed):
     (pattern edges and grazing refraction amplify rounding); the 99.9 % bar is for the named scenes."""
     w, cam = _random_world(rtc, seed)
     _check32(rtc, orc, renderer, w, cam, min_ok=0.98, ray_tol=0.02)
+
+
+# ---- row-tile sharding through rtc_render_device ---------------------------------------------------
+@pytest.mark.parametrize("precision", [0, 1])
+@pytest.mark.parametrize("count,tile", [(2, 16), (3, 4), (8, 16)])
+def test_shards_compact_gather_and_full_frame_destination(rtc, orc, renderer, precision, count, tile):
+    """Every shard rendered on this GPU: (a) compact buffers + rtc_assemble_device (the NCCL-gather
+    layout), (b) RTC_OPT_DST_FULL_FRAME straight into one frame (the peer-store layout).  Both must
+    equal the unsharded render bit for bit."""
+    import torch
+    world = rtc.scenes.reflect_refract_scene()
+    cam = rtc.scenes.reflect_refract_camera(200, 117, samples=1)
+    d = cam.flatten()
+    renderer.upload(world)
+    fmt = rtc.ffi.OUT_F64_RGB if precision == 0 else rtc.ffi.OUT_F32_RGB
+    dt = torch.float64 if precision == 0 else torch.float32
+    whole = torch.zeros((117, 200, 3), dtype=dt, device="cuda")
+    whole_hit = torch.zeros((117, 200), dtype=torch.uint8, device="cuda")
+    renderer.render_device(d, rtc.Renderer.make_opts(precision=precision, out_format=fmt), whole.data_ptr(), whole_hit.data_ptr())
+    o0 = rtc.Renderer.make_opts(precision=precision, out_format=fmt, shard_index=0, shard_count=count, tile_rows=tile)
+    stride = renderer.shard_rows(d, o0)
+    gathered = torch.zeros((count, stride, 200, 3), dtype=dt, device="cuda")
+    gathered_hit = torch.zeros((count, stride, 200), dtype=torch.uint8, device="cuda")
+    full = torch.zeros_like(whole)
+    full_hit = torch.zeros_like(whole_hit)
+    rows = 0
+    for k in range(count):
+        ok = rtc.Renderer.make_opts(precision=precision, out_format=fmt, shard_index=k, shard_count=count, tile_rows=tile)
+        rows += renderer.shard_rows(d, ok)
+        renderer.render_device(d, ok, gathered[k].data_ptr(), gathered_hit[k].data_ptr())
+        okf = rtc.Renderer.make_opts(precision=precision, out_format=fmt, shard_index=k, shard_count=count, tile_rows=tile,
+                                     flags=rtc.ffi.OPT_DST_FULL_FRAME)
+        renderer.render_device(d, okf, full.data_ptr(), full_hit.data_ptr())
+    assert rows == 117
+    frame = torch.zeros_like(whole)
+    frame_hit = torch.zeros_like(whole_hit)
+    renderer.assemble_device(d, o0, gathered.data_ptr(), stride, fmt, frame.data_ptr())
+    renderer.assemble_device(d, o0, gathered_hit.data_ptr(), stride, -1, frame_hit.data_ptr())
+    torch.cuda.synchronize()
+    assert torch.equal(frame, whole) and torch.equal(frame_hit, whole_hit)
+    assert torch.equal(full, whole) and torch.equal(full_hit, whole_hit)
