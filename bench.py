@@ -147,6 +147,7 @@ def run_gpu(args):
     import torch.distributed as dist
     import rtc_b200 as rtc
     from rtc_b200 import ffi
+    from rtc_b200.sharded import ShardedFrame
 
     rank = int(os.environ.get("RANK", "0"))
     world_size = int(os.environ.get("WORLD_SIZE", "1"))
@@ -165,34 +166,46 @@ def run_gpu(args):
     camd = cam.flatten()
     r.upload_flat(*flat)
     TILE = 16
-    mk = lambda prec, fmt: rtc.Renderer.make_opts(precision=prec, rect=ffi.RECT_FULL, max_depth=DEPTH, out_format=fmt,
-                                                  shard_index=rank, shard_count=N, tile_rows=TILE)
-    o32 = mk(ffi.PRECISION_F32_FAST, ffi.OUT_F32_RGB)
-    o64 = mk(ffi.PRECISION_F64_PARITY, ffi.OUT_F64_RGB)
-    o0 = rtc.Renderer.make_opts(shard_index=0, shard_count=N, tile_rows=TILE)
-    stride_rows = r.shard_rows(camd, o0)          # shard 0 owns the most rows
-    my_rows = r.shard_rows(camd, o32)
-    d32 = torch.zeros((stride_rows, W, 3), dtype=torch.float32, device=dev)
-    d64 = torch.zeros((stride_rows, W, 3), dtype=torch.float64, device=dev)
-    g32 = torch.empty((N, stride_rows, W, 3), dtype=torch.float32, device=dev) if (N > 1 and rank == 0) else None
-    g64 = torch.empty((N, stride_rows, W, 3), dtype=torch.float64, device=dev) if (N > 1 and rank == 0) else None
-    f32 = torch.empty((H, W, 3), dtype=torch.float32, device=dev) if (N > 1 and rank == 0) else None
-    f64 = torch.empty((H, W, 3), dtype=torch.float64, device=dev) if (N > 1 and rank == 0) else None
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)  # > 126 MB L2
-    stream = torch.cuda.current_stream().cuda_stream
+    # Everything timed runs on ONE non-default stream: the render kernels (rtc_render_device gets the raw
+    # cudaStream_t), the L2 flush, NCCL's stream dependencies and the CUDA events.  (A NULL stream would
+    # mean "the context's own stream + host synchronisation" to rtc_render_device.)
+    side = torch.cuda.Stream(device=dev)
+    torch.cuda.set_stream(side)
+    stream = side.cuda_stream
+    assert stream != 0
+    token = torch.zeros(1, dtype=torch.int32, device=dev)
 
     def sync_all():
         if N > 1:
             dist.barrier()
         torch.cuda.synchronize()
 
-    def frame(opts, shard, gathered, full, fmt):
-        """One frame: render this rank's interleaved row tiles, NCCL-gather to rank 0, de-interleave."""
-        r.render_device(camd, opts, shard.data_ptr(), None, stream)
-        if N > 1:
-            dist.gather(shard, [gathered[i] for i in range(N)] if rank == 0 else None, dst=0)
-            if rank == 0:
-                r.assemble_device(camd, opts, gathered.data_ptr(), stride_rows, fmt, full.data_ptr(), stream)
+    class Path:
+        """One (precision, output format, exchange mode) way of producing the frame on rank 0."""
+
+        def __init__(self, precision, fmt, mode):
+            self.sf = ShardedFrame(W, H, fmt, rank, N, dev, tile_rows=TILE, mode=mode)
+            self.sf.connect(r)
+            self.opts = self.sf.shard_opts(rtc.Renderer.make_opts, precision=precision, rect=ffi.RECT_FULL, max_depth=DEPTH)
+            self.fmt = fmt
+
+        def dst(self):
+            d = self.sf.destination()
+            return d if isinstance(d, int) else d.data_ptr()
+
+        def kernel_only(self):
+            r.render_device(camd, self.opts, self.dst(), None, stream)
+
+        def frame(self):
+            """render this rank's interleaved row tiles, then the exchange step that completes rank 0's frame"""
+            r.render_device(camd, self.opts, self.dst(), None, stream)
+            if N == 1:
+                return
+            if self.sf.mode == "nccl":
+                self.sf.exchange(lambda g, f: r.assemble_device(camd, self.opts, g.data_ptr(), self.sf.stride_rows, self.fmt, f.data_ptr(), stream))
+            else:
+                self.sf.exchange()       # 4-byte stream-ordered all-reduce: the completion signal (pixels went over NVLink already)
 
     def timed(fn, steps, warmup):
         for _ in range(warmup):
@@ -202,6 +215,8 @@ def run_gpu(args):
         t0 = time.time()
         for a, b in ev:
             flush.zero_()            # L2 flush between timed iterations, outside the event pair
+            if N > 1:
+                dist.all_reduce(token)   # line the ranks up before the step starts (outside the event pair)
             a.record()
             fn()
             b.record()
@@ -213,55 +228,82 @@ def run_gpu(args):
         return ms.cpu().numpy(), t0, t1
 
     # deterministic work counts of the frame, from the f64 parity kernel's counters (== the oracle's)
+    o64c = rtc.Renderer.make_opts(precision=ffi.PRECISION_F64_PARITY, rect=ffi.RECT_FULL, max_depth=DEPTH, out_format=ffi.OUT_F64_RGB,
+                                  shard_index=rank, shard_count=N, tile_rows=TILE)
+    o32c = rtc.Renderer.make_opts(precision=ffi.PRECISION_F32_FAST, rect=ffi.RECT_FULL, max_depth=DEPTH, out_format=ffi.OUT_F32_RGB,
+                                  shard_index=rank, shard_count=N, tile_rows=TILE)
+    my_rows = r.shard_rows(camd, o32c)
+    scratch = torch.empty((r.shard_rows(camd, o64c), W, 3), dtype=torch.float64, device=dev)
     st = ffi.RtcStats()
-    r.render_device(camd, o64, d64.data_ptr(), None, None, st)
+    r.render_device(camd, o64c, scratch.data_ptr(), None, None, st)
     counts = torch.tensor([st.rays, st.shaded_hits, st.shadow_rays, st.primary_hits], dtype=torch.float64, device=dev)
     st32 = ffi.RtcStats()
-    r.render_device(camd, o32, d32.data_ptr(), None, None, st32)
+    r.render_device(camd, o32c, scratch.data_ptr(), None, None, st32)
     counts32 = torch.tensor([st32.rays], dtype=torch.float64, device=dev)
     if N > 1:
         dist.all_reduce(counts)
         dist.all_reduce(counts32)
     rays, shaded = float(counts[0]), float(counts[1])
     flops = rays * FLOP_PER_RAY + shaded * FLOP_PER_SHADED_HIT
+    del scratch
 
+    main = Path(ffi.PRECISION_F32_FAST, ffi.OUT_F32_RGB, "p2p")
     sampler = ClockSampler(local_rank)
     if rank == 0:
         sampler.start()
-    ms32, t0, t1 = timed(lambda: frame(o32, d32, g32, f32, ffi.OUT_F32_RGB), args.steps, max(3, args.warmup))
+    ms32, t0, t1 = timed(main.frame, args.steps, max(3, args.warmup))
     clocks = sampler.stop(t0, t1) if rank == 0 else None
     total_ms = float(ms32.sum())
     ms_per_step = total_ms / args.steps
     value = rays * args.steps / (total_ms * 1e-3) / 1e6
     # kernel alone (this rank's shard), for the roofline
-    k32, _, _ = timed(lambda: r.render_device(camd, o32, d32.data_ptr(), None, stream), args.steps, 3)
+    k32, _, _ = timed(main.kernel_only, args.steps, 3)
     kernel_ms = float(k32.mean())
+    extra = {}
+    frame_check = None
+    if N > 1:
+        # same frame through the NCCL gather + de-interleave, and a bit-exact check of both assembled
+        # frames against rank 0's own unsharded render
+        alt = Path(ffi.PRECISION_F32_FAST, ffi.OUT_F32_RGB, "nccl")
+        msn, _, _ = timed(alt.frame, args.steps, 3)
+        extra["gather_nccl"] = {"ms_per_frame": float(msn.mean()), "mrays_per_s": rays / (float(msn.mean()) * 1e-3) / 1e6,
+                                "path": "compact shard buffers, dist.gather (NCCL send/recv) to rank 0, rtc_assemble_device"}
+        main.frame(); alt.frame(); sync_all()
+        if rank == 0:
+            ref = torch.empty((H, W, 3), dtype=torch.float32, device=dev)
+            r.render_device(camd, rtc.Renderer.make_opts(precision=ffi.PRECISION_F32_FAST, rect=ffi.RECT_FULL, max_depth=DEPTH,
+                                                         out_format=ffi.OUT_F32_RGB), ref.data_ptr(), None, None, None)
+            torch.cuda.synchronize()
+            frame_check = {"p2p_equals_1gpu_frame": bool(torch.equal(main.sf.frame, ref)),
+                           "nccl_equals_1gpu_frame": bool(torch.equal(alt.sf.frame, ref))}
+        alt.sf.close()
+        del alt
     n64 = max(1, min(args.steps, 5))
-    ms64, _, _ = timed(lambda: frame(o64, d64, g64, f64, ffi.OUT_F64_RGB), n64, 3)
-    k64, _, _ = timed(lambda: r.render_device(camd, o64, d64.data_ptr(), None, stream), n64, 3)
+    p64 = Path(ffi.PRECISION_F64_PARITY, ffi.OUT_F64_RGB, "p2p")
+    ms64, _, _ = timed(p64.frame, n64, 3)
+    k64, _, _ = timed(p64.kernel_only, n64, 3)
 
     # ---- e2e: the public API with HOST buffers: scene H2D + render + Canvas (f64) D2H every step ----
     oe = rtc.Renderer.make_opts(precision=ffi.PRECISION_F32_FAST, rect=ffi.RECT_FULL, max_depth=DEPTH, out_format=ffi.OUT_F64_RGB)
     h2d = C.sizeof(ffi.RtcShape) * flat[2] + C.sizeof(ffi.RtcLight) + C.sizeof(ffi.RtcCamera)
     e2e_steps = max(1, min(args.steps, 10))
+    d2h = H * W * 3 * 8
     if N == 1:
         host = np.zeros((H, W, 3), dtype=np.float64)
 
         def e2e_step():
             r.upload_flat(*flat)
             r.render(camd, oe, want_mask=False, out=host)
-        d2h = host.nbytes
     else:
-        oeN = mk(ffi.PRECISION_F32_FAST, ffi.OUT_F64_RGB)
+        pe = Path(ffi.PRECISION_F32_FAST, ffi.OUT_F64_RGB, "p2p")   # Canvas layout straight into rank 0's frame
         host_t = torch.empty((H, W, 3), dtype=torch.float64).pin_memory() if rank == 0 else None
 
         def e2e_step():
             r.upload_flat(*flat)
-            frame(oeN, d64, g64, f64, ffi.OUT_F64_RGB)
+            pe.frame()
             if rank == 0:
-                host_t.copy_(f64, non_blocking=True)
+                host_t.copy_(pe.sf.frame, non_blocking=True)
             torch.cuda.synchronize()
-        d2h = H * W * 3 * 8
     for _ in range(2):
         e2e_step()
     sync_all()
@@ -280,7 +322,7 @@ def run_gpu(args):
     if rank == 0:
         peaks = measured_peaks()
         p32 = r.measure_peak_tflops(ffi.PRECISION_F32_FAST)
-        p64 = r.measure_peak_tflops(ffi.PRECISION_F64_PARITY)
+        pk64 = r.measure_peak_tflops(ffi.PRECISION_F64_PARITY)
         my_share = my_rows / H
         achieved = flops * my_share / (kernel_ms * 1e-3) / 1e12
         line = {
@@ -289,30 +331,39 @@ def run_gpu(args):
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": {"workload": WORKLOAD, "rays_per_frame": int(rays), "rays_per_frame_f32_kernel": int(counts32[0]),
                        "shaded_hits_per_frame": int(shaded), "l2": "256 MB buffer rewritten between timed iterations (outside the events)",
-                       "parallelism": f"interleaved {TILE}-row tiles over {N} GPU(s)" + (", NCCL gather to rank 0 + de-interleave" if N > 1 else ""),
+                       "parallelism": f"interleaved {TILE}-row tiles over {N} GPU(s)" +
+                                      (", render kernels store pixels straight into rank 0's frame over NVLink (CUDA IPC peer mapping); "
+                                       "one 4-byte all-reduce as completion signal" if N > 1 else ""),
                        "timing": "CUDA events per step on the launch stream, max over ranks"},
             "roofline": {"bound": "fp32_non_tensor", "achieved": achieved, "peak": p32, "unit": "TFLOP/s", "frac": achieved / p32,
                          "traffic": None, "peak_source": "FFMA micro-benchmark on this GPU in this run (rtc_measure_peak_tflops)",
                          "peak_formula": FP32_FORMULA_PEAK, "frac_of_formula": achieved / FP32_FORMULA_PEAK,
-                         "algorithmic_gflop_per_frame": flops / 1e9, "kernel_ms": kernel_ms, "kernel": "render_f32_kernel",
-                         "hbm_gbs_measured_peak": peaks.get("hbm_gbs")},
+                         "algorithmic_gflop_per_frame": flops / 1e9, "kernel_ms": kernel_ms, "kernel": "render_f32_small_kernel",
+                         "hbm_gbs_measured_peak": peaks.get("hbm_gbs"),
+                         "hbm_gbs_achieved_frame_write": W * H * 12 * my_share / (kernel_ms * 1e-3) / 1e9},
             "f64": {"ms_per_frame": float(ms64.mean()), "mrays_per_s": rays / (float(ms64.mean()) * 1e-3) / 1e6,
                     "kernel_ms": float(k64.mean()), "tflops_algorithmic": flops * my_share / (float(k64.mean()) * 1e-3) / 1e12,
-                    "peak_dfma_tflops_measured": p64},
+                    "peak_dfma_tflops_measured": pk64},
             "e2e": {"value": rays / (e2e_ms * 1e-3) / 1e6, "unit": "Mrays/s", "ms_per_frame": e2e_ms, "h2d_bytes_per_step": int(h2d),
                     "d2h_bytes_per_step": int(d2h), "steps": e2e_steps,
                     "path": "rtc_scene_upload + rtc_render (f32 fast, F64_RGB Canvas layout) into a host buffer" if N == 1 else
-                            "rtc_scene_upload + rtc_render_device shards + NCCL gather + de-interleave + D2H on rank 0"},
-            "gpu_launches": args.steps * (1 if N == 1 else 2),
+                            "rtc_scene_upload + rtc_render_device shards with peer stores into rank 0's F64 Canvas frame + D2H on rank 0"},
+            "gpu_launches": args.steps,
             "clocks": clocks,
         }
+        line.update(extra)
+        if frame_check is not None:
+            line["frame_check"] = frame_check
         if N == 1 and not args.no_cpu_baseline:
             model, cores = cpu_info()
             s = oracle_sample(cores, 12.0)
             line["cpu_baseline"] = {"value": s["mrays_per_s"], "unit": "Mrays/s", "cores": cores, "kind": "port", "cpu": model,
                                     "sample": s["sample"], "ms_per_frame_extrapolated": s["ms_per_frame_extrapolated"]}
         print(json.dumps(line), flush=True)
+    main.sf.close()
+    p64.sf.close()
     if N > 1:
+        pe.sf.close()
         dist.barrier()
         dist.destroy_process_group()
     return 0

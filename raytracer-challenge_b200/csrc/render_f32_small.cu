@@ -50,38 +50,59 @@ __device__ __forceinline__ bool is_even(float v) { float h = v * 0.5f; return h 
 constexpr int kIdxBits = 6;
 constexpr unsigned kMask = (1u << kIdxBits) - 1u;
 
+// key = (bits(t) & ~kMask) | pos as ONE LOP3: the mask comes in a register so that the position can be
+// the instruction's immediate (with both as immediates ptxas needs two LOP3s; ALU-pipe instructions
+// dispatch at half rate on sm_100a, so each one costs as much as two FFMAs: tools/micro/issue_mix.cu).
+template <unsigned kPos>
+__device__ __forceinline__ unsigned key_of(float t, unsigned mask_reg) {
+    unsigned r;
+    asm("lop3.b32 %0, %1, %2, %3, 0xEA;" : "=r"(r) : "r"(__float_as_uint(t)), "r"(mask_reg), "n"(kPos));
+    return r;
+}
+
 // One sphere against a unit-length radiance ray (Sphere::intersect_local, src/shape.rs:361-375, with
 // a = d.d = 1 and b halved).  Only one root can be the hit: t1 when the origin is outside (c > 0),
 // t2 when it is inside (c < 0; then t1 < 0 < t2)  ->  t = -b - copysign(s, c).
-__device__ __forceinline__ unsigned offer_sphere(unsigned best, const float4 sp, F3 o, F3 d, unsigned pos) {
+template <unsigned kPos>
+__device__ __forceinline__ unsigned sphere_key(const float4 sp, F3 o, F3 d, unsigned mask_reg) {
     F3 L = mk(o.x - sp.x, o.y - sp.y, o.z - sp.z);
     float b = dot(d, L);
     float c = fmaf(L.z, L.z, fmaf(L.y, L.y, fmaf(L.x, L.x, -sp.w)));
     float s = sqrt_nan(fmaf(b, b, -c));                   // NaN when the ray misses: loses the min
-    float ss = __uint_as_float(__float_as_uint(s) | (__float_as_uint(c) & 0x80000000u));
-    return min(best, (__float_as_uint(-b - ss) & ~kMask) + pos);
+    unsigned ss;                                          // (c & 0x80000000) | s
+    asm("lop3.b32 %0, %1, %2, %3, 0xEA;" : "=r"(ss) : "r"(__float_as_uint(c)), "n"(0x80000000), "r"(__float_as_uint(s)));
+    return key_of<kPos>(-b - __uint_as_float(ss), mask_reg);
+}
+template <unsigned kPos>
+__device__ __forceinline__ unsigned plane_key(const float4 pl, F3 o, F3 d, unsigned mask_reg) {
+    return key_of<kPos>(-row4(pl, o) * rcp(row3(pl, d)), mask_reg);   // Plane::intersect_local, src/shape.rs:462-471; parallel: +-inf / NaN
 }
 
+template <int G> struct PlaneGroups {
+    static __device__ __forceinline__ unsigned run(const SmallParams& P, F3 o, F3 d, unsigned m, unsigned best) {
+        constexpr int g = kSmallMaxPlanes / 2 - G;
+        if (g >= P.npg) return best;
+        best = min(best, min(plane_key<2 * g>(P.planes[2 * g], o, d, m), plane_key<2 * g + 1>(P.planes[2 * g + 1], o, d, m)));
+        return PlaneGroups<G - 1>::run(P, o, d, m, best);
+    }
+};
+template <> struct PlaneGroups<0> { static __device__ __forceinline__ unsigned run(const SmallParams&, F3, F3, unsigned, unsigned best) { return best; } };
+template <int G> struct SphereGroups {
+    static __device__ __forceinline__ unsigned run(const SmallParams& P, F3 o, F3 d, unsigned m, unsigned best) {
+        constexpr int g = kSmallMaxUsph / 2 - G;
+        if (g >= P.nug) return best;
+        best = min(best, min(sphere_key<kSmallMaxPlanes + 2 * g>(P.usph[2 * g], o, d, m), sphere_key<kSmallMaxPlanes + 2 * g + 1>(P.usph[2 * g + 1], o, d, m)));
+        return SphereGroups<G - 1>::run(P, o, d, m, best);
+    }
+};
+template <> struct SphereGroups<0> { static __device__ __forceinline__ unsigned run(const SmallParams&, F3, F3, unsigned, unsigned best) { return best; } };
+
 // World::intersect + Intersections::get_hit for a unit-length ray: nearest root in [0, +inf).
-// Returns the packed key; >= kInfBits means "no hit".
-__device__ __forceinline__ unsigned intersect_small(const SmallParams& P, F3 o, F3 d) {
-    unsigned best = kInfBits;
-#pragma unroll
-    for (int g = 0; g < kSmallMaxPlanes / 4; ++g) {
-        if (g >= P.npg) break;
-#pragma unroll
-        for (int j = 0; j < 4; ++j) {                     // Plane::intersect_local, src/shape.rs:462-471
-            float t = -row4(P.planes[4 * g + j], o) * rcp(row3(P.planes_d[4 * g + j], d));  // parallel: +-inf / NaN
-            best = min(best, (__float_as_uint(t) & ~kMask) + (unsigned)(4 * g + j));
-        }
-    }
-#pragma unroll
-    for (int g = 0; g < kSmallMaxUsph / 4; ++g) {
-        if (g >= P.nug) break;
-#pragma unroll
-        for (int j = 0; j < 4; ++j) best = offer_sphere(best, P.usph[4 * g + j], o, d, (unsigned)(kSmallMaxPlanes + 4 * g + j));
-    }
-    return best;
+// Stream positions are compile-time constants (plane i -> i, sphere i -> 16 + i); shapes are tested in
+// groups of two with a warp-uniform exit per group.  Returns the packed key; >= kInfBits = no hit.
+__device__ __forceinline__ unsigned intersect_small(const SmallParams& P, F3 o, F3 d, unsigned mask_reg) {
+    unsigned best = PlaneGroups<kSmallMaxPlanes / 2>::run(P, o, d, mask_reg, kInfBits);
+    return SphereGroups<kSmallMaxUsph / 2>::run(P, o, d, mask_reg, best);
 }
 
 // World::is_shadowed_by_light (src/shape.rs:716-727) as an any-hit test over the segment
@@ -91,26 +112,27 @@ __device__ __forceinline__ unsigned intersect_small(const SmallParams& P, F3 o, 
 __device__ __forceinline__ bool shadow_small(const SmallParams& P, F3 o, F3 d) {
     float g = 1.0f;
 #pragma unroll
-    for (int k = 0; k < kSmallMaxPlanes / 4; ++k) {
+    for (int k = 0; k < kSmallMaxPlanes / 2; ++k) {
         if (k >= P.npg) break;
-#pragma unroll
-        for (int j = 0; j < 4; ++j) g = fminf(g, row4(P.splanes[4 * k + j], o));
+        g = fminf(g, fminf(row4(P.splanes[2 * k], o), row4(P.splanes[2 * k + 1], o)));
     }
     const float a = dot(d, d);
     const float nhia = -0.5f * rcp(a);
     const F3 d2 = mk(d.x + d.x, d.y + d.y, d.z + d.z);
 #pragma unroll
-    for (int k = 0; k < kSmallMaxUsph / 4; ++k) {
+    for (int k = 0; k < kSmallMaxUsph / 2; ++k) {
         if (k >= P.nug) break;
+        float fm[2];
 #pragma unroll
-        for (int j = 0; j < 4; ++j) {
-            const float4 sp = P.usph_s[4 * k + j];
+        for (int j = 0; j < 2; ++j) {
+            const float4 sp = P.usph_s[2 * k + j];
             F3 L = mk(o.x - sp.x, o.y - sp.y, o.z - sp.z);
             float f0 = fmaf(L.z, L.z, fmaf(L.y, L.y, fmaf(L.x, L.x, -sp.w)));
             float b2 = dot(d2, L);                        // f(t) = a t^2 + b2 t + f0
             float tc = __saturatef(b2 * nhia);
-            g = fminf(g, fmaf(tc, fmaf(a, tc, b2), f0));
+            fm[j] = fmaf(tc, fmaf(a, tc, b2), f0);
         }
+        g = fminf(g, fminf(fm[0], fm[1]));
     }
     return g <= 0.f;
 }
@@ -184,6 +206,8 @@ render_f32_small_kernel(const __grid_constant__ SmallParams P, void* __restrict_
     }
     const F3 light_pos = mk(P.light_pos[0], P.light_pos[1], P.light_pos[2]);
     const F3 light_int = mk(P.light_int[0], P.light_int[1], P.light_int[2]);
+    unsigned mask_reg;   // ~kMask in a register (see key_of)
+    asm volatile("mov.u32 %0, %1;" : "=r"(mask_reg) : "n"(~kMask));
     const unsigned full = 0xffffffffu;
     const int lane = threadIdx.x & 31;
     const unsigned lt_mask = (1u << lane) - 1u;
@@ -281,7 +305,7 @@ render_f32_small_kernel(const __grid_constant__ SmallParams P, void* __restrict_
         if (__all_sync(full, !has_ray && !have && exhausted)) break;
 
         // ------------------------------------------------------------ phase A: World::intersect (all lanes, idle ones trace a dummy)
-        const unsigned key = intersect_small(P, ro, rd);
+        const unsigned key = intersect_small(P, ro, rd, mask_reg);
         const bool hit = has_ray && key < kInfBits;
         n_rad += has_ray ? 1u : 0u;
         n_hits += hit ? 1u : 0u;

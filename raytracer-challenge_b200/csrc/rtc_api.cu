@@ -305,7 +305,7 @@ int flatten(const rtc_light* light, const rtc_shape* shapes, size_t n, HostScene
         for (int k = 0; k < kSmallMaxPlanes; ++k) sp.planes[k] = sp.planes_d[k] = sp.splanes[k] = make_float4(0.f, 0.f, 0.f, 1.f);
         for (int k = 0; k < kSmallMaxUsph; ++k) sp.usph[k] = sp.usph_s[k] = make_float4(0.f, 0.f, 0.f, -1.f);
         hs.srec.assign(kSmallMaxShapes, SmallRec32{});
-        sp.np = np; sp.nu = nu; sp.npg = (np + 3) / 4; sp.nug = (nu + 3) / 4;
+        sp.np = np; sp.nu = nu; sp.npg = (np + 1) / 2; sp.nug = (nu + 1) / 2;
         int n_glass = 0;
         auto fill_common = [&](SmallRec32& r, const rtc_shape& s, const ShadeRec32& q) {
             r.col_amb = q.col_amb; r.dif_spec = q.dif_spec;

@@ -104,7 +104,7 @@ struct SmallParams {
     float4 usph[kSmallMaxUsph];        // (cx, cy, cz, r^2); padding (0,0,0,-1): never hit
     float4 usph_s[kSmallMaxUsph];      // same again (the shadow loop's copy)
     float4 glass[kSmallMaxGlass];      // the spheres with refractive_index != 1
-    int npg, nug;                      // plane / sphere groups of four
+    int npg, nug;                      // plane / sphere groups of two
     int np, nu;
     int n_glass;                       // -1: fast n1/n2 test unavailable (a glass plane, or more than 8 glass spheres)
     int pad0;

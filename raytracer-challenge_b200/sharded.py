@@ -1,0 +1,146 @@
+"""Multi-GPU frame assembly for ``Camera::render``: one process per GPU
+(``torch.distributed``), the frame cut into interleaved row tiles (tile k -> rank k % world), the
+scene replicated on every GPU, and ONE exchange step that puts the finished frame on rank 0.
+
+Two exchange modes:
+
+* ``"nccl"``  — every rank renders into a compact shard buffer, ``dist.gather`` (grouped NCCL
+  send/recv over NVLink) collects the buffers on rank 0, ``rtc_assemble_device`` de-interleaves.
+* ``"p2p"``   — rank 0 exports its frame buffer through CUDA IPC (``rtc_ipc_export``), the other
+  ranks map it (``rtc_ipc_open``) and their render kernels store finished pixels straight into it
+  over NVLink (``RTC_OPT_DST_FULL_FRAME``): the transfer overlaps the rendering pixel by pixel and
+  the only collective left is the barrier that tells rank 0 the frame is complete.
+
+The reference has no multi-device path (rayon threads over one ``Canvas``, src/camera.rs:144-160);
+the tile-to-rank arithmetic here is the only "protocol", and it is pure index math so the same class
+runs on CPU tensors with the ``gloo`` backend in the tests (the renderer is then a stand-in callable).
+"""
+import torch
+import torch.distributed as dist
+
+from . import ffi
+
+
+def shard_rows(vsize, tile_rows, index, count):
+    """Rows of a ``vsize``-row frame owned by shard ``index`` of ``count`` (same as rtc_shard_rows)."""
+    if count <= 1:
+        return vsize
+    n_tiles = (vsize + tile_rows - 1) // tile_rows
+    return sum(min(vsize, (t + 1) * tile_rows) - t * tile_rows for t in range(index, n_tiles, count))
+
+
+def frame_rows_of_shard(vsize, tile_rows, index, count):
+    """Frame row of every compact row of shard ``index``, in compact order (a LongTensor)."""
+    rows = []
+    n_tiles = (vsize + tile_rows - 1) // tile_rows
+    for t in range(index, n_tiles, count):
+        rows.extend(range(t * tile_rows, min(vsize, (t + 1) * tile_rows)))
+    return torch.tensor(rows, dtype=torch.long)
+
+
+def deinterleave(gathered, vsize, tile_rows):
+    """Host/torch form of rtc_assemble_device: ``gathered`` is [count, stride_rows, ...] compact
+    shard buffers; returns the [vsize, ...] frame.  Used for CPU tensors (tests) only."""
+    count = gathered.shape[0]
+    frame = torch.empty((vsize,) + tuple(gathered.shape[2:]), dtype=gathered.dtype, device=gathered.device)
+    for k in range(count):
+        rows = frame_rows_of_shard(vsize, tile_rows, k, count).to(gathered.device)
+        frame[rows] = gathered[k, : rows.numel()]
+    return frame
+
+
+_TORCH_DTYPE = {ffi.OUT_F64_RGB: torch.float64, ffi.OUT_F32_RGB: torch.float32, ffi.OUT_U8_RGB: torch.uint8}
+
+
+class ShardedFrame:
+    """Buffers and exchange step of one camera's frame across the ranks of the default process
+    group.  Per frame a rank (1) renders its tiles into ``destination()`` with the options from
+    ``shard_opts()`` — ``Renderer.render_device`` on GPUs, any stand-in on CPU tensors in the
+    tests — and (2) calls ``exchange()``."""
+
+    def __init__(self, hsize, vsize, out_format, rank, world, device, tile_rows=16, mode="p2p", channels=3):
+        self.hsize, self.vsize, self.out_format = hsize, vsize, out_format
+        self.rank, self.world, self.device, self.tile_rows, self.mode = rank, world, device, tile_rows, mode
+        self.dtype = _TORCH_DTYPE[out_format]
+        self.stride_rows = shard_rows(vsize, tile_rows, 0, world)     # shard 0 owns the most rows
+        self.my_rows = shard_rows(vsize, tile_rows, rank, world)
+        self.channels = channels
+        shape_tail = (hsize, channels)
+        self.frame = None
+        self.shard = None
+        self.gathered = None
+        self.remote_ptr = None
+        self._ipc = None
+        self._token = None
+        if world == 1:
+            self.frame = torch.zeros((vsize,) + shape_tail, dtype=self.dtype, device=device)
+        elif mode == "nccl":
+            self.shard = torch.zeros((self.stride_rows,) + shape_tail, dtype=self.dtype, device=device)
+            if rank == 0:
+                self.gathered = torch.empty((world, self.stride_rows) + shape_tail, dtype=self.dtype, device=device)
+                self.frame = torch.empty((vsize,) + shape_tail, dtype=self.dtype, device=device)
+        elif mode == "p2p":
+            if rank == 0:
+                self.frame = torch.zeros((vsize,) + shape_tail, dtype=self.dtype, device=device)
+        else:
+            raise ValueError(f"unknown exchange mode {mode!r}")
+
+    # ---- p2p set-up: rank 0 exports the frame, the others map it ---------------------------------
+    def connect(self, renderer):
+        if self.world == 1 or self.mode != "p2p":
+            return
+        payload = [None]
+        if self.rank == 0:
+            handle, offset = renderer.ipc_export(self.frame.data_ptr())
+            payload = [(handle, offset)]
+        dist.broadcast_object_list(payload, src=0)
+        if self.rank != 0:
+            handle, offset = payload[0]
+            self.remote_ptr = renderer.ipc_open(handle, offset)
+            self._ipc = (renderer, self.remote_ptr, offset)
+        dist.barrier()
+
+    def close(self):
+        if self._ipc is not None:
+            renderer, ptr, offset = self._ipc
+            torch.cuda.synchronize()
+            renderer.ipc_close(ptr, offset)
+            self._ipc = None
+
+    # ---- one frame ---------------------------------------------------------------------------------
+    def shard_opts(self, make_opts, **kw):
+        flags = kw.pop("flags", 0)
+        if self.world > 1 and self.mode == "p2p":
+            flags |= ffi.OPT_DST_FULL_FRAME
+        return make_opts(out_format=self.out_format, shard_index=self.rank, shard_count=self.world,
+                         tile_rows=self.tile_rows, flags=flags, **kw)
+
+    def destination(self):
+        """Device pointer (or CPU tensor) this rank's render call writes to."""
+        if self.world == 1:
+            return self.frame
+        if self.mode == "nccl":
+            return self.shard
+        return self.frame if self.rank == 0 else self.remote_ptr
+
+    def exchange(self, assemble=None):
+        """The exchange step after every rank's render call was enqueued.  Returns the frame on
+        rank 0 (None elsewhere).  ``assemble(gathered, frame)`` de-interleaves on the device
+        (rtc_assemble_device); without it the torch index form is used (CPU tensors)."""
+        if self.world == 1:
+            return self.frame
+        if self.mode == "nccl":
+            dist.gather(self.shard, [self.gathered[i] for i in range(self.world)] if self.rank == 0 else None, dst=0)
+            if self.rank != 0:
+                return None
+            if assemble is not None:
+                assemble(self.gathered, self.frame)
+            else:
+                self.frame = deinterleave(self.gathered, self.vsize, self.tile_rows)
+            return self.frame
+        # p2p: all peer stores are complete once every rank's kernel has finished; a 4-byte
+        # stream-ordered all-reduce is the completion signal (no host synchronisation)
+        if self._token is None:
+            self._token = torch.zeros(1, dtype=torch.int32, device=self.device)
+        dist.all_reduce(self._token)
+        return self.frame if self.rank == 0 else None
