@@ -9,6 +9,9 @@
 #include <cstdlib>
 #include <cstring>
 #include <string>
+#include <condition_variable>
+#include <functional>
+#include <mutex>
 #include <thread>
 #include <vector>
 #include "rtc_common.h"
@@ -53,7 +56,9 @@ struct DevBuf {
 struct DeviceState {
     int dev = 0;
     cudaStream_t stream = nullptr;
+    cudaStream_t copy_stream = nullptr;   // D2H of finished bands while later bands render
     cudaEvent_t ev_k0 = nullptr, ev_k1 = nullptr, ev_c1 = nullptr;
+    cudaEvent_t ev_band[8] = {}, ev_copy[8] = {};
     // scene
     DevBuf<double2> sph64, pl64;
     DevBuf<float4> pl32, us32, gs32;
@@ -98,8 +103,66 @@ size_t elem_size(int out_format) {
 
 }  // namespace
 
+// Host worker pool of a context: splits the pinned-staging -> caller-buffer step (memcpy, or the
+// lossless f32 -> f64 widening of fast-mode frames) over the host cores while later bands are still
+// in flight over PCIe.
+class HostPool {
+public:
+    explicit HostPool(int n) {
+        for (int i = 0; i < n; ++i) workers_.emplace_back([this] { loop(); });
+    }
+    ~HostPool() {
+        { std::lock_guard<std::mutex> l(m_); stop_ = true; }
+        cv_.notify_all();
+        for (auto& t : workers_) t.join();
+    }
+    int size() const { return (int)workers_.size(); }
+    // run fn(i) for i in [0, n) on the pool and the calling thread; returns when all are done
+    void parallel_for(int n, const std::function<void(int)>& fn) {
+        if (n <= 0) return;
+        {
+            std::lock_guard<std::mutex> l(m_);
+            fn_ = &fn; next_ = 0; total_ = n; pending_ = n;
+        }
+        cv_.notify_all();
+        for (;;) {
+            int i;
+            { std::lock_guard<std::mutex> l(m_); if (next_ >= total_) break; i = next_++; }
+            fn(i);
+            std::lock_guard<std::mutex> l(m_);
+            --pending_;
+        }
+        std::unique_lock<std::mutex> l(m_);
+        done_.wait(l, [this] { return pending_ == 0; });
+        fn_ = nullptr;
+    }
+private:
+    void loop() {
+        for (;;) {
+            int i;
+            const std::function<void(int)>* fn;
+            {
+                std::unique_lock<std::mutex> l(m_);
+                cv_.wait(l, [this] { return stop_ || (fn_ && next_ < total_); });
+                if (stop_) return;
+                i = next_++; fn = fn_;
+            }
+            (*fn)(i);
+            std::lock_guard<std::mutex> l(m_);
+            if (--pending_ == 0) done_.notify_all();
+        }
+    }
+    std::vector<std::thread> workers_;
+    std::mutex m_;
+    std::condition_variable cv_, done_;
+    const std::function<void(int)>* fn_ = nullptr;
+    int next_ = 0, total_ = 0, pending_ = 0;
+    bool stop_ = false;
+};
+
 struct rtc_context {
     std::vector<DeviceState> devs;
+    HostPool* pool = nullptr;
     bool has_scene = false;
     // pinned staging for D2H (full frame), grown on demand
     unsigned char* pinned_rgb = nullptr;
@@ -418,21 +481,28 @@ int run_peak(DeviceState& d, double* out_tflops) {
     return RTC_OK;
 }
 
-void parallel_copy(unsigned char* dst, const unsigned char* src, size_t n) {
-    const size_t kMin = 8u << 20;
-    unsigned hw = std::thread::hardware_concurrency();
-    int nt = (int)std::min<size_t>(std::max(1u, std::min(hw, 16u)), n / kMin + 1);
-    if (nt <= 1) { std::memcpy(dst, src, n); return; }
-    std::vector<std::thread> pool;
-    size_t chunk = (n + nt - 1) / nt;
-    chunk = (chunk + 4095) & ~(size_t)4095;
-    for (int t = 0; t < nt; ++t) {
-        size_t b = (size_t)t * chunk;
-        if (b >= n) break;
-        size_t e = std::min(n, b + chunk);
-        pool.emplace_back([=] { std::memcpy(dst + b, src + b, e - b); });
+// Staging -> caller buffer for `n_elems` elements: plain copy, or f32 -> f64 widening (exact) when the
+// device produced f32 for an F64_RGB request (fast mode: halves the PCIe bytes).
+void host_deliver(rtc_context* ctx, unsigned char* dst, const unsigned char* src, size_t n_elems, size_t src_elem, size_t dst_elem) {
+    if (!ctx->pool) {
+        unsigned hw = std::thread::hardware_concurrency();
+        ctx->pool = new HostPool((int)std::max(1u, std::min(hw, 32u)) - 1);
     }
-    for (auto& th : pool) th.join();
+    const size_t kChunk = 256u << 10;   // elements per task
+    const int n_tasks = (int)((n_elems + kChunk - 1) / kChunk);
+    const bool widen = src_elem == 4 && dst_elem == 8;
+    auto task = [=](int i) {
+        const size_t b = (size_t)i * kChunk, e = std::min(n_elems, b + kChunk);
+        if (widen) {
+            const float* sp = reinterpret_cast<const float*>(src) + b;
+            double* dp = reinterpret_cast<double*>(dst) + b;
+            for (size_t k = 0; k < e - b; ++k) dp[k] = (double)sp[k];
+        } else {
+            std::memcpy(dst + b * dst_elem, src + b * src_elem, (e - b) * dst_elem);
+        }
+    };
+    if (n_tasks <= 1) { if (n_tasks == 1) task(0); return; }
+    ctx->pool->parallel_for(n_tasks, task);
 }
 
 // Camera part of the small-scene kernel parameter: Camera::ray_for_pixel_offset (src/camera.rs:64-76) reduced to
@@ -502,6 +572,11 @@ int rtc_context_create(const int* device_ids, int n_gpus, rtc_context** out_ctx)
         if (e == cudaSuccess) e = cudaEventCreate(&d.ev_k0);
         if (e == cudaSuccess) e = cudaEventCreate(&d.ev_k1);
         if (e == cudaSuccess) e = cudaEventCreate(&d.ev_c1);
+        if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&d.copy_stream, cudaStreamNonBlocking);
+        for (int b = 0; b < 8 && e == cudaSuccess; ++b) {
+            e = cudaEventCreateWithFlags(&d.ev_band[b], cudaEventDisableTiming);
+            if (e == cudaSuccess) e = cudaEventCreateWithFlags(&d.ev_copy[b], cudaEventDisableTiming);
+        }
         if (e == cudaSuccess) e = d.counters.ensure(1);
         if (e == cudaSuccess) e = d.work.ensure(1);
         if (e != cudaSuccess) {
@@ -530,11 +605,17 @@ void rtc_context_destroy(rtc_context* ctx) {
         if (d.ev_k0) cudaEventDestroy(d.ev_k0);
         if (d.ev_k1) cudaEventDestroy(d.ev_k1);
         if (d.ev_c1) cudaEventDestroy(d.ev_c1);
+        for (int b = 0; b < 8; ++b) {
+            if (d.ev_band[b]) cudaEventDestroy(d.ev_band[b]);
+            if (d.ev_copy[b]) cudaEventDestroy(d.ev_copy[b]);
+        }
+        if (d.copy_stream) { cudaStreamSynchronize(d.copy_stream); cudaStreamDestroy(d.copy_stream); }
         if (d.stream) cudaStreamDestroy(d.stream);
     }
     if (ctx->pinned_rgb) cudaFreeHost(ctx->pinned_rgb);
     if (ctx->pinned_hit) cudaFreeHost(ctx->pinned_hit);
     if (ctx->pinned_counters) cudaFreeHost(ctx->pinned_counters);
+    delete ctx->pool;
     delete ctx;
 }
 
@@ -709,9 +790,12 @@ extern "C" int rtc_render(rtc_context* ctx, const rtc_camera* cam, const rtc_ren
     if (!ctx->has_scene) return fail(RTC_ERR_NO_SCENE, "rtc_render before rtc_scene_upload");
     auto t0 = std::chrono::steady_clock::now();
     const int G = (int)ctx->devs.size();
-    const int tile_rows = opts->tile_rows > 0 ? opts->tile_rows : 16;
-    const size_t px_bytes = 3 * elem_size(opts->out_format);
-    const size_t row_bytes = (size_t)cam->hsize * px_bytes;
+    // Fast mode computes in f32: an F64_RGB (Canvas.pixels) request is produced as f32 on the device,
+    // crosses PCIe as f32 and is widened on the host (exact), halving the bytes of the dominant copy.
+    const int dev_fmt = (opts->precision == RTC_PRECISION_F32_FAST && opts->out_format == RTC_OUT_F64_RGB) ? RTC_OUT_F32_RGB : opts->out_format;
+    const size_t dev_elem = elem_size(dev_fmt), out_elem = elem_size(opts->out_format);
+    const size_t row_elems = (size_t)cam->hsize * 3;
+    const size_t row_bytes = row_elems * dev_elem;            // device / staging row
     const size_t frame_bytes = row_bytes * cam->vsize;
     const size_t mask_bytes = (size_t)cam->hsize * cam->vsize;
     rc = ensure_pinned(&ctx->pinned_rgb, &ctx->pinned_rgb_cap, frame_bytes);
@@ -720,12 +804,75 @@ extern "C" int rtc_render(rtc_context* ctx, const rtc_camera* cam, const rtc_ren
         rc = ensure_pinned(&ctx->pinned_hit, &ctx->pinned_hit_cap, mask_bytes);
         if (rc != RTC_OK) return rc;
     }
-    // Interleaved row tiles: tile k -> GPU k % G.  Every GPU renders its tiles into a compact
-    // buffer and copies each tile straight to its rows of the pinned frame over its own PCIe link.
+    rtc_render_opts dopts = *opts;
+    dopts.out_format = dev_fmt;
+    rtc_stats st;
+    std::memset(&st, 0, sizeof st);
+    unsigned char* user = (unsigned char*)out_rgb;
+
+    if (G == 1) {
+        // One GPU: the frame is rendered as up to 8 contiguous row bands (band b = shard b of B with
+        // tile_rows = ceil(vsize / B), written at frame positions).  Band b's D2H runs on the copy
+        // stream while band b+1 renders, and the host delivers band b while band b+1 crosses PCIe.
+        DeviceState& d = ctx->devs[0];
+        CUDA_TRY(cudaSetDevice(d.dev));
+        const int B = frame_bytes >= (32u << 20) ? 8 : (frame_bytes >= (4u << 20) ? 4 : 1);
+        const int band_rows = ((int)cam->vsize + B - 1) / B;
+        CUDA_TRY(d.rgb.ensure(frame_bytes));
+        if (out_hit_mask) CUDA_TRY(d.hit.ensure(mask_bytes));
+        CUDA_TRY(cudaMemsetAsync(d.counters.p, 0, sizeof(Counters), d.stream));
+        CUDA_TRY(cudaEventRecord(d.ev_k0, d.stream));
+        int n_bands = 0;
+        for (int b = 0; b < B; ++b) {
+            const int r0 = b * band_rows, r1 = std::min((int)cam->vsize, r0 + band_rows);
+            if (r0 >= r1) break;
+            ++n_bands;
+            CamParams cp = make_cam(cam, &dopts, b, B, band_rows);
+            cp.dst_full = 1;
+            rc = launch_on(d, cp, opts->precision, opts->flags, d.rgb.p, out_hit_mask ? d.hit.p : nullptr, d.counters.p, d.stream);
+            if (rc != RTC_OK) return rc;
+            CUDA_TRY(cudaEventRecord(d.ev_band[b], d.stream));
+            CUDA_TRY(cudaStreamWaitEvent(d.copy_stream, d.ev_band[b], 0));
+            CUDA_TRY(cudaMemcpyAsync(ctx->pinned_rgb + (size_t)r0 * row_bytes, d.rgb.p + (size_t)r0 * row_bytes, (size_t)(r1 - r0) * row_bytes,
+                                     cudaMemcpyDeviceToHost, d.copy_stream));
+            if (out_hit_mask)
+                CUDA_TRY(cudaMemcpyAsync(ctx->pinned_hit + (size_t)r0 * cam->hsize, d.hit.p + (size_t)r0 * cam->hsize, (size_t)(r1 - r0) * cam->hsize,
+                                         cudaMemcpyDeviceToHost, d.copy_stream));
+            CUDA_TRY(cudaEventRecord(d.ev_copy[b], d.copy_stream));
+        }
+        CUDA_TRY(cudaEventRecord(d.ev_k1, d.stream));
+        CUDA_TRY(cudaMemcpyAsync(&ctx->pinned_counters[0], d.counters.p, sizeof(Counters), cudaMemcpyDeviceToHost, d.stream));
+        double deliver_ms = 0.0;
+        for (int b = 0; b < n_bands; ++b) {
+            const int r0 = b * band_rows, r1 = std::min((int)cam->vsize, r0 + band_rows);
+            CUDA_TRY(cudaEventSynchronize(d.ev_copy[b]));
+            auto h0 = std::chrono::steady_clock::now();
+            host_deliver(ctx, user + (size_t)r0 * row_elems * out_elem, ctx->pinned_rgb + (size_t)r0 * row_bytes, (size_t)(r1 - r0) * row_elems, dev_elem, out_elem);
+            if (out_hit_mask) std::memcpy(out_hit_mask + (size_t)r0 * cam->hsize, ctx->pinned_hit + (size_t)r0 * cam->hsize, (size_t)(r1 - r0) * cam->hsize);
+            deliver_ms += std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - h0).count();
+        }
+        CUDA_TRY(cudaStreamSynchronize(d.stream));
+        float k_ms = 0.f;
+        CUDA_TRY(cudaEventElapsedTime(&k_ms, d.ev_k0, d.ev_k1));
+        const Counters& c = ctx->pinned_counters[0];
+        st.rays = c.rays; st.primary_hits = c.primary_hits; st.shaded_hits = c.shaded_hits; st.shadow_rays = c.shadow_rays;
+        st.kernel_launches = n_bands;
+        st.kernel_ms = k_ms;   // all bands (later bands share the GPU with the D2H of earlier ones)
+        st.total_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+        st.d2h_ms = st.total_ms - k_ms;   // whatever was not hidden behind the kernel: PCIe + host delivery
+        st.gather_ms = deliver_ms;
+        if (stats) *stats = st;
+        return RTC_OK;
+    }
+
+    // Several GPUs in one process: interleaved row tiles, tile k -> GPU k % G.  Every GPU renders its
+    // tiles into a compact buffer and copies each tile straight to its rows of the pinned frame over
+    // its own PCIe link.
+    const int tile_rows = opts->tile_rows > 0 ? opts->tile_rows : 16;
     for (int g = 0; g < G; ++g) {
         DeviceState& d = ctx->devs[g];
         CUDA_TRY(cudaSetDevice(d.dev));
-        CamParams cp = make_cam(cam, opts, g, G, tile_rows);
+        CamParams cp = make_cam(cam, &dopts, g, G, tile_rows);
         CUDA_TRY(d.rgb.ensure((size_t)cp.shard_rows * row_bytes));
         if (out_hit_mask) CUDA_TRY(d.hit.ensure((size_t)cp.shard_rows * cam->hsize));
         CUDA_TRY(cudaMemsetAsync(d.counters.p, 0, sizeof(Counters), d.stream));
@@ -733,27 +880,20 @@ extern "C" int rtc_render(rtc_context* ctx, const rtc_camera* cam, const rtc_ren
         rc = launch_on(d, cp, opts->precision, opts->flags, d.rgb.p, out_hit_mask ? d.hit.p : nullptr, d.counters.p, d.stream);
         if (rc != RTC_OK) return rc;
         CUDA_TRY(cudaEventRecord(d.ev_k1, d.stream));
-        if (G == 1) {
-            CUDA_TRY(cudaMemcpyAsync(ctx->pinned_rgb, d.rgb.p, frame_bytes, cudaMemcpyDeviceToHost, d.stream));
-            if (out_hit_mask) CUDA_TRY(cudaMemcpyAsync(ctx->pinned_hit, d.hit.p, mask_bytes, cudaMemcpyDeviceToHost, d.stream));
-        } else {
-            int n_tiles = ((int)cam->vsize + tile_rows - 1) / tile_rows;
-            int compact_row = 0;
-            for (int t = g; t < n_tiles; t += G) {
-                int r0 = t * tile_rows, r1 = std::min((int)cam->vsize, r0 + tile_rows);
-                CUDA_TRY(cudaMemcpyAsync(ctx->pinned_rgb + (size_t)r0 * row_bytes, d.rgb.p + (size_t)compact_row * row_bytes,
-                                         (size_t)(r1 - r0) * row_bytes, cudaMemcpyDeviceToHost, d.stream));
-                if (out_hit_mask)
-                    CUDA_TRY(cudaMemcpyAsync(ctx->pinned_hit + (size_t)r0 * cam->hsize, d.hit.p + (size_t)compact_row * cam->hsize,
-                                             (size_t)(r1 - r0) * cam->hsize, cudaMemcpyDeviceToHost, d.stream));
-                compact_row += r1 - r0;
-            }
+        int n_tiles = ((int)cam->vsize + tile_rows - 1) / tile_rows;
+        int compact_row = 0;
+        for (int t = g; t < n_tiles; t += G) {
+            int r0 = t * tile_rows, r1 = std::min((int)cam->vsize, r0 + tile_rows);
+            CUDA_TRY(cudaMemcpyAsync(ctx->pinned_rgb + (size_t)r0 * row_bytes, d.rgb.p + (size_t)compact_row * row_bytes,
+                                     (size_t)(r1 - r0) * row_bytes, cudaMemcpyDeviceToHost, d.stream));
+            if (out_hit_mask)
+                CUDA_TRY(cudaMemcpyAsync(ctx->pinned_hit + (size_t)r0 * cam->hsize, d.hit.p + (size_t)compact_row * cam->hsize,
+                                         (size_t)(r1 - r0) * cam->hsize, cudaMemcpyDeviceToHost, d.stream));
+            compact_row += r1 - r0;
         }
         CUDA_TRY(cudaMemcpyAsync(&ctx->pinned_counters[g], d.counters.p, sizeof(Counters), cudaMemcpyDeviceToHost, d.stream));
         CUDA_TRY(cudaEventRecord(d.ev_c1, d.stream));
     }
-    rtc_stats st;
-    std::memset(&st, 0, sizeof st);
     for (int g = 0; g < G; ++g) {
         DeviceState& d = ctx->devs[g];
         CUDA_TRY(cudaSetDevice(d.dev));
@@ -768,10 +908,11 @@ extern "C" int rtc_render(rtc_context* ctx, const rtc_camera* cam, const rtc_ren
         st.kernel_launches += 1;
     }
     auto t1 = std::chrono::steady_clock::now();
-    parallel_copy((unsigned char*)out_rgb, ctx->pinned_rgb, frame_bytes);
-    if (out_hit_mask) parallel_copy(out_hit_mask, ctx->pinned_hit, mask_bytes);
+    host_deliver(ctx, user, ctx->pinned_rgb, row_elems * cam->vsize, dev_elem, out_elem);
+    if (out_hit_mask) std::memcpy(out_hit_mask, ctx->pinned_hit, mask_bytes);
     auto t2 = std::chrono::steady_clock::now();
-    st.d2h_ms += std::chrono::duration<double, std::milli>(t2 - t1).count();
+    st.gather_ms = std::chrono::duration<double, std::milli>(t2 - t1).count();
+    st.d2h_ms += st.gather_ms;
     st.total_ms = std::chrono::duration<double, std::milli>(t2 - t0).count();
     if (stats) *stats = st;
     return RTC_OK;
