@@ -165,7 +165,7 @@ def run_gpu(args):
     flat = world.flatten()
     camd = cam.flatten()
     r.upload_flat(*flat)
-    TILE = 16
+    TILE = args.tile_rows
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)  # > 126 MB L2
     # Everything timed runs on ONE non-default stream: the render kernels (rtc_render_device gets the raw
     # cudaStream_t), the L2 flush, NCCL's stream dependencies and the CUDA events.  (A NULL stream would
@@ -266,6 +266,20 @@ def run_gpu(args):
         # frames against rank 0's own unsharded render
         alt = Path(ffi.PRECISION_F32_FAST, ffi.OUT_F32_RGB, "nccl")
         msn, _, _ = timed(alt.frame, args.steps, 3)
+        # kernel alone with a LOCAL destination (compact shard buffer) vs the peer-mapped frame, per rank
+        def per_rank(fn):
+            for _ in range(3):
+                fn()
+            sync_all()
+            evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+            for a, b in evs:
+                flush.zero_(); dist.all_reduce(token); a.record(); fn(); b.record()
+            sync_all()
+            mine = torch.tensor([sum(a.elapsed_time(b) for a, b in evs) / len(evs)], dtype=torch.float64, device=dev)
+            allr = [torch.zeros_like(mine) for _ in range(N)]
+            dist.all_gather(allr, mine)
+            return [round(float(x), 4) for x in allr]
+        extra["kernel_ms_per_rank"] = {"peer_frame_destination": per_rank(main.kernel_only), "local_destination": per_rank(alt.kernel_only)}
         extra["gather_nccl"] = {"ms_per_frame": float(msn.mean()), "mrays_per_s": rays / (float(msn.mean()) * 1e-3) / 1e6,
                                 "path": "compact shard buffers, dist.gather (NCCL send/recv) to rank 0, rtc_assemble_device"}
         main.frame(); alt.frame(); sync_all()
@@ -377,6 +391,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--tile-rows", type=int, default=16, help="rows per interleaved tile (multi-GPU sharding)")
     args = ap.parse_args()
     if args.impl == "reference":
         return run_reference(args)

@@ -69,12 +69,14 @@ __device__ __forceinline__ void intersect32(const Streams32& S, F3 o, F3 d, floa
     for (int i = 0; i < S.nu; ++i) {                     // Sphere::intersect_local, src/shape.rs:361-375
         float4 sp = S.usph[i];
         F3 L = mk(o.x - sp.x, o.y - sp.y, o.z - sp.z);
-        float b = dot(d, L);                             // half of the reference's b
-        float c = fmaf(L.z, L.z, fmaf(L.y, L.y, fmaf(L.x, L.x, -sp.w)));
-        float disc = fmaf(b, b, -a * c);
-        if (disc >= 0.f) {                               // most rays miss most spheres: skip the roots
-            float s = sqrtf(disc);
-            float t1 = (-b - s) * inv_a, t2 = (s - b) * inv_a;
+        // b^2 - a c cancels catastrophically in f32 for a small sphere far away (b^2 ~ c ~ 10^3, r^2 ~ 10^-2):
+        // use the distance of the centre from the ray instead, disc / a = r^2 - |L - (b/a) d|^2
+        float bia = dot(d, L) * inv_a;                   // half of the reference's b, over a
+        F3 q = mk(fmaf(-bia, d.x, L.x), fmaf(-bia, d.y, L.y), fmaf(-bia, d.z, L.z));
+        float dn = fmaf(-q.z, q.z, fmaf(-q.y, q.y, fmaf(-q.x, q.x, sp.w)));
+        if (dn >= 0.f) {                                 // most rays miss most spheres: skip the roots
+            float s = sqrtf(dn * inv_a);
+            float t1 = -bia - s, t2 = s - bia;
             float t = t1 >= 0.f ? t1 : t2;
             if (t >= 0.f && t < best_t) { best_t = t; hit = S.np + i; }
         }
@@ -83,13 +85,13 @@ __device__ __forceinline__ void intersect32(const Streams32& S, F3 o, F3 d, floa
         float4 r0 = S.gsph[3 * i], r1 = S.gsph[3 * i + 1], r2 = S.gsph[3 * i + 2];
         F3 lo = mk(row4(r0, o), row4(r1, o), row4(r2, o));
         F3 ld = mk(row3(r0, d), row3(r1, d), row3(r2, d));
-        float la = dot(ld, ld), b = dot(ld, lo), c = dot(lo, lo) - 1.f;
-        float disc = fmaf(b, b, -la * c);
-        float s = sqrtf(fmaxf(disc, 0.f));
-        float inv = rcp(la);
-        float t1 = (-b - s) * inv, t2 = (s - b) * inv;
+        float inv = rcp(dot(ld, ld)), bia = dot(ld, lo) * inv;
+        F3 q = mk(fmaf(-bia, ld.x, lo.x), fmaf(-bia, ld.y, lo.y), fmaf(-bia, ld.z, lo.z));   // closest approach to the centre
+        float dn = fmaf(-q.z, q.z, fmaf(-q.y, q.y, fmaf(-q.x, q.x, 1.f)));                    // disc / la, without cancellation
+        float s = sqrtf(fmaxf(dn, 0.f) * inv);
+        float t1 = -bia - s, t2 = s - bia;
         float t = t1 >= 0.f ? t1 : t2;
-        if (disc >= 0.f && t >= 0.f && t < best_t) { best_t = t; hit = S.np + S.nu + i; }
+        if (dn >= 0.f && t >= 0.f && t < best_t) { best_t = t; hit = S.np + S.nu + i; }
     }
 }
 
@@ -222,20 +224,20 @@ __device__ __forceinline__ bool shadow32(const Streams32& S, const float* __rest
         for (int i = 0; i < S.nu; ++i) {
             float4 sp = S.usph[i];
             F3 L = mk(o.x - sp.x, o.y - sp.y, o.z - sp.z);
-            float f0 = fmaf(L.z, L.z, fmaf(L.y, L.y, fmaf(L.x, L.x, -sp.w)));
-            float b = dot(d, L);
-            // f(t) = a t^2 + 2 b t + f0 is convex: its minimum over [0,1] is at clamp(-b/a, 0, 1)
-            float tc = __saturatef(-b * inv_a);
-            g = fminf(g, fmaf(tc, fmaf(a, tc, b + b), f0));
+            // f(t) = |L + t d|^2 - r^2 is convex: its minimum over [0,1] is at tc = clamp(-b/a, 0, 1); evaluated
+            // as |L + tc d|^2 - r^2 (no cancellation between large terms)
+            float tc = __saturatef(-dot(d, L) * inv_a);
+            F3 q = fma3(d, tc, L);
+            g = fminf(g, fmaf(q.z, q.z, fmaf(q.y, q.y, fmaf(q.x, q.x, -sp.w))));
         }
     } else {  // the light sits inside some sphere: a segment entirely inside it (f0 < 0 and f1 < 0) has no root
         for (int i = 0; i < S.nu; ++i) {
             float4 sp = S.usph[i];
             F3 L = mk(o.x - sp.x, o.y - sp.y, o.z - sp.z);
             float f0 = fmaf(L.z, L.z, fmaf(L.y, L.y, fmaf(L.x, L.x, -sp.w)));
-            float b = dot(d, L);
-            float tc = __saturatef(-b * inv_a);
-            float fmin = fmaf(tc, fmaf(a, tc, b + b), f0);
+            float tc = __saturatef(-dot(d, L) * inv_a);
+            F3 q = fma3(d, tc, L);
+            float fmin = fmaf(q.z, q.z, fmaf(q.y, q.y, fmaf(q.x, q.x, -sp.w)));
             g = fminf(g, fmaxf(fmin, -fmaxf(f0, usL[i])));
         }
     }
@@ -245,11 +247,12 @@ __device__ __forceinline__ bool shadow32(const Streams32& S, const float* __rest
             float4 r0 = S.gsph[3 * i], r1 = S.gsph[3 * i + 1], r2 = S.gsph[3 * i + 2];
             F3 lo = mk(row4(r0, o), row4(r1, o), row4(r2, o));
             F3 ld = mk(row3(r0, d), row3(r1, d), row3(r2, d));
-            float la = dot(ld, ld), b = dot(ld, lo), c = dot(lo, lo) - 1.f;
-            float disc = fmaf(b, b, -la * c);
-            if (disc >= 0.f) {
-                float s = sqrtf(disc), inv = rcp(la);
-                float t1 = (-b - s) * inv, t2 = (s - b) * inv;
+            float inv = rcp(dot(ld, ld)), bia = dot(ld, lo) * inv;
+            F3 q = mk(fmaf(-bia, ld.x, lo.x), fmaf(-bia, ld.y, lo.y), fmaf(-bia, ld.z, lo.z));
+            float dn = fmaf(-q.z, q.z, fmaf(-q.y, q.y, fmaf(-q.x, q.x, 1.f)));
+            if (dn >= 0.f) {
+                float s = sqrtf(dn * inv);
+                float t1 = -bia - s, t2 = s - bia;
                 float t = t1 >= 0.f ? t1 : t2;
                 hit |= t >= 0.f && t < 1.f;
             }
@@ -330,7 +333,10 @@ __device__ __noinline__ void compute_refractive32_unique(const Streams32& S, con
 #ifndef RTC_F32_MIN_BLOCKS
 #define RTC_F32_MIN_BLOCKS 6
 #endif
-template <bool kSmem, bool kUnique>
+// kSmem: shading records staged to shared memory; kUnique: world_ids are unique (<= 255 shapes);
+// kGlobal: the intersect streams stay in global memory (read through L1/L2 as warp-uniform loads) —
+// scenes of any size, e.g. the 10k-shape config C4.
+template <bool kSmem, bool kUnique, bool kGlobal>
 __global__ void __launch_bounds__(kThreads, RTC_F32_MIN_BLOCKS)
 render_f32_kernel(DevScene32 sc, CamParams cam, void* __restrict__ out_rgb, uint8_t* __restrict__ out_hit,
                   Counters* __restrict__ counters, unsigned* __restrict__ work) {
@@ -342,10 +348,12 @@ render_f32_kernel(DevScene32 sc, CamParams cam, void* __restrict__ out_rgb, uint
     const float* usL;
     const int32_t* gset;
     const int n_gset = sc.n_gset;
-    int light_inside_local = 0;
     const F3 light_pos = mk(sc.light_pos[0], sc.light_pos[1], sc.light_pos[2]);
     const F3 light_int = mk(sc.light_int[0], sc.light_int[1], sc.light_int[2]);
-    {
+    if (kGlobal) {
+        S.planes = sc.planes; S.usph = sc.usph; S.gsph = sc.gsph; S.pl_index = sc.pl_index; S.us_index = sc.us_index; S.gs_index = sc.gs_index;
+        plL = sc.plL; usL = sc.usL; gset = sc.gset;
+    } else {
         // stage the intersect streams (and, when small, the shading records): coalesced 16-byte loads
         float4* s_pl = smem4;
         float4* s_us = s_pl + S.np;
@@ -359,18 +367,8 @@ render_f32_kernel(DevScene32 sc, CamParams cam, void* __restrict__ out_rgb, uint
         float* s_usL = s_plL + S.np;
         int32_t* s_gset = reinterpret_cast<int32_t*>(s_usL + S.nu);
         for (int i = threadIdx.x; i < sc.n_gset && i < 16; i += kThreads) s_gset[i] = sc.gset[i];
-        for (int i = threadIdx.x; i < S.np; i += kThreads) {
-            float4 p = sc.planes[i];
-            s_pl[i] = p; s_pi[i] = sc.pl_index[i];
-            s_plL[i] = row4(p, light_pos);
-        }
-        for (int i = threadIdx.x; i < S.nu; i += kThreads) {
-            float4 p = sc.usph[i];
-            s_us[i] = p; s_ui[i] = sc.us_index[i];
-            F3 L = mk(light_pos.x - p.x, light_pos.y - p.y, light_pos.z - p.z);
-            s_usL[i] = dot(L, L) - p.w;
-            if (s_usL[i] < 0.f) light_inside_local = 1;
-        }
+        for (int i = threadIdx.x; i < S.np; i += kThreads) { s_pl[i] = sc.planes[i]; s_pi[i] = sc.pl_index[i]; s_plL[i] = sc.plL[i]; }
+        for (int i = threadIdx.x; i < S.nu; i += kThreads) { s_us[i] = sc.usph[i]; s_ui[i] = sc.us_index[i]; s_usL[i] = sc.usL[i]; }
         for (int i = threadIdx.x; i < 3 * S.ng; i += kThreads) s_gs[i] = sc.gsph[i];
         for (int i = threadIdx.x; i < S.ng; i += kThreads) s_gi[i] = sc.gs_index[i];
         if (kSmem) {
@@ -378,12 +376,12 @@ render_f32_kernel(DevScene32 sc, CamParams cam, void* __restrict__ out_rgb, uint
             for (int i = threadIdx.x; i < rec4; i += kThreads) s_rec[i] = g_rec[i];
             R = reinterpret_cast<const ShadeRec32*>(s_rec);
         }
-        light_inside_local = __syncthreads_or(light_inside_local);
+        __syncthreads();
         S.planes = s_pl; S.usph = s_us; S.gsph = s_gs; S.pl_index = s_pi; S.us_index = s_ui; S.gs_index = s_gi;
         plL = s_plL; usL = s_usL; gset = s_gset;
     }
 
-    const bool light_inside = light_inside_local != 0;
+    const bool light_inside = sc.light_inside != 0;
     const unsigned full = 0xffffffffu;
     const int lane = threadIdx.x & 31;
     const unsigned lt_mask = (1u << lane) - 1u;
@@ -628,8 +626,8 @@ cudaError_t launch_render_f32(const DevScene32& scene, const CamParams& cam, voi
     const int tiles = ((cam.hsize + kTileX - 1) / kTileX) * ((cam.shard_rows + kTileY - 1) / kTileY);
     const int warps = kThreads / 32;
     const bool small = streams + recs <= 40 * 1024;
-    if (!small && streams > 200 * 1024) return cudaErrorInvalidConfiguration;  // TODO(C4): tiled streaming of big scenes
-    const size_t smem = small ? streams + recs : streams;
+    const bool global_streams = !small && streams > 96 * 1024;   // big scenes: streams stay in global memory behind L1/L2
+    const size_t smem = global_streams ? 16 : (small ? streams + recs : streams);
     auto launch = [&](auto kernel) -> cudaError_t {
         cudaError_t er = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (er != cudaSuccess) return er;
@@ -640,8 +638,9 @@ cudaError_t launch_render_f32(const DevScene32& scene, const CamParams& cam, voi
         return cudaSuccess;
     };
     const bool uniq = scene.ids_unique != 0;
-    if (small) e = uniq ? launch(render_f32_kernel<true, true>) : launch(render_f32_kernel<true, false>);
-    else e = uniq ? launch(render_f32_kernel<false, true>) : launch(render_f32_kernel<false, false>);
+    if (global_streams) e = uniq ? launch(render_f32_kernel<false, true, true>) : launch(render_f32_kernel<false, false, true>);
+    else if (small) e = uniq ? launch(render_f32_kernel<true, true, false>) : launch(render_f32_kernel<true, false, false>);
+    else e = uniq ? launch(render_f32_kernel<false, true, false>) : launch(render_f32_kernel<false, false, false>);
     if (e != cudaSuccess) return e;
     return cudaGetLastError();
 }

@@ -63,6 +63,7 @@ struct DeviceState {
     DevBuf<double2> sph64, pl64;
     DevBuf<float4> pl32, us32, gs32;
     DevBuf<int32_t> sph_index, pl_index, us_index, gs_index, gset;
+    DevBuf<float> plL, usL;
     DevBuf<ShadeRec64> rec64;
     DevBuf<ShadeRec32> rec32;
     DevBuf<SmallRec32> srec;   // small-scene shading records, by stream position
@@ -229,6 +230,8 @@ struct HostScene {
     std::vector<double2> sph64, pl64;
     std::vector<float4> pl32, us32, gs32;
     std::vector<int32_t> sph_index, pl_index, us_index, gs_index, gset;
+    std::vector<float> plL, usL;
+    int light_inside = 0;
     std::vector<ShadeRec64> rec64;
     std::vector<ShadeRec32> rec32;
     int ids_unique = 1;
@@ -353,6 +356,19 @@ int flatten(const rtc_light* light, const rtc_shape* shapes, size_t n, HostScene
     for (int k = 0; k < np; ++k) if (shapes[hs.pl_index[k]].refractive_index != 1.0) hs.gset.push_back(k);
     for (int k = 0; k < nu; ++k) if (shapes[hs.us_index[k]].refractive_index != 1.0) hs.gset.push_back(np + k);
     for (int k = 0; k < (int)hs.gs_index.size(); ++k) if (shapes[hs.gs_index[k]].refractive_index != 1.0) hs.gset.push_back(np + nu + k);
+
+    // light-only terms of the shadow test (f32, from the f32 coefficients the kernels use)
+    {
+        const float lx = (float)light->position[0], ly = (float)light->position[1], lz = (float)light->position[2];
+        for (int k = 0; k < np; ++k) { const float4& q = hs.pl32[k]; hs.plL.push_back(fmaf(q.z, lz, fmaf(q.y, ly, fmaf(q.x, lx, q.w)))); }
+        for (int k = 0; k < nu; ++k) {
+            const float4& q = hs.us32[k];
+            const float dx = lx - q.x, dy = ly - q.y, dz = lz - q.z;
+            const float v = fmaf(dz, dz, fmaf(dy, dy, dx * dx)) - q.w;
+            hs.usL.push_back(v);
+            if (v < 0.f) hs.light_inside = 1;
+        }
+    }
 
     // ---- small-scene form: constant-bank streams + records by stream position ----
     SmallParams& sp = hs.small;
@@ -599,7 +615,7 @@ void rtc_context_destroy(rtc_context* ctx) {
     for (DeviceState& d : ctx->devs) {
         cudaSetDevice(d.dev);
         if (d.stream) cudaStreamSynchronize(d.stream);
-        d.sph64.release(); d.pl64.release(); d.pl32.release(); d.us32.release(); d.gs32.release(); d.us_index.release(); d.gs_index.release(); d.gset.release();
+        d.sph64.release(); d.pl64.release(); d.pl32.release(); d.us32.release(); d.gs32.release(); d.us_index.release(); d.gs_index.release(); d.gset.release(); d.plL.release(); d.usL.release();
         d.sph_index.release(); d.pl_index.release(); d.rec64.release(); d.rec32.release(); d.srec.release();
         d.rgb.release(); d.hit.release(); d.counters.release(); d.work.release();
         if (d.ev_k0) cudaEventDestroy(d.ev_k0);
@@ -634,6 +650,8 @@ int rtc_scene_upload(rtc_context* ctx, const rtc_light* light, const rtc_shape* 
         CUDA_TRY(upload(d.us_index, hs.us_index, d.stream));
         CUDA_TRY(upload(d.gs_index, hs.gs_index, d.stream));
         CUDA_TRY(upload(d.gset, hs.gset, d.stream));
+        CUDA_TRY(upload(d.plL, hs.plL, d.stream));
+        CUDA_TRY(upload(d.usL, hs.usL, d.stream));
         CUDA_TRY(upload(d.sph_index, hs.sph_index, d.stream));
         CUDA_TRY(upload(d.pl_index, hs.pl_index, d.stream));
         CUDA_TRY(upload(d.rec64, hs.rec64, d.stream));
@@ -655,6 +673,7 @@ int rtc_scene_upload(rtc_context* ctx, const rtc_light* light, const rtc_shape* 
         d.s32.planes = d.pl32.p; d.s32.pl_index = d.pl_index.p; d.s32.usph = d.us32.p; d.s32.us_index = d.us_index.p;
         d.s32.gsph = d.gs32.p; d.s32.gs_index = d.gs_index.p;
         d.s32.gset = d.gset.p; d.s32.n_gset = (int)hs.gset.size();
+        d.s32.plL = d.plL.p; d.s32.usL = d.usL.p; d.s32.light_inside = hs.light_inside;
         d.s32.rec = d.rec32.p;
         for (int k = 0; k < 3; ++k) {
             d.s64.light_pos[k] = light->position[k]; d.s64.light_int[k] = light->intensity[k];

@@ -76,6 +76,9 @@ struct DevScene32 {
     const ShadeRec32* rec;     // [n_shapes]
     const int32_t* gset;       // stream positions of the shapes with refractive_index != 1.0
     int n_gset;
+    const float* plL;          // [n_planes] f(light) = n.light + w   (shadow test: f(0) f(1) <= 0)
+    const float* usL;          // [n_usph]   |light - c|^2 - r^2
+    int light_inside;          // the light sits inside some uniform sphere
     float light_pos[3];
     float light_int[3];
 };

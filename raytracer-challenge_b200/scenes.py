@@ -101,8 +101,8 @@ def synthetic_scene(n_spheres=9992, seed=0xB200):
     Spheres: centre in [-20,20]x[0.4,12]x[-20,20], radius in [0.05,0.35]; every 10th is also
     non-uniformly scaled and rotated (exercises the stored inverse-transpose).  Materials: 70 %
     diffuse, 20 % reflective 0.3-0.9, 10 % glass.  Planes: checker floor, a thin transparent
-    "water" sheet, four striped walls (no ceiling: rays escaping upward are genuine misses) and
-    two tilted mirrors.  world_id wraps at 256 like the reference's release build.
+    "water" sheet, three striped planes, a tilted sub-floor and two tilted mirrors on the left; the
+    upper right of the view is open, so rays escaping there are genuine misses.  world_id wraps at 256 like the reference's release build.
     """
     w = World(Light(Color(1, 1, 1), (-10.0, 30.0, -10.0)))
     w.add_shape(Plane(_I(), Material(specular=0.0, reflectiveness=0.2,
@@ -116,13 +116,16 @@ def synthetic_scene(n_spheres=9992, seed=0xB200):
         p.set_transform(_I().scaling(0.5, 0.5, 0.5))
         return Material(ambient=0.05, diffuse=0.5, specular=0.0, reflectiveness=0.1, pattern=p)
 
-    w.add_shape(Plane(_I().rotation_z(math.pi / 2).translation(-25, 0, 0), wall()))
-    w.add_shape(Plane(_I().rotation_z(math.pi / 2).translation(25, 0, 0), wall()))
-    w.add_shape(Plane(_I().rotation_x(math.pi / 2).translation(0, 0, 25), wall()))
-    w.add_shape(Plane(_I().rotation_x(math.pi / 2).translation(0, 0, -40), wall()))
+    # The planes leave the upper right of the view open (no ceiling, no right or far wall, mirrors on the
+    # left), so rays escaping there are genuine misses for the hit/miss mask.
+    w.add_shape(Plane(_I().rotation_z(math.pi / 2).translation(-25, 0, 0), wall()))              # left wall
+    w.add_shape(Plane(_I().rotation_x(math.pi / 2).translation(0, 0, -40), wall()))              # wall behind the camera
+    w.add_shape(Plane(_I().rotation_x(0.06).translation(0, -6, 60), wall()))                      # ground rising gently behind the field
     mirror = dict(color=Color(0.05, 0.05, 0.05), ambient=0.0, diffuse=0.1, specular=0.9, shininess=300, reflectiveness=0.9)
-    w.add_shape(Plane(_I().rotation_x(math.pi / 2).rotation_y(0.5).rotation_x(-0.2).translation(-18, 0, 20), Material(**mirror)))
-    w.add_shape(Plane(_I().rotation_x(math.pi / 2).rotation_y(-0.5).rotation_x(-0.2).translation(18, 0, 20), Material(**mirror)))
+    w.add_shape(Plane(_I().rotation_z(math.pi / 2).rotation_y(-0.5).translation(-22, 0, 5), Material(**mirror)))
+    w.add_shape(Plane(_I().rotation_z(math.pi / 2).rotation_y(-0.3).rotation_z(0.15).translation(-24, 0, 18), Material(**mirror)))
+    w.add_shape(Plane(_I().rotation_z(0.08).translation(0, -0.3, 0),
+                      Material(color=Color(0.3, 0.25, 0.2), specular=0.0, diffuse=0.7)))               # slightly tilted sub-floor
     for i in range(n_spheres):
         u = [_u01(seed, i, k) for k in range(16)]
         cx, cy, cz = -20 + 40 * u[0], 0.4 + 11.6 * u[1], -20 + 40 * u[2]
