@@ -184,8 +184,8 @@ def run_gpu(args):
     class Path:
         """One (precision, output format, exchange mode) way of producing the frame on rank 0."""
 
-        def __init__(self, precision, fmt, mode):
-            self.sf = ShardedFrame(W, H, fmt, rank, N, dev, tile_rows=TILE, mode=mode)
+        def __init__(self, precision, fmt, mode, signal="flags"):
+            self.sf = ShardedFrame(W, H, fmt, rank, N, dev, tile_rows=TILE, mode=mode, signal=signal)
             self.sf.connect(r)
             self.opts = self.sf.shard_opts(rtc.Renderer.make_opts, precision=precision, rect=ffi.RECT_FULL, max_depth=DEPTH)
             self.fmt = fmt
@@ -205,7 +205,7 @@ def run_gpu(args):
             if self.sf.mode == "nccl":
                 self.sf.exchange(lambda g, f: r.assemble_device(camd, self.opts, g.data_ptr(), self.sf.stride_rows, self.fmt, f.data_ptr(), stream))
             else:
-                self.sf.exchange()       # 4-byte stream-ordered all-reduce: the completion signal (pixels went over NVLink already)
+                self.sf.exchange(stream=stream)   # completion flags over NVLink: no collective (pixels are already in rank 0's frame)
 
     def timed(fn, steps, warmup):
         for _ in range(warmup):
@@ -282,6 +282,10 @@ def run_gpu(args):
         extra["kernel_ms_per_rank"] = {"peer_frame_destination": per_rank(main.kernel_only), "local_destination": per_rank(alt.kernel_only)}
         extra["gather_nccl"] = {"ms_per_frame": float(msn.mean()), "mrays_per_s": rays / (float(msn.mean()) * 1e-3) / 1e6,
                                 "path": "compact shard buffers, dist.gather (NCCL send/recv) to rank 0, rtc_assemble_device"}
+        ar = Path(ffi.PRECISION_F32_FAST, ffi.OUT_F32_RGB, "p2p", signal="allreduce")
+        msa, _, _ = timed(ar.frame, args.steps, 3)
+        extra["p2p_allreduce_signal"] = {"ms_per_frame": float(msa.mean()), "path": "peer stores + 4-byte NCCL all-reduce as completion signal"}
+        ar.sf.close()
         main.frame(); alt.frame(); sync_all()
         if rank == 0:
             ref = torch.empty((H, W, 3), dtype=torch.float32, device=dev)
@@ -348,7 +352,7 @@ def run_gpu(args):
                        "shaded_hits_per_frame": int(shaded), "l2": "256 MB buffer rewritten between timed iterations (outside the events)",
                        "parallelism": f"interleaved {TILE}-row tiles over {N} GPU(s)" +
                                       (", render kernels store pixels straight into rank 0's frame over NVLink (CUDA IPC peer mapping); "
-                                       "one 4-byte all-reduce as completion signal" if N > 1 else ""),
+                                       "completion = one peer-stored flag per rank, rank 0 waits on its stream (no collective)" if N > 1 else ""),
                        "timing": "CUDA events per step on the launch stream, max over ranks"},
             "roofline": {"bound": "fp32_non_tensor", "achieved": achieved, "peak": p32, "unit": "TFLOP/s", "frac": achieved / p32,
                          "traffic": None, "peak_source": "FFMA micro-benchmark on this GPU in this run (rtc_measure_peak_tflops)",
@@ -391,7 +395,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--tile-rows", type=int, default=16, help="rows per interleaved tile (multi-GPU sharding)")
+    ap.add_argument("--tile-rows", type=int, default=4, help="rows per interleaved tile (multi-GPU sharding)")
     args = ap.parse_args()
     if args.impl == "reference":
         return run_reference(args)

@@ -135,6 +135,9 @@ typedef struct rtc_render_opts {
 /* f32 fast mode: use the general kernel (shared-memory streams, any shape count) even when the
  * scene fits the constant-bank small-scene kernel.  For testing one against the other. */
 #define RTC_OPT_F32_GENERAL_KERNEL 2
+/* f32 small-scene kernel: hand tiles out in linear order instead of "tiles that see a transparent
+ * surface first" (the scheduling pre-pass).  Same image either way; for measuring the difference. */
+#define RTC_OPT_LINEAR_TILE_ORDER 4
 
 #define RTC_MAX_DEPTH 8
 
@@ -214,6 +217,16 @@ int rtc_assemble_device(rtc_context* ctx, const rtc_camera* cam, const rtc_rende
 int rtc_ipc_export(rtc_context* ctx, const void* d_ptr, void* handle, uint64_t* offset);
 int rtc_ipc_open(rtc_context* ctx, const void* handle, uint64_t offset, void** out_d_ptr);
 int rtc_ipc_close(rtc_context* ctx, void* d_ptr, uint64_t offset);
+
+/* Completion flags for the peer-store frame assembly.  rtc_signal_device enqueues, after everything
+ * already on `stream` (NULL = the context's stream), a store of `value` to the 32-bit word at d_flag —
+ * which may be a peer-mapped word of another GPU (rtc_ipc_open) — with system-scope release: all
+ * earlier stores of this stream (the rendered pixels) are visible before the flag.  rtc_wait_device
+ * enqueues a kernel that returns once d_flags[i] >= value for all i in [0, n) (it gives up after about
+ * two seconds and the next CUDA call on the stream reports an error; no host synchronisation either
+ * way).  Rank 0 of a sharded render waits for the other ranks' flags instead of running a collective. */
+int rtc_signal_device(rtc_context* ctx, void* d_flag, uint32_t value, void* stream);
+int rtc_wait_device(rtc_context* ctx, const void* d_flags, int n, uint32_t value, void* stream);
 
 /* Register-resident FMA micro-benchmark on the context's first GPU: measured non-tensor peak
  * of the FP32 (precision = RTC_PRECISION_F32_FAST) or FP64 pipe in TFLOP/s (FMA = 2 flops),

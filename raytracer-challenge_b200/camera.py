@@ -133,6 +133,12 @@ class Renderer:
     def ipc_close(self, d_ptr, offset):
         ffi.check(self._lib.rtc_ipc_close(self._ctx, C.c_void_p(d_ptr), offset))
 
+    def signal_device(self, d_flag, value, stream=None):
+        ffi.check(self._lib.rtc_signal_device(self._ctx, C.c_void_p(d_flag), value, C.c_void_p(stream) if stream else None))
+
+    def wait_device(self, d_flags, n, value, stream=None):
+        ffi.check(self._lib.rtc_wait_device(self._ctx, C.c_void_p(d_flags), n, value, C.c_void_p(stream) if stream else None))
+
     def shard_rows(self, cam_desc, opts):
         return self._lib.rtc_shard_rows(C.byref(cam_desc), C.byref(opts))
 

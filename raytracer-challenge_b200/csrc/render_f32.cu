@@ -599,6 +599,13 @@ render_f32_kernel(DevScene32 sc, CamParams cam, void* __restrict__ out_rgb, uint
         }
     }
 
+    // The tile counter resets itself: the last block to finish zeroes work[0] (tiles handed out) and
+    // work[1] (blocks done), so a launch needs no memset in front of it.
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        __threadfence();
+        if (atomicAdd(work + 1, 1u) == gridDim.x - 1) { work[0] = 0u; work[1] = 0u; __threadfence(); }
+    }
     if (counters) {
         unsigned r = __reduce_add_sync(full, n_rays), h = __reduce_add_sync(full, n_shaded), ph = __reduce_add_sync(full, n_phits);
         if (lane == 0) {
@@ -615,8 +622,7 @@ render_f32_kernel(DevScene32 sc, CamParams cam, void* __restrict__ out_rgb, uint
 cudaError_t launch_render_f32(const DevScene32& scene, const CamParams& cam, void* d_rgb, uint8_t* d_hit,
                               Counters* d_counters, unsigned* d_work, cudaStream_t stream) {
     if (cam.shard_rows <= 0) return cudaSuccess;
-    cudaError_t e = cudaMemsetAsync(d_work, 0, sizeof(unsigned), stream);
-    if (e != cudaSuccess) return e;
+    cudaError_t e = cudaSuccess;   // d_work[0..1] are zero between launches (the kernel resets them)
     int dev = 0, sms = 0;
     cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);

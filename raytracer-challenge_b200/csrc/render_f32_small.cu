@@ -266,6 +266,7 @@ render_f32_small_kernel(const __grid_constant__ SmallParams P, void* __restrict_
                 if (lane == 0) t = atomicAdd(work, 1u);
                 t = __shfl_sync(full, t, 0);
                 if (t >= (unsigned)P.total_tiles) { exhausted = true; break; }
+                if (P.order) t = P.order[t];                  // heavy tiles first (classify_tiles_small_kernel)
                 const int ty = (int)(t / (unsigned)P.tiles_x);
                 wtx = ((int)t - ty * P.tiles_x) * kTileX;
                 wty = ty * kTileY;
@@ -417,6 +418,13 @@ render_f32_small_kernel(const __grid_constant__ SmallParams P, void* __restrict_
         }
     }
 
+    // The tile counter resets itself: the last block to finish zeroes work[0] (tiles handed out) and
+    // work[1] (blocks done), so a launch needs no memset in front of it.
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        __threadfence();
+        if (atomicAdd(work + 1, 1u) == gridDim.x - 1) { work[0] = 0u; work[1] = 0u; work[2] = 0u; work[3] = 0u; __threadfence(); }
+    }
     if (counters) {
         // every shaded hit casts exactly one shadow ray: rays = radiance rays + shaded hits
         const unsigned r = __reduce_add_sync(full, n_rad), h = __reduce_add_sync(full, n_hits), ph = __reduce_add_sync(full, n_phits);
@@ -429,18 +437,55 @@ render_f32_small_kernel(const __grid_constant__ SmallParams P, void* __restrict_
     }
 }
 
+// Tile scheduling pre-pass.  The frame time of a persistent kernel ends with the longest ray chain that
+// started last: a tile of glass pixels (up to 2^6 - 1 radiance rays per pixel) claimed at the very end
+// runs ~40 loop iterations on an almost empty GPU.  One primary ray through the centre of every 8x4
+// tile tells whether it sees a transparent surface; those tiles are handed out first
+// (order[0 .. heavy)), the others after them (filled from the back).  It changes the order in which
+// pixels are rendered, not what is rendered.  work[2] / work[3] count heavy / light tiles.
+__global__ void __launch_bounds__(kThreads)
+classify_tiles_small_kernel(const __grid_constant__ SmallParams P, unsigned* __restrict__ work) {
+    const unsigned full = 0xffffffffu;
+    const int lane = threadIdx.x & 31;
+    unsigned mask_reg;
+    asm volatile("mov.u32 %0, %1;" : "=r"(mask_reg) : "n"(~kMask));
+    const int t = blockIdx.x * kThreads + threadIdx.x;
+    const bool valid = t < P.total_tiles;
+    bool heavy = false;
+    if (valid) {
+        const int ty = t / P.tiles_x, tx = t - ty * P.tiles_x;
+        const int px = min(tx * kTileX + kTileX / 2, P.hsize - 1);
+        const int pr = min(ty * kTileY + kTileY / 2, P.shard_rows - 1);
+        const int py = P.shard_count > 1 ? shard_row_to_frame_row(pr, P.tile_rows, P.shard_index, P.shard_count) : pr;
+        const float fx = (float)px, fy = (float)py;          // the corner shared by the four centre pixels
+        F3 dir = mk(fmaf(P.cam_dx[0], fx, fmaf(P.cam_dy[0], fy, P.cam_d0[0])),
+                    fmaf(P.cam_dx[1], fx, fmaf(P.cam_dy[1], fy, P.cam_d0[1])),
+                    fmaf(P.cam_dx[2], fx, fmaf(P.cam_dy[2], fy, P.cam_d0[2])));
+        dir = dir * rsqrtf(dot(dir, dir));
+        const unsigned key = intersect_small(P, mk(P.cam_o[0], P.cam_o[1], P.cam_o[2]), dir, mask_reg);
+        if (key < kInfBits) heavy = P.rec[key & kMask].tr_ri.x != 0.f;
+    }
+    const unsigned mh = __ballot_sync(full, valid && heavy), ml = __ballot_sync(full, valid && !heavy);
+    unsigned bh = 0, bl = 0;
+    if (lane == 0) { if (mh) bh = atomicAdd(work + 2, (unsigned)__popc(mh)); if (ml) bl = atomicAdd(work + 3, (unsigned)__popc(ml)); }
+    bh = __shfl_sync(full, bh, 0); bl = __shfl_sync(full, bl, 0);
+    const unsigned below = (1u << lane) - 1u;
+    if (valid && heavy) P.order[bh + __popc(mh & below)] = (unsigned)t;
+    if (valid && !heavy) P.order[P.total_tiles - 1 - (int)(bl + __popc(ml & below))] = (unsigned)t;
+}
+
 }  // namespace
 
 cudaError_t launch_render_f32_small(const SmallParams& P, int out_format, void* d_rgb, uint8_t* d_hit, Counters* d_counters,
                                     unsigned* d_work, cudaStream_t stream) {
     if (P.shard_rows <= 0) return cudaSuccess;
-    cudaError_t e = cudaMemsetAsync(d_work, 0, sizeof(unsigned), stream);
-    if (e != cudaSuccess) return e;
+    cudaError_t e = cudaSuccess;   // d_work[0..1] are zero between launches (the kernel resets them)
     int dev = 0, sms = 0;
     cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
     const size_t smem = (size_t)(kSmallMaxPlanes + P.nu) * sizeof(SmallRec32) + 16;
     const int warps = kThreads / 32;
+    if (P.order) classify_tiles_small_kernel<<<(P.total_tiles + kThreads - 1) / kThreads, kThreads, 0, stream>>>(P, d_work);
     auto launch = [&](auto kernel) -> cudaError_t {
         int blocks_per_sm = 0;
         cudaError_t er = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks_per_sm, kernel, kThreads, smem);

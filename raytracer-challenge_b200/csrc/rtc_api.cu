@@ -75,7 +75,8 @@ struct DeviceState {
     DevBuf<unsigned char> rgb;
     DevBuf<unsigned char> hit;
     DevBuf<Counters> counters;
-    DevBuf<unsigned> work;  // tile counter of the persistent f32 kernel
+    DevBuf<unsigned> work;  // tile counter of the persistent f32 kernel (+ blocks done, heavy / light tile counts)
+    DevBuf<unsigned> order; // tile hand-out order of the small-scene kernel
 };
 
 // Allocation base of a device pointer (cuMemGetAddressRange, fetched through the runtime so that the
@@ -452,6 +453,24 @@ __global__ void assemble_rows_kernel(const U* __restrict__ gathered, U* __restri
     for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < row_units; i += (size_t)gridDim.x * blockDim.x) dst[i] = src[i];
 }
 
+// ---- completion flags (rtc_signal_device / rtc_wait_device) ---------------------------------------
+__global__ void signal_kernel(unsigned* flag, unsigned value) {
+    __threadfence_system();
+    asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(flag), "r"(value) : "memory");
+}
+__global__ void wait_kernel(const unsigned* flags, int n, unsigned value) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const long long t0 = clock64();
+    for (;;) {
+        unsigned v;
+        asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(flags + i) : "memory");
+        if ((int)(v - value) >= 0) break;
+        if (clock64() - t0 > 4000000000LL) { asm volatile("trap;"); }   // ~2 s: a rank died; fail loudly instead of hanging the GPU
+        __nanosleep(200);
+    }
+}
+
 // ---- FMA peak micro-benchmark --------------------------------------------------------------------
 template <typename T>
 __global__ void __launch_bounds__(256) fma_peak_kernel(T* out, int iters, T seed) {
@@ -546,6 +565,11 @@ int launch_on(DeviceState& d, const CamParams& cp, int precision, int flags, voi
     else if (d.small_ok && !(flags & RTC_OPT_F32_GENERAL_KERNEL)) {
         SmallParams P = d.small;
         fill_small_camera(P, cp);
+        P.order = nullptr;
+        if (P.max_depth > 0 && P.n_glass != 0 && P.total_tiles >= 4096 && !(flags & RTC_OPT_LINEAR_TILE_ORDER)) {
+            if (d.order.ensure((size_t)P.total_tiles) != cudaSuccess) return fail(RTC_ERR_CUDA, "tile order buffer");
+            P.order = d.order.p;
+        }
         e = launch_render_f32_small(P, cp.out_format, d_rgb, d_hit, d_counters, d.work.p, st);
     } else e = launch_render_f32(d.s32, cp, d_rgb, d_hit, d_counters, d.work.p, st);
     if (e != cudaSuccess) return fail(RTC_ERR_CUDA, std::string("kernel launch: ") + cudaGetErrorString(e));
@@ -594,7 +618,8 @@ int rtc_context_create(const int* device_ids, int n_gpus, rtc_context** out_ctx)
             if (e == cudaSuccess) e = cudaEventCreateWithFlags(&d.ev_copy[b], cudaEventDisableTiming);
         }
         if (e == cudaSuccess) e = d.counters.ensure(1);
-        if (e == cudaSuccess) e = d.work.ensure(1);
+        if (e == cudaSuccess) e = d.work.ensure(8);
+        if (e == cudaSuccess) e = cudaMemset(d.work.p, 0, 8 * sizeof(unsigned));
         if (e != cudaSuccess) {
             std::string m = cudaGetErrorString(e);
             rtc_context_destroy(ctx);
@@ -617,7 +642,7 @@ void rtc_context_destroy(rtc_context* ctx) {
         if (d.stream) cudaStreamSynchronize(d.stream);
         d.sph64.release(); d.pl64.release(); d.pl32.release(); d.us32.release(); d.gs32.release(); d.us_index.release(); d.gs_index.release(); d.gset.release(); d.plL.release(); d.usL.release();
         d.sph_index.release(); d.pl_index.release(); d.rec64.release(); d.rec32.release(); d.srec.release();
-        d.rgb.release(); d.hit.release(); d.counters.release(); d.work.release();
+        d.rgb.release(); d.hit.release(); d.counters.release(); d.work.release(); d.order.release();
         if (d.ev_k0) cudaEventDestroy(d.ev_k0);
         if (d.ev_k1) cudaEventDestroy(d.ev_k1);
         if (d.ev_c1) cudaEventDestroy(d.ev_c1);
@@ -788,6 +813,27 @@ int rtc_ipc_close(rtc_context* ctx, void* d_ptr, uint64_t offset) {
     if (!ctx || !d_ptr) return fail(RTC_ERR_INVALID_ARG, "rtc_ipc_close: null argument");
     CUDA_TRY(cudaSetDevice(ctx->devs[0].dev));
     CUDA_TRY(cudaIpcCloseMemHandle((char*)d_ptr - offset));
+    return RTC_OK;
+}
+
+int rtc_signal_device(rtc_context* ctx, void* d_flag, uint32_t value, void* stream) {
+    if (!ctx || !d_flag) return fail(RTC_ERR_INVALID_ARG, "rtc_signal_device: null argument");
+    DeviceState& d = ctx->devs[0];
+    CUDA_TRY(cudaSetDevice(d.dev));
+    cudaStream_t st = stream ? (cudaStream_t)stream : d.stream;
+    signal_kernel<<<1, 1, 0, st>>>((unsigned*)d_flag, value);
+    CUDA_TRY(cudaGetLastError());
+    return RTC_OK;
+}
+
+int rtc_wait_device(rtc_context* ctx, const void* d_flags, int n, uint32_t value, void* stream) {
+    if (!ctx || !d_flags || n < 0) return fail(RTC_ERR_INVALID_ARG, "rtc_wait_device: bad argument");
+    if (n == 0) return RTC_OK;
+    DeviceState& d = ctx->devs[0];
+    CUDA_TRY(cudaSetDevice(d.dev));
+    cudaStream_t st = stream ? (cudaStream_t)stream : d.stream;
+    wait_kernel<<<(n + 31) / 32, 32, 0, st>>>((const unsigned*)d_flags, n, value);
+    CUDA_TRY(cudaGetLastError());
     return RTC_OK;
 }
 

@@ -112,6 +112,7 @@ struct SmallParams {
     int n_glass;                       // -1: fast n1/n2 test unavailable (a glass plane, or more than 8 glass spheres)
     int pad0;
     const SmallRec32* rec;             // [64] by stream position (global, staged to shared memory per block)
+    unsigned* order;                   // [total_tiles] tile hand-out order (heavy tiles first), or null = linear
     float light_pos[3], light_int[3];
     float cam_o[3], cam_dx[3], cam_dy[3], cam_d0[3];   // ray dir = normalize(cam_dx (x+xo) + cam_dy (y+yo) + cam_d0)
     int hsize, shard_rows, xlim, ylim;

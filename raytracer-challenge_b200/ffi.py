@@ -20,6 +20,7 @@ OUT_F64_RGB, OUT_F32_RGB, OUT_U8_RGB = 0, 1, 2
 RTC_MAX_DEPTH = 8
 OPT_DST_FULL_FRAME = 1
 OPT_F32_GENERAL_KERNEL = 2
+OPT_LINEAR_TILE_ORDER = 4
 IPC_HANDLE_BYTES = 64
 
 
@@ -86,6 +87,8 @@ EXPORTS = [
     ("rtc_ipc_export", C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.POINTER(C.c_uint64)]),
     ("rtc_ipc_open", C.c_int, [C.c_void_p, C.c_void_p, C.c_uint64, C.POINTER(C.c_void_p)]),
     ("rtc_ipc_close", C.c_int, [C.c_void_p, C.c_void_p, C.c_uint64]),
+    ("rtc_signal_device", C.c_int, [C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p]),
+    ("rtc_wait_device", C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_uint32, C.c_void_p]),
     ("rtc_measure_peak_tflops", C.c_int, [C.c_void_p, C.c_int, C.POINTER(C.c_double)]),
 ]
 

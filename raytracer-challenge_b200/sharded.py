@@ -8,8 +8,10 @@ Two exchange modes:
   send/recv over NVLink) collects the buffers on rank 0, ``rtc_assemble_device`` de-interleaves.
 * ``"p2p"``   — rank 0 exports its frame buffer through CUDA IPC (``rtc_ipc_export``), the other
   ranks map it (``rtc_ipc_open``) and their render kernels store finished pixels straight into it
-  over NVLink (``RTC_OPT_DST_FULL_FRAME``): the transfer overlaps the rendering pixel by pixel and
-  the only collective left is the barrier that tells rank 0 the frame is complete.
+  over NVLink (``RTC_OPT_DST_FULL_FRAME``): the transfer overlaps the rendering pixel by pixel.
+  No collective is left: each rank then stores a sequence number into its word of a flag array in
+  rank 0's memory (``rtc_signal_device``, system-scope release after its pixels) and rank 0 waits
+  for the words on its stream (``rtc_wait_device``).
 
 The reference has no multi-device path (rayon threads over one ``Canvas``, src/camera.rs:144-160);
 the tile-to-rank arithmetic here is the only "protocol", and it is pure index math so the same class
@@ -58,7 +60,7 @@ class ShardedFrame:
     ``shard_opts()`` — ``Renderer.render_device`` on GPUs, any stand-in on CPU tensors in the
     tests — and (2) calls ``exchange()``."""
 
-    def __init__(self, hsize, vsize, out_format, rank, world, device, tile_rows=16, mode="p2p", channels=3):
+    def __init__(self, hsize, vsize, out_format, rank, world, device, tile_rows=16, mode="p2p", channels=3, signal="flags"):
         self.hsize, self.vsize, self.out_format = hsize, vsize, out_format
         self.rank, self.world, self.device, self.tile_rows, self.mode = rank, world, device, tile_rows, mode
         self.dtype = _TORCH_DTYPE[out_format]
@@ -70,8 +72,13 @@ class ShardedFrame:
         self.shard = None
         self.gathered = None
         self.remote_ptr = None
-        self._ipc = None
+        self._ipc = []
         self._token = None
+        self.signal = signal          # p2p completion: "flags" (peer-stored sequence numbers) or "allreduce" (4-byte NCCL all-reduce)
+        self.flags = None             # rank 0: int32[world]; other ranks: self.remote_flags (peer pointer)
+        self.remote_flags = None
+        self.seq = 0
+        self._renderer = None
         if world == 1:
             self.frame = torch.zeros((vsize,) + shape_tail, dtype=self.dtype, device=device)
         elif mode == "nccl":
@@ -82,36 +89,43 @@ class ShardedFrame:
         elif mode == "p2p":
             if rank == 0:
                 self.frame = torch.zeros((vsize,) + shape_tail, dtype=self.dtype, device=device)
+                self.flags = torch.zeros(max(world, 64), dtype=torch.int32, device=device)
         else:
             raise ValueError(f"unknown exchange mode {mode!r}")
 
     # ---- p2p set-up: rank 0 exports the frame, the others map it ---------------------------------
     def connect(self, renderer):
+        self._renderer = renderer
         if self.world == 1 or self.mode != "p2p":
             return
         payload = [None]
         if self.rank == 0:
-            handle, offset = renderer.ipc_export(self.frame.data_ptr())
-            payload = [(handle, offset)]
+            payload = [(renderer.ipc_export(self.frame.data_ptr()), renderer.ipc_export(self.flags.data_ptr()))]
         dist.broadcast_object_list(payload, src=0)
         if self.rank != 0:
-            handle, offset = payload[0]
-            self.remote_ptr = renderer.ipc_open(handle, offset)
-            self._ipc = (renderer, self.remote_ptr, offset)
+            (fh, foff), (gh, goff) = payload[0]
+            self.remote_ptr = renderer.ipc_open(fh, foff)
+            self._ipc.append((self.remote_ptr, foff))
+            self.remote_flags = renderer.ipc_open(gh, goff)
+            self._ipc.append((self.remote_flags, goff))
         dist.barrier()
 
     def close(self):
-        if self._ipc is not None:
-            renderer, ptr, offset = self._ipc
+        if self._ipc:
             torch.cuda.synchronize()
-            renderer.ipc_close(ptr, offset)
-            self._ipc = None
+            for ptr, offset in self._ipc:
+                self._renderer.ipc_close(ptr, offset)
+            self._ipc = []
 
     # ---- one frame ---------------------------------------------------------------------------------
     def shard_opts(self, make_opts, **kw):
         flags = kw.pop("flags", 0)
         if self.world > 1 and self.mode == "p2p":
             flags |= ffi.OPT_DST_FULL_FRAME
+            if self.rank != 0:
+                # peer stores: keep the pixel stream over NVLink even in time (the heavy-tiles-first order
+                # ends with a burst of cheap pixels that saturates rank 0's ingress; measured +27 us at N=8)
+                flags |= ffi.OPT_LINEAR_TILE_ORDER
         return make_opts(out_format=self.out_format, shard_index=self.rank, shard_count=self.world,
                          tile_rows=self.tile_rows, flags=flags, **kw)
 
@@ -123,7 +137,7 @@ class ShardedFrame:
             return self.shard
         return self.frame if self.rank == 0 else self.remote_ptr
 
-    def exchange(self, assemble=None):
+    def exchange(self, assemble=None, stream=None):
         """The exchange step after every rank's render call was enqueued.  Returns the frame on
         rank 0 (None elsewhere).  ``assemble(gathered, frame)`` de-interleaves on the device
         (rtc_assemble_device); without it the torch index form is used (CPU tensors)."""
@@ -138,8 +152,15 @@ class ShardedFrame:
             else:
                 self.frame = deinterleave(self.gathered, self.vsize, self.tile_rows)
             return self.frame
-        # p2p: all peer stores are complete once every rank's kernel has finished; a 4-byte
-        # stream-ordered all-reduce is the completion signal (no host synchronisation)
+        # p2p: all peer stores are complete once every rank's kernel has finished.
+        if self.signal == "flags":
+            self.seq += 1
+            if self.rank == 0:
+                self._renderer.wait_device(self.flags.data_ptr() + 4, self.world - 1, self.seq, stream)
+                return self.frame
+            self._renderer.signal_device(self.remote_flags + 4 * self.rank, self.seq, stream)
+            return None
+        # fallback: a 4-byte stream-ordered all-reduce as completion signal (no host synchronisation)
         if self._token is None:
             self._token = torch.zeros(1, dtype=torch.int32, device=self.device)
         dist.all_reduce(self._token)
