@@ -355,7 +355,11 @@ def run_gpu(args):
                                        "completion = one peer-stored flag per rank, rank 0 waits on its stream (no collective)" if N > 1 else ""),
                        "timing": "CUDA events per step on the launch stream, max over ranks"},
             "roofline": {"bound": "fp32_non_tensor", "achieved": achieved, "peak": p32, "unit": "TFLOP/s", "frac": achieved / p32,
-                         "traffic": None, "peak_source": "FFMA micro-benchmark on this GPU in this run (rtc_measure_peak_tflops)",
+                         "traffic": 61.65e6 if N == 1 else None,
+                         "traffic_note": "dram__bytes_read.sum + dram__bytes_write.sum of one 4K launch, ncu --set full capture "
+                                         "(profiles/r01_ncu_f32_small_1p47ms.txt): 61.5 MB written + 0.16 MB read; the frame is 99.5 MB, the "
+                                         "rest was still in the 126 MB L2 when the kernel ended; scene reads never reach HBM",
+                         "peak_source": "FFMA micro-benchmark on this GPU in this run (rtc_measure_peak_tflops)",
                          "peak_formula": FP32_FORMULA_PEAK, "frac_of_formula": achieved / FP32_FORMULA_PEAK,
                          "algorithmic_gflop_per_frame": flops / 1e9, "kernel_ms": kernel_ms, "kernel": "render_f32_small_kernel",
                          "hbm_gbs_measured_peak": peaks.get("hbm_gbs"),

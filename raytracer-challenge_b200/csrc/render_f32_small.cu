@@ -5,12 +5,12 @@
 // (src/camera.rs:64-114, src/shape.rs:677-781, src/material.rs:319-361) — but built so that the
 // brute-force loops issue almost nothing except FP32 math:
 //   * the intersect streams travel as a __grid_constant__ kernel parameter, i.e. they live in
-//     constant bank 0, and the loops are fully unrolled in groups of four with a warp-uniform exit
-//     per group: every plane / sphere coefficient is a c[0x0][imm] operand of the FFMA/FADD that
-//     uses it — no load instruction, no address arithmetic, no loop counter;
+//     constant bank 0, and the loops are fully unrolled in groups of two with a warp-uniform exit
+//     per group: coefficients arrive through LDC/LDCU at compile-time offsets (uniform registers feed
+//     the FFMA/FADD directly) — no address arithmetic, no loop counter, stream positions are immediates;
 //   * hit selection is ONE unsigned min per candidate root: for t >= 0 the IEEE bit pattern orders
 //     like the value, negative and NaN roots compare above +inf, so
-//         best = min(best, (bits(t) & ~mask) + stream_position)
+//         best = min(best, (bits(t) & ~mask) | stream_position)        (one LOP3 + half a VIMNMX3)
 //     keeps the nearest non-negative root together with its shape in a single register (the low
 //     6 mantissa bits carry the position: t is truncated by <= 2^-17 relative); there is no branch
 //     on the discriminant (sqrt of a negative discriminant is NaN, which loses the min);

@@ -12,6 +12,10 @@
 namespace rtc {
 namespace {
 
+#ifndef RTC_F64_UNROLL
+#define RTC_F64_UNROLL 1
+#endif
+constexpr int kUnroll = RTC_F64_UNROLL;   // shapes tested per loop trip in World::intersect (independent FP64 chains in flight)
 constexpr double kEps = 0.00000001;  // Vector::EPSILON, src/vec.rs:16
 constexpr int kBlockX = 16, kBlockY = 8, kThreads = kBlockX * kBlockY;
 
@@ -81,10 +85,12 @@ __device__ __forceinline__ void take(double t, int idx, double& best_t, int& bes
 __device__ __noinline__ void intersect_world(const Streams& S, V3 o, V3 d, double& best_t, int& best_idx) {
     best_t = __longlong_as_double(0x7ff0000000000000LL);
     best_idx = 0x7fffffff;
+#pragma unroll kUnroll
     for (int i = 0; i < S.np; ++i) {
         double t;
         if (plane_root(S.pl + 2 * i, o, d, t)) take(t, S.pl_index[i], best_t, best_idx);
     }
+#pragma unroll kUnroll
     for (int i = 0; i < S.ns; ++i) {
         double t1, t2;
         if (sphere_roots(S.sph + 6 * i, o, d, t1, t2)) {
@@ -226,7 +232,10 @@ __device__ __forceinline__ void thread_sample(int& sx, int& sy) {
 }
 
 template <bool kInSmem>
-__global__ void __launch_bounds__(kThreads)
+#ifndef RTC_F64_MIN_BLOCKS
+#define RTC_F64_MIN_BLOCKS 4
+#endif
+__global__ void __launch_bounds__(kThreads, RTC_F64_MIN_BLOCKS)
 render_f64_kernel(DevScene64 sc, CamParams cam, double* __restrict__ out_f64, float* __restrict__ out_f32,
                   uint8_t* __restrict__ out_u8, uint8_t* __restrict__ out_hit, Counters* __restrict__ counters) {
     extern __shared__ double2 smem[];

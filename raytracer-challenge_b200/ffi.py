@@ -8,7 +8,7 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "csrc", "librtc_b200.so")
+LIB_PATH = os.environ.get("RTC_B200_LIB") or os.path.join(_HERE, "csrc", "librtc_b200.so")   # override: kernel-variant experiments
 
 RTC_OK = 0
 RTC_ERR_INVALID_ARG, RTC_ERR_UNSUPPORTED, RTC_ERR_NO_DEVICE, RTC_ERR_CUDA, RTC_ERR_NO_SCENE, RTC_ERR_NCCL = 1, 2, 3, 4, 5, 6
