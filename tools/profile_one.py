@@ -1,5 +1,5 @@
 """Render a few frames of the reflect/refract scene through the C ABI (for ncu / sanitizer runs).
-usage: python tools/profile_one.py [f32|f64] [width] [height] [frames] [samples]"""
+usage: python tools/profile_one.py [f32|f64] [width] [height] [frames] [samples] [room|c4]"""
 import os
 import sys
 
@@ -15,8 +15,13 @@ h = int(sys.argv[3]) if len(sys.argv) > 3 else 1080
 frames = int(sys.argv[4]) if len(sys.argv) > 4 else 3
 samples = int(sys.argv[5]) if len(sys.argv) > 5 else 1
 r = rtc.Renderer([0])
-r.upload(rtc.scenes.reflect_refract_scene())
-cam = rtc.scenes.reflect_refract_camera(w, h, samples=samples).flatten()
+scene = sys.argv[6] if len(sys.argv) > 6 else "room"
+if scene == "c4":
+    r.upload(rtc.scenes.synthetic_scene())
+    cam = rtc.scenes.synthetic_camera(w, h, samples=samples).flatten()
+else:
+    r.upload(rtc.scenes.reflect_refract_scene())
+    cam = rtc.scenes.reflect_refract_camera(w, h, samples=samples).flatten()
 fmt = ffi.OUT_F32_RGB if prec == ffi.PRECISION_F32_FAST else ffi.OUT_F64_RGB
 opts = rtc.Renderer.make_opts(precision=prec, out_format=fmt)
 buf = torch.empty((h, w, 3), dtype=torch.float32 if fmt == ffi.OUT_F32_RGB else torch.float64, device="cuda")
