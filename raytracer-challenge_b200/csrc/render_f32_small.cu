@@ -60,6 +60,33 @@ __device__ __forceinline__ unsigned key_of(float t, unsigned mask_reg) {
     return r;
 }
 
+// Group dispatch.  Shapes are tested in groups of two; the group count is warp-uniform.  Default: a
+// chain with one uniform compare + branch per group.  RTC_F32S_DUFF: jump once into a fall-through
+// switch (groups run from the last to the first; min / top-2 do not depend on the order).
+template <int V> struct IntC { static constexpr int value = V; };
+#ifdef RTC_F32S_DUFF
+#define RTC_DUFF_CASE(k) case (k) + 1: if constexpr ((k) < N) f(IntC<((k) < N ? (k) : 0)>{});
+template <int N, class F>
+__device__ __forceinline__ void for_groups(int n, F&& f) {
+    switch (n) {
+        RTC_DUFF_CASE(23) RTC_DUFF_CASE(22) RTC_DUFF_CASE(21) RTC_DUFF_CASE(20) RTC_DUFF_CASE(19) RTC_DUFF_CASE(18)
+        RTC_DUFF_CASE(17) RTC_DUFF_CASE(16) RTC_DUFF_CASE(15) RTC_DUFF_CASE(14) RTC_DUFF_CASE(13) RTC_DUFF_CASE(12)
+        RTC_DUFF_CASE(11) RTC_DUFF_CASE(10) RTC_DUFF_CASE(9) RTC_DUFF_CASE(8) RTC_DUFF_CASE(7) RTC_DUFF_CASE(6)
+        RTC_DUFF_CASE(5) RTC_DUFF_CASE(4) RTC_DUFF_CASE(3) RTC_DUFF_CASE(2) RTC_DUFF_CASE(1) RTC_DUFF_CASE(0)
+        default: break;
+    }
+}
+#else
+template <int N, int G = 0, class F>
+__device__ __forceinline__ void for_groups(int n, F&& f) {
+    if constexpr (G < N) {
+        if (G >= n) return;
+        f(IntC<G>{});
+        for_groups<N, G + 1>(n, f);
+    }
+}
+#endif
+
 // One sphere against a unit-length radiance ray (Sphere::intersect_local, src/shape.rs:361-375, with
 // a = d.d = 1 and b halved).  Only one root can be the hit: t1 when the origin is outside (c > 0),
 // t2 when it is inside (c < 0; then t1 < 0 < t2)  ->  t = -b - copysign(s, c).
@@ -78,31 +105,21 @@ __device__ __forceinline__ unsigned plane_key(const float4 pl, F3 o, F3 d, unsig
     return key_of<kPos>(-row4(pl, o) * rcp(row3(pl, d)), mask_reg);   // Plane::intersect_local, src/shape.rs:462-471; parallel: +-inf / NaN
 }
 
-template <int G> struct PlaneGroups {
-    static __device__ __forceinline__ unsigned run(const SmallParams& P, F3 o, F3 d, unsigned m, unsigned best) {
-        constexpr int g = kSmallMaxPlanes / 2 - G;
-        if (g >= P.npg) return best;
-        best = min(best, min(plane_key<2 * g>(P.planes[2 * g], o, d, m), plane_key<2 * g + 1>(P.planes[2 * g + 1], o, d, m)));
-        return PlaneGroups<G - 1>::run(P, o, d, m, best);
-    }
-};
-template <> struct PlaneGroups<0> { static __device__ __forceinline__ unsigned run(const SmallParams&, F3, F3, unsigned, unsigned best) { return best; } };
-template <int G> struct SphereGroups {
-    static __device__ __forceinline__ unsigned run(const SmallParams& P, F3 o, F3 d, unsigned m, unsigned best) {
-        constexpr int g = kSmallMaxUsph / 2 - G;
-        if (g >= P.nug) return best;
-        best = min(best, min(sphere_key<kSmallMaxPlanes + 2 * g>(P.usph[2 * g], o, d, m), sphere_key<kSmallMaxPlanes + 2 * g + 1>(P.usph[2 * g + 1], o, d, m)));
-        return SphereGroups<G - 1>::run(P, o, d, m, best);
-    }
-};
-template <> struct SphereGroups<0> { static __device__ __forceinline__ unsigned run(const SmallParams&, F3, F3, unsigned, unsigned best) { return best; } };
-
 // World::intersect + Intersections::get_hit for a unit-length ray: nearest root in [0, +inf).
-// Stream positions are compile-time constants (plane i -> i, sphere i -> 16 + i); shapes are tested in
-// groups of two with a warp-uniform exit per group.  Returns the packed key; >= kInfBits = no hit.
+// Stream positions are compile-time constants (plane i -> i, sphere i -> 16 + i).  Returns the packed
+// key; >= kInfBits = no hit.
 __device__ __forceinline__ unsigned intersect_small(const SmallParams& P, F3 o, F3 d, unsigned mask_reg) {
-    unsigned best = PlaneGroups<kSmallMaxPlanes / 2>::run(P, o, d, mask_reg, kInfBits);
-    return SphereGroups<kSmallMaxUsph / 2>::run(P, o, d, mask_reg, best);
+    unsigned best = kInfBits;
+    for_groups<kSmallMaxPlanes / 2>(P.npg, [&](auto gc) {
+        constexpr int g = decltype(gc)::value;
+        best = min(best, min(plane_key<2 * g>(P.planes[2 * g], o, d, mask_reg), plane_key<2 * g + 1>(P.planes[2 * g + 1], o, d, mask_reg)));
+    });
+    for_groups<kSmallMaxUsph / 2>(P.nug, [&](auto gc) {
+        constexpr int g = decltype(gc)::value;
+        best = min(best, min(sphere_key<kSmallMaxPlanes + 2 * g>(P.usph[2 * g], o, d, mask_reg),
+                             sphere_key<kSmallMaxPlanes + 2 * g + 1>(P.usph[2 * g + 1], o, d, mask_reg)));
+    });
+    return best;
 }
 
 // World::is_shadowed_by_light (src/shape.rs:716-727) as an any-hit test over the segment
@@ -111,17 +128,15 @@ __device__ __forceinline__ unsigned intersect_small(const SmallParams& P, F3 o, 
 //   sphere: f(t) = a t^2 + 2 b t + f0 is convex, its minimum over [0,1] is at clamp(-b/a, 0, 1)
 __device__ __forceinline__ bool shadow_small(const SmallParams& P, F3 o, F3 d) {
     float g = 1.0f;
-#pragma unroll
-    for (int k = 0; k < kSmallMaxPlanes / 2; ++k) {
-        if (k >= P.npg) break;
+    for_groups<kSmallMaxPlanes / 2>(P.npg, [&](auto gc) {
+        constexpr int k = decltype(gc)::value;
         g = fminf(g, fminf(row4(P.splanes[2 * k], o), row4(P.splanes[2 * k + 1], o)));
-    }
+    });
     const float a = dot(d, d);
     const float nhia = -0.5f * rcp(a);
     const F3 d2 = mk(d.x + d.x, d.y + d.y, d.z + d.z);
-#pragma unroll
-    for (int k = 0; k < kSmallMaxUsph / 2; ++k) {
-        if (k >= P.nug) break;
+    for_groups<kSmallMaxUsph / 2>(P.nug, [&](auto gc) {
+        constexpr int k = decltype(gc)::value;
         float fm[2];
 #pragma unroll
         for (int j = 0; j < 2; ++j) {
@@ -133,7 +148,7 @@ __device__ __forceinline__ bool shadow_small(const SmallParams& P, F3 o, F3 d) {
             fm[j] = fmaf(tc, fmaf(a, tc, b2), f0);
         }
         g = fminf(g, fminf(fm[0], fm[1]));
-    }
+    });
     return g <= 0.f;
 }
 
@@ -141,40 +156,45 @@ __device__ __forceinline__ bool shadow_small(const SmallParams& P, F3 o, F3 d) {
 // world_ids are unique on this path): a shape is a container iff it has exactly one negative-t
 // entry (plane: t < 0; sphere: origin inside), containers are ordered by (t, stream position), and
 //   n1 = ri(last container)            n2 = hit is a container ? ri(last container other than it) : ri(hit)
-// Negative floats order in reverse as unsigned, so bits(t) ^ 0x80000000 turns "latest negative t"
-// into an unsigned min as well; ties go to the later position via (mask - pos).
-__device__ __noinline__ void compute_refractive_small(const SmallParams& P, const SmallRec32* __restrict__ R, F3 o, F3 d,
-                                                      int hit_pos, float& n1, float& n2) {
-    unsigned top1 = 0xffffffffu, top2 = 0xffffffffu;   // smallest / second smallest key
-    auto offer = [&](float t, int pos) {               // only called with t < 0
-        unsigned k = ((__float_as_uint(t) ^ 0x80000000u) & ~kMask) + (kMask - (unsigned)pos);
-        top2 = min(top2, max(top1, k));
-        top1 = min(top1, k);
-    };
-    bool hit_is_container = false;
-#pragma unroll 1
-    for (int i = 0; i < P.np; ++i) {                   // a plane behind the origin counts as a container
-        float4 pl = P.planes[i];
-        float t = -row4(pl, o) * rcp(row3(pl, d));
-        if (t < 0.f) offer(t, i);
-    }
-#pragma unroll 1
-    for (int i = 0; i < P.nu; ++i) {                   // t1 < 0 <= t2  <=>  the origin is inside (c < 0)
-        float4 sp = P.usph[i];
-        F3 L = mk(o.x - sp.x, o.y - sp.y, o.z - sp.z);
-        float c = fmaf(L.z, L.z, fmaf(L.y, L.y, fmaf(L.x, L.x, -sp.w)));
-        if (c < 0.f) {
-            float b = dot(d, L);
-            offer(-b - sqrtf(fmaf(b, b, -c)), kSmallMaxPlanes + i);
-            hit_is_container |= kSmallMaxPlanes + i == hit_pos;
-        }
-    }
-    const int p1 = top1 == 0xffffffffu ? -1 : (int)(kMask - (top1 & kMask));
-    const int p2 = top2 == 0xffffffffu ? -1 : (int)(kMask - (top2 & kMask));
-    n1 = p1 >= 0 ? R[p1].tr_ri.y : 1.0f;
-    if (p1 == hit_pos) n2 = p2 >= 0 ? R[p2].tr_ri.y : 1.0f;
-    else if (hit_is_container) n2 = n1;
-    else n2 = R[hit_pos].tr_ri.y;
+// "Latest negative t" is the NEAREST hit of the reversed ray (o, -d), so the same unsigned-min keys as
+// in intersect_small apply with t' = -t: a plane is a container when t' > 0, a sphere when the origin
+// is inside it (c < 0; then t' = b + sqrt(b^2 - c) > 0) — for c >= 0 the sign bit of ~c is OR-ed into
+// the key, which then loses the min like a negative root.  Ties go to the later stream position
+// (the low bits carry kMask - pos).  Two smallest keys = last container and the one before it.
+struct Top2 { unsigned a, b; };   // smallest, second smallest
+__device__ __forceinline__ Top2 offer2(Top2 t, unsigned k0, unsigned k1) {
+    const unsigned lo = min(k0, k1), hi = max(k0, k1);
+    Top2 r;
+    r.b = min(t.b, min(hi, max(t.a, lo)));
+    r.a = min(t.a, lo);
+    return r;
+}
+template <unsigned kPos>
+__device__ __forceinline__ unsigned plane_back_key(const float4 pl, F3 o, F3 d, unsigned mask_reg) {
+    return key_of<kMask - kPos>(row4(pl, o) * rcp(row3(pl, d)), mask_reg);
+}
+template <unsigned kPos>
+__device__ __forceinline__ unsigned sphere_back_key(const float4 sp, F3 o, F3 d, unsigned mask_reg) {
+    F3 L = mk(o.x - sp.x, o.y - sp.y, o.z - sp.z);
+    float b = dot(d, L);
+    float c = fmaf(L.z, L.z, fmaf(L.y, L.y, fmaf(L.x, L.x, -sp.w)));
+    float tb = b + sqrt_nan(fmaf(b, b, -c));
+    unsigned u;                                           // (~bits(c) & 0x80000000) | bits(tb)
+    asm("lop3.b32 %0, %1, %2, %3, 0xAE;" : "=r"(u) : "r"(__float_as_uint(c)), "n"(0x80000000), "r"(__float_as_uint(tb)));
+    return key_of<kMask - kPos>(__uint_as_float(u), mask_reg);
+}
+__device__ __forceinline__ Top2 containers_small(const SmallParams& P, F3 o, F3 d, unsigned mask_reg) {
+    Top2 t; t.a = t.b = 0xffffffffu;
+    for_groups<kSmallMaxPlanes / 2>(P.npg, [&](auto gc) {
+        constexpr int g = decltype(gc)::value;
+        t = offer2(t, plane_back_key<2 * g>(P.planes_d[2 * g], o, d, mask_reg), plane_back_key<2 * g + 1>(P.planes_d[2 * g + 1], o, d, mask_reg));
+    });
+    for_groups<kSmallMaxUsph / 2>(P.nug, [&](auto gc) {
+        constexpr int g = decltype(gc)::value;
+        t = offer2(t, sphere_back_key<kSmallMaxPlanes + 2 * g>(P.usph[2 * g], o, d, mask_reg),
+                   sphere_back_key<kSmallMaxPlanes + 2 * g + 1>(P.usph[2 * g + 1], o, d, mask_reg));
+    });
+    return t;
 }
 
 // Pattern::pattern_at for the rarely used kinds (src/material.rs:67-69,133-135,163-170,233-241)
@@ -187,16 +207,35 @@ __device__ __noinline__ F3 pattern_rare(int kind, F3 a, F3 b, F3 p) {
     }
 }
 
+// Shading records are read through explicit 32-bit shared-window addresses: indexing the generic
+// `extern __shared__` pointer makes ptxas rebuild the window base (S2R CgaCtaId + MOV + LEA) every
+// loop iteration; a base computed once plus `hpos * sizeof(SmallRec32)` is one IMAD.
+__device__ __forceinline__ float4 lds4(unsigned addr) {
+    float4 v;
+    asm("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(addr));
+    return v;
+}
+__device__ __forceinline__ float lds1(unsigned addr) {
+    float v;
+    asm("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(addr));
+    return v;
+}
+constexpr unsigned kRecBytes = (unsigned)sizeof(SmallRec32);
+constexpr unsigned kOffNrm = 0, kOffColAmb = 16, kOffDifSpec = 32, kOffTrRi = 48, kOffP0 = 64, kOffP1 = 80, kOffP2 = 96, kOffPa = 112, kOffPb = 128;
+static_assert(sizeof(SmallRec32) == 144, "SmallRec32 layout");
+
 #ifndef RTC_F32S_MIN_BLOCKS
 #define RTC_F32S_MIN_BLOCKS 6
 #endif
 
-template <int kFmt>
+// kAux: the launch wants the work counters and/or the hit mask; without them (the plain frame) the
+// per-iteration bookkeeping for both is compiled out.
+template <int kFmt, bool kAux>
 __global__ void __launch_bounds__(kThreads, RTC_F32S_MIN_BLOCKS)
 render_f32_small_kernel(const __grid_constant__ SmallParams P, void* __restrict__ out_rgb, uint8_t* __restrict__ out_hit,
                         Counters* __restrict__ counters, unsigned* __restrict__ work) {
     extern __shared__ float4 smem4[];
-    SmallRec32* R = reinterpret_cast<SmallRec32*>(smem4);
+    const unsigned rbase = (unsigned)__cvta_generic_to_shared(smem4);
     {   // stage the shading records (indexed by stream position): coalesced 16-byte loads
         constexpr int kRec4 = (int)(sizeof(SmallRec32) / 16);
         const float4* g_rec = reinterpret_cast<const float4*>(P.rec);
@@ -252,7 +291,7 @@ render_f32_small_kernel(const __grid_constant__ SmallParams P, void* __restrict_
                         o[k] = (uint8_t)(q < 0 ? 0 : (q > 255 ? 255 : q));
                     }
                 }
-                if (out_hit) out_hit[p] = (uint8_t)hitbits;
+                if (kAux && out_hit) out_hit[p] = (uint8_t)hitbits;
                 have = false;
             }
         }
@@ -308,20 +347,22 @@ render_f32_small_kernel(const __grid_constant__ SmallParams P, void* __restrict_
         // ------------------------------------------------------------ phase A: World::intersect (all lanes, idle ones trace a dummy)
         const unsigned key = intersect_small(P, ro, rd, mask_reg);
         const bool hit = has_ray && key < kInfBits;
-        n_rad += has_ray ? 1u : 0u;
-        n_hits += hit ? 1u : 0u;
-        if (hit && primary) { hitbits |= 1u << sub; ++n_phits; }
+        if (kAux) {
+            n_rad += has_ray ? 1u : 0u;
+            n_hits += hit ? 1u : 0u;
+            if (hit && primary) { hitbits |= 1u << sub; ++n_phits; }
+        }
         has_ray = hit;                                        // miss: World::color_at -> black (src/shape.rs:708)
 
         // ------------------------------------------------------------ phase B: prepare_computations (src/shape.rs:75-96,144-152)
         const int hpos = hit ? (int)(key & kMask) : 0;
         const float t = __uint_as_float((key & ~kMask) | ((kMask + 1u) >> 1));   // centre of the truncation interval
-        const SmallRec32& rec = R[hpos];
-        const float4 tr = rec.tr_ri;
+        const unsigned rec = rbase + (unsigned)hpos * kRecBytes;
+        const float4 tr = lds4(rec + kOffTrRi);
         F3 p = fma3(rd, hit ? t : 0.f, ro);                   // Ray::position
         F3 hn;
         {
-            const float4 nr = rec.nrm;                        // plane: constant normal; sphere: (p - c) / r
+            const float4 nr = lds4(rec + kOffNrm);            // plane: constant normal; sphere: (p - c) / r
             hn = mk(fmaf(p.x, nr.w, nr.x), fmaf(p.y, nr.w, nr.y), fmaf(p.z, nr.w, nr.z));
             // p carries t's truncation error (<= 2^-18 relative), so |hn| is only ~1e-4 from 1; the
             // reflected / refracted directions must stay unit length (the sphere test assumes a = 1)
@@ -338,7 +379,18 @@ render_f32_small_kernel(const __grid_constant__ SmallParams P, void* __restrict_
                 inside_glass |= fmaf(L.z, L.z, fmaf(L.y, L.y, fmaf(L.x, L.x, -sp4.w))) < 0.f;
             }
             // origin inside no shape with ri != 1: every container has ri 1.0 -> n1 = 1, n2 = ri(hit)
-            if (inside_glass) compute_refractive_small(P, R, ro, rd, hpos, hn1, hn2);
+            if (inside_glass) {
+                const Top2 top = containers_small(P, ro, rd, mask_reg);
+                const int p1 = top.a < kInfBits ? (int)(kMask - (top.a & kMask)) : -1;
+                const int p2 = top.b < kInfBits ? (int)(kMask - (top.b & kMask)) : -1;
+                // the hit shape is a container iff it is a sphere with the origin inside: |n(ro)| < 1
+                const float4 nr = lds4(rec + kOffNrm);
+                const F3 no = mk(fmaf(ro.x, nr.w, nr.x), fmaf(ro.y, nr.w, nr.y), fmaf(ro.z, nr.w, nr.z));
+                const bool hit_is_container = hpos >= kSmallMaxPlanes && dot(no, no) < 1.f;
+                hn1 = p1 >= 0 ? lds1(rbase + (unsigned)p1 * kRecBytes + kOffTrRi + 4) : 1.0f;
+                if (p1 == hpos) hn2 = p2 >= 0 ? lds1(rbase + (unsigned)p2 * kRecBytes + kOffTrRi + 4) : 1.0f;
+                else if (hit_is_container) hn2 = hn1;
+            }
         }
         const float dn = dot(rd, hn);
         if (dn > 0.f) hn = mk(-hn.x, -hn.y, -hn.z);           // inside: normal . eyev < 0
@@ -351,12 +403,12 @@ render_f32_small_kernel(const __grid_constant__ SmallParams P, void* __restrict_
 
         // ------------------------------------------------------------ phase D: shade_hit
         if (hit) {
-            const float4 ca = rec.col_amb, ds = rec.dif_spec;
+            const float4 ca = lds4(rec + kOffColAmb), ds = lds4(rec + kOffDifSpec);
             const int pkind = __float_as_int(tr.z);
             F3 base = xyz(ca);
             if (pkind != RTC_PATTERN_NONE) {                  // Pattern::pattern_at_shape at over_point
-                const F3 pp = mk(row4(rec.p0, hp), row4(rec.p1, hp), row4(rec.p2, hp));
-                const float4 pa = rec.pa, pb = rec.pb;
+                const F3 pp = mk(row4(lds4(rec + kOffP0), hp), row4(lds4(rec + kOffP1), hp), row4(lds4(rec + kOffP2), hp));
+                const float4 pa = lds4(rec + kOffPa), pb = lds4(rec + kOffPb);
                 if (pkind == RTC_PATTERN_STRIPE || pkind == RTC_PATTERN_CHECKER) {
                     // stripe: floor(x) % 2 ; checker: (floor x + floor y + floor z) % 2   (pb.w = 0 / 1)
                     const float s = fmaf(pb.w, floorf(pp.y) + floorf(pp.z), floorf(pp.x));
@@ -425,7 +477,7 @@ render_f32_small_kernel(const __grid_constant__ SmallParams P, void* __restrict_
         __threadfence();
         if (atomicAdd(work + 1, 1u) == gridDim.x - 1) { work[0] = 0u; work[1] = 0u; work[2] = 0u; work[3] = 0u; __threadfence(); }
     }
-    if (counters) {
+    if (kAux && counters) {
         // every shaded hit casts exactly one shadow ray: rays = radiance rays + shaded hits
         const unsigned r = __reduce_add_sync(full, n_rad), h = __reduce_add_sync(full, n_hits), ph = __reduce_add_sync(full, n_phits);
         if (lane == 0) {
@@ -494,10 +546,11 @@ cudaError_t launch_render_f32_small(const SmallParams& P, int out_format, void* 
         kernel<<<grid, kThreads, smem, stream>>>(P, d_rgb, d_hit, d_counters, d_work);
         return cudaGetLastError();
     };
+    const bool aux = d_counters != nullptr || d_hit != nullptr;
     switch (out_format) {
-        case RTC_OUT_F64_RGB: return launch(render_f32_small_kernel<RTC_OUT_F64_RGB>);
-        case RTC_OUT_F32_RGB: return launch(render_f32_small_kernel<RTC_OUT_F32_RGB>);
-        default:              return launch(render_f32_small_kernel<RTC_OUT_U8_RGB>);
+        case RTC_OUT_F64_RGB: return aux ? launch(render_f32_small_kernel<RTC_OUT_F64_RGB, true>) : launch(render_f32_small_kernel<RTC_OUT_F64_RGB, false>);
+        case RTC_OUT_F32_RGB: return aux ? launch(render_f32_small_kernel<RTC_OUT_F32_RGB, true>) : launch(render_f32_small_kernel<RTC_OUT_F32_RGB, false>);
+        default:              return aux ? launch(render_f32_small_kernel<RTC_OUT_U8_RGB, true>) : launch(render_f32_small_kernel<RTC_OUT_U8_RGB, false>);
     }
 }
 
