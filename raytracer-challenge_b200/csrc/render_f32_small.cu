@@ -224,6 +224,11 @@ constexpr unsigned kRecBytes = (unsigned)sizeof(SmallRec32);
 constexpr unsigned kOffNrm = 0, kOffColAmb = 16, kOffDifSpec = 32, kOffTrRi = 48, kOffP0 = 64, kOffP1 = 80, kOffP2 = 96, kOffPa = 112, kOffPb = 128;
 static_assert(sizeof(SmallRec32) == 144, "SmallRec32 layout");
 
+#ifdef RTC_F32S_TRACE   // diagnostic build only (tools/trace_tail.py): per-warp start / tiles-exhausted / end times
+__device__ unsigned long long g_trace[16384 * 4];
+__device__ __forceinline__ unsigned long long gtime() { unsigned long long t; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t)); return t; }
+#endif
+
 #ifndef RTC_F32S_MIN_BLOCKS
 #define RTC_F32S_MIN_BLOCKS 6
 #endif
@@ -268,6 +273,11 @@ render_f32_small_kernel(const __grid_constant__ SmallParams P, void* __restrict_
     float4 stk_a[kMaxStack], stk_b[kMaxStack];  // pending refraction rays: (o, weight), (d, remaining)
     int sp = 0;
     unsigned n_rad = 0, n_hits = 0, n_phits = 0;
+#ifdef RTC_F32S_TRACE
+    const unsigned long long tr_t0 = gtime();
+    unsigned long long tr_t1 = 0;
+    unsigned tr_iters = 0, tr_tail_iters = 0;
+#endif
 
     for (;;) {
         // ------------------------------------------------------------ lanes without a ray
@@ -343,6 +353,10 @@ render_f32_small_kernel(const __grid_constant__ SmallParams P, void* __restrict_
             }
         }
         if (__all_sync(full, !has_ray && !have && exhausted)) break;
+#ifdef RTC_F32S_TRACE
+        if (exhausted && tr_t1 == 0) tr_t1 = gtime();
+        ++tr_iters; if (exhausted) ++tr_tail_iters;
+#endif
 
         // ------------------------------------------------------------ phase A: World::intersect (all lanes, idle ones trace a dummy)
         const unsigned key = intersect_small(P, ro, rd, mask_reg);
@@ -470,6 +484,12 @@ render_f32_small_kernel(const __grid_constant__ SmallParams P, void* __restrict_
         }
     }
 
+#ifdef RTC_F32S_TRACE
+    if (lane == 0) {
+        const unsigned w = blockIdx.x * (kThreads / 32) + (threadIdx.x >> 5);
+        if (w < 16384) { g_trace[4 * w] = tr_t0; g_trace[4 * w + 1] = tr_t1; g_trace[4 * w + 2] = gtime(); g_trace[4 * w + 3] = ((unsigned long long)tr_iters << 32) | tr_tail_iters; }
+    }
+#endif
     // The tile counter resets itself: the last block to finish zeroes work[0] (tiles handed out) and
     // work[1] (blocks done), so a launch needs no memset in front of it.
     __syncthreads();
@@ -527,6 +547,12 @@ classify_tiles_small_kernel(const __grid_constant__ SmallParams P, unsigned* __r
 }
 
 }  // namespace
+
+#ifdef RTC_F32S_TRACE
+extern "C" int rtc_debug_read_trace(unsigned long long* dst, int n_words) {
+    return (int)cudaMemcpyFromSymbol(dst, g_trace, sizeof(unsigned long long) * (size_t)n_words);
+}
+#endif
 
 cudaError_t launch_render_f32_small(const SmallParams& P, int out_format, void* d_rgb, uint8_t* d_hit, Counters* d_counters,
                                     unsigned* d_work, cudaStream_t stream) {
