@@ -53,8 +53,18 @@ struct Streams32 {
 // upper bound (+inf for radiance rays, 1 for shadow rays whose direction is light - point, which
 // is the reference's `h.t < distance` in units of the unnormalised direction, src/shape.rs:716-727).
 // `hit` is a position in the concatenated stream order planes | uniform spheres | general spheres.
-__device__ __forceinline__ void intersect32(const Streams32& S, F3 o, F3 d, float& best_t, int& hit) {
+// kCollect (scenes with aliased world_ids): every list entry with t < 0 that the loops come across is
+// appended to `neg` as (t, 2 * stream position + root) — Intersection::compute_refractive needs exactly
+// those entries (src/shape.rs:115-141), and the line of a ray meets only a few of 10^4 spheres, so keeping
+// them costs a few instructions inside the rare "line meets sphere" branch instead of two more passes
+// over every shape.  n_neg counts all of them; entries beyond kNegCap are dropped and the caller falls
+// back to the passes.
+constexpr int kNegCap = 48;
+template <bool kCollect>
+__device__ __forceinline__ void intersect32(const Streams32& S, F3 o, F3 d, float& best_t, int& hit, float2* neg, int& n_neg) {
     hit = -1;
+    if (kCollect) n_neg = 0;
+    auto keep = [&](float t, int code) { if (n_neg < kNegCap) neg[n_neg] = make_float2(t, __int_as_float(code)); ++n_neg; };
     const float a = dot(d, d);
     const float inv_a = rcp(a);
 #pragma unroll 2
@@ -79,6 +89,7 @@ __device__ __forceinline__ void intersect32(const Streams32& S, F3 o, F3 d, floa
             float t1 = -bia - s, t2 = s - bia;
             float t = t1 >= 0.f ? t1 : t2;
             if (t >= 0.f && t < best_t) { best_t = t; hit = S.np + i; }
+            if (kCollect && t1 < 0.f) { keep(t1, 2 * (S.np + i)); if (t2 < 0.f) keep(t2, 2 * (S.np + i) + 1); }
         }
     }
     for (int i = 0; i < S.ng; ++i) {                     // Shape::intersect: ray.transform(inverse) first
@@ -92,6 +103,7 @@ __device__ __forceinline__ void intersect32(const Streams32& S, F3 o, F3 d, floa
         float t1 = -bia - s, t2 = s - bia;
         float t = t1 >= 0.f ? t1 : t2;
         if (dn >= 0.f && t >= 0.f && t < best_t) { best_t = t; hit = S.np + S.nu + i; }
+        if (kCollect && dn >= 0.f && t1 < 0.f) { keep(t1, 2 * (S.np + S.nu + i)); if (t2 < 0.f) keep(t2, 2 * (S.np + S.nu + i) + 1); }
     }
 }
 
@@ -169,6 +181,48 @@ __device__ __noinline__ void compute_refractive32(const Streams32& S, const Shad
     Cont32 top1, top2;
     top1.idx = -1; top2.idx = -1; top1.t = top2.t = 0.f; top1.ord = top2.ord = 0; top1.id = top2.id = -1;
     for_each_negative(S, o, d, [&](float t, int idx, int root, bool) {
+        int id = __float_as_int(rec[idx].pa.w) & 255;
+        if ((parity[id >> 5] >> (id & 31)) & 1u) {
+            Cont32 e; e.t = t; e.ord = 2 * idx + root; e.idx = idx; e.id = id;
+            offer32(e, top1, top2);
+        }
+    });
+    n1 = top1.idx >= 0 ? rec[top1.idx].tr_ri.y : 1.0f;
+    int hid = __float_as_int(rec[hit_idx].pa.w) & 255;
+    bool hit_is_container = (parity[hid >> 5] >> (hid & 31)) & 1u;
+    if (hit_is_container) {
+        if (top1.idx >= 0 && top1.id == hid) n2 = top2.idx >= 0 ? rec[top2.idx].tr_ri.y : 1.0f;
+        else n2 = top1.idx >= 0 ? rec[top1.idx].tr_ri.y : 1.0f;
+    } else {
+        n2 = rec[hit_idx].tr_ri.y;
+    }
+}
+
+// The same, from the negative entries phase A kept for this ray (intersect32<true>) plus the planes.
+__device__ __noinline__ void compute_refractive32_kept(const Streams32& S, const ShadeRec32* rec, F3 o, F3 d, int hit_idx,
+                                                       const float2* neg, int n_neg, float& n1, float& n2) {
+    unsigned parity[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) parity[k] = 0u;
+    auto for_each = [&](auto f) {
+        for (int i = 0; i < S.np; ++i) {
+            float4 pl = S.planes[i];
+            float t = -row4(pl, o) * rcp(row3(pl, d));
+            if (t < 0.f) f(t, S.pl_index[i], 0);
+        }
+        for (int k = 0; k < n_neg; ++k) {
+            const float2 e = neg[k];
+            const int code = __float_as_int(e.y);
+            f(e.x, stream_to_shape(S, code >> 1), code & 1);
+        }
+    };
+    for_each([&](float, int idx, int) {
+        int id = __float_as_int(rec[idx].pa.w) & 255;
+        parity[id >> 5] ^= 1u << (id & 31);
+    });
+    Cont32 top1, top2;
+    top1.idx = -1; top2.idx = -1; top1.t = top2.t = 0.f; top1.ord = top2.ord = 0; top1.id = top2.id = -1;
+    for_each([&](float t, int idx, int root) {
         int id = __float_as_int(rec[idx].pa.w) & 255;
         if ((parity[id >> 5] >> (id & 31)) & 1u) {
             Cont32 e; e.t = t; e.ord = 2 * idx + root; e.idx = idx; e.id = id;
@@ -414,6 +468,8 @@ render_f32_kernel(DevScene32 sc, CamParams cam, void* __restrict__ out_rgb, uint
     float4 stk_a[kMaxStack], stk_b[kMaxStack];  // pending refraction rays: (o, w), (d, remaining)
     int sp = 0;
     unsigned n_rays = 0, n_shaded = 0, n_phits = 0;
+    float2 neg[kUnique ? 1 : kNegCap];   // negative-t entries of the current ray (aliased world_ids only)
+    int n_neg = 0;
 
     for (;;) {
         // ---------------------------------------------------------------- refill lanes without a ray
@@ -488,7 +544,7 @@ render_f32_kernel(DevScene32 sc, CamParams cam, void* __restrict__ out_rgb, uint
         // ---------------------------------------------------------------- phase A: World::intersect, radiance rays
         float t = __int_as_float(0x7f800000);
         int hit = -1;
-        if (has_ray) { intersect32(S, ro, rd, t, hit); ++n_rays; }
+        if (has_ray) { intersect32<!kUnique>(S, ro, rd, t, hit, neg, n_neg); ++n_rays; }
         if (has_ray && is_primary && hit >= 0) { hitbits |= 1u << sub; ++n_phits; }
         if (hit < 0) has_ray = false;   // World::color_at -> background_color (black), src/shape.rs:708
 
@@ -512,7 +568,8 @@ render_f32_kernel(DevScene32 sc, CamParams cam, void* __restrict__ out_rgb, uint
             if (tr.x != 0.f) {                                    // Intersection::compute_refractive
                 if (kUnique && n_gset <= 16 && !origin_in_gset(S, gset, n_gset, ro, rd)) { hn1 = 1.f; hn2 = tr.y; }
                 else if (kUnique) compute_refractive32_unique(S, R, ro, rd, hidx, hn1, hn2);
-                else compute_refractive32(S, R, ro, rd, hidx, hn1, hn2);
+                else if (n_neg <= kNegCap) compute_refractive32_kept(S, R, ro, rd, hidx, neg, n_neg, hn1, hn2);
+                else compute_refractive32(S, R, ro, rd, hidx, hn1, hn2);   // more entries than were kept: the two passes
             }
             if (dot(hn, rd) > 0.f) hn = mk(-hn.x, -hn.y, -hn.z);  // inside: normal . eyev < 0 (src/shape.rs:77-78)
             hp = fma3(hn, kEps32, p);                             // over_point
