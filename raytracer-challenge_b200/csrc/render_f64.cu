@@ -82,13 +82,25 @@ __device__ __forceinline__ bool plane_root(const double2* r, V3 o, V3 d, double&
 __device__ __forceinline__ void take(double t, int idx, double& best_t, int& best_idx) {
     if (t >= 0.0 && (t < best_t || (t == best_t && idx < best_idx))) { best_t = t; best_idx = idx; }
 }
-__device__ __noinline__ void intersect_world(const Streams& S, V3 o, V3 d, double& best_t, int& best_idx) {
+// kCollect (radiance rays): the list entries with t < 0 that the loops come across are kept in `neg`
+// (t, 2 * shape index + root): they are all Intersection::compute_refractive looks at, so a transparent
+// hit needs no further pass over the shapes.  n_neg counts all of them; beyond kNegCap they are dropped
+// and compute_refractive falls back to its two passes.
+struct Neg { double t; int ord; int pad; };
+constexpr int kNegCap = 48;
+template <bool kCollect>
+__device__ __noinline__ void intersect_world(const Streams& S, V3 o, V3 d, double& best_t, int& best_idx, Neg* neg, int& n_neg) {
     best_t = __longlong_as_double(0x7ff0000000000000LL);
     best_idx = 0x7fffffff;
+    if (kCollect) n_neg = 0;
+    auto keep = [&](double t, int ord) { if (n_neg < kNegCap) { neg[n_neg].t = t; neg[n_neg].ord = ord; } ++n_neg; };
 #pragma unroll kUnroll
     for (int i = 0; i < S.np; ++i) {
         double t;
-        if (plane_root(S.pl + 2 * i, o, d, t)) take(t, S.pl_index[i], best_t, best_idx);
+        if (plane_root(S.pl + 2 * i, o, d, t)) {
+            take(t, S.pl_index[i], best_t, best_idx);
+            if (kCollect && t < 0.0) keep(t, 2 * S.pl_index[i]);
+        }
     }
 #pragma unroll kUnroll
     for (int i = 0; i < S.ns; ++i) {
@@ -96,7 +108,10 @@ __device__ __noinline__ void intersect_world(const Streams& S, V3 o, V3 d, doubl
         if (sphere_roots(S.sph + 6 * i, o, d, t1, t2)) {
             int idx = S.sph_index[i];
             if (t1 >= 0.0) take(t1, idx, best_t, best_idx);
-            else take(t2, idx, best_t, best_idx);
+            else {
+                take(t2, idx, best_t, best_idx);
+                if (kCollect) { if (t1 < 0.0) keep(t1, 2 * idx); if (t2 < 0.0) keep(t2, 2 * idx + 1); }
+            }
         }
     }
     if (best_idx == 0x7fffffff) best_idx = -1;
@@ -161,6 +176,33 @@ __device__ __noinline__ void compute_refractive(const Streams& S, const DevScene
                 if (t2 < 0.0) { Cont e; e.t = t2; e.ord = 2 * idx + 1; e.idx = idx; e.id = id; offer(e, top1, top2); }
             }
         }
+    }
+    n1 = top1.idx >= 0 ? sc.rec[top1.idx].refractive_index : 1.0;
+    int hid = sc.rec[hit_idx].world_id & 255;
+    bool hit_is_container = (parity[hid >> 5] >> (hid & 31)) & 1u;
+    if (hit_is_container) {
+        if (top1.idx >= 0 && top1.id == hid) n2 = top2.idx >= 0 ? sc.rec[top2.idx].refractive_index : 1.0;
+        else n2 = top1.idx >= 0 ? sc.rec[top1.idx].refractive_index : 1.0;
+    } else {
+        n2 = sc.rec[hit_idx].refractive_index;
+    }
+}
+
+// The same from the entries intersect_world<true> kept for this ray.
+__device__ __noinline__ void compute_refractive_kept(const DevScene64& sc, int hit_idx, const Neg* neg, int n_neg, double& n1, double& n2) {
+    unsigned parity[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) parity[k] = 0u;
+    for (int k = 0; k < n_neg; ++k) {
+        int id = sc.rec[neg[k].ord >> 1].world_id & 255;
+        parity[id >> 5] ^= 1u << (id & 31);
+    }
+    Cont top1, top2;
+    top1.idx = -1; top2.idx = -1; top1.t = top2.t = 0.0; top1.ord = top2.ord = 0; top1.id = top2.id = -1;
+    for (int k = 0; k < n_neg; ++k) {
+        const int idx = neg[k].ord >> 1;
+        const int id = sc.rec[idx].world_id & 255;
+        if ((parity[id >> 5] >> (id & 31)) & 1u) { Cont e; e.t = neg[k].t; e.ord = neg[k].ord; e.idx = idx; e.id = id; offer(e, top1, top2); }
     }
     n1 = top1.idx >= 0 ? sc.rec[top1.idx].refractive_index : 1.0;
     int hid = sc.rec[hit_idx].world_id & 255;
@@ -285,6 +327,8 @@ render_f64_kernel(DevScene64 sc, CamParams cam, double* __restrict__ out_f64, fl
         const V3 light_pos = mk(sc.light_pos[0], sc.light_pos[1], sc.light_pos[2]);
         const V3 light_int = mk(sc.light_int[0], sc.light_int[1], sc.light_int[2]);
         Frame stack[RTC_MAX_DEPTH];
+        Neg kept[kNegCap];   // negative-t entries of the current radiance ray
+        int n_neg = 0, n_shadow_neg = 0;
         int level = 0;
         int remaining = cam.max_depth;
         bool first = true;
@@ -294,7 +338,7 @@ render_f64_kernel(DevScene64 sc, CamParams cam, double* __restrict__ out_f64, fl
             bool descended = false;
             double t; int idx;
             ++n_rays;
-            intersect_world(S, ro, rd, t, idx);
+            intersect_world<true>(S, ro, rd, t, idx, kept, n_neg);
             if (first) { primary_hit = idx >= 0; first = false; }
             if (idx < 0) {
                 color = mk(0., 0., 0.);  // background_color, src/shape.rs:652
@@ -307,7 +351,10 @@ render_f64_kernel(DevScene64 sc, CamParams cam, double* __restrict__ out_f64, fl
                 V3 ln = rec.kind == RTC_SHAPE_PLANE ? mk(0., 1., 0.) : lp;
                 V3 normal = normalize(xvec3(rec.invt, ln));
                 double n1 = 1.0, n2 = 1.0;
-                if (rec.transparency != 0.0) compute_refractive(S, sc, ro, rd, idx, n1, n2);
+                if (rec.transparency != 0.0) {
+                    if (n_neg <= kNegCap) compute_refractive_kept(sc, idx, kept, n_neg, n1, n2);
+                    else compute_refractive(S, sc, ro, rd, idx, n1, n2);   // more entries than were kept: the two passes
+                }
                 bool inside = dot(normal, eyev) < 0.0;
                 if (inside) normal = neg(normal);
                 V3 over_point = add(point, mul(normal, kEps));
@@ -319,7 +366,7 @@ render_f64_kernel(DevScene64 sc, CamParams cam, double* __restrict__ out_f64, fl
                 V3 sdir = normalize(v);
                 double st; int sidx;
                 ++n_rays; ++n_shadow; ++n_shaded;
-                intersect_world(S, over_point, sdir, st, sidx);
+                intersect_world<false>(S, over_point, sdir, st, sidx, kept, n_shadow_neg);
                 bool shadowed = sidx >= 0 && st < distance;
                 V3 surface = lighting(rec, light_pos, light_int, over_point, eyev, normal, shadowed);
                 // shade_hit's children (src/shape.rs:689-699, 729-766)
