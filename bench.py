@@ -371,7 +371,11 @@ def run_gpu(args):
                     "d2h_bytes_per_step": int(d2h), "steps": e2e_steps,
                     "path": "rtc_scene_upload + rtc_render (f32 fast, F64_RGB Canvas layout) into a host buffer" if N == 1 else
                             "rtc_scene_upload + rtc_render_device shards with peer stores into rank 0's F64 Canvas frame + D2H on rank 0"},
-            "gpu_launches": args.steps,
+            # kernels of this library inside the timed region, all ranks: rank 0 runs the tile scheduling pre-pass +
+            # the render kernel (+ the flag wait when N > 1); every other rank the render kernel + its flag store
+            "gpu_launches": args.steps * (2 if N == 1 else 3 + 2 * (N - 1)),
+            "gpu_launches_per_step": {"rank0": ["classify_tiles_small_kernel", "render_f32_small_kernel"] + (["wait_kernel"] if N > 1 else []),
+                                      "other_ranks": ["render_f32_small_kernel", "signal_kernel"] if N > 1 else []},
             "clocks": clocks,
         }
         line.update(extra)
