@@ -355,9 +355,9 @@ def run_gpu(args):
                                        "completion = one peer-stored flag per rank, rank 0 waits on its stream (no collective)" if N > 1 else ""),
                        "timing": "CUDA events per step on the launch stream, max over ranks"},
             "roofline": {"bound": "fp32_non_tensor", "achieved": achieved, "peak": p32, "unit": "TFLOP/s", "frac": achieved / p32,
-                         "traffic": 61.65e6 if N == 1 else None,
+                         "traffic": 64.56e6 if N == 1 else None,
                          "traffic_note": "dram__bytes_read.sum + dram__bytes_write.sum of one 4K launch, ncu --set full capture "
-                                         "(profiles/r01_ncu_f32_small_1p47ms.txt): 61.5 MB written + 0.16 MB read; the frame is 99.5 MB, the "
+                                         "(profiles/r01_ncu_f32_small_1p25ms.txt): 63.3 MB written + 1.2 MB read; the frame is 99.5 MB, the "
                                          "rest was still in the 126 MB L2 when the kernel ended; scene reads never reach HBM",
                          "peak_source": "FFMA micro-benchmark on this GPU in this run (rtc_measure_peak_tflops)",
                          "peak_formula": FP32_FORMULA_PEAK, "frac_of_formula": achieved / FP32_FORMULA_PEAK,
