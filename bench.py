@@ -312,7 +312,7 @@ def run_gpu(args):
 
         def e2e_step():
             r.upload_flat(*flat)
-            r.render(camd, oe, want_mask=False, out=host)
+            r.render(camd, oe, want_mask=False, out=host, want_stats=False)
     else:
         pe = Path(ffi.PRECISION_F32_FAST, ffi.OUT_F64_RGB, "p2p")   # Canvas layout straight into rank 0's frame
         host_t = torch.empty((H, W, 3), dtype=torch.float64).pin_memory() if rank == 0 else None

@@ -91,17 +91,19 @@ class Renderer:
         o.shard_index, o.shard_count, o.tile_rows, o.flags = shard_index, shard_count, tile_rows, flags
         return o
 
-    def render(self, cam_desc, opts, want_mask=True, out=None):
-        """rtc_render into host numpy buffers.  Returns (rgb, hit_mask, stats)."""
+    def render(self, cam_desc, opts, want_mask=True, out=None, want_stats=True):
+        """rtc_render into host numpy buffers.  Returns (rgb, hit_mask, stats); stats is None with
+        want_stats=False (the library then launches the kernels without their work counters, as the
+        Rust shim of INTEGRATION.md does)."""
         h, w = cam_desc.vsize, cam_desc.hsize
         dt = {ffi.OUT_F64_RGB: np.float64, ffi.OUT_F32_RGB: np.float32, ffi.OUT_U8_RGB: np.uint8}[opts.out_format]
         rgb = out if out is not None else np.empty((h, w, 3), dtype=dt)
         assert rgb.dtype == dt and rgb.flags["C_CONTIGUOUS"] and rgb.size == h * w * 3
         mask = np.empty((h, w), dtype=np.uint8) if want_mask else None
-        stats = ffi.RtcStats()
+        stats = ffi.RtcStats() if want_stats else None
         ffi.check(self._lib.rtc_render(
             self._ctx, C.byref(cam_desc), C.byref(opts), rgb.ctypes.data_as(C.c_void_p),
-            mask.ctypes.data_as(C.c_void_p) if mask is not None else None, C.byref(stats)))
+            mask.ctypes.data_as(C.c_void_p) if mask is not None else None, C.byref(stats) if want_stats else None))
         return rgb, mask, stats
 
     def render_device(self, cam_desc, opts, d_rgb, d_mask=None, stream=None, stats=None):

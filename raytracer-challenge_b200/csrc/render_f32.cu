@@ -524,7 +524,7 @@ render_f32_kernel(DevScene32 sc, CamParams cam, void* __restrict__ out_rgb, uint
                 px = tx * kTileX + (k & (kTileX - 1));
                 pr = ty * kTileY + k / kTileX;
                 if (px < (int)cam.hsize && pr < cam.shard_rows) {
-                    py = cam.shard_count > 1 ? shard_row_to_frame_row(pr, cam.tile_rows, cam.shard_index, cam.shard_count) : pr;
+                    py = cam.row0 + (cam.shard_count > 1 ? shard_row_to_frame_row(pr, cam.tile_rows, cam.shard_index, cam.shard_count) : pr);
                     have = true; sub = 0; acc = mk(0, 0, 0); hitbits = 0;
                     if (!(px < (int)cam.xlim && py < (int)cam.ylim)) sub = n_sub;  // outside the rect: stays black
                 }

@@ -328,7 +328,7 @@ render_f32_small_kernel(const __grid_constant__ SmallParams P, void* __restrict_
                 px = wtx + (k & (kTileX - 1));
                 pr = wty + (k >> 3);
                 if (px < P.hsize && pr < P.shard_rows) {
-                    py = P.shard_count > 1 ? shard_row_to_frame_row(pr, P.tile_rows, P.shard_index, P.shard_count) : pr;
+                    py = P.row0 + (P.shard_count > 1 ? shard_row_to_frame_row(pr, P.tile_rows, P.shard_index, P.shard_count) : pr);
                     have = true; sub = 0; acc = mk(0.f, 0.f, 0.f); hitbits = 0;
                     if (!(px < P.xlim && py < P.ylim)) sub = n_sub;   // outside the rect: stays black
                 }
@@ -528,7 +528,7 @@ classify_tiles_small_kernel(const __grid_constant__ SmallParams P, unsigned* __r
         const int ty = t / P.tiles_x, tx = t - ty * P.tiles_x;
         const int px = min(tx * kTileX + kTileX / 2, P.hsize - 1);
         const int pr = min(ty * kTileY + kTileY / 2, P.shard_rows - 1);
-        const int py = P.shard_count > 1 ? shard_row_to_frame_row(pr, P.tile_rows, P.shard_index, P.shard_count) : pr;
+        const int py = P.row0 + (P.shard_count > 1 ? shard_row_to_frame_row(pr, P.tile_rows, P.shard_index, P.shard_count) : pr);
         const float fx = (float)px, fy = (float)py;          // the corner shared by the four centre pixels
         F3 dir = mk(fmaf(P.cam_dx[0], fx, fmaf(P.cam_dy[0], fy, P.cam_d0[0])),
                     fmaf(P.cam_dx[1], fx, fmaf(P.cam_dy[1], fy, P.cam_d0[1])),

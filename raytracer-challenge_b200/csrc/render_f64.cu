@@ -305,7 +305,7 @@ render_f64_kernel(DevScene64 sc, CamParams cam, double* __restrict__ out_f64, fl
     const int px = sx / ss, pr = sy / ss;     // pixel x, compact shard row
     const bool in_image = px < (int)cam.hsize && pr < cam.shard_rows;
     int py = 0;
-    if (in_image) py = cam.shard_count > 1 ? shard_row_to_frame_row(pr, cam.tile_rows, cam.shard_index, cam.shard_count) : pr;
+    if (in_image) py = cam.row0 + (cam.shard_count > 1 ? shard_row_to_frame_row(pr, cam.tile_rows, cam.shard_index, cam.shard_count) : pr);
     const bool active = in_image && px < (int)cam.xlim && py < (int)cam.ylim;
 
     V3 result = mk(0., 0., 0.);

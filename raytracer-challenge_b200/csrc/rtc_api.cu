@@ -18,6 +18,8 @@
 
 using namespace rtc;
 
+extern "C" void rtc_host_widen_f32_f64(double* dst, const float* src, size_t n);   // host_simd.cpp
+
 namespace {
 
 thread_local std::string g_err;
@@ -223,6 +225,7 @@ CamParams make_cam(const rtc_camera* cam, const rtc_render_opts* o, int shard_in
     c.shard_rows = shard_num_rows((int)cam->vsize, c.tile_rows, c.shard_index, c.shard_count);
     c.out_format = o->out_format;
     c.dst_full = 0;
+    c.row0 = 0;
     return c;
 }
 
@@ -529,9 +532,7 @@ void host_deliver(rtc_context* ctx, unsigned char* dst, const unsigned char* src
     auto task = [=](int i) {
         const size_t b = (size_t)i * kChunk, e = std::min(n_elems, b + kChunk);
         if (widen) {
-            const float* sp = reinterpret_cast<const float*>(src) + b;
-            double* dp = reinterpret_cast<double*>(dst) + b;
-            for (size_t k = 0; k < e - b; ++k) dp[k] = (double)sp[k];
+            rtc_host_widen_f32_f64(reinterpret_cast<double*>(dst) + b, reinterpret_cast<const float*>(src) + b, e - b);   // host_simd.cpp
         } else {
             std::memcpy(dst + b * dst_elem, src + b * src_elem, (e - b) * dst_elem);
         }
@@ -551,7 +552,7 @@ void fill_small_camera(SmallParams& P, const CamParams& cam) {
         P.cam_d0[k] = (float)(cam.half_width * v[4 * k + 0] + cam.half_height * v[4 * k + 1] - v[4 * k + 2]);
     }
     P.hsize = (int)cam.hsize; P.shard_rows = cam.shard_rows; P.xlim = (int)cam.xlim; P.ylim = (int)cam.ylim;
-    P.shard_index = cam.shard_index; P.shard_count = cam.shard_count; P.tile_rows = cam.tile_rows; P.dst_full = cam.dst_full;
+    P.shard_index = cam.shard_index; P.shard_count = cam.shard_count; P.tile_rows = cam.tile_rows; P.dst_full = cam.dst_full; P.row0 = cam.row0;
     P.n_sub = cam.samples == 1 ? 1 : 4;
     P.max_depth = cam.max_depth;
     P.tiles_x = ((int)cam.hsize + 7) / 8;
@@ -876,25 +877,47 @@ extern "C" int rtc_render(rtc_context* ctx, const rtc_camera* cam, const rtc_ren
     unsigned char* user = (unsigned char*)out_rgb;
 
     if (G == 1) {
-        // One GPU: the frame is rendered as up to 8 contiguous row bands (band b = shard b of B with
-        // tile_rows = ceil(vsize / B), written at frame positions).  Band b's D2H runs on the copy
-        // stream while band b+1 renders, and the host delivers band b while band b+1 crosses PCIe.
+        // One GPU: the frame is rendered as up to 8 contiguous row bands (one launch each, rows
+        // [row0, row0 + rows) written at their frame positions).  Band b's D2H runs on the copy stream
+        // while band b+1 renders, and the host delivers band b while band b+1 crosses PCIe.
+        //  * fast mode is copy- and delivery-bound (99.5 MB at ~56 GB/s and a ~1.8 ms host widening against a
+        //    1.25 ms kernel): eight equal bands keep all three stages busy (measured 2.5 ms; small-large-small
+        //    bands 3.2 ms, because a large band is delivered only after its whole copy);
+        //  * parity mode is kernel-bound: few large bands first (every launch has its own tail), and what is
+        //    left after the last kernel is the copy and delivery of a sixteenth of the frame.
         DeviceState& d = ctx->devs[0];
         CUDA_TRY(cudaSetDevice(d.dev));
-        const int B = frame_bytes >= (32u << 20) ? 8 : (frame_bytes >= (4u << 20) ? 4 : 1);
-        const int band_rows = ((int)cam->vsize + B - 1) / B;
+        static const int kPlanEq8[] = {1, 1, 1, 1, 1, 1, 1, 1}, kPlanF64[] = {6, 5, 3, 1, 1}, kPlanMid[] = {1, 2, 1}, kPlanOne[] = {1};
+        const int* plan = kPlanOne; int n_plan = 1, plan_sum = 1;
+        if (frame_bytes >= (32u << 20)) {
+            if (opts->precision == RTC_PRECISION_F64_PARITY) { plan = kPlanF64; n_plan = 5; plan_sum = 16; }
+            else { plan = kPlanEq8; n_plan = 8; plan_sum = 8; }
+        } else if (frame_bytes >= (4u << 20)) { plan = kPlanMid; n_plan = 3; plan_sum = 4; }
+        if (const char* env = std::getenv("RTC_B200_BANDS")) {   // experiments: N equal bands
+            static int eq[8] = {1, 1, 1, 1, 1, 1, 1, 1};
+            plan = eq; n_plan = std::max(1, std::min(8, std::atoi(env))); plan_sum = n_plan;
+        }
+        int band_r0[9];
+        int n_bands = 0;
+        {
+            int acc = 0, prev = 0;
+            for (int b = 0; b < n_plan; ++b) {
+                acc += plan[b];
+                int r = b + 1 == n_plan ? (int)cam->vsize : (int)((long long)cam->vsize * acc / plan_sum) / 4 * 4;   // whole 8x4 tiles
+                if (r > prev) { band_r0[n_bands++] = prev; prev = r; }
+            }
+            band_r0[n_bands] = (int)cam->vsize;
+        }
         CUDA_TRY(d.rgb.ensure(frame_bytes));
         if (out_hit_mask) CUDA_TRY(d.hit.ensure(mask_bytes));
         CUDA_TRY(cudaMemsetAsync(d.counters.p, 0, sizeof(Counters), d.stream));
         CUDA_TRY(cudaEventRecord(d.ev_k0, d.stream));
-        int n_bands = 0;
-        for (int b = 0; b < B; ++b) {
-            const int r0 = b * band_rows, r1 = std::min((int)cam->vsize, r0 + band_rows);
-            if (r0 >= r1) break;
-            ++n_bands;
-            CamParams cp = make_cam(cam, &dopts, b, B, band_rows);
-            cp.dst_full = 1;
-            rc = launch_on(d, cp, opts->precision, opts->flags, d.rgb.p, out_hit_mask ? d.hit.p : nullptr, d.counters.p, d.stream);
+        for (int b = 0; b < n_bands; ++b) {
+            const int r0 = band_r0[b], r1 = band_r0[b + 1];
+            CamParams cp = make_cam(cam, &dopts, 0, 1, 16);
+            cp.dst_full = 1; cp.row0 = r0; cp.shard_rows = r1 - r0;
+            // work counters only when the caller asked for stats: the plain kernel instantiation carries no book-keeping
+            rc = launch_on(d, cp, opts->precision, opts->flags, d.rgb.p, out_hit_mask ? d.hit.p : nullptr, stats ? d.counters.p : nullptr, d.stream);
             if (rc != RTC_OK) return rc;
             CUDA_TRY(cudaEventRecord(d.ev_band[b], d.stream));
             CUDA_TRY(cudaStreamWaitEvent(d.copy_stream, d.ev_band[b], 0));
@@ -909,7 +932,7 @@ extern "C" int rtc_render(rtc_context* ctx, const rtc_camera* cam, const rtc_ren
         CUDA_TRY(cudaMemcpyAsync(&ctx->pinned_counters[0], d.counters.p, sizeof(Counters), cudaMemcpyDeviceToHost, d.stream));
         double deliver_ms = 0.0;
         for (int b = 0; b < n_bands; ++b) {
-            const int r0 = b * band_rows, r1 = std::min((int)cam->vsize, r0 + band_rows);
+            const int r0 = band_r0[b], r1 = band_r0[b + 1];
             CUDA_TRY(cudaEventSynchronize(d.ev_copy[b]));
             auto h0 = std::chrono::steady_clock::now();
             host_deliver(ctx, user + (size_t)r0 * row_elems * out_elem, ctx->pinned_rgb + (size_t)r0 * row_bytes, (size_t)(r1 - r0) * row_elems, dev_elem, out_elem);

@@ -118,6 +118,7 @@ struct SmallParams {
     int hsize, shard_rows, xlim, ylim;
     int shard_index, shard_count, tile_rows, dst_full;
     int n_sub, max_depth, tiles_x, total_tiles;
+    int row0, pad1;                    // first frame row of the launch (row bands of rtc_render)
 };
 
 // ---- per-launch parameters --------------------------------------------------------------------
@@ -133,6 +134,7 @@ struct CamParams {
     int32_t shard_rows;   // rows in this shard's compact buffer
     int32_t out_format;   // RTC_OUT_*
     int32_t dst_full;     // 1: the destination is a full frame (rows at their frame positions), not the compact shard buffer
+    int32_t row0;         // first frame row of this launch (rtc_render's row bands: shard_count == 1, rows [row0, row0 + shard_rows))
 };
 
 struct Counters {
