@@ -158,6 +158,8 @@ def run_gpu(args):
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
     if N > 1:
+        # stdout carries exactly one JSON line: NCCL's own messages (e.g. its version banner under NCCL_DEBUG) go to stderr
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
         dist.init_process_group("nccl", device_id=dev)
     r = rtc.Renderer([local_rank])
     world = rtc.scenes.reflect_refract_scene()
