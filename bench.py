@@ -158,9 +158,21 @@ def run_gpu(args):
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
     if N > 1:
-        # stdout carries exactly one JSON line: NCCL's own messages (e.g. its version banner under NCCL_DEBUG) go to stderr
-        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
-        dist.init_process_group("nccl", device_id=dev)
+        # stdout carries exactly one JSON line: whatever NCCL prints while its communicators come up (the version
+        # banner under NCCL_DEBUG) is sent to stderr by pointing fd 1 at fd 2 until the first collective is done
+        sys.stdout.flush()
+        saved_stdout = os.dup(1)
+        os.dup2(2, 1)
+        try:
+            dist.init_process_group("nccl", device_id=dev)
+            warm = torch.zeros(1, device=dev)
+            dist.all_reduce(warm)
+            dist.barrier()
+            torch.cuda.synchronize()
+        finally:
+            sys.stdout.flush()
+            os.dup2(saved_stdout, 1)
+            os.close(saved_stdout)
     r = rtc.Renderer([local_rank])
     world = rtc.scenes.reflect_refract_scene()
     cam = rtc.scenes.reflect_refract_camera(W, H)
@@ -316,14 +328,15 @@ def run_gpu(args):
             r.upload_flat(*flat)
             r.render(camd, oe, want_mask=False, out=host, want_stats=False)
     else:
-        pe = Path(ffi.PRECISION_F32_FAST, ffi.OUT_F64_RGB, "p2p")   # Canvas layout straight into rank 0's frame
-        host_t = torch.empty((H, W, 3), dtype=torch.float64).pin_memory() if rank == 0 else None
+        d2h = H * W * 3 * 4   # as at N = 1: the frame crosses PCIe as f32 and is widened into the f64 Canvas layout on the host
+        pe = Path(ffi.PRECISION_F32_FAST, ffi.OUT_F32_RGB, "p2p")   # every rank's pixels straight into rank 0's f32 frame
+        host = np.zeros((H, W, 3), dtype=np.float64) if rank == 0 else None
 
         def e2e_step():
             r.upload_flat(*flat)
             pe.frame()
-            if rank == 0:
-                host_t.copy_(pe.sf.frame, non_blocking=True)
+            if rank == 0:   # rtc_download_frame: banded D2H behind the completion flags + host delivery
+                r.download_frame(pe.sf.frame.data_ptr(), ffi.OUT_F32_RGB, W, H, host, stream)
             torch.cuda.synchronize()
     for _ in range(2):
         e2e_step()
@@ -372,7 +385,7 @@ def run_gpu(args):
             "e2e": {"value": rays / (e2e_ms * 1e-3) / 1e6, "unit": "Mrays/s", "ms_per_frame": e2e_ms, "h2d_bytes_per_step": int(h2d),
                     "d2h_bytes_per_step": int(d2h), "steps": e2e_steps,
                     "path": "rtc_scene_upload + rtc_render (f32 fast, F64_RGB Canvas layout) into a host buffer" if N == 1 else
-                            "rtc_scene_upload + rtc_render_device shards with peer stores into rank 0's F64 Canvas frame + D2H on rank 0"},
+                            "rtc_scene_upload + rtc_render_device shards with peer stores into rank 0's frame + rtc_download_frame (f32 over PCIe, widened into the f64 Canvas layout) on rank 0"},
             # kernels of this library inside the timed region, all ranks: rank 0 runs the tile scheduling pre-pass +
             # the render kernel (+ the flag wait when N > 1); every other rank the render kernel + its flag store
             "gpu_launches": args.steps * (2 if N == 1 else 3 + 2 * (N - 1)),

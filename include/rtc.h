@@ -228,6 +228,16 @@ int rtc_ipc_close(rtc_context* ctx, void* d_ptr, uint64_t offset);
 int rtc_signal_device(rtc_context* ctx, void* d_flag, uint32_t value, void* stream);
 int rtc_wait_device(rtc_context* ctx, const void* d_flags, int n, uint32_t value, void* stream);
 
+/* Canvas delivery for the device-buffer entry points: copies a finished frame (hsize*vsize pixels of
+ * `dev_format`, on the context's first GPU) into the caller's HOST buffer of `out_format`, after everything
+ * already enqueued on `stream` (NULL = the context's stream).  Row bands cross PCIe on the copy stream while
+ * the host delivers the previous band; dev_format F32_RGB with out_format F64_RGB widens on the host (exact),
+ * which halves the PCIe bytes of a fast-mode frame.  This is the step between rank 0's assembled frame
+ * (rtc_render_device + peer stores / rtc_assemble_device) and Canvas.pixels (src/canvas.rs:17-22).
+ * Supported: dev_format == out_format, or F32 -> F64.  Returns when out_rgb is complete. */
+int rtc_download_frame(rtc_context* ctx, const void* d_frame, int dev_format, uint32_t hsize, uint32_t vsize,
+                       int out_format, void* out_rgb, void* stream);
+
 /* Register-resident FMA micro-benchmark on the context's first GPU: measured non-tensor peak
  * of the FP32 (precision = RTC_PRECISION_F32_FAST) or FP64 pipe in TFLOP/s (FMA = 2 flops),
  * used as the roofline denominator beside the formula peak. */

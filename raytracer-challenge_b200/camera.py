@@ -118,6 +118,15 @@ class Renderer:
             self._ctx, C.byref(cam_desc), C.byref(opts), C.c_void_p(d_gathered), shard_stride_rows,
             elem_kind, C.c_void_p(d_frame), C.c_void_p(stream) if stream else None))
 
+    def download_frame(self, d_frame, dev_format, hsize, vsize, out, stream=None):
+        """rtc_download_frame: a finished device frame into the host numpy array `out` (same format, or
+        f32 -> f64 widening), after the work already enqueued on `stream`."""
+        fmt = {np.dtype(np.float64): ffi.OUT_F64_RGB, np.dtype(np.float32): ffi.OUT_F32_RGB, np.dtype(np.uint8): ffi.OUT_U8_RGB}[out.dtype]
+        assert out.flags["C_CONTIGUOUS"] and out.size == hsize * vsize * 3
+        ffi.check(self._lib.rtc_download_frame(self._ctx, C.c_void_p(d_frame), dev_format, hsize, vsize, fmt,
+                                               out.ctypes.data_as(C.c_void_p), C.c_void_p(stream) if stream else None))
+        return out
+
     def ipc_export(self, d_ptr):
         """-> (handle bytes, offset) for the allocation containing device pointer d_ptr."""
         h = (C.c_ubyte * ffi.IPC_HANDLE_BYTES)()

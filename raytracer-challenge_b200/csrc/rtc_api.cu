@@ -848,6 +848,42 @@ int rtc_measure_peak_tflops(rtc_context* ctx, int precision, double* out_tflops)
 }  // extern "C"
 
 // ---- rtc_render: host buffers in, host buffers out ------------------------------------------------
+extern "C" int rtc_download_frame(rtc_context* ctx, const void* d_frame, int dev_format, uint32_t hsize, uint32_t vsize,
+                                  int out_format, void* out_rgb, void* stream) {
+    if (!ctx || !d_frame || !out_rgb || hsize == 0 || vsize == 0) return fail(RTC_ERR_INVALID_ARG, "rtc_download_frame: null argument");
+    if (dev_format < RTC_OUT_F64_RGB || dev_format > RTC_OUT_U8_RGB || out_format < RTC_OUT_F64_RGB || out_format > RTC_OUT_U8_RGB)
+        return fail(RTC_ERR_INVALID_ARG, "rtc_download_frame: bad format");
+    if (dev_format != out_format && !(dev_format == RTC_OUT_F32_RGB && out_format == RTC_OUT_F64_RGB))
+        return fail(RTC_ERR_UNSUPPORTED, "rtc_download_frame: only equal formats or F32 -> F64");
+    DeviceState& d = ctx->devs[0];
+    CUDA_TRY(cudaSetDevice(d.dev));
+    const size_t dev_elem = elem_size(dev_format), out_elem = elem_size(out_format);
+    const size_t row_elems = (size_t)hsize * 3, row_bytes = row_elems * dev_elem, frame_bytes = row_bytes * vsize;
+    int rc = ensure_pinned(&ctx->pinned_rgb, &ctx->pinned_rgb_cap, frame_bytes);
+    if (rc != RTC_OK) return rc;
+    cudaStream_t src_stream = stream ? (cudaStream_t)stream : d.stream;
+    const int B = frame_bytes >= (32u << 20) ? 8 : (frame_bytes >= (4u << 20) ? 4 : 1);
+    const int band_rows = ((int)vsize + B - 1) / B;
+    CUDA_TRY(cudaEventRecord(d.ev_band[0], src_stream));
+    CUDA_TRY(cudaStreamWaitEvent(d.copy_stream, d.ev_band[0], 0));
+    int n_bands = 0;
+    for (int b = 0; b < B; ++b) {
+        const int r0 = b * band_rows, r1 = std::min((int)vsize, r0 + band_rows);
+        if (r0 >= r1) break;
+        ++n_bands;
+        CUDA_TRY(cudaMemcpyAsync(ctx->pinned_rgb + (size_t)r0 * row_bytes, (const unsigned char*)d_frame + (size_t)r0 * row_bytes,
+                                 (size_t)(r1 - r0) * row_bytes, cudaMemcpyDeviceToHost, d.copy_stream));
+        CUDA_TRY(cudaEventRecord(d.ev_copy[b], d.copy_stream));
+    }
+    for (int b = 0; b < n_bands; ++b) {
+        const int r0 = b * band_rows, r1 = std::min((int)vsize, r0 + band_rows);
+        CUDA_TRY(cudaEventSynchronize(d.ev_copy[b]));
+        host_deliver(ctx, (unsigned char*)out_rgb + (size_t)r0 * row_elems * out_elem, ctx->pinned_rgb + (size_t)r0 * row_bytes,
+                     (size_t)(r1 - r0) * row_elems, dev_elem, out_elem);
+    }
+    return RTC_OK;
+}
+
 extern "C" int rtc_render(rtc_context* ctx, const rtc_camera* cam, const rtc_render_opts* opts, void* out_rgb,
                           uint8_t* out_hit_mask, rtc_stats* stats) {
     if (!ctx || !out_rgb) return fail(RTC_ERR_INVALID_ARG, "rtc_render: null argument");

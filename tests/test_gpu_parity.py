@@ -281,6 +281,26 @@ def test_f32_light_inside_sphere_takes_general_kernel(rtc, orc, renderer):
     _check32(rtc, orc, renderer, w, cam, min_ok=0.99, ray_tol=0.01)
 
 
+def test_download_frame_matches_rtc_render(rtc, orc, renderer):
+    """rtc_download_frame (device frame -> host Canvas buffer, f32 -> f64 widening on the host) delivers
+    exactly what rtc_render delivers for the same options."""
+    import torch
+    world = rtc.scenes.reflect_refract_scene()
+    cam = rtc.scenes.reflect_refract_camera(1280, 720)      # > 4 MB: several bands
+    renderer.upload(world)
+    d = cam.flatten()
+    f = rtc.ffi
+    want, _, _ = renderer.render(d, rtc.Renderer.make_opts(precision=f.PRECISION_F32_FAST, out_format=f.OUT_F64_RGB))
+    dev = torch.empty((720, 1280, 3), dtype=torch.float32, device="cuda")
+    renderer.render_device(d, rtc.Renderer.make_opts(precision=f.PRECISION_F32_FAST, out_format=f.OUT_F32_RGB), dev.data_ptr())
+    got64 = renderer.download_frame(dev.data_ptr(), f.OUT_F32_RGB, 1280, 720, np.empty((720, 1280, 3), np.float64))
+    got32 = renderer.download_frame(dev.data_ptr(), f.OUT_F32_RGB, 1280, 720, np.empty((720, 1280, 3), np.float32))
+    assert np.array_equal(got64, want)
+    assert np.array_equal(got32.astype(np.float64), want)
+    with pytest.raises(rtc.ffi.RtcError):
+        renderer.download_frame(dev.data_ptr(), f.OUT_F32_RGB, 1280, 720, np.empty((720, 1280, 3), np.uint8))
+
+
 def test_f32_reference_rect_and_formats(rtc, orc, renderer):
     world = rtc.scenes.reflect_refract_scene()
     cam = rtc.scenes.reflect_refract_camera(96, 48)
