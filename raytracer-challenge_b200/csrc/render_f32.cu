@@ -46,8 +46,24 @@ __device__ __forceinline__ float row3(float4 r, F3 p) { return fmaf(r.z, p.z, fm
 struct Streams32 {
     const float4* planes; const int32_t* pl_index; int np;
     const float4* usph;   const int32_t* us_index; int nu;
-    const float4* gsph;   const int32_t* gs_index; int ng;
+    const float4* gsph;   const int32_t* gs_index; int ng;   // general spheres [0, ng), then cubes [ng, ng + nc): 3 inverse rows each
+    int nc;
 };
+
+// Cube::intersect_local (src/shape.rs:540-591) in object space: slab test per axis.  A zero direction
+// component gives +-inf (or NaN for a ray in a face plane, which fminf / fmaxf skip, like f64::max / min).
+__device__ __forceinline__ bool cube_slab32(const float4* r, F3 o, F3 d, float& tmin, float& tmax) {
+    const float4 r0 = r[0], r1 = r[1], r2 = r[2];
+    const F3 lo = mk(row4(r0, o), row4(r1, o), row4(r2, o));
+    const F3 ld = mk(row3(r0, d), row3(r1, d), row3(r2, d));
+    const float ix = rcp(ld.x), iy = rcp(ld.y), iz = rcp(ld.z);
+    const float x0 = (-1.f - lo.x) * ix, x1 = (1.f - lo.x) * ix;
+    const float y0 = (-1.f - lo.y) * iy, y1 = (1.f - lo.y) * iy;
+    const float z0 = (-1.f - lo.z) * iz, z1 = (1.f - lo.z) * iz;
+    tmin = fmaxf(fminf(x0, x1), fmaxf(fminf(y0, y1), fminf(z0, z1)));
+    tmax = fminf(fmaxf(x0, x1), fminf(fmaxf(y0, y1), fmaxf(z0, z1)));
+    return tmin < tmax;
+}
 
 // World::intersect + get_hit for one ray: nearest t in [0, best_t).  best_t comes in as the
 // upper bound (+inf for radiance rays, 1 for shadow rays whose direction is light - point, which
@@ -104,6 +120,14 @@ __device__ __forceinline__ void intersect32(const Streams32& S, F3 o, F3 d, floa
         float t = t1 >= 0.f ? t1 : t2;
         if (dn >= 0.f && t >= 0.f && t < best_t) { best_t = t; hit = S.np + S.nu + i; }
         if (kCollect && dn >= 0.f && t1 < 0.f) { keep(t1, 2 * (S.np + S.nu + i)); if (t2 < 0.f) keep(t2, 2 * (S.np + S.nu + i) + 1); }
+    }
+    for (int i = S.ng; i < S.ng + S.nc; ++i) {           // Cube
+        float t1, t2;
+        if (cube_slab32(S.gsph + 3 * i, o, d, t1, t2)) {
+            float t = t1 >= 0.f ? t1 : t2;
+            if (t >= 0.f && t < best_t) { best_t = t; hit = S.np + S.nu + i; }
+            if (kCollect && t1 < 0.f) { keep(t1, 2 * (S.np + S.nu + i)); if (t2 < 0.f) keep(t2, 2 * (S.np + S.nu + i) + 1); }
+        }
     }
 }
 
@@ -163,6 +187,13 @@ __device__ __forceinline__ void for_each_negative(const Streams32& S, F3 o, F3 d
         if (disc >= 0.f) {
             float s = sqrtf(disc), inv = rcp(la);
             float t1 = (-b - s) * inv, t2 = (s - b) * inv;
+            if (t1 < 0.f) f(t1, S.gs_index[i], 0, !(t2 < 0.f));
+            if (t2 < 0.f) f(t2, S.gs_index[i], 1, false);
+        }
+    }
+    for (int i = S.ng; i < S.ng + S.nc; ++i) {
+        float t1, t2;
+        if (cube_slab32(S.gsph + 3 * i, o, d, t1, t2)) {
             if (t1 < 0.f) f(t1, S.gs_index[i], 0, !(t2 < 0.f));
             if (t2 < 0.f) f(t2, S.gs_index[i], 1, false);
         }
@@ -312,6 +343,13 @@ __device__ __forceinline__ bool shadow32(const Streams32& S, const float* __rest
             }
         }
     }
+    for (int i = S.ng; i < S.ng + S.nc; ++i) {   // cubes: nearest non-negative root below 1
+        float t1, t2;
+        if (cube_slab32(S.gsph + 3 * i, o, d, t1, t2)) {
+            float t = t1 >= 0.f ? t1 : t2;
+            hit |= t >= 0.f && t < 1.f;
+        }
+    }
     return hit;
 }
 
@@ -330,10 +368,13 @@ __device__ __forceinline__ bool origin_in_gset(const Streams32& S, const int32_t
             float4 sp = S.usph[pos - S.np];
             F3 L = mk(o.x - sp.x, o.y - sp.y, o.z - sp.z);
             any |= fmaf(L.z, L.z, fmaf(L.y, L.y, fmaf(L.x, L.x, -sp.w))) < 0.f;                      // origin inside
-        } else {
+        } else if (pos < S.np + S.nu + S.ng) {
             const float4* r = S.gsph + 3 * (pos - S.np - S.nu);
             F3 lo = mk(row4(r[0], o), row4(r[1], o), row4(r[2], o));
             any |= dot(lo, lo) < 1.f;
+        } else {                                                                                       // cube: one negative entry
+            float t1, t2;
+            any |= cube_slab32(S.gsph + 3 * (pos - S.np - S.nu), o, d, t1, t2) && t1 < 0.f && !(t2 < 0.f);
         }
     }
     return any;
@@ -378,6 +419,11 @@ __device__ __noinline__ void compute_refractive32_unique(const Streams32& S, con
             offer((-b - sqrtf(fmaf(b, b, -la * c))) * rcp(la), S.gs_index[i]);
         }
     }
+#pragma unroll 1
+    for (int i = S.ng; i < S.ng + S.nc; ++i) {  // a cube is a container iff exactly one of its two entries is negative
+        float t1, t2;
+        if (cube_slab32(S.gsph + 3 * i, o, d, t1, t2) && t1 < 0.f && !(t2 < 0.f)) offer(t1, S.gs_index[i]);
+    }
     n1 = i1st >= 0 ? rec[i1st].tr_ri.y : 1.0f;
     if (i1st == hit_idx) n2 = i2nd >= 0 ? rec[i2nd].tr_ri.y : 1.0f;
     else if (hit_is_container) n2 = i1st >= 0 ? rec[i1st].tr_ri.y : 1.0f;
@@ -396,7 +442,8 @@ render_f32_kernel(DevScene32 sc, CamParams cam, void* __restrict__ out_rgb, uint
                   Counters* __restrict__ counters, unsigned* __restrict__ work) {
     extern __shared__ float4 smem4[];
     Streams32 S;
-    S.np = sc.n_planes; S.nu = sc.n_usph; S.ng = sc.n_gsph;
+    S.np = sc.n_planes; S.nu = sc.n_usph; S.ng = sc.n_gsph; S.nc = sc.n_cube;
+    const int n_obj = sc.n_gsph + sc.n_cube;   // object-space shapes: general spheres, then cubes
     const ShadeRec32* R = sc.rec;
     const float* plL;  // f(1) of the shadow test per plane / per uniform sphere (depends on the light only)
     const float* usL;
@@ -412,19 +459,19 @@ render_f32_kernel(DevScene32 sc, CamParams cam, void* __restrict__ out_rgb, uint
         float4* s_pl = smem4;
         float4* s_us = s_pl + S.np;
         float4* s_gs = s_us + S.nu;
-        float4* s_rec = s_gs + 3 * S.ng;
+        float4* s_rec = s_gs + 3 * n_obj;
         const int rec4 = kSmem ? (int)(sizeof(ShadeRec32) / 16) * sc.n_shapes : 0;
         int32_t* s_pi = reinterpret_cast<int32_t*>(s_rec + rec4);
         int32_t* s_ui = s_pi + S.np;
         int32_t* s_gi = s_ui + S.nu;
-        float* s_plL = reinterpret_cast<float*>(s_gi + S.ng);
+        float* s_plL = reinterpret_cast<float*>(s_gi + n_obj);
         float* s_usL = s_plL + S.np;
         int32_t* s_gset = reinterpret_cast<int32_t*>(s_usL + S.nu);
         for (int i = threadIdx.x; i < sc.n_gset && i < 16; i += kThreads) s_gset[i] = sc.gset[i];
         for (int i = threadIdx.x; i < S.np; i += kThreads) { s_pl[i] = sc.planes[i]; s_pi[i] = sc.pl_index[i]; s_plL[i] = sc.plL[i]; }
         for (int i = threadIdx.x; i < S.nu; i += kThreads) { s_us[i] = sc.usph[i]; s_ui[i] = sc.us_index[i]; s_usL[i] = sc.usL[i]; }
-        for (int i = threadIdx.x; i < 3 * S.ng; i += kThreads) s_gs[i] = sc.gsph[i];
-        for (int i = threadIdx.x; i < S.ng; i += kThreads) s_gi[i] = sc.gs_index[i];
+        for (int i = threadIdx.x; i < 3 * n_obj; i += kThreads) s_gs[i] = sc.gsph[i];
+        for (int i = threadIdx.x; i < n_obj; i += kThreads) s_gi[i] = sc.gs_index[i];
         if (kSmem) {
             const float4* g_rec = reinterpret_cast<const float4*>(sc.rec);
             for (int i = threadIdx.x; i < rec4; i += kThreads) s_rec[i] = g_rec[i];
@@ -562,6 +609,13 @@ render_f32_kernel(DevScene32 sc, CamParams cam, void* __restrict__ out_rgb, uint
             else if (geom == GEOM_USPHERE) { float4 g = rec.g0; hn = (p - xyz(g)) * g.w; }
             else {                                                // Shape::normal_at, src/shape.rs:34-40
                 F3 lp = mk(row4(rec.g0, p), row4(rec.g1, p), row4(rec.g2, p));
+                if (geom == GEOM_CUBE) {                          // Cube::normal_at_local, src/shape.rs:601-610 (t rows = transpose(inverse), :623-629)
+                    const float ax = fabsf(lp.x), ay = fabsf(lp.y), az = fabsf(lp.z);
+                    const float maxc = fmaxf(ax, fmaxf(ay, az));
+                    if (maxc == ax) lp = mk(lp.x, 0.f, 0.f);
+                    else if (maxc == ay) lp = mk(0.f, lp.y, 0.f);
+                    else lp = mk(0.f, 0.f, lp.z);
+                }
                 F3 wn = mk(row3(rec.t0, lp), row3(rec.t1, lp), row3(rec.t2, lp));
                 hn = wn * rsqrtf(dot(wn, wn));
             }
@@ -683,8 +737,9 @@ cudaError_t launch_render_f32(const DevScene32& scene, const CamParams& cam, voi
     int dev = 0, sms = 0;
     cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-    const size_t streams = (size_t)(scene.n_planes + scene.n_usph + 3 * scene.n_gsph) * 16 +
-                           (size_t)(scene.n_planes + scene.n_usph + scene.n_gsph) * 4 + (size_t)(scene.n_planes + scene.n_usph) * 4 + 16 * 4 + 16;
+    const int n_obj = scene.n_gsph + scene.n_cube;
+    const size_t streams = (size_t)(scene.n_planes + scene.n_usph + 3 * n_obj) * 16 +
+                           (size_t)(scene.n_planes + scene.n_usph + n_obj) * 4 + (size_t)(scene.n_planes + scene.n_usph) * 4 + 16 * 4 + 16;
     const size_t recs = (size_t)scene.n_shapes * sizeof(ShadeRec32);
     const int tiles = ((cam.hsize + kTileX - 1) / kTileX) * ((cam.shard_rows + kTileY - 1) / kTileY);
     const int warps = kThreads / 32;

@@ -43,7 +43,8 @@ __device__ __forceinline__ V3 xvec3(const double* m9, V3 p) {
 }
 
 struct Streams {  // intersect streams, in shared memory when they fit, else global
-    const double2* sph; const int32_t* sph_index; int ns;
+    const double2* sph; const int32_t* sph_index; int ns;   // spheres [0, ns), then cubes [ns, ns + nc): same 3x4 inverse rows
+    int nc;
     const double2* pl;  const int32_t* pl_index;  int np;
 };
 
@@ -65,6 +66,44 @@ __device__ __forceinline__ bool sphere_roots(const double2* r, V3 o, V3 d, doubl
     t1 = (-b - s) / (2. * a);
     t2 = (-b + s) / (2. * a);
     return true;
+}
+// Cube::check_axis (src/shape.rs:540-564)
+__device__ __forceinline__ void check_axis(double origin, double direction, double& tmin, double& tmax) {
+    const double tmin_numerator = -1.0 - origin;
+    const double tmax_numerator = 1. - origin;
+    if (fabs(direction) >= kEps) {
+        tmin = tmin_numerator / direction;
+        tmax = tmax_numerator / direction;
+    } else {
+        const double inf = __longlong_as_double(0x7ff0000000000000LL);
+        tmin = tmin_numerator >= 0.0 ? inf : -inf;
+        tmax = tmax_numerator >= 0.0 ? inf : -inf;
+    }
+    if (tmin > tmax) { const double t = tmin; tmin = tmax; tmax = t; }
+}
+// Shape::intersect + Cube::intersect_local (src/shape.rs:618-621, 577-591): same ray transform as the
+// sphere, slab test per axis; f64::max / f64::min return the other operand for a NaN, like fmax / fmin.
+__device__ __forceinline__ bool cube_roots(const double2* r, V3 o, V3 d, double& t1, double& t2) {
+    double2 a0 = r[0], a1 = r[1], b0 = r[2], b1 = r[3], c0 = r[4], c1 = r[5];
+    double ox = a0.x * o.x + a0.y * o.y + a1.x * o.z + a1.y;
+    double oy = b0.x * o.x + b0.y * o.y + b1.x * o.z + b1.y;
+    double oz = c0.x * o.x + c0.y * o.y + c1.x * o.z + c1.y;
+    double dx = a0.x * d.x + a0.y * d.y + a1.x * d.z;
+    double dy = b0.x * d.x + b0.y * d.y + b1.x * d.z;
+    double dz = c0.x * d.x + c0.y * d.y + c1.x * d.z;
+    double xmin, xmax, ymin, ymax, zmin, zmax;
+    check_axis(ox, dx, xmin, xmax);
+    check_axis(oy, dy, ymin, ymax);
+    check_axis(oz, dz, zmin, zmax);
+    const double tmin = fmax(xmin, fmax(ymin, zmin));
+    const double tmax = fmin(xmax, fmin(ymax, zmax));
+    if (!(tmin < tmax)) return false;
+    t1 = tmin; t2 = tmax;
+    return true;
+}
+// stream entry i: a sphere below ns, a cube from there on (warp-uniform)
+__device__ __forceinline__ bool solid_roots(const Streams& S, int i, V3 o, V3 d, double& t1, double& t2) {
+    return i < S.ns ? sphere_roots(S.sph + 6 * i, o, d, t1, t2) : cube_roots(S.sph + 6 * i, o, d, t1, t2);
 }
 // Plane::intersect_local (src/shape.rs:462-471)
 __device__ __forceinline__ bool plane_root(const double2* r, V3 o, V3 d, double& t) {
@@ -103,9 +142,9 @@ __device__ __noinline__ void intersect_world(const Streams& S, V3 o, V3 d, doubl
         }
     }
 #pragma unroll kUnroll
-    for (int i = 0; i < S.ns; ++i) {
+    for (int i = 0; i < S.ns + S.nc; ++i) {
         double t1, t2;
-        if (sphere_roots(S.sph + 6 * i, o, d, t1, t2)) {
+        if (solid_roots(S, i, o, d, t1, t2)) {
             int idx = S.sph_index[i];
             if (t1 >= 0.0) take(t1, idx, best_t, best_idx);
             else {
@@ -147,9 +186,9 @@ __device__ __noinline__ void compute_refractive(const Streams& S, const DevScene
             parity[id >> 5] ^= 1u << (id & 31);
         }
     }
-    for (int i = 0; i < S.ns; ++i) {
+    for (int i = 0; i < S.ns + S.nc; ++i) {
         double t1, t2;
-        if (sphere_roots(S.sph + 6 * i, o, d, t1, t2)) {
+        if (solid_roots(S, i, o, d, t1, t2)) {
             int id = sc.rec[S.sph_index[i]].world_id & 255;
             if (t1 < 0.0) parity[id >> 5] ^= 1u << (id & 31);
             if (t2 < 0.0) parity[id >> 5] ^= 1u << (id & 31);
@@ -166,9 +205,9 @@ __device__ __noinline__ void compute_refractive(const Streams& S, const DevScene
             if ((parity[id >> 5] >> (id & 31)) & 1u) { Cont e; e.t = t; e.ord = 2 * idx; e.idx = idx; e.id = id; offer(e, top1, top2); }
         }
     }
-    for (int i = 0; i < S.ns; ++i) {
+    for (int i = 0; i < S.ns + S.nc; ++i) {
         double t1, t2;
-        if (sphere_roots(S.sph + 6 * i, o, d, t1, t2)) {
+        if (solid_roots(S, i, o, d, t1, t2)) {
             int idx = S.sph_index[i];
             int id = sc.rec[idx].world_id & 255;
             if ((parity[id >> 5] >> (id & 31)) & 1u) {
@@ -282,16 +321,17 @@ render_f64_kernel(DevScene64 sc, CamParams cam, double* __restrict__ out_f64, fl
                   uint8_t* __restrict__ out_u8, uint8_t* __restrict__ out_hit, Counters* __restrict__ counters) {
     extern __shared__ double2 smem[];
     Streams S;
-    S.ns = sc.n_spheres; S.np = sc.n_planes;
+    S.ns = sc.n_spheres; S.nc = sc.n_cubes; S.np = sc.n_planes;
+    const int n_solid = sc.n_spheres + sc.n_cubes;
     if (kInSmem) {
         // stage the intersect streams: coalesced 16-byte loads, one pass per block
         double2* s_sph = smem;
-        double2* s_pl = s_sph + 6 * sc.n_spheres;
+        double2* s_pl = s_sph + 6 * n_solid;
         int32_t* s_si = reinterpret_cast<int32_t*>(s_pl + 2 * sc.n_planes);
-        int32_t* s_pi = s_si + sc.n_spheres;
-        for (int i = threadIdx.x; i < 6 * sc.n_spheres; i += kThreads) s_sph[i] = sc.sph_rows[i];
+        int32_t* s_pi = s_si + n_solid;
+        for (int i = threadIdx.x; i < 6 * n_solid; i += kThreads) s_sph[i] = sc.sph_rows[i];
         for (int i = threadIdx.x; i < 2 * sc.n_planes; i += kThreads) s_pl[i] = sc.pl_rows[i];
-        for (int i = threadIdx.x; i < sc.n_spheres; i += kThreads) s_si[i] = sc.sph_index[i];
+        for (int i = threadIdx.x; i < n_solid; i += kThreads) s_si[i] = sc.sph_index[i];
         for (int i = threadIdx.x; i < sc.n_planes; i += kThreads) s_pi[i] = sc.pl_index[i];
         __syncthreads();
         S.sph = s_sph; S.pl = s_pl; S.sph_index = s_si; S.pl_index = s_pi;
@@ -349,6 +389,13 @@ render_f64_kernel(DevScene64 sc, CamParams cam, double* __restrict__ out_f64, fl
                 V3 eyev = neg(rd);
                 V3 lp = xpoint(rec.inv, point);                                    // Shape::normal_at :34-40
                 V3 ln = rec.kind == RTC_SHAPE_PLANE ? mk(0., 1., 0.) : lp;
+                if (rec.kind == RTC_SHAPE_CUBE) {                                  // Cube::normal_at_local :601-610; rec.invt = transpose(inverse), :623-629
+                    const double ax = fabs(lp.x), ay = fabs(lp.y), az = fabs(lp.z);
+                    const double maxc = fmax(ax, fmax(ay, az));
+                    if (maxc == ax) ln = mk(lp.x, 0., 0.);
+                    else if (maxc == ay) ln = mk(0., lp.y, 0.);
+                    else ln = mk(0., 0., lp.z);
+                }
                 V3 normal = normalize(xvec3(rec.invt, ln));
                 double n1 = 1.0, n2 = 1.0;
                 if (rec.transparency != 0.0) {
@@ -513,7 +560,7 @@ cudaError_t launch_render_f64(const DevScene64& scene, const CamParams& cam, voi
     double* o64 = cam.out_format == RTC_OUT_F64_RGB ? (double*)d_rgb : nullptr;
     float* o32 = cam.out_format == RTC_OUT_F32_RGB ? (float*)d_rgb : nullptr;
     uint8_t* o8 = cam.out_format == RTC_OUT_U8_RGB ? (uint8_t*)d_rgb : nullptr;
-    size_t smem = (size_t)scene.n_spheres * (6 * 16 + 4) + (size_t)scene.n_planes * (2 * 16 + 4) + 16;
+    size_t smem = (size_t)(scene.n_spheres + scene.n_cubes) * (6 * 16 + 4) + (size_t)scene.n_planes * (2 * 16 + 4) + 16;
     if (smem <= 200 * 1024) {
         cudaError_t e = cudaFuncSetAttribute(render_f64_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e != cudaSuccess) return e;

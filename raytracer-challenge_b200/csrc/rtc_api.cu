@@ -234,6 +234,8 @@ struct HostScene {
     std::vector<double2> sph64, pl64;
     std::vector<float4> pl32, us32, gs32;
     std::vector<int32_t> sph_index, pl_index, us_index, gs_index, gset;
+    std::vector<double2> cub64; std::vector<float4> cb32; std::vector<int32_t> cub_index;   // cubes: appended to sph64 / gs32 after the spheres
+    int n_spheres = 0, n_gsph = 0, n_cubes = 0;
     std::vector<float> plL, usL;
     int light_inside = 0;
     std::vector<ShadeRec64> rec64;
@@ -267,9 +269,7 @@ int flatten(const rtc_light* light, const rtc_shape* shapes, size_t n, HostScene
     hs.rec32.resize(n);
     for (size_t i = 0; i < n; ++i) {
         const rtc_shape& s = shapes[i];
-        if (s.kind == RTC_SHAPE_CUBE)
-            return fail(RTC_ERR_UNSUPPORTED, "shape " + std::to_string(i) + ": Cube (src/shape.rs:500-630) is not on the device path yet");
-        if (s.kind != RTC_SHAPE_SPHERE && s.kind != RTC_SHAPE_PLANE)
+        if (s.kind != RTC_SHAPE_SPHERE && s.kind != RTC_SHAPE_PLANE && s.kind != RTC_SHAPE_CUBE)
             return fail(RTC_ERR_INVALID_ARG, "shape " + std::to_string(i) + ": bad kind");
         if (s.pattern_kind < RTC_PATTERN_NONE || s.pattern_kind > RTC_PATTERN_GRID)
             return fail(RTC_ERR_INVALID_ARG, "shape " + std::to_string(i) + ": bad pattern kind");
@@ -284,7 +284,8 @@ int flatten(const rtc_light* light, const rtc_shape* shapes, size_t n, HostScene
         std::memset(&r, 0, sizeof r);
         for (int k = 0; k < 12; ++k) r.inv[k] = s.inv[k];
         for (int rr = 0; rr < 3; ++rr)
-            for (int cc = 0; cc < 3; ++cc) r.invt[3 * rr + cc] = s.inv_t[4 * rr + cc];
+            for (int cc = 0; cc < 3; ++cc)   // Cube::normal_at derives the transpose from the inverse per hit (src/shape.rs:623-629): the stored one is not read
+                r.invt[3 * rr + cc] = s.kind == RTC_SHAPE_CUBE ? s.inv[4 * cc + rr] : s.inv_t[4 * rr + cc];
         for (int k = 0; k < 3; ++k) { r.color[k] = s.color[k]; r.pat_a[k] = s.pat_a[k]; r.pat_b[k] = s.pat_b[k]; }
         r.ambient = s.ambient; r.diffuse = s.diffuse; r.specular = s.specular; r.shininess = s.shininess;
         r.reflective = s.reflective; r.transparency = s.transparency; r.refractive_index = s.refractive_index;
@@ -340,6 +341,19 @@ int flatten(const rtc_light* light, const rtc_shape* shapes, size_t n, HostScene
                 }
                 hs.gs_index.push_back((int32_t)i);
             }
+        } else if (s.kind == RTC_SHAPE_CUBE) {
+            geom = GEOM_CUBE;
+            const double* m = s.inv;
+            for (int rr = 0; rr < 3; ++rr) {
+                hs.cub64.push_back(make_double2(m[4 * rr + 0], m[4 * rr + 1]));
+                hs.cub64.push_back(make_double2(m[4 * rr + 2], m[4 * rr + 3]));
+                float4 row = make_float4((float)m[4 * rr], (float)m[4 * rr + 1], (float)m[4 * rr + 2], (float)m[4 * rr + 3]);
+                hs.cb32.push_back(row);
+                (rr == 0 ? q.g0 : rr == 1 ? q.g1 : q.g2) = row;
+                float4 trow = make_float4((float)m[rr], (float)m[4 + rr], (float)m[8 + rr], 0.f);   // row rr of transpose(inverse 3x3)
+                (rr == 0 ? q.t0 : rr == 1 ? q.t1 : q.t2) = trow;
+            }
+            hs.cub_index.push_back((int32_t)i);
         } else {
             geom = GEOM_PLANE;
             hs.pl64.push_back(make_double2(s.inv[4], s.inv[5]));
@@ -354,7 +368,13 @@ int flatten(const rtc_light* light, const rtc_shape* shapes, size_t n, HostScene
         q.tr_ri = make_float4((float)s.transparency, (float)s.refractive_index, __int_as_float_host(s.pattern_kind),
                               __int_as_float_host(geom));
     }
-    // stream positions (planes | uniform spheres | general spheres) of the shapes whose refractive
+    // cubes travel behind the spheres in the same streams (same 3x4 inverse rows; the kernels switch test at the count)
+    hs.n_spheres = (int)hs.sph_index.size(); hs.n_gsph = (int)hs.gs_index.size(); hs.n_cubes = (int)hs.cub_index.size();
+    hs.sph64.insert(hs.sph64.end(), hs.cub64.begin(), hs.cub64.end());
+    hs.sph_index.insert(hs.sph_index.end(), hs.cub_index.begin(), hs.cub_index.end());
+    hs.gs32.insert(hs.gs32.end(), hs.cb32.begin(), hs.cb32.end());
+    hs.gs_index.insert(hs.gs_index.end(), hs.cub_index.begin(), hs.cub_index.end());
+    // stream positions (planes | uniform spheres | general spheres | cubes) of the shapes whose refractive
     // index is not 1.0: the only ones that can change n1/n2 (fast path of compute_refractive)
     const int np = (int)hs.pl_index.size(), nu = (int)hs.us_index.size();
     for (int k = 0; k < np; ++k) if (shapes[hs.pl_index[k]].refractive_index != 1.0) hs.gset.push_back(k);
@@ -689,9 +709,9 @@ int rtc_scene_upload(rtc_context* ctx, const rtc_light* light, const rtc_shape* 
             d.small.rec = d.srec.p;
         }
         d.s64.n_shapes = d.s32.n_shapes = (int)n_shapes;
-        d.s64.n_spheres = (int)hs.sph_index.size();
+        d.s64.n_spheres = hs.n_spheres; d.s64.n_cubes = hs.n_cubes;
         d.s32.n_usph = (int)hs.us_index.size();
-        d.s32.n_gsph = (int)hs.gs_index.size();
+        d.s32.n_gsph = hs.n_gsph; d.s32.n_cube = hs.n_cubes;
         d.s64.n_planes = d.s32.n_planes = (int)hs.pl_index.size();
         d.s64.ids_unique = d.s32.ids_unique = hs.ids_unique;
         d.s64.sph_rows = d.sph64.p; d.s64.pl_rows = d.pl64.p; d.s64.sph_index = d.sph_index.p; d.s64.pl_index = d.pl_index.p;

@@ -37,8 +37,9 @@ struct __align__(16) ShadeRec64 {
 
 struct DevScene64 {
     int n_shapes, n_spheres, n_planes, ids_unique;
-    const double2* sph_rows;   // [n_spheres][6]: r0.xy r0.zw r1.xy r1.zw r2.xy r2.zw
-    const int32_t* sph_index;  // [n_spheres] original shape index
+    int n_cubes, pad0;         // cubes follow the spheres in sph_rows / sph_index (same 3x4 inverse rows, src/shape.rs:618-621)
+    const double2* sph_rows;   // [n_spheres + n_cubes][6]: r0.xy r0.zw r1.xy r1.zw r2.xy r2.zw
+    const int32_t* sph_index;  // [n_spheres + n_cubes] original shape index
     const double2* pl_rows;    // [n_planes][2]: r1.xy r1.zw
     const int32_t* pl_index;   // [n_planes]
     const ShadeRec64* rec;     // [n_shapes]
@@ -52,12 +53,13 @@ struct DevScene64 {
 //   uniform spheres (cx, cy, cz, r^2): spheres whose transform is a similarity (uniform scale +
 //                   rotation + translation) are ordinary world-space spheres
 //   general spheres 3 rows of the inverse (any affine transform), tested in object space
+//   cubes           3 rows of the inverse, slab test in object space (Cube::intersect_local, src/shape.rs:577-591)
 // Geometry kinds of a shading record:
-enum { GEOM_PLANE = 0, GEOM_USPHERE = 1, GEOM_GSPHERE = 2 };
+enum { GEOM_PLANE = 0, GEOM_USPHERE = 1, GEOM_GSPHERE = 2, GEOM_CUBE = 3 };
 
 struct __align__(16) ShadeRec32 {
-    float4 g0, g1, g2;  // plane: g0.xyz = unit world normal | usphere: g0 = (c, 1/r) | gsphere: inverse rows
-    float4 t0, t1, t2;  // gsphere: rows of the stored inverse-transpose 3x3
+    float4 g0, g1, g2;  // plane: g0.xyz = unit world normal | usphere: g0 = (c, 1/r) | gsphere, cube: inverse rows
+    float4 t0, t1, t2;  // gsphere: rows of the stored inverse-transpose 3x3 | cube: rows of transpose(inverse 3x3) (src/shape.rs:623-629)
     float4 col_amb;     // colour rgb, ambient
     float4 dif_spec;    // diffuse, specular, shininess, reflective
     float4 tr_ri;       // transparency, refractive_index, (int) pattern_kind, (int) geom kind
@@ -67,6 +69,7 @@ struct __align__(16) ShadeRec32 {
 
 struct DevScene32 {
     int n_shapes, n_planes, n_usph, n_gsph, ids_unique;
+    int n_cube;                // cubes follow the general spheres in gsph / gs_index (object-space slab test)
     const float4* planes;      // [n_planes]
     const int32_t* pl_index;   // original shape index
     const float4* usph;        // [n_usph]

@@ -6,11 +6,14 @@
 * ``bench_scene()``            — the criterion bench's scene (``benches/render.rs:11-67``).
 * ``synthetic_scene()``        — C4: 9,992 random spheres + 8 planes, seed 0xB200.
 * ``default_world()``          — ``World::default()`` (``src/shape.rs:784-795``).
+* ``cube_scene()``             — a room of cubes (``src/shape.rs:500-630``), §8 f1.
 """
 import math
+import random as _random
 
 from .camera import Camera
-from .scene import (CheckerPattern, Color, Light, Material, Plane, Sphere, StripePattern, World)
+from .scene import (CheckerPattern, Color, Cube, GradientPattern, GridPattern, Light, Material, Plane, RingPattern, Sphere,
+                    StripePattern, TestPattern, World)
 from .transform import Matrix
 
 _I = Matrix.identity
@@ -153,3 +156,37 @@ def synthetic_camera(hsize=3840, vsize=2160, samples=1):
                                     Matrix.make_view_transform((0.0, 6.0, -30.0), (0.0, 3.0, 0.0), (0.0, 1.0, 0.0)))
     cam.set_samples(samples)
     return cam
+
+
+# ---- Cube scenes -----------------------------------------------------------
+def cube_scene(seed=7, n_cubes=9, with_spheres=True, hsize=200, vsize=140):
+    """-> (World, Camera).  SURVEY.md §8 f1 (Cube, src/shape.rs:500-630).  A room of cubes: axis-aligned, rotated, sheared, scaled thin; opaque, mirror, glass (reflective and
+    transparent), patterned; a cube nested in a glass cube; a sphere inside a glass cube; a plane floor."""
+    rnd = _random.Random(seed)
+    I = Matrix.identity
+    w = World(Light(Color(1, 1, 1), (-6, 8, -7)))
+    floor = Material(specular=0.0, reflectiveness=0.3, pattern=CheckerPattern(Color(0.3, 0.3, 0.3), Color(0.7, 0.7, 0.7)))
+    w.add_shape(Plane(I().translation(0, -1, 0), floor))
+    w.add_shape(Cube(I().scaling(12, 8, 12).translation(0, 6.9, 0), Material(color=Color(0.6, 0.7, 0.8), specular=0.1)))  # the room: camera inside a cube
+    glass = dict(diffuse=0.2, specular=0.9, shininess=300, reflectiveness=0.7, transparency=0.9, refractive_index=1.5)
+    w.add_shape(Cube(I().scaling(1.2, 1.2, 1.2).rotation_y(0.5).translation(-1.5, 0.21, 2), Material(color=Color(0.05, 0.1, 0.05), **glass)))
+    w.add_shape(Cube(I().scaling(0.5, 0.5, 0.5).rotation_y(0.5).translation(-1.5, 0.0, 2), Material(color=Color(0.9, 0.2, 0.2))))  # nested
+    w.add_shape(Cube(I().scaling(1.0, 0.7, 1.0).rotation_z(0.3).rotation_y(-0.4).translation(2.0, 0.4, 3), Material(color=Color(0.1, 0.05, 0.1), **glass)))
+    if with_spheres:
+        w.add_shape(Sphere(I().scaling(0.4, 0.4, 0.4).translation(2.0, 0.4, 3), Material(color=Color(0.2, 0.4, 0.9))))  # inside the glass cube
+        w.add_shape(Sphere(I().scaling(0.7, 0.7, 0.7).translation(0.3, -0.3, 0.5), Material(color=Color(0.1, 0.1, 0.1), **glass)))
+    pats = [StripePattern, CheckerPattern, GradientPattern, RingPattern, GridPattern, TestPattern]
+    for k in range(n_cubes):
+        m = I().scaling(rnd.uniform(0.2, 0.8), rnd.uniform(0.05, 0.9), rnd.uniform(0.2, 0.8))
+        if k % 3 == 1:
+            m = m.shearing(rnd.uniform(-.4, .4), 0, 0, rnd.uniform(-.4, .4), 0, 0)
+        m = m.rotation_x(rnd.uniform(0, 3)).rotation_y(rnd.uniform(0, 3)).translation(rnd.uniform(-4, 4), rnd.uniform(-0.5, 2.5), rnd.uniform(0, 7))
+        mat = Material(color=Color(rnd.random(), rnd.random(), rnd.random()), diffuse=rnd.uniform(0.3, 0.9), specular=rnd.uniform(0, 0.9),
+                           shininess=rnd.uniform(5, 200), reflectiveness=rnd.choice([0, 0, 0.4, 0.8]))
+        if k % 2 == 0:
+            p = pats[k % len(pats)](Color(rnd.random(), rnd.random(), rnd.random()), Color(rnd.random(), rnd.random(), rnd.random()))
+            p.set_transform(I().scaling(0.3, 0.3, 0.3).rotation_y(rnd.uniform(0, 3)))
+            mat.set_pattern(p)
+        w.add_shape(Cube(m, mat))
+    cam = Camera.new_with_transform(hsize, vsize, 1.1, Matrix.make_view_transform((0.5, 2.2, -6.5), (0, 0.6, 3), (0, 1, 0)))
+    return w, cam

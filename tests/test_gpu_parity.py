@@ -166,11 +166,6 @@ def test_output_formats(rtc, orc, renderer):
 
 
 def test_unsupported_inputs_are_errors_not_fallbacks(rtc, renderer):
-    w = rtc.World.default()
-    w.add_shape(rtc.Cube())
-    with pytest.raises(rtc.ffi.RtcError) as e:
-        renderer.upload(w)
-    assert e.value.code == rtc.ffi.RTC_ERR_UNSUPPORTED
     w2 = rtc.World.default()
     w2.shapes[0].material.color = None
     with pytest.raises(rtc.ffi.RtcError):
@@ -185,6 +180,45 @@ def test_unsupported_inputs_are_errors_not_fallbacks(rtc, renderer):
     with pytest.raises(rtc.ffi.RtcError) as e:
         fresh.render(rtc.Camera.new(4, 4, 1.0).flatten(), rtc.Renderer.make_opts())
     assert e.value.code == rtc.ffi.RTC_ERR_NO_SCENE
+
+
+# ---- Cube (src/shape.rs:500-630) -----------------------------------------------------
+def _cube_world(rtc, seed=7, n_cubes=9, with_spheres=True):
+    return rtc.scenes.cube_scene(seed, n_cubes, with_spheres)
+
+
+@pytest.mark.parametrize("seed", [7, 8, 9])
+def test_cubes_f64_parity(rtc, orc, renderer, seed):
+    w, cam = _cube_world(rtc, seed)
+    _check64(rtc, orc, renderer, w, cam)
+
+
+def test_cubes_only_axis_aligned_rays_f64(rtc, orc, renderer):
+    """Rays parallel to cube faces (|direction| < EPSILON on an axis -> the +-infinity branch of check_axis,
+    src/shape.rs:549-559), seen head-on by a camera looking down -z at unit cubes; depth 0 and 5."""
+    I = rtc.Matrix.identity
+    w = rtc.World(rtc.Light(rtc.Color(1, 1, 1), (0, 0, 10)))
+    w.add_shape(rtc.Cube(I(), rtc.Material(color=rtc.Color(0.8, 0.3, 0.2), reflectiveness=0.5)))
+    w.add_shape(rtc.Cube(I().translation(2.5, 0, 0), rtc.Material(color=rtc.Color(0.1, 0.1, 0.1), transparency=0.9, reflectiveness=0.6, refractive_index=1.4)))
+    w.add_shape(rtc.Cube(I().scaling(8, 8, 0.5).translation(0, 0, -4), rtc.Material(color=rtc.Color(0.4, 0.5, 0.9))))
+    cam = rtc.Camera.new_with_transform(96, 64, 0.9, rtc.Matrix.make_view_transform((0, 0, 8), (0, 0, 0), (0, 1, 0)))
+    for depth in (0, 5):
+        _check64(rtc, orc, renderer, w, cam, max_depth=depth)
+
+
+def test_cubes_with_aliased_world_ids_f64_and_f32(rtc, orc, renderer):
+    """> 255 shapes (u8 world_ids wrap, src/shape.rs:661-667) with cubes among them: the containers of
+    compute_refractive are toggled by id, cubes included."""
+    w, cam = _cube_world(rtc, 11, n_cubes=300, with_spheres=True)
+    _check64(rtc, orc, renderer, w, cam)
+    _check32(rtc, orc, renderer, w, cam, min_ok=0.995)
+
+
+@pytest.mark.parametrize("seed", [7, 8])
+def test_cubes_f32(rtc, orc, renderer, seed):
+    w, cam = _cube_world(rtc, seed)
+    ok, mm, stats = _check32(rtc, orc, renderer, w, cam, min_ok=0.998)
+    assert mm == 0   # closed room
 
 
 # ---- f32 fast mode ---------------------------------------------------------------------------------

@@ -25,13 +25,18 @@ def cases():
     yield "criterion_bench_40x30", w, cam, rtc.ffi.RECT_FULL, 5
     cam = rtc.Camera.new_with_transform(11, 11, math.pi / 2., rtc.Matrix.make_view_transform((0., 0., -5.), (0., 0., 0.), (0., 1., 0.)))
     yield "default_world_11x11", rtc.World.default(), cam, rtc.ffi.RECT_REFERENCE_RENDER, 5
+    w, cam = rtc.scenes.cube_scene(7, hsize=60, vsize=42)
+    yield "cube_room_60x42", w, cam, rtc.ffi.RECT_FULL, 5
     yield "synthetic_200_spheres_48x27", rtc.scenes.synthetic_scene(n_spheres=200), rtc.scenes.synthetic_camera(48, 27), rtc.ffi.RECT_FULL, 5
 
 
 if __name__ == "__main__":
     out = os.path.join(ROOT, "tests", "golden")
     os.makedirs(out, exist_ok=True)
+    only = sys.argv[1:]   # optional: names to (re)generate; default all
     for name, world, cam, rect, depth in cases():
+        if only and name not in only:
+            continue
         rgb, hit, cnt = orc.render(world, cam, rect=rect, max_depth=depth, threads=os.cpu_count() or 1)
         np.savez_compressed(os.path.join(out, name + ".npz"), rgb=rgb, hit=hit, rect=rect, depth=depth,
                             counters=np.array([cnt.rays, cnt.shadow_rays, cnt.shaded_hits], dtype=np.uint64))
