@@ -238,6 +238,15 @@ int rtc_wait_device(rtc_context* ctx, const void* d_flags, int n, uint32_t value
 int rtc_download_frame(rtc_context* ctx, const void* d_frame, int dev_format, uint32_t hsize, uint32_t vsize,
                        int out_format, void* out_rgb, void* stream);
 
+/* Canvas::to_imgbuf (src/canvas.rs:61-79), the step behind the path when an image file is written: packs a
+ * finished device frame (F64_RGB or F32_RGB, n_pixels pixels) into RGBA8 on the device — per channel
+ * Color::scale(component.powf(1/gamma), 255) with the reference's truncate-then-clamp rule
+ * (src/color.rs:55-65,100-114), alpha 255; `gamma` is Canvas.gamma (1.0 by default, src/canvas.rs:30).
+ * 4 bytes per pixel instead of 24 then cross NVLink / PCIe.  Both buffers 16-byte aligned.
+ * Enqueued on `stream` (NULL = the context's stream, synchronised before returning). */
+int rtc_pack_rgba8_device(rtc_context* ctx, const void* d_frame, int frame_format, size_t n_pixels, float gamma,
+                          void* d_out_rgba, void* stream);
+
 /* Register-resident FMA micro-benchmark on the context's first GPU: measured non-tensor peak
  * of the FP32 (precision = RTC_PRECISION_F32_FAST) or FP64 pipe in TFLOP/s (FMA = 2 flops),
  * used as the roofline denominator beside the formula peak. */

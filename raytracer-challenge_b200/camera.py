@@ -118,6 +118,11 @@ class Renderer:
             self._ctx, C.byref(cam_desc), C.byref(opts), C.c_void_p(d_gathered), shard_stride_rows,
             elem_kind, C.c_void_p(d_frame), C.c_void_p(stream) if stream else None))
 
+    def pack_rgba8_device(self, d_frame, frame_format, n_pixels, gamma, d_out_rgba, stream=None):
+        """rtc_pack_rgba8_device: Canvas::to_imgbuf on the device (gamma, truncate-then-clamp, alpha 255)."""
+        ffi.check(self._lib.rtc_pack_rgba8_device(self._ctx, C.c_void_p(d_frame), frame_format, n_pixels, C.c_float(gamma),
+                                                  C.c_void_p(d_out_rgba), C.c_void_p(stream) if stream else None))
+
     def download_frame(self, d_frame, dev_format, hsize, vsize, out, stream=None):
         """rtc_download_frame: a finished device frame into the host numpy array `out` (same format, or
         f32 -> f64 widening), after the work already enqueued on `stream`."""

@@ -476,6 +476,47 @@ __global__ void assemble_rows_kernel(const U* __restrict__ gathered, U* __restri
     for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < row_units; i += (size_t)gridDim.x * blockDim.x) dst[i] = src[i];
 }
 
+// ---- RGBA8 pack (rtc_pack_rgba8_device): Canvas::to_imgbuf, src/canvas.rs:61-79 ----------------------
+// channel = Color::scale(component.powf(1/gamma), 255) (src/color.rs:55-65,100-114): `as i32` truncates toward
+// zero, saturates and maps NaN to 0, then the value is clamped to [0, 255]; alpha = 255.  HBM-bound:
+// 24 (f64) or 12 (f32) bytes read and 4 written per pixel; a thread packs four pixels — 16-byte loads, one
+// 16-byte store.
+__device__ __forceinline__ unsigned pack_channel(double c, double inv_gamma, bool use_gamma) {
+    if (use_gamma) c = pow(c, inv_gamma);
+    const double v = c * 255.0;
+    int q = v != v ? 0 : (v >= 2147483647.0 ? 2147483647 : (v <= -2147483648.0 ? (-2147483647 - 1) : (int)v));
+    return (unsigned)(q < 0 ? 0 : (q > 255 ? 255 : q));
+}
+template <typename T>
+__global__ void __launch_bounds__(256) pack_rgba8_kernel(const T* __restrict__ rgb, uint32_t* __restrict__ out, size_t n_pixels,
+                                                         double inv_gamma, int use_gamma) {
+    const size_t n_quads = n_pixels / 4;
+    for (size_t q = (size_t)blockIdx.x * blockDim.x + threadIdx.x; q < n_quads; q += (size_t)gridDim.x * blockDim.x) {
+        double c[12];
+        if (sizeof(T) == 8) {
+            const double2* src = reinterpret_cast<const double2*>(rgb) + 6 * q;
+#pragma unroll
+            for (int k = 0; k < 6; ++k) { const double2 v = src[k]; c[2 * k] = v.x; c[2 * k + 1] = v.y; }
+        } else {
+            const float4* src = reinterpret_cast<const float4*>(rgb) + 3 * q;
+#pragma unroll
+            for (int k = 0; k < 3; ++k) { const float4 v = src[k]; c[4 * k] = v.x; c[4 * k + 1] = v.y; c[4 * k + 2] = v.z; c[4 * k + 3] = v.w; }
+        }
+        uint4 px;
+        unsigned* w = &px.x;
+#pragma unroll
+        for (int k = 0; k < 4; ++k)
+            w[k] = pack_channel(c[3 * k], inv_gamma, use_gamma) | (pack_channel(c[3 * k + 1], inv_gamma, use_gamma) << 8) |
+                   (pack_channel(c[3 * k + 2], inv_gamma, use_gamma) << 16) | 0xff000000u;
+        reinterpret_cast<uint4*>(out)[q] = px;
+    }
+    // the last n_pixels % 4 pixels
+    const size_t tail = n_quads * 4 + (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (tail < n_pixels)
+        out[tail] = pack_channel((double)rgb[3 * tail], inv_gamma, use_gamma) | (pack_channel((double)rgb[3 * tail + 1], inv_gamma, use_gamma) << 8) |
+                    (pack_channel((double)rgb[3 * tail + 2], inv_gamma, use_gamma) << 16) | 0xff000000u;
+}
+
 // ---- completion flags (rtc_signal_device / rtc_wait_device) ---------------------------------------
 __global__ void signal_kernel(unsigned* flag, unsigned value) {
     __threadfence_system();
@@ -868,6 +909,29 @@ int rtc_measure_peak_tflops(rtc_context* ctx, int precision, double* out_tflops)
 }  // extern "C"
 
 // ---- rtc_render: host buffers in, host buffers out ------------------------------------------------
+extern "C" int rtc_pack_rgba8_device(rtc_context* ctx, const void* d_frame, int frame_format, size_t n_pixels, float gamma,
+                                     void* d_out_rgba, void* stream) {
+    if (!ctx || !d_frame || !d_out_rgba) return fail(RTC_ERR_INVALID_ARG, "rtc_pack_rgba8_device: null argument");
+    if (frame_format != RTC_OUT_F64_RGB && frame_format != RTC_OUT_F32_RGB) return fail(RTC_ERR_INVALID_ARG, "rtc_pack_rgba8_device: frame must be F64_RGB or F32_RGB");
+    if (((uintptr_t)d_frame | (uintptr_t)d_out_rgba) % 16 != 0) return fail(RTC_ERR_INVALID_ARG, "rtc_pack_rgba8_device: buffers must be 16-byte aligned");
+    if (n_pixels == 0) return RTC_OK;
+    DeviceState& d = ctx->devs[0];
+    CUDA_TRY(cudaSetDevice(d.dev));
+    cudaStream_t st = stream ? (cudaStream_t)stream : d.stream;
+    int sms = 0;
+    CUDA_TRY(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, d.dev));
+    const size_t want = (n_pixels / 4 + 255) / 256 + 1;
+    const int grid = (int)std::max<size_t>(1, std::min<size_t>(want, (size_t)sms * 8));   // a multiple of the SM count, grid-stride beyond
+    // gamma.recip() is computed in f32 and widened (src/color.rs:56: `gamma.recip().into()`)
+    const double inv_gamma = (double)(1.0f / gamma);
+    const int use_gamma = gamma != 1.0f;   // powf(x, 1.0) == x
+    if (frame_format == RTC_OUT_F64_RGB) pack_rgba8_kernel<double><<<grid, 256, 0, st>>>((const double*)d_frame, (uint32_t*)d_out_rgba, n_pixels, inv_gamma, use_gamma);
+    else pack_rgba8_kernel<float><<<grid, 256, 0, st>>>((const float*)d_frame, (uint32_t*)d_out_rgba, n_pixels, inv_gamma, use_gamma);
+    CUDA_TRY(cudaGetLastError());
+    if (!stream) CUDA_TRY(cudaStreamSynchronize(st));
+    return RTC_OK;
+}
+
 extern "C" int rtc_download_frame(rtc_context* ctx, const void* d_frame, int dev_format, uint32_t hsize, uint32_t vsize,
                                   int out_format, void* out_rgb, void* stream) {
     if (!ctx || !d_frame || !out_rgb || hsize == 0 || vsize == 0) return fail(RTC_ERR_INVALID_ARG, "rtc_download_frame: null argument");

@@ -89,6 +89,7 @@ EXPORTS = [
     ("rtc_ipc_close", C.c_int, [C.c_void_p, C.c_void_p, C.c_uint64]),
     ("rtc_signal_device", C.c_int, [C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p]),
     ("rtc_wait_device", C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_uint32, C.c_void_p]),
+    ("rtc_pack_rgba8_device", C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_size_t, C.c_float, C.c_void_p, C.c_void_p]),
     ("rtc_download_frame", C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_uint32, C.c_uint32, C.c_int, C.c_void_p, C.c_void_p]),
     ("rtc_measure_peak_tflops", C.c_int, [C.c_void_p, C.c_int, C.POINTER(C.c_double)]),
 ]

@@ -315,6 +315,57 @@ def test_f32_light_inside_sphere_takes_general_kernel(rtc, orc, renderer):
     _check32(rtc, orc, renderer, w, cam, min_ok=0.99, ray_tol=0.01)
 
 
+@pytest.mark.parametrize("dtype", [np.float64, np.float32])
+@pytest.mark.parametrize("gamma", [1.0, 2.2, 0.5])
+def test_pack_rgba8_is_canvas_to_imgbuf(rtc, orc, renderer, dtype, gamma):
+    """rtc_pack_rgba8_device against Canvas::to_imgbuf (src/canvas.rs:61-79): channel =
+    Color::scale(component.powf(1/gamma), 255) with `as i32` truncation / saturation / NaN -> 0 and the clamp
+    (src/color.rs:55-65,100-114), alpha 255.  gamma = 1 (the Canvas default) must be exact; with a gamma the
+    device pow may differ from the host's by an ulp, which can move a value across a truncation boundary."""
+    import torch
+    rng = np.random.default_rng(5)
+    n = 1_000_003                                   # not a multiple of 4: exercises the tail pixels
+    vals = rng.uniform(-0.2, 1.6, size=(n, 3))
+    vals[:256, 0] = np.arange(256) / 255.0          # exact level boundaries
+    vals[256:512, 1] = np.nextafter(np.arange(256) / 255.0, -1.0)
+    vals[600, :] = (np.nan, np.inf, -np.inf)
+    vals[601, :] = (1e300, -1e300, 0.0)
+    vals[602, :] = (-0.0, 1.0, 0.999999999)
+    with np.errstate(over="ignore"):
+        src = vals.astype(dtype)               # 1e300 -> inf in f32, on purpose
+    fmt = rtc.ffi.OUT_F64_RGB if dtype == np.float64 else rtc.ffi.OUT_F32_RGB
+    dev = torch.from_numpy(src).cuda()
+    out = torch.zeros(n, dtype=torch.int32, device="cuda")
+    renderer.pack_rgba8_device(dev.data_ptr(), fmt, n, gamma, out.data_ptr())
+    got = out.cpu().numpy().view(np.uint8).reshape(n, 4)
+    x = src.astype(np.float64)
+    if gamma != 1.0:
+        with np.errstate(all="ignore"):
+            x = np.power(x, np.float64(np.float32(1.0) / np.float32(gamma)))
+    want = orc.quantize_u8(x)
+    assert (got[:, 3] == 255).all()
+    diff = np.abs(got[:, :3].astype(int) - want.astype(int))
+    if gamma == 1.0:
+        assert diff.max() == 0
+    else:
+        assert diff.max() <= 1 and (diff != 0).mean() < 1e-4, (diff.max(), (diff != 0).mean())
+
+
+def test_pack_rgba8_of_a_rendered_frame(rtc, orc, renderer):
+    import torch
+    world = rtc.scenes.reflect_refract_scene()
+    cam = rtc.scenes.reflect_refract_camera(160, 90)
+    renderer.upload(world)
+    f = rtc.ffi
+    dev = torch.empty((90, 160, 3), dtype=torch.float64, device="cuda")
+    renderer.render_device(cam.flatten(), rtc.Renderer.make_opts(precision=f.PRECISION_F64_PARITY, out_format=f.OUT_F64_RGB), dev.data_ptr())
+    out = torch.zeros(90 * 160, dtype=torch.int32, device="cuda")
+    renderer.pack_rgba8_device(dev.data_ptr(), f.OUT_F64_RGB, 90 * 160, 1.0, out.data_ptr())
+    got = out.cpu().numpy().view(np.uint8).reshape(90, 160, 4)
+    u8, _, _ = renderer.render(cam.flatten(), rtc.Renderer.make_opts(precision=f.PRECISION_F64_PARITY, out_format=f.OUT_U8_RGB))
+    assert np.array_equal(got[:, :, :3], u8) and np.array_equal(got[:, :, :3], orc.quantize_u8(dev.cpu().numpy()))
+
+
 def test_download_frame_matches_rtc_render(rtc, orc, renderer):
     """rtc_download_frame (device frame -> host Canvas buffer, f32 -> f64 widening on the host) delivers
     exactly what rtc_render delivers for the same options."""
