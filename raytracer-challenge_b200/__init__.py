@@ -16,3 +16,4 @@ from .scene import (CheckerPattern, Color, Cube, GradientPattern, GridPattern, L
                     Pattern, Plane, RingPattern, Shape, Sphere, StripePattern, TestPattern, World)
 from .transform import EPSILON, Matrix  # noqa: F401
 from . import scenes  # noqa: F401
+from . import loader  # noqa: F401,E402  (scene front-ends: YAML dialect, Lua-table schema)

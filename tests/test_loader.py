@@ -1,0 +1,186 @@
+"""Scene front-ends: the YAML dialect of the book's scene files and the reference's
+Lua-table schema (src/lua.rs:186-330) build the same flattened scene as the builder API."""
+import ctypes as C
+import math
+
+import numpy as np
+import pytest
+
+
+def _flat_bytes(world):
+    light, shapes, n = world.flatten()
+    return bytes(C.string_at(C.addressof(light), C.sizeof(light))), bytes(C.string_at(C.addressof(shapes), C.sizeof(shapes))), n
+
+
+def _same_camera(a, b):
+    fa, fb = a.flatten(), b.flatten()
+    return bytes(C.string_at(C.addressof(fa), C.sizeof(fa))) == bytes(C.string_at(C.addressof(fb), C.sizeof(fb)))
+
+
+ROOM_YAML = """
+# the reflect/refract room, written in the book's scene dialect from raytracer-challenge_b200/scenes.py
+- add: camera
+  width: 400
+  height: 200
+  field-of-view: 1.152
+  from: [-2.6, 1.5, -3.9]
+  to: [-0.6, 1, -0.8]
+  up: [0, 1, 0]
+- add: light
+  at: [-4.9, 4.9, -1]
+  intensity: [1, 1, 1]
+- define: wall-material
+  value:
+    pattern:
+      type: stripes
+      colors: [[0.45, 0.45, 0.45], [0.55, 0.55, 0.55]]
+      transform: [[scale, 0.25, 0.25, 0.25], [rotate-y, 1.5708]]
+    ambient: 0
+    diffuse: 0.4
+    specular: 0
+    reflective: 0.3
+- define: upright
+  value: [[rotate-y, 1.5708], [rotate-z, 1.5708]]
+- define: glass
+  value: {ambient: 0, diffuse: 0.4, specular: 0.9, shininess: 300, reflective: 0.9, transparency: 0.9, refractive-index: 1.5}
+- define: blue-glass
+  extend: glass
+  value: {color: [0, 0, 0.2]}
+- define: green-glass
+  extend: glass
+  value: {color: [0, 0.2, 0]}
+- add: plane
+  transform: [[rotate-y, 0.31415]]
+  material:
+    pattern: {type: checkers, colors: [[0.35, 0.35, 0.35], [0.65, 0.65, 0.65]]}
+    specular: 0
+    reflective: 0.4
+- add: plane
+  transform: [[translate, 0, 5, 0]]
+  material: {color: [0.8, 0.8, 0.8], ambient: 0.3, specular: 0}
+- add: plane
+  transform: [upright, [translate, -5, 0, 0]]
+  material: wall-material
+- add: plane
+  transform: [upright, [translate, 5, 0, 0]]
+  material: wall-material
+- add: plane
+  transform: [[rotate-x, 1.5708], [translate, 0, 0, 5]]
+  material: wall-material
+- add: plane
+  transform: [[rotate-x, 1.5708], [translate, 0, 0, -5]]
+  material: wall-material
+- add: sphere
+  transform: [[scale, 0.4, 0.4, 0.4], [translate, 4.6, 0.4, 1]]
+  material: {color: [0.8, 0.5, 0.3], shininess: 50}
+- add: sphere
+  transform: [[scale, 0.3, 0.3, 0.3], [translate, 4.7, 0.3, 0.4]]
+  material: {color: [0.9, 0.4, 0.5], shininess: 50}
+- add: sphere
+  transform: [[scale, 0.5, 0.5, 0.5], [translate, -1, 0.5, 4.5]]
+  material: {color: [0.4, 0.9, 0.6], shininess: 50}
+- add: sphere
+  transform: [[scale, 0.3, 0.3, 0.3], [translate, -1.7, 0.3, 4.7]]
+  material: {color: [0.4, 0.6, 0.9], shininess: 50}
+- add: sphere
+  transform: [[translate, -0.6, 1, 0.6]]
+  material: {color: [1, 0.3, 0.2], specular: 0.4, shininess: 5}
+- add: sphere
+  transform: [[scale, 0.7, 0.7, 0.7], [translate, 0.6, 0.7, -0.6]]
+  material: blue-glass
+- add: sphere
+  transform: [[scale, 0.5, 0.5, 0.5], [translate, -0.7, 0.5, -0.8]]
+  material: green-glass
+"""
+
+
+def test_yaml_room_equals_the_builder_api_scene(rtc):
+    world, cam = rtc.loader.load_yaml(ROOM_YAML)
+    assert _flat_bytes(world) == _flat_bytes(rtc.scenes.reflect_refract_scene())
+    assert _same_camera(cam, rtc.scenes.reflect_refract_camera(400, 200))
+
+
+def test_yaml_cube_shear_and_defaults(rtc):
+    text = """
+- add: camera
+  width: 32
+  height: 16
+  field-of-view: 0.9
+  from: [0, 1, -5]
+  to: [0, 0, 0]
+  up: [0, 1, 0]
+- add: light
+  at: [-3, 4, -5]
+  intensity: [1, 0.9, 0.8]
+- add: light            # World holds one light: ignored
+  at: [9, 9, 9]
+  intensity: [1, 1, 1]
+- add: cube
+  transform: [[shear, 0.1, 0, 0, 0.2, 0, 0], [rotate-x, 0.3], [translate, 1, 2, 3]]
+- add: sphere
+"""
+    world, cam = rtc.loader.load_yaml(text)
+    I = rtc.Matrix.identity
+    want = rtc.World(rtc.Light(rtc.Color(1, 0.9, 0.8), (-3., 4., -5.)))
+    want.add_shape(rtc.Cube(I().shearing(0.1, 0, 0, 0.2, 0, 0).rotation_x(0.3).translation(1, 2, 3), rtc.Material()))
+    want.add_shape(rtc.Sphere(I(), rtc.Material()))
+    assert _flat_bytes(world) == _flat_bytes(want)
+    assert world.shapes[0].kind == rtc.ffi.SHAPE_CUBE and world.shapes[1].material.color is not None
+
+
+@pytest.mark.parametrize("bad", [
+    "- add: torus\n",
+    "- add: sphere\n  material: nosuch\n",
+    "- add: sphere\n  transform: [[twist, 1]]\n",
+    "- add: sphere\n  material: {glow: 1}\n",
+    "- add: sphere\n",                                   # no camera / light
+])
+def test_yaml_errors_name_the_problem(rtc, bad):
+    with pytest.raises(ValueError):
+        rtc.loader.load_yaml(bad)
+
+
+def test_lua_table_schema(rtc):
+    """Same keys and order of operations as src/lua.rs:186-330: rotate_x, rotate_y, rotate_z, uniform scale,
+    then position; the first light; material keys; shape-level color / pattern override."""
+    table = {
+        "lights": [{"color": {"r": 1, "g": 1, "b": 1}, "position": {"x": -10, "y": 10, "z": -10}},
+                   {"color": {"r": 0, "g": 0, "b": 1}, "position": {"x": 0, "y": 0, "z": 0}}],
+        "shapes": [
+            {"type": "plane", "position": {"x": 0, "y": -1, "z": 0},
+             "material": {"reflectiveness": 0.3, "specular": 0.1},
+             "pattern": {"type": "checks", "color_a": {"r": 1, "g": 1, "b": 1}, "color_b": {"r": 0, "g": 0, "b": 0}, "scale": 0.5}},
+            {"type": "sphere", "rotate_y": 0.4, "rotate_x": 0.2, "scale": 0.75, "position": {"x": 1, "y": 0, "z": 2},
+             "material": {"transparency": 0.9, "refractive_index": 1.5, "color": {"r": 0.1, "g": 0.1, "b": 0.1}}},
+            {"type": "cube", "rotate_z": 0.7, "position": {"x": -2, "y": 0, "z": 3}, "color": {"r": 0.2, "g": 0.6, "b": 0.3}},
+        ],
+    }
+    world = rtc.loader.world_from_table(table)
+    I = rtc.Matrix.identity
+    want = rtc.World(rtc.Light(rtc.Color(1, 1, 1), (-10., 10., -10.)))
+    pat = rtc.CheckerPattern(rtc.Color(1, 1, 1), rtc.Color(0, 0, 0))
+    pat.set_transform(I().scaling(0.5, 0.5, 0.5))
+    m0 = rtc.Material(reflectiveness=0.3, specular=0.1)
+    m0.pattern = pat
+    want.add_shape(rtc.Plane(I().translation(0, -1, 0), m0))
+    want.add_shape(rtc.Sphere(I().rotation_x(0.2).rotation_y(0.4).scaling(0.75, 0.75, 0.75).translation(1, 0, 2),
+                              rtc.Material(color=rtc.Color(0.1, 0.1, 0.1), transparency=0.9, refractive_index=1.5)))
+    want.add_shape(rtc.Cube(I().rotation_z(0.7).translation(-2, 0, 3), rtc.Material(color=rtc.Color(0.2, 0.6, 0.3))))
+    assert _flat_bytes(world) == _flat_bytes(want)
+    cam = rtc.loader.camera_from_table({"position": {"x": 0, "y": 1.5, "z": -5}, "lookat": {"x": 0, "y": 1, "z": 0}, "up": {"x": 0, "y": 1, "z": 0},
+                                        "screenwidth": 64, "screenheight": 48, "fov": math.pi / 3, "samples": 0})
+    want_cam = rtc.Camera.new_with_transform(64, 48, math.pi / 3, rtc.Matrix.make_view_transform((0, 1.5, -5), (0, 1, 0), (0, 1, 0)))
+    want_cam.set_samples(0)
+    assert _same_camera(cam, want_cam)
+    with pytest.raises(ValueError):
+        rtc.loader.world_from_table({"lights": table["lights"], "shapes": [{"type": "cone"}]})
+    with pytest.raises(ValueError):
+        rtc.loader.world_from_table({"lights": table["lights"], "shapes": [{"type": "sphere", "material": {"glow": 1}}]})
+
+
+def test_loaded_scene_renders_like_the_builder_scene_on_the_oracle(rtc, orc):
+    world, cam = rtc.loader.load_yaml(ROOM_YAML.replace("width: 400", "width: 48").replace("height: 200", "height: 24"))
+    got, hit, _ = orc.render(world, cam, rect=rtc.ffi.RECT_FULL, max_depth=5, threads=2)
+    want, want_hit, _ = orc.render(rtc.scenes.reflect_refract_scene(), rtc.scenes.reflect_refract_camera(48, 24), rect=rtc.ffi.RECT_FULL,
+                                   max_depth=5, threads=2)
+    assert np.array_equal(got, want) and np.array_equal(hit, want_hit)
