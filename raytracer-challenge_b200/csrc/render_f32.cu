@@ -24,7 +24,6 @@ namespace rtc {
 namespace {
 
 constexpr float kEps32 = 1e-4f;
-constexpr float kPlaneEps = 1e-8f;  // abs(d.y) < EPSILON -> parallel (src/shape.rs:463)
 constexpr int kThreads = 128;
 constexpr int kTileX = 8, kTileY = 4;
 constexpr int kBatch = kTileX * kTileY;  // pixels a warp claims per atomic: one 8x4 tile
@@ -32,7 +31,6 @@ constexpr int kMaxStack = RTC_MAX_DEPTH;
 
 struct F3 { float x, y, z; };
 __device__ __forceinline__ F3 mk(float x, float y, float z) { F3 v; v.x = x; v.y = y; v.z = z; return v; }
-__device__ __forceinline__ F3 operator+(F3 a, F3 b) { return mk(a.x + b.x, a.y + b.y, a.z + b.z); }
 __device__ __forceinline__ F3 operator-(F3 a, F3 b) { return mk(a.x - b.x, a.y - b.y, a.z - b.z); }
 __device__ __forceinline__ F3 operator*(F3 a, float m) { return mk(a.x * m, a.y * m, a.z * m); }
 __device__ __forceinline__ F3 operator*(F3 a, F3 b) { return mk(a.x * b.x, a.y * b.y, a.z * b.z); }
@@ -76,7 +74,7 @@ __device__ __forceinline__ bool cube_slab32(const float4* r, F3 o, F3 d, float& 
 // over every shape.  n_neg counts all of them; entries beyond kNegCap are dropped and the caller falls
 // back to the passes.
 constexpr int kNegCap = 48;
-template <bool kCollect>
+template <bool kCollect, bool kCubes>
 __device__ __forceinline__ void intersect32(const Streams32& S, F3 o, F3 d, float& best_t, int& hit, float2* neg, int& n_neg) {
     hit = -1;
     if (kCollect) n_neg = 0;
@@ -121,7 +119,7 @@ __device__ __forceinline__ void intersect32(const Streams32& S, F3 o, F3 d, floa
         if (dn >= 0.f && t >= 0.f && t < best_t) { best_t = t; hit = S.np + S.nu + i; }
         if (kCollect && dn >= 0.f && t1 < 0.f) { keep(t1, 2 * (S.np + S.nu + i)); if (t2 < 0.f) keep(t2, 2 * (S.np + S.nu + i) + 1); }
     }
-    for (int i = S.ng; i < S.ng + S.nc; ++i) {           // Cube
+    if (kCubes) for (int i = S.ng; i < S.ng + S.nc; ++i) {   // Cube
         float t1, t2;
         if (cube_slab32(S.gsph + 3 * i, o, d, t1, t2)) {
             float t = t1 >= 0.f ? t1 : t2;
@@ -293,6 +291,7 @@ __device__ __forceinline__ F3 pattern_at32(int kind, F3 a, F3 b, F3 p) {
 // a plane is a sign change of f(t) = n.(p + t d) + w between t=0 and t=1, and for a sphere needs
 // no square root: f(0) f(1) < 0 (one root inside) or both roots inside.  f(1) depends only on the
 // light and is precomputed per shape (plL / usL, staged beside the streams).
+template <bool kCubes>
 __device__ __forceinline__ bool shadow32(const Streams32& S, const float* __restrict__ plL, const float* __restrict__ usL,
                                          bool light_inside, F3 o, F3 d) {
     // every test is reduced to "g <= 0" and the g's are min-accumulated: FMNMX instead of predicates
@@ -343,7 +342,7 @@ __device__ __forceinline__ bool shadow32(const Streams32& S, const float* __rest
             }
         }
     }
-    for (int i = S.ng; i < S.ng + S.nc; ++i) {   // cubes: nearest non-negative root below 1
+    if (kCubes) for (int i = S.ng; i < S.ng + S.nc; ++i) {   // cubes: nearest non-negative root below 1
         float t1, t2;
         if (cube_slab32(S.gsph + 3 * i, o, d, t1, t2)) {
             float t = t1 >= 0.f ? t1 : t2;
@@ -436,7 +435,8 @@ __device__ __noinline__ void compute_refractive32_unique(const Streams32& S, con
 // kSmem: shading records staged to shared memory; kUnique: world_ids are unique (<= 255 shapes);
 // kGlobal: the intersect streams stay in global memory (read through L1/L2 as warp-uniform loads) —
 // scenes of any size, e.g. the 10k-shape config C4.
-template <bool kSmem, bool kUnique, bool kGlobal>
+// kCubes: the scene has cubes (object-space slab tests behind the general spheres); scenes without them compile none of it
+template <bool kSmem, bool kUnique, bool kGlobal, bool kCubes>
 __global__ void __launch_bounds__(kThreads, RTC_F32_MIN_BLOCKS)
 render_f32_kernel(DevScene32 sc, CamParams cam, void* __restrict__ out_rgb, uint8_t* __restrict__ out_hit,
                   Counters* __restrict__ counters, unsigned* __restrict__ work) {
@@ -591,7 +591,7 @@ render_f32_kernel(DevScene32 sc, CamParams cam, void* __restrict__ out_rgb, uint
         // ---------------------------------------------------------------- phase A: World::intersect, radiance rays
         float t = __int_as_float(0x7f800000);
         int hit = -1;
-        if (has_ray) { intersect32<!kUnique>(S, ro, rd, t, hit, neg, n_neg); ++n_rays; }
+        if (has_ray) { intersect32<!kUnique, kCubes>(S, ro, rd, t, hit, neg, n_neg); ++n_rays; }
         if (has_ray && is_primary && hit >= 0) { hitbits |= 1u << sub; ++n_phits; }
         if (hit < 0) has_ray = false;   // World::color_at -> background_color (black), src/shape.rs:708
 
@@ -609,7 +609,7 @@ render_f32_kernel(DevScene32 sc, CamParams cam, void* __restrict__ out_rgb, uint
             else if (geom == GEOM_USPHERE) { float4 g = rec.g0; hn = (p - xyz(g)) * g.w; }
             else {                                                // Shape::normal_at, src/shape.rs:34-40
                 F3 lp = mk(row4(rec.g0, p), row4(rec.g1, p), row4(rec.g2, p));
-                if (geom == GEOM_CUBE) {                          // Cube::normal_at_local, src/shape.rs:601-610 (t rows = transpose(inverse), :623-629)
+                if (kCubes && geom == GEOM_CUBE) {                          // Cube::normal_at_local, src/shape.rs:601-610 (t rows = transpose(inverse), :623-629)
                     const float ax = fabsf(lp.x), ay = fabsf(lp.y), az = fabsf(lp.z);
                     const float maxc = fmaxf(ax, fmaxf(ay, az));
                     if (maxc == ax) lp = mk(lp.x, 0.f, 0.f);
@@ -631,7 +631,7 @@ render_f32_kernel(DevScene32 sc, CamParams cam, void* __restrict__ out_rgb, uint
 
         // ---------------------------------------------------------------- phase C: is_shadowed (any-hit)
         bool shadowed = false;
-        if (hit >= 0) { shadowed = shadow32(S, plL, usL, light_inside, hp, light_pos - hp); ++n_rays; ++n_shaded; }
+        if (hit >= 0) { shadowed = shadow32<kCubes>(S, plL, usL, light_inside, hp, light_pos - hp); ++n_rays; ++n_shaded; }
 
         // ---------------------------------------------------------------- phase D: shade_hit
         if (hit >= 0) {
@@ -755,10 +755,13 @@ cudaError_t launch_render_f32(const DevScene32& scene, const CamParams& cam, voi
         kernel<<<grid, kThreads, smem, stream>>>(scene, cam, d_rgb, d_hit, d_counters, d_work);
         return cudaSuccess;
     };
-    const bool uniq = scene.ids_unique != 0;
-    if (global_streams) e = uniq ? launch(render_f32_kernel<false, true, true>) : launch(render_f32_kernel<false, false, true>);
-    else if (small) e = uniq ? launch(render_f32_kernel<true, true, false>) : launch(render_f32_kernel<true, false, false>);
-    else e = uniq ? launch(render_f32_kernel<false, true, false>) : launch(render_f32_kernel<false, false, false>);
+    const bool uniq = scene.ids_unique != 0, cubes = scene.n_cube > 0;
+#define RTC_LAUNCH32(SM, GL) (uniq ? (cubes ? launch(render_f32_kernel<SM, true, GL, true>) : launch(render_f32_kernel<SM, true, GL, false>)) \
+                                   : (cubes ? launch(render_f32_kernel<SM, false, GL, true>) : launch(render_f32_kernel<SM, false, GL, false>)))
+    if (global_streams) e = RTC_LAUNCH32(false, true);
+    else if (small) e = RTC_LAUNCH32(true, false);
+    else e = RTC_LAUNCH32(false, false);
+#undef RTC_LAUNCH32
     if (e != cudaSuccess) return e;
     return cudaGetLastError();
 }

@@ -32,7 +32,6 @@ constexpr unsigned kInfBits = 0x7f800000u;
 
 struct F3 { float x, y, z; };
 __device__ __forceinline__ F3 mk(float x, float y, float z) { F3 v; v.x = x; v.y = y; v.z = z; return v; }
-__device__ __forceinline__ F3 operator+(F3 a, F3 b) { return mk(a.x + b.x, a.y + b.y, a.z + b.z); }
 __device__ __forceinline__ F3 operator-(F3 a, F3 b) { return mk(a.x - b.x, a.y - b.y, a.z - b.z); }
 __device__ __forceinline__ F3 operator*(F3 a, float m) { return mk(a.x * m, a.y * m, a.z * m); }
 __device__ __forceinline__ F3 operator*(F3 a, F3 b) { return mk(a.x * b.x, a.y * b.y, a.z * b.z); }
@@ -557,7 +556,7 @@ extern "C" int rtc_debug_read_trace(unsigned long long* dst, int n_words) {
 cudaError_t launch_render_f32_small(const SmallParams& P, int out_format, void* d_rgb, uint8_t* d_hit, Counters* d_counters,
                                     unsigned* d_work, cudaStream_t stream) {
     if (P.shard_rows <= 0) return cudaSuccess;
-    cudaError_t e = cudaSuccess;   // d_work[0..1] are zero between launches (the kernel resets them)
+    // d_work[0..3] are zero between launches (the kernel resets them)
     int dev = 0, sms = 0;
     cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);

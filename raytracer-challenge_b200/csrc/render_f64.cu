@@ -101,10 +101,6 @@ __device__ __forceinline__ bool cube_roots(const double2* r, V3 o, V3 d, double&
     t1 = tmin; t2 = tmax;
     return true;
 }
-// stream entry i: a sphere below ns, a cube from there on (warp-uniform)
-__device__ __forceinline__ bool solid_roots(const Streams& S, int i, V3 o, V3 d, double& t1, double& t2) {
-    return i < S.ns ? sphere_roots(S.sph + 6 * i, o, d, t1, t2) : cube_roots(S.sph + 6 * i, o, d, t1, t2);
-}
 // Plane::intersect_local (src/shape.rs:462-471)
 __device__ __forceinline__ bool plane_root(const double2* r, V3 o, V3 d, double& t) {
     double2 b0 = r[0], b1 = r[1];
@@ -127,7 +123,7 @@ __device__ __forceinline__ void take(double t, int idx, double& best_t, int& bes
 // and compute_refractive falls back to its two passes.
 struct Neg { double t; int ord; int pad; };
 constexpr int kNegCap = 48;
-template <bool kCollect>
+template <bool kCollect, bool kCubes>
 __device__ __noinline__ void intersect_world(const Streams& S, V3 o, V3 d, double& best_t, int& best_idx, Neg* neg, int& n_neg) {
     best_t = __longlong_as_double(0x7ff0000000000000LL);
     best_idx = 0x7fffffff;
@@ -142,9 +138,20 @@ __device__ __noinline__ void intersect_world(const Streams& S, V3 o, V3 d, doubl
         }
     }
 #pragma unroll kUnroll
-    for (int i = 0; i < S.ns + S.nc; ++i) {
+    for (int i = 0; i < S.ns; ++i) {
         double t1, t2;
-        if (solid_roots(S, i, o, d, t1, t2)) {
+        if (sphere_roots(S.sph + 6 * i, o, d, t1, t2)) {
+            int idx = S.sph_index[i];
+            if (t1 >= 0.0) take(t1, idx, best_t, best_idx);
+            else {
+                take(t2, idx, best_t, best_idx);
+                if (kCollect) { if (t1 < 0.0) keep(t1, 2 * idx); if (t2 < 0.0) keep(t2, 2 * idx + 1); }
+            }
+        }
+    }
+    if (kCubes) for (int i = S.ns; i < S.ns + S.nc; ++i) {   // cubes: behind the spheres in the same stream
+        double t1, t2;
+        if (cube_roots(S.sph + 6 * i, o, d, t1, t2)) {
             int idx = S.sph_index[i];
             if (t1 >= 0.0) take(t1, idx, best_t, best_idx);
             else {
@@ -173,6 +180,7 @@ __device__ __forceinline__ void offer(Cont e, Cont& top1, Cont& top2) {
     if (top1.idx < 0 || later(e, top1)) { top2 = top1; top1 = e; }
     else if (top2.idx < 0 || later(e, top2)) top2 = e;
 }
+template <bool kCubes>
 __device__ __noinline__ void compute_refractive(const Streams& S, const DevScene64& sc, V3 o, V3 d, int hit_idx,
                                                 double& n1, double& n2) {
     unsigned parity[8];
@@ -186,9 +194,17 @@ __device__ __noinline__ void compute_refractive(const Streams& S, const DevScene
             parity[id >> 5] ^= 1u << (id & 31);
         }
     }
-    for (int i = 0; i < S.ns + S.nc; ++i) {
+    for (int i = 0; i < S.ns; ++i) {
         double t1, t2;
-        if (solid_roots(S, i, o, d, t1, t2)) {
+        if (sphere_roots(S.sph + 6 * i, o, d, t1, t2)) {
+            int id = sc.rec[S.sph_index[i]].world_id & 255;
+            if (t1 < 0.0) parity[id >> 5] ^= 1u << (id & 31);
+            if (t2 < 0.0) parity[id >> 5] ^= 1u << (id & 31);
+        }
+    }
+    if (kCubes) for (int i = S.ns; i < S.ns + S.nc; ++i) {   // cubes: behind the spheres in the same stream
+        double t1, t2;
+        if (cube_roots(S.sph + 6 * i, o, d, t1, t2)) {
             int id = sc.rec[S.sph_index[i]].world_id & 255;
             if (t1 < 0.0) parity[id >> 5] ^= 1u << (id & 31);
             if (t2 < 0.0) parity[id >> 5] ^= 1u << (id & 31);
@@ -205,9 +221,20 @@ __device__ __noinline__ void compute_refractive(const Streams& S, const DevScene
             if ((parity[id >> 5] >> (id & 31)) & 1u) { Cont e; e.t = t; e.ord = 2 * idx; e.idx = idx; e.id = id; offer(e, top1, top2); }
         }
     }
-    for (int i = 0; i < S.ns + S.nc; ++i) {
+    for (int i = 0; i < S.ns; ++i) {
         double t1, t2;
-        if (solid_roots(S, i, o, d, t1, t2)) {
+        if (sphere_roots(S.sph + 6 * i, o, d, t1, t2)) {
+            int idx = S.sph_index[i];
+            int id = sc.rec[idx].world_id & 255;
+            if ((parity[id >> 5] >> (id & 31)) & 1u) {
+                if (t1 < 0.0) { Cont e; e.t = t1; e.ord = 2 * idx; e.idx = idx; e.id = id; offer(e, top1, top2); }
+                if (t2 < 0.0) { Cont e; e.t = t2; e.ord = 2 * idx + 1; e.idx = idx; e.id = id; offer(e, top1, top2); }
+            }
+        }
+    }
+    if (kCubes) for (int i = S.ns; i < S.ns + S.nc; ++i) {   // cubes: behind the spheres in the same stream
+        double t1, t2;
+        if (cube_roots(S.sph + 6 * i, o, d, t1, t2)) {
             int idx = S.sph_index[i];
             int id = sc.rec[idx].world_id & 255;
             if ((parity[id >> 5] >> (id & 31)) & 1u) {
@@ -312,7 +339,8 @@ __device__ __forceinline__ void thread_sample(int& sx, int& sy) {
     sy = blockIdx.y * kBlockY + (w >> 1) * 4 + (l >> 3);
 }
 
-template <bool kInSmem>
+// kCubes: the scene has cubes (src/shape.rs:500-630); scenes without them run exactly the sphere / plane code
+template <bool kInSmem, bool kCubes>
 #ifndef RTC_F64_MIN_BLOCKS
 #define RTC_F64_MIN_BLOCKS 4
 #endif
@@ -378,7 +406,7 @@ render_f64_kernel(DevScene64 sc, CamParams cam, double* __restrict__ out_f64, fl
             bool descended = false;
             double t; int idx;
             ++n_rays;
-            intersect_world<true>(S, ro, rd, t, idx, kept, n_neg);
+            intersect_world<true, kCubes>(S, ro, rd, t, idx, kept, n_neg);
             if (first) { primary_hit = idx >= 0; first = false; }
             if (idx < 0) {
                 color = mk(0., 0., 0.);  // background_color, src/shape.rs:652
@@ -389,7 +417,7 @@ render_f64_kernel(DevScene64 sc, CamParams cam, double* __restrict__ out_f64, fl
                 V3 eyev = neg(rd);
                 V3 lp = xpoint(rec.inv, point);                                    // Shape::normal_at :34-40
                 V3 ln = rec.kind == RTC_SHAPE_PLANE ? mk(0., 1., 0.) : lp;
-                if (rec.kind == RTC_SHAPE_CUBE) {                                  // Cube::normal_at_local :601-610; rec.invt = transpose(inverse), :623-629
+                if (kCubes && rec.kind == RTC_SHAPE_CUBE) {                                  // Cube::normal_at_local :601-610; rec.invt = transpose(inverse), :623-629
                     const double ax = fabs(lp.x), ay = fabs(lp.y), az = fabs(lp.z);
                     const double maxc = fmax(ax, fmax(ay, az));
                     if (maxc == ax) ln = mk(lp.x, 0., 0.);
@@ -400,7 +428,7 @@ render_f64_kernel(DevScene64 sc, CamParams cam, double* __restrict__ out_f64, fl
                 double n1 = 1.0, n2 = 1.0;
                 if (rec.transparency != 0.0) {
                     if (n_neg <= kNegCap) compute_refractive_kept(sc, idx, kept, n_neg, n1, n2);
-                    else compute_refractive(S, sc, ro, rd, idx, n1, n2);   // more entries than were kept: the two passes
+                    else compute_refractive<kCubes>(S, sc, ro, rd, idx, n1, n2);   // more entries than were kept: the two passes
                 }
                 bool inside = dot(normal, eyev) < 0.0;
                 if (inside) normal = neg(normal);
@@ -413,7 +441,7 @@ render_f64_kernel(DevScene64 sc, CamParams cam, double* __restrict__ out_f64, fl
                 V3 sdir = normalize(v);
                 double st; int sidx;
                 ++n_rays; ++n_shadow; ++n_shaded;
-                intersect_world<false>(S, over_point, sdir, st, sidx, kept, n_shadow_neg);
+                intersect_world<false, kCubes>(S, over_point, sdir, st, sidx, kept, n_shadow_neg);
                 bool shadowed = sidx >= 0 && st < distance;
                 V3 surface = lighting(rec, light_pos, light_int, over_point, eyev, normal, shadowed);
                 // shade_hit's children (src/shape.rs:689-699, 729-766)
@@ -561,13 +589,19 @@ cudaError_t launch_render_f64(const DevScene64& scene, const CamParams& cam, voi
     float* o32 = cam.out_format == RTC_OUT_F32_RGB ? (float*)d_rgb : nullptr;
     uint8_t* o8 = cam.out_format == RTC_OUT_U8_RGB ? (uint8_t*)d_rgb : nullptr;
     size_t smem = (size_t)(scene.n_spheres + scene.n_cubes) * (6 * 16 + 4) + (size_t)scene.n_planes * (2 * 16 + 4) + 16;
-    if (smem <= 200 * 1024) {
-        cudaError_t e = cudaFuncSetAttribute(render_f64_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-        if (e != cudaSuccess) return e;
-        render_f64_kernel<true><<<grid, kThreads, smem, stream>>>(scene, cam, o64, o32, o8, d_hit, d_counters);
-    } else {
-        render_f64_kernel<false><<<grid, kThreads, 0, stream>>>(scene, cam, o64, o32, o8, d_hit, d_counters);
-    }
+    auto launch = [&](auto kernel, size_t bytes) -> cudaError_t {
+        if (bytes) {
+            cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
+            if (e != cudaSuccess) return e;
+        }
+        kernel<<<grid, kThreads, bytes, stream>>>(scene, cam, o64, o32, o8, d_hit, d_counters);
+        return cudaSuccess;
+    };
+    const bool cubes = scene.n_cubes > 0;
+    cudaError_t e;
+    if (smem <= 200 * 1024) e = cubes ? launch(render_f64_kernel<true, true>, smem) : launch(render_f64_kernel<true, false>, smem);
+    else e = cubes ? launch(render_f64_kernel<false, true>, 0) : launch(render_f64_kernel<false, false>, 0);
+    if (e != cudaSuccess) return e;
     return cudaGetLastError();
 }
 
