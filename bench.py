@@ -24,7 +24,7 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
 WORKLOAD = "C3: reflect-refract room (jamis.yml, 13 shapes), 3840x2160, 1 spp, depth 5"
-W, H, DEPTH = 3840, 2160, 5
+W, H, DEPTH, SAMPLES = 3840, 2160, 5, 1   # the metric's configuration (BASELINE.json configs[2]); --workload c5 switches to configs[4]
 N_SPHERES, N_PLANES = 7, 6
 FLOP_PER_RAY = 54 * N_SPHERES + 13 * N_PLANES   # algorithmic flops per World::intersect
 FLOP_PER_SHADED_HIT = 150
@@ -94,7 +94,7 @@ def oracle_sample(threads, target_seconds=12.0):
     import orc
     import rtc_b200 as rtc
     world = rtc.scenes.reflect_refract_scene()
-    cam = rtc.scenes.reflect_refract_camera(W, H)
+    cam = rtc.scenes.reflect_refract_camera(W, H, samples=SAMPLES)
     ow = orc.OracleWorld(world)
     # calibrate on a coarse lattice, then size the real sample
     idx = orc.lattice(W, H, step=64, n_random=0)
@@ -175,7 +175,7 @@ def run_gpu(args):
             os.close(saved_stdout)
     r = rtc.Renderer([local_rank])
     world = rtc.scenes.reflect_refract_scene()
-    cam = rtc.scenes.reflect_refract_camera(W, H)
+    cam = rtc.scenes.reflect_refract_camera(W, H, samples=SAMPLES)
     flat = world.flatten()
     camd = cam.flatten()
     r.upload_flat(*flat)
@@ -419,7 +419,13 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--tile-rows", type=int, default=4, help="rows per interleaved tile (multi-GPU sharding)")
+    ap.add_argument("--workload", default="c3", choices=["c3", "c5"],
+                    help="c3 (default): the metric's 4K frame; c5: BASELINE.json configs[4], 7680x4320 with the deterministic 2x2 supersample")
     args = ap.parse_args()
+    if args.workload == "c5":
+        global WORKLOAD, W, H, SAMPLES
+        WORKLOAD = "C5: reflect-refract room (jamis.yml, 13 shapes), 7680x4320, deterministic 2x2 supersample, depth 5"
+        W, H, SAMPLES = 7680, 4320, 0
     if args.impl == "reference":
         return run_reference(args)
     return run_gpu(args)

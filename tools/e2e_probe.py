@@ -24,3 +24,14 @@ for name, prec, fmt in (("f32 kernel -> f64 Canvas", 1, ffi.OUT_F64_RGB), ("f32 
     plain = min(_timed(lambda: r.render(cam, opts, want_mask=False, out=bufs[fmt], want_stats=False)) for _ in range(6))
     dt, st = best
     print(f"{name:26s} wall {dt:7.3f} ms (no stats: {plain:7.3f}) | total {st.total_ms:7.3f} kernel {st.kernel_ms:6.3f} after-kernel {st.d2h_ms:6.3f} host-delivery {st.gather_ms:6.3f}")
+flat = rtc.scenes.reflect_refract_scene().flatten()
+ts = []
+for _ in range(20):
+    t = time.perf_counter(); r.upload_flat(*flat); ts.append((time.perf_counter() - t) * 1e3)
+print(f"rtc_scene_upload (13 shapes): min {min(ts):.3f} ms  median {sorted(ts)[10]:.3f} ms")
+host = bufs[ffi.OUT_F64_RGB]
+oe = rtc.Renderer.make_opts(precision=1, out_format=ffi.OUT_F64_RGB)
+ts = []
+for _ in range(12):
+    t = time.perf_counter(); r.upload_flat(*flat); r.render(cam, oe, want_mask=False, out=host, want_stats=False); ts.append((time.perf_counter() - t) * 1e3)
+print(f"upload + render (the bench's e2e step): min {min(ts):.3f} ms  median {sorted(ts)[6]:.3f} ms")
