@@ -138,6 +138,9 @@ typedef struct rtc_render_opts {
 /* f32 small-scene kernel: hand tiles out in linear order instead of "tiles that see a transparent
  * surface first" (the scheduling pre-pass).  Same image either way; for measuring the difference. */
 #define RTC_OPT_LINEAR_TILE_ORDER 4
+/* f32 general kernel, scenes whose streams stay in global memory: test every shape exactly instead of
+ * filtering by bounding sphere first.  Same image either way (the filter is conservative); for checking that. */
+#define RTC_OPT_NO_BOUND_FILTER 8
 
 #define RTC_MAX_DEPTH 8
 

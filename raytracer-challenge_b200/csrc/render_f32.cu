@@ -46,6 +46,7 @@ struct Streams32 {
     const float4* usph;   const int32_t* us_index; int nu;
     const float4* gsph;   const int32_t* gs_index; int ng;   // general spheres [0, ng), then cubes [ng, ng + nc): 3 inverse rows each
     int nc;
+    const float4* bound; int nb4; float cmax, rmax;   // bounding-sphere filter (DevScene32::bound), kFilter kernels only
 };
 
 // Cube::intersect_local (src/shape.rs:540-591) in object space: slab test per axis.  A zero direction
@@ -74,7 +75,42 @@ __device__ __forceinline__ bool cube_slab32(const float4* r, F3 o, F3 d, float& 
 // over every shape.  n_neg counts all of them; entries beyond kNegCap are dropped and the caller falls
 // back to the passes.
 constexpr int kNegCap = 48;
-template <bool kCollect, bool kCubes>
+
+// Bounding-sphere filter (kFilter kernels: 10^3+ shapes, streams in global memory).  |(c - o) x d^| is the distance
+// of the centre from the ray's line; with m = o x d^ it is |c x d^ - m|, six FFMA per shape and three more for
+// the squared length minus R^2 (the stream stores -R^2).  `exact(i)` runs for every entry i of the bound stream
+// whose line distance is within R plus the rounding margin: E bounds the error of this test plus that of the
+// exact tests (each a few dozen ulps of |c| + |o|), so no shape an exact test would accept is skipped and the
+// image is the one the unfiltered loops produce (RTC_OPT_NO_BOUND_FILTER renders that one for comparison).
+// Four shapes per trip, one branch per trip: the exact tests sit behind it.
+template <typename F>
+__device__ __forceinline__ void sweep_bounds(const Streams32& S, F3 o, F3 d, F exact) {
+    const F3 dh = d * rsqrtf(dot(d, d));
+    const F3 m = mk(o.y * dh.z - o.z * dh.y, o.z * dh.x - o.x * dh.z, o.x * dh.y - o.y * dh.x);
+    const float E = 3.8e-6f * (S.cmax + fabsf(o.x) + fabsf(o.y) + fabsf(o.z));
+    const float margin = fmaf(E, 2.f * S.rmax + E, 2e-6f * S.rmax * S.rmax);
+    auto gap = [&](float4 b) {
+        const float vx = fmaf(-b.z, dh.y, fmaf(b.y, dh.z, -m.x));
+        const float vy = fmaf(-b.x, dh.z, fmaf(b.z, dh.x, -m.y));
+        const float vz = fmaf(-b.y, dh.x, fmaf(b.x, dh.y, -m.z));
+        return fmaf(vz, vz, fmaf(vy, vy, fmaf(vx, vx, b.w)));
+    };
+#pragma unroll 2
+    for (int g = 0; g < S.nb4; g += 4) {
+        const float4 b0 = S.bound[g], b1 = S.bound[g + 1], b2 = S.bound[g + 2], b3 = S.bound[g + 3];
+        const float s0 = gap(b0), s1 = gap(b1), s2 = gap(b2), s3 = gap(b3);
+        if (fminf(fminf(s0, s1), fminf(s2, s3)) <= margin) {
+            unsigned cand = (s0 <= margin ? 1u : 0u) | (s1 <= margin ? 2u : 0u) | (s2 <= margin ? 4u : 0u) | (s3 <= margin ? 8u : 0u);
+            do {
+                const int k = __ffs(cand) - 1;
+                cand &= cand - 1u;
+                exact(g + k);
+            } while (cand);
+        }
+    }
+}
+
+template <bool kCollect, bool kCubes, bool kFilter>
 __device__ __forceinline__ void intersect32(const Streams32& S, F3 o, F3 d, float& best_t, int& hit, float2* neg, int& n_neg) {
     hit = -1;
     if (kCollect) n_neg = 0;
@@ -89,8 +125,7 @@ __device__ __forceinline__ void intersect32(const Streams32& S, F3 o, F3 d, floa
         float t = -oy * rcp(dy);
         if (t >= 0.f && t < best_t) { best_t = t; hit = i; }  // dy ~ 0 -> t = +-inf or NaN: never taken
     }
-#pragma unroll 2
-    for (int i = 0; i < S.nu; ++i) {                     // Sphere::intersect_local, src/shape.rs:361-375
+    auto usph = [&](int i) {                             // Sphere::intersect_local, src/shape.rs:361-375
         float4 sp = S.usph[i];
         F3 L = mk(o.x - sp.x, o.y - sp.y, o.z - sp.z);
         // b^2 - a c cancels catastrophically in f32 for a small sphere far away (b^2 ~ c ~ 10^3, r^2 ~ 10^-2):
@@ -105,8 +140,8 @@ __device__ __forceinline__ void intersect32(const Streams32& S, F3 o, F3 d, floa
             if (t >= 0.f && t < best_t) { best_t = t; hit = S.np + i; }
             if (kCollect && t1 < 0.f) { keep(t1, 2 * (S.np + i)); if (t2 < 0.f) keep(t2, 2 * (S.np + i) + 1); }
         }
-    }
-    for (int i = 0; i < S.ng; ++i) {                     // Shape::intersect: ray.transform(inverse) first
+    };
+    auto gsph = [&](int i) {                             // Shape::intersect: ray.transform(inverse) first
         float4 r0 = S.gsph[3 * i], r1 = S.gsph[3 * i + 1], r2 = S.gsph[3 * i + 2];
         F3 lo = mk(row4(r0, o), row4(r1, o), row4(r2, o));
         F3 ld = mk(row3(r0, d), row3(r1, d), row3(r2, d));
@@ -118,14 +153,26 @@ __device__ __forceinline__ void intersect32(const Streams32& S, F3 o, F3 d, floa
         float t = t1 >= 0.f ? t1 : t2;
         if (dn >= 0.f && t >= 0.f && t < best_t) { best_t = t; hit = S.np + S.nu + i; }
         if (kCollect && dn >= 0.f && t1 < 0.f) { keep(t1, 2 * (S.np + S.nu + i)); if (t2 < 0.f) keep(t2, 2 * (S.np + S.nu + i) + 1); }
-    }
-    if (kCubes) for (int i = S.ng; i < S.ng + S.nc; ++i) {   // Cube
+    };
+    auto cube = [&](int i) {                             // Cube
         float t1, t2;
         if (cube_slab32(S.gsph + 3 * i, o, d, t1, t2)) {
             float t = t1 >= 0.f ? t1 : t2;
             if (t >= 0.f && t < best_t) { best_t = t; hit = S.np + S.nu + i; }
             if (kCollect && t1 < 0.f) { keep(t1, 2 * (S.np + S.nu + i)); if (t2 < 0.f) keep(t2, 2 * (S.np + S.nu + i) + 1); }
         }
+    };
+    if (kFilter) {
+        sweep_bounds(S, o, d, [&](int i) {
+            if (i < S.nu) usph(i);
+            else if (!kCubes || i - S.nu < S.ng) gsph(i - S.nu);
+            else cube(i - S.nu);
+        });
+    } else {
+#pragma unroll 2
+        for (int i = 0; i < S.nu; ++i) usph(i);
+        for (int i = 0; i < S.ng; ++i) gsph(i);
+        if (kCubes) for (int i = S.ng; i < S.ng + S.nc; ++i) cube(i);
     }
 }
 
@@ -291,7 +338,7 @@ __device__ __forceinline__ F3 pattern_at32(int kind, F3 a, F3 b, F3 p) {
 // a plane is a sign change of f(t) = n.(p + t d) + w between t=0 and t=1, and for a sphere needs
 // no square root: f(0) f(1) < 0 (one root inside) or both roots inside.  f(1) depends only on the
 // light and is precomputed per shape (plL / usL, staged beside the streams).
-template <bool kCubes>
+template <bool kCubes, bool kFilter>
 __device__ __forceinline__ bool shadow32(const Streams32& S, const float* __restrict__ plL, const float* __restrict__ usL,
                                          bool light_inside, F3 o, F3 d) {
     // every test is reduced to "g <= 0" and the g's are min-accumulated: FMNMX instead of predicates
@@ -303,53 +350,63 @@ __device__ __forceinline__ bool shadow32(const Streams32& S, const float* __rest
         float4 pl = S.planes[i];
         g = fminf(g, row4(pl, o) * plL[i]);            // f(0) f(1) <= 0: the two ends on opposite sides
     }
-    if (!light_inside) {
-#pragma unroll 2
-        for (int i = 0; i < S.nu; ++i) {
-            float4 sp = S.usph[i];
-            F3 L = mk(o.x - sp.x, o.y - sp.y, o.z - sp.z);
-            // f(t) = |L + t d|^2 - r^2 is convex: its minimum over [0,1] is at tc = clamp(-b/a, 0, 1); evaluated
-            // as |L + tc d|^2 - r^2 (no cancellation between large terms)
-            float tc = __saturatef(-dot(d, L) * inv_a);
-            F3 q = fma3(d, tc, L);
-            g = fminf(g, fmaf(q.z, q.z, fmaf(q.y, q.y, fmaf(q.x, q.x, -sp.w))));
+    bool hit = false;
+    auto usph = [&](int i) {
+        float4 sp = S.usph[i];
+        F3 L = mk(o.x - sp.x, o.y - sp.y, o.z - sp.z);
+        // f(t) = |L + t d|^2 - r^2 is convex: its minimum over [0,1] is at tc = clamp(-b/a, 0, 1); evaluated
+        // as |L + tc d|^2 - r^2 (no cancellation between large terms)
+        float tc = __saturatef(-dot(d, L) * inv_a);
+        F3 q = fma3(d, tc, L);
+        g = fminf(g, fmaf(q.z, q.z, fmaf(q.y, q.y, fmaf(q.x, q.x, -sp.w))));
+    };
+    auto usph_in = [&](int i) {  // the light sits inside some sphere: a segment entirely inside it (f0 < 0 and f1 < 0) has no root
+        float4 sp = S.usph[i];
+        F3 L = mk(o.x - sp.x, o.y - sp.y, o.z - sp.z);
+        float f0 = fmaf(L.z, L.z, fmaf(L.y, L.y, fmaf(L.x, L.x, -sp.w)));
+        float tc = __saturatef(-dot(d, L) * inv_a);
+        F3 q = fma3(d, tc, L);
+        float fmin = fmaf(q.z, q.z, fmaf(q.y, q.y, fmaf(q.x, q.x, -sp.w)));
+        g = fminf(g, fmaxf(fmin, -fmaxf(f0, usL[i])));
+    };
+    auto gsph = [&](int i) {     // genuinely affine spheres: nearest-root test in object space
+        float4 r0 = S.gsph[3 * i], r1 = S.gsph[3 * i + 1], r2 = S.gsph[3 * i + 2];
+        F3 lo = mk(row4(r0, o), row4(r1, o), row4(r2, o));
+        F3 ld = mk(row3(r0, d), row3(r1, d), row3(r2, d));
+        float inv = rcp(dot(ld, ld)), bia = dot(ld, lo) * inv;
+        F3 q = mk(fmaf(-bia, ld.x, lo.x), fmaf(-bia, ld.y, lo.y), fmaf(-bia, ld.z, lo.z));
+        float dn = fmaf(-q.z, q.z, fmaf(-q.y, q.y, fmaf(-q.x, q.x, 1.f)));
+        if (dn >= 0.f) {
+            float s = sqrtf(dn * inv);
+            float t1 = -bia - s, t2 = s - bia;
+            float t = t1 >= 0.f ? t1 : t2;
+            hit |= t >= 0.f && t < 1.f;
         }
-    } else {  // the light sits inside some sphere: a segment entirely inside it (f0 < 0 and f1 < 0) has no root
-        for (int i = 0; i < S.nu; ++i) {
-            float4 sp = S.usph[i];
-            F3 L = mk(o.x - sp.x, o.y - sp.y, o.z - sp.z);
-            float f0 = fmaf(L.z, L.z, fmaf(L.y, L.y, fmaf(L.x, L.x, -sp.w)));
-            float tc = __saturatef(-dot(d, L) * inv_a);
-            F3 q = fma3(d, tc, L);
-            float fmin = fmaf(q.z, q.z, fmaf(q.y, q.y, fmaf(q.x, q.x, -sp.w)));
-            g = fminf(g, fmaxf(fmin, -fmaxf(f0, usL[i])));
-        }
-    }
-    bool hit = g <= 0.f;
-    if (S.ng > 0) {  // genuinely affine spheres: nearest-root test in object space
-        for (int i = 0; i < S.ng; ++i) {
-            float4 r0 = S.gsph[3 * i], r1 = S.gsph[3 * i + 1], r2 = S.gsph[3 * i + 2];
-            F3 lo = mk(row4(r0, o), row4(r1, o), row4(r2, o));
-            F3 ld = mk(row3(r0, d), row3(r1, d), row3(r2, d));
-            float inv = rcp(dot(ld, ld)), bia = dot(ld, lo) * inv;
-            F3 q = mk(fmaf(-bia, ld.x, lo.x), fmaf(-bia, ld.y, lo.y), fmaf(-bia, ld.z, lo.z));
-            float dn = fmaf(-q.z, q.z, fmaf(-q.y, q.y, fmaf(-q.x, q.x, 1.f)));
-            if (dn >= 0.f) {
-                float s = sqrtf(dn * inv);
-                float t1 = -bia - s, t2 = s - bia;
-                float t = t1 >= 0.f ? t1 : t2;
-                hit |= t >= 0.f && t < 1.f;
-            }
-        }
-    }
-    if (kCubes) for (int i = S.ng; i < S.ng + S.nc; ++i) {   // cubes: nearest non-negative root below 1
+    };
+    auto cube = [&](int i) {     // cubes: nearest non-negative root below 1
         float t1, t2;
         if (cube_slab32(S.gsph + 3 * i, o, d, t1, t2)) {
             float t = t1 >= 0.f ? t1 : t2;
             hit |= t >= 0.f && t < 1.f;
         }
+    };
+    if (kFilter) {
+        sweep_bounds(S, o, d, [&](int i) {
+            if (i < S.nu) { if (light_inside) usph_in(i); else usph(i); }
+            else if (!kCubes || i - S.nu < S.ng) gsph(i - S.nu);
+            else cube(i - S.nu);
+        });
+    } else {
+        if (!light_inside) {
+#pragma unroll 2
+            for (int i = 0; i < S.nu; ++i) usph(i);
+        } else {
+            for (int i = 0; i < S.nu; ++i) usph_in(i);
+        }
+        for (int i = 0; i < S.ng; ++i) gsph(i);
+        if (kCubes) for (int i = S.ng; i < S.ng + S.nc; ++i) cube(i);
     }
-    return hit;
+    return hit || g <= 0.f;
 }
 
 // compute_refractive when every world_id is unique (<= 255 shapes): a shape is a container iff it
@@ -434,9 +491,9 @@ __device__ __noinline__ void compute_refractive32_unique(const Streams32& S, con
 #endif
 // kSmem: shading records staged to shared memory; kUnique: world_ids are unique (<= 255 shapes);
 // kGlobal: the intersect streams stay in global memory (read through L1/L2 as warp-uniform loads) —
-// scenes of any size, e.g. the 10k-shape config C4.
+// scenes of any size, e.g. the 10k-shape config C4; 2 = with the bounding-sphere filter in front (sweep_bounds).
 // kCubes: the scene has cubes (object-space slab tests behind the general spheres); scenes without them compile none of it
-template <bool kSmem, bool kUnique, bool kGlobal, bool kCubes>
+template <bool kSmem, bool kUnique, int kGlobal, bool kCubes>
 __global__ void __launch_bounds__(kThreads, RTC_F32_MIN_BLOCKS)
 render_f32_kernel(DevScene32 sc, CamParams cam, void* __restrict__ out_rgb, uint8_t* __restrict__ out_hit,
                   Counters* __restrict__ counters, unsigned* __restrict__ work) {
@@ -451,6 +508,8 @@ render_f32_kernel(DevScene32 sc, CamParams cam, void* __restrict__ out_rgb, uint
     const int n_gset = sc.n_gset;
     const F3 light_pos = mk(sc.light_pos[0], sc.light_pos[1], sc.light_pos[2]);
     const F3 light_int = mk(sc.light_int[0], sc.light_int[1], sc.light_int[2]);
+    constexpr bool kFilter = kGlobal == 2;
+    S.bound = sc.bound; S.nb4 = sc.n_bound4; S.cmax = sc.bound_cmax; S.rmax = sc.bound_rmax;
     if (kGlobal) {
         S.planes = sc.planes; S.usph = sc.usph; S.gsph = sc.gsph; S.pl_index = sc.pl_index; S.us_index = sc.us_index; S.gs_index = sc.gs_index;
         plL = sc.plL; usL = sc.usL; gset = sc.gset;
@@ -591,7 +650,7 @@ render_f32_kernel(DevScene32 sc, CamParams cam, void* __restrict__ out_rgb, uint
         // ---------------------------------------------------------------- phase A: World::intersect, radiance rays
         float t = __int_as_float(0x7f800000);
         int hit = -1;
-        if (has_ray) { intersect32<!kUnique, kCubes>(S, ro, rd, t, hit, neg, n_neg); ++n_rays; }
+        if (has_ray) { intersect32<!kUnique, kCubes, kFilter>(S, ro, rd, t, hit, neg, n_neg); ++n_rays; }
         if (has_ray && is_primary && hit >= 0) { hitbits |= 1u << sub; ++n_phits; }
         if (hit < 0) has_ray = false;   // World::color_at -> background_color (black), src/shape.rs:708
 
@@ -631,7 +690,7 @@ render_f32_kernel(DevScene32 sc, CamParams cam, void* __restrict__ out_rgb, uint
 
         // ---------------------------------------------------------------- phase C: is_shadowed (any-hit)
         bool shadowed = false;
-        if (hit >= 0) { shadowed = shadow32<kCubes>(S, plL, usL, light_inside, hp, light_pos - hp); ++n_rays; ++n_shaded; }
+        if (hit >= 0) { shadowed = shadow32<kCubes, kFilter>(S, plL, usL, light_inside, hp, light_pos - hp); ++n_rays; ++n_shaded; }
 
         // ---------------------------------------------------------------- phase D: shade_hit
         if (hit >= 0) {
@@ -758,9 +817,10 @@ cudaError_t launch_render_f32(const DevScene32& scene, const CamParams& cam, voi
     const bool uniq = scene.ids_unique != 0, cubes = scene.n_cube > 0;
 #define RTC_LAUNCH32(SM, GL) (uniq ? (cubes ? launch(render_f32_kernel<SM, true, GL, true>) : launch(render_f32_kernel<SM, true, GL, false>)) \
                                    : (cubes ? launch(render_f32_kernel<SM, false, GL, true>) : launch(render_f32_kernel<SM, false, GL, false>)))
-    if (global_streams) e = RTC_LAUNCH32(false, true);
-    else if (small) e = RTC_LAUNCH32(true, false);
-    else e = RTC_LAUNCH32(false, false);
+    if (global_streams && scene.n_bound4 > 0) e = RTC_LAUNCH32(false, 2);
+    else if (global_streams) e = RTC_LAUNCH32(false, 1);
+    else if (small) e = RTC_LAUNCH32(true, 0);
+    else e = RTC_LAUNCH32(false, 0);
 #undef RTC_LAUNCH32
     if (e != cudaSuccess) return e;
     return cudaGetLastError();

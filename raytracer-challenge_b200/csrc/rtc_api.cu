@@ -11,6 +11,7 @@
 #include <string>
 #include <condition_variable>
 #include <functional>
+#include <limits>
 #include <mutex>
 #include <thread>
 #include <vector>
@@ -63,7 +64,7 @@ struct DeviceState {
     cudaEvent_t ev_band[8] = {}, ev_copy[8] = {};
     // scene
     DevBuf<double2> sph64, pl64;
-    DevBuf<float4> pl32, us32, gs32;
+    DevBuf<float4> pl32, us32, gs32, bound;
     DevBuf<int32_t> sph_index, pl_index, us_index, gs_index, gset;
     DevBuf<float> plL, usL;
     DevBuf<ShadeRec64> rec64;
@@ -238,6 +239,8 @@ struct HostScene {
     int n_spheres = 0, n_gsph = 0, n_cubes = 0;
     std::vector<float> plL, usL;
     int light_inside = 0;
+    std::vector<float4> bound;            // bounding spheres of us32 | gs32 objects (DevScene32::bound)
+    float bound_cmax = 0.f, bound_rmax = 0.f;
     std::vector<ShadeRec64> rec64;
     std::vector<ShadeRec32> rec32;
     int ids_unique = 1;
@@ -261,6 +264,53 @@ void mul34(const double* a, const double* b, double* out) {  // (a as 3x4 affine
             if (c == 3) s += a[4 * r + 3];
             out[4 * r + c] = s;
         }
+}
+
+// Smallest and largest eigenvalue of a symmetric 3x3 matrix (cyclic Jacobi rotations).
+void sym3_eig_minmax(double g[3][3], double& lo, double& hi) {
+    for (int sweep = 0; sweep < 32; ++sweep) {
+        double off = std::fabs(g[0][1]) + std::fabs(g[0][2]) + std::fabs(g[1][2]);
+        if (off <= 1e-300 || off <= 1e-18 * (std::fabs(g[0][0]) + std::fabs(g[1][1]) + std::fabs(g[2][2]))) break;
+        for (int p = 0; p < 2; ++p)
+            for (int q = p + 1; q < 3; ++q) {
+                if (g[p][q] == 0.0) continue;
+                double theta = (g[q][q] - g[p][p]) / (2.0 * g[p][q]);
+                double t = (theta >= 0 ? 1.0 : -1.0) / (std::fabs(theta) + std::sqrt(theta * theta + 1.0));
+                double c = 1.0 / std::sqrt(t * t + 1.0), sn = t * c;
+                for (int k = 0; k < 3; ++k) { double a = g[k][p], b = g[k][q]; g[k][p] = c * a - sn * b; g[k][q] = sn * a + c * b; }
+                for (int k = 0; k < 3; ++k) { double a = g[p][k], b = g[q][k]; g[p][k] = c * a - sn * b; g[q][k] = sn * a + c * b; }
+            }
+    }
+    lo = std::min(g[0][0], std::min(g[1][1], g[2][2]));
+    hi = std::max(g[0][0], std::max(g[1][1], g[2][2]));
+}
+
+// World-space bounding sphere of {p : |A p + t|_2 <= unit_radius} (A, t = the shape's inverse, rows 0..2):
+// centre = -A^-1 t, radius = unit_radius / sigma_min(A), padded for the f32 rounding of the coefficients
+// the exact tests read.  Returns false when A is too close to singular for the bound to mean anything.
+bool bounding_sphere(const double* inv, double unit_radius, double c[3], double& radius) {
+    const double a[3][3] = {{inv[0], inv[1], inv[2]}, {inv[4], inv[5], inv[6]}, {inv[8], inv[9], inv[10]}};
+    const double t[3] = {inv[3], inv[7], inv[11]};
+    const double det = a[0][0] * (a[1][1] * a[2][2] - a[1][2] * a[2][1]) - a[0][1] * (a[1][0] * a[2][2] - a[1][2] * a[2][0]) +
+                       a[0][2] * (a[1][0] * a[2][1] - a[1][1] * a[2][0]);
+    if (!(std::fabs(det) > 0.0) || !std::isfinite(det)) return false;
+    double m[3][3];   // A^-1 by cofactors
+    for (int i = 0; i < 3; ++i)
+        for (int j = 0; j < 3; ++j) {
+            const int i1 = (i + 1) % 3, i2 = (i + 2) % 3, j1 = (j + 1) % 3, j2 = (j + 2) % 3;
+            m[j][i] = (a[i1][j1] * a[i2][j2] - a[i1][j2] * a[i2][j1]) / det;
+        }
+    for (int i = 0; i < 3; ++i) c[i] = -(m[i][0] * t[0] + m[i][1] * t[1] + m[i][2] * t[2]);
+    double g[3][3];
+    for (int i = 0; i < 3; ++i)
+        for (int j = 0; j < 3; ++j) g[i][j] = a[0][i] * a[0][j] + a[1][i] * a[1][j] + a[2][i] * a[2][j];
+    double lo, hi;
+    sym3_eig_minmax(g, lo, hi);
+    if (!(lo > 0.0) || !std::isfinite(hi)) return false;
+    const double cond = std::sqrt(hi / lo);
+    const double cn = std::fabs(c[0]) + std::fabs(c[1]) + std::fabs(c[2]);
+    radius = unit_radius / std::sqrt(lo) * (1.0 + 1e-4) + 4.0 * 5.97e-8 * cn * cond;
+    return std::isfinite(radius) && std::isfinite(cn);
 }
 
 int flatten(const rtc_light* light, const rtc_shape* shapes, size_t n, HostScene& hs) {
@@ -380,6 +430,34 @@ int flatten(const rtc_light* light, const rtc_shape* shapes, size_t n, HostScene
     for (int k = 0; k < np; ++k) if (shapes[hs.pl_index[k]].refractive_index != 1.0) hs.gset.push_back(k);
     for (int k = 0; k < nu; ++k) if (shapes[hs.us_index[k]].refractive_index != 1.0) hs.gset.push_back(np + k);
     for (int k = 0; k < (int)hs.gs_index.size(); ++k) if (shapes[hs.gs_index[k]].refractive_index != 1.0) hs.gset.push_back(np + nu + k);
+
+    // bounding spheres in stream order (uniform spheres are their own bound); a shape without a finite bound
+    // switches the filter off for the scene
+    {
+        bool ok = true;
+        double cmax = 0.0, rmax = 0.0;
+        for (int k = 0; k < nu; ++k) {
+            const float4& u = hs.us32[k];
+            hs.bound.push_back(make_float4(u.x, u.y, u.z, -u.w));
+            cmax = std::max(cmax, (double)std::fabs(u.x) + std::fabs(u.y) + std::fabs(u.z));
+            rmax = std::max(rmax, std::sqrt((double)u.w));
+            ok = ok && std::isfinite(u.w) && std::isfinite(cmax);
+        }
+        for (int k = 0; ok && k < (int)hs.gs_index.size(); ++k) {
+            double c[3], r = 0.0;
+            ok = bounding_sphere(shapes[hs.gs_index[k]].inv, k < hs.n_gsph ? 1.0 : std::sqrt(3.0), c, r);
+            if (!ok) break;
+            hs.bound.push_back(make_float4((float)c[0], (float)c[1], (float)c[2], -(float)(r * r)));
+            cmax = std::max(cmax, std::fabs(c[0]) + std::fabs(c[1]) + std::fabs(c[2]));
+            rmax = std::max(rmax, r);
+        }
+        ok = ok && std::isfinite(cmax) && std::isfinite(rmax) && cmax < 1e15 && rmax < 1e15;
+        if (!ok) hs.bound.clear();
+        else {
+            while (hs.bound.size() % 4) hs.bound.push_back(make_float4(0.f, 0.f, 0.f, std::numeric_limits<float>::infinity()));
+            hs.bound_cmax = (float)(cmax * (1.0 + 1e-6)); hs.bound_rmax = (float)(rmax * (1.0 + 1e-6));
+        }
+    }
 
     // light-only terms of the shadow test (f32, from the f32 coefficients the kernels use)
     {
@@ -633,7 +711,11 @@ int launch_on(DeviceState& d, const CamParams& cp, int precision, int flags, voi
             P.order = d.order.p;
         }
         e = launch_render_f32_small(P, cp.out_format, d_rgb, d_hit, d_counters, d.work.p, st);
-    } else e = launch_render_f32(d.s32, cp, d_rgb, d_hit, d_counters, d.work.p, st);
+    } else {
+        DevScene32 s32 = d.s32;
+        if (flags & RTC_OPT_NO_BOUND_FILTER) s32.n_bound4 = 0;
+        e = launch_render_f32(s32, cp, d_rgb, d_hit, d_counters, d.work.p, st);
+    }
     if (e != cudaSuccess) return fail(RTC_ERR_CUDA, std::string("kernel launch: ") + cudaGetErrorString(e));
     return RTC_OK;
 }
@@ -702,7 +784,7 @@ void rtc_context_destroy(rtc_context* ctx) {
     for (DeviceState& d : ctx->devs) {
         cudaSetDevice(d.dev);
         if (d.stream) cudaStreamSynchronize(d.stream);
-        d.sph64.release(); d.pl64.release(); d.pl32.release(); d.us32.release(); d.gs32.release(); d.us_index.release(); d.gs_index.release(); d.gset.release(); d.plL.release(); d.usL.release();
+        d.sph64.release(); d.pl64.release(); d.pl32.release(); d.us32.release(); d.gs32.release(); d.us_index.release(); d.gs_index.release(); d.gset.release(); d.plL.release(); d.usL.release(); d.bound.release();
         d.sph_index.release(); d.pl_index.release(); d.rec64.release(); d.rec32.release(); d.srec.release();
         d.rgb.release(); d.hit.release(); d.counters.release(); d.work.release(); d.order.release();
         if (d.ev_k0) cudaEventDestroy(d.ev_k0);
@@ -739,6 +821,7 @@ int rtc_scene_upload(rtc_context* ctx, const rtc_light* light, const rtc_shape* 
         CUDA_TRY(upload(d.gset, hs.gset, d.stream));
         CUDA_TRY(upload(d.plL, hs.plL, d.stream));
         CUDA_TRY(upload(d.usL, hs.usL, d.stream));
+        CUDA_TRY(upload(d.bound, hs.bound, d.stream));
         CUDA_TRY(upload(d.sph_index, hs.sph_index, d.stream));
         CUDA_TRY(upload(d.pl_index, hs.pl_index, d.stream));
         CUDA_TRY(upload(d.rec64, hs.rec64, d.stream));
@@ -762,6 +845,7 @@ int rtc_scene_upload(rtc_context* ctx, const rtc_light* light, const rtc_shape* 
         d.s32.gset = d.gset.p; d.s32.n_gset = (int)hs.gset.size();
         d.s32.plL = d.plL.p; d.s32.usL = d.usL.p; d.s32.light_inside = hs.light_inside;
         d.s32.rec = d.rec32.p;
+        d.s32.bound = d.bound.p; d.s32.n_bound4 = (int)hs.bound.size(); d.s32.bound_cmax = hs.bound_cmax; d.s32.bound_rmax = hs.bound_rmax;
         for (int k = 0; k < 3; ++k) {
             d.s64.light_pos[k] = light->position[k]; d.s64.light_int[k] = light->intensity[k];
             d.s32.light_pos[k] = (float)light->position[k]; d.s32.light_int[k] = (float)light->intensity[k];

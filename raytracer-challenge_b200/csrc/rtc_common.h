@@ -82,6 +82,13 @@ struct DevScene32 {
     const float* plL;          // [n_planes] f(light) = n.light + w   (shadow test: f(0) f(1) <= 0)
     const float* usL;          // [n_usph]   |light - c|^2 - r^2
     int light_inside;          // the light sits inside some uniform sphere
+    // Bounding spheres (cx, cy, cz, -R^2) of the uniform spheres | general spheres | cubes, in stream order,
+    // padded to a multiple of four with (0, 0, 0, +inf).  Scenes whose streams stay in global memory (10^3+
+    // shapes) test a ray against these first — 9 FFMA per shape — and run the exact test of a shape only
+    // when the ray's line passes within R + rounding margin of its centre.  n_bound4 = 0: no filter.
+    const float4* bound;
+    int n_bound4;
+    float bound_cmax, bound_rmax;   // max |c|_1 and max R over the entries (rounding margin of the filter)
     float light_pos[3];
     float light_int[3];
 };

@@ -21,6 +21,7 @@ RTC_MAX_DEPTH = 8
 OPT_DST_FULL_FRAME = 1
 OPT_F32_GENERAL_KERNEL = 2
 OPT_LINEAR_TILE_ORDER = 4
+OPT_NO_BOUND_FILTER = 8
 IPC_HANDLE_BYTES = 64
 
 

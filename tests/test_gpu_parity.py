@@ -514,6 +514,57 @@ def test_c4_synthetic_10k_4k_lattice(rtc, orc, renderer, c4_flat):
     _lattice_check(rtc, orc, renderer, c4_flat, cam, step=32, n_random=1024, f32_min_ok=0.97)
 
 
+def _big_mixed_world(rtc):
+    """6,000 random spheres (every 10th affine) + 300 cubes and 60 needle-like ellipsoids: more than fits the
+    shared-memory streams, so the f32 general kernel keeps them in global memory behind the bounding-sphere filter."""
+    import math
+    from rtc_b200.scene import Cube, Material, Sphere, Color
+    from rtc_b200.transform import Matrix
+    w = rtc.scenes.synthetic_scene(n_spheres=6000, seed=0xC0BE)
+    u = lambda i, k: rtc.scenes._u01(0xC0BE5, i, k)
+    for i in range(300):
+        m = Matrix.identity().scaling(0.1 + 0.5 * u(i, 0), 0.1 + 0.5 * u(i, 1), 0.1 + 0.5 * u(i, 2))
+        m = m.rotation_x(6.283 * u(i, 3)).rotation_y(6.283 * u(i, 4)).translation(-18 + 36 * u(i, 5), 0.5 + 9 * u(i, 6), -18 + 36 * u(i, 7))
+        glass = i % 7 == 0
+        w.add_shape(Cube(m, Material(color=Color(0.2 + 0.7 * u(i, 8), 0.2 + 0.7 * u(i, 9), 0.3), reflectiveness=0.5 if glass else 0.1,
+                                     transparency=0.8 if glass else 0.0, refractive_index=1.5 if glass else 1.0)))
+    for i in range(60):
+        m = Matrix.identity().scaling(0.02, 1.5 + 2 * u(i, 10), 0.05).rotation_z(6.283 * u(i, 11)).rotation_y(6.283 * u(i, 12))
+        m = m.translation(-15 + 30 * u(i, 13), 2 + 6 * u(i, 14), -15 + 30 * u(i, 15))
+        w.add_shape(Sphere(m, Material(color=Color(0.9, 0.4, 0.1), reflectiveness=0.3)))
+    return w
+
+
+def test_bounding_sphere_filter_changes_nothing(rtc, renderer, c4_flat):
+    """Scenes whose streams stay in global memory run the exact shape tests behind a bounding-sphere filter
+    (render_f32.cu sweep_bounds).  The filter is conservative: the frame, the hit mask and the ray counters are
+    those of the plain brute-force loops (RTC_OPT_NO_BOUND_FILTER), bit for bit — spheres, affine spheres,
+    cubes, needle-shaped ellipsoids, aliased world_ids."""
+    import torch
+    ffi = rtc.ffi
+    for flat, cam in ((c4_flat, rtc.scenes.synthetic_camera(640, 360)),
+                      (_big_mixed_world(rtc).flatten(), rtc.scenes.synthetic_camera(480, 270))):
+        renderer.upload_flat(*flat)
+        d = cam.flatten()
+        out = []
+        for flags in (0, ffi.OPT_NO_BOUND_FILTER):
+            buf = torch.empty((d.vsize, d.hsize, 3), dtype=torch.float32, device="cuda")
+            hit = torch.empty((d.vsize, d.hsize), dtype=torch.uint8, device="cuda")
+            st = ffi.RtcStats()
+            renderer.render_device(d, rtc.Renderer.make_opts(precision=ffi.PRECISION_F32_FAST, out_format=ffi.OUT_F32_RGB, flags=flags),
+                                   buf.data_ptr(), hit.data_ptr(), None, st)
+            out.append((buf, hit, (st.rays, st.primary_hits, st.shaded_hits, st.shadow_rays)))
+        assert torch.equal(out[0][1], out[1][1])
+        assert torch.equal(out[0][0], out[1][0])
+        assert out[0][2] == out[1][2] and out[0][2][0] > d.hsize * d.vsize
+
+
+def test_big_mixed_world_f64_parity_and_f32(rtc, orc, renderer):
+    """The same mixed world against the oracle (f64 parity; f32 within the C4 tolerance) on a small frame."""
+    cam = rtc.scenes.synthetic_camera(96, 54)
+    _lattice_check(rtc, orc, renderer, _big_mixed_world(rtc).flatten(), cam, step=1, n_random=0, f32_min_ok=0.97)
+
+
 def test_c5_8k_supersampled_lattice(rtc, orc, renderer):
     """C5: the reflect/refract room at 7680x4320 with the deterministic 2x2 supersample (samples = 0)."""
     world = rtc.scenes.reflect_refract_scene()
