@@ -34,8 +34,8 @@ enum {
     RTC_OK = 0,
     RTC_ERR_INVALID_ARG = 1,  /* null pointer, bad enum, bad size */
     RTC_ERR_UNSUPPORTED = 2,  /* e.g. material with neither colour nor pattern (the reference
-                                 panics: src/material.rs:331), samples >= 2 (rand::thread_rng,
-                                 src/camera.rs:84-92) */
+                                 panics: src/material.rs:331), samples > 255 (a u8 in the
+                                 reference, src/camera.rs:26) */
     RTC_ERR_NO_DEVICE = 3,    /* no CUDA device / driver: the path never falls back to the CPU */
     RTC_ERR_CUDA = 4,         /* a CUDA runtime call failed; see rtc_last_error() */
     RTC_ERR_NO_SCENE = 5,     /* rtc_render* before rtc_scene_upload */
@@ -92,8 +92,20 @@ typedef struct rtc_light {
 } rtc_light;
 
 /* Camera (src/camera.rs:16-27): the derived fields computed by Camera::new (:39-58) and
- * the private view_transform_inv (:25).  samples = antialiasing_samples: 1 = one centre
- * sample, 0 = the deterministic 2x2 supersample (:96-113 with an empty resample loop). */
+ * the private view_transform_inv (:25).  samples = antialiasing_samples (a u8, 0..255), Camera::render_pixel
+ * (:94-114): 1 = one centre sample; otherwise four fixed sub-samples at (.25/.75)^2, their mean, and — when
+ * any of the four is further than 0.01 from the mean (Color::distance_from, src/color.rs:122-126) — `samples`
+ * extra samples at random sub-pixel offsets, the mean taken over all 4 + samples (Camera::resample, :84-92).
+ * samples = 0 is therefore the deterministic 2x2 supersample.
+ *
+ * Resample offsets.  The reference draws them from rand::thread_rng() (:85-89; x offset first, then y), so two
+ * of its own runs differ.  Here they come from a counter-based stream, reproducible and independent of the
+ * order pixels are rendered in:
+ *     u(pixel, k, axis) = splitmix64( splitmix64(aa_seed) ^ ((pixel_index << 9) | (k << 1) | axis) )
+ *     splitmix64(x): x += 0x9E3779B97F4A7C15; x = (x ^ x>>30) * 0xBF58476D1CE4E5B9;
+ *                    x = (x ^ x>>27) * 0x94D049BB133111EB; return x ^ x>>31          (64-bit wrap-around)
+ *     offset = (u >> 11) * 2^-53 in [0, 1)      (f32 fast mode: (u >> 40) * 2^-24)
+ * with pixel_index = y*hsize + x, k = 0..samples-1 the extra sample, axis 0 = x, 1 = y. */
 typedef struct rtc_camera {
     uint32_t hsize;
     uint32_t vsize;
@@ -102,7 +114,7 @@ typedef struct rtc_camera {
     double pixel_size;
     double view_inv[16];
     uint32_t samples;
-    uint32_t reserved;
+    uint32_t aa_seed;   /* seed of the resample offsets (samples >= 2); any value */
 } rtc_camera;
 
 enum { RTC_PRECISION_F64_PARITY = 0, RTC_PRECISION_F32_FAST = 1 };
@@ -186,7 +198,8 @@ int rtc_scene_upload(rtc_context* ctx, const rtc_light* light, const rtc_shape* 
  * caller's HOST buffers.  out_rgb: hsize*vsize*3 elements of opts->out_format, row-major
  * y*hsize+x (Canvas.pixels, src/canvas.rs:43-46); pixels outside the rect are 0 (src/canvas.rs:37-41).
  * out_hit_mask (nullable): hsize*vsize bytes, bit k set when sub-sample k's primary ray hit
- * a shape (World::color_at's Some/None, src/shape.rs:704-709).  stats nullable. */
+ * a shape (World::color_at's Some/None, src/shape.rs:704-709; the four fixed sub-samples only, not the
+ * resample pass).  stats nullable. */
 int rtc_render(rtc_context* ctx, const rtc_camera* cam, const rtc_render_opts* opts, void* out_rgb,
                uint8_t* out_hit_mask, rtc_stats* stats);
 

@@ -108,7 +108,8 @@ int orc_render(const orc_world* w, const rtc_camera* cam, int rect, int max_dept
         c.view_transform_inv = Matrix::from_row_major(cam->view_inv);
         c.antialiasing_samples = (uint8_t)cam->samples;
         c.max_reflections = (uint8_t)max_depth;
-        if (cam->samples > 1) throw std::runtime_error("oracle: samples must be 0 or 1");
+        if (cam->samples > 255) throw std::runtime_error("oracle: antialiasing_samples is a u8 (src/camera.rs:26)");
+        c.aa_seed = cam->aa_seed;
         const size_t total = pixel_indices ? n_pixels : (size_t)cam->hsize * cam->vsize;
         const uint32_t xlim = rect == 0 ? cam->hsize - 1 : cam->hsize;
         const uint32_t ylim = rect == 0 ? cam->vsize - 1 : cam->vsize;
@@ -168,6 +169,33 @@ int orc_render(const orc_world* w, const rtc_camera* cam, int rect, int max_dept
         g_err = e.what();
         return 1;
     }
+}
+
+// One sample of Camera::render_pixel: world.color_at(camera.ray_for_pixel_offset(x, xo, y, yo), max_depth)
+// (src/camera.rs:64-76,96-105).  Lets the tests restate render_pixel / resample (:84-114) a second time, in
+// Python, on top of single samples, and compare that with orc_render's statement of it.
+int orc_sample(const orc_world* w, const rtc_camera* cam, uint32_t x, double xo, uint32_t y, double yo, int max_depth,
+               double* out_rgb) {
+    try {
+        Camera c(cam->hsize, cam->vsize, 0.0);
+        c.half_width = cam->half_width;
+        c.half_height = cam->half_height;
+        c.pixel_size = cam->pixel_size;
+        c.view_transform_inv = Matrix::from_row_major(cam->view_inv);
+        Color col = w->world.color_at(c.ray_for_pixel_offset(x, xo, y, yo), (uint8_t)max_depth);
+        out_rgb[0] = col.red; out_rgb[1] = col.green; out_rgb[2] = col.blue;
+        return 0;
+    } catch (const std::exception& e) {
+        g_err = e.what();
+        return 1;
+    }
+}
+
+// The resample offset stream of include/rtc.h ("Resample offsets") as the oracle states it.
+double orc_resample_offset(uint32_t aa_seed, uint32_t hsize, uint32_t x, uint32_t y, uint32_t k, uint32_t axis) {
+    Camera c(hsize, 1, 0.0);
+    c.aa_seed = aa_seed;
+    return c.resample_offset(x, y, k, axis);
 }
 
 // ---- restated transform builders, for checking the product's host mirror -------------------
@@ -231,7 +259,7 @@ int orc_camera_new(uint32_t hsize, uint32_t vsize, double fov, const double* vie
         out->pixel_size = c.pixel_size;
         c.view_transform_inv.to_row_major(out->view_inv);
         out->samples = 1;
-        out->reserved = 0;
+        out->aa_seed = 0;
         return 0;
     } catch (const std::exception& e) {
         g_err = e.what();

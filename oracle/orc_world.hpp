@@ -334,8 +334,26 @@ struct Camera {
         return Ray(origin, direction);
     }
     Ray ray_for_pixel(uint32_t x, uint32_t y) const { return ray_for_pixel_offset(x, 0.5, y, 0.5); }
-    // :94-114.  `hit_bits`: bit k = sub-sample k's primary ray hit something.
-    // samples >= 2 needs rand::thread_rng (src/camera.rs:84-92) -> not reproducible -> refused.
+    // Sub-pixel offsets of the resample pass.  The reference draws them from rand::thread_rng()
+    // (src/camera.rs:85-89: x offset first, then y, per extra sample), which no run can reproduce; the
+    // ABI (include/rtc.h, "Resample offsets") fixes a counter-based stream instead:
+    //   u(pixel, k, axis) = splitmix64( splitmix64(aa_seed) ^ ((pixel_index << 9) | (k << 1) | axis) )
+    //   offset = (u >> 11) * 2^-53   in [0, 1)
+    // PARITY UNPINNED against the reference for samples >= 2 (it is non-deterministic there); everything
+    // else in render_pixel / resample follows the reference statement by statement.
+    uint32_t aa_seed = 0;
+    static uint64_t splitmix64(uint64_t x) {
+        x += 0x9E3779B97F4A7C15ull;
+        x = (x ^ (x >> 30)) * 0xBF58476D1CE4E5B9ull;
+        x = (x ^ (x >> 27)) * 0x94D049BB133111EBull;
+        return x ^ (x >> 31);
+    }
+    double resample_offset(uint32_t x, uint32_t y, unsigned k, unsigned axis) const {
+        uint64_t pixel_index = (uint64_t)y * hsize + x;
+        uint64_t u = splitmix64(splitmix64((uint64_t)aa_seed) ^ ((pixel_index << 9) | ((uint64_t)k << 1) | axis));
+        return (double)(u >> 11) * (1.0 / 9007199254740992.0);
+    }
+    // :94-114 + resample :84-92.  `hit_bits`: bit k = fixed sub-sample k's primary ray hit something.
     Color render_pixel(uint32_t x, uint32_t y, const World& world, uint8_t* hit_bits = nullptr) const {
         bool h = false;
         if (antialiasing_samples == 1) {
@@ -343,8 +361,6 @@ struct Camera {
             if (hit_bits) *hit_bits = h ? 1 : 0;
             return c;
         } else {
-            if (antialiasing_samples != 0)
-                throw std::runtime_error("oracle: antialiasing_samples >= 2 is non-deterministic in the reference");
             static const double ox[4] = {0.25, 0.75, 0.25, 0.75};
             static const double oy[4] = {0.25, 0.25, 0.75, 0.75};
             std::vector<Color> sample;
@@ -358,7 +374,14 @@ struct Camera {
             bool any = false;
             for (const Color& c : sample)
                 if (c.distance_from(average) > 0.01) any = true;
-            if (any) average = Color::average_over(sample);  // resample with 0 extra samples (:84-92)
+            if (any) {                                                                 // resample, :84-92
+                for (unsigned k = 0; k < antialiasing_samples; ++k) {
+                    double xo = resample_offset(x, y, k, 0);   // Rust evaluates arguments left to right:
+                    double yo = resample_offset(x, y, k, 1);   // x's rng.gen() before y's
+                    sample.push_back(world.color_at(ray_for_pixel_offset(x, xo, y, yo), max_reflections));
+                }
+                average = Color::average_over(sample);
+            }
             return average;
         }
     }

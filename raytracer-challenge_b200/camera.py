@@ -191,6 +191,7 @@ class Camera:
         self.pixel_size = (self.half_width * 2.) / float(self.hsize)
         self.view_transform_inv = Matrix.identity()
         self.antialiasing_samples = 1
+        self.aa_seed = 0   # seed of the resample offsets (samples >= 2; include/rtc.h "Resample offsets")
 
     @staticmethod
     def new(hsize, vsize, fov):
@@ -202,7 +203,9 @@ class Camera:
         c.view_transform_inv = m.inverse()
         return c
 
-    def set_samples(self, n):  # :60
+    def set_samples(self, n):  # :60 (n: u8)
+        if not 0 <= int(n) <= 255:
+            raise ValueError("antialiasing_samples is a u8 (src/camera.rs:26)")
         self.antialiasing_samples = int(n)
 
     def flatten(self):
@@ -211,6 +214,7 @@ class Camera:
         d.half_width, d.half_height, d.pixel_size = self.half_width, self.half_height, self.pixel_size
         d.view_inv[:] = self.view_transform_inv.to_row_major()
         d.samples = self.antialiasing_samples
+        d.aa_seed = self.aa_seed & 0xffffffff
         return d
 
     def _render(self, world, rect, precision, renderer, max_depth):

@@ -28,10 +28,12 @@ constexpr int kThreads = 128;
 constexpr int kTileX = 8, kTileY = 4;
 constexpr int kBatch = kTileX * kTileY;  // pixels a warp claims per atomic: one 8x4 tile
 constexpr int kMaxStack = RTC_MAX_DEPTH;
+constexpr int kSubOutside = 1 << 20;   // sub-sample cursor of a pixel outside the rect: nothing to trace
 
 struct F3 { float x, y, z; };
 __device__ __forceinline__ F3 mk(float x, float y, float z) { F3 v; v.x = x; v.y = y; v.z = z; return v; }
 __device__ __forceinline__ F3 operator-(F3 a, F3 b) { return mk(a.x - b.x, a.y - b.y, a.z - b.z); }
+__device__ __forceinline__ F3 operator+(F3 a, F3 b) { return mk(a.x + b.x, a.y + b.y, a.z + b.z); }
 __device__ __forceinline__ F3 operator*(F3 a, float m) { return mk(a.x * m, a.y * m, a.z * m); }
 __device__ __forceinline__ F3 operator*(F3 a, F3 b) { return mk(a.x * b.x, a.y * b.y, a.z * b.z); }
 __device__ __forceinline__ float dot(F3 a, F3 b) { return fmaf(a.z, b.z, fmaf(a.y, b.y, a.x * b.x)); }
@@ -549,7 +551,14 @@ render_f32_kernel(DevScene32 sc, CamParams cam, void* __restrict__ out_rgb, uint
     const int tiles_y = (cam.shard_rows + kTileY - 1) / kTileY;
     const unsigned total_tiles = (unsigned)(tiles_x * tiles_y);
     const int n_sub = cam.samples == 1 ? 1 : 4;
-    const float w0 = cam.samples == 1 ? 1.0f : 0.25f;
+    // antialiasing_samples >= 2 (Camera::render_pixel + resample, src/camera.rs:84-114): the lane keeps the four fixed
+    // samples apart (local memory: touched once per sample), compares them with their mean and, where they disagree,
+    // goes on with `samples` more at counter-based offsets (include/rtc.h); rays then carry weight 1 and the sum is
+    // divided at the end.  samples 0 / 1 keep the weighted accumulation (x 0.25 is exact, so 0 gives the same bits either way).
+    const bool aa = cam.samples >= 2;
+    const int n_extra = aa ? (int)cam.samples : 0;
+    const uint64_t aa_seed_mixed = splitmix64((uint64_t)cam.aa_seed);
+    const float w0 = (cam.samples == 1 || aa) ? 1.0f : 0.25f;
     const F3 cam_origin = mk((float)cam.vinv[3], (float)cam.vinv[7], (float)cam.vinv[11]);  // Vinv * (0,0,0)
     // Camera::ray_for_pixel_offset (src/camera.rs:64-76): pixel - origin = Vinv3 * (wx, wy, -1) with
     // wx = half_width - (x + xo) ps, wy = half_height - (y + yo) ps  ==  cam_dx (x+xo) + cam_dy (y+yo) + cam_d0
@@ -570,6 +579,9 @@ render_f32_kernel(DevScene32 sc, CamParams cam, void* __restrict__ out_rgb, uint
     bool have = false;
     int px = 0, pr = 0, py = 0, sub = 0;
     F3 acc = mk(0, 0, 0);
+    float aa_s[12];                 // the four fixed samples of the pixel (aa only)
+    F3 aa_tot = mk(0, 0, 0);        // Color::average_over's running sums
+    int aa_ntot = n_sub;            // samples this pixel takes: 4, or 4 + n_extra once the fixed four disagree
     unsigned hitbits = 0;
     float4 stk_a[kMaxStack], stk_b[kMaxStack];  // pending refraction rays: (o, w), (d, remaining)
     int sp = 0;
@@ -586,8 +598,24 @@ render_f32_kernel(DevScene32 sc, CamParams cam, void* __restrict__ out_rgb, uint
             is_primary = false; has_ray = true;
         }
         if (!has_ray && have) {
-            if (sub + 1 < n_sub) ++sub;   // next sub-sample of the same pixel
+            if (aa && sub < aa_ntot) {          // a sample of the pixel is complete
+                aa_tot = aa_tot + acc;
+                if (sub < 4) { aa_s[3 * sub] = acc.x; aa_s[3 * sub + 1] = acc.y; aa_s[3 * sub + 2] = acc.z; }
+                if (sub == 3) {                 // any(|sample - mean| > 0.01) -> resample (src/camera.rs:107-110)
+                    const F3 mean = aa_tot * 0.25f;
+                    bool any = false;
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) {
+                        const F3 dl = mk(aa_s[3 * k], aa_s[3 * k + 1], aa_s[3 * k + 2]) - mean;
+                        any = any || dot(dl, dl) > 1.0e-4f;
+                    }
+                    if (any) aa_ntot = 4 + n_extra;
+                }
+                acc = mk(0, 0, 0);
+            }
+            if (sub + 1 < aa_ntot) ++sub;   // next sub-sample of the same pixel
             else {
+                if (aa) acc = aa_tot * (1.0f / (float)aa_ntot);
                 // pixel finished: Canvas::write_pixel (src/canvas.rs:43-46)
                 size_t p = (size_t)(cam.dst_full ? py : pr) * cam.hsize + px;
                 if (cam.out_format == RTC_OUT_F64_RGB) {
@@ -632,14 +660,22 @@ render_f32_kernel(DevScene32 sc, CamParams cam, void* __restrict__ out_rgb, uint
                 if (px < (int)cam.hsize && pr < cam.shard_rows) {
                     py = cam.row0 + (cam.shard_count > 1 ? shard_row_to_frame_row(pr, cam.tile_rows, cam.shard_index, cam.shard_count) : pr);
                     have = true; sub = 0; acc = mk(0, 0, 0); hitbits = 0;
-                    if (!(px < (int)cam.xlim && py < (int)cam.ylim)) sub = n_sub;  // outside the rect: stays black
+                    aa_tot = mk(0, 0, 0); aa_ntot = n_sub;
+                    if (!(px < (int)cam.xlim && py < (int)cam.ylim)) sub = kSubOutside;  // outside the rect: stays black
                 }
             }
             wnext += take;
         }
-        if (!has_ray && have && sub < n_sub) {
-            float fx = (float)px + (n_sub == 1 ? 0.5f : ((sub & 1) ? 0.75f : 0.25f));
-            float fy = (float)py + (n_sub == 1 ? 0.5f : ((sub & 2) ? 0.75f : 0.25f));
+        if (!has_ray && have && sub < aa_ntot) {
+            float xo = n_sub == 1 ? 0.5f : ((sub & 1) ? 0.75f : 0.25f);
+            float yo = n_sub == 1 ? 0.5f : ((sub & 2) ? 0.75f : 0.25f);
+            if (aa && sub >= 4) {               // Camera::resample's offsets (src/camera.rs:84-92; include/rtc.h)
+                const uint64_t pixel_index = (uint64_t)py * cam.hsize + (uint64_t)px;
+                xo = (float)(unsigned)(resample_bits(aa_seed_mixed, pixel_index, (unsigned)(sub - 4), 0u) >> 40) * 5.9604644775390625e-8f;
+                yo = (float)(unsigned)(resample_bits(aa_seed_mixed, pixel_index, (unsigned)(sub - 4), 1u) >> 40) * 5.9604644775390625e-8f;
+            }
+            float fx = (float)px + xo;
+            float fy = (float)py + yo;
             F3 dir = fma3(cam_dx, fx, fma3(cam_dy, fy, cam_d0));
             rd = dir * rsqrtf(dot(dir, dir));
             ro = cam_origin; rw = w0; remaining = cam.max_depth; is_primary = true; has_ray = true;
@@ -651,7 +687,7 @@ render_f32_kernel(DevScene32 sc, CamParams cam, void* __restrict__ out_rgb, uint
         float t = __int_as_float(0x7f800000);
         int hit = -1;
         if (has_ray) { intersect32<!kUnique, kCubes, kFilter>(S, ro, rd, t, hit, neg, n_neg); ++n_rays; }
-        if (has_ray && is_primary && hit >= 0) { hitbits |= 1u << sub; ++n_phits; }
+        if (has_ray && is_primary && hit >= 0) { if (sub < 4) hitbits |= 1u << sub; ++n_phits; }
         if (hit < 0) has_ray = false;   // World::color_at -> background_color (black), src/shape.rs:708
 
         // ---------------------------------------------------------------- phase B: prepare_computations

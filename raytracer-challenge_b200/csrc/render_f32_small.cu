@@ -29,10 +29,12 @@ constexpr int kTileX = 8, kTileY = 4;
 constexpr int kBatch = kTileX * kTileY;
 constexpr int kMaxStack = RTC_MAX_DEPTH;
 constexpr unsigned kInfBits = 0x7f800000u;
+constexpr int kSubOutside = 1 << 20;   // sub-sample cursor of a pixel outside the rect: nothing to trace
 
 struct F3 { float x, y, z; };
 __device__ __forceinline__ F3 mk(float x, float y, float z) { F3 v; v.x = x; v.y = y; v.z = z; return v; }
 __device__ __forceinline__ F3 operator-(F3 a, F3 b) { return mk(a.x - b.x, a.y - b.y, a.z - b.z); }
+__device__ __forceinline__ F3 operator+(F3 a, F3 b) { return mk(a.x + b.x, a.y + b.y, a.z + b.z); }
 __device__ __forceinline__ F3 operator*(F3 a, float m) { return mk(a.x * m, a.y * m, a.z * m); }
 __device__ __forceinline__ F3 operator*(F3 a, F3 b) { return mk(a.x * b.x, a.y * b.y, a.z * b.z); }
 __device__ __forceinline__ float dot(F3 a, F3 b) { return fmaf(a.z, b.z, fmaf(a.y, b.y, a.x * b.x)); }
@@ -234,7 +236,11 @@ __device__ __forceinline__ unsigned long long gtime() { unsigned long long t; as
 
 // kAux: the launch wants the work counters and/or the hit mask; without them (the plain frame) the
 // per-iteration bookkeeping for both is compiled out.
-template <int kFmt, bool kAux>
+// kAA: antialiasing_samples >= 2 (Camera::render_pixel + resample, src/camera.rs:84-114): the lane keeps the four fixed
+// samples apart (local memory, touched once per sample), compares them with their mean and, where they disagree, goes on
+// with `samples` more at counter-based offsets (include/rtc.h); rays carry weight 1 and the sum is divided at the end.
+// Frames with samples 0 / 1 run the kAA = false code, unchanged.
+template <int kFmt, bool kAux, bool kAA>
 __global__ void __launch_bounds__(kThreads, RTC_F32S_MIN_BLOCKS)
 render_f32_small_kernel(const __grid_constant__ SmallParams P, void* __restrict__ out_rgb, uint8_t* __restrict__ out_hit,
                         Counters* __restrict__ counters, unsigned* __restrict__ work) {
@@ -255,7 +261,8 @@ render_f32_small_kernel(const __grid_constant__ SmallParams P, void* __restrict_
     const int lane = threadIdx.x & 31;
     const unsigned lt_mask = (1u << lane) - 1u;
     const int n_sub = P.n_sub;
-    const float w0 = n_sub == 1 ? 1.0f : 0.25f;
+    const float w0 = (n_sub == 1 || kAA) ? 1.0f : 0.25f;
+    const uint64_t aa_seed_mixed = kAA ? splitmix64((uint64_t)P.aa_seed) : 0ull;
 
     // warp-uniform tile cursor
     int wnext = kBatch;        // next pixel of the current tile
@@ -268,6 +275,9 @@ render_f32_small_kernel(const __grid_constant__ SmallParams P, void* __restrict_
     int remaining = 0;
     int px = 0, pr = 0, py = 0, sub = 0;
     F3 acc = mk(0.f, 0.f, 0.f);
+    float aa_s[12];                   // kAA: the four fixed samples of the pixel
+    F3 aa_tot = mk(0.f, 0.f, 0.f);    // kAA: Color::average_over's running sums
+    int aa_ntot = n_sub;              // samples this pixel takes: 4, or 4 + n_extra once the fixed four disagree
     unsigned hitbits = 0;
     float4 stk_a[kMaxStack], stk_b[kMaxStack];  // pending refraction rays: (o, weight), (d, remaining)
     int sp = 0;
@@ -281,8 +291,24 @@ render_f32_small_kernel(const __grid_constant__ SmallParams P, void* __restrict_
     for (;;) {
         // ------------------------------------------------------------ lanes without a ray
         if (!has_ray && sp == 0 && have) {
-            if (sub + 1 < n_sub) ++sub;
+            if (kAA && sub < aa_ntot) {                       // a sample of the pixel is complete
+                aa_tot = aa_tot + acc;
+                if (sub < 4) { aa_s[3 * sub] = acc.x; aa_s[3 * sub + 1] = acc.y; aa_s[3 * sub + 2] = acc.z; }
+                if (sub == 3) {                               // any(|sample - mean| > 0.01) -> resample (src/camera.rs:107-110)
+                    const F3 mean = aa_tot * 0.25f;
+                    bool any = false;
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) {
+                        const F3 dl = mk(aa_s[3 * k], aa_s[3 * k + 1], aa_s[3 * k + 2]) - mean;
+                        any = any || dot(dl, dl) > 1.0e-4f;
+                    }
+                    if (any) aa_ntot = 4 + P.n_extra;
+                }
+                acc = mk(0.f, 0.f, 0.f);
+            }
+            if (sub + 1 < (kAA ? aa_ntot : n_sub)) ++sub;
             else {                                            // Canvas::write_pixel (src/canvas.rs:43-46)
+                if (kAA) acc = aa_tot * (1.0f / (float)aa_ntot);
                 size_t p = (size_t)(P.dst_full ? py : pr) * (size_t)P.hsize + (size_t)px;
                 if (kFmt == RTC_OUT_F64_RGB) {
                     double* o = (double*)out_rgb + 3 * p;
@@ -329,7 +355,8 @@ render_f32_small_kernel(const __grid_constant__ SmallParams P, void* __restrict_
                 if (px < P.hsize && pr < P.shard_rows) {
                     py = P.row0 + (P.shard_count > 1 ? shard_row_to_frame_row(pr, P.tile_rows, P.shard_index, P.shard_count) : pr);
                     have = true; sub = 0; acc = mk(0.f, 0.f, 0.f); hitbits = 0;
-                    if (!(px < P.xlim && py < P.ylim)) sub = n_sub;   // outside the rect: stays black
+                    if (kAA) { aa_tot = mk(0.f, 0.f, 0.f); aa_ntot = n_sub; }
+                    if (!(px < P.xlim && py < P.ylim)) sub = kSubOutside;   // outside the rect: stays black
                 }
             }
             wnext += take;
@@ -340,9 +367,16 @@ render_f32_small_kernel(const __grid_constant__ SmallParams P, void* __restrict_
                 const float4 a = stk_a[sp], b = stk_b[sp];
                 ro = xyz(a); rw = a.w; rd = xyz(b); remaining = __float_as_int(b.w);
                 primary = false; has_ray = true;
-            } else if (have && sub < n_sub) {                 // Camera::ray_for_pixel_offset (src/camera.rs:64-76)
-                const float fx = (float)px + (n_sub == 1 ? 0.5f : ((sub & 1) ? 0.75f : 0.25f));
-                const float fy = (float)py + (n_sub == 1 ? 0.5f : ((sub & 2) ? 0.75f : 0.25f));
+            } else if (have && sub < (kAA ? aa_ntot : n_sub)) {   // Camera::ray_for_pixel_offset (src/camera.rs:64-76)
+                float xo = n_sub == 1 ? 0.5f : ((sub & 1) ? 0.75f : 0.25f);
+                float yo = n_sub == 1 ? 0.5f : ((sub & 2) ? 0.75f : 0.25f);
+                if (kAA && sub >= 4) {                        // Camera::resample's offsets (src/camera.rs:84-92; include/rtc.h)
+                    const uint64_t pixel_index = (uint64_t)py * (uint64_t)P.hsize + (uint64_t)px;
+                    xo = (float)(unsigned)(resample_bits(aa_seed_mixed, pixel_index, (unsigned)(sub - 4), 0u) >> 40) * 5.9604644775390625e-8f;
+                    yo = (float)(unsigned)(resample_bits(aa_seed_mixed, pixel_index, (unsigned)(sub - 4), 1u) >> 40) * 5.9604644775390625e-8f;
+                }
+                const float fx = (float)px + xo;
+                const float fy = (float)py + yo;
                 F3 dir = mk(fmaf(P.cam_dx[0], fx, fmaf(P.cam_dy[0], fy, P.cam_d0[0])),
                             fmaf(P.cam_dx[1], fx, fmaf(P.cam_dy[1], fy, P.cam_d0[1])),
                             fmaf(P.cam_dx[2], fx, fmaf(P.cam_dy[2], fy, P.cam_d0[2])));
@@ -363,7 +397,7 @@ render_f32_small_kernel(const __grid_constant__ SmallParams P, void* __restrict_
         if (kAux) {
             n_rad += has_ray ? 1u : 0u;
             n_hits += hit ? 1u : 0u;
-            if (hit && primary) { hitbits |= 1u << sub; ++n_phits; }
+            if (hit && primary) { if (!kAA || sub < 4) hitbits |= 1u << sub; ++n_phits; }
         }
         has_ray = hit;                                        // miss: World::color_at -> black (src/shape.rs:708)
 
@@ -572,10 +606,15 @@ cudaError_t launch_render_f32_small(const SmallParams& P, int out_format, void* 
         return cudaGetLastError();
     };
     const bool aux = d_counters != nullptr || d_hit != nullptr;
+    auto pick = [&](auto fmt) -> cudaError_t {
+        constexpr int kF = decltype(fmt)::value;
+        if (P.n_extra > 0) return aux ? launch(render_f32_small_kernel<kF, true, true>) : launch(render_f32_small_kernel<kF, false, true>);
+        return aux ? launch(render_f32_small_kernel<kF, true, false>) : launch(render_f32_small_kernel<kF, false, false>);
+    };
     switch (out_format) {
-        case RTC_OUT_F64_RGB: return aux ? launch(render_f32_small_kernel<RTC_OUT_F64_RGB, true>) : launch(render_f32_small_kernel<RTC_OUT_F64_RGB, false>);
-        case RTC_OUT_F32_RGB: return aux ? launch(render_f32_small_kernel<RTC_OUT_F32_RGB, true>) : launch(render_f32_small_kernel<RTC_OUT_F32_RGB, false>);
-        default:              return aux ? launch(render_f32_small_kernel<RTC_OUT_U8_RGB, true>) : launch(render_f32_small_kernel<RTC_OUT_U8_RGB, false>);
+        case RTC_OUT_F64_RGB: return pick(IntC<RTC_OUT_F64_RGB>{});
+        case RTC_OUT_F32_RGB: return pick(IntC<RTC_OUT_F32_RGB>{});
+        default:              return pick(IntC<RTC_OUT_U8_RGB>{});
     }
 }
 

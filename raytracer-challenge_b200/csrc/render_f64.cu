@@ -7,6 +7,7 @@
 // (src/shape.rs:685-766) becomes an explicit per-thread stack of at most max_depth frames,
 // evaluated in the reference's post-order so every colour is combined with the same operations
 // in the same order.
+#include <type_traits>
 #include "rtc_common.h"
 
 namespace rtc {
@@ -340,7 +341,8 @@ __device__ __forceinline__ void thread_sample(int& sx, int& sy) {
 }
 
 // kCubes: the scene has cubes (src/shape.rs:500-630); scenes without them run exactly the sphere / plane code
-template <bool kInSmem, bool kCubes>
+// kResample: antialiasing_samples >= 2 (the resample passes of Camera::render_pixel, src/camera.rs:84-114)
+template <bool kInSmem, bool kCubes, bool kResample>
 #ifndef RTC_F64_MIN_BLOCKS
 #define RTC_F64_MIN_BLOCKS 4
 #endif
@@ -380,10 +382,25 @@ render_f64_kernel(DevScene64 sc, CamParams cam, double* __restrict__ out_f64, fl
     bool primary_hit = false;
     unsigned n_rays = 0, n_shadow = 0, n_shaded = 0;
 
-    if (active) {
+    // Camera::render_pixel (src/camera.rs:94-114).  Pass 0 traces this thread's fixed sample; with
+    // antialiasing_samples >= 2 the four threads of a pixel then share the resample pass (:84-92): extra sample
+    // k = 4 (pass - 1) + q goes to quad member q, and the colours are summed in k order like Color::average_over.
+    const int n_extra = kResample ? (int)cam.samples : 0;
+    const unsigned full_mask = 0xffffffffu;
+    const int lane = threadIdx.x & 31;
+    const int quad_base = lane & 0x16;                   // lane of the pixel's (.25, .25) sample in the 8x4 warp patch
+    const int quad_member = (lane & 1) | ((lane >> 2) & 2);
+    double xo = ss == 1 ? 0.5 : ((sx & 1) ? 0.75 : 0.25);
+    double yo = ss == 1 ? 0.5 : ((sy & 1) ? 0.75 : 0.25);
+    bool trace_now = active;
+    bool need_resample = false;
+    double reds = 0., greens = 0., blues = 0.;           // Color::average_over's running sums (src/color.rs:128-139)
+    unsigned hit_bits = 0;
+
+    for (int pass = 0;; ++pass) {
+    V3 sample_color = mk(0., 0., 0.);
+    if (trace_now) {
         // Camera::ray_for_pixel_offset (src/camera.rs:64-76)
-        double xo = ss == 1 ? 0.5 : ((sx & 1) ? 0.75 : 0.25);
-        double yo = ss == 1 ? 0.5 : ((sy & 1) ? 0.75 : 0.25);
         double xoffset = ((double)px + xo) * cam.pixel_size;
         double yoffset = ((double)py + yo) * cam.pixel_size;
         double world_x = cam.half_width - xoffset;
@@ -399,7 +416,7 @@ render_f64_kernel(DevScene64 sc, CamParams cam, double* __restrict__ out_f64, fl
         int n_neg = 0, n_shadow_neg = 0;
         int level = 0;
         int remaining = cam.max_depth;
-        bool first = true;
+        bool first = pass == 0;
         for (;;) {
             // ---- World::color_at(ray, remaining)  (src/shape.rs:702-710) ----
             V3 color;
@@ -524,28 +541,66 @@ render_f64_kernel(DevScene64 sc, CamParams cam, double* __restrict__ out_f64, fl
                 --level; ++remaining;
             }
             if (resumed) continue;
-            result = color;
+            sample_color = color;
             break;
         }
     }
 
-    // ---- combine sub-samples (Camera::render_pixel, src/camera.rs:96-113; Color::average_over) ----
-    unsigned hit_bits = primary_hit ? 1u : 0u;
-    if (ss == 2) {
-        const unsigned full = 0xffffffffu;
-        int l = threadIdx.x & 31;
-        double r1 = __shfl_sync(full, result.x, l + 1), g1 = __shfl_sync(full, result.y, l + 1), b1 = __shfl_sync(full, result.z, l + 1);
-        double r2 = __shfl_sync(full, result.x, l + 8), g2 = __shfl_sync(full, result.y, l + 8), b2 = __shfl_sync(full, result.z, l + 8);
-        double r3 = __shfl_sync(full, result.x, l + 9), g3 = __shfl_sync(full, result.y, l + 9), b3 = __shfl_sync(full, result.z, l + 9);
-        unsigned h1 = __shfl_sync(full, hit_bits, l + 1), h2 = __shfl_sync(full, hit_bits, l + 8), h3 = __shfl_sync(full, hit_bits, l + 9);
-        double reds = 0., greens = 0., blues = 0.;
-        reds += result.x; greens += result.y; blues += result.z;
-        reds += r1; greens += g1; blues += b1;
-        reds += r2; greens += g2; blues += b2;
-        reds += r3; greens += g3; blues += b3;
+    if (pass == 0) {
+        result = sample_color;
+        hit_bits = primary_hit ? 1u : 0u;
+        if (ss == 1) break;
+        // ---- combine the fixed sub-samples (src/camera.rs:96-113; Color::average_over) ----
+        const int src[4] = {quad_base, quad_base + 1, quad_base + 8, quad_base + 9};
+        bool any = false;
+        double sr[4], sg[4], sb[4];
+        unsigned bits = 0;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            sr[k] = __shfl_sync(full_mask, sample_color.x, src[k]);
+            sg[k] = __shfl_sync(full_mask, sample_color.y, src[k]);
+            sb[k] = __shfl_sync(full_mask, sample_color.z, src[k]);
+            bits |= __shfl_sync(full_mask, hit_bits, src[k]) << k;
+            reds += sr[k]; greens += sg[k]; blues += sb[k];
+        }
+        hit_bits = bits;
         result = mk(reds / 4.0, greens / 4.0, blues / 4.0);
-        hit_bits = hit_bits | (h1 << 1) | (h2 << 2) | (h3 << 3);
+        if (n_extra == 0) break;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {                    // Color::distance_from, src/color.rs:122-126
+            const double dr = sr[k] - result.x, dg = sg[k] - result.y, db = sb[k] - result.z;
+            if (sqrt(dr * dr + dg * dg + db * db) > 0.01) any = true;
+        }
+        need_resample = active && any;
+        if (!__any_sync(full_mask, need_resample)) break;
+    } else {
+        // the four extra samples of this pass, in list order
+        const int src[4] = {quad_base, quad_base + 1, quad_base + 8, quad_base + 9};
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            const double r = __shfl_sync(full_mask, sample_color.x, src[q]);
+            const double g = __shfl_sync(full_mask, sample_color.y, src[q]);
+            const double b = __shfl_sync(full_mask, sample_color.z, src[q]);
+            if (4 * (pass - 1) + q < n_extra) { reds += r; greens += g; blues += b; }
+        }
+        if (4 * pass >= n_extra) {
+            if (need_resample) {
+                const double l = (double)(4 + n_extra);
+                result = mk(reds / l, greens / l, blues / l);
+            }
+            break;
+        }
     }
+    {   // next pass: extra sample k of this pixel (Camera::resample, src/camera.rs:84-92; offsets: include/rtc.h)
+        const int k = 4 * pass + quad_member;
+        trace_now = need_resample && k < n_extra;
+        const uint64_t seed_mixed = splitmix64((uint64_t)cam.aa_seed);
+        const uint64_t pixel_index = (uint64_t)py * cam.hsize + (uint64_t)px;
+        xo = (double)(resample_bits(seed_mixed, pixel_index, (unsigned)k, 0u) >> 11) * (1.0 / 9007199254740992.0);
+        yo = (double)(resample_bits(seed_mixed, pixel_index, (unsigned)k, 1u) >> 11) * (1.0 / 9007199254740992.0);
+    }
+    }
+
     const bool writer = in_image && (ss == 1 || (((sx | sy) & 1) == 0));
     if (writer) {
         size_t p = (size_t)(cam.dst_full ? py : pr) * cam.hsize + px;
@@ -597,10 +652,15 @@ cudaError_t launch_render_f64(const DevScene64& scene, const CamParams& cam, voi
         kernel<<<grid, kThreads, bytes, stream>>>(scene, cam, o64, o32, o8, d_hit, d_counters);
         return cudaSuccess;
     };
-    const bool cubes = scene.n_cubes > 0;
+    const bool cubes = scene.n_cubes > 0, resample = cam.samples >= 2;
     cudaError_t e;
-    if (smem <= 200 * 1024) e = cubes ? launch(render_f64_kernel<true, true>, smem) : launch(render_f64_kernel<true, false>, smem);
-    else e = cubes ? launch(render_f64_kernel<false, true>, 0) : launch(render_f64_kernel<false, false>, 0);
+    auto pick = [&](auto in_smem, size_t bytes) -> cudaError_t {
+        constexpr bool kS = decltype(in_smem)::value;
+        if (resample) return cubes ? launch(render_f64_kernel<kS, true, true>, bytes) : launch(render_f64_kernel<kS, false, true>, bytes);
+        return cubes ? launch(render_f64_kernel<kS, true, false>, bytes) : launch(render_f64_kernel<kS, false, false>, bytes);
+    };
+    if (smem <= 200 * 1024) e = pick(std::true_type{}, smem);
+    else e = pick(std::false_type{}, 0);
     if (e != cudaSuccess) return e;
     return cudaGetLastError();
 }

@@ -193,10 +193,7 @@ int validate_opts(const rtc_camera* cam, const rtc_render_opts* o) {
     if (!cam || !o) return fail(RTC_ERR_INVALID_ARG, "null camera or opts");
     if (cam->hsize == 0 || cam->vsize == 0) return fail(RTC_ERR_INVALID_ARG, "empty image");
     if ((uint64_t)cam->hsize * cam->vsize > (1ull << 31)) return fail(RTC_ERR_INVALID_ARG, "image too large");
-    if (cam->samples > 1)
-        return fail(RTC_ERR_UNSUPPORTED,
-                    "antialiasing_samples >= 2 draws from rand::thread_rng in the reference (src/camera.rs:84-92); "
-                    "only 1 and 0 (deterministic 2x2) are reproducible");
+    if (cam->samples > 255) return fail(RTC_ERR_UNSUPPORTED, "antialiasing_samples is a u8 in the reference (src/camera.rs:26)");
     if (o->precision != RTC_PRECISION_F64_PARITY && o->precision != RTC_PRECISION_F32_FAST)
         return fail(RTC_ERR_INVALID_ARG, "bad precision");
     if (o->rect != RTC_RECT_REFERENCE_RENDER && o->rect != RTC_RECT_FULL) return fail(RTC_ERR_INVALID_ARG, "bad rect");
@@ -216,6 +213,7 @@ CamParams make_cam(const rtc_camera* cam, const rtc_render_opts* o, int shard_in
     c.pixel_size = cam->pixel_size;
     for (int i = 0; i < 12; ++i) c.vinv[i] = cam->view_inv[i];
     c.samples = cam->samples;
+    c.aa_seed = cam->aa_seed;
     // Camera::render loops 0..vsize-1 x 0..hsize-1 (src/camera.rs:120-121)
     c.xlim = o->rect == RTC_RECT_REFERENCE_RENDER ? cam->hsize - 1 : cam->hsize;
     c.ylim = o->rect == RTC_RECT_REFERENCE_RENDER ? cam->vsize - 1 : cam->vsize;
@@ -693,6 +691,8 @@ void fill_small_camera(SmallParams& P, const CamParams& cam) {
     P.hsize = (int)cam.hsize; P.shard_rows = cam.shard_rows; P.xlim = (int)cam.xlim; P.ylim = (int)cam.ylim;
     P.shard_index = cam.shard_index; P.shard_count = cam.shard_count; P.tile_rows = cam.tile_rows; P.dst_full = cam.dst_full; P.row0 = cam.row0;
     P.n_sub = cam.samples == 1 ? 1 : 4;
+    P.n_extra = cam.samples >= 2 ? (int)cam.samples : 0;
+    P.aa_seed = cam.aa_seed;
     P.max_depth = cam.max_depth;
     P.tiles_x = ((int)cam.hsize + 7) / 8;
     P.total_tiles = P.tiles_x * ((cam.shard_rows + 3) / 4);

@@ -120,7 +120,7 @@ struct SmallParams {
     int npg, nug;                      // plane / sphere groups of two
     int np, nu;
     int n_glass;                       // -1: fast n1/n2 test unavailable (a glass plane, or more than 8 glass spheres)
-    int pad0;
+    int n_extra;                       // antialiasing_samples when >= 2 (resample passes, src/camera.rs:84-92), else 0
     const SmallRec32* rec;             // [64] by stream position (global, staged to shared memory per block)
     unsigned* order;                   // [total_tiles] tile hand-out order (heavy tiles first), or null = linear
     float light_pos[3], light_int[3];
@@ -128,7 +128,8 @@ struct SmallParams {
     int hsize, shard_rows, xlim, ylim;
     int shard_index, shard_count, tile_rows, dst_full;
     int n_sub, max_depth, tiles_x, total_tiles;
-    int row0, pad1;                    // first frame row of the launch (row bands of rtc_render)
+    int row0;                          // first frame row of the launch (row bands of rtc_render)
+    unsigned aa_seed;                  // seed of the resample offsets (include/rtc.h)
 };
 
 // ---- per-launch parameters --------------------------------------------------------------------
@@ -136,7 +137,8 @@ struct CamParams {
     uint32_t hsize, vsize;
     double half_width, half_height, pixel_size;
     double vinv[12];  // rows 0..2 of view_transform_inv (src/camera.rs:25)
-    uint32_t samples; // 1 or 0 (= deterministic 2x2)
+    uint32_t samples; // 1 = centre sample; else 2x2 fixed sub-samples + `samples` resamples where they disagree (src/camera.rs:84-114)
+    uint32_t aa_seed; // seed of the resample offsets (include/rtc.h)
     uint32_t xlim, ylim;  // rect: pixels with x >= xlim or y >= ylim are written black
     int32_t max_depth;
     // row-tile sharding: tile k (rows [k*tile_rows, ...)) belongs to shard k % shard_count
@@ -150,6 +152,17 @@ struct CamParams {
 struct Counters {
     unsigned long long rays, primary_hits, shaded_hits, shadow_rays;
 };
+
+// Resample offsets (include/rtc.h, "Resample offsets"): 64 random bits for (pixel, extra sample k, axis).
+__host__ __device__ inline uint64_t splitmix64(uint64_t x) {
+    x += 0x9E3779B97F4A7C15ull;
+    x = (x ^ (x >> 30)) * 0xBF58476D1CE4E5B9ull;
+    x = (x ^ (x >> 27)) * 0x94D049BB133111EBull;
+    return x ^ (x >> 31);
+}
+__host__ __device__ inline uint64_t resample_bits(uint64_t seed_mixed, uint64_t pixel_index, unsigned k, unsigned axis) {
+    return splitmix64(seed_mixed ^ ((pixel_index << 9) | ((uint64_t)k << 1) | (uint64_t)axis));
+}
 
 // Map a compact shard row to the frame row (tiles stacked in frame order).
 __host__ __device__ inline int shard_row_to_frame_row(int r, int tile_rows, int shard_index, int shard_count) {

@@ -47,7 +47,7 @@ class RtcCamera(C.Structure):
         ("hsize", C.c_uint32), ("vsize", C.c_uint32),
         ("half_width", C.c_double), ("half_height", C.c_double), ("pixel_size", C.c_double),
         ("view_inv", C.c_double * 16),
-        ("samples", C.c_uint32), ("reserved", C.c_uint32),
+        ("samples", C.c_uint32), ("aa_seed", C.c_uint32),
     ]
 
 

@@ -56,6 +56,11 @@ def lib():
         L.orc_view_transform.argtypes = [C.POINTER(C.c_double)] * 4
         L.orc_camera_new.argtypes = [C.c_uint32, C.c_uint32, C.c_double, C.POINTER(C.c_double), C.POINTER(ffi.RtcCamera)]
         L.orc_quantize_u8.argtypes = [C.c_void_p, C.c_size_t, C.c_void_p]
+        L.orc_sample.restype = C.c_int
+        L.orc_sample.argtypes = [C.c_void_p, C.POINTER(ffi.RtcCamera), C.c_uint32, C.c_double, C.c_uint32, C.c_double, C.c_int,
+                                 C.POINTER(C.c_double)]
+        L.orc_resample_offset.restype = C.c_double
+        L.orc_resample_offset.argtypes = [C.c_uint32] * 6
         _lib = L
     return _lib
 
@@ -92,6 +97,19 @@ class OracleWorld:
         if rc != 0:
             raise RuntimeError("oracle: " + lib().orc_last_error().decode())
         return rgb, hit, cnt
+
+
+def sample(oracle_world, cam, x, xo, y, yo, max_depth=5):
+    """world.color_at(camera.ray_for_pixel_offset(x, xo, y, yo), max_depth) -> (r, g, b) as Python floats."""
+    desc = cam.flatten() if hasattr(cam, "flatten") else cam
+    out = (C.c_double * 3)()
+    if lib().orc_sample(oracle_world._h, C.byref(desc), x, xo, y, yo, max_depth, out) != 0:
+        raise RuntimeError("oracle: " + lib().orc_last_error().decode())
+    return (out[0], out[1], out[2])
+
+
+def resample_offset(aa_seed, hsize, x, y, k, axis):
+    return lib().orc_resample_offset(aa_seed, hsize, x, y, k, axis)
 
 
 def render(world, cam, rect=ffi.RECT_FULL, max_depth=5, threads=1, pixels=None):

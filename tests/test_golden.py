@@ -16,7 +16,7 @@ def _cases():
     return list(make_golden.cases())
 
 
-NAMES = ["c1_room_64x32", "c1_room_64x32_render_rect", "c1_room_32x16_ss2x2", "c1_room_48x24_depth2", "criterion_bench_40x30",
+NAMES = ["c1_room_64x32", "c1_room_64x32_render_rect", "c1_room_32x16_ss2x2", "c1_room_40x20_aa5_seed7", "c1_room_48x24_depth2", "criterion_bench_40x30",
          "default_world_11x11", "cube_room_60x42", "synthetic_200_spheres_48x27"]
 
 

@@ -172,9 +172,10 @@ def test_unsupported_inputs_are_errors_not_fallbacks(rtc, renderer):
         renderer.upload(w2)
     renderer.upload(rtc.World.default())
     cam = rtc.Camera.new(16, 16, 1.0)
-    cam.set_samples(4)
+    d = cam.flatten()
+    d.samples = 256   # antialiasing_samples is a u8 in the reference (src/camera.rs:26)
     with pytest.raises(rtc.ffi.RtcError) as e:
-        renderer.render(cam.flatten(), rtc.Renderer.make_opts())
+        renderer.render(d, rtc.Renderer.make_opts())
     assert e.value.code == rtc.ffi.RTC_ERR_UNSUPPORTED
     fresh = rtc.Renderer([0])
     with pytest.raises(rtc.ffi.RtcError) as e:

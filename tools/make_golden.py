@@ -19,6 +19,9 @@ def cases():
     yield "c1_room_64x32", rtc.scenes.reflect_refract_scene(), rtc.scenes.reflect_refract_camera(64, 32), rtc.ffi.RECT_FULL, 5
     yield "c1_room_64x32_render_rect", rtc.scenes.reflect_refract_scene(), rtc.scenes.reflect_refract_camera(64, 32), rtc.ffi.RECT_REFERENCE_RENDER, 5
     yield "c1_room_32x16_ss2x2", rtc.scenes.reflect_refract_scene(), rtc.scenes.reflect_refract_camera(32, 16, samples=0), rtc.ffi.RECT_FULL, 5
+    cam = rtc.scenes.reflect_refract_camera(40, 20, samples=5)   # render_pixel's resample pass, offsets per include/rtc.h
+    cam.aa_seed = 7
+    yield "c1_room_40x20_aa5_seed7", rtc.scenes.reflect_refract_scene(), cam, rtc.ffi.RECT_FULL, 5
     yield "c1_room_48x24_depth2", rtc.scenes.reflect_refract_scene(), rtc.scenes.reflect_refract_camera(48, 24), rtc.ffi.RECT_FULL, 2
     w, cam = rtc.scenes.bench_scene()
     cam = rtc.Camera.new_with_transform(40, 30, math.pi / 3.0, rtc.Matrix.make_view_transform((0., 7., 0.), (0., 0., 0.), (1., 0., 0.)))
