@@ -85,11 +85,14 @@ typedef struct rtc_shape {
     double pat_b[3];
 } rtc_shape;
 
-/* World.light (src/shape.rs:635, src/material.rs:10-14): a single point light. */
+/* World.light (src/shape.rs:635, src/material.rs:10-14): a point light.  The reference's World holds one. */
 typedef struct rtc_light {
     double intensity[3];
     double position[3];
 } rtc_light;
+
+/* rtc_scene_upload_lights accepts up to this many lights. */
+#define RTC_MAX_LIGHTS 8
 
 /* Camera (src/camera.rs:16-27): the derived fields computed by Camera::new (:39-58) and
  * the private view_transform_inv (:25).  samples = antialiasing_samples (a u8, 0..255), Camera::render_pixel
@@ -193,6 +196,16 @@ void rtc_context_destroy(rtc_context* ctx);
  * World.light, and packs them into structure-of-arrays device buffers on every GPU of the
  * context.  Replaces what World::intersect (src/shape.rs:677-683) reads per ray. */
 int rtc_scene_upload(rtc_context* ctx, const rtc_light* light, const rtc_shape* shapes, size_t n_shapes);
+
+/* Same flattening pass for a world with several point lights — the "FIXME -- multiple lights" of World::shade_hit
+ * (src/shape.rs:686; the Lua loader already reads a list of lights and keeps the first, src/lua.rs:148-150).
+ * The reference has no statement of this to mirror; the semantics are the book's shade_hit, built from the
+ * reference's own pieces: surface = lighting(light_0, .., is_shadowed_by_light(over_point, light_0))
+ * + lighting(light_1, .., is_shadowed_by_light(over_point, light_1)) + ... added in list order (each term carries the
+ * material's ambient share, as Material::lighting does, src/material.rs:335-340), one shadow ray per light and
+ * shaded hit.  n_lights = 1 is rtc_scene_upload exactly.  1 <= n_lights <= RTC_MAX_LIGHTS. */
+int rtc_scene_upload_lights(rtc_context* ctx, const rtc_light* lights, size_t n_lights, const rtc_shape* shapes,
+                            size_t n_shapes);
 
 /* Camera::render / render_async (src/camera.rs:116-160): renders the uploaded scene into the
  * caller's HOST buffers.  out_rgb: hsize*vsize*3 elements of opts->out_format, row-major

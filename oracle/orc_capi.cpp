@@ -91,6 +91,13 @@ orc_world* orc_world_create(const rtc_light* light, const rtc_shape* shapes, siz
     }
 }
 
+// Lights 1..n-1 of a multi-light world (extension, orc_world.hpp shade_hit); light 0 is orc_world_create's.
+int orc_world_add_light(orc_world* w, const rtc_light* light) {
+    w->world.extra_lights.emplace_back(Color(light->intensity[0], light->intensity[1], light->intensity[2]),
+                                       Point(light->position[0], light->position[1], light->position[2]));
+    return 0;
+}
+
 void orc_world_destroy(orc_world* w) { delete w; }
 
 // Renders with the restated Camera::render_pixel.  rect: 0 = Camera::render's bounds

@@ -183,6 +183,7 @@ struct Cube : Shape {
 struct World {
     std::vector<std::unique_ptr<Shape>> shapes;
     Light light;
+    std::vector<Light> extra_lights;   // extension, see shade_hit
     uint8_t last_world_id = 0;
 
     explicit World(const Light& l) : light(l) {}                                      // :642
@@ -216,6 +217,13 @@ struct World {
         tls_counters().shaded_hits++;
         Color surface_color = comp.object->get_material().lighting(
             light, comp.object, comp.over_point, comp.eyev, comp.normal, is_shadowed(comp.over_point));
+        // "FIXME -- multiple lights" (:686): the reference keeps one light and already passes it to
+        // is_shadowed_by_light (:716).  EXTENSION (no reference statement to follow): further lights
+        // contribute lighting(light_k, ..., is_shadowed_by_light(over_point, light_k)) each, added in list order — the
+        // book's shade_hit.  With no extra light this is the reference's statement above, bit for bit.
+        for (const Light& l : extra_lights)
+            surface_color = surface_color.add(comp.object->get_material().lighting(
+                l, comp.object, comp.over_point, comp.eyev, comp.normal, is_shadowed_by_light(comp.over_point, l)));
         Color reflected = reflected_color(comp, reflections_remaining);
         Color refracted = refracted_color(comp, reflections_remaining);
         const Material& material = comp.object->get_material();

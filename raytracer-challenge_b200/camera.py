@@ -78,7 +78,11 @@ class Renderer:
 
     def upload(self, world):
         light, shapes, n = world.flatten()
-        ffi.check(self._lib.rtc_scene_upload(self._ctx, C.byref(light), shapes, n))
+        if getattr(world, "extra_lights", None):
+            lights = world.flatten_lights()
+            ffi.check(self._lib.rtc_scene_upload_lights(self._ctx, lights, len(lights), shapes, n))
+        else:
+            ffi.check(self._lib.rtc_scene_upload(self._ctx, C.byref(light), shapes, n))
 
     def upload_flat(self, light, shapes, n):
         ffi.check(self._lib.rtc_scene_upload(self._ctx, C.byref(light), shapes, n))

@@ -543,7 +543,6 @@ render_f32_kernel(DevScene32 sc, CamParams cam, void* __restrict__ out_rgb, uint
         plL = s_plL; usL = s_usL; gset = s_gset;
     }
 
-    const bool light_inside = sc.light_inside != 0;
     const unsigned full = 0xffffffffu;
     const int lane = threadIdx.x & 31;
     const unsigned lt_mask = (1u << lane) - 1u;
@@ -724,35 +723,56 @@ render_f32_kernel(DevScene32 sc, CamParams cam, void* __restrict__ out_rgb, uint
             hp = fma3(hn, kEps32, p);                             // over_point
         }
 
-        // ---------------------------------------------------------------- phase C: is_shadowed (any-hit)
-        bool shadowed = false;
-        if (hit >= 0) { shadowed = shadow32<kCubes, kFilter>(S, plL, usL, light_inside, hp, light_pos - hp); ++n_rays; ++n_shaded; }
-
-        // ---------------------------------------------------------------- phase D: shade_hit
+        // ---------------------------------------------------------------- phases C + D, part 1: is_shadowed (any-hit) and
+        // Material::lighting (src/material.rs:319-361) at over_point — once per light (rtc_scene_upload_lights: the terms
+        // add up in list order, include/rtc.h; the reference's World has one light, src/shape.rs:686).  The loop bound is
+        // warp-uniform, so all lanes still run each shadow test in lock step.
+        F3 surface = mk(0, 0, 0);
+        F3 base = mk(0, 0, 0);
         if (hit >= 0) {
-            // Material::lighting (src/material.rs:319-361) at over_point
+            ++n_shaded;
             const ShadeRec32& rec = R[hidx];
-            const float4 ca = rec.col_amb, ds = rec.dif_spec, tr = rec.tr_ri;
-            const int pkind = __float_as_int(tr.z);
-            F3 base = xyz(ca);
+            const int pkind = __float_as_int(rec.tr_ri.z);
+            base = xyz(rec.col_amb);
             if (pkind != RTC_PATTERN_NONE) {
                 F3 pp = mk(row4(rec.p0, hp), row4(rec.p1, hp), row4(rec.p2, hp));
                 base = pattern_at32(pkind, xyz(rec.pa), xyz(rec.pb), pp);
             }
-            const F3 eff = base * light_int;
-            F3 surface = eff * ca.w;                                   // ambient
-            const F3 eye = mk(-rd.x, -rd.y, -rd.z);
-            if (!shadowed) {
-                F3 lv = light_pos - hp;
-                lv = lv * rsqrtf(dot(lv, lv));
-                float ldn = dot(lv, hn);
-                if (ldn >= 0.f) {
-                    surface = fma3(eff, ds.x * ldn, surface);          // diffuse
-                    F3 rv = fma3(hn, 2.f * ldn, mk(-lv.x, -lv.y, -lv.z));  // (-lightv).reflect(normal)
-                    float rde = dot(rv, eye);
-                    if (rde > 0.f) surface = fma3(light_int, ds.y * __powf(rde, ds.z), surface);
+        }
+        for (int li = 0; li < sc.n_lights; ++li) {
+            F3 lpos = light_pos, lint = light_int;
+            const float* pL = plL; const float* uL = usL;
+            if (li > 0) {
+                lpos = xyz(sc.lights[2 * li]); lint = xyz(sc.lights[2 * li + 1]);
+                pL = sc.plL + li * S.np; uL = sc.usL + li * S.nu;
+            }
+            const bool inside = ((sc.light_inside >> li) & 1) != 0;
+            bool shadowed = false;
+            if (hit >= 0) { shadowed = shadow32<kCubes, kFilter>(S, pL, uL, inside, hp, lpos - hp); ++n_rays; }
+            if (hit >= 0) {
+                const ShadeRec32& rec = R[hidx];
+                const float4 ca = rec.col_amb, ds = rec.dif_spec;
+                const F3 eff = base * lint;
+                surface = fma3(eff, ca.w, surface);                        // ambient
+                if (!shadowed) {
+                    F3 lv = lpos - hp;
+                    lv = lv * rsqrtf(dot(lv, lv));
+                    float ldn = dot(lv, hn);
+                    if (ldn >= 0.f) {
+                        surface = fma3(eff, ds.x * ldn, surface);          // diffuse
+                        F3 rv = fma3(hn, 2.f * ldn, mk(-lv.x, -lv.y, -lv.z));  // (-lightv).reflect(normal)
+                        float rde = -dot(rv, rd);                          // rv . eye
+                        if (rde > 0.f) surface = fma3(lint, ds.y * __powf(rde, ds.z), surface);
+                    }
                 }
             }
+        }
+
+        // ---------------------------------------------------------------- phase D, part 2: shade_hit's children
+        if (hit >= 0) {
+            const ShadeRec32& rec = R[hidx];
+            const float4 ds = rec.dif_spec, tr = rec.tr_ri;
+            const F3 eye = mk(-rd.x, -rd.y, -rd.z);
             acc = fma3(surface, rw, acc);
             // children (src/shape.rs:689-699, 729-781) as weighted rays
             const float k_refl = ds.w, k_tr = tr.x;

@@ -341,8 +341,9 @@ __device__ __forceinline__ void thread_sample(int& sx, int& sy) {
 }
 
 // kCubes: the scene has cubes (src/shape.rs:500-630); scenes without them run exactly the sphere / plane code
-// kResample: antialiasing_samples >= 2 (the resample passes of Camera::render_pixel, src/camera.rs:84-114)
-template <bool kInSmem, bool kCubes, bool kResample>
+// kExt: antialiasing_samples >= 2 (the resample passes of Camera::render_pixel, src/camera.rs:84-114) and / or more than one
+// light (rtc_scene_upload_lights); frames with neither run the kExt = false code, which compiles none of it
+template <bool kInSmem, bool kCubes, bool kExt>
 #ifndef RTC_F64_MIN_BLOCKS
 #define RTC_F64_MIN_BLOCKS 4
 #endif
@@ -385,7 +386,8 @@ render_f64_kernel(DevScene64 sc, CamParams cam, double* __restrict__ out_f64, fl
     // Camera::render_pixel (src/camera.rs:94-114).  Pass 0 traces this thread's fixed sample; with
     // antialiasing_samples >= 2 the four threads of a pixel then share the resample pass (:84-92): extra sample
     // k = 4 (pass - 1) + q goes to quad member q, and the colours are summed in k order like Color::average_over.
-    const int n_extra = kResample ? (int)cam.samples : 0;
+    const int n_extra = (kExt && cam.samples >= 2) ? (int)cam.samples : 0;
+    const int n_lights = kExt ? sc.n_lights : 1;
     const unsigned full_mask = 0xffffffffu;
     const int lane = threadIdx.x & 31;
     const int quad_base = lane & 0x16;                   // lane of the pixel's (.25, .25) sample in the 8x4 warp patch
@@ -452,15 +454,27 @@ render_f64_kernel(DevScene64 sc, CamParams cam, double* __restrict__ out_f64, fl
                 V3 over_point = add(point, mul(normal, kEps));
                 V3 under_point = sub(point, mul(normal, kEps));
                 V3 reflectv = reflect(rd, normal);
-                // World::is_shadowed_by_light (src/shape.rs:716-727)
-                V3 v = sub(light_pos, over_point);
-                double distance = sqrt(v.x * v.x + v.y * v.y + v.z * v.z);
-                V3 sdir = normalize(v);
-                double st; int sidx;
-                ++n_rays; ++n_shadow; ++n_shaded;
-                intersect_world<false, kCubes>(S, over_point, sdir, st, sidx, kept, n_shadow_neg);
-                bool shadowed = sidx >= 0 && st < distance;
-                V3 surface = lighting(rec, light_pos, light_int, over_point, eyev, normal, shadowed);
+                // surface = lighting(light, .., is_shadowed(over_point)) (src/shape.rs:686-688); with rtc_scene_upload_lights
+                // one such term per light, added in list order (the "FIXME -- multiple lights" of :686; include/rtc.h)
+                ++n_shaded;
+                V3 surface = mk(0., 0., 0.);
+                for (int li = 0; li < n_lights; ++li) {
+                    V3 lpos = light_pos, lint = light_int;
+                    if (li > 0) {
+                        const double* L = sc.lights + 6 * li;
+                        lpos = mk(L[0], L[1], L[2]); lint = mk(L[3], L[4], L[5]);
+                    }
+                    // World::is_shadowed_by_light (src/shape.rs:716-727)
+                    V3 v = sub(lpos, over_point);
+                    double distance = sqrt(v.x * v.x + v.y * v.y + v.z * v.z);
+                    V3 sdir = normalize(v);
+                    double st; int sidx;
+                    ++n_rays; ++n_shadow;
+                    intersect_world<false, kCubes>(S, over_point, sdir, st, sidx, kept, n_shadow_neg);
+                    bool shadowed = sidx >= 0 && st < distance;
+                    V3 term = lighting(rec, lpos, lint, over_point, eyev, normal, shadowed);
+                    surface = li == 0 ? term : add(surface, term);
+                }
                 // shade_hit's children (src/shape.rs:689-699, 729-766)
                 bool want_refl = remaining != 0 && !(rec.reflective <= 0.);
                 bool want_refr = false;
@@ -652,7 +666,7 @@ cudaError_t launch_render_f64(const DevScene64& scene, const CamParams& cam, voi
         kernel<<<grid, kThreads, bytes, stream>>>(scene, cam, o64, o32, o8, d_hit, d_counters);
         return cudaSuccess;
     };
-    const bool cubes = scene.n_cubes > 0, resample = cam.samples >= 2;
+    const bool cubes = scene.n_cubes > 0, resample = cam.samples >= 2 || scene.n_lights > 1;
     cudaError_t e;
     auto pick = [&](auto in_smem, size_t bytes) -> cudaError_t {
         constexpr bool kS = decltype(in_smem)::value;

@@ -67,6 +67,8 @@ struct DeviceState {
     DevBuf<float4> pl32, us32, gs32, bound;
     DevBuf<int32_t> sph_index, pl_index, us_index, gs_index, gset;
     DevBuf<float> plL, usL;
+    DevBuf<double> lights64;   // [n_lights][6]
+    DevBuf<float4> lights32;   // [n_lights][2]
     DevBuf<ShadeRec64> rec64;
     DevBuf<ShadeRec32> rec32;
     DevBuf<SmallRec32> srec;   // small-scene shading records, by stream position
@@ -235,8 +237,9 @@ struct HostScene {
     std::vector<int32_t> sph_index, pl_index, us_index, gs_index, gset;
     std::vector<double2> cub64; std::vector<float4> cb32; std::vector<int32_t> cub_index;   // cubes: appended to sph64 / gs32 after the spheres
     int n_spheres = 0, n_gsph = 0, n_cubes = 0;
-    std::vector<float> plL, usL;
-    int light_inside = 0;
+    std::vector<float> plL, usL;          // [n_lights][np], [n_lights][nu]
+    std::vector<double> lights64; std::vector<float4> lights32;
+    int light_inside = 0;                 // bit k: light k inside some uniform sphere
     std::vector<float4> bound;            // bounding spheres of us32 | gs32 objects (DevScene32::bound)
     float bound_cmax = 0.f, bound_rmax = 0.f;
     std::vector<ShadeRec64> rec64;
@@ -311,7 +314,8 @@ bool bounding_sphere(const double* inv, double unit_radius, double c[3], double&
     return std::isfinite(radius) && std::isfinite(cn);
 }
 
-int flatten(const rtc_light* light, const rtc_shape* shapes, size_t n, HostScene& hs) {
+int flatten(const rtc_light* lights, size_t n_lights, const rtc_shape* shapes, size_t n, HostScene& hs) {
+    const rtc_light* light = lights;   // light 0 = World.light
     bool seen[256] = {false};
     hs.rec64.resize(n);
     hs.rec32.resize(n);
@@ -457,23 +461,29 @@ int flatten(const rtc_light* light, const rtc_shape* shapes, size_t n, HostScene
         }
     }
 
-    // light-only terms of the shadow test (f32, from the f32 coefficients the kernels use)
-    {
-        const float lx = (float)light->position[0], ly = (float)light->position[1], lz = (float)light->position[2];
+    // light-only terms of the shadow test (f32, from the f32 coefficients the kernels use), one row per light
+    for (size_t li = 0; li < n_lights; ++li) {
+        const rtc_light& L = lights[li];
+        const float lx = (float)L.position[0], ly = (float)L.position[1], lz = (float)L.position[2];
         for (int k = 0; k < np; ++k) { const float4& q = hs.pl32[k]; hs.plL.push_back(fmaf(q.z, lz, fmaf(q.y, ly, fmaf(q.x, lx, q.w)))); }
         for (int k = 0; k < nu; ++k) {
             const float4& q = hs.us32[k];
             const float dx = lx - q.x, dy = ly - q.y, dz = lz - q.z;
             const float v = fmaf(dz, dz, fmaf(dy, dy, dx * dx)) - q.w;
             hs.usL.push_back(v);
-            if (v < 0.f) hs.light_inside = 1;
+            if (v < 0.f) hs.light_inside |= 1 << li;
         }
+        for (int k = 0; k < 3; ++k) hs.lights64.push_back(L.position[k]);
+        for (int k = 0; k < 3; ++k) hs.lights64.push_back(L.intensity[k]);
+        hs.lights32.push_back(make_float4(lx, ly, lz, 0.f));
+        hs.lights32.push_back(make_float4((float)L.intensity[0], (float)L.intensity[1], (float)L.intensity[2], 0.f));
     }
 
     // ---- small-scene form: constant-bank streams + records by stream position ----
     SmallParams& sp = hs.small;
     std::memset(&sp, 0, sizeof sp);
-    bool ok = np <= kSmallMaxPlanes && nu <= kSmallMaxUsph && hs.gs_index.empty() && hs.ids_unique && np + nu > 0;
+    bool ok = np <= kSmallMaxPlanes && nu <= kSmallMaxUsph && hs.gs_index.empty() && hs.ids_unique && np + nu > 0 &&
+              n_lights == 1;   // the shadow coefficients of this form are folded with the one light
     const double lp[3] = {light->position[0], light->position[1], light->position[2]};
     for (int k = 0; ok && k < nu; ++k) {   // light inside a sphere: the convex-minimum shadow test does not apply
         const float4& u = hs.us32[k];
@@ -784,7 +794,7 @@ void rtc_context_destroy(rtc_context* ctx) {
     for (DeviceState& d : ctx->devs) {
         cudaSetDevice(d.dev);
         if (d.stream) cudaStreamSynchronize(d.stream);
-        d.sph64.release(); d.pl64.release(); d.pl32.release(); d.us32.release(); d.gs32.release(); d.us_index.release(); d.gs_index.release(); d.gset.release(); d.plL.release(); d.usL.release(); d.bound.release();
+        d.sph64.release(); d.pl64.release(); d.pl32.release(); d.us32.release(); d.gs32.release(); d.us_index.release(); d.gs_index.release(); d.gset.release(); d.plL.release(); d.usL.release(); d.lights64.release(); d.lights32.release(); d.bound.release();
         d.sph_index.release(); d.pl_index.release(); d.rec64.release(); d.rec32.release(); d.srec.release();
         d.rgb.release(); d.hit.release(); d.counters.release(); d.work.release(); d.order.release();
         if (d.ev_k0) cudaEventDestroy(d.ev_k0);
@@ -805,9 +815,14 @@ void rtc_context_destroy(rtc_context* ctx) {
 }
 
 int rtc_scene_upload(rtc_context* ctx, const rtc_light* light, const rtc_shape* shapes, size_t n_shapes) {
+    return rtc_scene_upload_lights(ctx, light, 1, shapes, n_shapes);
+}
+
+int rtc_scene_upload_lights(rtc_context* ctx, const rtc_light* light, size_t n_lights, const rtc_shape* shapes, size_t n_shapes) {
     if (!ctx || !light || (!shapes && n_shapes)) return fail(RTC_ERR_INVALID_ARG, "rtc_scene_upload: null argument");
+    if (n_lights < 1 || n_lights > RTC_MAX_LIGHTS) return fail(RTC_ERR_INVALID_ARG, "rtc_scene_upload_lights: 1 <= n_lights <= RTC_MAX_LIGHTS");
     HostScene hs;
-    int rc = flatten(light, shapes, n_shapes, hs);
+    int rc = flatten(light, n_lights, shapes, n_shapes, hs);
     if (rc != RTC_OK) return rc;
     for (DeviceState& d : ctx->devs) {
         CUDA_TRY(cudaSetDevice(d.dev));
@@ -821,6 +836,8 @@ int rtc_scene_upload(rtc_context* ctx, const rtc_light* light, const rtc_shape* 
         CUDA_TRY(upload(d.gset, hs.gset, d.stream));
         CUDA_TRY(upload(d.plL, hs.plL, d.stream));
         CUDA_TRY(upload(d.usL, hs.usL, d.stream));
+        CUDA_TRY(upload(d.lights64, hs.lights64, d.stream));
+        CUDA_TRY(upload(d.lights32, hs.lights32, d.stream));
         CUDA_TRY(upload(d.bound, hs.bound, d.stream));
         CUDA_TRY(upload(d.sph_index, hs.sph_index, d.stream));
         CUDA_TRY(upload(d.pl_index, hs.pl_index, d.stream));
@@ -844,6 +861,8 @@ int rtc_scene_upload(rtc_context* ctx, const rtc_light* light, const rtc_shape* 
         d.s32.gsph = d.gs32.p; d.s32.gs_index = d.gs_index.p;
         d.s32.gset = d.gset.p; d.s32.n_gset = (int)hs.gset.size();
         d.s32.plL = d.plL.p; d.s32.usL = d.usL.p; d.s32.light_inside = hs.light_inside;
+        d.s64.n_lights = d.s32.n_lights = (int)n_lights;
+        d.s64.lights = d.lights64.p; d.s32.lights = d.lights32.p;
         d.s32.rec = d.rec32.p;
         d.s32.bound = d.bound.p; d.s32.n_bound4 = (int)hs.bound.size(); d.s32.bound_cmax = hs.bound_cmax; d.s32.bound_rmax = hs.bound_rmax;
         for (int k = 0; k < 3; ++k) {

@@ -43,8 +43,10 @@ struct DevScene64 {
     const double2* pl_rows;    // [n_planes][2]: r1.xy r1.zw
     const int32_t* pl_index;   // [n_planes]
     const ShadeRec64* rec;     // [n_shapes]
-    double light_pos[3];
+    double light_pos[3];       // light 0 (World.light, src/shape.rs:635)
     double light_int[3];
+    int n_lights, pad1;        // rtc_scene_upload_lights: lights 1..n_lights-1 live in `lights`
+    const double* lights;      // [n_lights][6]: position xyz, intensity rgb
 };
 
 // ---- f32 (fast) layout ------------------------------------------------------------------------
@@ -81,7 +83,7 @@ struct DevScene32 {
     int n_gset;
     const float* plL;          // [n_planes] f(light) = n.light + w   (shadow test: f(0) f(1) <= 0)
     const float* usL;          // [n_usph]   |light - c|^2 - r^2
-    int light_inside;          // the light sits inside some uniform sphere
+    int light_inside;          // bit k: light k sits inside some uniform sphere
     // Bounding spheres (cx, cy, cz, -R^2) of the uniform spheres | general spheres | cubes, in stream order,
     // padded to a multiple of four with (0, 0, 0, +inf).  Scenes whose streams stay in global memory (10^3+
     // shapes) test a ray against these first — 9 FFMA per shape — and run the exact test of a shape only
@@ -89,8 +91,10 @@ struct DevScene32 {
     const float4* bound;
     int n_bound4;
     float bound_cmax, bound_rmax;   // max |c|_1 and max R over the entries (rounding margin of the filter)
-    float light_pos[3];
+    float light_pos[3];        // light 0
     float light_int[3];
+    int n_lights;              // rtc_scene_upload_lights: plL / usL hold n_lights rows; lights 1.. read them from global memory
+    const float4* lights;      // [n_lights][2]: position, intensity
 };
 
 // ---- f32 small-scene layout (render_f32_small.cu) ------------------------------------------------

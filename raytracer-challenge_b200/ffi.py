@@ -18,6 +18,7 @@ PRECISION_F64_PARITY, PRECISION_F32_FAST = 0, 1
 RECT_REFERENCE_RENDER, RECT_FULL = 0, 1
 OUT_F64_RGB, OUT_F32_RGB, OUT_U8_RGB = 0, 1, 2
 RTC_MAX_DEPTH = 8
+MAX_LIGHTS = 8   # RTC_MAX_LIGHTS
 OPT_DST_FULL_FRAME = 1
 OPT_F32_GENERAL_KERNEL = 2
 OPT_LINEAR_TILE_ORDER = 4
@@ -78,6 +79,7 @@ EXPORTS = [
     ("rtc_context_create", C.c_int, [C.POINTER(C.c_int), C.c_int, C.POINTER(C.c_void_p)]),
     ("rtc_context_destroy", None, [C.c_void_p]),
     ("rtc_scene_upload", C.c_int, [C.c_void_p, C.POINTER(RtcLight), C.POINTER(RtcShape), C.c_size_t]),
+    ("rtc_scene_upload_lights", C.c_int, [C.c_void_p, C.POINTER(RtcLight), C.c_size_t, C.POINTER(RtcShape), C.c_size_t]),
     ("rtc_render", C.c_int, [C.c_void_p, C.POINTER(RtcCamera), C.POINTER(RtcRenderOpts), C.c_void_p,
                              C.c_void_p, C.POINTER(RtcStats)]),
     ("rtc_shard_rows", C.c_int, [C.POINTER(RtcCamera), C.POINTER(RtcRenderOpts)]),

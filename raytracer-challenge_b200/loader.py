@@ -96,12 +96,14 @@ def _material(spec, defs, what):
     return m
 
 
-def load_yaml(text):
-    """-> (World, Camera).  `text` is the YAML document (a string or an open file)."""
+def load_yaml(text, all_lights=False):
+    """-> (World, Camera).  `text` is the YAML document (a string or an open file).  The reference's World holds one
+    point light, so by default the first `add: light` counts; all_lights=True keeps every light of the file
+    (World.add_light -> rtc_scene_upload_lights, the book's multi-light shade_hit)."""
     doc = yaml.safe_load(text)
     if not isinstance(doc, list):
         raise ValueError("scene file: the top level is a list of `add:` / `define:` items")
-    defs, cam, light, shapes = {}, None, None, []
+    defs, cam, light, shapes, more_lights = {}, None, None, [], []
     for n, item in enumerate(doc):
         what = f"item {n}"
         if "define" in item:
@@ -119,6 +121,8 @@ def load_yaml(text):
         elif item.get("add") == "light":
             if light is None:                          # World holds one point light (src/shape.rs:635): the first one counts
                 light = Light(_color(item["intensity"], what), tuple(map(float, item["at"])))
+            elif all_lights:
+                more_lights.append(Light(_color(item["intensity"], what), tuple(map(float, item["at"]))))
         elif item.get("add") in _SHAPES:
             shapes.append(_SHAPES[item["add"]](_apply_ops(Matrix.identity(), item.get("transform"), defs, what),
                                                _material(item.get("material"), defs, what)))
@@ -127,6 +131,8 @@ def load_yaml(text):
     if cam is None or light is None:
         raise ValueError("scene file: needs one `add: camera` and one `add: light`")
     world = World(light)
+    for l in more_lights:
+        world.add_light(l)
     for s in shapes:
         world.add_shape(s)
     return world, cam
@@ -204,10 +210,15 @@ def camera_from_table(t):       # src/lua.rs:234-247
     return cam
 
 
-def world_from_table(t):        # src/lua.rs:303-330
+def world_from_table(t, all_lights=False):        # src/lua.rs:303-330
+    """lights_from_table keeps the first light of the list (src/lua.rs:148-150); all_lights=True keeps them all."""
     lights = t["lights"]
-    first = lights[0] if isinstance(lights, (list, tuple)) else lights[1]   # Lua sequences start at 1
+    seq = list(lights) if isinstance(lights, (list, tuple)) else [lights[k] for k in sorted(lights)]   # Lua sequences start at 1
+    first = seq[0]
     world = World(Light(_rgb(first["color"], "light.color"), _xyz(first["position"], "light.position")))
+    if all_lights:
+        for l in seq[1:]:
+            world.add_light(Light(_rgb(l["color"], "light.color"), _xyz(l["position"], "light.position")))
     for shape in t["shapes"]:
         kind = shape.get("type")
         if kind not in _SHAPES:

@@ -197,6 +197,7 @@ class World:
     def __init__(self, light=None):
         self.shapes = []
         self.light = light if light is not None else Light()
+        self.extra_lights = []   # lights 1.. of a multi-light world (rtc_scene_upload_lights; the reference keeps one)
         self.last_world_id = 0
 
     @staticmethod
@@ -225,6 +226,23 @@ class World:
         self.last_world_id = new_id
         self.shapes.append(s)
         return self
+
+    def add_light(self, light):
+        """A further point light: the 'FIXME -- multiple lights' of World::shade_hit (src/shape.rs:686).  Each light adds
+        lighting(light, .., is_shadowed_by_light(over_point, light)) to the surface colour (include/rtc.h)."""
+        if 1 + len(self.extra_lights) >= ffi.MAX_LIGHTS:
+            raise ValueError("at most %d lights" % ffi.MAX_LIGHTS)
+        self.extra_lights.append(light)
+        return self
+
+    def flatten_lights(self):
+        """-> (RtcLight * n_lights): World.light first, then the lights added with add_light."""
+        ls = [self.light] + list(self.extra_lights)
+        arr = (ffi.RtcLight * len(ls))()
+        for d, l in zip(arr, ls):
+            d.intensity[:] = list(l.intensity)
+            d.position[:] = list(l.position)
+        return arr
 
     def get_shape(self, i):
         return self.shapes[i]

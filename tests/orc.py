@@ -47,6 +47,7 @@ def lib():
         L.orc_world_create.restype = C.c_void_p
         L.orc_world_create.argtypes = [C.POINTER(ffi.RtcLight), C.POINTER(ffi.RtcShape), C.c_size_t]
         L.orc_world_destroy.argtypes = [C.c_void_p]
+        L.orc_world_add_light.argtypes = [C.c_void_p, C.POINTER(ffi.RtcLight)]
         L.orc_render.restype = C.c_int
         L.orc_render.argtypes = [C.c_void_p, C.POINTER(ffi.RtcCamera), C.c_int, C.c_int, C.c_int, C.c_void_p,
                                  C.c_size_t, C.c_void_p, C.c_void_p, C.POINTER(OrcCounters)]
@@ -71,6 +72,9 @@ class OracleWorld:
         self._h = lib().orc_world_create(C.byref(light), shapes, n)
         if not self._h:
             raise RuntimeError("oracle: " + lib().orc_last_error().decode())
+        if flat is None and getattr(world, "extra_lights", None):
+            for l in world.flatten_lights()[1:]:
+                lib().orc_world_add_light(self._h, C.byref(l))
 
     def __del__(self):
         if getattr(self, "_h", None):
