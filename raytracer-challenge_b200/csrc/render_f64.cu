@@ -47,6 +47,7 @@ struct Streams {  // intersect streams, in shared memory when they fit, else glo
     const double2* sph; const int32_t* sph_index; int ns;   // spheres [0, ns), then cubes [ns, ns + nc): same 3x4 inverse rows
     int nc;
     const double2* pl;  const int32_t* pl_index;  int np;
+    const float4* bound; int nb4; float cmax, rmax;         // f32 bounding spheres of [0, ns + nc) (DevScene64::bound); nb4 = 0: none
 };
 
 // Shape::intersect + Sphere::intersect_local (src/shape.rs:23-26, 361-375)
@@ -138,8 +139,7 @@ __device__ __noinline__ void intersect_world(const Streams& S, V3 o, V3 d, doubl
             if (kCollect && t < 0.0) keep(t, 2 * S.pl_index[i]);
         }
     }
-#pragma unroll kUnroll
-    for (int i = 0; i < S.ns; ++i) {
+    auto sphere = [&](int i) {
         double t1, t2;
         if (sphere_roots(S.sph + 6 * i, o, d, t1, t2)) {
             int idx = S.sph_index[i];
@@ -149,8 +149,8 @@ __device__ __noinline__ void intersect_world(const Streams& S, V3 o, V3 d, doubl
                 if (kCollect) { if (t1 < 0.0) keep(t1, 2 * idx); if (t2 < 0.0) keep(t2, 2 * idx + 1); }
             }
         }
-    }
-    if (kCubes) for (int i = S.ns; i < S.ns + S.nc; ++i) {   // cubes: behind the spheres in the same stream
+    };
+    auto cube = [&](int i) {   // cubes: behind the spheres in the same stream
         double t1, t2;
         if (cube_roots(S.sph + 6 * i, o, d, t1, t2)) {
             int idx = S.sph_index[i];
@@ -160,6 +160,40 @@ __device__ __noinline__ void intersect_world(const Streams& S, V3 o, V3 d, doubl
                 if (kCollect) { if (t1 < 0.0) keep(t1, 2 * idx); if (t2 < 0.0) keep(t2, 2 * idx + 1); }
             }
         }
+    };
+    if (S.nb4 > 0) {
+        // f32 line-distance filter in front of the exact tests (DevScene64::bound).  |(c - o) x d^| is the distance of
+        // the centre from the ray's line; with m = o x d^ it is |c x d^ - m|.  E bounds the rounding of this test (o, d
+        // rounded to f32, the cross products, an approximate 1/|d|) with a factor ~10 to spare; a shape is skipped only
+        // when its gap is provably positive, i.e. when the exact test below would find disc < 0 (no list entry, no
+        // negative-t entry either).  A NaN gap (degenerate ray) counts as a candidate.
+        const float fox = (float)o.x, foy = (float)o.y, foz = (float)o.z;
+        float fdx = (float)d.x, fdy = (float)d.y, fdz = (float)d.z;
+        const float inv_len = rsqrtf(fmaf(fdz, fdz, fmaf(fdy, fdy, fdx * fdx)));
+        fdx *= inv_len; fdy *= inv_len; fdz *= inv_len;
+        const float mx = foy * fdz - foz * fdy, my = foz * fdx - fox * fdz, mz = fox * fdy - foy * fdx;
+        const float E = 3.8e-6f * (S.cmax + fabsf(fox) + fabsf(foy) + fabsf(foz));
+        const float margin = fmaf(E, 2.f * S.rmax + E, 2e-6f * S.rmax * S.rmax);
+        auto gap = [&](float4 b) {
+            const float vx = fmaf(-b.z, fdy, fmaf(b.y, fdz, -mx));
+            const float vy = fmaf(-b.x, fdz, fmaf(b.z, fdx, -my));
+            const float vz = fmaf(-b.y, fdx, fmaf(b.x, fdy, -mz));
+            return fmaf(vz, vz, fmaf(vy, vy, fmaf(vx, vx, b.w)));
+        };
+        for (int g = 0; g < S.nb4; g += 4) {
+            const float4 b0 = S.bound[g], b1 = S.bound[g + 1], b2 = S.bound[g + 2], b3 = S.bound[g + 3];
+            const float s0 = gap(b0), s1 = gap(b1), s2 = gap(b2), s3 = gap(b3);
+            unsigned cand = (!(s0 > margin) ? 1u : 0u) | (!(s1 > margin) ? 2u : 0u) | (!(s2 > margin) ? 4u : 0u) | (!(s3 > margin) ? 8u : 0u);
+            while (cand) {
+                const int i = g + __ffs(cand) - 1;
+                cand &= cand - 1u;
+                if (!kCubes || i < S.ns) sphere(i); else cube(i);
+            }
+        }
+    } else {
+#pragma unroll kUnroll
+        for (int i = 0; i < S.ns; ++i) sphere(i);
+        if (kCubes) for (int i = S.ns; i < S.ns + S.nc; ++i) cube(i);
     }
     if (best_idx == 0x7fffffff) best_idx = -1;
 }
@@ -358,17 +392,20 @@ render_f64_kernel(DevScene64 sc, CamParams cam, double* __restrict__ out_f64, fl
         // stage the intersect streams: coalesced 16-byte loads, one pass per block
         double2* s_sph = smem;
         double2* s_pl = s_sph + 6 * n_solid;
-        int32_t* s_si = reinterpret_cast<int32_t*>(s_pl + 2 * sc.n_planes);
+        float4* s_bound = reinterpret_cast<float4*>(s_pl + 2 * sc.n_planes);
+        int32_t* s_si = reinterpret_cast<int32_t*>(s_bound + sc.n_bound4);
         int32_t* s_pi = s_si + n_solid;
         for (int i = threadIdx.x; i < 6 * n_solid; i += kThreads) s_sph[i] = sc.sph_rows[i];
         for (int i = threadIdx.x; i < 2 * sc.n_planes; i += kThreads) s_pl[i] = sc.pl_rows[i];
+        for (int i = threadIdx.x; i < sc.n_bound4; i += kThreads) s_bound[i] = sc.bound[i];
         for (int i = threadIdx.x; i < n_solid; i += kThreads) s_si[i] = sc.sph_index[i];
         for (int i = threadIdx.x; i < sc.n_planes; i += kThreads) s_pi[i] = sc.pl_index[i];
         __syncthreads();
-        S.sph = s_sph; S.pl = s_pl; S.sph_index = s_si; S.pl_index = s_pi;
+        S.sph = s_sph; S.pl = s_pl; S.sph_index = s_si; S.pl_index = s_pi; S.bound = s_bound;
     } else {
-        S.sph = sc.sph_rows; S.pl = sc.pl_rows; S.sph_index = sc.sph_index; S.pl_index = sc.pl_index;
+        S.sph = sc.sph_rows; S.pl = sc.pl_rows; S.sph_index = sc.sph_index; S.pl_index = sc.pl_index; S.bound = sc.bound;
     }
+    S.nb4 = sc.n_bound4; S.cmax = sc.bound_cmax; S.rmax = sc.bound_rmax;
 
     const int ss = cam.samples == 1 ? 1 : 2;  // samples per pixel edge
     int sx, sy;
@@ -657,7 +694,7 @@ cudaError_t launch_render_f64(const DevScene64& scene, const CamParams& cam, voi
     double* o64 = cam.out_format == RTC_OUT_F64_RGB ? (double*)d_rgb : nullptr;
     float* o32 = cam.out_format == RTC_OUT_F32_RGB ? (float*)d_rgb : nullptr;
     uint8_t* o8 = cam.out_format == RTC_OUT_U8_RGB ? (uint8_t*)d_rgb : nullptr;
-    size_t smem = (size_t)(scene.n_spheres + scene.n_cubes) * (6 * 16 + 4) + (size_t)scene.n_planes * (2 * 16 + 4) + 16;
+    size_t smem = (size_t)(scene.n_spheres + scene.n_cubes) * (6 * 16 + 4) + (size_t)scene.n_planes * (2 * 16 + 4) + (size_t)scene.n_bound4 * 16 + 16;
     auto launch = [&](auto kernel, size_t bytes) -> cudaError_t {
         if (bytes) {
             cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);

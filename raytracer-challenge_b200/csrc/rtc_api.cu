@@ -67,6 +67,7 @@ struct DeviceState {
     DevBuf<float4> pl32, us32, gs32, bound;
     DevBuf<int32_t> sph_index, pl_index, us_index, gs_index, gset;
     DevBuf<float> plL, usL;
+    DevBuf<float4> bound64;
     DevBuf<double> lights64;   // [n_lights][6]
     DevBuf<float4> lights32;   // [n_lights][2]
     DevBuf<ShadeRec64> rec64;
@@ -242,6 +243,8 @@ struct HostScene {
     int light_inside = 0;                 // bit k: light k inside some uniform sphere
     std::vector<float4> bound;            // bounding spheres of us32 | gs32 objects (DevScene32::bound)
     float bound_cmax = 0.f, bound_rmax = 0.f;
+    std::vector<float4> bound64;          // bounding spheres of the sph64 entries (spheres | cubes; DevScene64::bound)
+    float bound64_cmax = 0.f, bound64_rmax = 0.f;
     std::vector<ShadeRec64> rec64;
     std::vector<ShadeRec32> rec32;
     int ids_unique = 1;
@@ -458,6 +461,28 @@ int flatten(const rtc_light* lights, size_t n_lights, const rtc_shape* shapes, s
         else {
             while (hs.bound.size() % 4) hs.bound.push_back(make_float4(0.f, 0.f, 0.f, std::numeric_limits<float>::infinity()));
             hs.bound_cmax = (float)(cmax * (1.0 + 1e-6)); hs.bound_rmax = (float)(rmax * (1.0 + 1e-6));
+        }
+    }
+
+    // the same for the parity kernel's stream (spheres | cubes in sph64 order)
+    {
+        bool ok = true;
+        double cmax = 0.0, rmax = 0.0;
+        for (int k = 0; ok && k < (int)hs.sph_index.size(); ++k) {
+            double c[3], r = 0.0;
+            ok = bounding_sphere(shapes[hs.sph_index[k]].inv, k < hs.n_spheres ? 1.0 : std::sqrt(3.0), c, r);
+            if (!ok) break;
+            // the centre is rounded to f32 (<= 6e-8 |c| per component): widen the radius by that much
+            r += 2e-7 * (std::fabs(c[0]) + std::fabs(c[1]) + std::fabs(c[2]));
+            hs.bound64.push_back(make_float4((float)c[0], (float)c[1], (float)c[2], -(float)(r * r * (1.0 + 1e-6))));
+            cmax = std::max(cmax, std::fabs(c[0]) + std::fabs(c[1]) + std::fabs(c[2]));
+            rmax = std::max(rmax, r);
+        }
+        ok = ok && std::isfinite(cmax) && std::isfinite(rmax) && cmax < 1e15 && rmax < 1e15;
+        if (!ok) hs.bound64.clear();
+        else {
+            while (hs.bound64.size() % 4) hs.bound64.push_back(make_float4(0.f, 0.f, 0.f, std::numeric_limits<float>::infinity()));
+            hs.bound64_cmax = (float)(cmax * (1.0 + 1e-6)); hs.bound64_rmax = (float)(rmax * (1.0 + 1e-6));
         }
     }
 
@@ -711,7 +736,11 @@ void fill_small_camera(SmallParams& P, const CamParams& cam) {
 int launch_on(DeviceState& d, const CamParams& cp, int precision, int flags, void* d_rgb, uint8_t* d_hit, Counters* d_counters,
               cudaStream_t st) {
     cudaError_t e;
-    if (precision == RTC_PRECISION_F64_PARITY) e = launch_render_f64(d.s64, cp, d_rgb, d_hit, d_counters, st);
+    if (precision == RTC_PRECISION_F64_PARITY) {
+        DevScene64 s64 = d.s64;
+        if (flags & RTC_OPT_NO_BOUND_FILTER) s64.n_bound4 = 0;
+        e = launch_render_f64(s64, cp, d_rgb, d_hit, d_counters, st);
+    }
     else if (d.small_ok && !(flags & RTC_OPT_F32_GENERAL_KERNEL)) {
         SmallParams P = d.small;
         fill_small_camera(P, cp);
@@ -794,7 +823,7 @@ void rtc_context_destroy(rtc_context* ctx) {
     for (DeviceState& d : ctx->devs) {
         cudaSetDevice(d.dev);
         if (d.stream) cudaStreamSynchronize(d.stream);
-        d.sph64.release(); d.pl64.release(); d.pl32.release(); d.us32.release(); d.gs32.release(); d.us_index.release(); d.gs_index.release(); d.gset.release(); d.plL.release(); d.usL.release(); d.lights64.release(); d.lights32.release(); d.bound.release();
+        d.sph64.release(); d.pl64.release(); d.pl32.release(); d.us32.release(); d.gs32.release(); d.us_index.release(); d.gs_index.release(); d.gset.release(); d.plL.release(); d.usL.release(); d.lights64.release(); d.lights32.release(); d.bound64.release(); d.bound.release();
         d.sph_index.release(); d.pl_index.release(); d.rec64.release(); d.rec32.release(); d.srec.release();
         d.rgb.release(); d.hit.release(); d.counters.release(); d.work.release(); d.order.release();
         if (d.ev_k0) cudaEventDestroy(d.ev_k0);
@@ -839,6 +868,7 @@ int rtc_scene_upload_lights(rtc_context* ctx, const rtc_light* light, size_t n_l
         CUDA_TRY(upload(d.lights64, hs.lights64, d.stream));
         CUDA_TRY(upload(d.lights32, hs.lights32, d.stream));
         CUDA_TRY(upload(d.bound, hs.bound, d.stream));
+        CUDA_TRY(upload(d.bound64, hs.bound64, d.stream));
         CUDA_TRY(upload(d.sph_index, hs.sph_index, d.stream));
         CUDA_TRY(upload(d.pl_index, hs.pl_index, d.stream));
         CUDA_TRY(upload(d.rec64, hs.rec64, d.stream));
@@ -864,6 +894,7 @@ int rtc_scene_upload_lights(rtc_context* ctx, const rtc_light* light, size_t n_l
         d.s64.n_lights = d.s32.n_lights = (int)n_lights;
         d.s64.lights = d.lights64.p; d.s32.lights = d.lights32.p;
         d.s32.rec = d.rec32.p;
+        d.s64.bound = d.bound64.p; d.s64.n_bound4 = (int)hs.bound64.size(); d.s64.bound_cmax = hs.bound64_cmax; d.s64.bound_rmax = hs.bound64_rmax;
         d.s32.bound = d.bound.p; d.s32.n_bound4 = (int)hs.bound.size(); d.s32.bound_cmax = hs.bound_cmax; d.s32.bound_rmax = hs.bound_rmax;
         for (int k = 0; k < 3; ++k) {
             d.s64.light_pos[k] = light->position[k]; d.s64.light_int[k] = light->intensity[k];

@@ -47,6 +47,15 @@ struct DevScene64 {
     double light_int[3];
     int n_lights, pad1;        // rtc_scene_upload_lights: lights 1..n_lights-1 live in `lights`
     const double* lights;      // [n_lights][6]: position xyz, intensity rgb
+    // f32 bounding spheres (cx, cy, cz, -R^2) of the spheres | cubes in sph_rows order, padded to a multiple of four with
+    // (0, 0, 0, +inf): the parity kernel runs a shape's exact f64 test only when the ray's LINE passes within R plus a
+    // rounding margin of the centre (nine FFMA on the otherwise idle FP32 pipe against ~54 unfused FP64 operations).  A
+    // shape the filter skips is one whose exact test finds no root, so the list of intersections — and with it every
+    // bit of the frame and every counter — is unchanged.  n_bound4 = 0: no filter (RTC_OPT_NO_BOUND_FILTER, or a shape
+    // without a finite bound).
+    const float4* bound;
+    int n_bound4;
+    float bound_cmax, bound_rmax;
 };
 
 // ---- f32 (fast) layout ------------------------------------------------------------------------

@@ -560,6 +560,38 @@ def test_bounding_sphere_filter_changes_nothing(rtc, renderer, c4_flat):
         assert out[0][2] == out[1][2] and out[0][2][0] > d.hsize * d.vsize
 
 
+def test_f64_line_distance_filter_changes_nothing(rtc, renderer, c4_flat):
+    """The parity kernel runs a sphere's / cube's exact f64 test only when an f32 test says the ray's line passes within
+    its bounding sphere plus a rounding margin (render_f64.cu intersect_world).  Skipped shapes have no root, so frame,
+    hit mask and counters are those of the plain loops (RTC_OPT_NO_BOUND_FILTER) bit for bit: the room (streams in
+    shared memory), 10k spheres (global memory), cubes / needles / affine spheres, resample pass, two lights."""
+    import torch
+    ffi = rtc.ffi
+    two = rtc.scenes.reflect_refract_scene()
+    two.add_light(rtc.Light(rtc.Color(0.3, 0.5, 0.9), (3.5, 3.0, -3.0)))
+    cube_world, cube_cam = rtc.scenes.cube_scene(7, hsize=120, vsize=84)
+    for world, flat, cam in ((rtc.scenes.reflect_refract_scene(), None, rtc.scenes.reflect_refract_camera(640, 320)),
+                             (rtc.scenes.reflect_refract_scene(), None, rtc.scenes.reflect_refract_camera(160, 80, samples=3)),
+                             (two, None, rtc.scenes.reflect_refract_camera(200, 100)),
+                             (cube_world, None, cube_cam),
+                             (None, c4_flat, rtc.scenes.synthetic_camera(320, 180)),
+                             (None, _big_mixed_world(rtc).flatten(), rtc.scenes.synthetic_camera(240, 135))):
+        if world is not None:
+            renderer.upload(world)
+        else:
+            renderer.upload_flat(*flat)
+        d = cam.flatten()
+        out = []
+        for flags in (0, ffi.OPT_NO_BOUND_FILTER):
+            buf = torch.empty((d.vsize, d.hsize, 3), dtype=torch.float64, device="cuda")
+            hit = torch.empty((d.vsize, d.hsize), dtype=torch.uint8, device="cuda")
+            st = ffi.RtcStats()
+            renderer.render_device(d, rtc.Renderer.make_opts(precision=ffi.PRECISION_F64_PARITY, flags=flags), buf.data_ptr(), hit.data_ptr(), None, st)
+            out.append((buf, hit, (st.rays, st.primary_hits, st.shaded_hits, st.shadow_rays), st.kernel_ms))
+        assert torch.equal(out[0][1], out[1][1]) and torch.equal(out[0][0], out[1][0])
+        assert out[0][2] == out[1][2] and out[0][2][0] >= d.hsize * d.vsize
+
+
 def test_big_mixed_world_f64_parity_and_f32(rtc, orc, renderer):
     """The same mixed world against the oracle (f64 parity; f32 within the C4 tolerance) on a small frame."""
     cam = rtc.scenes.synthetic_camera(96, 54)
