@@ -328,16 +328,30 @@ def run_gpu(args):
             r.upload_flat(*flat)
             r.render(camd, oe, want_mask=False, out=host, want_stats=False)
     else:
-        d2h = H * W * 3 * 4   # as at N = 1: the frame crosses PCIe as f32 and is widened into the f64 Canvas layout on the host
-        pe = Path(ffi.PRECISION_F32_FAST, ffi.OUT_F32_RGB, "p2p")   # every rank's pixels straight into rank 0's f32 frame
-        host = np.zeros((H, W, 3), dtype=np.float64) if rank == 0 else None
+        # N rank processes, one Canvas: the f64 frame lives in host memory all ranks map (POSIX shared memory created by
+        # rank 0) and every rank's rtc_render fills in the rows of its shard — kernel, D2H over its own PCIe link (f32) and
+        # widening by its own host threads.  No gather, no collective on the data path; h2d / d2h bytes are per rank.
+        from multiprocessing import shared_memory
+        d2h = my_rows * W * 3 * 4
+        name = [None]
+        if rank == 0:
+            shm = shared_memory.SharedMemory(create=True, size=H * W * 3 * 8)
+            name[0] = shm.name
+        dist.broadcast_object_list(name, src=0)
+        if rank != 0:
+            shm = shared_memory.SharedMemory(name=name[0])
+            try:   # the creator unlinks it; keep the resource tracker of the other ranks out of it
+                from multiprocessing import resource_tracker
+                resource_tracker.unregister(shm._name, "shared_memory")
+            except Exception:
+                pass
+        host = np.ndarray((H, W, 3), dtype=np.float64, buffer=shm.buf)
+        oes = rtc.Renderer.make_opts(precision=ffi.PRECISION_F32_FAST, rect=ffi.RECT_FULL, max_depth=DEPTH, out_format=ffi.OUT_F64_RGB,
+                                     shard_index=rank, shard_count=N, tile_rows=TILE)
 
         def e2e_step():
             r.upload_flat(*flat)
-            pe.frame()
-            if rank == 0:   # rtc_download_frame: banded D2H behind the completion flags + host delivery
-                r.download_frame(pe.sf.frame.data_ptr(), ffi.OUT_F32_RGB, W, H, host, stream)
-            torch.cuda.synchronize()
+            r.render(camd, oes, want_mask=False, out=host, want_stats=False)
     for _ in range(2):
         e2e_step()
     sync_all()
@@ -352,6 +366,15 @@ def run_gpu(args):
     if N > 1:
         dist.all_reduce(e2e_t, op=dist.ReduceOp.MAX)
     e2e_ms = float(e2e_t.mean()) * 1e3
+    if N > 1:
+        sync_all()   # every rank's rows are in the shared frame: it must be the frame one GPU renders
+        if rank == 0:
+            ref = torch.empty((H, W, 3), dtype=torch.float32, device=dev)
+            r.render_device(camd, rtc.Renderer.make_opts(precision=ffi.PRECISION_F32_FAST, rect=ffi.RECT_FULL, max_depth=DEPTH,
+                                                         out_format=ffi.OUT_F32_RGB), ref.data_ptr(), None, None, None)
+            torch.cuda.synchronize()
+            frame_check["e2e_shared_host_frame_equals_1gpu_frame"] = bool(np.array_equal(host, ref.cpu().numpy().astype(np.float64)))
+            del ref
 
     if rank == 0:
         peaks = measured_peaks()
@@ -385,7 +408,8 @@ def run_gpu(args):
             "e2e": {"value": rays / (e2e_ms * 1e-3) / 1e6, "unit": "Mrays/s", "ms_per_frame": e2e_ms, "h2d_bytes_per_step": int(h2d),
                     "d2h_bytes_per_step": int(d2h), "steps": e2e_steps,
                     "path": "rtc_scene_upload + rtc_render (f32 fast, F64_RGB Canvas layout) into a host buffer" if N == 1 else
-                            "rtc_scene_upload + rtc_render_device shards with peer stores into rank 0's frame + rtc_download_frame (f32 over PCIe, widened into the f64 Canvas layout) on rank 0"},
+                            "every rank: rtc_scene_upload + rtc_render of its shard (interleaved row tiles) into ONE f64 Canvas frame in host memory shared by the rank "
+                            "processes — f32 over the rank's own PCIe link, widened by its own host threads; no gather; bytes are per rank; time = max over ranks"},
             # kernels of this library inside the timed region, all ranks: rank 0 runs the tile scheduling pre-pass +
             # the render kernel (+ the flag wait when N > 1); every other rank the render kernel + its flag store
             "gpu_launches": args.steps * (2 if N == 1 else 3 + 2 * (N - 1)),
@@ -402,10 +426,15 @@ def run_gpu(args):
             line["cpu_baseline"] = {"value": s["mrays_per_s"], "unit": "Mrays/s", "cores": cores, "kind": "port", "cpu": model,
                                     "sample": s["sample"], "ms_per_frame_extrapolated": s["ms_per_frame_extrapolated"]}
         print(json.dumps(line), flush=True)
+    if N > 1:
+        del host
+        sync_all()
+        shm.close()
+        if rank == 0:
+            shm.unlink()
     main.sf.close()
     p64.sf.close()
     if N > 1:
-        pe.sf.close()
         dist.barrier()
         dist.destroy_process_group()
     return 0

@@ -133,9 +133,11 @@ typedef struct rtc_render_opts {
     int32_t rect;        /* RTC_RECT_* */
     int32_t max_depth;   /* Camera::MAX_REFLECTIONS = 5 (src/camera.rs:31); 0..RTC_MAX_DEPTH */
     int32_t out_format;  /* RTC_OUT_* */
-    /* Row-tile sharding (rtc_render_device only; rtc_render shards over the context's GPUs
-     * itself).  Tile k = rows [k*tile_rows, (k+1)*tile_rows) belongs to shard k % shard_count.
-     * shard_count <= 1 renders the whole frame. */
+    /* Row-tile sharding.  Tile k = rows [k*tile_rows, (k+1)*tile_rows) belongs to shard k % shard_count.
+     * shard_count <= 1 renders the whole frame.  rtc_render_device: the shard's compact buffer (or its rows of a
+     * full frame with RTC_OPT_DST_FULL_FRAME).  rtc_render on a one-GPU context: out_rgb / out_hit_mask are the FULL
+     * frame and only the shard's rows are written (one process per GPU filling a frame in shared host memory, every
+     * GPU over its own PCIe link); a context with several GPUs shards over them itself and ignores these fields. */
     int32_t shard_index;
     int32_t shard_count;
     int32_t tile_rows;

@@ -1130,6 +1130,85 @@ extern "C" int rtc_render(rtc_context* ctx, const rtc_camera* cam, const rtc_ren
     std::memset(&st, 0, sizeof st);
     unsigned char* user = (unsigned char*)out_rgb;
 
+    if (G == 1 && opts->shard_count > 1) {
+        // One shard of the frame, one process per GPU (torchrun style): out_rgb is the FULL frame — typically memory the
+        // rank processes share — and this call fills in the rows of its shard only (tile k -> shard k % shard_count).
+        // Every GPU delivers its rows over its own PCIe link and its own host threads: no gather step, no collective.
+        // The shard is rendered into a compact device buffer by one launch; its D2H runs in up to four chunks of whole
+        // tiles and the host places (and, in fast mode, widens) the tiles of chunk c while chunk c+1 crosses PCIe.
+        DeviceState& d = ctx->devs[0];
+        CUDA_TRY(cudaSetDevice(d.dev));
+        const int tile_rows = opts->tile_rows > 0 ? opts->tile_rows : 16;
+        CamParams cp = make_cam(cam, &dopts, opts->shard_index, opts->shard_count, tile_rows);
+        const int shard_rows = cp.shard_rows;
+        if (shard_rows <= 0) { if (stats) *stats = st; return RTC_OK; }
+        const size_t shard_bytes = (size_t)shard_rows * row_bytes;
+        CUDA_TRY(d.rgb.ensure(shard_bytes));
+        if (out_hit_mask) CUDA_TRY(d.hit.ensure((size_t)shard_rows * cam->hsize));
+        CUDA_TRY(cudaMemsetAsync(d.counters.p, 0, sizeof(Counters), d.stream));
+        CUDA_TRY(cudaEventRecord(d.ev_k0, d.stream));
+        rc = launch_on(d, cp, opts->precision, opts->flags, d.rgb.p, out_hit_mask ? d.hit.p : nullptr, stats ? d.counters.p : nullptr, d.stream);
+        if (rc != RTC_OK) return rc;
+        CUDA_TRY(cudaEventRecord(d.ev_k1, d.stream));
+        CUDA_TRY(cudaStreamWaitEvent(d.copy_stream, d.ev_k1, 0));
+        const int n_tiles = (shard_rows + tile_rows - 1) / tile_rows;
+        const int n_chunks = std::max(1, std::min(n_tiles, shard_bytes >= (4u << 20) ? 4 : 1));
+        int chunk_t0[5];
+        for (int c = 0; c <= n_chunks; ++c) chunk_t0[c] = (int)((long long)n_tiles * c / n_chunks);
+        for (int c = 0; c < n_chunks; ++c) {
+            const int r0 = chunk_t0[c] * tile_rows, r1 = std::min(shard_rows, chunk_t0[c + 1] * tile_rows);
+            CUDA_TRY(cudaMemcpyAsync(ctx->pinned_rgb + (size_t)r0 * row_bytes, d.rgb.p + (size_t)r0 * row_bytes, (size_t)(r1 - r0) * row_bytes,
+                                     cudaMemcpyDeviceToHost, d.copy_stream));
+            if (out_hit_mask)
+                CUDA_TRY(cudaMemcpyAsync(ctx->pinned_hit + (size_t)r0 * cam->hsize, d.hit.p + (size_t)r0 * cam->hsize, (size_t)(r1 - r0) * cam->hsize,
+                                         cudaMemcpyDeviceToHost, d.copy_stream));
+            CUDA_TRY(cudaEventRecord(d.ev_copy[c], d.copy_stream));
+        }
+        if (stats) CUDA_TRY(cudaMemcpyAsync(&ctx->pinned_counters[0], d.counters.p, sizeof(Counters), cudaMemcpyDeviceToHost, d.stream));
+        if (!ctx->pool) {   // shard_count rank processes share the host cores: a share of them each
+            unsigned hw = std::thread::hardware_concurrency();
+            if (const char* env = std::getenv("RTC_B200_HOST_THREADS")) hw = (unsigned)std::max(1, std::atoi(env));
+            else hw = std::max(1u, std::min(hw, 32u) / (unsigned)opts->shard_count);
+            ctx->pool = new HostPool((int)hw - 1);
+        }
+        const bool widen = dev_elem == 4 && out_elem == 8;
+        const int shard_index = opts->shard_index, shard_count = opts->shard_count;
+        const unsigned char* staged = ctx->pinned_rgb;
+        const unsigned char* staged_hit = ctx->pinned_hit;
+        const size_t hsize = cam->hsize;
+        double deliver_ms = 0.0;
+        for (int c = 0; c < n_chunks; ++c) {
+            CUDA_TRY(cudaEventSynchronize(d.ev_copy[c]));
+            auto h0 = std::chrono::steady_clock::now();
+            const int t0c = chunk_t0[c];
+            auto task = [=](int i) {   // one tile: compact rows [r0, r1) -> their frame rows (contiguous in both)
+                const int r0 = (t0c + i) * tile_rows, r1 = std::min(shard_rows, r0 + tile_rows);
+                const size_t fr = (size_t)shard_row_to_frame_row(r0, tile_rows, shard_index, shard_count);
+                const size_t n = (size_t)(r1 - r0) * row_elems;
+                if (widen) rtc_host_widen_f32_f64(reinterpret_cast<double*>(user) + fr * row_elems, reinterpret_cast<const float*>(staged) + (size_t)r0 * row_elems, n);
+                else std::memcpy(user + fr * row_elems * out_elem, staged + (size_t)r0 * row_bytes, n * out_elem);
+                if (out_hit_mask) std::memcpy(out_hit_mask + fr * hsize, staged_hit + (size_t)r0 * hsize, (size_t)(r1 - r0) * hsize);
+            };
+            const int n_c = chunk_t0[c + 1] - t0c;
+            if (n_c == 1) task(0); else if (n_c > 1) ctx->pool->parallel_for(n_c, task);
+            deliver_ms += std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - h0).count();
+        }
+        CUDA_TRY(cudaStreamSynchronize(d.stream));
+        float k_ms = 0.f;
+        CUDA_TRY(cudaEventElapsedTime(&k_ms, d.ev_k0, d.ev_k1));
+        if (stats) {
+            const Counters& c = ctx->pinned_counters[0];
+            st.rays = c.rays; st.primary_hits = c.primary_hits; st.shaded_hits = c.shaded_hits; st.shadow_rays = c.shadow_rays;
+        }
+        st.kernel_launches = 1;
+        st.kernel_ms = k_ms;
+        st.total_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+        st.d2h_ms = st.total_ms - k_ms;
+        st.gather_ms = deliver_ms;
+        if (stats) *stats = st;
+        return RTC_OK;
+    }
+
     if (G == 1) {
         // One GPU: the frame is rendered as up to 8 contiguous row bands (one launch each, rows
         // [row0, row0 + rows) written at their frame positions).  Band b's D2H runs on the copy stream

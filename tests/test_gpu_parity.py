@@ -463,6 +463,36 @@ def test_shards_compact_gather_and_full_frame_destination(rtc, orc, renderer, pr
     assert torch.equal(full, whole) and torch.equal(full_hit, whole_hit)
 
 
+@pytest.mark.parametrize("precision", [0, 1])
+@pytest.mark.parametrize("count,tile,size", [(2, 4, (200, 117)), (3, 16, (200, 117)), (8, 4, (1920, 1080))])
+def test_rtc_render_shards_into_one_host_frame(rtc, renderer, precision, count, tile, size):
+    """rtc_render with shard_count > 1 (one-GPU context): every call fills in its shard's rows of the caller's full
+    host frame and leaves the other rows alone — what N rank processes do with a frame in shared host memory.  All
+    shards together equal the unsharded frame bit for bit (f64 Canvas layout, fast mode widened on the host)."""
+    world = rtc.scenes.reflect_refract_scene()
+    cam = rtc.scenes.reflect_refract_camera(size[0], size[1])
+    d = cam.flatten()
+    renderer.upload(world)
+    whole, whole_hit, st = renderer.render(d, rtc.Renderer.make_opts(precision=precision))
+    frame = np.full((size[1], size[0], 3), -7.0)
+    mask = np.full((size[1], size[0]), 99, dtype=np.uint8)
+    rays = 0
+    for k in range(count):
+        o = rtc.Renderer.make_opts(precision=precision, shard_index=k, shard_count=count, tile_rows=tile)
+        if k == 1:   # the other shards' rows are untouched
+            before = frame.copy()
+        stats = rtc.ffi.RtcStats()
+        import ctypes as C
+        rtc.ffi.check(rtc.ffi.lib().rtc_render(renderer.handle, C.byref(d), C.byref(o), frame.ctypes.data_as(C.c_void_p),
+                                               mask.ctypes.data_as(C.c_void_p), C.byref(stats)))
+        rays += stats.rays
+        if k == 1:
+            rows = np.arange(size[1])
+            mine = (rows // tile) % count == 1
+            assert np.array_equal(frame[~mine], before[~mine]) and not np.array_equal(frame[mine], before[mine])
+    assert np.array_equal(frame, whole) and np.array_equal(mask, whole_hit) and rays == st.rays
+
+
 # ---- configs C4 and C5 of BASELINE.json ------------------------------------------------------------
 @pytest.fixture(scope="module")
 def c4_flat(rtc):
