@@ -407,6 +407,7 @@ def run_gpu(args):
                     "peak_dfma_tflops_measured": pk64},
             "e2e": {"value": rays / (e2e_ms * 1e-3) / 1e6, "unit": "Mrays/s", "ms_per_frame": e2e_ms, "h2d_bytes_per_step": int(h2d),
                     "d2h_bytes_per_step": int(d2h), "steps": e2e_steps,
+                    "ms_per_frame_min": float(e2e_t.min()) * 1e3, "ms_per_frame_median": float(e2e_t.median()) * 1e3,
                     "path": "rtc_scene_upload + rtc_render (f32 fast, F64_RGB Canvas layout) into a host buffer" if N == 1 else
                             "every rank: rtc_scene_upload + rtc_render of its shard (interleaved row tiles) into ONE f64 Canvas frame in host memory shared by the rank "
                             "processes — f32 over the rank's own PCIe link, widened by its own host threads; no gather; bytes are per rank; time = max over ranks"},
