@@ -49,6 +49,7 @@ struct Streams32 {
     const float4* gsph;   const int32_t* gs_index; int ng;   // general spheres [0, ng), then cubes [ng, ng + nc): 3 inverse rows each
     int nc;
     const float4* bound; int nb4; float cmax, rmax;   // bounding-sphere filter (DevScene32::bound), kFilter kernels only
+    const float4* gbound; float gcmax, grmax;         // one bound per eight entries of `bound` (DevScene32::gbound)
 };
 
 // Cube::intersect_local (src/shape.rs:540-591) in object space: slab test per axis.  A zero direction
@@ -89,16 +90,16 @@ template <typename F>
 __device__ __forceinline__ void sweep_bounds(const Streams32& S, F3 o, F3 d, F exact) {
     const F3 dh = d * rsqrtf(dot(d, d));
     const F3 m = mk(o.y * dh.z - o.z * dh.y, o.z * dh.x - o.x * dh.z, o.x * dh.y - o.y * dh.x);
-    const float E = 3.8e-6f * (S.cmax + fabsf(o.x) + fabsf(o.y) + fabsf(o.z));
+    const float E = 3.8e-6f * (fmaxf(S.cmax, S.gcmax) + fabsf(o.x) + fabsf(o.y) + fabsf(o.z));
     const float margin = fmaf(E, 2.f * S.rmax + E, 2e-6f * S.rmax * S.rmax);
+    const float gmargin = fmaf(E, 2.f * S.grmax + E, 2e-6f * S.grmax * S.grmax);
     auto gap = [&](float4 b) {
         const float vx = fmaf(-b.z, dh.y, fmaf(b.y, dh.z, -m.x));
         const float vy = fmaf(-b.x, dh.z, fmaf(b.z, dh.x, -m.y));
         const float vz = fmaf(-b.y, dh.x, fmaf(b.x, dh.y, -m.z));
         return fmaf(vz, vz, fmaf(vy, vy, fmaf(vx, vx, b.w)));
     };
-#pragma unroll 2
-    for (int g = 0; g < S.nb4; g += 4) {
+    auto members = [&](int g) {    // four entries of `bound`, one branch: the exact tests sit behind it
         const float4 b0 = S.bound[g], b1 = S.bound[g + 1], b2 = S.bound[g + 2], b3 = S.bound[g + 3];
         const float s0 = gap(b0), s1 = gap(b1), s2 = gap(b2), s3 = gap(b3);
         if (fminf(fminf(s0, s1), fminf(s2, s3)) <= margin) {
@@ -107,6 +108,22 @@ __device__ __forceinline__ void sweep_bounds(const Streams32& S, F3 o, F3 d, F e
                 const int k = __ffs(cand) - 1;
                 cand &= cand - 1u;
                 exact(g + k);
+            } while (cand);
+        }
+    };
+    // group level: the streams of a big scene are in Morton order, eight consecutive entries share a bounding sphere;
+    // a ray whose line misses it (same test, same kind of margin) skips the eight.  Four groups per trip.
+    const int n_groups = S.nb4 >> 3;   // gbound is padded to a multiple of four with never-hit entries
+    for (int g8 = 0; g8 < n_groups; g8 += 4) {
+        const float4 q0 = S.gbound[g8], q1 = S.gbound[g8 + 1], q2 = S.gbound[g8 + 2], q3 = S.gbound[g8 + 3];
+        const float t0 = gap(q0), t1 = gap(q1), t2 = gap(q2), t3 = gap(q3);
+        if (fminf(fminf(t0, t1), fminf(t2, t3)) <= gmargin) {
+            unsigned cand = (t0 <= gmargin ? 1u : 0u) | (t1 <= gmargin ? 2u : 0u) | (t2 <= gmargin ? 4u : 0u) | (t3 <= gmargin ? 8u : 0u);
+            do {
+                const int k = __ffs(cand) - 1;
+                cand &= cand - 1u;
+#pragma unroll 1
+                for (int h = 0; h < 8; h += 4) members(8 * (g8 + k) + h);
             } while (cand);
         }
     }
@@ -512,6 +529,7 @@ render_f32_kernel(DevScene32 sc, CamParams cam, void* __restrict__ out_rgb, uint
     const F3 light_int = mk(sc.light_int[0], sc.light_int[1], sc.light_int[2]);
     constexpr bool kFilter = kGlobal == 2;
     S.bound = sc.bound; S.nb4 = sc.n_bound4; S.cmax = sc.bound_cmax; S.rmax = sc.bound_rmax;
+    S.gbound = sc.gbound; S.gcmax = sc.gbound_cmax; S.grmax = sc.gbound_rmax;
     if (kGlobal) {
         S.planes = sc.planes; S.usph = sc.usph; S.gsph = sc.gsph; S.pl_index = sc.pl_index; S.us_index = sc.us_index; S.gs_index = sc.gs_index;
         plL = sc.plL; usL = sc.usL; gset = sc.gset;

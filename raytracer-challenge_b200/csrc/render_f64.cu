@@ -48,6 +48,7 @@ struct Streams {  // intersect streams, in shared memory when they fit, else glo
     int nc;
     const double2* pl;  const int32_t* pl_index;  int np;
     const float4* bound; int nb4; float cmax, rmax;         // f32 bounding spheres of [0, ns + nc) (DevScene64::bound); nb4 = 0: none
+    const float4* gbound; float gcmax, grmax;               // one per eight entries of `bound` (DevScene64::gbound), padded to a multiple of four
 };
 
 // Shape::intersect + Sphere::intersect_local (src/shape.rs:23-26, 361-375)
@@ -125,7 +126,8 @@ __device__ __forceinline__ void take(double t, int idx, double& best_t, int& bes
 // and compute_refractive falls back to its two passes.
 struct Neg { double t; int ord; int pad; };
 constexpr int kNegCap = 48;
-template <bool kCollect, bool kCubes>
+// kGroups: two-level filter (streams in global memory: big scenes, Morton order); otherwise entries four at a time
+template <bool kCollect, bool kCubes, bool kGroups>
 __device__ __noinline__ void intersect_world(const Streams& S, V3 o, V3 d, double& best_t, int& best_idx, Neg* neg, int& n_neg) {
     best_t = __longlong_as_double(0x7ff0000000000000LL);
     best_idx = 0x7fffffff;
@@ -174,16 +176,19 @@ __device__ __noinline__ void intersect_world(const Streams& S, V3 o, V3 d, doubl
     const float inv_len = rsqrtf(fmaf(fdz, fdz, fmaf(fdy, fdy, fdx * fdx)));
     fdx *= inv_len; fdy *= inv_len; fdz *= inv_len;
     const float mx = foy * fdz - foz * fdy, my = foz * fdx - fox * fdz, mz = fox * fdy - foy * fdx;
-    const float E = 3.8e-6f * (S.cmax + fabsf(fox) + fabsf(foy) + fabsf(foz));
+    const float E = 3.8e-6f * (fmaxf(S.cmax, S.gcmax) + fabsf(fox) + fabsf(foy) + fabsf(foz));
     const float margin = fmaf(E, 2.f * S.rmax + E, 2e-6f * S.rmax * S.rmax);
+    const float gmargin = fmaf(E, 2.f * S.grmax + E, 2e-6f * S.grmax * S.grmax);
     auto gap = [&](float4 b) {
         const float vx = fmaf(-b.z, fdy, fmaf(b.y, fdz, -mx));
         const float vy = fmaf(-b.x, fdz, fmaf(b.z, fdx, -my));
         const float vz = fmaf(-b.y, fdx, fmaf(b.x, fdy, -mz));
         return fmaf(vz, vz, fmaf(vy, vy, fmaf(vx, vx, b.w)));
     };
+    // Two levels: eight consecutive entries (big scenes are stored in Morton order: neighbours in space) share a
+    // bounding sphere, four such groups per trip; inside a candidate group, four entries per trip.
     const int n_solid = S.ns + (kCubes ? S.nc : 0);
-    for (int g = 0; g < n_solid; g += 4) {   // (unroll 2 measured: room 7.35 -> 8.8 ms, C4 unchanged)
+    auto members = [&](int g) {   // entries g .. g+3: the exact tests of the candidates
         unsigned cand;
         if (filter) {   // the padding entries of the last group have gap = +inf: never candidates
             const float4 b0 = S.bound[g], b1 = S.bound[g + 1], b2 = S.bound[g + 2], b3 = S.bound[g + 3];
@@ -196,6 +201,26 @@ __device__ __noinline__ void intersect_world(const Streams& S, V3 o, V3 d, doubl
             const int i = g + __ffs(cand) - 1;
             cand &= cand - 1u;
             if (!kCubes || i < S.ns) sphere(i); else cube(i);
+        }
+    };
+    if (!kGroups) {
+        for (int g = 0; g < n_solid; g += 4) members(g);   // (unroll 2 measured: room 7.35 -> 8.8 ms)
+    } else {
+        const int n_groups = (n_solid + 7) >> 3;
+        for (int g8 = 0; g8 < n_groups; g8 += 4) {
+            unsigned gcand = n_groups - g8 >= 4 ? 15u : (1u << (n_groups - g8)) - 1u;
+            if (filter) {   // the padding groups have gap = +inf: never candidates
+                const float4 q0 = S.gbound[g8], q1 = S.gbound[g8 + 1], q2 = S.gbound[g8 + 2], q3 = S.gbound[g8 + 3];
+                const float t0 = gap(q0), t1 = gap(q1), t2 = gap(q2), t3 = gap(q3);
+                gcand = (!(t0 > gmargin) ? 1u : 0u) | (!(t1 > gmargin) ? 2u : 0u) | (!(t2 > gmargin) ? 4u : 0u) | (!(t3 > gmargin) ? 8u : 0u);
+            }
+            while (gcand) {
+                const int gk = g8 + __ffs(gcand) - 1;
+                gcand &= gcand - 1u;
+#pragma unroll 1
+                for (int h = 0; h < 8; h += 4)
+                    if (8 * gk + h < n_solid) members(8 * gk + h);
+            }
         }
     }
     if (best_idx == 0x7fffffff) best_idx = -1;
@@ -396,19 +421,22 @@ render_f64_kernel(DevScene64 sc, CamParams cam, double* __restrict__ out_f64, fl
         double2* s_sph = smem;
         double2* s_pl = s_sph + 6 * n_solid;
         float4* s_bound = reinterpret_cast<float4*>(s_pl + 2 * sc.n_planes);
-        int32_t* s_si = reinterpret_cast<int32_t*>(s_bound + sc.n_bound4);
+        float4* s_gbound = s_bound + sc.n_bound4;
+        const int n_gb = sc.n_bound4 > 0 ? ((sc.n_bound4 >> 3) + 3) / 4 * 4 : 0;
+        int32_t* s_si = reinterpret_cast<int32_t*>(s_gbound + n_gb);
         int32_t* s_pi = s_si + n_solid;
         for (int i = threadIdx.x; i < 6 * n_solid; i += kThreads) s_sph[i] = sc.sph_rows[i];
         for (int i = threadIdx.x; i < 2 * sc.n_planes; i += kThreads) s_pl[i] = sc.pl_rows[i];
         for (int i = threadIdx.x; i < sc.n_bound4; i += kThreads) s_bound[i] = sc.bound[i];
+        for (int i = threadIdx.x; i < n_gb; i += kThreads) s_gbound[i] = sc.gbound[i];
         for (int i = threadIdx.x; i < n_solid; i += kThreads) s_si[i] = sc.sph_index[i];
         for (int i = threadIdx.x; i < sc.n_planes; i += kThreads) s_pi[i] = sc.pl_index[i];
         __syncthreads();
-        S.sph = s_sph; S.pl = s_pl; S.sph_index = s_si; S.pl_index = s_pi; S.bound = s_bound;
+        S.sph = s_sph; S.pl = s_pl; S.sph_index = s_si; S.pl_index = s_pi; S.bound = s_bound; S.gbound = s_gbound;
     } else {
-        S.sph = sc.sph_rows; S.pl = sc.pl_rows; S.sph_index = sc.sph_index; S.pl_index = sc.pl_index; S.bound = sc.bound;
+        S.sph = sc.sph_rows; S.pl = sc.pl_rows; S.sph_index = sc.sph_index; S.pl_index = sc.pl_index; S.bound = sc.bound; S.gbound = sc.gbound;
     }
-    S.nb4 = sc.n_bound4; S.cmax = sc.bound_cmax; S.rmax = sc.bound_rmax;
+    S.nb4 = sc.n_bound4; S.cmax = sc.bound_cmax; S.rmax = sc.bound_rmax; S.gcmax = sc.gbound_cmax; S.grmax = sc.gbound_rmax;
 
     const int ss = cam.samples == 1 ? 1 : 2;  // samples per pixel edge
     int sx, sy;
@@ -465,7 +493,7 @@ render_f64_kernel(DevScene64 sc, CamParams cam, double* __restrict__ out_f64, fl
             bool descended = false;
             double t; int idx;
             ++n_rays;
-            intersect_world<true, kCubes>(S, ro, rd, t, idx, kept, n_neg);
+            intersect_world<true, kCubes, !kInSmem>(S, ro, rd, t, idx, kept, n_neg);
             if (first) { primary_hit = idx >= 0; first = false; }
             if (idx < 0) {
                 color = mk(0., 0., 0.);  // background_color, src/shape.rs:652
@@ -510,7 +538,7 @@ render_f64_kernel(DevScene64 sc, CamParams cam, double* __restrict__ out_f64, fl
                     V3 sdir = normalize(v);
                     double st; int sidx;
                     ++n_rays; ++n_shadow;
-                    intersect_world<false, kCubes>(S, over_point, sdir, st, sidx, kept, n_shadow_neg);
+                    intersect_world<false, kCubes, !kInSmem>(S, over_point, sdir, st, sidx, kept, n_shadow_neg);
                     bool shadowed = sidx >= 0 && st < distance;
                     V3 term = lighting(rec, lpos, lint, over_point, eyev, normal, shadowed);
                     surface = li == 0 ? term : add(surface, term);
@@ -697,7 +725,7 @@ cudaError_t launch_render_f64(const DevScene64& scene, const CamParams& cam, voi
     double* o64 = cam.out_format == RTC_OUT_F64_RGB ? (double*)d_rgb : nullptr;
     float* o32 = cam.out_format == RTC_OUT_F32_RGB ? (float*)d_rgb : nullptr;
     uint8_t* o8 = cam.out_format == RTC_OUT_U8_RGB ? (uint8_t*)d_rgb : nullptr;
-    size_t smem = (size_t)(scene.n_spheres + scene.n_cubes) * (6 * 16 + 4) + (size_t)scene.n_planes * (2 * 16 + 4) + (size_t)scene.n_bound4 * 16 + 16;
+    size_t smem = (size_t)(scene.n_spheres + scene.n_cubes) * (6 * 16 + 4) + (size_t)scene.n_planes * (2 * 16 + 4) + (size_t)scene.n_bound4 * 16 + (size_t)(scene.n_bound4 > 0 ? ((scene.n_bound4 >> 3) + 3) / 4 * 4 : 0) * 16 + 16;
     auto launch = [&](auto kernel, size_t bytes) -> cudaError_t {
         if (bytes) {
             cudaError_t e = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);

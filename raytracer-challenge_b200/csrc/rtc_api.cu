@@ -3,6 +3,7 @@
 // row-tile de-interleave, and the FMA peak micro-benchmark.
 // No CPU path exists here: every compute entry point needs a CUDA device.
 #include <algorithm>
+#include <array>
 #include <atomic>
 #include <chrono>
 #include <cmath>
@@ -68,7 +69,7 @@ struct DeviceState {
     DevBuf<float4> pl32, us32, gs32, bound;
     DevBuf<int32_t> sph_index, pl_index, us_index, gs_index, gset;
     DevBuf<float> plL, usL;
-    DevBuf<float4> bound64;
+    DevBuf<float4> bound64, gbound, gbound64;
     DevBuf<double> lights64;   // [n_lights][6]
     DevBuf<float4> lights32;   // [n_lights][2]
     DevBuf<ShadeRec64> rec64;
@@ -268,6 +269,8 @@ struct HostScene {
     float bound_cmax = 0.f, bound_rmax = 0.f;
     std::vector<float4> bound64;          // bounding spheres of the sph64 entries (spheres | cubes; DevScene64::bound)
     float bound64_cmax = 0.f, bound64_rmax = 0.f;
+    std::vector<float4> gbound, gbound64; // one bounding sphere per kGroup consecutive entries of bound / bound64
+    float gbound_cmax = 0.f, gbound_rmax = 0.f, gbound64_cmax = 0.f, gbound64_rmax = 0.f;
     std::vector<ShadeRec64> rec64;
     std::vector<ShadeRec32> rec32;
     int ids_unique = 1;
@@ -338,6 +341,79 @@ bool bounding_sphere(const double* inv, double unit_radius, double c[3], double&
     const double cn = std::fabs(c[0]) + std::fabs(c[1]) + std::fabs(c[2]);
     radius = unit_radius / std::sqrt(lo) * (1.0 + 1e-4) + 4.0 * 5.97e-8 * cn * cond;
     return std::isfinite(radius) && std::isfinite(cn);
+}
+
+// ---- spatial order + group bounds for big scenes -----------------------------------------------------
+// The intersect streams of a scene are read front to back by every ray (brute force, World::intersect
+// src/shape.rs:677-683), so their order is free as long as the index arrays follow: hit selection takes the smallest t
+// (ties: the parity kernel compares shape indices, the fast kernels take the first in stream order — equal f32 roots of
+// different shapes are not a case the tolerance cares about).  Streams with >= kSortMin entries are put in Morton order
+// of the shapes' centres, so that kGroup consecutive entries are neighbours in space and one bounding sphere around
+// them (DevScene32::gbound / DevScene64::gbound) lets a ray skip all of them with one nine-FFMA line-distance test.
+constexpr size_t kSortMin = 64;
+constexpr int kGroup = 8;
+
+std::vector<int> morton_order(const std::vector<std::array<double, 3>>& c) {
+    const size_t n = c.size();
+    std::vector<int> perm(n);
+    for (size_t i = 0; i < n; ++i) perm[i] = (int)i;
+    if (n < kSortMin) return perm;
+    double lo[3] = {1e300, 1e300, 1e300}, hi[3] = {-1e300, -1e300, -1e300};
+    for (const auto& p : c)
+        for (int k = 0; k < 3; ++k) { if (!std::isfinite(p[k])) return perm; lo[k] = std::min(lo[k], p[k]); hi[k] = std::max(hi[k], p[k]); }
+    std::vector<uint32_t> code(n);
+    auto spread = [](uint32_t v) {   // 10 bits -> every third bit
+        v &= 1023u;
+        v = (v | (v << 16)) & 0x030000FFu; v = (v | (v << 8)) & 0x0300F00Fu;
+        v = (v | (v << 4)) & 0x030C30C3u; v = (v | (v << 2)) & 0x09249249u;
+        return v;
+    };
+    for (size_t i = 0; i < n; ++i) {
+        uint32_t q[3];
+        for (int k = 0; k < 3; ++k) {
+            const double ext = hi[k] - lo[k];
+            q[k] = ext > 0.0 ? (uint32_t)std::min(1023.0, (c[i][k] - lo[k]) / ext * 1024.0) : 0u;
+        }
+        code[i] = spread(q[0]) | (spread(q[1]) << 1) | (spread(q[2]) << 2);
+    }
+    std::stable_sort(perm.begin(), perm.end(), [&](int a, int b) { return code[a] < code[b]; });
+    return perm;
+}
+template <typename T>
+void apply_perm(std::vector<T>& v, const std::vector<int>& perm, size_t stride) {
+    std::vector<T> out(v.size());
+    for (size_t i = 0; i < perm.size(); ++i)
+        for (size_t k = 0; k < stride; ++k) out[i * stride + k] = v[(size_t)perm[i] * stride + k];
+    v.swap(out);
+}
+// Bounding spheres (cx, cy, cz, -R^2) of each kGroup consecutive entries of `bound` (padding entries have w = +inf and
+// are ignored; `bound` is padded to a multiple of kGroup first).  Returns false when there is nothing to group.
+bool group_bounds(std::vector<float4>& bound, std::vector<float4>& gbound, float& gcmax, float& grmax) {
+    gbound.clear(); gcmax = 0.f; grmax = 0.f;
+    if (bound.empty()) return false;
+    while (bound.size() % kGroup) bound.push_back(make_float4(0.f, 0.f, 0.f, std::numeric_limits<float>::infinity()));
+    double cm = 0.0, rm = 0.0;
+    for (size_t g = 0; g < bound.size(); g += kGroup) {
+        double c[3] = {0, 0, 0}; int m = 0;
+        for (int k = 0; k < kGroup; ++k) { const float4& b = bound[g + k]; if (std::isinf(b.w)) continue; c[0] += b.x; c[1] += b.y; c[2] += b.z; ++m; }
+        if (m == 0) { gbound.push_back(make_float4(0.f, 0.f, 0.f, std::numeric_limits<float>::infinity())); continue; }
+        for (int k = 0; k < 3; ++k) c[k] /= m;
+        double r = 0.0;
+        for (int k = 0; k < kGroup; ++k) {
+            const float4& b = bound[g + k];
+            if (std::isinf(b.w)) continue;
+            const double dx = b.x - c[0], dy = b.y - c[1], dz = b.z - c[2];
+            r = std::max(r, std::sqrt(dx * dx + dy * dy + dz * dz) + std::sqrt(std::max(0.0, -(double)b.w)));
+        }
+        const double cn = std::fabs(c[0]) + std::fabs(c[1]) + std::fabs(c[2]);
+        r = r * (1.0 + 1e-6) + 2e-7 * cn;   // the centre is rounded to f32
+        gbound.push_back(make_float4((float)c[0], (float)c[1], (float)c[2], -(float)(r * r * (1.0 + 1e-6))));
+        cm = std::max(cm, cn); rm = std::max(rm, r);
+    }
+    if (!std::isfinite(cm) || !std::isfinite(rm)) { gbound.clear(); return false; }
+    while (gbound.size() % 4) gbound.push_back(make_float4(0.f, 0.f, 0.f, std::numeric_limits<float>::infinity()));   // four groups per trip
+    gcmax = (float)(cm * (1.0 + 1e-6)); grmax = (float)(rm * (1.0 + 1e-6));
+    return true;
 }
 
 int flatten(const rtc_light* lights, size_t n_lights, const rtc_shape* shapes, size_t n, HostScene& hs) {
@@ -446,6 +522,35 @@ int flatten(const rtc_light* lights, size_t n_lights, const rtc_shape* shapes, s
         q.tr_ri = make_float4((float)s.transparency, (float)s.refractive_index, __int_as_float_host(s.pattern_kind),
                               __int_as_float_host(geom));
     }
+    // big scenes: Morton order per stream (see morton_order)
+    {
+        auto centres_of = [&](const std::vector<int32_t>& index, double unit_radius) {
+            std::vector<std::array<double, 3>> c(index.size());
+            for (size_t k = 0; k < index.size(); ++k) {
+                double r = 0.0;
+                if (!bounding_sphere(shapes[index[k]].inv, unit_radius, c[k].data(), r)) c[k] = {NAN, NAN, NAN};
+            }
+            return c;
+        };
+        if (hs.us_index.size() >= kSortMin) {
+            std::vector<std::array<double, 3>> c(hs.us32.size());
+            for (size_t k = 0; k < c.size(); ++k) c[k] = {hs.us32[k].x, hs.us32[k].y, hs.us32[k].z};
+            const std::vector<int> perm = morton_order(c);
+            apply_perm(hs.us32, perm, 1); apply_perm(hs.us_index, perm, 1);
+        }
+        if (hs.gs_index.size() >= kSortMin) {
+            const std::vector<int> perm = morton_order(centres_of(hs.gs_index, 1.0));
+            apply_perm(hs.gs32, perm, 3); apply_perm(hs.gs_index, perm, 1);
+        }
+        if (hs.cub_index.size() >= kSortMin) {
+            const std::vector<int> perm = morton_order(centres_of(hs.cub_index, std::sqrt(3.0)));
+            apply_perm(hs.cb32, perm, 3); apply_perm(hs.cub64, perm, 6); apply_perm(hs.cub_index, perm, 1);
+        }
+        if (hs.sph_index.size() >= kSortMin) {
+            const std::vector<int> perm = morton_order(centres_of(hs.sph_index, 1.0));
+            apply_perm(hs.sph64, perm, 6); apply_perm(hs.sph_index, perm, 1);
+        }
+    }
     // cubes travel behind the spheres in the same streams (same 3x4 inverse rows; the kernels switch test at the count)
     hs.n_spheres = (int)hs.sph_index.size(); hs.n_gsph = (int)hs.gs_index.size(); hs.n_cubes = (int)hs.cub_index.size();
     hs.sph64.insert(hs.sph64.end(), hs.cub64.begin(), hs.cub64.end());
@@ -482,8 +587,8 @@ int flatten(const rtc_light* lights, size_t n_lights, const rtc_shape* shapes, s
         ok = ok && std::isfinite(cmax) && std::isfinite(rmax) && cmax < 1e15 && rmax < 1e15;
         if (!ok) hs.bound.clear();
         else {
-            while (hs.bound.size() % 4) hs.bound.push_back(make_float4(0.f, 0.f, 0.f, std::numeric_limits<float>::infinity()));
             hs.bound_cmax = (float)(cmax * (1.0 + 1e-6)); hs.bound_rmax = (float)(rmax * (1.0 + 1e-6));
+            if (!group_bounds(hs.bound, hs.gbound, hs.gbound_cmax, hs.gbound_rmax)) hs.bound.clear();
         }
     }
 
@@ -504,8 +609,8 @@ int flatten(const rtc_light* lights, size_t n_lights, const rtc_shape* shapes, s
         ok = ok && std::isfinite(cmax) && std::isfinite(rmax) && cmax < 1e15 && rmax < 1e15;
         if (!ok) hs.bound64.clear();
         else {
-            while (hs.bound64.size() % 4) hs.bound64.push_back(make_float4(0.f, 0.f, 0.f, std::numeric_limits<float>::infinity()));
             hs.bound64_cmax = (float)(cmax * (1.0 + 1e-6)); hs.bound64_rmax = (float)(rmax * (1.0 + 1e-6));
+            if (!group_bounds(hs.bound64, hs.gbound64, hs.gbound64_cmax, hs.gbound64_rmax)) hs.bound64.clear();
         }
     }
 
@@ -860,7 +965,7 @@ void rtc_context_destroy(rtc_context* ctx) {
     for (DeviceState& d : ctx->devs) {
         cudaSetDevice(d.dev);
         if (d.stream) cudaStreamSynchronize(d.stream);
-        d.sph64.release(); d.pl64.release(); d.pl32.release(); d.us32.release(); d.gs32.release(); d.us_index.release(); d.gs_index.release(); d.gset.release(); d.plL.release(); d.usL.release(); d.lights64.release(); d.lights32.release(); d.bound64.release(); d.bound.release();
+        d.sph64.release(); d.pl64.release(); d.pl32.release(); d.us32.release(); d.gs32.release(); d.us_index.release(); d.gs_index.release(); d.gset.release(); d.plL.release(); d.usL.release(); d.lights64.release(); d.lights32.release(); d.bound64.release(); d.gbound.release(); d.gbound64.release(); d.bound.release();
         d.sph_index.release(); d.pl_index.release(); d.rec64.release(); d.rec32.release(); d.srec.release();
         d.rgb.release(); d.hit.release(); d.counters.release(); d.work.release(); d.order.release();
         if (d.ev_k0) cudaEventDestroy(d.ev_k0);
@@ -906,6 +1011,8 @@ int rtc_scene_upload_lights(rtc_context* ctx, const rtc_light* light, size_t n_l
         CUDA_TRY(upload(d.lights32, hs.lights32, d.stream));
         CUDA_TRY(upload(d.bound, hs.bound, d.stream));
         CUDA_TRY(upload(d.bound64, hs.bound64, d.stream));
+        CUDA_TRY(upload(d.gbound, hs.gbound, d.stream));
+        CUDA_TRY(upload(d.gbound64, hs.gbound64, d.stream));
         CUDA_TRY(upload(d.sph_index, hs.sph_index, d.stream));
         CUDA_TRY(upload(d.pl_index, hs.pl_index, d.stream));
         CUDA_TRY(upload(d.rec64, hs.rec64, d.stream));
@@ -932,6 +1039,8 @@ int rtc_scene_upload_lights(rtc_context* ctx, const rtc_light* light, size_t n_l
         d.s64.lights = d.lights64.p; d.s32.lights = d.lights32.p;
         d.s32.rec = d.rec32.p;
         d.s64.bound = d.bound64.p; d.s64.n_bound4 = (int)hs.bound64.size(); d.s64.bound_cmax = hs.bound64_cmax; d.s64.bound_rmax = hs.bound64_rmax;
+        d.s64.gbound = d.gbound64.p; d.s64.gbound_cmax = hs.gbound64_cmax; d.s64.gbound_rmax = hs.gbound64_rmax;
+        d.s32.gbound = d.gbound.p; d.s32.gbound_cmax = hs.gbound_cmax; d.s32.gbound_rmax = hs.gbound_rmax;
         d.s32.bound = d.bound.p; d.s32.n_bound4 = (int)hs.bound.size(); d.s32.bound_cmax = hs.bound_cmax; d.s32.bound_rmax = hs.bound_rmax;
         for (int k = 0; k < 3; ++k) {
             d.s64.light_pos[k] = light->position[k]; d.s64.light_int[k] = light->intensity[k];

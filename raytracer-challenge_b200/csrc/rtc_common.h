@@ -54,8 +54,12 @@ struct DevScene64 {
     // bit of the frame and every counter — is unchanged.  n_bound4 = 0: no filter (RTC_OPT_NO_BOUND_FILTER, or a shape
     // without a finite bound).
     const float4* bound;
-    int n_bound4;
+    int n_bound4;              // entries of `bound` (a multiple of eight)
     float bound_cmax, bound_rmax;
+    // one bounding sphere per eight consecutive entries of `bound` (big scenes are stored in Morton order, so eight
+    // neighbours in the stream are neighbours in space): a ray whose line misses it skips the eight member tests
+    const float4* gbound;
+    float gbound_cmax, gbound_rmax;
 };
 
 // ---- f32 (fast) layout ------------------------------------------------------------------------
@@ -98,8 +102,10 @@ struct DevScene32 {
     // shapes) test a ray against these first — 9 FFMA per shape — and run the exact test of a shape only
     // when the ray's line passes within R + rounding margin of its centre.  n_bound4 = 0: no filter.
     const float4* bound;
-    int n_bound4;
+    int n_bound4;                   // entries of `bound` (a multiple of eight)
     float bound_cmax, bound_rmax;   // max |c|_1 and max R over the entries (rounding margin of the filter)
+    const float4* gbound;           // one bounding sphere per eight consecutive entries of `bound` (Morton-ordered streams)
+    float gbound_cmax, gbound_rmax;
     float light_pos[3];        // light 0
     float light_int[3];
     int n_lights;              // rtc_scene_upload_lights: plL / usL hold n_lights rows; lights 1.. read them from global memory
