@@ -107,7 +107,8 @@ def oracle_sample(threads, target_seconds=12.0):
     _, _, c = ow.render(cam, threads=threads, pixels=idx)
     return {"mrays_per_s": c.rays / c.seconds / 1e6, "rays": int(c.rays), "pixels": int(idx.size), "seconds": c.seconds,
             "ms_per_frame_extrapolated": (W * H / idx.size) * c.seconds * 1e3,
-            "sample": f"every {step}th pixel in x and y of the {W}x{H} frame ({idx.size} px, {c.rays} rays, {c.seconds:.1f} s)"}
+            "sample": (f"the whole {W}x{H} frame" if step == 1 else f"every {step}th pixel in x and y of the {W}x{H} frame") +
+                      f" ({idx.size} px, {c.rays} rays, {c.seconds:.1f} s)"}
 
 
 def run_reference(args):
@@ -331,21 +332,10 @@ def run_gpu(args):
         # N rank processes, one Canvas: the f64 frame lives in host memory all ranks map (POSIX shared memory created by
         # rank 0) and every rank's rtc_render fills in the rows of its shard — kernel, D2H over its own PCIe link (f32) and
         # widening by its own host threads.  No gather, no collective on the data path; h2d / d2h bytes are per rank.
-        from multiprocessing import shared_memory
+        from rtc_b200.sharded import SharedHostFrame
         d2h = my_rows * W * 3 * 4
-        name = [None]
-        if rank == 0:
-            shm = shared_memory.SharedMemory(create=True, size=H * W * 3 * 8)
-            name[0] = shm.name
-        dist.broadcast_object_list(name, src=0)
-        if rank != 0:
-            shm = shared_memory.SharedMemory(name=name[0])
-            try:   # the creator unlinks it; keep the resource tracker of the other ranks out of it
-                from multiprocessing import resource_tracker
-                resource_tracker.unregister(shm._name, "shared_memory")
-            except Exception:
-                pass
-        host = np.ndarray((H, W, 3), dtype=np.float64, buffer=shm.buf)
+        shared = SharedHostFrame(W, H, rank, N)
+        host = shared.array
         oes = rtc.Renderer.make_opts(precision=ffi.PRECISION_F32_FAST, rect=ffi.RECT_FULL, max_depth=DEPTH, out_format=ffi.OUT_F64_RGB,
                                      shard_index=rank, shard_count=N, tile_rows=TILE)
 
@@ -429,10 +419,8 @@ def run_gpu(args):
         print(json.dumps(line), flush=True)
     if N > 1:
         del host
-        sync_all()
-        shm.close()
-        if rank == 0:
-            shm.unlink()
+        torch.cuda.synchronize()
+        shared.close()
     main.sf.close()
     p64.sf.close()
     if N > 1:

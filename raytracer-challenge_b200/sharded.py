@@ -165,3 +165,39 @@ class ShardedFrame:
             self._token = torch.zeros(1, dtype=torch.int32, device=self.device)
         dist.all_reduce(self._token)
         return self.frame if self.rank == 0 else None
+
+
+class SharedHostFrame:
+    """One Canvas frame (hsize x vsize x 3, f64 by default) in host memory that all rank processes of a node map:
+    POSIX shared memory created by rank 0, its name broadcast over the process group.  Every rank's ``rtc_render`` with
+    ``shard_index = rank, shard_count = world`` fills in the rows of its shard (include/rtc.h, rtc_render_opts) — its
+    own PCIe link, its own host threads, no gather and no collective on the data path.  ``array`` is the numpy view."""
+
+    def __init__(self, hsize, vsize, rank, world, dtype="float64"):
+        import numpy as np
+        from multiprocessing import shared_memory
+        self.rank, self.world = rank, world
+        nbytes = int(hsize) * int(vsize) * 3 * np.dtype(dtype).itemsize
+        name = [None]
+        if rank == 0:
+            self._shm = shared_memory.SharedMemory(create=True, size=nbytes)
+            name[0] = self._shm.name
+        if world > 1:
+            dist.broadcast_object_list(name, src=0)
+        if rank != 0:
+            self._shm = shared_memory.SharedMemory(name=name[0])
+            try:   # rank 0 unlinks the segment; keep the other ranks' resource trackers out of it
+                from multiprocessing import resource_tracker
+                resource_tracker.unregister(self._shm._name, "shared_memory")
+            except Exception:
+                pass
+        self.array = np.ndarray((vsize, hsize, 3), dtype=dtype, buffer=self._shm.buf)
+
+    def close(self):
+        """Collective: every rank drops its view, then rank 0 removes the segment."""
+        self.array = None
+        if self.world > 1:
+            dist.barrier()
+        self._shm.close()
+        if self.rank == 0:
+            self._shm.unlink()

@@ -71,6 +71,51 @@ def test_sharded_frame_over_gloo_matches_unsharded(world, vsize, tile, _built):
     assert q.get(timeout=5) is True
 
 
+def _worker_shared(rank, world, port, vsize, hsize, tile, q):
+    sys.path.insert(0, ROOT)
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        import rtc_b200 as rtc
+        import orc
+        from rtc_b200.sharded import SharedHostFrame, frame_rows_of_shard
+        scene = rtc.scenes.reflect_refract_scene()
+        cam = rtc.scenes.reflect_refract_camera(hsize, vsize)
+        shared = SharedHostFrame(hsize, vsize, rank, world)
+        if rank == 0:
+            shared.array[:] = -1.0
+        dist.barrier()
+        rows = frame_rows_of_shard(vsize, tile, rank, world).numpy()
+        pix = (rows[:, None] * hsize + np.arange(hsize)[None, :]).reshape(-1)
+        rgb, _, _ = orc.render(scene, cam, pixels=pix)              # what rtc_render(shard opts) delivers: this rank's rows
+        shared.array[rows] = rgb.reshape(rows.size, hsize, 3)
+        dist.barrier()
+        if rank == 0:
+            want, _, _ = orc.render(scene, cam)
+            q.put(bool(np.array_equal(shared.array, want)))
+        shared.close()
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world,vsize,tile", [(2, 33, 4), (3, 50, 8)])
+def test_shared_host_frame_over_gloo(world, vsize, tile, _built):
+    """The end-to-end N > 1 path of bench.py on CPU: one frame in shared host memory, every rank fills in the rows of
+    its shard (here the oracle stands in for rtc_render's shard mode), no exchange step."""
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_worker_shared, args=(r, world, port, vsize, 48, tile, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    for p in procs:
+        p.join(120)
+        assert p.exitcode == 0
+    assert q.get(timeout=5) is True
+
+
 def test_deinterleave_index_math():
     from rtc_b200.sharded import deinterleave, frame_rows_of_shard, shard_rows
     for vsize in (1, 15, 16, 17, 100):
