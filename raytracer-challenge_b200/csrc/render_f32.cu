@@ -99,32 +99,34 @@ __device__ __forceinline__ void sweep_bounds(const Streams32& S, F3 o, F3 d, F e
         const float vz = fmaf(-b.y, dh.x, fmaf(b.x, dh.y, -m.z));
         return fmaf(vz, vz, fmaf(vy, vy, fmaf(vx, vx, b.w)));
     };
-    auto members = [&](int g) {    // four entries of `bound`, one branch: the exact tests sit behind it
-        const float4 b0 = S.bound[g], b1 = S.bound[g + 1], b2 = S.bound[g + 2], b3 = S.bound[g + 3];
-        const float s0 = gap(b0), s1 = gap(b1), s2 = gap(b2), s3 = gap(b3);
-        if (fminf(fminf(s0, s1), fminf(s2, s3)) <= margin) {
-            unsigned cand = (s0 <= margin ? 1u : 0u) | (s1 <= margin ? 2u : 0u) | (s2 <= margin ? 4u : 0u) | (s3 <= margin ? 8u : 0u);
-            do {
-                const int k = __ffs(cand) - 1;
-                cand &= cand - 1u;
-                exact(g + k);
-            } while (cand);
+    // Group level: the streams of a big scene are in Morton order, eight consecutive entries share a bounding sphere; a
+    // ray whose line misses it (same test, same kind of margin) skips the eight.  The group tests of 32 groups run
+    // branch-free into one bit mask per lane; the lanes then drain their masks side by side — a warp pays for the
+    // largest number of candidate groups any of its lanes has in the block, not for every trip in which some lane has one.
+    const int n_groups = S.nb4 >> 3;   // gbound is padded to a multiple of 32 with never-hit entries
+    for (int gb = 0; gb < n_groups; gb += 32) {
+        unsigned gm = 0u;
+#pragma unroll 2
+        for (int j = 0; j < 32; j += 4) {
+            const float4 q0 = S.gbound[gb + j], q1 = S.gbound[gb + j + 1], q2 = S.gbound[gb + j + 2], q3 = S.gbound[gb + j + 3];
+            const float t0 = gap(q0), t1 = gap(q1), t2 = gap(q2), t3 = gap(q3);
+            gm |= ((t0 <= gmargin ? 1u : 0u) | (t1 <= gmargin ? 2u : 0u) | (t2 <= gmargin ? 4u : 0u) | (t3 <= gmargin ? 8u : 0u)) << j;
         }
-    };
-    // group level: the streams of a big scene are in Morton order, eight consecutive entries share a bounding sphere;
-    // a ray whose line misses it (same test, same kind of margin) skips the eight.  Four groups per trip.
-    const int n_groups = S.nb4 >> 3;   // gbound is padded to a multiple of four with never-hit entries
-    for (int g8 = 0; g8 < n_groups; g8 += 4) {
-        const float4 q0 = S.gbound[g8], q1 = S.gbound[g8 + 1], q2 = S.gbound[g8 + 2], q3 = S.gbound[g8 + 3];
-        const float t0 = gap(q0), t1 = gap(q1), t2 = gap(q2), t3 = gap(q3);
-        if (fminf(fminf(t0, t1), fminf(t2, t3)) <= gmargin) {
-            unsigned cand = (t0 <= gmargin ? 1u : 0u) | (t1 <= gmargin ? 2u : 0u) | (t2 <= gmargin ? 4u : 0u) | (t3 <= gmargin ? 8u : 0u);
-            do {
-                const int k = __ffs(cand) - 1;
-                cand &= cand - 1u;
-#pragma unroll 1
-                for (int h = 0; h < 8; h += 4) members(8 * (g8 + k) + h);
-            } while (cand);
+        while (gm) {
+            const int g = 8 * (gb + __ffs(gm) - 1);
+            gm &= gm - 1u;
+            unsigned cm = 0u;   // the eight members
+#pragma unroll
+            for (int j = 0; j < 8; j += 4) {
+                const float4 b0 = S.bound[g + j], b1 = S.bound[g + j + 1], b2 = S.bound[g + j + 2], b3 = S.bound[g + j + 3];
+                const float s0 = gap(b0), s1 = gap(b1), s2 = gap(b2), s3 = gap(b3);
+                cm |= ((s0 <= margin ? 1u : 0u) | (s1 <= margin ? 2u : 0u) | (s2 <= margin ? 4u : 0u) | (s3 <= margin ? 8u : 0u)) << j;
+            }
+            while (cm) {
+                const int k = __ffs(cm) - 1;
+                cm &= cm - 1u;
+                exact(g + k);
+            }
         }
     }
 }

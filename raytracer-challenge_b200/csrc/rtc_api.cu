@@ -411,7 +411,7 @@ bool group_bounds(std::vector<float4>& bound, std::vector<float4>& gbound, float
         cm = std::max(cm, cn); rm = std::max(rm, r);
     }
     if (!std::isfinite(cm) || !std::isfinite(rm)) { gbound.clear(); return false; }
-    while (gbound.size() % 4) gbound.push_back(make_float4(0.f, 0.f, 0.f, std::numeric_limits<float>::infinity()));   // four groups per trip
+    while (gbound.size() % 32) gbound.push_back(make_float4(0.f, 0.f, 0.f, std::numeric_limits<float>::infinity()));   // the f32 kernel tests 32 groups per block, the f64 kernel four per trip
     gcmax = (float)(cm * (1.0 + 1e-6)); grmax = (float)(rm * (1.0 + 1e-6));
     return true;
 }
