@@ -103,6 +103,8 @@ __device__ __forceinline__ void sweep_bounds(const Streams32& S, F3 o, F3 d, F e
     // ray whose line misses it (same test, same kind of margin) skips the eight.  The group tests of 32 groups run
     // branch-free into one bit mask per lane; the lanes then drain their masks side by side — a warp pays for the
     // largest number of candidate groups any of its lanes has in the block, not for every trip in which some lane has one.
+    // (A third level — one sphere per 32 groups, every lane walking its own candidate blocks — pays in the parity kernel,
+    // C4 211 -> 177 ms, but not here: the group loads stop being warp-uniform, C4 122 -> 133 ms.)
     const int n_groups = S.nb4 >> 3;   // gbound is padded to a multiple of 32 with never-hit entries
     for (int gb = 0; gb < n_groups; gb += 32) {
         unsigned gm = 0u;

@@ -48,7 +48,8 @@ struct Streams {  // intersect streams, in shared memory when they fit, else glo
     int nc;
     const double2* pl;  const int32_t* pl_index;  int np;
     const float4* bound; int nb4; float cmax, rmax;         // f32 bounding spheres of [0, ns + nc) (DevScene64::bound); nb4 = 0: none
-    const float4* gbound; float gcmax, grmax;               // one per eight entries of `bound` (DevScene64::gbound), padded to a multiple of four
+    const float4* gbound; float gcmax, grmax;               // one per eight entries of `bound` (DevScene64::gbound), padded to a multiple of 32
+    const float4* sbound; float scmax, srmax;               // one per 32 groups (DevScene64::sbound), padded to a multiple of 32
 };
 
 // Shape::intersect + Sphere::intersect_local (src/shape.rs:23-26, 361-375)
@@ -176,9 +177,10 @@ __device__ __noinline__ void intersect_world(const Streams& S, V3 o, V3 d, doubl
     const float inv_len = rsqrtf(fmaf(fdz, fdz, fmaf(fdy, fdy, fdx * fdx)));
     fdx *= inv_len; fdy *= inv_len; fdz *= inv_len;
     const float mx = foy * fdz - foz * fdy, my = foz * fdx - fox * fdz, mz = fox * fdy - foy * fdx;
-    const float E = 3.8e-6f * (fmaxf(S.cmax, S.gcmax) + fabsf(fox) + fabsf(foy) + fabsf(foz));
+    const float E = 3.8e-6f * (fmaxf(fmaxf(S.cmax, S.gcmax), S.scmax) + fabsf(fox) + fabsf(foy) + fabsf(foz));
     const float margin = fmaf(E, 2.f * S.rmax + E, 2e-6f * S.rmax * S.rmax);
     const float gmargin = fmaf(E, 2.f * S.grmax + E, 2e-6f * S.grmax * S.grmax);
+    const float smargin = fmaf(E, 2.f * S.srmax + E, 2e-6f * S.srmax * S.srmax);
     auto gap = [&](float4 b) {
         const float vx = fmaf(-b.z, fdy, fmaf(b.y, fdz, -mx));
         const float vy = fmaf(-b.x, fdz, fmaf(b.z, fdx, -my));
@@ -206,38 +208,55 @@ __device__ __noinline__ void intersect_world(const Streams& S, V3 o, V3 d, doubl
     if (!kGroups) {
         for (int g = 0; g < n_solid; g += 4) members(g);   // (unroll 2 measured: room 7.35 -> 8.8 ms)
     } else {
-        // 32 group tests run branch-free into one bit mask per lane, then the lanes drain their masks side by side: a
-        // warp pays for the largest number of candidate groups any lane has in the block (gbound is padded to a
-        // multiple of 32 with never-hit entries).  Without the filter every group and every member is a candidate.
+        // Three levels, each a line-distance test against a bounding sphere: blocks of 32 groups (256 entries), groups
+        // of eight entries, entries.  32 tests of a level run branch-free into one bit mask per lane and the lanes then
+        // drain their masks side by side, every lane walking its own candidate blocks and groups (per-lane addresses
+        // below the block level): a warp pays for the largest number of candidates any of its lanes has.  The bound
+        // arrays are padded to multiples of 32 with never-hit entries.  Without the filter everything is a candidate.
         const int n_groups = (n_solid + 7) >> 3;
-        for (int gb = 0; gb < n_groups; gb += 32) {
-            unsigned gm = n_groups - gb >= 32 ? 0xffffffffu : (1u << (n_groups - gb)) - 1u;
+        const int n_blocks = (n_groups + 31) >> 5;
+        for (int sb = 0; sb < n_blocks; sb += 32) {
+            unsigned sm = n_blocks - sb >= 32 ? 0xffffffffu : (1u << (n_blocks - sb)) - 1u;
             if (filter) {
-                gm = 0u;
+                sm = 0u;
 #pragma unroll 2
                 for (int j = 0; j < 32; j += 4) {
-                    const float4 q0 = S.gbound[gb + j], q1 = S.gbound[gb + j + 1], q2 = S.gbound[gb + j + 2], q3 = S.gbound[gb + j + 3];
+                    const float4 q0 = S.sbound[sb + j], q1 = S.sbound[sb + j + 1], q2 = S.sbound[sb + j + 2], q3 = S.sbound[sb + j + 3];
                     const float t0 = gap(q0), t1 = gap(q1), t2 = gap(q2), t3 = gap(q3);
-                    gm |= ((!(t0 > gmargin) ? 1u : 0u) | (!(t1 > gmargin) ? 2u : 0u) | (!(t2 > gmargin) ? 4u : 0u) | (!(t3 > gmargin) ? 8u : 0u)) << j;
+                    sm |= ((!(t0 > smargin) ? 1u : 0u) | (!(t1 > smargin) ? 2u : 0u) | (!(t2 > smargin) ? 4u : 0u) | (!(t3 > smargin) ? 8u : 0u)) << j;
                 }
             }
-            while (gm) {
-                const int g = 8 * (gb + __ffs(gm) - 1);
-                gm &= gm - 1u;
-                unsigned cm = n_solid - g >= 8 ? 255u : (1u << (n_solid - g)) - 1u;
-                if (filter) {   // the padding entries of the last group have gap = +inf: never candidates
-                    cm = 0u;
-#pragma unroll
-                    for (int j = 0; j < 8; j += 4) {
-                        const float4 b0 = S.bound[g + j], b1 = S.bound[g + j + 1], b2 = S.bound[g + j + 2], b3 = S.bound[g + j + 3];
-                        const float s0 = gap(b0), s1 = gap(b1), s2 = gap(b2), s3 = gap(b3);
-                        cm |= ((!(s0 > margin) ? 1u : 0u) | (!(s1 > margin) ? 2u : 0u) | (!(s2 > margin) ? 4u : 0u) | (!(s3 > margin) ? 8u : 0u)) << j;
+            while (sm) {
+                const int gb = 32 * (sb + __ffs(sm) - 1);
+                sm &= sm - 1u;
+                unsigned gm = n_groups - gb >= 32 ? 0xffffffffu : (1u << (n_groups - gb)) - 1u;
+                if (filter) {
+                    gm = 0u;
+#pragma unroll 2
+                    for (int j = 0; j < 32; j += 4) {
+                        const float4 q0 = S.gbound[gb + j], q1 = S.gbound[gb + j + 1], q2 = S.gbound[gb + j + 2], q3 = S.gbound[gb + j + 3];
+                        const float t0 = gap(q0), t1 = gap(q1), t2 = gap(q2), t3 = gap(q3);
+                        gm |= ((!(t0 > gmargin) ? 1u : 0u) | (!(t1 > gmargin) ? 2u : 0u) | (!(t2 > gmargin) ? 4u : 0u) | (!(t3 > gmargin) ? 8u : 0u)) << j;
                     }
                 }
-                while (cm) {
-                    const int i = g + __ffs(cm) - 1;
-                    cm &= cm - 1u;
-                    if (!kCubes || i < S.ns) sphere(i); else cube(i);
+                while (gm) {
+                    const int g = 8 * (gb + __ffs(gm) - 1);
+                    gm &= gm - 1u;
+                    unsigned cm = n_solid - g >= 8 ? 255u : (1u << (n_solid - g)) - 1u;
+                    if (filter) {   // the padding entries of the last group have gap = +inf: never candidates
+                        cm = 0u;
+#pragma unroll
+                        for (int j = 0; j < 8; j += 4) {
+                            const float4 b0 = S.bound[g + j], b1 = S.bound[g + j + 1], b2 = S.bound[g + j + 2], b3 = S.bound[g + j + 3];
+                            const float s0 = gap(b0), s1 = gap(b1), s2 = gap(b2), s3 = gap(b3);
+                            cm |= ((!(s0 > margin) ? 1u : 0u) | (!(s1 > margin) ? 2u : 0u) | (!(s2 > margin) ? 4u : 0u) | (!(s3 > margin) ? 8u : 0u)) << j;
+                        }
+                    }
+                    while (cm) {
+                        const int i = g + __ffs(cm) - 1;
+                        cm &= cm - 1u;
+                        if (!kCubes || i < S.ns) sphere(i); else cube(i);
+                    }
                 }
             }
         }
@@ -456,6 +475,7 @@ render_f64_kernel(DevScene64 sc, CamParams cam, double* __restrict__ out_f64, fl
         S.sph = sc.sph_rows; S.pl = sc.pl_rows; S.sph_index = sc.sph_index; S.pl_index = sc.pl_index; S.bound = sc.bound; S.gbound = sc.gbound;
     }
     S.nb4 = sc.n_bound4; S.cmax = sc.bound_cmax; S.rmax = sc.bound_rmax; S.gcmax = sc.gbound_cmax; S.grmax = sc.gbound_rmax;
+    S.sbound = sc.sbound; S.scmax = sc.sbound_cmax; S.srmax = sc.sbound_rmax;
 
     const int ss = cam.samples == 1 ? 1 : 2;  // samples per pixel edge
     int sx, sy;

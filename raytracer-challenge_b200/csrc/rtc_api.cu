@@ -69,7 +69,7 @@ struct DeviceState {
     DevBuf<float4> pl32, us32, gs32, bound;
     DevBuf<int32_t> sph_index, pl_index, us_index, gs_index, gset;
     DevBuf<float> plL, usL;
-    DevBuf<float4> bound64, gbound, gbound64;
+    DevBuf<float4> bound64, gbound, gbound64, sbound, sbound64;
     DevBuf<double> lights64;   // [n_lights][6]
     DevBuf<float4> lights32;   // [n_lights][2]
     DevBuf<ShadeRec64> rec64;
@@ -271,6 +271,8 @@ struct HostScene {
     float bound64_cmax = 0.f, bound64_rmax = 0.f;
     std::vector<float4> gbound, gbound64; // one bounding sphere per kGroup consecutive entries of bound / bound64
     float gbound_cmax = 0.f, gbound_rmax = 0.f, gbound64_cmax = 0.f, gbound64_rmax = 0.f;
+    std::vector<float4> sbound, sbound64; // one bounding sphere per 32 consecutive groups (a block of 256 entries)
+    float sbound_cmax = 0.f, sbound_rmax = 0.f, sbound64_cmax = 0.f, sbound64_rmax = 0.f;
     std::vector<ShadeRec64> rec64;
     std::vector<ShadeRec32> rec32;
     int ids_unique = 1;
@@ -386,20 +388,22 @@ void apply_perm(std::vector<T>& v, const std::vector<int>& perm, size_t stride) 
         for (size_t k = 0; k < stride; ++k) out[i * stride + k] = v[(size_t)perm[i] * stride + k];
     v.swap(out);
 }
-// Bounding spheres (cx, cy, cz, -R^2) of each kGroup consecutive entries of `bound` (padding entries have w = +inf and
-// are ignored; `bound` is padded to a multiple of kGroup first).  Returns false when there is nothing to group.
-bool group_bounds(std::vector<float4>& bound, std::vector<float4>& gbound, float& gcmax, float& grmax) {
+// Bounding spheres (cx, cy, cz, -R^2) of each `group` consecutive entries of `bound` (padding entries have w = +inf and
+// are ignored; `bound` is padded to a multiple of `group` first, the result to a multiple of `pad_out`, with never-hit
+// entries).  Returns false when there is nothing to group.
+bool group_bounds(std::vector<float4>& bound, int group, int pad_out, std::vector<float4>& gbound, float& gcmax, float& grmax) {
+    const float4 never = make_float4(0.f, 0.f, 0.f, std::numeric_limits<float>::infinity());
     gbound.clear(); gcmax = 0.f; grmax = 0.f;
     if (bound.empty()) return false;
-    while (bound.size() % kGroup) bound.push_back(make_float4(0.f, 0.f, 0.f, std::numeric_limits<float>::infinity()));
+    while (bound.size() % (size_t)group) bound.push_back(never);
     double cm = 0.0, rm = 0.0;
-    for (size_t g = 0; g < bound.size(); g += kGroup) {
+    for (size_t g = 0; g < bound.size(); g += (size_t)group) {
         double c[3] = {0, 0, 0}; int m = 0;
-        for (int k = 0; k < kGroup; ++k) { const float4& b = bound[g + k]; if (std::isinf(b.w)) continue; c[0] += b.x; c[1] += b.y; c[2] += b.z; ++m; }
-        if (m == 0) { gbound.push_back(make_float4(0.f, 0.f, 0.f, std::numeric_limits<float>::infinity())); continue; }
+        for (int k = 0; k < group; ++k) { const float4& b = bound[g + k]; if (std::isinf(b.w)) continue; c[0] += b.x; c[1] += b.y; c[2] += b.z; ++m; }
+        if (m == 0) { gbound.push_back(never); continue; }
         for (int k = 0; k < 3; ++k) c[k] /= m;
         double r = 0.0;
-        for (int k = 0; k < kGroup; ++k) {
+        for (int k = 0; k < group; ++k) {
             const float4& b = bound[g + k];
             if (std::isinf(b.w)) continue;
             const double dx = b.x - c[0], dy = b.y - c[1], dz = b.z - c[2];
@@ -411,7 +415,7 @@ bool group_bounds(std::vector<float4>& bound, std::vector<float4>& gbound, float
         cm = std::max(cm, cn); rm = std::max(rm, r);
     }
     if (!std::isfinite(cm) || !std::isfinite(rm)) { gbound.clear(); return false; }
-    while (gbound.size() % 32) gbound.push_back(make_float4(0.f, 0.f, 0.f, std::numeric_limits<float>::infinity()));   // the f32 kernel tests 32 groups per block, the f64 kernel four per trip
+    while (gbound.size() % (size_t)pad_out) gbound.push_back(never);
     gcmax = (float)(cm * (1.0 + 1e-6)); grmax = (float)(rm * (1.0 + 1e-6));
     return true;
 }
@@ -588,7 +592,9 @@ int flatten(const rtc_light* lights, size_t n_lights, const rtc_shape* shapes, s
         if (!ok) hs.bound.clear();
         else {
             hs.bound_cmax = (float)(cmax * (1.0 + 1e-6)); hs.bound_rmax = (float)(rmax * (1.0 + 1e-6));
-            if (!group_bounds(hs.bound, hs.gbound, hs.gbound_cmax, hs.gbound_rmax)) hs.bound.clear();
+            // eight entries per group, 32 groups per block (256 entries), padded so that a kernel can read whole blocks
+            if (!group_bounds(hs.bound, kGroup, 32, hs.gbound, hs.gbound_cmax, hs.gbound_rmax) ||
+                !group_bounds(hs.gbound, 32, 32, hs.sbound, hs.sbound_cmax, hs.sbound_rmax)) hs.bound.clear();
         }
     }
 
@@ -610,7 +616,8 @@ int flatten(const rtc_light* lights, size_t n_lights, const rtc_shape* shapes, s
         if (!ok) hs.bound64.clear();
         else {
             hs.bound64_cmax = (float)(cmax * (1.0 + 1e-6)); hs.bound64_rmax = (float)(rmax * (1.0 + 1e-6));
-            if (!group_bounds(hs.bound64, hs.gbound64, hs.gbound64_cmax, hs.gbound64_rmax)) hs.bound64.clear();
+            if (!group_bounds(hs.bound64, kGroup, 32, hs.gbound64, hs.gbound64_cmax, hs.gbound64_rmax) ||
+                !group_bounds(hs.gbound64, 32, 32, hs.sbound64, hs.sbound64_cmax, hs.sbound64_rmax)) hs.bound64.clear();
         }
     }
 
@@ -965,7 +972,7 @@ void rtc_context_destroy(rtc_context* ctx) {
     for (DeviceState& d : ctx->devs) {
         cudaSetDevice(d.dev);
         if (d.stream) cudaStreamSynchronize(d.stream);
-        d.sph64.release(); d.pl64.release(); d.pl32.release(); d.us32.release(); d.gs32.release(); d.us_index.release(); d.gs_index.release(); d.gset.release(); d.plL.release(); d.usL.release(); d.lights64.release(); d.lights32.release(); d.bound64.release(); d.gbound.release(); d.gbound64.release(); d.bound.release();
+        d.sph64.release(); d.pl64.release(); d.pl32.release(); d.us32.release(); d.gs32.release(); d.us_index.release(); d.gs_index.release(); d.gset.release(); d.plL.release(); d.usL.release(); d.lights64.release(); d.lights32.release(); d.bound64.release(); d.gbound.release(); d.gbound64.release(); d.sbound.release(); d.sbound64.release(); d.bound.release();
         d.sph_index.release(); d.pl_index.release(); d.rec64.release(); d.rec32.release(); d.srec.release();
         d.rgb.release(); d.hit.release(); d.counters.release(); d.work.release(); d.order.release();
         if (d.ev_k0) cudaEventDestroy(d.ev_k0);
@@ -1013,6 +1020,8 @@ int rtc_scene_upload_lights(rtc_context* ctx, const rtc_light* light, size_t n_l
         CUDA_TRY(upload(d.bound64, hs.bound64, d.stream));
         CUDA_TRY(upload(d.gbound, hs.gbound, d.stream));
         CUDA_TRY(upload(d.gbound64, hs.gbound64, d.stream));
+        CUDA_TRY(upload(d.sbound, hs.sbound, d.stream));
+        CUDA_TRY(upload(d.sbound64, hs.sbound64, d.stream));
         CUDA_TRY(upload(d.sph_index, hs.sph_index, d.stream));
         CUDA_TRY(upload(d.pl_index, hs.pl_index, d.stream));
         CUDA_TRY(upload(d.rec64, hs.rec64, d.stream));
@@ -1041,6 +1050,8 @@ int rtc_scene_upload_lights(rtc_context* ctx, const rtc_light* light, size_t n_l
         d.s64.bound = d.bound64.p; d.s64.n_bound4 = (int)hs.bound64.size(); d.s64.bound_cmax = hs.bound64_cmax; d.s64.bound_rmax = hs.bound64_rmax;
         d.s64.gbound = d.gbound64.p; d.s64.gbound_cmax = hs.gbound64_cmax; d.s64.gbound_rmax = hs.gbound64_rmax;
         d.s32.gbound = d.gbound.p; d.s32.gbound_cmax = hs.gbound_cmax; d.s32.gbound_rmax = hs.gbound_rmax;
+        d.s64.sbound = d.sbound64.p; d.s64.sbound_cmax = hs.sbound64_cmax; d.s64.sbound_rmax = hs.sbound64_rmax;
+        d.s32.sbound = d.sbound.p; d.s32.sbound_cmax = hs.sbound_cmax; d.s32.sbound_rmax = hs.sbound_rmax;
         d.s32.bound = d.bound.p; d.s32.n_bound4 = (int)hs.bound.size(); d.s32.bound_cmax = hs.bound_cmax; d.s32.bound_rmax = hs.bound_rmax;
         for (int k = 0; k < 3; ++k) {
             d.s64.light_pos[k] = light->position[k]; d.s64.light_int[k] = light->intensity[k];

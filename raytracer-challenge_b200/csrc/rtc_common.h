@@ -60,6 +60,8 @@ struct DevScene64 {
     // neighbours in the stream are neighbours in space): a ray whose line misses it skips the eight member tests
     const float4* gbound;
     float gbound_cmax, gbound_rmax;
+    const float4* sbound;      // and one per 32 consecutive groups (a block of 256 entries), padded to a multiple of 32
+    float sbound_cmax, sbound_rmax;
 };
 
 // ---- f32 (fast) layout ------------------------------------------------------------------------
@@ -106,6 +108,8 @@ struct DevScene32 {
     float bound_cmax, bound_rmax;   // max |c|_1 and max R over the entries (rounding margin of the filter)
     const float4* gbound;           // one bounding sphere per eight consecutive entries of `bound` (Morton-ordered streams)
     float gbound_cmax, gbound_rmax;
+    const float4* sbound;           // one per 32 consecutive groups (a block of 256 entries); the f32 kernels do not use it (measured slower)
+    float sbound_cmax, sbound_rmax;
     float light_pos[3];        // light 0
     float light_int[3];
     int n_lights;              // rtc_scene_upload_lights: plL / usL hold n_lights rows; lights 1.. read them from global memory
