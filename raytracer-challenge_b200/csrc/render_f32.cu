@@ -50,6 +50,7 @@ struct Streams32 {
     int nc;
     const float4* bound; int nb4; float cmax, rmax;   // bounding-sphere filter (DevScene32::bound), kFilter kernels only
     const float4* gbound; float gcmax, grmax;         // one bound per eight entries of `bound` (DevScene32::gbound)
+    const float4* sbound; float scmax, srmax;         // one bound per 32 groups (DevScene32::sbound)
 };
 
 // Cube::intersect_local (src/shape.rs:540-591) in object space: slab test per axis.  A zero direction
@@ -90,9 +91,10 @@ template <typename F>
 __device__ __forceinline__ void sweep_bounds(const Streams32& S, F3 o, F3 d, F exact) {
     const F3 dh = d * rsqrtf(dot(d, d));
     const F3 m = mk(o.y * dh.z - o.z * dh.y, o.z * dh.x - o.x * dh.z, o.x * dh.y - o.y * dh.x);
-    const float E = 3.8e-6f * (fmaxf(S.cmax, S.gcmax) + fabsf(o.x) + fabsf(o.y) + fabsf(o.z));
+    const float E = 3.8e-6f * (fmaxf(fmaxf(S.cmax, S.gcmax), S.scmax) + fabsf(o.x) + fabsf(o.y) + fabsf(o.z));
     const float margin = fmaf(E, 2.f * S.rmax + E, 2e-6f * S.rmax * S.rmax);
     const float gmargin = fmaf(E, 2.f * S.grmax + E, 2e-6f * S.grmax * S.grmax);
+    const float smargin = fmaf(E, 2.f * S.srmax + E, 2e-6f * S.srmax * S.srmax);
     auto gap = [&](float4 b) {
         const float vx = fmaf(-b.z, dh.y, fmaf(b.y, dh.z, -m.x));
         const float vy = fmaf(-b.x, dh.z, fmaf(b.z, dh.x, -m.y));
@@ -103,31 +105,46 @@ __device__ __forceinline__ void sweep_bounds(const Streams32& S, F3 o, F3 d, F e
     // ray whose line misses it (same test, same kind of margin) skips the eight.  The group tests of 32 groups run
     // branch-free into one bit mask per lane; the lanes then drain their masks side by side — a warp pays for the
     // largest number of candidate groups any of its lanes has in the block, not for every trip in which some lane has one.
-    // (A third level — one sphere per 32 groups, every lane walking its own candidate blocks — pays in the parity kernel,
-    // C4 211 -> 177 ms, but not here: the group loads stop being warp-uniform, C4 122 -> 133 ms.)
-    const int n_groups = S.nb4 >> 3;   // gbound is padded to a multiple of 32 with never-hit entries
-    for (int gb = 0; gb < n_groups; gb += 32) {
-        unsigned gm = 0u;
+    // Block level: 32 consecutive groups (256 entries) share one more bounding sphere.  A block is swept when ANY lane of
+    // the warp (of the lanes running this sweep together) comes near it, so the group loads below stay warp-uniform; the
+    // coherent warps — primary rays, shadow rays of neighbouring hits, reflections in the planar mirrors — skip most
+    // blocks.  (Every lane walking its own candidate blocks instead pays in the parity kernel, C4 211 -> 177 ms, but not
+    // here: with per-lane addresses for the group loads C4 went 122 -> 133 ms.)
+    const int n_blocks = (S.nb4 + 255) >> 8;   // sbound and gbound are padded to multiples of 32 with never-hit entries
+    for (int sb = 0; sb < n_blocks; sb += 32) {
+        unsigned sm = 0u;
 #pragma unroll 2
         for (int j = 0; j < 32; j += 4) {
-            const float4 q0 = S.gbound[gb + j], q1 = S.gbound[gb + j + 1], q2 = S.gbound[gb + j + 2], q3 = S.gbound[gb + j + 3];
+            const float4 q0 = S.sbound[sb + j], q1 = S.sbound[sb + j + 1], q2 = S.sbound[sb + j + 2], q3 = S.sbound[sb + j + 3];
             const float t0 = gap(q0), t1 = gap(q1), t2 = gap(q2), t3 = gap(q3);
-            gm |= ((t0 <= gmargin ? 1u : 0u) | (t1 <= gmargin ? 2u : 0u) | (t2 <= gmargin ? 4u : 0u) | (t3 <= gmargin ? 8u : 0u)) << j;
+            sm |= ((t0 <= smargin ? 1u : 0u) | (t1 <= smargin ? 2u : 0u) | (t2 <= smargin ? 4u : 0u) | (t3 <= smargin ? 8u : 0u)) << j;
         }
-        while (gm) {
-            const int g = 8 * (gb + __ffs(gm) - 1);
-            gm &= gm - 1u;
-            unsigned cm = 0u;   // the eight members
-#pragma unroll
-            for (int j = 0; j < 8; j += 4) {
-                const float4 b0 = S.bound[g + j], b1 = S.bound[g + j + 1], b2 = S.bound[g + j + 2], b3 = S.bound[g + j + 3];
-                const float s0 = gap(b0), s1 = gap(b1), s2 = gap(b2), s3 = gap(b3);
-                cm |= ((s0 <= margin ? 1u : 0u) | (s1 <= margin ? 2u : 0u) | (s2 <= margin ? 4u : 0u) | (s3 <= margin ? 8u : 0u)) << j;
+        unsigned wm = __reduce_or_sync(__activemask(), sm);   // a lane's own candidates are always in it
+        while (wm) {
+            const int gb = 32 * (sb + __ffs(wm) - 1);
+            wm &= wm - 1u;
+            unsigned gm = 0u;
+#pragma unroll 2
+            for (int j = 0; j < 32; j += 4) {
+                const float4 q0 = S.gbound[gb + j], q1 = S.gbound[gb + j + 1], q2 = S.gbound[gb + j + 2], q3 = S.gbound[gb + j + 3];
+                const float t0 = gap(q0), t1 = gap(q1), t2 = gap(q2), t3 = gap(q3);
+                gm |= ((t0 <= gmargin ? 1u : 0u) | (t1 <= gmargin ? 2u : 0u) | (t2 <= gmargin ? 4u : 0u) | (t3 <= gmargin ? 8u : 0u)) << j;
             }
-            while (cm) {
-                const int k = __ffs(cm) - 1;
-                cm &= cm - 1u;
-                exact(g + k);
+            while (gm) {
+                const int g = 8 * (gb + __ffs(gm) - 1);
+                gm &= gm - 1u;
+                unsigned cm = 0u;   // the eight members
+#pragma unroll
+                for (int j = 0; j < 8; j += 4) {
+                    const float4 b0 = S.bound[g + j], b1 = S.bound[g + j + 1], b2 = S.bound[g + j + 2], b3 = S.bound[g + j + 3];
+                    const float s0 = gap(b0), s1 = gap(b1), s2 = gap(b2), s3 = gap(b3);
+                    cm |= ((s0 <= margin ? 1u : 0u) | (s1 <= margin ? 2u : 0u) | (s2 <= margin ? 4u : 0u) | (s3 <= margin ? 8u : 0u)) << j;
+                }
+                while (cm) {
+                    const int k = __ffs(cm) - 1;
+                    cm &= cm - 1u;
+                    exact(g + k);
+                }
             }
         }
     }
@@ -534,6 +551,7 @@ render_f32_kernel(DevScene32 sc, CamParams cam, void* __restrict__ out_rgb, uint
     constexpr bool kFilter = kGlobal == 2;
     S.bound = sc.bound; S.nb4 = sc.n_bound4; S.cmax = sc.bound_cmax; S.rmax = sc.bound_rmax;
     S.gbound = sc.gbound; S.gcmax = sc.gbound_cmax; S.grmax = sc.gbound_rmax;
+    S.sbound = sc.sbound; S.scmax = sc.sbound_cmax; S.srmax = sc.sbound_rmax;
     if (kGlobal) {
         S.planes = sc.planes; S.usph = sc.usph; S.gsph = sc.gsph; S.pl_index = sc.pl_index; S.us_index = sc.us_index; S.gs_index = sc.gs_index;
         plL = sc.plL; usL = sc.usL; gset = sc.gset;

@@ -108,7 +108,7 @@ struct DevScene32 {
     float bound_cmax, bound_rmax;   // max |c|_1 and max R over the entries (rounding margin of the filter)
     const float4* gbound;           // one bounding sphere per eight consecutive entries of `bound` (Morton-ordered streams)
     float gbound_cmax, gbound_rmax;
-    const float4* sbound;           // one per 32 consecutive groups (a block of 256 entries); the f32 kernels do not use it (measured slower)
+    const float4* sbound;           // one per 32 consecutive groups (a block of 256 entries), padded to a multiple of 32
     float sbound_cmax, sbound_rmax;
     float light_pos[3];        // light 0
     float light_int[3];
