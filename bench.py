@@ -27,6 +27,17 @@ WORKLOAD = "C3: reflect-refract room (jamis.yml, 13 shapes), 3840x2160, 1 spp, d
 W, H, DEPTH, SAMPLES = 3840, 2160, 5, 1   # the metric's configuration (BASELINE.json configs[2]); --workload c5 switches to configs[4]
 N_SPHERES, N_PLANES = 7, 6
 FLOP_PER_RAY = 54 * N_SPHERES + 13 * N_PLANES   # algorithmic flops per World::intersect
+WORKLOAD_KEY = "c3"
+
+
+def make_scene(rtc):
+    return rtc.scenes.synthetic_scene() if WORKLOAD_KEY == "c4" else rtc.scenes.reflect_refract_scene()
+
+
+def make_camera(rtc):
+    if WORKLOAD_KEY == "c4":
+        return rtc.scenes.synthetic_camera(W, H, samples=SAMPLES)
+    return rtc.scenes.reflect_refract_camera(W, H, samples=SAMPLES)
 FLOP_PER_SHADED_HIT = 150
 FP32_FORMULA_PEAK = 148 * 128 * 2 * 1.965e9 / 1e12  # TFLOP/s, non-tensor, at clocks.max.sm
 
@@ -93,8 +104,8 @@ def oracle_sample(threads, target_seconds=12.0):
     import numpy as np
     import orc
     import rtc_b200 as rtc
-    world = rtc.scenes.reflect_refract_scene()
-    cam = rtc.scenes.reflect_refract_camera(W, H, samples=SAMPLES)
+    world = make_scene(rtc)
+    cam = make_camera(rtc)
     ow = orc.OracleWorld(world)
     # calibrate on a coarse lattice, then size the real sample
     idx = orc.lattice(W, H, step=64, n_random=0)
@@ -175,8 +186,8 @@ def run_gpu(args):
             os.dup2(saved_stdout, 1)
             os.close(saved_stdout)
     r = rtc.Renderer([local_rank])
-    world = rtc.scenes.reflect_refract_scene()
-    cam = rtc.scenes.reflect_refract_camera(W, H, samples=SAMPLES)
+    world = make_scene(rtc)
+    cam = make_camera(rtc)
     flat = world.flatten()
     camd = cam.flatten()
     r.upload_flat(*flat)
@@ -383,13 +394,15 @@ def run_gpu(args):
                                        "completion = one peer-stored flag per rank, rank 0 waits on its stream (no collective)" if N > 1 else ""),
                        "timing": "CUDA events per step on the launch stream, max over ranks"},
             "roofline": {"bound": "fp32_non_tensor", "achieved": achieved, "peak": p32, "unit": "TFLOP/s", "frac": achieved / p32,
-                         "traffic": 64.56e6 if N == 1 else None,
+                         "traffic": 64.56e6 if (N == 1 and WORKLOAD_KEY == "c3") else None,
                          "traffic_note": "dram__bytes_read.sum + dram__bytes_write.sum of one 4K launch, ncu --set full capture "
                                          "(profiles/r01_ncu_f32_small_1p25ms.txt): 63.3 MB written + 1.2 MB read; the frame is 99.5 MB, the "
                                          "rest was still in the 126 MB L2 when the kernel ended; scene reads never reach HBM",
                          "peak_source": "FFMA micro-benchmark on this GPU in this run (rtc_measure_peak_tflops)",
                          "peak_formula": FP32_FORMULA_PEAK, "frac_of_formula": achieved / FP32_FORMULA_PEAK,
-                         "algorithmic_gflop_per_frame": flops / 1e9, "kernel_ms": kernel_ms, "kernel": "render_f32_small_kernel",
+                         "algorithmic_gflop_per_frame": flops / 1e9, "kernel_ms": kernel_ms,
+                         "kernel": "render_f32_kernel (general; the bounding-sphere filter skips most of the algorithmic shape tests, so frac can exceed 1)"
+                                   if WORKLOAD_KEY == "c4" else "render_f32_small_kernel",
                          "hbm_gbs_measured_peak": peaks.get("hbm_gbs"),
                          "hbm_gbs_achieved_frame_write": W * H * 12 * my_share / (kernel_ms * 1e-3) / 1e9},
             "f64": {"ms_per_frame": float(ms64.mean()), "mrays_per_s": rays / (float(ms64.mean()) * 1e-3) / 1e6,
@@ -437,13 +450,19 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--tile-rows", type=int, default=4, help="rows per interleaved tile (multi-GPU sharding)")
-    ap.add_argument("--workload", default="c3", choices=["c3", "c5"],
-                    help="c3 (default): the metric's 4K frame; c5: BASELINE.json configs[4], 7680x4320 with the deterministic 2x2 supersample")
+    ap.add_argument("--workload", default="c3", choices=["c3", "c4", "c5"],
+                    help="c3 (default): the metric's 4K frame; c4: BASELINE.json configs[3], 10k random spheres + planes at 4K; "
+                         "c5: configs[4], 7680x4320 with the deterministic 2x2 supersample")
     args = ap.parse_args()
+    global WORKLOAD, W, H, SAMPLES, WORKLOAD_KEY, N_SPHERES, N_PLANES, FLOP_PER_RAY
+    WORKLOAD_KEY = args.workload
     if args.workload == "c5":
-        global WORKLOAD, W, H, SAMPLES
         WORKLOAD = "C5: reflect-refract room (jamis.yml, 13 shapes), 7680x4320, deterministic 2x2 supersample, depth 5"
         W, H, SAMPLES = 7680, 4320, 0
+    if args.workload == "c4":
+        WORKLOAD = "C4: 9,992 random spheres + 8 planes (seed 0xB200, u8 world_ids wrap), 3840x2160, 1 spp, depth 5"
+        N_SPHERES, N_PLANES = 9992, 8
+        FLOP_PER_RAY = 54 * N_SPHERES + 13 * N_PLANES
     if args.impl == "reference":
         return run_reference(args)
     return run_gpu(args)
