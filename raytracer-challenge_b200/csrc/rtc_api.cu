@@ -1378,7 +1378,11 @@ extern "C" int rtc_render(rtc_context* ctx, const rtc_camera* cam, const rtc_ren
         static const int kPlanEq8[] = {1, 1, 1, 1, 1, 1, 1, 1}, kPlanF64[] = {6, 5, 3, 1, 1}, kPlanMid[] = {1, 2, 1}, kPlanOne[] = {1};
         const int* plan = kPlanOne; int n_plan = 1, plan_sum = 1;
         if (frame_bytes >= (32u << 20)) {
-            if (opts->precision == RTC_PRECISION_F64_PARITY) { plan = kPlanF64; n_plan = 5; plan_sum = 16; }
+            // kernel-bound frames: parity mode, and fast mode outside the small-scene kernel (every launch has its own
+            // tail of deep ray trees: eight bands of the 10k-shape frame took 173 ms against 117 ms for one launch)
+            const bool kernel_bound = opts->precision == RTC_PRECISION_F64_PARITY || !d.small_ok || (opts->flags & RTC_OPT_F32_GENERAL_KERNEL);
+            if (d.s64.n_shapes > 256) { plan = kPlanOne; n_plan = 1; plan_sum = 1; }   // tens of ms of kernel, ms-long tails: one launch, then the copy
+            else if (kernel_bound) { plan = kPlanF64; n_plan = 5; plan_sum = 16; }
             else { plan = kPlanEq8; n_plan = 8; plan_sum = 8; }
         } else if (frame_bytes >= (4u << 20)) { plan = kPlanMid; n_plan = 3; plan_sum = 4; }
         if (const char* env = std::getenv("RTC_B200_BANDS")) {   // experiments: N equal bands
