@@ -283,6 +283,25 @@ int rtc_pack_rgba8_device(rtc_context* ctx, const void* d_frame, int frame_forma
  * used as the roofline denominator beside the formula peak. */
 int rtc_measure_peak_tflops(rtc_context* ctx, int precision, double* out_tflops);
 
+/* Host-only self-check of the scene flattening pass (no device needed, nothing is uploaded): runs the pass on the
+ * given world and verifies what the kernels rely on — every shape sits in exactly one intersect stream of each
+ * precision (the streams of big scenes are reordered along a Morton curve), and every shape's bounding sphere lies
+ * inside the bounding sphere of its group of eight, every group's inside its block's (the two upper levels of the
+ * line-distance filter in front of the exact shape tests).  RTC_OK and *out filled when the pass ran; the caller
+ * inspects the fields.  Replaces nothing in the reference: World::intersect is a plain loop (src/shape.rs:677-683). */
+typedef struct rtc_selfcheck {
+    int32_t n_planes, n_uniform_spheres, n_general_spheres, n_cubes;
+    int32_t streams_are_permutations;   /* 1: each shape index appears exactly once per precision */
+    int32_t morton_sorted;              /* 1: at least one stream was reordered (>= 64 entries) */
+    int32_t n_groups_f32, n_blocks_f32, n_groups_f64, n_blocks_f64;   /* 0: no filter for that precision */
+    int32_t small_scene_form;           /* 1: the scene fits the constant-bank f32 kernel */
+    int32_t reserved;
+    double worst_enclosure_f32;         /* max over entries of (distance of centres + r_child - r_parent) / r_parent; <= 0 = enclosed */
+    double worst_enclosure_f64;
+} rtc_selfcheck;
+int rtc_scene_selfcheck(const rtc_light* lights, size_t n_lights, const rtc_shape* shapes, size_t n_shapes,
+                        rtc_selfcheck* out);
+
 #ifdef __cplusplus
 }
 #endif

@@ -1190,6 +1190,55 @@ int rtc_wait_device(rtc_context* ctx, const void* d_flags, int n, uint32_t value
     return RTC_OK;
 }
 
+int rtc_scene_selfcheck(const rtc_light* lights, size_t n_lights, const rtc_shape* shapes, size_t n_shapes, rtc_selfcheck* out) {
+    if (!lights || !out || (!shapes && n_shapes)) return fail(RTC_ERR_INVALID_ARG, "rtc_scene_selfcheck: null argument");
+    if (n_lights < 1 || n_lights > RTC_MAX_LIGHTS) return fail(RTC_ERR_INVALID_ARG, "rtc_scene_selfcheck: 1 <= n_lights <= RTC_MAX_LIGHTS");
+    HostScene hs;
+    int rc = flatten(lights, n_lights, shapes, n_shapes, hs);
+    if (rc != RTC_OK) return rc;
+    std::memset(out, 0, sizeof *out);
+    out->n_planes = (int32_t)hs.pl_index.size();
+    out->n_uniform_spheres = (int32_t)hs.us_index.size();
+    out->n_general_spheres = hs.n_gsph;
+    out->n_cubes = hs.n_cubes;
+    out->small_scene_form = hs.small_ok ? 1 : 0;
+    auto is_perm = [&](std::initializer_list<const std::vector<int32_t>*> parts) {
+        std::vector<int> seen(n_shapes, 0);
+        size_t total = 0;
+        for (const auto* v : parts)
+            for (int32_t i : *v) { if (i < 0 || (size_t)i >= n_shapes) return false; ++seen[i]; ++total; }
+        if (total != n_shapes) return false;
+        for (int c : seen) if (c != 1) return false;
+        return true;
+    };
+    out->streams_are_permutations = (is_perm({&hs.pl_index, &hs.us_index, &hs.gs_index}) && is_perm({&hs.pl_index, &hs.sph_index})) ? 1 : 0;
+    auto ascending = [](const std::vector<int32_t>& v, size_t b, size_t e) { for (size_t k = b + 1; k < e; ++k) if (v[k] < v[k - 1]) return false; return true; };
+    out->morton_sorted = (!ascending(hs.us_index, 0, hs.us_index.size()) || !ascending(hs.sph_index, 0, (size_t)hs.n_spheres) ||
+                          !ascending(hs.gs_index, 0, (size_t)hs.n_gsph)) ? 1 : 0;
+    auto worst = [](const std::vector<float4>& child, const std::vector<float4>& parent, size_t per) {
+        double w = -1.0;
+        for (size_t i = 0; i < child.size(); ++i) {
+            const float4& c = child[i];
+            if (std::isinf(c.w)) continue;
+            const float4& p = parent[i / per];
+            if (std::isinf(p.w)) return 1e300;   // a real entry under a never-hit parent
+            const double dx = (double)c.x - p.x, dy = (double)c.y - p.y, dz = (double)c.z - p.z;
+            const double rc = std::sqrt(std::max(0.0, -(double)c.w)), rp = std::sqrt(std::max(0.0, -(double)p.w));
+            w = std::max(w, (std::sqrt(dx * dx + dy * dy + dz * dz) + rc - rp) / std::max(rp, 1e-300));
+        }
+        return w;
+    };
+    if (!hs.bound.empty()) {
+        out->n_groups_f32 = (int32_t)(hs.bound.size() / kGroup); out->n_blocks_f32 = (int32_t)((hs.bound.size() / kGroup + 31) / 32);
+        out->worst_enclosure_f32 = std::max(worst(hs.bound, hs.gbound, kGroup), worst(hs.gbound, hs.sbound, 32));
+    }
+    if (!hs.bound64.empty()) {
+        out->n_groups_f64 = (int32_t)(hs.bound64.size() / kGroup); out->n_blocks_f64 = (int32_t)((hs.bound64.size() / kGroup + 31) / 32);
+        out->worst_enclosure_f64 = std::max(worst(hs.bound64, hs.gbound64, kGroup), worst(hs.gbound64, hs.sbound64, 32));
+    }
+    return RTC_OK;
+}
+
 int rtc_measure_peak_tflops(rtc_context* ctx, int precision, double* out_tflops) {
     if (!ctx || !out_tflops) return fail(RTC_ERR_INVALID_ARG, "rtc_measure_peak_tflops: null argument");
     DeviceState& d = ctx->devs[0];

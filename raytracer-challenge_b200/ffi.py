@@ -95,9 +95,16 @@ EXPORTS = [
     ("rtc_pack_rgba8_device", C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_size_t, C.c_float, C.c_void_p, C.c_void_p]),
     ("rtc_download_frame", C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_uint32, C.c_uint32, C.c_int, C.c_void_p, C.c_void_p]),
     ("rtc_measure_peak_tflops", C.c_int, [C.c_void_p, C.c_int, C.POINTER(C.c_double)]),
+    ("rtc_scene_selfcheck", C.c_int, [C.POINTER(RtcLight), C.c_size_t, C.POINTER(RtcShape), C.c_size_t, C.c_void_p]),
 ]
 
 _lib = None
+
+
+class RtcSelfcheck(C.Structure):
+    _fields_ = [(n, C.c_int32) for n in ("n_planes", "n_uniform_spheres", "n_general_spheres", "n_cubes", "streams_are_permutations",
+                                          "morton_sorted", "n_groups_f32", "n_blocks_f32", "n_groups_f64", "n_blocks_f64",
+                                          "small_scene_form", "reserved")] + [("worst_enclosure_f32", C.c_double), ("worst_enclosure_f64", C.c_double)]
 
 
 class RtcError(RuntimeError):
