@@ -34,6 +34,37 @@ def test_struct_layouts_match_header(rtc):
     assert C.sizeof(f.RtcStats) == 5 * 8 + 5 * 8
 
 
+def test_field_offsets_match_a_c_compiler(rtc, tmp_path):
+    """Every field of every struct of include/rtc.h at the offset gcc gives it == the ctypes mirror (ffi.py), which is
+    what the Rust #[repr(C)] structs of INTEGRATION.md have to match too."""
+    import shutil
+    import subprocess
+    if not shutil.which("gcc"):
+        pytest.skip("no gcc")
+    f = rtc.ffi
+    structs = {"rtc_shape": f.RtcShape, "rtc_light": f.RtcLight, "rtc_camera": f.RtcCamera, "rtc_render_opts": f.RtcRenderOpts,
+               "rtc_stats": f.RtcStats, "rtc_selfcheck": f.RtcSelfcheck}
+    lines = ['#include <stdio.h>', '#include <stddef.h>', '#include "rtc.h"', 'int main(void) {']
+    for cname, ct in structs.items():
+        lines.append(f'  printf("{cname} size %zu\\n", sizeof({cname}));')
+        for fname, _ in ct._fields_:
+            lines.append(f'  printf("{cname} {fname} %zu\\n", offsetof({cname}, {fname}));')
+    lines += ['  return 0;', '}']
+    src = tmp_path / "offsets.c"
+    src.write_text("\n".join(lines))
+    exe = tmp_path / "offsets"
+    subprocess.run(["gcc", "-std=c99", "-I", os.path.join(ROOT, "include"), "-o", str(exe), str(src)], check=True)
+    out = subprocess.run([str(exe)], check=True, stdout=subprocess.PIPE, text=True).stdout
+    seen = 0
+    for line in out.splitlines():
+        cname, field, value = line.split()
+        ct = structs[cname]
+        want = C.sizeof(ct) if field == "size" else getattr(ct, field).offset
+        assert int(value) == want, line
+        seen += 1
+    assert seen == sum(len(ct._fields_) + 1 for ct in structs.values())
+
+
 def test_shard_rows_partition_the_frame(rtc):
     L = rtc.ffi.lib()
     cam = rtc.ffi.RtcCamera()
