@@ -28,9 +28,19 @@ __device__ __forceinline__ V3 mul(V3 a, double m) { return mk(a.x * m, a.y * m, 
 __device__ __forceinline__ V3 mulc(V3 a, V3 b) { return mk(a.x * b.x, a.y * b.y, a.z * b.z); }
 __device__ __forceinline__ V3 neg(V3 a) { return mk(-a.x, -a.y, -a.z); }
 __device__ __forceinline__ double dot(V3 a, V3 b) { return a.x * b.x + a.y * b.y + a.z * b.z; }   // src/vec.rs:78
+// IEEE division and square root of the path.  By default they are inlined where they stand (30 + 11 copies of the
+// ~15-instruction sequences in the C3 variant); -DRTC_F64_SHARED_DIV makes each a single non-inlined routine (same
+// operations, same bits) to shrink the instruction footprint — an experiment knob, see DESIGN.md §8 item 3.
+#ifdef RTC_F64_SHARED_DIV
+__device__ __noinline__ double ddiv(double a, double b) { return a / b; }
+__device__ __noinline__ double dsqrt(double a) { return sqrt(a); }
+#else
+__device__ __forceinline__ double ddiv(double a, double b) { return a / b; }
+__device__ __forceinline__ double dsqrt(double a) { return sqrt(a); }
+#endif
 __device__ __forceinline__ V3 normalize(V3 a) {                                                    // src/vec.rs:65-76
-    double m = sqrt(a.x * a.x + a.y * a.y + a.z * a.z);
-    return mk(a.x / m, a.y / m, a.z / m);
+    double m = dsqrt(a.x * a.x + a.y * a.y + a.z * a.z);
+    return mk(ddiv(a.x, m), ddiv(a.y, m), ddiv(a.z, m));
 }
 __device__ __forceinline__ V3 reflect(V3 v, V3 n) { return sub(v, mul(n, 2. * dot(v, n))); }       // src/vec.rs:106
 // Matrix::transform_point / transform_vector, src/transform.rs:107-128 (sums left to right)
@@ -66,9 +76,9 @@ __device__ __forceinline__ bool sphere_roots(const double2* r, V3 o, V3 d, doubl
     double c = (ox * ox + oy * oy + oz * oz) - 1.;
     double disc = (b * b) - 4. * a * c;
     if (disc < 0.) return false;
-    double s = sqrt(disc);
-    t1 = (-b - s) / (2. * a);
-    t2 = (-b + s) / (2. * a);
+    double s = dsqrt(disc);
+    t1 = ddiv(-b - s, 2. * a);
+    t2 = ddiv(-b + s, 2. * a);
     return true;
 }
 // Cube::check_axis (src/shape.rs:540-564)
@@ -76,8 +86,8 @@ __device__ __forceinline__ void check_axis(double origin, double direction, doub
     const double tmin_numerator = -1.0 - origin;
     const double tmax_numerator = 1. - origin;
     if (fabs(direction) >= kEps) {
-        tmin = tmin_numerator / direction;
-        tmax = tmax_numerator / direction;
+        tmin = ddiv(tmin_numerator, direction);
+        tmax = ddiv(tmax_numerator, direction);
     } else {
         const double inf = __longlong_as_double(0x7ff0000000000000LL);
         tmin = tmin_numerator >= 0.0 ? inf : -inf;
@@ -111,7 +121,7 @@ __device__ __forceinline__ bool plane_root(const double2* r, V3 o, V3 d, double&
     double dy = b0.x * d.x + b0.y * d.y + b1.x * d.z;
     if (fabs(dy) < kEps) return false;
     double oy = b0.x * o.x + b0.y * o.y + b1.x * o.z + b1.y;
-    t = -oy / dy;
+    t = ddiv(-oy, dy);
     return true;
 }
 
@@ -573,7 +583,7 @@ render_f64_kernel(DevScene64 sc, CamParams cam, double* __restrict__ out_f64, fl
                     }
                     // World::is_shadowed_by_light (src/shape.rs:716-727)
                     V3 v = sub(lpos, over_point);
-                    double distance = sqrt(v.x * v.x + v.y * v.y + v.z * v.z);
+                    double distance = dsqrt(v.x * v.x + v.y * v.y + v.z * v.z);
                     V3 sdir = normalize(v);
                     double st; int sidx;
                     ++n_rays; ++n_shadow;
@@ -587,11 +597,11 @@ render_f64_kernel(DevScene64 sc, CamParams cam, double* __restrict__ out_f64, fl
                 bool want_refr = false;
                 V3 fo = mk(0., 0., 0.), fd = mk(0., 0., 0.);
                 if (remaining != 0 && rec.transparency != 0.0) {
-                    double n_ratio = n1 / n2;
+                    double n_ratio = ddiv(n1, n2);
                     double cos_i = dot(eyev, normal);
                     double sin2_t = (n_ratio * n_ratio) * (1.0 - (cos_i * cos_i));
                     if (!(sin2_t > 1.0)) {
-                        double cos_t = sqrt(1.0 - sin2_t);
+                        double cos_t = dsqrt(1.0 - sin2_t);
                         fd = sub(mul(normal, n_ratio * cos_i - cos_t), mul(eyev, n_ratio));
                         fo = under_point;
                         want_refr = true;
@@ -603,14 +613,14 @@ render_f64_kernel(DevScene64 sc, CamParams cam, double* __restrict__ out_f64, fl
                     double cs = dot(eyev, normal);
                     bool tir = false;
                     if (n1 > n2) {
-                        double n = n1 / n2;
+                        double n = ddiv(n1, n2);
                         double sin2_t = (n * n) * (1.0 - (cs * cs));
                         if (sin2_t > 1.0) tir = true;
-                        else cs = sqrt(1.0 - sin2_t);
+                        else cs = dsqrt(1.0 - sin2_t);
                     }
                     if (tir) reflectance = 1.0;
                     else {
-                        double q = (n1 - n2) / (n1 + n2);
+                        double q = ddiv(n1 - n2, n1 + n2);
                         double r0 = q * q;
                         double m = 1.0 - cs;
                         double m2 = m * m;
