@@ -39,7 +39,8 @@ enum {
     RTC_ERR_NO_DEVICE = 3,    /* no CUDA device / driver: the path never falls back to the CPU */
     RTC_ERR_CUDA = 4,         /* a CUDA runtime call failed; see rtc_last_error() */
     RTC_ERR_NO_SCENE = 5,     /* rtc_render* before rtc_scene_upload */
-    RTC_ERR_NCCL = 6
+    RTC_ERR_NCCL = 6,
+    RTC_ERR_TIMEOUT = 7       /* rtc_wait_result: a completion flag did not arrive within the context's wait timeout */
 };
 
 /* src/shape.rs:281 (Sphere), :405 (Plane), :500 (Cube) */
@@ -155,9 +156,17 @@ typedef struct rtc_render_opts {
 /* f32 small-scene kernel: hand tiles out in linear order instead of "tiles that see a transparent
  * surface first" (the scheduling pre-pass).  Same image either way; for measuring the difference. */
 #define RTC_OPT_LINEAR_TILE_ORDER 4
-/* f32 general kernel, scenes whose streams stay in global memory: test every shape exactly instead of
- * filtering by bounding sphere first.  Same image either way (the filter is conservative); for checking that. */
+/* Both precisions, scenes with a bounding-sphere hierarchy (the parity kernel: any scene with spheres or cubes; fast
+ * mode: scenes whose streams stay in global memory): run every shape's exact test instead of filtering by bounding
+ * sphere first.  Same image, hit mask and counters either way (the filter is conservative); for checking that. */
 #define RTC_OPT_NO_BOUND_FILTER 8
+/* rtc_render: deliver by DMA straight into the caller's buffer in out_format (no pinned staging, no host pass).  Needs
+ * the buffer registered (rtc_register_host_buffer), else RTC_ERR_INVALID_ARG.  Without this flag the library chooses:
+ * registered buffers get the direct delivery except for the one case where staging wins — a whole fast-mode frame on one
+ * GPU into an F64_RGB Canvas, which crosses PCIe as f32 (half the bytes) and is widened by host threads. */
+#define RTC_OPT_DELIVER_DIRECT 16
+/* rtc_render: never deliver directly (measure the staged path with a registered buffer). */
+#define RTC_OPT_DELIVER_STAGED 32
 
 #define RTC_MAX_DEPTH 8
 
@@ -189,7 +198,10 @@ int rtc_device_count(void);
 /* A context owns streams, the device scene, frame buffers and pinned staging for the GPUs in
  * device_ids (n_gpus >= 1; NULL device_ids = devices 0..n_gpus-1).  It amortises set-up over
  * frames (the reference re-renders per GIF frame: src/lua.rs:34-41).  One thread at a time
- * per context; different contexts may be used concurrently (Camera::render takes &self,
+ * per context and ONE launch stream in flight per context: the persistent kernels share the context's tile
+ * counter, so a render enqueued on a second stream (or rtc_render beside a user-stream rtc_render_device)
+ * must be ordered after the previous one by the caller (an event or a synchronise).  Different contexts may be
+ * used concurrently (Camera::render takes &self,
  * &World and both are Sync: src/shape.rs:17, src/material.rs:33). */
 int rtc_context_create(const int* device_ids, int n_gpus, rtc_context** out_ctx);
 void rtc_context_destroy(rtc_context* ctx);
@@ -209,6 +221,14 @@ int rtc_scene_upload(rtc_context* ctx, const rtc_light* light, const rtc_shape* 
 int rtc_scene_upload_lights(rtc_context* ctx, const rtc_light* lights, size_t n_lights, const rtc_shape* shapes,
                             size_t n_shapes);
 
+/* Long-lived caller frames (the Canvas a renderer reuses per GIF frame, src/lua.rs:34-41; a frame in memory shared by
+ * one process per GPU): register the buffer once (cudaHostRegister: page-locked and visible to every GPU of the machine)
+ * and rtc_render delivers finished rows into it by DMA — no staging copy and no pass by host threads; each GPU writes
+ * its rows over its own PCIe link.  ptr / bytes must cover every out_rgb later passed from inside the range.
+ * Unregister before freeing the memory.  Replaces nothing in the reference (Canvas.pixels is a Vec, src/canvas.rs:17-22). */
+int rtc_register_host_buffer(rtc_context* ctx, void* ptr, size_t bytes);
+int rtc_unregister_host_buffer(rtc_context* ctx, void* ptr);
+
 /* Camera::render / render_async (src/camera.rs:116-160): renders the uploaded scene into the
  * caller's HOST buffers.  out_rgb: hsize*vsize*3 elements of opts->out_format, row-major
  * y*hsize+x (Canvas.pixels, src/canvas.rs:43-46); pixels outside the rect are 0 (src/canvas.rs:37-41).
@@ -223,6 +243,10 @@ int rtc_shard_rows(const rtc_camera* cam, const rtc_render_opts* opts);
 
 /* Same render, DEVICE buffers on the context's first GPU, enqueued on `stream`
  * (a cudaStream_t; NULL = the context's own stream, synchronised before returning).
+ * A context with several GPUs shards the frame over them (interleaved row tiles of opts->tile_rows rows, tile k ->
+ * GPU k % n_gpus; opts' shard fields are ignored): every GPU's kernel stores its pixels straight into the frame on the
+ * first GPU through peer access (NVLink), ordered by events — `stream` continues when all of them are done.  The
+ * destination is then always a full frame.  RTC_ERR_UNSUPPORTED when a GPU cannot reach the first one.
  * With shard_count > 1, d_out_rgb / d_out_hit_mask are the shard's compact buffers:
  * rtc_shard_rows() rows of hsize pixels, owned tiles stacked in frame order.
  * Counters and kernel_ms in `stats` are only filled when stream == NULL. */
@@ -253,11 +277,19 @@ int rtc_ipc_close(rtc_context* ctx, void* d_ptr, uint64_t offset);
  * already on `stream` (NULL = the context's stream), a store of `value` to the 32-bit word at d_flag —
  * which may be a peer-mapped word of another GPU (rtc_ipc_open) — with system-scope release: all
  * earlier stores of this stream (the rendered pixels) are visible before the flag.  rtc_wait_device
- * enqueues a kernel that returns once d_flags[i] >= value for all i in [0, n) (it gives up after about
- * two seconds and the next CUDA call on the stream reports an error; no host synchronisation either
- * way).  Rank 0 of a sharded render waits for the other ranks' flags instead of running a collective. */
+ * enqueues a kernel that returns once d_flags[i] >= value for all i in [0, n) (no host synchronisation either
+ * way).  Rank 0 of a sharded render waits for the other ranks' flags instead of running a collective.
+ * A wait gives up after the context's wait timeout (default 60 s — parity-mode frames of big scenes take seconds;
+ * rtc_set_wait_timeout changes it): it then records the index of the first missing flag in the context and returns
+ * — the stream goes on and the CUDA context stays usable; whatever the stream does next sees an incomplete frame.
+ * rtc_wait_result synchronises `stream` and reports it: RTC_OK, or RTC_ERR_TIMEOUT with *first_missing = i (the rank
+ * whose flag did not arrive; nullable) — call it before consuming a frame when a peer may have died.
+ * The same flags give back-pressure between frames: the consumer signals "frame k consumed" after its last read and
+ * the producers wait for it before they overwrite the frame (raytracer-challenge_b200/sharded.py). */
 int rtc_signal_device(rtc_context* ctx, void* d_flag, uint32_t value, void* stream);
 int rtc_wait_device(rtc_context* ctx, const void* d_flags, int n, uint32_t value, void* stream);
+int rtc_set_wait_timeout(rtc_context* ctx, double seconds);
+int rtc_wait_result(rtc_context* ctx, void* stream, int* first_missing);
 
 /* Canvas delivery for the device-buffer entry points: copies a finished frame (hsize*vsize pixels of
  * `dev_format`, on the context's first GPU) into the caller's HOST buffer of `out_format`, after everything

@@ -19,6 +19,7 @@
 //   * EPSILON: the reference offsets over_point/under_point by 1e-8, below f32 resolution
 //     (SURVEY.md F4).  Fast mode uses kEps32 = 1e-4 (the book's value) for the same purpose.
 #include "rtc_common.h"
+#include "parity64.cuh"
 
 namespace rtc {
 namespace {
@@ -80,29 +81,57 @@ __device__ __forceinline__ bool cube_slab32(const float4* r, F3 o, F3 d, float& 
 // back to the passes.
 constexpr int kNegCap = 48;
 
-// Bounding-sphere filter (kFilter kernels: 10^3+ shapes, streams in global memory).  |(c - o) x d^| is the distance
-// of the centre from the ray's line; with m = o x d^ it is |c x d^ - m|, six FFMA per shape and three more for
-// the squared length minus R^2 (the stream stores -R^2).  `exact(i)` runs for every entry i of the bound stream
-// whose line distance is within R plus the rounding margin: E bounds the error of this test plus that of the
-// exact tests (each a few dozen ulps of |c| + |o|), so no shape an exact test would accept is skipped and the
-// image is the one the unfiltered loops produce (RTC_OPT_NO_BOUND_FILTER renders that one for comparison).
-// Four shapes per trip, one branch per trip: the exact tests sit behind it.
+// Bounding-sphere filter (kFilter kernels: 10^3+ shapes, streams in global memory) — a RAY query.  |(c - o) x d^| is
+// the distance of a centre from the ray's line; with m = o x d^ it is |c x d^ - m|, six FFMA per shape and three more
+// for the squared length minus R^2 (the stream stores -R^2).  s = (c - o) . d^ is the centre's position along the ray
+// (three more FFMA): a shape can only matter to a query interested in positions [lo, hi] along the ray when the
+// interval [s - R, s + R] reaches into it, i.e. when q = max(lo - s, s - hi, 0) has q^2 <= R^2.
+//   radiance rays, World::intersect + get_hit (src/shape.rs:677-683, 195-232): [0, current nearest hit] — hi shrinks
+//     while the sweep runs (the exact test of a candidate updates it), so everything behind a hit already found and
+//     everything behind the origin is skipped;
+//   shadow rays, is_shadowed_by_light (:716-727): [0, distance to the light];
+//   the negative-t entries Intersection::compute_refractive needs (:115-141): (-inf, 0], run only for hits on a
+//     transparent material.
+// `exact(i)` runs for every entry i of the bound stream that passes.  E bounds the error of these tests plus that of
+// the exact tests (each a few dozen ulps of |c| + |o|), so no shape an exact test would accept for the interval is
+// skipped and the image is the one the unfiltered loops produce (RTC_OPT_NO_BOUND_FILTER renders that one for
+// comparison).  A NaN never culls.  Four shapes per trip, one branch per trip: the exact tests sit behind it.
+struct RayQ {
+    F3 dh, m;        // unit direction, o x dh
+    float od;        // o . dh
+    float len;       // |d|: position along the ray = t * len
+    float E;         // absolute error bound of the positions computed here
+    float margin, gmargin, smargin;
+};
+__device__ __forceinline__ RayQ make_rayq(const Streams32& S, F3 o, F3 d) {
+    RayQ q;
+    const float dd = dot(d, d), il = rsqrtf(dd);
+    q.dh = d * il;
+    q.len = dd * il;
+    q.m = mk(o.y * q.dh.z - o.z * q.dh.y, o.z * q.dh.x - o.x * q.dh.z, o.x * q.dh.y - o.y * q.dh.x);
+    q.od = dot(o, q.dh);
+    q.E = 3.8e-6f * (fmaxf(fmaxf(S.cmax, S.gcmax), S.scmax) + fabsf(o.x) + fabsf(o.y) + fabsf(o.z));
+    q.margin = fmaf(q.E, 2.f * S.rmax + q.E, 2e-6f * S.rmax * S.rmax);
+    q.gmargin = fmaf(q.E, 2.f * S.grmax + q.E, 2e-6f * S.grmax * S.grmax);
+    q.smargin = fmaf(q.E, 2.f * S.srmax + q.E, 2e-6f * S.srmax * S.srmax);
+    return q;
+}
+// lo / hi: the interval of positions along the ray (in world units, rounding margin E included by the caller); hi is read
+// again before every test, so `exact` may shrink it.
 template <typename F>
-__device__ __forceinline__ void sweep_bounds(const Streams32& S, F3 o, F3 d, F exact) {
-    const F3 dh = d * rsqrtf(dot(d, d));
-    const F3 m = mk(o.y * dh.z - o.z * dh.y, o.z * dh.x - o.x * dh.z, o.x * dh.y - o.y * dh.x);
-    const float E = 3.8e-6f * (fmaxf(fmaxf(S.cmax, S.gcmax), S.scmax) + fabsf(o.x) + fabsf(o.y) + fabsf(o.z));
-    const float margin = fmaf(E, 2.f * S.rmax + E, 2e-6f * S.rmax * S.rmax);
-    const float gmargin = fmaf(E, 2.f * S.grmax + E, 2e-6f * S.grmax * S.grmax);
-    const float smargin = fmaf(E, 2.f * S.srmax + E, 2e-6f * S.srmax * S.srmax);
-    auto gap = [&](float4 b) {
+__device__ __forceinline__ void sweep_bounds(const Streams32& S, const RayQ& Q, float lo, const float& hi, F exact) {
+    const F3 dh = Q.dh, m = Q.m;
+    auto pass = [&](float4 b, float mg) -> bool {
         const float vx = fmaf(-b.z, dh.y, fmaf(b.y, dh.z, -m.x));
         const float vy = fmaf(-b.x, dh.z, fmaf(b.z, dh.x, -m.y));
         const float vz = fmaf(-b.y, dh.x, fmaf(b.x, dh.y, -m.z));
-        return fmaf(vz, vz, fmaf(vy, vy, fmaf(vx, vx, b.w)));
+        const float gap = fmaf(vz, vz, fmaf(vy, vy, fmaf(vx, vx, b.w)));
+        const float s = fmaf(b.z, dh.z, fmaf(b.y, dh.y, fmaf(b.x, dh.x, -Q.od)));
+        const float q = fmaxf(fmaxf(lo - s, s - hi), 0.f);
+        return !(gap > mg) && !(fmaf(q, q, b.w) > 0.f);
     };
     // Group level: the streams of a big scene are in Morton order, eight consecutive entries share a bounding sphere; a
-    // ray whose line misses it (same test, same kind of margin) skips the eight.  The group tests of 32 groups run
+    // ray that misses it (same test, same kind of margin) skips the eight.  The group tests of 32 groups run
     // branch-free into one bit mask per lane; the lanes then drain their masks side by side — a warp pays for the
     // largest number of candidate groups any of its lanes has in the block, not for every trip in which some lane has one.
     // Block level: 32 consecutive groups (256 entries) share one more bounding sphere.  A block is swept when ANY lane of
@@ -116,8 +145,7 @@ __device__ __forceinline__ void sweep_bounds(const Streams32& S, F3 o, F3 d, F e
 #pragma unroll 2
         for (int j = 0; j < 32; j += 4) {
             const float4 q0 = S.sbound[sb + j], q1 = S.sbound[sb + j + 1], q2 = S.sbound[sb + j + 2], q3 = S.sbound[sb + j + 3];
-            const float t0 = gap(q0), t1 = gap(q1), t2 = gap(q2), t3 = gap(q3);
-            sm |= ((t0 <= smargin ? 1u : 0u) | (t1 <= smargin ? 2u : 0u) | (t2 <= smargin ? 4u : 0u) | (t3 <= smargin ? 8u : 0u)) << j;
+            sm |= ((pass(q0, Q.smargin) ? 1u : 0u) | (pass(q1, Q.smargin) ? 2u : 0u) | (pass(q2, Q.smargin) ? 4u : 0u) | (pass(q3, Q.smargin) ? 8u : 0u)) << j;
         }
         unsigned wm = __reduce_or_sync(__activemask(), sm);   // a lane's own candidates are always in it
         while (wm) {
@@ -127,8 +155,7 @@ __device__ __forceinline__ void sweep_bounds(const Streams32& S, F3 o, F3 d, F e
 #pragma unroll 2
             for (int j = 0; j < 32; j += 4) {
                 const float4 q0 = S.gbound[gb + j], q1 = S.gbound[gb + j + 1], q2 = S.gbound[gb + j + 2], q3 = S.gbound[gb + j + 3];
-                const float t0 = gap(q0), t1 = gap(q1), t2 = gap(q2), t3 = gap(q3);
-                gm |= ((t0 <= gmargin ? 1u : 0u) | (t1 <= gmargin ? 2u : 0u) | (t2 <= gmargin ? 4u : 0u) | (t3 <= gmargin ? 8u : 0u)) << j;
+                gm |= ((pass(q0, Q.gmargin) ? 1u : 0u) | (pass(q1, Q.gmargin) ? 2u : 0u) | (pass(q2, Q.gmargin) ? 4u : 0u) | (pass(q3, Q.gmargin) ? 8u : 0u)) << j;
             }
             while (gm) {
                 const int g = 8 * (gb + __ffs(gm) - 1);
@@ -137,8 +164,7 @@ __device__ __forceinline__ void sweep_bounds(const Streams32& S, F3 o, F3 d, F e
 #pragma unroll
                 for (int j = 0; j < 8; j += 4) {
                     const float4 b0 = S.bound[g + j], b1 = S.bound[g + j + 1], b2 = S.bound[g + j + 2], b3 = S.bound[g + j + 3];
-                    const float s0 = gap(b0), s1 = gap(b1), s2 = gap(b2), s3 = gap(b3);
-                    cm |= ((s0 <= margin ? 1u : 0u) | (s1 <= margin ? 2u : 0u) | (s2 <= margin ? 4u : 0u) | (s3 <= margin ? 8u : 0u)) << j;
+                    cm |= ((pass(b0, Q.margin) ? 1u : 0u) | (pass(b1, Q.margin) ? 2u : 0u) | (pass(b2, Q.margin) ? 4u : 0u) | (pass(b3, Q.margin) ? 8u : 0u)) << j;
                 }
                 while (cm) {
                     const int k = __ffs(cm) - 1;
@@ -150,7 +176,7 @@ __device__ __forceinline__ void sweep_bounds(const Streams32& S, F3 o, F3 d, F e
     }
 }
 
-template <bool kCollect, bool kCubes, bool kFilter>
+template <bool kCollect, bool kCubes>
 __device__ __forceinline__ void intersect32(const Streams32& S, F3 o, F3 d, float& best_t, int& hit, float2* neg, int& n_neg) {
     hit = -1;
     if (kCollect) n_neg = 0;
@@ -202,18 +228,10 @@ __device__ __forceinline__ void intersect32(const Streams32& S, F3 o, F3 d, floa
             if (kCollect && t1 < 0.f) { keep(t1, 2 * (S.np + S.nu + i)); if (t2 < 0.f) keep(t2, 2 * (S.np + S.nu + i) + 1); }
         }
     };
-    if (kFilter) {
-        sweep_bounds(S, o, d, [&](int i) {
-            if (i < S.nu) usph(i);
-            else if (!kCubes || i - S.nu < S.ng) gsph(i - S.nu);
-            else cube(i - S.nu);
-        });
-    } else {
 #pragma unroll 2
-        for (int i = 0; i < S.nu; ++i) usph(i);
-        for (int i = 0; i < S.ng; ++i) gsph(i);
-        if (kCubes) for (int i = S.ng; i < S.ng + S.nc; ++i) cube(i);
-    }
+    for (int i = 0; i < S.nu; ++i) usph(i);
+    for (int i = 0; i < S.ng; ++i) gsph(i);
+    if (kCubes) for (int i = S.ng; i < S.ng + S.nc; ++i) cube(i);
 }
 
 __device__ __forceinline__ int stream_to_shape(const Streams32& S, int pos) {
@@ -431,10 +449,16 @@ __device__ __forceinline__ bool shadow32(const Streams32& S, const float* __rest
         }
     };
     if (kFilter) {
-        sweep_bounds(S, o, d, [&](int i) {
+        // segment query: only shapes that reach into [0, |light - p|] along the ray; a lane that has found its occluder
+        // stops looking (hi = -inf culls everything: any-hit)
+        const RayQ Q = make_rayq(S, o, d);
+        const float lo = -Q.E;
+        float hi = fmaf(Q.len, 1.000002f, Q.E);
+        sweep_bounds(S, Q, lo, hi, [&](int i) {
             if (i < S.nu) { if (light_inside) usph_in(i); else usph(i); }
             else if (!kCubes || i - S.nu < S.ng) gsph(i - S.nu);
             else cube(i - S.nu);
+            if (hit || g <= 0.f) hi = -__int_as_float(0x7f800000);
         });
     } else {
         if (!light_inside) {
@@ -447,6 +471,93 @@ __device__ __forceinline__ bool shadow32(const Streams32& S, const float* __rest
         if (kCubes) for (int i = S.ng; i < S.ng + S.nc; ++i) cube(i);
     }
     return hit || g <= 0.f;
+}
+
+// ---- kRefine kernels (scenes whose streams stay in global memory: 10^3+ shapes, e.g. config C4) ----------------------
+// Thousands of small spheres are strongly diverging mirrors: a hit-point error of one f32 ulp is amplified ~10^3 per
+// sphere-to-sphere bounce, so an all-f32 path leaves the reference's ray tree after two or three bounces.  These kernels
+// therefore keep the GEOMETRY of the radiance rays in f64, in the reference's operation order (parity64.cuh, the
+// statements the parity kernel runs): the ray (o, d) is carried in f64 from bounce to bounce; the f32 bounding-sphere
+// hierarchy only selects candidates (a conservative filter), each candidate's exact test is Sphere / Cube / Plane::
+// intersect_local in f64 on the stored inverse of the shape's f64 record, hit selection follows the insertion sort's tie
+// rule, and hit point, normal, over / under point, reflected and refracted directions and n1 / n2 are the f64 ones.  The
+// ray tree is then the parity kernel's, node for node; what stays in f32 is what does not feed back into geometry:
+// the filter, the any-hit shadow test, patterns, Phong lighting, Schlick weights and the colour sums.
+template <bool kCubes, bool kFilter>
+__device__ __forceinline__ void intersect_mixed(const Streams32& S, const ShadeRec64* __restrict__ R64, F3 o, F3 d, p64::V3 od, p64::V3 dd,
+                                                double& best_t, int& best_idx) {
+    best_t = __longlong_as_double(0x7ff0000000000000LL);
+    best_idx = 0x7fffffff;
+    for (int i = 0; i < S.np; ++i) {                     // Plane::intersect_local, src/shape.rs:462-471
+        const int idx = S.pl_index[i];
+        double t;
+        if (p64::plane_root(reinterpret_cast<const double2*>(R64[idx].inv + 4), od, dd, t)) p64::take(t, idx, best_t, best_idx);
+    }
+    const RayQ Q = make_rayq(S, o, d);
+    const float lo = -Q.E;
+    // positions beyond the nearest hit found so far cannot hold the hit (an equal t loses or wins by shape index: kept by the margin)
+    auto bound_of = [&](double t) { return fmaf(__double2float_ru(t) * Q.len, 1.000002f, Q.E); };
+    float hi = bound_of(best_t);
+    auto exact = [&](int i) {
+        const int idx = i < S.nu ? S.us_index[i] : S.gs_index[i - S.nu];
+        const double2* rows = reinterpret_cast<const double2*>(R64[idx].inv);
+        double t1, t2;
+        const bool any = (kCubes && i - S.nu >= S.ng) ? p64::cube_roots(rows, od, dd, t1, t2) : p64::sphere_roots(rows, od, dd, t1, t2);
+        if (any) {
+            p64::take(t1 >= 0.0 ? t1 : t2, idx, best_t, best_idx);
+            hi = bound_of(best_t);
+        }
+    };
+    if (kFilter) sweep_bounds(S, Q, lo, hi, exact);
+    else for (int i = 0; i < S.nu + S.ng + (kCubes ? S.nc : 0); ++i) exact(i);
+    if (best_idx == 0x7fffffff) best_idx = -1;
+}
+
+// Intersection::compute_refractive (src/shape.rs:115-141) for a hit on a transparent material, list-free as in the
+// parity kernel (parity64.cuh): only entries with t < 0 matter, i.e. shapes that reach behind the ray origin — a second
+// query over (-inf, 0], run twice: pass 0 takes the parity of the negative entries per world_id (u8 ids alias beyond 255
+// shapes), pass 1 keeps the last two containers.
+template <bool kCubes, bool kFilter>
+__device__ __noinline__ void containers_mixed(const Streams32& S, const ShadeRec64* __restrict__ R64, F3 o, F3 d, p64::V3 od, p64::V3 dd,
+                                              int hit_idx, double& n1, double& n2) {
+    unsigned parity[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) parity[k] = 0u;
+    p64::Cont top1, top2;
+    top1.idx = -1; top2.idx = -1; top1.t = top2.t = 0.0; top1.ord = top2.ord = 0; top1.id = top2.id = -1;
+    const RayQ Q = make_rayq(S, o, d);
+    const float lo = -__int_as_float(0x7f800000), hi = Q.E;
+#pragma unroll 1
+    for (int pass = 0; pass < 2; ++pass) {
+        auto entry = [&](double t, int idx, int root) {
+            const int id = R64[idx].world_id & 255;
+            if (pass == 0) parity[id >> 5] ^= 1u << (id & 31);
+            else if ((parity[id >> 5] >> (id & 31)) & 1u) { p64::Cont e; e.t = t; e.ord = 2 * idx + root; e.idx = idx; e.id = id; p64::offer(e, top1, top2); }
+        };
+        for (int i = 0; i < S.np; ++i) {
+            const int idx = S.pl_index[i];
+            double t;
+            if (p64::plane_root(reinterpret_cast<const double2*>(R64[idx].inv + 4), od, dd, t) && t < 0.0) entry(t, idx, 0);
+        }
+        auto exact = [&](int i) {
+            const int idx = i < S.nu ? S.us_index[i] : S.gs_index[i - S.nu];
+            const double2* rows = reinterpret_cast<const double2*>(R64[idx].inv);
+            double t1, t2;
+            const bool any = (kCubes && i - S.nu >= S.ng) ? p64::cube_roots(rows, od, dd, t1, t2) : p64::sphere_roots(rows, od, dd, t1, t2);
+            if (any) { if (t1 < 0.0) entry(t1, idx, 0); if (t2 < 0.0) entry(t2, idx, 1); }
+        };
+        if (kFilter) sweep_bounds(S, Q, lo, hi, exact);
+        else for (int i = 0; i < S.nu + S.ng + (kCubes ? S.nc : 0); ++i) exact(i);
+    }
+    n1 = top1.idx >= 0 ? R64[top1.idx].refractive_index : 1.0;
+    const int hid = R64[hit_idx].world_id & 255;
+    const bool hit_is_container = (parity[hid >> 5] >> (hid & 31)) & 1u;
+    if (hit_is_container) {
+        if (top1.idx >= 0 && top1.id == hid) n2 = top2.idx >= 0 ? R64[top2.idx].refractive_index : 1.0;
+        else n2 = top1.idx >= 0 ? R64[top1.idx].refractive_index : 1.0;
+    } else {
+        n2 = R64[hit_idx].refractive_index;
+    }
 }
 
 // compute_refractive when every world_id is unique (<= 255 shapes): a shape is a container iff it
@@ -529,12 +640,16 @@ __device__ __noinline__ void compute_refractive32_unique(const Streams32& S, con
 #ifndef RTC_F32_MIN_BLOCKS
 #define RTC_F32_MIN_BLOCKS 6
 #endif
+#ifndef RTC_F32_REFINE_MIN_BLOCKS
+#define RTC_F32_REFINE_MIN_BLOCKS 4   // kRefine kernels carry the ray and the hit geometry in f64: 128 registers, like the parity kernel
+#endif
 // kSmem: shading records staged to shared memory; kUnique: world_ids are unique (<= 255 shapes);
 // kGlobal: the intersect streams stay in global memory (read through L1/L2 as warp-uniform loads) —
 // scenes of any size, e.g. the 10k-shape config C4; 2 = with the bounding-sphere filter in front (sweep_bounds).
 // kCubes: the scene has cubes (object-space slab tests behind the general spheres); scenes without them compile none of it
+// kGlobal != 0 is also kRefine: the geometry of the radiance rays in f64 (see intersect_mixed)
 template <bool kSmem, bool kUnique, int kGlobal, bool kCubes>
-__global__ void __launch_bounds__(kThreads, RTC_F32_MIN_BLOCKS)
+__global__ void __launch_bounds__(kThreads, kGlobal ? RTC_F32_REFINE_MIN_BLOCKS : RTC_F32_MIN_BLOCKS)
 render_f32_kernel(DevScene32 sc, CamParams cam, void* __restrict__ out_rgb, uint8_t* __restrict__ out_hit,
                   Counters* __restrict__ counters, unsigned* __restrict__ work) {
     extern __shared__ float4 smem4[];
@@ -549,6 +664,8 @@ render_f32_kernel(DevScene32 sc, CamParams cam, void* __restrict__ out_rgb, uint
     const F3 light_pos = mk(sc.light_pos[0], sc.light_pos[1], sc.light_pos[2]);
     const F3 light_int = mk(sc.light_int[0], sc.light_int[1], sc.light_int[2]);
     constexpr bool kFilter = kGlobal == 2;
+    constexpr bool kRefine = kGlobal != 0;
+    const ShadeRec64* __restrict__ R64 = sc.rec64;
     S.bound = sc.bound; S.nb4 = sc.n_bound4; S.cmax = sc.bound_cmax; S.rmax = sc.bound_rmax;
     S.gbound = sc.gbound; S.gcmax = sc.gbound_cmax; S.grmax = sc.gbound_rmax;
     S.sbound = sc.sbound; S.scmax = sc.sbound_cmax; S.srmax = sc.sbound_rmax;
@@ -622,18 +739,28 @@ render_f32_kernel(DevScene32 sc, CamParams cam, void* __restrict__ out_rgb, uint
     F3 aa_tot = mk(0, 0, 0);        // Color::average_over's running sums
     int aa_ntot = n_sub;            // samples this pixel takes: 4, or 4 + n_extra once the fixed four disagree
     unsigned hitbits = 0;
-    float4 stk_a[kMaxStack], stk_b[kMaxStack];  // pending refraction rays: (o, w), (d, remaining)
+    float4 stk_a[kRefine ? 1 : kMaxStack], stk_b[kRefine ? 1 : kMaxStack];  // pending refraction rays: (o, w), (d, remaining)
+    // kRefine: the ray in f64 (ro / rd are its f32 roundings, refreshed every iteration) and the pending refraction rays in f64
+    p64::V3 rod = p64::mk(0., 0., 0.), rdd = p64::mk(0., 0., 1.);
+    double2 stk_d0[kRefine ? kMaxStack : 1], stk_d1[kRefine ? kMaxStack : 1], stk_d2[kRefine ? kMaxStack : 1];   // (ox oy) (oz dx) (dy dz)
+    float2 stk_w[kRefine ? kMaxStack : 1];                                                                       // (weight, remaining)
     int sp = 0;
     unsigned n_rays = 0, n_shaded = 0, n_phits = 0;
-    float2 neg[kUnique ? 1 : kNegCap];   // negative-t entries of the current ray (aliased world_ids only)
+    float2 neg[(kUnique || kRefine) ? 1 : kNegCap];   // negative-t entries of the current ray (aliased world_ids only)
     int n_neg = 0;
 
     for (;;) {
         // ---------------------------------------------------------------- refill lanes without a ray
         if (!has_ray && sp > 0) {
             --sp;
-            float4 a = stk_a[sp], b = stk_b[sp];
-            ro = xyz(a); rw = a.w; rd = xyz(b); remaining = __float_as_int(b.w);
+            if (kRefine) {
+                const double2 a = stk_d0[sp], b = stk_d1[sp], c = stk_d2[sp];
+                const float2 w = stk_w[sp];
+                rod = p64::mk(a.x, a.y, b.x); rdd = p64::mk(b.y, c.x, c.y); rw = w.x; remaining = __float_as_int(w.y);
+            } else {
+                float4 a = stk_a[sp], b = stk_b[sp];
+                ro = xyz(a); rw = a.w; rd = xyz(b); remaining = __float_as_int(b.w);
+            }
             is_primary = false; has_ray = true;
         }
         if (!has_ray && have) {
@@ -713,11 +840,29 @@ render_f32_kernel(DevScene32 sc, CamParams cam, void* __restrict__ out_rgb, uint
                 xo = (float)(unsigned)(resample_bits(aa_seed_mixed, pixel_index, (unsigned)(sub - 4), 0u) >> 40) * 5.9604644775390625e-8f;
                 yo = (float)(unsigned)(resample_bits(aa_seed_mixed, pixel_index, (unsigned)(sub - 4), 1u) >> 40) * 5.9604644775390625e-8f;
             }
-            float fx = (float)px + xo;
-            float fy = (float)py + yo;
-            F3 dir = fma3(cam_dx, fx, fma3(cam_dy, fy, cam_d0));
-            rd = dir * rsqrtf(dot(dir, dir));
-            ro = cam_origin; rw = w0; remaining = cam.max_depth; is_primary = true; has_ray = true;
+            if (kRefine) {                      // Camera::ray_for_pixel_offset in f64, the reference's statements (src/camera.rs:64-76)
+                double xod = n_sub == 1 ? 0.5 : ((sub & 1) ? 0.75 : 0.25);
+                double yod = n_sub == 1 ? 0.5 : ((sub & 2) ? 0.75 : 0.25);
+                if (aa && sub >= 4) {
+                    const uint64_t pixel_index = (uint64_t)py * cam.hsize + (uint64_t)px;
+                    xod = (double)(resample_bits(aa_seed_mixed, pixel_index, (unsigned)(sub - 4), 0u) >> 11) * (1.0 / 9007199254740992.0);
+                    yod = (double)(resample_bits(aa_seed_mixed, pixel_index, (unsigned)(sub - 4), 1u) >> 11) * (1.0 / 9007199254740992.0);
+                }
+                const double xoffset = ((double)px + xod) * cam.pixel_size;
+                const double yoffset = ((double)py + yod) * cam.pixel_size;
+                const double world_x = cam.half_width - xoffset;
+                const double world_y = cam.half_height - yoffset;
+                const p64::V3 pixel = p64::xpoint(cam.vinv, p64::mk(world_x, world_y, -1.));
+                const p64::V3 origin = p64::xpoint(cam.vinv, p64::mk(0., 0., 0.));
+                rod = origin; rdd = p64::normalize(p64::sub(pixel, origin));
+            } else {
+                float fx = (float)px + xo;
+                float fy = (float)py + yo;
+                F3 dir = fma3(cam_dx, fx, fma3(cam_dy, fy, cam_d0));
+                rd = dir * rsqrtf(dot(dir, dir));
+                ro = cam_origin;
+            }
+            rw = w0; remaining = cam.max_depth; is_primary = true; has_ray = true;
         }
         if (!has_ray && !have && exhausted) dead = true;
         if (__all_sync(full, dead)) break;
@@ -725,7 +870,14 @@ render_f32_kernel(DevScene32 sc, CamParams cam, void* __restrict__ out_rgb, uint
         // ---------------------------------------------------------------- phase A: World::intersect, radiance rays
         float t = __int_as_float(0x7f800000);
         int hit = -1;
-        if (has_ray) { intersect32<!kUnique, kCubes, kFilter>(S, ro, rd, t, hit, neg, n_neg); ++n_rays; }
+        double t64 = 0.0;
+        if (kRefine) {
+            ro = mk((float)rod.x, (float)rod.y, (float)rod.z);   // f32 roundings of the ray: the filter, the shading
+            rd = mk((float)rdd.x, (float)rdd.y, (float)rdd.z);
+            if (has_ray) { intersect_mixed<kCubes, kFilter>(S, R64, ro, rd, rod, rdd, t64, hit); ++n_rays; }   // hit = shape index
+        } else {
+            if (has_ray) { intersect32<!kUnique, kCubes>(S, ro, rd, t, hit, neg, n_neg); ++n_rays; }            // hit = stream position
+        }
         if (has_ray && is_primary && hit >= 0) { if (sub < 4) hitbits |= 1u << sub; ++n_phits; }
         if (hit < 0) has_ray = false;   // World::color_at -> background_color (black), src/shape.rs:708
 
@@ -733,7 +885,81 @@ render_f32_kernel(DevScene32 sc, CamParams cam, void* __restrict__ out_rgb, uint
         F3 hp = mk(0, 0, 0), hn = mk(0, 1, 0);
         float hn1 = 1.f, hn2 = 1.f;
         int hidx = 0;
-        if (hit >= 0) {
+        float rw_hit = rw;          // weight of the ray that produced this hit (kRefine sets up the children before shading)
+        if (kRefine && hit >= 0) {
+            // prepare_computations in f64, the parity kernel's statements (src/shape.rs:75-96, 144-152, 34-40), then
+            // shade_hit's children (:689-699, 729-781): the next ray and the pending refraction ray leave this block in f64;
+            // the shadow test and the shading below get f32 roundings (hp with the f32 epsilon, hn, rd).
+            hidx = hit;
+            const ShadeRec64& r64 = R64[hidx];
+            const ShadeRec32& rec = R[hidx];
+            const float4 ds = rec.dif_spec, tr = rec.tr_ri;
+            const p64::V3 point = p64::add(rod, p64::mul(rdd, t64));
+            const p64::V3 eyev = p64::neg(rdd);
+            const p64::V3 lp = p64::xpoint(r64.inv, point);
+            p64::V3 ln = r64.kind == RTC_SHAPE_PLANE ? p64::mk(0., 1., 0.) : lp;
+            if (kCubes && r64.kind == RTC_SHAPE_CUBE) {            // Cube::normal_at_local :601-610; r64.invt = transpose(inverse), :623-629
+                const double ax = fabs(lp.x), ay = fabs(lp.y), az = fabs(lp.z);
+                const double maxc = fmax(ax, fmax(ay, az));
+                if (maxc == ax) ln = p64::mk(lp.x, 0., 0.);
+                else if (maxc == ay) ln = p64::mk(0., lp.y, 0.);
+                else ln = p64::mk(0., 0., lp.z);
+            }
+            p64::V3 normal = p64::normalize(p64::xvec3(r64.invt, ln));
+            double n1 = 1.0, n2 = 1.0;
+            if (tr.x != 0.f) containers_mixed<kCubes, kFilter>(S, R64, ro, rd, rod, rdd, hidx, n1, n2);
+            if (p64::dot(normal, eyev) < 0.0) normal = p64::neg(normal);
+            const p64::V3 over_point = p64::add(point, p64::mul(normal, p64::kEps));
+            const double cos_i = p64::dot(eyev, normal);
+            hn = mk((float)normal.x, (float)normal.y, (float)normal.z);
+            hp = fma3(hn, kEps32, mk((float)point.x, (float)point.y, (float)point.z));
+            hn1 = (float)n1; hn2 = (float)n2;
+            const float k_refl = ds.w, k_tr = tr.x;
+            float refl_w = rw * k_refl, refr_w = rw * k_tr;
+            if (k_refl > 0.f && k_tr > 0.f) {                          // World::reflectance (Schlick): a weight, f32
+                float cs = (float)cos_i, refl = 0.f;
+                bool tir = false;
+                if (hn1 > hn2) {
+                    float nn = hn1 / hn2;
+                    float sin2_t = nn * nn * (1.f - cs * cs);
+                    if (sin2_t > 1.f) tir = true; else cs = sqrtf(1.f - sin2_t);
+                }
+                if (tir) refl = 1.f;
+                else {
+                    float q = (hn1 - hn2) / (hn1 + hn2), r0 = q * q, m1 = 1.f - cs, m2 = m1 * m1;
+                    refl = fmaf(1.f - r0, m2 * m2 * m1, r0);
+                }
+                refl_w *= refl; refr_w *= 1.f - refl;
+            }
+            const bool want_refl = remaining != 0 && k_refl > 0.f;
+            bool want_refr = false;
+            p64::V3 fo = p64::mk(0., 0., 0.), fd = p64::mk(0., 0., 1.);
+            if (remaining != 0 && k_tr != 0.f) {                       // refracted_color, src/shape.rs:751-766
+                const double n_ratio = p64::ddiv(n1, n2);
+                const double sin2_t = (n_ratio * n_ratio) * (1.0 - (cos_i * cos_i));
+                if (!(sin2_t > 1.0)) {
+                    const double cos_t = p64::dsqrt(1.0 - sin2_t);
+                    fd = p64::sub(p64::mul(normal, n_ratio * cos_i - cos_t), p64::mul(eyev, n_ratio));
+                    fo = p64::sub(point, p64::mul(normal, p64::kEps));   // under_point
+                    want_refr = true;
+                }
+            }
+            if (want_refl) {
+                if (want_refr && sp < kMaxStack) {
+                    stk_d0[sp] = make_double2(fo.x, fo.y); stk_d1[sp] = make_double2(fo.z, fd.x); stk_d2[sp] = make_double2(fd.y, fd.z);
+                    stk_w[sp] = make_float2(refr_w, __int_as_float(remaining - 1));
+                    ++sp;
+                }
+                rdd = p64::reflect(rdd, normal);                       // reflectv, src/shape.rs:86
+                rod = over_point; rw = refl_w; --remaining;
+            } else if (want_refr) {
+                rod = fo; rdd = fd; rw = refr_w; --remaining;
+            } else {
+                has_ray = false;
+            }
+            is_primary = false;
+        }
+        if (!kRefine && hit >= 0) {
             hidx = stream_to_shape(S, hit);
             const ShadeRec32& rec = R[hidx];
             const float4 tr = rec.tr_ri;
@@ -813,7 +1039,8 @@ render_f32_kernel(DevScene32 sc, CamParams cam, void* __restrict__ out_rgb, uint
             const ShadeRec32& rec = R[hidx];
             const float4 ds = rec.dif_spec, tr = rec.tr_ri;
             const F3 eye = mk(-rd.x, -rd.y, -rd.z);
-            acc = fma3(surface, rw, acc);
+            acc = fma3(surface, rw_hit, acc);
+            if (!kRefine) {   // (kRefine: the children were set up in phase B)
             // children (src/shape.rs:689-699, 729-781) as weighted rays
             const float k_refl = ds.w, k_tr = tr.x;
             const bool both = k_refl > 0.f && k_tr > 0.f;
@@ -861,6 +1088,7 @@ render_f32_kernel(DevScene32 sc, CamParams cam, void* __restrict__ out_rgb, uint
                 ro = fo; rd = fd; rw = refr_w; --remaining;
             } else {
                 has_ray = false;
+            }
             }
         }
     }

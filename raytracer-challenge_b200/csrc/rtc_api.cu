@@ -85,6 +85,8 @@ struct DeviceState {
     DevBuf<Counters> counters;
     DevBuf<unsigned> work;  // tile counter of the persistent f32 kernel (+ blocks done, heavy / light tile counts)
     DevBuf<unsigned> order; // tile hand-out order of the small-scene kernel
+    DevBuf<unsigned> wait_status;   // rtc_wait_device: 0, or 1 + index of the first flag that did not arrive in time
+    bool peer_to_first = false;     // this GPU can store into the context's first GPU (rtc_render_device on several GPUs)
 };
 
 // Allocation base of a device pointer (cuMemGetAddressRange, fetched through the runtime so that the
@@ -202,6 +204,9 @@ struct rtc_context {
     unsigned char* pinned_hit = nullptr;
     size_t pinned_hit_cap = 0;
     Counters* pinned_counters = nullptr;  // one per device
+    unsigned* pinned_status = nullptr;    // rtc_wait_result reads the wait status word through this
+    std::vector<std::pair<unsigned char*, size_t>> registered;   // rtc_register_host_buffer ranges
+    double wait_timeout_s = 60.0;
 };
 
 namespace {
@@ -625,7 +630,15 @@ int flatten(const rtc_light* lights, size_t n_lights, const rtc_shape* shapes, s
     for (size_t li = 0; li < n_lights; ++li) {
         const rtc_light& L = lights[li];
         const float lx = (float)L.position[0], ly = (float)L.position[1], lz = (float)L.position[2];
-        for (int k = 0; k < np; ++k) { const float4& q = hs.pl32[k]; hs.plL.push_back(fmaf(q.z, lz, fmaf(q.y, ly, fmaf(q.x, lx, q.w)))); }
+        for (int k = 0; k < np; ++k) {
+            // f(light) == 0: the light lies in the plane.  The reference's shadow ray then meets the plane at t == distance
+            // (up to rounding), which fails `h.t < distance` (src/shape.rs:724): such a plane never shadows.  A NaN factor
+            // drops out of the kernels' fminf accumulation.
+            const rtc_shape& ps = shapes[hs.pl_index[k]];
+            const double f1 = ps.inv[4] * L.position[0] + ps.inv[5] * L.position[1] + ps.inv[6] * L.position[2] + ps.inv[7];
+            const float4& q = hs.pl32[k];
+            hs.plL.push_back(f1 == 0.0 ? std::numeric_limits<float>::quiet_NaN() : fmaf(q.z, lz, fmaf(q.y, ly, fmaf(q.x, lx, q.w))));
+        }
         for (int k = 0; k < nu; ++k) {
             const float4& q = hs.us32[k];
             const float dx = lx - q.x, dy = ly - q.y, dz = lz - q.z;
@@ -672,6 +685,7 @@ int flatten(const rtc_light* lights, size_t n_lights, const rtc_shape* shapes, s
             const double sc = f1 / (std::fabs(f1) > 0.0 ? std::fabs(f1) : 1.0);   // sign only: keeps the magnitudes of the plane
             sp.splanes[k] = make_float4((float)(shapes[i].inv[4] * sc), (float)(shapes[i].inv[5] * sc), (float)(shapes[i].inv[6] * sc),
                                         (float)(shapes[i].inv[7] * sc));
+            if (f1 == 0.0) sp.splanes[k] = make_float4(0.f, 0.f, 0.f, 1.f);   // the light lies in the plane: it never shadows (see plL above)
             SmallRec32& r = hs.srec[k];
             const float4 g0 = hs.rec32[i].g0;
             r.nrm = make_float4(g0.x, g0.y, g0.z, 0.f);
@@ -768,15 +782,21 @@ __global__ void signal_kernel(unsigned* flag, unsigned value) {
     __threadfence_system();
     asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(flag), "r"(value) : "memory");
 }
-__global__ void wait_kernel(const unsigned* flags, int n, unsigned value) {
+// A wait that runs out of time records which flag is missing (1 + its index, the smallest one wins) and returns: the
+// stream goes on, the CUDA context stays usable (a trap would poison it: every buffer and the scene of the waiting
+// process lost), and the host learns about it from rtc_wait_result.
+__global__ void wait_kernel(const unsigned* flags, int n, unsigned value, unsigned long long timeout_ns, unsigned* status) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
-    const long long t0 = clock64();
+    unsigned long long t0;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
     for (;;) {
         unsigned v;
         asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(flags + i) : "memory");
         if ((int)(v - value) >= 0) break;
-        if (clock64() - t0 > 4000000000LL) { asm volatile("trap;"); }   // ~2 s: a rank died; fail loudly instead of hanging the GPU
+        unsigned long long t1;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
+        if (t1 - t0 > timeout_ns) { atomicMin(status, (unsigned)i + 1u); break; }
         __nanosleep(200);
     }
 }
@@ -952,6 +972,16 @@ int rtc_context_create(const int* device_ids, int n_gpus, rtc_context** out_ctx)
         if (e == cudaSuccess) e = d.counters.ensure(1);
         if (e == cudaSuccess) e = d.work.ensure(8);
         if (e == cudaSuccess) e = cudaMemset(d.work.p, 0, 8 * sizeof(unsigned));
+        if (e == cudaSuccess) e = d.wait_status.ensure(1);
+        if (e == cudaSuccess) e = cudaMemset(d.wait_status.p, 0xff, sizeof(unsigned));
+        if (e == cudaSuccess && g > 0) {   // peer stores into the first GPU's frame (rtc_render_device on several GPUs)
+            int can = 0;
+            if (cudaDeviceCanAccessPeer(&can, d.dev, ctx->devs[0].dev) == cudaSuccess && can) {
+                cudaError_t pe = cudaDeviceEnablePeerAccess(ctx->devs[0].dev, 0);
+                if (pe == cudaSuccess || pe == cudaErrorPeerAccessAlreadyEnabled) d.peer_to_first = true;
+            }
+            cudaGetLastError();
+        }
         if (e != cudaSuccess) {
             std::string m = cudaGetErrorString(e);
             rtc_context_destroy(ctx);
@@ -959,6 +989,7 @@ int rtc_context_create(const int* device_ids, int n_gpus, rtc_context** out_ctx)
         }
     }
     cudaError_t e = cudaMallocHost((void**)&ctx->pinned_counters, sizeof(Counters) * n_gpus);
+    if (e == cudaSuccess) e = cudaMallocHost((void**)&ctx->pinned_status, sizeof(unsigned));
     if (e != cudaSuccess) {
         rtc_context_destroy(ctx);
         return fail(RTC_ERR_CUDA, std::string("rtc_context_create: ") + cudaGetErrorString(e));
@@ -974,7 +1005,7 @@ void rtc_context_destroy(rtc_context* ctx) {
         if (d.stream) cudaStreamSynchronize(d.stream);
         d.sph64.release(); d.pl64.release(); d.pl32.release(); d.us32.release(); d.gs32.release(); d.us_index.release(); d.gs_index.release(); d.gset.release(); d.plL.release(); d.usL.release(); d.lights64.release(); d.lights32.release(); d.bound64.release(); d.gbound.release(); d.gbound64.release(); d.sbound.release(); d.sbound64.release(); d.bound.release();
         d.sph_index.release(); d.pl_index.release(); d.rec64.release(); d.rec32.release(); d.srec.release();
-        d.rgb.release(); d.hit.release(); d.counters.release(); d.work.release(); d.order.release();
+        d.rgb.release(); d.hit.release(); d.counters.release(); d.work.release(); d.order.release(); d.wait_status.release();
         if (d.ev_k0) cudaEventDestroy(d.ev_k0);
         if (d.ev_k1) cudaEventDestroy(d.ev_k1);
         if (d.ev_c1) cudaEventDestroy(d.ev_c1);
@@ -988,6 +1019,8 @@ void rtc_context_destroy(rtc_context* ctx) {
     if (ctx->pinned_rgb) cudaFreeHost(ctx->pinned_rgb);
     if (ctx->pinned_hit) cudaFreeHost(ctx->pinned_hit);
     if (ctx->pinned_counters) cudaFreeHost(ctx->pinned_counters);
+    if (ctx->pinned_status) cudaFreeHost(ctx->pinned_status);
+    for (auto& r : ctx->registered) cudaHostUnregister(r.first);
     delete ctx->pool;
     delete ctx;
 }
@@ -1047,6 +1080,7 @@ int rtc_scene_upload_lights(rtc_context* ctx, const rtc_light* light, size_t n_l
         d.s64.n_lights = d.s32.n_lights = (int)n_lights;
         d.s64.lights = d.lights64.p; d.s32.lights = d.lights32.p;
         d.s32.rec = d.rec32.p;
+        d.s32.rec64 = d.rec64.p;
         d.s64.bound = d.bound64.p; d.s64.n_bound4 = (int)hs.bound64.size(); d.s64.bound_cmax = hs.bound64_cmax; d.s64.bound_rmax = hs.bound64_rmax;
         d.s64.gbound = d.gbound64.p; d.s64.gbound_cmax = hs.gbound64_cmax; d.s64.gbound_rmax = hs.gbound64_rmax;
         d.s32.gbound = d.gbound.p; d.s32.gbound_cmax = hs.gbound_cmax; d.s32.gbound_rmax = hs.gbound_rmax;
@@ -1077,6 +1111,53 @@ int rtc_render_device(rtc_context* ctx, const rtc_camera* cam, const rtc_render_
     if (rc != RTC_OK) return rc;
     if (!ctx->has_scene) return fail(RTC_ERR_NO_SCENE, "rtc_render_device before rtc_scene_upload");
     DeviceState& d = ctx->devs[0];
+    const int G = (int)ctx->devs.size();
+    if (G > 1) {
+        // Several GPUs in one process: GPU g renders tiles g, g + G, ... and its kernel stores the pixels straight into the
+        // frame on the first GPU through peer access (NVLink) while it is still tracing; events order the launches after
+        // what `stream` held before and let `stream` continue when every GPU is done.  No staging buffer, no collective.
+        for (int g = 1; g < G; ++g)
+            if (!ctx->devs[g].peer_to_first)
+                return fail(RTC_ERR_UNSUPPORTED, "rtc_render_device: GPU " + std::to_string(ctx->devs[g].dev) + " has no peer access to GPU " + std::to_string(d.dev));
+        const int tile_rows = opts->tile_rows > 0 ? opts->tile_rows : 16;
+        CUDA_TRY(cudaSetDevice(d.dev));
+        cudaStream_t s0 = stream ? (cudaStream_t)stream : d.stream;
+        auto t0 = std::chrono::steady_clock::now();
+        const bool counters = !stream && stats;
+        CUDA_TRY(cudaEventRecord(d.ev_band[0], s0));                    // "everything enqueued before this call"
+        for (int g = G - 1; g >= 0; --g) {                              // the first GPU last: its stream then waits for the others
+            DeviceState& dg = ctx->devs[g];
+            CUDA_TRY(cudaSetDevice(dg.dev));
+            cudaStream_t sg = g == 0 ? s0 : dg.stream;
+            if (g > 0) CUDA_TRY(cudaStreamWaitEvent(sg, d.ev_band[0], 0));
+            if (counters) CUDA_TRY(cudaMemsetAsync(dg.counters.p, 0, sizeof(Counters), sg));
+            CamParams cp = make_cam(cam, opts, g, G, tile_rows);
+            cp.dst_full = 1;
+            if (g == 0) CUDA_TRY(cudaEventRecord(d.ev_k0, s0));
+            rc = launch_on(dg, cp, opts->precision, opts->flags | (g > 0 ? RTC_OPT_LINEAR_TILE_ORDER : 0), d_out_rgb, d_out_hit_mask,
+                           counters ? dg.counters.p : nullptr, sg);
+            if (rc != RTC_OK) return rc;
+            if (counters) CUDA_TRY(cudaMemcpyAsync(&ctx->pinned_counters[g], dg.counters.p, sizeof(Counters), cudaMemcpyDeviceToHost, sg));
+            if (g > 0) CUDA_TRY(cudaEventRecord(dg.ev_k1, sg));
+        }
+        for (int g = 1; g < G; ++g) CUDA_TRY(cudaStreamWaitEvent(s0, ctx->devs[g].ev_k1, 0));
+        CUDA_TRY(cudaEventRecord(d.ev_k1, s0));
+        if (stream) return RTC_OK;
+        CUDA_TRY(cudaStreamSynchronize(s0));
+        if (stats) {
+            std::memset(stats, 0, sizeof *stats);
+            float ms = 0.f;
+            CUDA_TRY(cudaEventElapsedTime(&ms, d.ev_k0, d.ev_k1));
+            for (int g = 0; g < G; ++g) {
+                const Counters& c = ctx->pinned_counters[g];
+                stats->rays += c.rays; stats->primary_hits += c.primary_hits; stats->shaded_hits += c.shaded_hits; stats->shadow_rays += c.shadow_rays;
+            }
+            stats->kernel_launches = (uint64_t)G;
+            stats->kernel_ms = ms;
+            stats->total_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+        }
+        return RTC_OK;
+    }
     CUDA_TRY(cudaSetDevice(d.dev));
     CamParams cp = make_cam(cam, opts, opts->shard_index, opts->shard_count, opts->tile_rows);
     cp.dst_full = (opts->flags & RTC_OPT_DST_FULL_FRAME) ? 1 : 0;
@@ -1185,9 +1266,55 @@ int rtc_wait_device(rtc_context* ctx, const void* d_flags, int n, uint32_t value
     DeviceState& d = ctx->devs[0];
     CUDA_TRY(cudaSetDevice(d.dev));
     cudaStream_t st = stream ? (cudaStream_t)stream : d.stream;
-    wait_kernel<<<(n + 31) / 32, 32, 0, st>>>((const unsigned*)d_flags, n, value);
+    const unsigned long long timeout_ns = (unsigned long long)(ctx->wait_timeout_s * 1e9);
+    wait_kernel<<<(n + 31) / 32, 32, 0, st>>>((const unsigned*)d_flags, n, value, timeout_ns, d.wait_status.p);
     CUDA_TRY(cudaGetLastError());
     return RTC_OK;
+}
+
+int rtc_set_wait_timeout(rtc_context* ctx, double seconds) {
+    if (!ctx || !(seconds > 0.0) || seconds > 86400.0) return fail(RTC_ERR_INVALID_ARG, "rtc_set_wait_timeout: bad argument");
+    ctx->wait_timeout_s = seconds;
+    return RTC_OK;
+}
+
+int rtc_wait_result(rtc_context* ctx, void* stream, int* first_missing) {
+    if (!ctx) return fail(RTC_ERR_INVALID_ARG, "rtc_wait_result: null context");
+    DeviceState& d = ctx->devs[0];
+    CUDA_TRY(cudaSetDevice(d.dev));
+    cudaStream_t st = stream ? (cudaStream_t)stream : d.stream;
+    CUDA_TRY(cudaMemcpyAsync(ctx->pinned_status, d.wait_status.p, sizeof(unsigned), cudaMemcpyDeviceToHost, st));
+    CUDA_TRY(cudaStreamSynchronize(st));
+    const unsigned v = *ctx->pinned_status;
+    if (first_missing) *first_missing = v == 0xffffffffu ? -1 : (int)v - 1;
+    if (v == 0xffffffffu) return RTC_OK;
+    CUDA_TRY(cudaMemsetAsync(d.wait_status.p, 0xff, sizeof(unsigned), st));
+    CUDA_TRY(cudaStreamSynchronize(st));
+    return fail(RTC_ERR_TIMEOUT, "rtc_wait_device: flag " + std::to_string(v - 1) + " did not arrive within " + std::to_string(ctx->wait_timeout_s) + " s");
+}
+
+int rtc_register_host_buffer(rtc_context* ctx, void* ptr, size_t bytes) {
+    if (!ctx || !ptr || bytes == 0) return fail(RTC_ERR_INVALID_ARG, "rtc_register_host_buffer: bad argument");
+    for (auto& r : ctx->registered)
+        if (r.first == (unsigned char*)ptr) return r.second >= bytes ? RTC_OK : fail(RTC_ERR_INVALID_ARG, "rtc_register_host_buffer: already registered with a smaller size");
+    CUDA_TRY(cudaSetDevice(ctx->devs[0].dev));
+    cudaError_t e = cudaHostRegister(ptr, bytes, cudaHostRegisterPortable);
+    if (e == cudaErrorHostMemoryAlreadyRegistered) { cudaGetLastError(); return fail(RTC_ERR_INVALID_ARG, "rtc_register_host_buffer: the range overlaps memory another owner registered"); }
+    if (e != cudaSuccess) { cudaGetLastError(); return fail(RTC_ERR_CUDA, std::string("cudaHostRegister: ") + cudaGetErrorString(e)); }
+    ctx->registered.emplace_back((unsigned char*)ptr, bytes);
+    return RTC_OK;
+}
+
+int rtc_unregister_host_buffer(rtc_context* ctx, void* ptr) {
+    if (!ctx || !ptr) return fail(RTC_ERR_INVALID_ARG, "rtc_unregister_host_buffer: bad argument");
+    for (size_t i = 0; i < ctx->registered.size(); ++i)
+        if (ctx->registered[i].first == (unsigned char*)ptr) {
+            for (DeviceState& d : ctx->devs) { cudaSetDevice(d.dev); cudaStreamSynchronize(d.stream); cudaStreamSynchronize(d.copy_stream); }
+            CUDA_TRY(cudaHostUnregister(ptr));
+            ctx->registered.erase(ctx->registered.begin() + (long)i);
+            return RTC_OK;
+        }
+    return fail(RTC_ERR_INVALID_ARG, "rtc_unregister_host_buffer: not a registered buffer");
 }
 
 int rtc_scene_selfcheck(const rtc_light* lights, size_t n_lights, const rtc_shape* shapes, size_t n_shapes, rtc_selfcheck* out) {
@@ -1310,6 +1437,111 @@ extern "C" int rtc_download_frame(rtc_context* ctx, const void* d_frame, int dev
     return RTC_OK;
 }
 
+namespace {
+
+bool is_registered(const rtc_context* ctx, const void* p, size_t bytes) {
+    const unsigned char* q = (const unsigned char*)p;
+    for (const auto& r : ctx->registered)
+        if (q >= r.first && q + bytes <= r.first + r.second) return true;
+    return false;
+}
+
+// One shard of the frame (interleaved row tiles: tile k -> shard k % shard_count) on GPU `d`, delivered into the caller's
+// FULL host frame `user` at its frame rows — the unit of work of one rank process (one process per GPU, frame in shared
+// host memory) and of one GPU of a several-GPU context.  The shard is rendered into a compact device buffer by one launch.
+//   direct : the kernel writes out_format; pitched 2-D DMA copies place the tiles at their frame rows in the (registered)
+//            caller buffer — no staging, no host pass; the last, shorter tile of the frame goes by a 1-D copy
+//   staged : D2H of the compact buffer into pinned staging (at row `stage_row0`) in up to four chunks of whole tiles; the
+//            tiles of chunk c are placed (and, f32 -> f64, widened) by the host while chunk c+1 crosses PCIe — by `pool`,
+//            or by the calling thread alone when pool is null (the GPUs of a several-GPU context deliver side by side)
+int render_shard(rtc_context* ctx, DeviceState& d, const rtc_camera* cam, const rtc_render_opts* opts, int dev_fmt, bool direct,
+                 int shard_index, int shard_count, int tile_rows, unsigned char* user, uint8_t* out_hit_mask, size_t stage_row0,
+                 HostPool* pool, bool want_counters, Counters* pinned_counter, rtc_stats& st) {
+    auto t0 = std::chrono::steady_clock::now();
+    CUDA_TRY(cudaSetDevice(d.dev));
+    rtc_render_opts dopts = *opts;
+    dopts.out_format = dev_fmt;
+    const size_t dev_elem = elem_size(dev_fmt), out_elem = elem_size(opts->out_format);
+    const size_t row_elems = (size_t)cam->hsize * 3, row_bytes = row_elems * dev_elem, hsize = cam->hsize;
+    CamParams cp = make_cam(cam, &dopts, shard_index, shard_count, tile_rows);
+    const int shard_rows = cp.shard_rows;
+    if (shard_rows <= 0) return RTC_OK;
+    const size_t shard_bytes = (size_t)shard_rows * row_bytes;
+    CUDA_TRY(d.rgb.ensure(shard_bytes));
+    if (out_hit_mask) CUDA_TRY(d.hit.ensure((size_t)shard_rows * hsize));
+    if (want_counters) CUDA_TRY(cudaMemsetAsync(d.counters.p, 0, sizeof(Counters), d.stream));
+    CUDA_TRY(cudaEventRecord(d.ev_k0, d.stream));
+    int rc = launch_on(d, cp, opts->precision, opts->flags, d.rgb.p, out_hit_mask ? d.hit.p : nullptr, want_counters ? d.counters.p : nullptr, d.stream);
+    if (rc != RTC_OK) return rc;
+    CUDA_TRY(cudaEventRecord(d.ev_k1, d.stream));
+    if (want_counters) CUDA_TRY(cudaMemcpyAsync(pinned_counter, d.counters.p, sizeof(Counters), cudaMemcpyDeviceToHost, d.stream));
+    CUDA_TRY(cudaStreamWaitEvent(d.copy_stream, d.ev_k1, 0));
+    const int n_tiles = (shard_rows + tile_rows - 1) / tile_rows;
+    double deliver_ms = 0.0;
+    unsigned char* stage_hit = ctx->pinned_hit ? ctx->pinned_hit + stage_row0 * hsize : nullptr;
+    if (direct) {
+        const int n_full = shard_rows / tile_rows;                       // only the frame's last tile can be short
+        const size_t tile_bytes = (size_t)tile_rows * row_bytes;
+        unsigned char* dst0 = user + (size_t)shard_index * tile_bytes;   // frame row of the shard's tile 0
+        if (n_full > 0)
+            CUDA_TRY(cudaMemcpy2DAsync(dst0, tile_bytes * (size_t)shard_count, d.rgb.p, tile_bytes, tile_bytes, (size_t)n_full, cudaMemcpyDeviceToHost, d.copy_stream));
+        if (n_full < n_tiles) {
+            const int r0 = n_full * tile_rows;
+            const size_t fr = (size_t)shard_row_to_frame_row(r0, tile_rows, shard_index, shard_count);
+            CUDA_TRY(cudaMemcpyAsync(user + fr * row_bytes, d.rgb.p + (size_t)r0 * row_bytes, (size_t)(shard_rows - r0) * row_bytes, cudaMemcpyDeviceToHost, d.copy_stream));
+        }
+        if (out_hit_mask) CUDA_TRY(cudaMemcpyAsync(stage_hit, d.hit.p, (size_t)shard_rows * hsize, cudaMemcpyDeviceToHost, d.copy_stream));
+        CUDA_TRY(cudaStreamSynchronize(d.copy_stream));
+        if (out_hit_mask)
+            for (int t = 0; t < n_tiles; ++t) {
+                const int r0 = t * tile_rows, r1 = std::min(shard_rows, r0 + tile_rows);
+                std::memcpy(out_hit_mask + (size_t)shard_row_to_frame_row(r0, tile_rows, shard_index, shard_count) * hsize, stage_hit + (size_t)r0 * hsize, (size_t)(r1 - r0) * hsize);
+            }
+    } else {
+        unsigned char* staged = ctx->pinned_rgb + stage_row0 * row_bytes;
+        const int n_chunks = std::max(1, std::min(n_tiles, shard_bytes >= (4u << 20) ? 4 : 1));
+        int chunk_t0[5];
+        for (int c = 0; c <= n_chunks; ++c) chunk_t0[c] = (int)((long long)n_tiles * c / n_chunks);
+        for (int c = 0; c < n_chunks; ++c) {
+            const int r0 = chunk_t0[c] * tile_rows, r1 = std::min(shard_rows, chunk_t0[c + 1] * tile_rows);
+            CUDA_TRY(cudaMemcpyAsync(staged + (size_t)r0 * row_bytes, d.rgb.p + (size_t)r0 * row_bytes, (size_t)(r1 - r0) * row_bytes, cudaMemcpyDeviceToHost, d.copy_stream));
+            if (out_hit_mask)
+                CUDA_TRY(cudaMemcpyAsync(stage_hit + (size_t)r0 * hsize, d.hit.p + (size_t)r0 * hsize, (size_t)(r1 - r0) * hsize, cudaMemcpyDeviceToHost, d.copy_stream));
+            CUDA_TRY(cudaEventRecord(d.ev_copy[c], d.copy_stream));
+        }
+        const bool widen = dev_elem == 4 && out_elem == 8;
+        for (int c = 0; c < n_chunks; ++c) {
+            CUDA_TRY(cudaEventSynchronize(d.ev_copy[c]));
+            auto h0 = std::chrono::steady_clock::now();
+            const int t0c = chunk_t0[c];
+            auto task = [=](int i) {   // one tile: compact rows [r0, r1) -> their frame rows (contiguous in both)
+                const int r0 = (t0c + i) * tile_rows, r1 = std::min(shard_rows, r0 + tile_rows);
+                const size_t fr = (size_t)shard_row_to_frame_row(r0, tile_rows, shard_index, shard_count);
+                const size_t n = (size_t)(r1 - r0) * row_elems;
+                if (widen) rtc_host_widen_f32_f64(reinterpret_cast<double*>(user) + fr * row_elems, reinterpret_cast<const float*>(staged) + (size_t)r0 * row_elems, n);
+                else std::memcpy(user + fr * row_elems * out_elem, staged + (size_t)r0 * row_bytes, n * out_elem);
+                if (out_hit_mask) std::memcpy(out_hit_mask + fr * hsize, stage_hit + (size_t)r0 * hsize, (size_t)(r1 - r0) * hsize);
+            };
+            const int n_c = chunk_t0[c + 1] - t0c;
+            if (pool && n_c > 1) pool->parallel_for(n_c, task);
+            else for (int i = 0; i < n_c; ++i) task(i);
+            deliver_ms += std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - h0).count();
+        }
+    }
+    CUDA_TRY(cudaStreamSynchronize(d.stream));
+    float k_ms = 0.f;
+    CUDA_TRY(cudaEventElapsedTime(&k_ms, d.ev_k0, d.ev_k1));
+    if (want_counters) { st.rays = pinned_counter->rays; st.primary_hits = pinned_counter->primary_hits; st.shaded_hits = pinned_counter->shaded_hits; st.shadow_rays = pinned_counter->shadow_rays; }
+    st.kernel_launches = 1;
+    st.kernel_ms = k_ms;
+    st.total_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+    st.d2h_ms = st.total_ms - k_ms;
+    st.gather_ms = deliver_ms;
+    return RTC_OK;
+}
+
+}  // namespace
+
 extern "C" int rtc_render(rtc_context* ctx, const rtc_camera* cam, const rtc_render_opts* opts, void* out_rgb,
                           uint8_t* out_hit_mask, rtc_stats* stats) {
     if (!ctx || !out_rgb) return fail(RTC_ERR_INVALID_ARG, "rtc_render: null argument");
@@ -1318,16 +1550,28 @@ extern "C" int rtc_render(rtc_context* ctx, const rtc_camera* cam, const rtc_ren
     if (!ctx->has_scene) return fail(RTC_ERR_NO_SCENE, "rtc_render before rtc_scene_upload");
     auto t0 = std::chrono::steady_clock::now();
     const int G = (int)ctx->devs.size();
-    // Fast mode computes in f32: an F64_RGB (Canvas.pixels) request is produced as f32 on the device,
-    // crosses PCIe as f32 and is widened on the host (exact), halving the bytes of the dominant copy.
-    const int dev_fmt = (opts->precision == RTC_PRECISION_F32_FAST && opts->out_format == RTC_OUT_F64_RGB) ? RTC_OUT_F32_RGB : opts->out_format;
-    const size_t dev_elem = elem_size(dev_fmt), out_elem = elem_size(opts->out_format);
+    const size_t out_elem = elem_size(opts->out_format);
     const size_t row_elems = (size_t)cam->hsize * 3;
+    const size_t mask_bytes = (size_t)cam->hsize * cam->vsize;
+    const bool sharded = G > 1 || opts->shard_count > 1;
+    // Delivery.  A registered caller buffer (rtc_register_host_buffer) takes finished rows by DMA in out_format: no staging,
+    // no host pass.  The one case where staging wins: a whole fast-mode frame on ONE GPU into an F64_RGB Canvas crosses
+    // PCIe as f32 (99.5 MB instead of 199 MB at 4K over the one link) and is widened by the host threads (exact).
+    const bool registered = is_registered(ctx, out_rgb, row_elems * cam->vsize * out_elem);
+    if ((opts->flags & RTC_OPT_DELIVER_DIRECT) && !registered)
+        return fail(RTC_ERR_INVALID_ARG, "rtc_render: RTC_OPT_DELIVER_DIRECT needs a buffer registered with rtc_register_host_buffer");
+    const bool f32_wins = !sharded && opts->precision == RTC_PRECISION_F32_FAST && opts->out_format == RTC_OUT_F64_RGB;
+    const bool direct = registered && !(opts->flags & RTC_OPT_DELIVER_STAGED) && ((opts->flags & RTC_OPT_DELIVER_DIRECT) || !f32_wins);
+    // Staged fast mode computes in f32: an F64_RGB (Canvas.pixels) request is produced as f32 on the device,
+    // crosses PCIe as f32 and is widened on the host (exact), halving the bytes of the dominant copy.
+    const int dev_fmt = (!direct && opts->precision == RTC_PRECISION_F32_FAST && opts->out_format == RTC_OUT_F64_RGB) ? RTC_OUT_F32_RGB : opts->out_format;
+    const size_t dev_elem = elem_size(dev_fmt);
     const size_t row_bytes = row_elems * dev_elem;            // device / staging row
     const size_t frame_bytes = row_bytes * cam->vsize;
-    const size_t mask_bytes = (size_t)cam->hsize * cam->vsize;
-    rc = ensure_pinned(&ctx->pinned_rgb, &ctx->pinned_rgb_cap, frame_bytes);
-    if (rc != RTC_OK) return rc;
+    if (!direct) {
+        rc = ensure_pinned(&ctx->pinned_rgb, &ctx->pinned_rgb_cap, frame_bytes);
+        if (rc != RTC_OK) return rc;
+    }
     if (out_hit_mask) {
         rc = ensure_pinned(&ctx->pinned_hit, &ctx->pinned_hit_cap, mask_bytes);
         if (rc != RTC_OK) return rc;
@@ -1342,73 +1586,13 @@ extern "C" int rtc_render(rtc_context* ctx, const rtc_camera* cam, const rtc_ren
 
     if (G == 1 && opts->shard_count > 1) {
         // One shard of the frame, one process per GPU (torchrun style): out_rgb is the FULL frame — typically memory the
-        // rank processes share — and this call fills in the rows of its shard only (tile k -> shard k % shard_count).
-        // Every GPU delivers its rows over its own PCIe link and its own host threads: no gather step, no collective.
-        // The shard is rendered into a compact device buffer by one launch; its D2H runs in up to four chunks of whole
-        // tiles and the host places (and, in fast mode, widens) the tiles of chunk c while chunk c+1 crosses PCIe.
-        DeviceState& d = ctx->devs[0];
-        CUDA_TRY(cudaSetDevice(d.dev));
+        // rank processes share — and this call fills in the rows of its shard only.  Every GPU delivers its rows over its
+        // own PCIe link (and, staged, by its own host threads): no gather step, no collective.
         const int tile_rows = opts->tile_rows > 0 ? opts->tile_rows : 16;
-        CamParams cp = make_cam(cam, &dopts, opts->shard_index, opts->shard_count, tile_rows);
-        const int shard_rows = cp.shard_rows;
-        if (shard_rows <= 0) { if (stats) *stats = st; return RTC_OK; }
-        const size_t shard_bytes = (size_t)shard_rows * row_bytes;
-        CUDA_TRY(d.rgb.ensure(shard_bytes));
-        if (out_hit_mask) CUDA_TRY(d.hit.ensure((size_t)shard_rows * cam->hsize));
-        CUDA_TRY(cudaMemsetAsync(d.counters.p, 0, sizeof(Counters), d.stream));
-        CUDA_TRY(cudaEventRecord(d.ev_k0, d.stream));
-        rc = launch_on(d, cp, opts->precision, opts->flags, d.rgb.p, out_hit_mask ? d.hit.p : nullptr, stats ? d.counters.p : nullptr, d.stream);
+        rc = render_shard(ctx, ctx->devs[0], cam, opts, dev_fmt, direct, opts->shard_index, opts->shard_count, tile_rows, user, out_hit_mask, 0,
+                          ctx->pool, stats != nullptr, &ctx->pinned_counters[0], st);
         if (rc != RTC_OK) return rc;
-        CUDA_TRY(cudaEventRecord(d.ev_k1, d.stream));
-        CUDA_TRY(cudaStreamWaitEvent(d.copy_stream, d.ev_k1, 0));
-        const int n_tiles = (shard_rows + tile_rows - 1) / tile_rows;
-        const int n_chunks = std::max(1, std::min(n_tiles, shard_bytes >= (4u << 20) ? 4 : 1));
-        int chunk_t0[5];
-        for (int c = 0; c <= n_chunks; ++c) chunk_t0[c] = (int)((long long)n_tiles * c / n_chunks);
-        for (int c = 0; c < n_chunks; ++c) {
-            const int r0 = chunk_t0[c] * tile_rows, r1 = std::min(shard_rows, chunk_t0[c + 1] * tile_rows);
-            CUDA_TRY(cudaMemcpyAsync(ctx->pinned_rgb + (size_t)r0 * row_bytes, d.rgb.p + (size_t)r0 * row_bytes, (size_t)(r1 - r0) * row_bytes,
-                                     cudaMemcpyDeviceToHost, d.copy_stream));
-            if (out_hit_mask)
-                CUDA_TRY(cudaMemcpyAsync(ctx->pinned_hit + (size_t)r0 * cam->hsize, d.hit.p + (size_t)r0 * cam->hsize, (size_t)(r1 - r0) * cam->hsize,
-                                         cudaMemcpyDeviceToHost, d.copy_stream));
-            CUDA_TRY(cudaEventRecord(d.ev_copy[c], d.copy_stream));
-        }
-        if (stats) CUDA_TRY(cudaMemcpyAsync(&ctx->pinned_counters[0], d.counters.p, sizeof(Counters), cudaMemcpyDeviceToHost, d.stream));
-        const bool widen = dev_elem == 4 && out_elem == 8;
-        const int shard_index = opts->shard_index, shard_count = opts->shard_count;
-        const unsigned char* staged = ctx->pinned_rgb;
-        const unsigned char* staged_hit = ctx->pinned_hit;
-        const size_t hsize = cam->hsize;
-        double deliver_ms = 0.0;
-        for (int c = 0; c < n_chunks; ++c) {
-            CUDA_TRY(cudaEventSynchronize(d.ev_copy[c]));
-            auto h0 = std::chrono::steady_clock::now();
-            const int t0c = chunk_t0[c];
-            auto task = [=](int i) {   // one tile: compact rows [r0, r1) -> their frame rows (contiguous in both)
-                const int r0 = (t0c + i) * tile_rows, r1 = std::min(shard_rows, r0 + tile_rows);
-                const size_t fr = (size_t)shard_row_to_frame_row(r0, tile_rows, shard_index, shard_count);
-                const size_t n = (size_t)(r1 - r0) * row_elems;
-                if (widen) rtc_host_widen_f32_f64(reinterpret_cast<double*>(user) + fr * row_elems, reinterpret_cast<const float*>(staged) + (size_t)r0 * row_elems, n);
-                else std::memcpy(user + fr * row_elems * out_elem, staged + (size_t)r0 * row_bytes, n * out_elem);
-                if (out_hit_mask) std::memcpy(out_hit_mask + fr * hsize, staged_hit + (size_t)r0 * hsize, (size_t)(r1 - r0) * hsize);
-            };
-            const int n_c = chunk_t0[c + 1] - t0c;
-            if (n_c == 1) task(0); else if (n_c > 1) ctx->pool->parallel_for(n_c, task);
-            deliver_ms += std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - h0).count();
-        }
-        CUDA_TRY(cudaStreamSynchronize(d.stream));
-        float k_ms = 0.f;
-        CUDA_TRY(cudaEventElapsedTime(&k_ms, d.ev_k0, d.ev_k1));
-        if (stats) {
-            const Counters& c = ctx->pinned_counters[0];
-            st.rays = c.rays; st.primary_hits = c.primary_hits; st.shaded_hits = c.shaded_hits; st.shadow_rays = c.shadow_rays;
-        }
-        st.kernel_launches = 1;
-        st.kernel_ms = k_ms;
         st.total_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
-        st.d2h_ms = st.total_ms - k_ms;
-        st.gather_ms = deliver_ms;
         if (stats) *stats = st;
         return RTC_OK;
     }
@@ -1416,7 +1600,7 @@ extern "C" int rtc_render(rtc_context* ctx, const rtc_camera* cam, const rtc_ren
     if (G == 1) {
         // One GPU: the frame is rendered as up to 8 contiguous row bands (one launch each, rows
         // [row0, row0 + rows) written at their frame positions).  Band b's D2H runs on the copy stream
-        // while band b+1 renders, and the host delivers band b while band b+1 crosses PCIe.
+        // while band b+1 renders, and (staged) the host delivers band b while band b+1 crosses PCIe.
         //  * fast mode is copy- and delivery-bound (99.5 MB at ~56 GB/s and a ~1.8 ms host widening against a
         //    1.25 ms kernel): eight equal bands keep all three stages busy (measured 2.5 ms; small-large-small
         //    bands 3.2 ms, because a large band is delivered only after its whole copy);
@@ -1434,10 +1618,6 @@ extern "C" int rtc_render(rtc_context* ctx, const rtc_camera* cam, const rtc_ren
             else if (kernel_bound) { plan = kPlanF64; n_plan = 5; plan_sum = 16; }
             else { plan = kPlanEq8; n_plan = 8; plan_sum = 8; }
         } else if (frame_bytes >= (4u << 20)) { plan = kPlanMid; n_plan = 3; plan_sum = 4; }
-        if (const char* env = std::getenv("RTC_B200_BANDS")) {   // experiments: N equal bands
-            static int eq[8] = {1, 1, 1, 1, 1, 1, 1, 1};
-            plan = eq; n_plan = std::max(1, std::min(8, std::atoi(env))); plan_sum = n_plan;
-        }
         int band_r0[9];
         int n_bands = 0;
         {
@@ -1462,7 +1642,8 @@ extern "C" int rtc_render(rtc_context* ctx, const rtc_camera* cam, const rtc_ren
             if (rc != RTC_OK) return rc;
             CUDA_TRY(cudaEventRecord(d.ev_band[b], d.stream));
             CUDA_TRY(cudaStreamWaitEvent(d.copy_stream, d.ev_band[b], 0));
-            CUDA_TRY(cudaMemcpyAsync(ctx->pinned_rgb + (size_t)r0 * row_bytes, d.rgb.p + (size_t)r0 * row_bytes, (size_t)(r1 - r0) * row_bytes,
+            // direct: the band goes straight to its rows of the caller's (registered) frame
+            CUDA_TRY(cudaMemcpyAsync((direct ? user : ctx->pinned_rgb) + (size_t)r0 * row_bytes, d.rgb.p + (size_t)r0 * row_bytes, (size_t)(r1 - r0) * row_bytes,
                                      cudaMemcpyDeviceToHost, d.copy_stream));
             if (out_hit_mask)
                 CUDA_TRY(cudaMemcpyAsync(ctx->pinned_hit + (size_t)r0 * cam->hsize, d.hit.p + (size_t)r0 * cam->hsize, (size_t)(r1 - r0) * cam->hsize,
@@ -1476,7 +1657,7 @@ extern "C" int rtc_render(rtc_context* ctx, const rtc_camera* cam, const rtc_ren
             const int r0 = band_r0[b], r1 = band_r0[b + 1];
             CUDA_TRY(cudaEventSynchronize(d.ev_copy[b]));
             auto h0 = std::chrono::steady_clock::now();
-            host_deliver(ctx, user + (size_t)r0 * row_elems * out_elem, ctx->pinned_rgb + (size_t)r0 * row_bytes, (size_t)(r1 - r0) * row_elems, dev_elem, out_elem);
+            if (!direct) host_deliver(ctx, user + (size_t)r0 * row_elems * out_elem, ctx->pinned_rgb + (size_t)r0 * row_bytes, (size_t)(r1 - r0) * row_elems, dev_elem, out_elem);
             if (out_hit_mask) std::memcpy(out_hit_mask + (size_t)r0 * cam->hsize, ctx->pinned_hit + (size_t)r0 * cam->hsize, (size_t)(r1 - r0) * cam->hsize);
             deliver_ms += std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - h0).count();
         }
@@ -1494,55 +1675,33 @@ extern "C" int rtc_render(rtc_context* ctx, const rtc_camera* cam, const rtc_ren
         return RTC_OK;
     }
 
-    // Several GPUs in one process: interleaved row tiles, tile k -> GPU k % G.  Every GPU renders its
-    // tiles into a compact buffer and copies each tile straight to its rows of the pinned frame over
-    // its own PCIe link.
+    // Several GPUs in ONE process (what a Rust camera.render(&world) on a multi-GPU box gets): interleaved row tiles, tile
+    // k -> GPU k % G.  One host thread per GPU runs that GPU's shard — launch, D2H over its own PCIe link, delivery into
+    // the caller's frame — side by side with the others: launches are concurrent, nothing waits for the slowest GPU
+    // before its own rows are delivered, and there is no gather (the shards' rows are disjoint).
     const int tile_rows = opts->tile_rows > 0 ? opts->tile_rows : 16;
+    std::vector<size_t> stage_row0(G, 0);
+    for (int g = 1; g < G; ++g) stage_row0[g] = stage_row0[g - 1] + (size_t)shard_num_rows((int)cam->vsize, tile_rows, g - 1, G);
+    std::vector<rtc_stats> gst(G);
+    std::vector<int> grc(G, RTC_OK);
+    std::vector<std::string> gerr(G);
+    for (auto& x : gst) std::memset(&x, 0, sizeof x);
+    auto job = [&](int g) {
+        grc[g] = render_shard(ctx, ctx->devs[g], cam, opts, dev_fmt, direct, g, G, tile_rows, user, out_hit_mask, stage_row0[g], nullptr,
+                              stats != nullptr, &ctx->pinned_counters[g], gst[g]);
+        if (grc[g] != RTC_OK) gerr[g] = g_err;   // g_err is thread_local: carry the worker's message to the caller
+    };
+    ctx->pool->parallel_for(G, job);
+    for (int g = 0; g < G; ++g)
+        if (grc[g] != RTC_OK) return fail(grc[g], "GPU " + std::to_string(ctx->devs[g].dev) + ": " + gerr[g]);
     for (int g = 0; g < G; ++g) {
-        DeviceState& d = ctx->devs[g];
-        CUDA_TRY(cudaSetDevice(d.dev));
-        CamParams cp = make_cam(cam, &dopts, g, G, tile_rows);
-        CUDA_TRY(d.rgb.ensure((size_t)cp.shard_rows * row_bytes));
-        if (out_hit_mask) CUDA_TRY(d.hit.ensure((size_t)cp.shard_rows * cam->hsize));
-        CUDA_TRY(cudaMemsetAsync(d.counters.p, 0, sizeof(Counters), d.stream));
-        CUDA_TRY(cudaEventRecord(d.ev_k0, d.stream));
-        rc = launch_on(d, cp, opts->precision, opts->flags, d.rgb.p, out_hit_mask ? d.hit.p : nullptr, d.counters.p, d.stream);
-        if (rc != RTC_OK) return rc;
-        CUDA_TRY(cudaEventRecord(d.ev_k1, d.stream));
-        int n_tiles = ((int)cam->vsize + tile_rows - 1) / tile_rows;
-        int compact_row = 0;
-        for (int t = g; t < n_tiles; t += G) {
-            int r0 = t * tile_rows, r1 = std::min((int)cam->vsize, r0 + tile_rows);
-            CUDA_TRY(cudaMemcpyAsync(ctx->pinned_rgb + (size_t)r0 * row_bytes, d.rgb.p + (size_t)compact_row * row_bytes,
-                                     (size_t)(r1 - r0) * row_bytes, cudaMemcpyDeviceToHost, d.stream));
-            if (out_hit_mask)
-                CUDA_TRY(cudaMemcpyAsync(ctx->pinned_hit + (size_t)r0 * cam->hsize, d.hit.p + (size_t)compact_row * cam->hsize,
-                                         (size_t)(r1 - r0) * cam->hsize, cudaMemcpyDeviceToHost, d.stream));
-            compact_row += r1 - r0;
-        }
-        CUDA_TRY(cudaMemcpyAsync(&ctx->pinned_counters[g], d.counters.p, sizeof(Counters), cudaMemcpyDeviceToHost, d.stream));
-        CUDA_TRY(cudaEventRecord(d.ev_c1, d.stream));
+        st.kernel_ms = std::max(st.kernel_ms, gst[g].kernel_ms);
+        st.d2h_ms = std::max(st.d2h_ms, gst[g].d2h_ms);
+        st.gather_ms = std::max(st.gather_ms, gst[g].gather_ms);
+        st.rays += gst[g].rays; st.primary_hits += gst[g].primary_hits; st.shaded_hits += gst[g].shaded_hits; st.shadow_rays += gst[g].shadow_rays;
+        st.kernel_launches += gst[g].kernel_launches;
     }
-    for (int g = 0; g < G; ++g) {
-        DeviceState& d = ctx->devs[g];
-        CUDA_TRY(cudaSetDevice(d.dev));
-        CUDA_TRY(cudaStreamSynchronize(d.stream));
-        float k_ms = 0.f, c_ms = 0.f;
-        CUDA_TRY(cudaEventElapsedTime(&k_ms, d.ev_k0, d.ev_k1));
-        CUDA_TRY(cudaEventElapsedTime(&c_ms, d.ev_k1, d.ev_c1));
-        st.kernel_ms = std::max(st.kernel_ms, (double)k_ms);
-        st.d2h_ms = std::max(st.d2h_ms, (double)c_ms);
-        const Counters& c = ctx->pinned_counters[g];
-        st.rays += c.rays; st.primary_hits += c.primary_hits; st.shaded_hits += c.shaded_hits; st.shadow_rays += c.shadow_rays;
-        st.kernel_launches += 1;
-    }
-    auto t1 = std::chrono::steady_clock::now();
-    host_deliver(ctx, user, ctx->pinned_rgb, row_elems * cam->vsize, dev_elem, out_elem);
-    if (out_hit_mask) std::memcpy(out_hit_mask, ctx->pinned_hit, mask_bytes);
-    auto t2 = std::chrono::steady_clock::now();
-    st.gather_ms = std::chrono::duration<double, std::milli>(t2 - t1).count();
-    st.d2h_ms += st.gather_ms;
-    st.total_ms = std::chrono::duration<double, std::milli>(t2 - t0).count();
+    st.total_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
     if (stats) *stats = st;
     return RTC_OK;
 }

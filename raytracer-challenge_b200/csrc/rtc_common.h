@@ -94,6 +94,7 @@ struct DevScene32 {
     const float4* gsph;        // [n_gsph][3]
     const int32_t* gs_index;
     const ShadeRec32* rec;     // [n_shapes]
+    const ShadeRec64* rec64;   // [n_shapes] the parity kernel's records: big scenes (kRefine kernels) take the geometry of a hit from them in f64
     const int32_t* gset;       // stream positions of the shapes with refractive_index != 1.0
     int n_gset;
     const float* plL;          // [n_planes] f(light) = n.light + w   (shadow test: f(0) f(1) <= 0)
