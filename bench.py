@@ -39,6 +39,13 @@ def make_camera(rtc):
         return rtc.scenes.synthetic_camera(W, H, samples=SAMPLES)
     return rtc.scenes.reflect_refract_camera(W, H, samples=SAMPLES)
 FLOP_PER_SHADED_HIT = 150
+# Executed-instruction figures of the timed kernel from the kept `ncu --set full` capture (a number measured under a
+# profiler is never a bench value: these describe the kernel, the timings above are CUDA events).  Refreshed per round.
+HW_PROFILE = {
+    "c3": {"source": "profiles/r01_ncu_f32_small_1p25ms.txt", "fma_pipe_pct": 43.7, "alu_pipe_pct": 37.9, "issue_active_pct": 84.7,
+           "lanes_per_instruction": 28.45, "registers": 74, "dram_bytes_per_launch": 64.56e6,
+           "dram_note": "63.3 MB written + 1.2 MB read per 4K launch; the frame is 99.5 MB, the rest was still in the 126 MB L2 when the kernel ended"},
+}
 FP32_FORMULA_PEAK = 148 * 128 * 2 * 1.965e9 / 1e12  # TFLOP/s, non-tensor, at clocks.max.sm
 
 
@@ -122,6 +129,36 @@ def oracle_sample(threads, target_seconds=12.0):
                       f" ({idx.size} px, {c.rays} rays, {c.seconds:.1f} s)"}
 
 
+def arm_config(N, TILE):
+    """`config` of the JSON line: the workload, identical in both arms (the driver compares the two dicts); what differs
+    between the arms — how each is timed, the frame's work counts — sits beside it (`timing_note`, `work`)."""
+    return {"workload": WORKLOAD, "n_gpus": N,
+            "parallelism": f"interleaved {TILE}-row tiles over {N} GPU(s)" if N > 1 else "one GPU, whole frame",
+            "l2": "inputs are KBs, the output frame is written once; a 256 MB buffer is rewritten between timed GPU iterations (outside the events)"}
+
+
+def oracle_frame_check(frames, step=32, n_random=2048):
+    """The oracle as the CHECKER of the frames the bench just timed (outside every timed region): a pixel lattice of the
+    workload's frame, f64 parity frame within 1e-9, f32 fast frame within 1/255 after the 8-bit rule on >= 99.9 %."""
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import numpy as np
+    import orc
+    import rtc_b200 as rtc
+    world, cam = make_scene(rtc), make_camera(rtc)
+    idx = orc.lattice(W, H, step=step, n_random=n_random)
+    want, want_hit, _ = orc.OracleWorld(world).render(cam, threads=os.cpu_count() or 1, pixels=idx, max_depth=DEPTH)
+    out = {"lattice": f"every {step}th pixel in x and y + {n_random} random pixels ({idx.size} px) against the CPU oracle"}
+    if "f64" in frames:
+        out["f64_max_abs_err"] = float(np.abs(frames["f64"].reshape(-1, 3)[idx] - want).max())
+        out["f64_within_1e-9"] = bool(out["f64_max_abs_err"] <= 1e-9)
+    if "f32" in frames:
+        q_got = orc.quantize_u8(frames["f32"].reshape(-1, 3)[idx].astype(np.float64)).astype(int)
+        q_want = orc.quantize_u8(want).astype(int)
+        out["f32_fraction_within_1_of_255"] = float((np.abs(q_got - q_want).max(axis=1) <= 1).mean())
+        out["f32_meets_99.9pct"] = bool(out["f32_fraction_within_1_of_255"] >= 0.999)
+    return out
+
+
 def run_reference(args):
     """--impl reference: the reference's own CPU implementation of the path.  The Rust crate cannot
     be built here (no cargo/rustc), so this is the oracle port — a line-by-line C++
@@ -143,7 +180,8 @@ def run_reference(args):
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": secs / max(1, args.steps) * 1e3,
         "ms_per_frame_extrapolated": sum(r["ms_per_frame_extrapolated"] for r in runs) / len(runs),
         "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": {"workload": WORKLOAD, "timing": "host wall clock around Camera::render_pixel over a pixel lattice"},
+        "config": arm_config(args.gpus, args.tile_rows),
+        "timing_note": "host wall clock around the oracle's Camera::render_pixel loop over the sample named in cpu_baseline.sample, all host threads",
         "cpu_baseline": {"value": value, "unit": "Mrays/s", "cores": cores, "kind": "port", "cpu": model,
                          "sample": runs[-1]["sample"]},
         "e2e": {"value": value, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
@@ -225,13 +263,15 @@ def run_gpu(args):
 
         def frame(self):
             """render this rank's interleaved row tiles, then the exchange step that completes rank 0's frame"""
-            r.render_device(camd, self.opts, self.dst(), None, stream)
             if N == 1:
+                r.render_device(camd, self.opts, self.dst(), None, stream)
                 return
+            self.sf.render(r, camd, self.opts, stream)   # p2p: the other ranks' kernels wait for 'previous frame consumed' and store their flag themselves
             if self.sf.mode == "nccl":
                 self.sf.exchange(lambda g, f: r.assemble_device(camd, self.opts, g.data_ptr(), self.sf.stride_rows, self.fmt, f.data_ptr(), stream))
             else:
                 self.sf.exchange(stream=stream)   # completion flags over NVLink: no collective (pixels are already in rank 0's frame)
+                self.sf.release(stream)           # rank 0 has no consumer here: the frame is free again at once
 
     def timed(fn, steps, warmup):
         for _ in range(warmup):
@@ -328,54 +368,106 @@ def run_gpu(args):
     k64, _, _ = timed(p64.kernel_only, n64, 3)
 
     # ---- e2e: the public API with HOST buffers: scene H2D + render + Canvas (f64) D2H every step ----
-    oe = rtc.Renderer.make_opts(precision=ffi.PRECISION_F32_FAST, rect=ffi.RECT_FULL, max_depth=DEPTH, out_format=ffi.OUT_F64_RGB)
+    oe = rtc.Renderer.make_opts(precision=ffi.PRECISION_F32_FAST, rect=ffi.RECT_FULL, max_depth=DEPTH, out_format=ffi.OUT_F64_RGB,
+                                shard_index=rank, shard_count=N, tile_rows=TILE)
+    oe64 = rtc.Renderer.make_opts(precision=ffi.PRECISION_F64_PARITY, rect=ffi.RECT_FULL, max_depth=DEPTH, out_format=ffi.OUT_F64_RGB,
+                                  shard_index=rank, shard_count=N, tile_rows=TILE)
     h2d = C.sizeof(ffi.RtcShape) * flat[2] + C.sizeof(ffi.RtcLight) + C.sizeof(ffi.RtcCamera)
     e2e_steps = max(1, min(args.steps, 10))
-    d2h = H * W * 3 * 8
-    if N == 1:
-        d2h = H * W * 3 * 4   # fast mode: the frame crosses PCIe as f32 and is widened to the f64 Canvas layout on the host
-        host = np.zeros((H, W, 3), dtype=np.float64)
+    # One Canvas frame (f64, Canvas.pixels' layout).  N = 1: a numpy array; N > 1: host memory all rank processes map (POSIX
+    # shared memory created by rank 0) — every rank's rtc_render fills in the rows of its shard over its own PCIe link; no
+    # gather, no collective on the data path.  The frame is registered (rtc_register_host_buffer), so the library may deliver
+    # by DMA straight into it; h2d / d2h bytes are per rank.
+    from rtc_b200.sharded import SharedHostFrame
+    shared = SharedHostFrame(W, H, rank, N)
+    host = shared.array
+    shared.register(r)
 
-        def e2e_step():
+    def e2e_run(opts, steps):
+        def step():
             r.upload_flat(*flat)
-            r.render(camd, oe, want_mask=False, out=host, want_stats=False)
-    else:
-        # N rank processes, one Canvas: the f64 frame lives in host memory all ranks map (POSIX shared memory created by
-        # rank 0) and every rank's rtc_render fills in the rows of its shard — kernel, D2H over its own PCIe link (f32) and
-        # widening by its own host threads.  No gather, no collective on the data path; h2d / d2h bytes are per rank.
-        from rtc_b200.sharded import SharedHostFrame
-        d2h = my_rows * W * 3 * 4
-        shared = SharedHostFrame(W, H, rank, N)
-        host = shared.array
-        oes = rtc.Renderer.make_opts(precision=ffi.PRECISION_F32_FAST, rect=ffi.RECT_FULL, max_depth=DEPTH, out_format=ffi.OUT_F64_RGB,
-                                     shard_index=rank, shard_count=N, tile_rows=TILE)
-
-        def e2e_step():
-            r.upload_flat(*flat)
-            r.render(camd, oes, want_mask=False, out=host, want_stats=False)
-    for _ in range(2):
-        e2e_step()
-    sync_all()
-    e2e_times = []
-    for _ in range(e2e_steps):
+            r.render(camd, opts, want_mask=False, out=host, want_stats=False)
+        for _ in range(2):
+            step()
         sync_all()
-        a = time.perf_counter()
-        e2e_step()
-        torch.cuda.synchronize()
-        e2e_times.append(time.perf_counter() - a)
-    e2e_t = torch.tensor(e2e_times, dtype=torch.float64, device=dev)
-    if N > 1:
-        dist.all_reduce(e2e_t, op=dist.ReduceOp.MAX)
-    e2e_ms = float(e2e_t.mean()) * 1e3
-    if N > 1:
-        sync_all()   # every rank's rows are in the shared frame: it must be the frame one GPU renders
-        if rank == 0:
-            ref = torch.empty((H, W, 3), dtype=torch.float32, device=dev)
-            r.render_device(camd, rtc.Renderer.make_opts(precision=ffi.PRECISION_F32_FAST, rect=ffi.RECT_FULL, max_depth=DEPTH,
-                                                         out_format=ffi.OUT_F32_RGB), ref.data_ptr(), None, None, None)
+        ts = []
+        for _ in range(steps):
+            sync_all()
+            a = time.perf_counter()
+            step()
             torch.cuda.synchronize()
-            frame_check["e2e_shared_host_frame_equals_1gpu_frame"] = bool(np.array_equal(host, ref.cpu().numpy().astype(np.float64)))
-            del ref
+            ts.append(time.perf_counter() - a)
+        t = torch.tensor(ts, dtype=torch.float64, device=dev)
+        if N > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)   # per step: the slowest rank
+        sync_all()
+        return t
+
+    def with_flags(o, fl):
+        o2 = ffi.RtcRenderOpts.from_buffer_copy(bytes(o))
+        o2.flags |= fl
+        return o2
+
+    # fast mode, the library's own delivery choice: N = 1 stages f32 over the one PCIe link and widens on the host (half the
+    # bytes); N > 1 DMA-writes f64 rows straight into the registered frame (no host pass)
+    e2e_t = e2e_run(oe, e2e_steps)
+    e2e_ms = float(e2e_t.mean()) * 1e3
+    direct_default = N > 1
+    d2h = my_rows * W * 3 * (8 if direct_default else 4)
+    e2e_frame_ok = None
+    if N > 1 and rank == 0:
+        ref = torch.empty((H, W, 3), dtype=torch.float32, device=dev)
+        r.render_device(camd, rtc.Renderer.make_opts(precision=ffi.PRECISION_F32_FAST, rect=ffi.RECT_FULL, max_depth=DEPTH,
+                                                     out_format=ffi.OUT_F32_RGB), ref.data_ptr(), None, None, None)
+        torch.cuda.synchronize()
+        ref_host = ref.cpu().numpy().astype(np.float64)
+        del ref
+        e2e_frame_ok = bool(np.array_equal(host, ref_host))
+    # the other delivery for comparison, and parity mode end to end (direct: 24 B/pixel cross PCIe either way)
+    alt_t = e2e_run(with_flags(oe, ffi.OPT_DELIVER_STAGED if direct_default else ffi.OPT_DELIVER_DIRECT), max(1, e2e_steps // 2))
+    e64_t = e2e_run(oe64, max(1, min(e2e_steps, 3)))
+    frames = {}
+    if N == 1:
+        frames["f64"] = host.copy()                       # the parity frame just delivered end to end
+        e2e_run(oe, 1)
+        frames["f32"] = host.copy()
+    # ---- the drop-in's own multi-GPU path: ONE process, rtc_context_create over the N GPUs, one rtc_render call ----
+    single = None
+    if N > 1:
+        sync_all()
+        if rank == 0:
+            try:
+                rs = rtc.Renderer(list(range(N)))
+                rs.upload_flat(*flat)
+                rs.register_host_buffer(host)
+                osp = rtc.Renderer.make_opts(precision=ffi.PRECISION_F32_FAST, rect=ffi.RECT_FULL, max_depth=DEPTH, out_format=ffi.OUT_F64_RGB, tile_rows=TILE)
+                ts = []
+                for i in range(2 + e2e_steps):
+                    host[0, 0, 0] = -1.0
+                    a = time.perf_counter()
+                    rs.upload_flat(*flat)
+                    rs.render(camd, osp, want_mask=False, out=host, want_stats=False)
+                    ts.append(time.perf_counter() - a)
+                ts = ts[2:]
+                single = {"ms_per_frame": sum(ts) / len(ts) * 1e3, "ms_per_frame_min": min(ts) * 1e3, "steps": len(ts),
+                          "value": rays / (sum(ts) / len(ts)) / 1e6, "unit": "Mrays/s", "frame_equals_1gpu_frame": bool(np.array_equal(host, ref_host)),
+                          "path": f"one process: rtc_context_create over {N} GPUs, rtc_scene_upload + one rtc_render into the registered f64 Canvas frame "
+                                  "(one host thread per GPU, interleaved row tiles, pitched DMA per GPU over its own PCIe link); the other rank "
+                                  "processes idle at a barrier meanwhile"}
+                dfr = torch.empty((H, W, 3), dtype=torch.float32, device=dev)
+                osd = rtc.Renderer.make_opts(precision=ffi.PRECISION_F32_FAST, rect=ffi.RECT_FULL, max_depth=DEPTH, out_format=ffi.OUT_F32_RGB, tile_rows=TILE)
+                kms = []
+                for i in range(3 + e2e_steps):
+                    st1 = ffi.RtcStats()
+                    rs.render_device(camd, osd, dfr.data_ptr(), None, None, st1)
+                    kms.append(st1.kernel_ms)
+                single["device_frame_ms"] = sum(kms[3:]) / len(kms[3:])
+                single["device_frame_equals_1gpu_frame"] = bool(np.array_equal(dfr.cpu().numpy().astype(np.float64), ref_host))
+                rs.unregister_host_buffer(host)
+                rs.close()
+            except Exception as ex:   # reported, never hidden
+                single = {"error": repr(ex)}
+        sync_all()
 
     if rank == 0:
         peaks = measured_peaks()
@@ -383,57 +475,80 @@ def run_gpu(args):
         pk64 = r.measure_peak_tflops(ffi.PRECISION_F64_PARITY)
         my_share = my_rows / H
         achieved = flops * my_share / (kernel_ms * 1e-3) / 1e12
+        hw = HW_PROFILE.get(WORKLOAD_KEY) if N == 1 else None
+        c4 = WORKLOAD_KEY == "c4"
         line = {
             "metric": "Mrays/s", "value": value, "unit": "Mrays/s", "n_gpus": N, "steps": args.steps, "warmup": max(3, args.warmup),
             "ms_per_step": ms_per_step, "ms_per_frame": ms_per_step, "higher_is_better": True, "scaling": "strong",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": WORKLOAD, "rays_per_frame": int(rays), "rays_per_frame_f32_kernel": int(counts32[0]),
-                       "shaded_hits_per_frame": int(shaded), "l2": "256 MB buffer rewritten between timed iterations (outside the events)",
-                       "parallelism": f"interleaved {TILE}-row tiles over {N} GPU(s)" +
-                                      (", render kernels store pixels straight into rank 0's frame over NVLink (CUDA IPC peer mapping); "
-                                       "completion = one peer-stored flag per rank, rank 0 waits on its stream (no collective)" if N > 1 else ""),
-                       "timing": "CUDA events per step on the launch stream, max over ranks"},
-            "roofline": {"bound": "fp32_non_tensor", "achieved": achieved, "peak": p32, "unit": "TFLOP/s", "frac": achieved / p32,
-                         "traffic": 64.56e6 if (N == 1 and WORKLOAD_KEY == "c3") else None,
-                         "traffic_note": "dram__bytes_read.sum + dram__bytes_write.sum of one 4K launch, ncu --set full capture "
-                                         "(profiles/r01_ncu_f32_small_1p25ms.txt): 63.3 MB written + 1.2 MB read; the frame is 99.5 MB, the "
-                                         "rest was still in the 126 MB L2 when the kernel ended; scene reads never reach HBM",
+            "config": arm_config(N, TILE),
+            "timing_note": "CUDA events per step on the launch stream, max over ranks" +
+                           ("; the render kernels store pixels straight into rank 0's frame over NVLink (CUDA IPC peer mapping); completion = one peer-stored "
+                            "flag per rank written by the render kernel's last block, rank 0 waits on its stream (no collective); back-pressure flag "
+                            "from rank 0's consumer" if N > 1 else ""),
+            "work": {"rays_per_frame": int(rays), "rays_per_frame_f32_kernel": int(counts32[0]), "shaded_hits_per_frame": int(shaded)},
+            # `frac` is the ALGORITHMIC fraction SURVEY.md 8(d) defines (flops of the brute-force loops / time / FFMA peak); `hw`
+            # is what the hardware counters of the kept ncu capture say for the same kernel (profiles/, from_profile).  On C4
+            # the hierarchy skips ~98 % of the algorithmic shape tests, so an algorithmic fraction says nothing there: null.
+            "roofline": {"bound": "fp32_non_tensor", "achieved": None if c4 else achieved, "peak": p32, "unit": "TFLOP/s",
+                         "frac": None if c4 else achieved / p32,
+                         "frac_note": "C4: the bounding-sphere hierarchy skips most algorithmic tests; see hw (executed-instruction utilisation)" if c4 else
+                                      "algorithmic flops (54 / ray x sphere, 13 / ray x plane, 150 / shaded hit) over the kernel time, against the FFMA peak",
+                         "hw": hw,
+                         "traffic": (hw or {}).get("dram_bytes_per_launch"), "traffic_source": "from_profile" if hw else None,
                          "peak_source": "FFMA micro-benchmark on this GPU in this run (rtc_measure_peak_tflops)",
-                         "peak_formula": FP32_FORMULA_PEAK, "frac_of_formula": achieved / FP32_FORMULA_PEAK,
+                         "peak_formula": FP32_FORMULA_PEAK, "frac_of_formula": None if c4 else achieved / FP32_FORMULA_PEAK,
                          "algorithmic_gflop_per_frame": flops / 1e9, "kernel_ms": kernel_ms,
-                         "kernel": "render_f32_kernel (general; the bounding-sphere filter skips most of the algorithmic shape tests, so frac can exceed 1)"
-                                   if WORKLOAD_KEY == "c4" else "render_f32_small_kernel",
+                         "kernel": "render_f32_kernel<kRefine> (f32 hierarchy + shading, f64 ray geometry)" if c4 else "render_f32_small_kernel",
                          "hbm_gbs_measured_peak": peaks.get("hbm_gbs"),
                          "hbm_gbs_achieved_frame_write": W * H * 12 * my_share / (kernel_ms * 1e-3) / 1e9},
             "f64": {"ms_per_frame": float(ms64.mean()), "mrays_per_s": rays / (float(ms64.mean()) * 1e-3) / 1e6,
                     "kernel_ms": float(k64.mean()), "tflops_algorithmic": flops * my_share / (float(k64.mean()) * 1e-3) / 1e12,
-                    "peak_dfma_tflops_measured": pk64},
+                    "peak_dfma_tflops_measured": pk64,
+                    "e2e": {"ms_per_frame": float(e64_t.mean()) * 1e3, "value": rays / float(e64_t.mean()) / 1e6, "unit": "Mrays/s",
+                            "d2h_bytes_per_step": int(my_rows * W * 3 * 8),
+                            "path": "rtc_scene_upload + rtc_render (f64 parity) delivered by DMA straight into the registered f64 Canvas frame"}},
             "e2e": {"value": rays / (e2e_ms * 1e-3) / 1e6, "unit": "Mrays/s", "ms_per_frame": e2e_ms, "h2d_bytes_per_step": int(h2d),
                     "d2h_bytes_per_step": int(d2h), "steps": e2e_steps,
                     "ms_per_frame_min": float(e2e_t.min()) * 1e3, "ms_per_frame_median": float(e2e_t.median()) * 1e3,
-                    "path": "rtc_scene_upload + rtc_render (f32 fast, F64_RGB Canvas layout) into a host buffer" if N == 1 else
-                            "every rank: rtc_scene_upload + rtc_render of its shard (interleaved row tiles) into ONE f64 Canvas frame in host memory shared by the rank "
-                            "processes — f32 over the rank's own PCIe link, widened by its own host threads; no gather; bytes are per rank; time = max over ranks"},
-            # kernels of this library inside the timed region, all ranks: rank 0 runs the tile scheduling pre-pass +
-            # the render kernel (+ the flag wait when N > 1); every other rank the render kernel + its flag store
-            "gpu_launches": args.steps * (2 if N == 1 else 3 + 2 * (N - 1)),
-            "gpu_launches_per_step": {"rank0": ["classify_tiles_small_kernel", "render_f32_small_kernel"] + (["wait_kernel"] if N > 1 else []),
-                                      "other_ranks": ["render_f32_small_kernel", "signal_kernel"] if N > 1 else []},
+                    "pcie_gbs_per_link": d2h / (e2e_ms * 1e-3) / 1e9,
+                    "path": "rtc_scene_upload + rtc_render (f32 fast, F64_RGB Canvas layout) into a registered host buffer: the frame crosses PCIe "
+                            "as f32 (half the bytes over the one link) and host threads widen it into the Canvas" if N == 1 else
+                            "every rank: rtc_scene_upload + rtc_render of its shard (interleaved row tiles) into ONE registered f64 Canvas frame in host memory "
+                            "shared by the rank processes — pitched DMA of f64 rows over the rank's own PCIe link, no staging, no host pass, no gather; "
+                            "bytes are per rank; time = max over ranks per step",
+                    "other_delivery": {"ms_per_frame": float(alt_t.mean()) * 1e3,
+                                       "path": "forced direct f64 DMA" if N == 1 else "staged: f32 over PCIe + widening by the rank's host threads (round 1's path)"}},
+            # kernels of this library inside the timed region, all ranks: rank 0 runs the tile scheduling pre-pass + the render
+            # kernel (+ the flag wait and the 'consumed' flag store when N > 1); every other rank ONE launch: its render kernel
+            # waits for the back-pressure flag and stores its completion flag itself
+            "gpu_launches": args.steps * (2 if N == 1 else 4 + (N - 1)),
+            "gpu_launches_per_step": {"rank0": ["classify_tiles_small_kernel", "render_f32_small_kernel"] + (["wait_kernel", "signal_kernel"] if N > 1 else []),
+                                      "other_ranks": ["render_f32_small_kernel"] if N > 1 else []},
             "clocks": clocks,
         }
+        if c4:
+            line["gpu_launches"] = args.steps * (1 if N == 1 else 3 + 3 * (N - 1))
+            line["gpu_launches_per_step"] = {"rank0": ["render_f32_kernel"] + (["wait_kernel", "signal_kernel"] if N > 1 else []),
+                                             "other_ranks": ["wait_kernel", "render_f32_kernel", "signal_kernel"] if N > 1 else []}
         line.update(extra)
+        if single is not None:
+            line["e2e_single_process"] = single
         if frame_check is not None:
+            if e2e_frame_ok is not None:
+                frame_check["e2e_shared_host_frame_equals_1gpu_frame"] = e2e_frame_ok
             line["frame_check"] = frame_check
+        if N == 1:
+            line["frame_check"] = oracle_frame_check(frames) if WORKLOAD_KEY != "c4" else oracle_frame_check(frames, step=64, n_random=512)
         if N == 1 and not args.no_cpu_baseline:
             model, cores = cpu_info()
             s = oracle_sample(cores, 12.0)
             line["cpu_baseline"] = {"value": s["mrays_per_s"], "unit": "Mrays/s", "cores": cores, "kind": "port", "cpu": model,
                                     "sample": s["sample"], "ms_per_frame_extrapolated": s["ms_per_frame_extrapolated"]}
         print(json.dumps(line), flush=True)
-    if N > 1:
-        del host
-        torch.cuda.synchronize()
-        shared.close()
+    del host
+    torch.cuda.synchronize()
+    shared.close()
     main.sf.close()
     p64.sf.close()
     if N > 1:

@@ -291,6 +291,18 @@ int rtc_wait_device(rtc_context* ctx, const void* d_flags, int n, uint32_t value
 int rtc_set_wait_timeout(rtc_context* ctx, double seconds);
 int rtc_wait_result(rtc_context* ctx, void* stream, int* first_missing);
 
+/* rtc_render_device with the flag protocol folded into the launch (one process per GPU, peer-store frame assembly):
+ * the render starts only once *d_wait_flag >= wait_value (NULL: at once) — the consumer has released the destination
+ * frame — and when the last pixel is out, done_value is release-stored to *d_done_flag at system scope (NULL: no
+ * store).  Both flags may be peer-mapped words of another GPU.  The small-scene fast kernel does both inside its one
+ * launch (every block polls the wait flag before its first store; the last block to retire stores the done flag after
+ * system-scope fences), so a rank's frame is a single kernel; the other kernels get the flag kernels of
+ * rtc_wait_device / rtc_signal_device enqueued around them.  A wait that times out is reported by rtc_wait_result.
+ * One-GPU contexts; `stream` is required (nothing is synchronised). */
+int rtc_render_device_synced(rtc_context* ctx, const rtc_camera* cam, const rtc_render_opts* opts, void* d_out_rgb,
+                             uint8_t* d_out_hit_mask, void* stream, const void* d_wait_flag, uint32_t wait_value,
+                             void* d_done_flag, uint32_t done_value);
+
 /* Canvas delivery for the device-buffer entry points: copies a finished frame (hsize*vsize pixels of
  * `dev_format`, on the context's first GPU) into the caller's HOST buffer of `out_format`, after everything
  * already enqueued on `stream` (NULL = the context's stream).  Row bands cross PCIe on the copy stream while

@@ -117,6 +117,13 @@ class Renderer:
             C.c_void_p(d_mask) if d_mask else None, C.c_void_p(stream) if stream else None,
             C.byref(stats) if stats is not None else None))
 
+    def render_device_synced(self, cam_desc, opts, d_rgb, stream, wait_flag=None, wait_value=0, done_flag=None, done_value=0, d_mask=None):
+        """rtc_render_device_synced: render ordered after *wait_flag >= wait_value, done_value release-stored to *done_flag
+        when the pixels are out (raw device pointers; peer-mapped words allowed)."""
+        ffi.check(self._lib.rtc_render_device_synced(
+            self._ctx, C.byref(cam_desc), C.byref(opts), C.c_void_p(d_rgb), C.c_void_p(d_mask) if d_mask else None, C.c_void_p(stream),
+            C.c_void_p(wait_flag) if wait_flag else None, wait_value, C.c_void_p(done_flag) if done_flag else None, done_value))
+
     def assemble_device(self, cam_desc, opts, d_gathered, shard_stride_rows, elem_kind, d_frame, stream=None):
         ffi.check(self._lib.rtc_assemble_device(
             self._ctx, C.byref(cam_desc), C.byref(opts), C.c_void_p(d_gathered), shard_stride_rows,
@@ -158,6 +165,24 @@ class Renderer:
 
     def wait_device(self, d_flags, n, value, stream=None):
         ffi.check(self._lib.rtc_wait_device(self._ctx, C.c_void_p(d_flags), n, value, C.c_void_p(stream) if stream else None))
+
+    def set_wait_timeout(self, seconds):
+        ffi.check(self._lib.rtc_set_wait_timeout(self._ctx, C.c_double(seconds)))
+
+    def wait_result(self, stream=None):
+        """rtc_wait_result: synchronises the stream; raises RtcError(RTC_ERR_TIMEOUT) naming the missing flag when an
+        earlier rtc_wait_device ran out of time."""
+        missing = C.c_int(-1)
+        ffi.check(self._lib.rtc_wait_result(self._ctx, C.c_void_p(stream) if stream else None, C.byref(missing)))
+
+    def register_host_buffer(self, array):
+        """rtc_register_host_buffer for a numpy array the caller keeps alive (a long-lived Canvas frame): rtc_render then
+        delivers into it by DMA, without staging or host threads."""
+        assert array.flags["C_CONTIGUOUS"]
+        ffi.check(self._lib.rtc_register_host_buffer(self._ctx, array.ctypes.data_as(C.c_void_p), array.nbytes))
+
+    def unregister_host_buffer(self, array):
+        ffi.check(self._lib.rtc_unregister_host_buffer(self._ctx, array.ctypes.data_as(C.c_void_p)))
 
     def shard_rows(self, cam_desc, opts):
         return self._lib.rtc_shard_rows(C.byref(cam_desc), C.byref(opts))

@@ -251,6 +251,18 @@ render_f32_small_kernel(const __grid_constant__ SmallParams P, void* __restrict_
         const float4* g_rec = reinterpret_cast<const float4*>(P.rec);
         for (int i = threadIdx.x; i < kRec4 * P.np; i += kThreads) smem4[i] = g_rec[i];
         for (int i = threadIdx.x; i < kRec4 * P.nu; i += kThreads) smem4[kRec4 * kSmallMaxPlanes + i] = g_rec[kRec4 * kSmallMaxPlanes + i];
+        if (P.wait_flag && threadIdx.x == 0) {   // back-pressure: the destination frame is free once the consumer says so
+            unsigned long long t0, t1;
+            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+            for (;;) {
+                unsigned v;
+                asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(P.wait_flag) : "memory");
+                if ((int)(v - P.wait_value) >= 0) break;
+                asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
+                if (t1 - t0 > P.wait_timeout_ns) { atomicMin(P.wait_status, 1u); break; }   // recorded, not trapped (rtc_wait_result)
+                __nanosleep(200);
+            }
+        }
         __syncthreads();
     }
     const F3 light_pos = mk(P.light_pos[0], P.light_pos[1], P.light_pos[2]);
@@ -525,10 +537,18 @@ render_f32_small_kernel(const __grid_constant__ SmallParams P, void* __restrict_
 #endif
     // The tile counter resets itself: the last block to finish zeroes work[0] (tiles handed out) and
     // work[1] (blocks done), so a launch needs no memset in front of it.
+    // With a completion flag the block's pixels (possibly peer stores) are fenced at system scope before the block counts
+    // itself done; the last block then fences again and release-stores the flag: whoever acquires the flag sees the frame.
     __syncthreads();
     if (threadIdx.x == 0) {
-        __threadfence();
-        if (atomicAdd(work + 1, 1u) == gridDim.x - 1) { work[0] = 0u; work[1] = 0u; work[2] = 0u; work[3] = 0u; __threadfence(); }
+        if (P.done_flag) __threadfence_system(); else __threadfence();
+        if (atomicAdd(work + 1, 1u) == gridDim.x - 1) {
+            work[0] = 0u; work[1] = 0u; work[2] = 0u; work[3] = 0u; __threadfence();
+            if (P.done_flag) {
+                __threadfence_system();
+                asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(P.done_flag), "r"(P.done_value) : "memory");
+            }
+        }
     }
     if (kAux && counters) {
         // every shaded hit casts exactly one shadow ray: rays = radiance rays + shaded hits

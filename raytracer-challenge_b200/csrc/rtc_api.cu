@@ -902,9 +902,20 @@ void fill_small_camera(SmallParams& P, const CamParams& cam) {
     P.total_tiles = P.tiles_x * ((cam.shard_rows + 3) / 4);
 }
 
+// rtc_render_device_synced: start after *wait_flag >= wait_value, release-store done_value to *done_flag when the pixels are out
+struct SyncSpec {
+    const unsigned* wait_flag; unsigned wait_value;
+    unsigned* done_flag; unsigned done_value;
+    unsigned long long timeout_ns;
+};
+
 int launch_on(DeviceState& d, const CamParams& cp, int precision, int flags, void* d_rgb, uint8_t* d_hit, Counters* d_counters,
-              cudaStream_t st) {
+              cudaStream_t st, const SyncSpec* sync = nullptr) {
     cudaError_t e;
+    const bool fused = sync && precision == RTC_PRECISION_F32_FAST && d.small_ok && !(flags & RTC_OPT_F32_GENERAL_KERNEL);
+    if (sync && !fused && sync->wait_flag) {   // kernels without the fused form: the flag kernels around the launch
+        wait_kernel<<<1, 32, 0, st>>>(sync->wait_flag, 1, sync->wait_value, sync->timeout_ns, d.wait_status.p);
+    }
     if (precision == RTC_PRECISION_F64_PARITY) {
         DevScene64 s64 = d.s64;
         if (flags & RTC_OPT_NO_BOUND_FILTER) s64.n_bound4 = 0;
@@ -913,6 +924,11 @@ int launch_on(DeviceState& d, const CamParams& cp, int precision, int flags, voi
     else if (d.small_ok && !(flags & RTC_OPT_F32_GENERAL_KERNEL)) {
         SmallParams P = d.small;
         fill_small_camera(P, cp);
+        P.wait_flag = nullptr; P.done_flag = nullptr; P.wait_status = d.wait_status.p; P.wait_value = P.done_value = 0u; P.wait_timeout_ns = 0ull;
+        if (fused) {
+            P.wait_flag = sync->wait_flag; P.wait_value = sync->wait_value; P.done_flag = sync->done_flag; P.done_value = sync->done_value;
+            P.wait_timeout_ns = sync->timeout_ns;
+        }
         P.order = nullptr;
         if (P.max_depth > 0 && P.n_glass != 0 && P.total_tiles >= 4096 && !(flags & RTC_OPT_LINEAR_TILE_ORDER)) {
             if (d.order.ensure((size_t)P.total_tiles) != cudaSuccess) return fail(RTC_ERR_CUDA, "tile order buffer");
@@ -925,6 +941,10 @@ int launch_on(DeviceState& d, const CamParams& cp, int precision, int flags, voi
         e = launch_render_f32(s32, cp, d_rgb, d_hit, d_counters, d.work.p, st);
     }
     if (e != cudaSuccess) return fail(RTC_ERR_CUDA, std::string("kernel launch: ") + cudaGetErrorString(e));
+    if (sync && !fused && sync->done_flag) {
+        signal_kernel<<<1, 1, 0, st>>>(sync->done_flag, sync->done_value);
+        if ((e = cudaGetLastError()) != cudaSuccess) return fail(RTC_ERR_CUDA, std::string("signal launch: ") + cudaGetErrorString(e));
+    }
     return RTC_OK;
 }
 
@@ -1291,6 +1311,21 @@ int rtc_wait_result(rtc_context* ctx, void* stream, int* first_missing) {
     CUDA_TRY(cudaMemsetAsync(d.wait_status.p, 0xff, sizeof(unsigned), st));
     CUDA_TRY(cudaStreamSynchronize(st));
     return fail(RTC_ERR_TIMEOUT, "rtc_wait_device: flag " + std::to_string(v - 1) + " did not arrive within " + std::to_string(ctx->wait_timeout_s) + " s");
+}
+
+int rtc_render_device_synced(rtc_context* ctx, const rtc_camera* cam, const rtc_render_opts* opts, void* d_out_rgb, uint8_t* d_out_hit_mask,
+                             void* stream, const void* d_wait_flag, uint32_t wait_value, void* d_done_flag, uint32_t done_value) {
+    if (!ctx || !d_out_rgb || !stream) return fail(RTC_ERR_INVALID_ARG, "rtc_render_device_synced: null argument (a stream is required)");
+    int rc = validate_opts(cam, opts);
+    if (rc != RTC_OK) return rc;
+    if (!ctx->has_scene) return fail(RTC_ERR_NO_SCENE, "rtc_render_device_synced before rtc_scene_upload");
+    if (ctx->devs.size() != 1) return fail(RTC_ERR_UNSUPPORTED, "rtc_render_device_synced: one-GPU contexts (one process per GPU)");
+    DeviceState& d = ctx->devs[0];
+    CUDA_TRY(cudaSetDevice(d.dev));
+    CamParams cp = make_cam(cam, opts, opts->shard_index, opts->shard_count, opts->tile_rows);
+    cp.dst_full = (opts->flags & RTC_OPT_DST_FULL_FRAME) ? 1 : 0;
+    SyncSpec sy{(const unsigned*)d_wait_flag, wait_value, (unsigned*)d_done_flag, done_value, (unsigned long long)(ctx->wait_timeout_s * 1e9)};
+    return launch_on(d, cp, opts->precision, opts->flags, d_out_rgb, d_out_hit_mask, nullptr, (cudaStream_t)stream, &sy);
 }
 
 int rtc_register_host_buffer(rtc_context* ctx, void* ptr, size_t bytes) {

@@ -154,6 +154,12 @@ struct SmallParams {
     int n_sub, max_depth, tiles_x, total_tiles;
     int row0;                          // first frame row of the launch (row bands of rtc_render)
     unsigned aa_seed;                  // seed of the resample offsets (include/rtc.h)
+    // rtc_render_device_synced, fused: every block starts only once *wait_flag >= wait_value (the consumer is done with the
+    // previous frame: the destination may be overwritten), and the last block to finish release-stores done_value to
+    // *done_flag at system scope after every block's pixels are visible there (peer stores over NVLink included)
+    const unsigned* wait_flag; unsigned* done_flag; unsigned* wait_status;
+    unsigned wait_value, done_value;
+    unsigned long long wait_timeout_ns;
 };
 
 // ---- per-launch parameters --------------------------------------------------------------------

@@ -11,7 +11,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("RTC_B200_LIB") or os.path.join(_HERE, "csrc", "librtc_b200.so")   # override: kernel-variant experiments
 
 RTC_OK = 0
-RTC_ERR_INVALID_ARG, RTC_ERR_UNSUPPORTED, RTC_ERR_NO_DEVICE, RTC_ERR_CUDA, RTC_ERR_NO_SCENE, RTC_ERR_NCCL = 1, 2, 3, 4, 5, 6
+RTC_ERR_INVALID_ARG, RTC_ERR_UNSUPPORTED, RTC_ERR_NO_DEVICE, RTC_ERR_CUDA, RTC_ERR_NO_SCENE, RTC_ERR_NCCL, RTC_ERR_TIMEOUT = 1, 2, 3, 4, 5, 6, 7
 SHAPE_SPHERE, SHAPE_PLANE, SHAPE_CUBE = 0, 1, 2
 PATTERN_NONE, PATTERN_TEST, PATTERN_STRIPE, PATTERN_GRADIENT, PATTERN_RING, PATTERN_CHECKER, PATTERN_GRID = range(7)
 PRECISION_F64_PARITY, PRECISION_F32_FAST = 0, 1
@@ -23,6 +23,8 @@ OPT_DST_FULL_FRAME = 1
 OPT_F32_GENERAL_KERNEL = 2
 OPT_LINEAR_TILE_ORDER = 4
 OPT_NO_BOUND_FILTER = 8
+OPT_DELIVER_DIRECT = 16
+OPT_DELIVER_STAGED = 32
 IPC_HANDLE_BYTES = 64
 
 
@@ -92,6 +94,12 @@ EXPORTS = [
     ("rtc_ipc_close", C.c_int, [C.c_void_p, C.c_void_p, C.c_uint64]),
     ("rtc_signal_device", C.c_int, [C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p]),
     ("rtc_wait_device", C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_uint32, C.c_void_p]),
+    ("rtc_set_wait_timeout", C.c_int, [C.c_void_p, C.c_double]),
+    ("rtc_wait_result", C.c_int, [C.c_void_p, C.c_void_p, C.POINTER(C.c_int)]),
+    ("rtc_render_device_synced", C.c_int, [C.c_void_p, C.POINTER(RtcCamera), C.POINTER(RtcRenderOpts), C.c_void_p, C.c_void_p, C.c_void_p,
+                                           C.c_void_p, C.c_uint32, C.c_void_p, C.c_uint32]),
+    ("rtc_register_host_buffer", C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t]),
+    ("rtc_unregister_host_buffer", C.c_int, [C.c_void_p, C.c_void_p]),
     ("rtc_pack_rgba8_device", C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_size_t, C.c_float, C.c_void_p, C.c_void_p]),
     ("rtc_download_frame", C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_uint32, C.c_uint32, C.c_int, C.c_void_p, C.c_void_p]),
     ("rtc_measure_peak_tflops", C.c_int, [C.c_void_p, C.c_int, C.POINTER(C.c_double)]),

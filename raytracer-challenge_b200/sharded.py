@@ -9,9 +9,12 @@ Two exchange modes:
 * ``"p2p"``   — rank 0 exports its frame buffer through CUDA IPC (``rtc_ipc_export``), the other
   ranks map it (``rtc_ipc_open``) and their render kernels store finished pixels straight into it
   over NVLink (``RTC_OPT_DST_FULL_FRAME``): the transfer overlaps the rendering pixel by pixel.
-  No collective is left: each rank then stores a sequence number into its word of a flag array in
-  rank 0's memory (``rtc_signal_device``, system-scope release after its pixels) and rank 0 waits
-  for the words on its stream (``rtc_wait_device``).
+  No collective is left.  A flag array in rank 0's memory carries the protocol, frame k = 1, 2, ...:
+  word r (r >= 1) = "rank r's pixels of frame k are in" (release-stored at system scope after them,
+  by the last block of the render kernel itself: ``rtc_render_device_synced``), word 0 = "rank 0's
+  consumer is done with frame k" (``release()``).  Rank 0 waits for words 1.. on its stream
+  (``rtc_wait_device``); the other ranks' kernels wait for word 0 >= k - 1 before their first store —
+  back-pressure: a rank that runs ahead cannot overwrite a frame rank 0 is still reading.
 
 The reference has no multi-device path (rayon threads over one ``Canvas``, src/camera.rs:144-160);
 the tile-to-rank arithmetic here is the only "protocol", and it is pure index math so the same class
@@ -137,6 +140,27 @@ class ShardedFrame:
             return self.shard
         return self.frame if self.rank == 0 else self.remote_ptr
 
+    def render(self, renderer, cam_desc, opts, stream):
+        """Enqueue this rank's render of the next frame into ``destination()``.  In p2p mode with flags the non-zero
+        ranks use ``rtc_render_device_synced``: wait for 'previous frame consumed', store the completion flag from the
+        kernel's last block."""
+        dst = self.destination()
+        dst = dst if isinstance(dst, int) else dst.data_ptr()
+        if self.world > 1 and self.mode == "p2p" and self.signal == "flags" and self.rank != 0:
+            k = self.seq + 1
+            renderer.render_device_synced(cam_desc, opts, dst, stream, wait_flag=self.remote_flags, wait_value=k - 1,
+                                          done_flag=self.remote_flags + 4 * self.rank, done_value=k)
+            self._fused = True
+        else:
+            renderer.render_device(cam_desc, opts, dst, None, stream)
+            self._fused = False
+
+    def release(self, stream=None):
+        """Rank 0, after the consumer of the frame ``exchange()`` returned has been enqueued on ``stream``: the other
+        ranks may overwrite the frame (word 0 of the flag array = frames consumed).  No-op elsewhere."""
+        if self.world > 1 and self.mode == "p2p" and self.signal == "flags" and self.rank == 0:
+            self._renderer.signal_device(self.flags.data_ptr(), self.seq, stream)
+
     def exchange(self, assemble=None, stream=None):
         """The exchange step after every rank's render call was enqueued.  Returns the frame on
         rank 0 (None elsewhere).  ``assemble(gathered, frame)`` de-interleaves on the device
@@ -158,7 +182,9 @@ class ShardedFrame:
             if self.rank == 0:
                 self._renderer.wait_device(self.flags.data_ptr() + 4, self.world - 1, self.seq, stream)
                 return self.frame
-            self._renderer.signal_device(self.remote_flags + 4 * self.rank, self.seq, stream)
+            if not getattr(self, "_fused", False):   # the render call was not render(): store the flag behind it
+                self._renderer.signal_device(self.remote_flags + 4 * self.rank, self.seq, stream)
+            self._fused = False
             return None
         # fallback: a 4-byte stream-ordered all-reduce as completion signal (no host synchronisation)
         if self._token is None:
@@ -192,9 +218,23 @@ class SharedHostFrame:
             except Exception:
                 pass
         self.array = np.ndarray((vsize, hsize, 3), dtype=dtype, buffer=self._shm.buf)
+        self._registered_with = None
+
+    def register(self, renderer):
+        """rtc_register_host_buffer on this process's mapping of the segment: this rank's rtc_render then delivers its
+        rows by DMA straight into the shared frame (no staging, no host threads).  Rank 0 touches the pages first."""
+        if self.rank == 0:
+            self.array[:] = 0.0
+        if self.world > 1:
+            dist.barrier()
+        renderer.register_host_buffer(self.array)
+        self._registered_with = renderer
 
     def close(self):
         """Collective: every rank drops its view, then rank 0 removes the segment."""
+        if self._registered_with is not None:
+            self._registered_with.unregister_host_buffer(self.array)
+            self._registered_with = None
         self.array = None
         if self.world > 1:
             dist.barrier()

@@ -223,9 +223,12 @@ def test_cubes_f32(rtc, orc, renderer, seed):
 
 
 # ---- f32 fast mode ---------------------------------------------------------------------------------
-def _check32(rtc, orc, renderer, world, cam, rect=1, max_depth=5, min_ok=0.999, ray_tol=0.002, general=False):
+def _check32(rtc, orc, renderer, world, cam, rect=1, max_depth=5, min_ok=0.999, ray_tol=0.002, general=False, mask_tol=1e-3):
     """general=True forces the general f32 kernel (render_f32.cu); otherwise scenes that fit take the
-    constant-bank small-scene kernel (render_f32_small.cu)."""
+    constant-bank small-scene kernel (render_f32_small.cu).  Hit mask: an all-f32 primary ray can fall on the other side
+    of a silhouette than the f64 one, so open scenes get a stated allowance (mask_tol, a fraction of the pixels; the
+    callers with closed rooms assert zero); big scenes, whose geometry runs in f64, are held to an exact mask
+    (_lattice_check)."""
     renderer.upload(world)
     want, want_hit, cnt = orc.OracleWorld(world).render(cam, rect=rect, max_depth=max_depth, threads=NCPU)
     opts = rtc.Renderer.make_opts(precision=rtc.ffi.PRECISION_F32_FAST, rect=rect, max_depth=max_depth,
@@ -237,6 +240,7 @@ def _check32(rtc, orc, renderer, world, cam, rect=1, max_depth=5, min_ok=0.999, 
     ok = (np.abs(q_got - q_want).max(axis=2) <= 1).mean()
     assert ok >= min_ok, f"only {ok:.5f} of pixels within 1/255"
     mask_mismatch = int((hit != want_hit).sum())
+    assert mask_mismatch <= mask_tol * hit.size, f"f32 hit mask differs from the oracle's on {mask_mismatch} of {hit.size} pixels"
     assert abs(int(stats.rays) - int(cnt.rays)) <= ray_tol * cnt.rays, (stats.rays, cnt.rays)
     return ok, mask_mismatch, stats
 
@@ -502,7 +506,7 @@ def c4_flat(rtc):
     return world.flatten()
 
 
-def _lattice_check(rtc, orc, renderer, flat, cam, step, n_random, f32_min_ok, depth=5):
+def _lattice_check(rtc, orc, renderer, flat, cam, step, n_random, f32_min_ok, depth=5, f32_mask_exact=True):
     """Full-size frames the oracle cannot finish in seconds: the GPU renders the whole frame, the
     oracle a pixel lattice (every `step`-th pixel in x and y + random pixels), BASELINE.md §3."""
     renderer.upload_flat(*flat)
@@ -517,32 +521,42 @@ def _lattice_check(rtc, orc, renderer, flat, cam, step, n_random, f32_min_ok, de
     q_got = orc.quantize_u8(got32.reshape(-1, 3)[idx].astype(np.float64)).astype(int)
     q_want = orc.quantize_u8(want).astype(int)
     ok = (np.abs(q_got - q_want).max(axis=1) <= 1).mean()
-    assert ok >= f32_min_ok, f"f32: only {ok:.5f} of lattice pixels within 1/255"
+    mm = int((hit32.reshape(-1)[idx] != want_hit).sum())
+    assert mm == 0 if f32_mask_exact else mm <= 1e-3 * idx.size, f"f32 hit mask differs from the oracle's on {mm} of {idx.size} lattice pixels"
+    if ok < f32_min_ok:   # say where it fails before failing: the fraction per recursion depth limit
+        per_depth = {}
+        for dd in range(0, depth):
+            w_d, _, _ = orc.OracleWorld(flat=flat).render(cam, max_depth=dd, threads=NCPU, pixels=idx)
+            g_d, _, _ = renderer.render(d, rtc.Renderer.make_opts(precision=rtc.ffi.PRECISION_F32_FAST, max_depth=dd, out_format=rtc.ffi.OUT_F32_RGB))
+            qd = orc.quantize_u8(g_d.reshape(-1, 3)[idx].astype(np.float64)).astype(int)
+            per_depth[dd] = float((np.abs(qd - orc.quantize_u8(w_d).astype(int)).max(axis=1) <= 1).mean())
+        raise AssertionError(f"f32: only {ok:.5f} of lattice pixels within 1/255 at depth {depth}; by depth limit: {per_depth}")
     assert abs(int(st32.rays) - int(st.rays)) <= 0.01 * st.rays
     return st, st32, ok
 
 
 def test_c4_synthetic_10k_small_frame(rtc, orc, renderer, c4_flat):
     """Every pixel of a 96x54 frame of the 10k-shape scene: f64 parity (aliased world_ids, affine
-    spheres, glass) and the f32 general kernel with its streams in global memory."""
+    spheres, glass) and fast mode — the kRefine kernel (f64 ray geometry behind the f32 hierarchy) at the
+    north star's 99.9 % bar, hit mask exact on an open scene with genuine misses."""
     cam = rtc.scenes.synthetic_camera(96, 54)
-    st, st32, ok = _lattice_check(rtc, orc, renderer, c4_flat, cam, step=1, n_random=0, f32_min_ok=0.975)
+    st, st32, ok = _lattice_check(rtc, orc, renderer, c4_flat, cam, step=1, n_random=0, f32_min_ok=0.999)
     assert 0 < st.primary_hits < 96 * 54          # open scene: genuine misses in the mask
 
 
-def test_c4_f32_is_within_tolerance_until_the_sphere_billiard_turns_chaotic(rtc, orc, renderer, c4_flat):
+def test_c4_f32_meets_the_bar_at_every_depth_limit(rtc, orc, renderer, c4_flat):
     """Thousands of r = 0.05..0.35 spheres are strongly diverging mirrors: a hit-point error of one f32
-    ulp (4e-6 at |p| ~ 40) is amplified ~10^3 per sphere-to-sphere bounce, so no f32 path can follow the
-    f64 reference beyond two or three such bounces.  Up to depth 1 the fast mode meets
-    the 99.9 % bar of the north star; at depth 5 it is measured and held to a looser, documented one."""
+    ulp (4e-6 at |p| ~ 40) is amplified ~10^3 per sphere-to-sphere bounce, so an all-f32 path leaves the
+    f64 reference's ray tree after two or three bounces (round 1: 97.5 % at depth 5).  The kRefine kernels carry the
+    geometry of the radiance rays in f64: the bar is the north star's at every depth limit."""
     cam = rtc.scenes.synthetic_camera(192, 108)
-    _lattice_check(rtc, orc, renderer, c4_flat, cam, step=1, n_random=0, f32_min_ok=0.999, depth=0)
-    _lattice_check(rtc, orc, renderer, c4_flat, cam, step=1, n_random=0, f32_min_ok=0.998, depth=1)
+    for depth in (0, 1, 2, 3):
+        _lattice_check(rtc, orc, renderer, c4_flat, cam, step=1, n_random=0, f32_min_ok=0.999, depth=depth)
 
 
 def test_c4_synthetic_10k_4k_lattice(rtc, orc, renderer, c4_flat):
     cam = rtc.scenes.synthetic_camera(3840, 2160)
-    _lattice_check(rtc, orc, renderer, c4_flat, cam, step=32, n_random=1024, f32_min_ok=0.97)
+    _lattice_check(rtc, orc, renderer, c4_flat, cam, step=32, n_random=1024, f32_min_ok=0.999)
 
 
 def _big_mixed_world(rtc):
@@ -623,9 +637,19 @@ def test_f64_line_distance_filter_changes_nothing(rtc, renderer, c4_flat):
 
 
 def test_big_mixed_world_f64_parity_and_f32(rtc, orc, renderer):
-    """The same mixed world against the oracle (f64 parity; f32 within the C4 tolerance) on a small frame."""
+    """The same mixed world against the oracle on a small frame: f64 parity; fast mode at the 99.9 % bar with an exact
+    hit mask (cubes, needle ellipsoids and affine spheres through the f64 exact tests of the kRefine kernel)."""
     cam = rtc.scenes.synthetic_camera(96, 54)
-    _lattice_check(rtc, orc, renderer, _big_mixed_world(rtc).flatten(), cam, step=1, n_random=0, f32_min_ok=0.97)
+    _lattice_check(rtc, orc, renderer, _big_mixed_world(rtc).flatten(), cam, step=1, n_random=0, f32_min_ok=0.999)
+
+
+def test_c3_4k_lattice(rtc, orc, renderer):
+    """C3, the frame every bench number is quoted on: the reflect/refract room at 3840x2160, 1 sample per pixel, depth
+    5 — both precisions against the oracle on every 16th pixel in x and y plus 4096 random pixels."""
+    world = rtc.scenes.reflect_refract_scene()
+    cam = rtc.scenes.reflect_refract_camera(3840, 2160)
+    st, st32, ok = _lattice_check(rtc, orc, renderer, world.flatten(), cam, step=16, n_random=4096, f32_min_ok=0.999)
+    assert st.primary_hits == 3840 * 2160 and st.rays == 103212494
 
 
 def test_c5_8k_supersampled_lattice(rtc, orc, renderer):
