@@ -434,7 +434,11 @@ def run_gpu(args):
     # ---- the drop-in's own multi-GPU path: ONE process, rtc_context_create over the N GPUs, one rtc_render call ----
     single = None
     if N > 1:
-        sync_all()
+        # the other rank processes must leave their GPUs IDLE meanwhile: an NCCL barrier is a kernel spinning on every GPU,
+        # which the driver would time-slice against rank 0's kernels there; they wait on the CPU (gloo) instead
+        cpu_group = dist.new_group(backend="gloo")
+        torch.cuda.synchronize()
+        dist.barrier(group=cpu_group)
         if rank == 0:
             try:
                 rs = rtc.Renderer(list(range(N)))
@@ -467,6 +471,7 @@ def run_gpu(args):
                 rs.close()
             except Exception as ex:   # reported, never hidden
                 single = {"error": repr(ex)}
+        dist.barrier(group=cpu_group)
         sync_all()
 
     if rank == 0:

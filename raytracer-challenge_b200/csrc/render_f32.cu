@@ -116,61 +116,95 @@ __device__ __forceinline__ RayQ make_rayq(const Streams32& S, F3 o, F3 d) {
     q.smargin = fmaf(q.E, 2.f * S.srmax + q.E, 2e-6f * S.srmax * S.srmax);
     return q;
 }
-// lo / hi: the interval of positions along the ray (in world units, rounding margin E included by the caller); hi is read
-// again before every test, so `exact` may shrink it.
-template <typename F>
-__device__ __forceinline__ void sweep_bounds(const Streams32& S, const RayQ& Q, float lo, const float& hi, F exact) {
+// ---- warp-cooperative queries (kFilter kernels) -------------------------------------------------------------------
+// Thirty-two rays walking the hierarchy side by side diverge: every lane has other candidate blocks, groups and
+// members, and a warp pays for the union (round 1: 12 of 32 lanes busy in the member and exact tests).  Here the warp
+// takes its rays ONE AT A TIME and spends its 32 lanes on the hierarchy instead: lane j tests block j, then group j of
+// the chosen block, then member (j & 7) of four candidate groups at once; the exact tests of a step run on the lanes
+// that found the candidates.  Every bound is loaded once, as one coalesced 512-byte row, and the loop nest is uniform.
+// Blocks are visited NEAREST FIRST: each lane turns its block's entry position max(s - R, 0) into a key
+// (float bits, low 6 bits = block slot), a warp min picks the next block, and the walk stops when that block
+// starts beyond `hi` — for radiance rays the nearest hit so far, which the exact tests keep shrinking.
+// A ray's query constants travel through shared memory: its lane publishes them, all lanes read them back (broadcast).
+struct WarpSlots {
+    float4* qa; float4* qb; float4* qc;       // RayQ: (dh, od) (m, len) (E, margin, gmargin, smargin)
+    double2* d0; double2* d1; double2* d2;    // the ray in f64: (ox oy) (oz dx) (dy dz)
+    float4* so; float4* sd;                   // shadow ray in f32: (o, 0) (d, 0); the containers query keeps its parity words in `so`
+};
+constexpr int kWarpSlotBytes = 8 * 32 * 16;
+__device__ __forceinline__ WarpSlots warp_slots(void* smem_base) {
+    WarpSlots W;
+    char* base = reinterpret_cast<char*>(smem_base) + (threadIdx.x >> 5) * kWarpSlotBytes;
+    W.qa = reinterpret_cast<float4*>(base); W.qb = W.qa + 32; W.qc = W.qb + 32;
+    W.d0 = reinterpret_cast<double2*>(W.qc + 32); W.d1 = W.d0 + 32; W.d2 = W.d1 + 32;
+    W.so = reinterpret_cast<float4*>(W.d2 + 32); W.sd = W.so + 32;
+    return W;
+}
+__device__ __forceinline__ void publish_rayq(const WarpSlots& W, int lane, const RayQ& q) {
+    W.qa[lane] = make_float4(q.dh.x, q.dh.y, q.dh.z, q.od);
+    W.qb[lane] = make_float4(q.m.x, q.m.y, q.m.z, q.len);
+    W.qc[lane] = make_float4(q.E, q.margin, q.gmargin, q.smargin);
+}
+__device__ __forceinline__ RayQ load_rayq(const WarpSlots& W, int w) {
+    const float4 a = W.qa[w], b = W.qb[w], c = W.qc[w];
+    RayQ q;
+    q.dh = mk(a.x, a.y, a.z); q.od = a.w; q.m = mk(b.x, b.y, b.z); q.len = b.w;
+    q.E = c.x; q.margin = c.y; q.gmargin = c.z; q.smargin = c.w;
+    return q;
+}
+
+// One ray (Q, warp-uniform), all 32 lanes.  [lo, hi]: the positions along the ray the query cares about (rounding margin E
+// included by the caller); `hi` is read again before every test, so `step` may shrink it.  step(c, i) is called by ALL
+// lanes once per member step — c says this lane holds candidate entry i of the bound stream — and returns true
+// (warp-uniform) to end the query.
+template <typename Step>
+__device__ __forceinline__ void warp_query(const Streams32& S, const RayQ& Q, float lo, float& hi, Step&& step) {
+    const unsigned full = 0xffffffffu;
+    const int lane = threadIdx.x & 31;
     const F3 dh = Q.dh, m = Q.m;
-    auto pass = [&](float4 b, float mg) -> bool {
+    auto test = [&](float4 b, float mg, float& s) -> bool {
         const float vx = fmaf(-b.z, dh.y, fmaf(b.y, dh.z, -m.x));
         const float vy = fmaf(-b.x, dh.z, fmaf(b.z, dh.x, -m.y));
         const float vz = fmaf(-b.y, dh.x, fmaf(b.x, dh.y, -m.z));
         const float gap = fmaf(vz, vz, fmaf(vy, vy, fmaf(vx, vx, b.w)));
-        const float s = fmaf(b.z, dh.z, fmaf(b.y, dh.y, fmaf(b.x, dh.x, -Q.od)));
+        s = fmaf(b.z, dh.z, fmaf(b.y, dh.y, fmaf(b.x, dh.x, -Q.od)));
         const float q = fmaxf(fmaxf(lo - s, s - hi), 0.f);
-        return !(gap > mg) && !(fmaf(q, q, b.w) > 0.f);
+        return !(gap > mg) && !(fmaf(q, q, b.w) > 0.f);   // a NaN never culls; padding entries (w = +inf) never pass
     };
-    // Group level: the streams of a big scene are in Morton order, eight consecutive entries share a bounding sphere; a
-    // ray that misses it (same test, same kind of margin) skips the eight.  The group tests of 32 groups run
-    // branch-free into one bit mask per lane; the lanes then drain their masks side by side — a warp pays for the
-    // largest number of candidate groups any of its lanes has in the block, not for every trip in which some lane has one.
-    // Block level: 32 consecutive groups (256 entries) share one more bounding sphere.  A block is swept when ANY lane of
-    // the warp (of the lanes running this sweep together) comes near it, so the group loads below stay warp-uniform; the
-    // coherent warps — primary rays, shadow rays of neighbouring hits, reflections in the planar mirrors — skip most
-    // blocks.  (Every lane walking its own candidate blocks instead pays in the parity kernel, C4 211 -> 177 ms, but not
-    // here: with per-lane addresses for the group loads C4 went 122 -> 133 ms.)
-    const int n_blocks = (S.nb4 + 255) >> 8;   // sbound and gbound are padded to multiples of 32 with never-hit entries
-    for (int sb = 0; sb < n_blocks; sb += 32) {
-        unsigned sm = 0u;
-#pragma unroll 2
-        for (int j = 0; j < 32; j += 4) {
-            const float4 q0 = S.sbound[sb + j], q1 = S.sbound[sb + j + 1], q2 = S.sbound[sb + j + 2], q3 = S.sbound[sb + j + 3];
-            sm |= ((pass(q0, Q.smargin) ? 1u : 0u) | (pass(q1, Q.smargin) ? 2u : 0u) | (pass(q2, Q.smargin) ? 4u : 0u) | (pass(q3, Q.smargin) ? 8u : 0u)) << j;
-        }
-        unsigned wm = __reduce_or_sync(__activemask(), sm);   // a lane's own candidates are always in it
-        while (wm) {
-            const int gb = 32 * (sb + __ffs(wm) - 1);
-            wm &= wm - 1u;
-            unsigned gm = 0u;
-#pragma unroll 2
-            for (int j = 0; j < 32; j += 4) {
-                const float4 q0 = S.gbound[gb + j], q1 = S.gbound[gb + j + 1], q2 = S.gbound[gb + j + 2], q3 = S.gbound[gb + j + 3];
-                gm |= ((pass(q0, Q.gmargin) ? 1u : 0u) | (pass(q1, Q.gmargin) ? 2u : 0u) | (pass(q2, Q.gmargin) ? 4u : 0u) | (pass(q3, Q.gmargin) ? 8u : 0u)) << j;
-            }
+    auto block_key = [&](int slot, int blk) -> unsigned {   // entry position of the block, rounded down, | its slot
+        float s;
+        RTC_CHECK(blk >= 0 && blk < ((((S.nb4 + 255) >> 8) + 31) & ~31));
+        const float4 b = S.sbound[blk];
+        if (!test(b, Q.smargin, s)) return 0xffffffffu;
+        const float entry = fmaxf(s - sqrtf(-b.w) - Q.E, 0.f);
+        return (__float_as_uint(entry) & ~63u) | (unsigned)slot;
+    };
+    const int n_blocks = (S.nb4 + 255) >> 8;
+    const int n_pad = (n_blocks + 31) & ~31;      // sbound / gbound are padded to multiples of 32 with never-hit entries
+    for (int sb0 = 0; sb0 < n_blocks; sb0 += 64) {
+        unsigned k0 = block_key(lane, sb0 + lane);
+        unsigned k1 = sb0 + 32 < n_pad ? block_key(32 + lane, sb0 + 32 + lane) : 0xffffffffu;
+        for (;;) {
+            const unsigned mine = min(k0, k1);
+            const unsigned k = __reduce_min_sync(full, mine);
+            if (k == 0xffffffffu) break;
+            if (__uint_as_float(k & ~63u) > hi) break;       // every block left starts beyond the interval
+            if (mine == k) { if (k0 == k) k0 = 0xffffffffu; else k1 = 0xffffffffu; }
+            const int gb = 32 * (sb0 + (int)(k & 63u));
+            float sg;
+            RTC_CHECK(gb >= 0 && gb + 31 < (((S.nb4 >> 3) + 31) & ~31));
+            unsigned gm = __ballot_sync(full, test(S.gbound[gb + lane], Q.gmargin, sg));
             while (gm) {
-                const int g = 8 * (gb + __ffs(gm) - 1);
-                gm &= gm - 1u;
-                unsigned cm = 0u;   // the eight members
+                // the four lowest candidate groups of the block: lane l tests member (l & 7) of group number (l >> 3)
+                int sel = -1;
 #pragma unroll
-                for (int j = 0; j < 8; j += 4) {
-                    const float4 b0 = S.bound[g + j], b1 = S.bound[g + j + 1], b2 = S.bound[g + j + 2], b3 = S.bound[g + j + 3];
-                    cm |= ((pass(b0, Q.margin) ? 1u : 0u) | (pass(b1, Q.margin) ? 2u : 0u) | (pass(b2, Q.margin) ? 4u : 0u) | (pass(b3, Q.margin) ? 8u : 0u)) << j;
+                for (int u = 0; u < 4; ++u) {
+                    if (gm) { const int gpos = __ffs(gm) - 1; gm &= gm - 1u; if ((lane >> 3) == u) sel = gpos; }
                 }
-                while (cm) {
-                    const int k = __ffs(cm) - 1;
-                    cm &= cm - 1u;
-                    exact(g + k);
-                }
+                bool c = false;
+                int i = 0;
+                if (sel >= 0) { i = 8 * (gb + sel) + (lane & 7); RTC_CHECK(i >= 0 && i < S.nb4); float sm; c = test(S.bound[i], Q.margin, sm); }
+                if (step(c, i)) return;
             }
         }
     }
@@ -396,7 +430,38 @@ __device__ __forceinline__ F3 pattern_at32(int kind, F3 a, F3 b, F3 p) {
 // a plane is a sign change of f(t) = n.(p + t d) + w between t=0 and t=1, and for a sphere needs
 // no square root: f(0) f(1) < 0 (one root inside) or both roots inside.  f(1) depends only on the
 // light and is precomputed per shape (plL / usL, staged beside the streams).
-template <bool kCubes, bool kFilter>
+// One entry i of the bound stream (uniform spheres | general spheres | cubes) against the segment o -> o + d: does it have a
+// root in [0, 1)?  The per-shape terms of shadow32 below, as a predicate (kFilter kernels: the candidates of a query).
+template <bool kCubes>
+__device__ __forceinline__ bool shadow_exact(const Streams32& S, const float* __restrict__ usL, bool light_inside, int i, F3 o, F3 d, float inv_a) {
+    if (i < S.nu) {
+        const float4 sp = S.usph[i];
+        const F3 L = mk(o.x - sp.x, o.y - sp.y, o.z - sp.z);
+        const float tc = __saturatef(-dot(d, L) * inv_a);
+        const F3 q = fma3(d, tc, L);
+        const float fmin = fmaf(q.z, q.z, fmaf(q.y, q.y, fmaf(q.x, q.x, -sp.w)));
+        if (!light_inside) return fmin <= 0.f;
+        const float f0 = fmaf(L.z, L.z, fmaf(L.y, L.y, fmaf(L.x, L.x, -sp.w)));
+        return fmaxf(fmin, -fmaxf(f0, usL[i])) <= 0.f;
+    }
+    const int k = i - S.nu;
+    float t1, t2;
+    if (!kCubes || k < S.ng) {
+        const float4 r0 = S.gsph[3 * k], r1 = S.gsph[3 * k + 1], r2 = S.gsph[3 * k + 2];
+        const F3 lo = mk(row4(r0, o), row4(r1, o), row4(r2, o));
+        const F3 ld = mk(row3(r0, d), row3(r1, d), row3(r2, d));
+        const float inv = rcp(dot(ld, ld)), bia = dot(ld, lo) * inv;
+        const F3 q = mk(fmaf(-bia, ld.x, lo.x), fmaf(-bia, ld.y, lo.y), fmaf(-bia, ld.z, lo.z));
+        const float dn = fmaf(-q.z, q.z, fmaf(-q.y, q.y, fmaf(-q.x, q.x, 1.f)));
+        if (!(dn >= 0.f)) return false;
+        const float sq = sqrtf(dn * inv);
+        t1 = -bia - sq; t2 = sq - bia;
+    } else if (!cube_slab32(S.gsph + 3 * k, o, d, t1, t2)) return false;
+    const float t = t1 >= 0.f ? t1 : t2;
+    return t >= 0.f && t < 1.f;
+}
+
+template <bool kCubes>
 __device__ __forceinline__ bool shadow32(const Streams32& S, const float* __restrict__ plL, const float* __restrict__ usL,
                                          bool light_inside, F3 o, F3 d) {
     // every test is reduced to "g <= 0" and the g's are min-accumulated: FMNMX instead of predicates
@@ -427,50 +492,36 @@ __device__ __forceinline__ bool shadow32(const Streams32& S, const float* __rest
         float fmin = fmaf(q.z, q.z, fmaf(q.y, q.y, fmaf(q.x, q.x, -sp.w)));
         g = fminf(g, fmaxf(fmin, -fmaxf(f0, usL[i])));
     };
-    auto gsph = [&](int i) {     // genuinely affine spheres: nearest-root test in object space
-        float4 r0 = S.gsph[3 * i], r1 = S.gsph[3 * i + 1], r2 = S.gsph[3 * i + 2];
-        F3 lo = mk(row4(r0, o), row4(r1, o), row4(r2, o));
-        F3 ld = mk(row3(r0, d), row3(r1, d), row3(r2, d));
-        float inv = rcp(dot(ld, ld)), bia = dot(ld, lo) * inv;
-        F3 q = mk(fmaf(-bia, ld.x, lo.x), fmaf(-bia, ld.y, lo.y), fmaf(-bia, ld.z, lo.z));
-        float dn = fmaf(-q.z, q.z, fmaf(-q.y, q.y, fmaf(-q.x, q.x, 1.f)));
-        if (dn >= 0.f) {
-            float s = sqrtf(dn * inv);
-            float t1 = -bia - s, t2 = s - bia;
-            float t = t1 >= 0.f ? t1 : t2;
-            hit |= t >= 0.f && t < 1.f;
-        }
-    };
-    auto cube = [&](int i) {     // cubes: nearest non-negative root below 1
-        float t1, t2;
-        if (cube_slab32(S.gsph + 3 * i, o, d, t1, t2)) {
-            float t = t1 >= 0.f ? t1 : t2;
-            hit |= t >= 0.f && t < 1.f;
-        }
-    };
-    if (kFilter) {
-        // segment query: only shapes that reach into [0, |light - p|] along the ray; a lane that has found its occluder
-        // stops looking (hi = -inf culls everything: any-hit)
-        const RayQ Q = make_rayq(S, o, d);
-        const float lo = -Q.E;
-        float hi = fmaf(Q.len, 1.000002f, Q.E);
-        sweep_bounds(S, Q, lo, hi, [&](int i) {
-            if (i < S.nu) { if (light_inside) usph_in(i); else usph(i); }
-            else if (!kCubes || i - S.nu < S.ng) gsph(i - S.nu);
-            else cube(i - S.nu);
-            if (hit || g <= 0.f) hi = -__int_as_float(0x7f800000);
-        });
-    } else {
-        if (!light_inside) {
+    if (!light_inside) {
 #pragma unroll 2
-            for (int i = 0; i < S.nu; ++i) usph(i);
-        } else {
-            for (int i = 0; i < S.nu; ++i) usph_in(i);
-        }
-        for (int i = 0; i < S.ng; ++i) gsph(i);
-        if (kCubes) for (int i = S.ng; i < S.ng + S.nc; ++i) cube(i);
+        for (int i = 0; i < S.nu; ++i) usph(i);
+    } else {
+        for (int i = 0; i < S.nu; ++i) usph_in(i);
     }
+    for (int i = S.nu; i < S.nu + S.ng + (kCubes ? S.nc : 0); ++i) hit |= shadow_exact<kCubes>(S, usL, light_inside, i, o, d, inv_a);
     return hit || g <= 0.f;
+}
+
+// kFilter kernels: the plane terms of the shadow test stay with the ray's lane ...
+__device__ __forceinline__ bool shadow_planes32(const Streams32& S, const float* __restrict__ plL, F3 o) {
+    float g = 1.0f;
+#pragma unroll 2
+    for (int i = 0; i < S.np; ++i) g = fminf(g, row4(S.planes[i], o) * plL[i]);
+    return g <= 0.f;
+}
+// ... and the solids are an any-hit segment query by the whole warp: [0, |light - p|], over at the first occluder.
+template <bool kCubes>
+__device__ __forceinline__ bool coop_shadow(const Streams32& S, const float* __restrict__ usL, bool light_inside, const RayQ& Q, F3 o, F3 d) {
+    const float inv_a = rcp(dot(d, d));
+    float hi = fmaf(Q.len, 1.000002f, Q.E);
+    bool shadowed = false;
+    warp_query(S, Q, -Q.E, hi, [&](bool c, int i) -> bool {
+        bool occ = false;
+        if (c) occ = shadow_exact<kCubes>(S, usL, light_inside, i, o, d, inv_a);
+        if (__any_sync(0xffffffffu, occ)) { shadowed = true; return true; }
+        return false;
+    });
+    return shadowed;
 }
 
 // ---- kRefine kernels (scenes whose streams stay in global memory: 10^3+ shapes, e.g. config C4) ----------------------
@@ -483,9 +534,7 @@ __device__ __forceinline__ bool shadow32(const Streams32& S, const float* __rest
 // rule, and hit point, normal, over / under point, reflected and refracted directions and n1 / n2 are the f64 ones.  The
 // ray tree is then the parity kernel's, node for node; what stays in f32 is what does not feed back into geometry:
 // the filter, the any-hit shadow test, patterns, Phong lighting, Schlick weights and the colour sums.
-template <bool kCubes, bool kFilter>
-__device__ __forceinline__ void intersect_mixed(const Streams32& S, const ShadeRec64* __restrict__ R64, F3 o, F3 d, p64::V3 od, p64::V3 dd,
-                                                double& best_t, int& best_idx) {
+__device__ __forceinline__ void planes_mixed(const Streams32& S, const ShadeRec64* __restrict__ R64, p64::V3 od, p64::V3 dd, double& best_t, int& best_idx) {
     best_t = __longlong_as_double(0x7ff0000000000000LL);
     best_idx = 0x7fffffff;
     for (int i = 0; i < S.np; ++i) {                     // Plane::intersect_local, src/shape.rs:462-471
@@ -493,40 +542,73 @@ __device__ __forceinline__ void intersect_mixed(const Streams32& S, const ShadeR
         double t;
         if (p64::plane_root(reinterpret_cast<const double2*>(R64[idx].inv + 4), od, dd, t)) p64::take(t, idx, best_t, best_idx);
     }
-    const RayQ Q = make_rayq(S, o, d);
-    const float lo = -Q.E;
+}
+// entry i of the bound stream -> its shape, its two list entries (t1 <= t2)
+template <bool kCubes>
+__device__ __forceinline__ bool roots_mixed(const Streams32& S, const ShadeRec64* __restrict__ R64, int i, p64::V3 od, p64::V3 dd, int& idx, double& t1, double& t2) {
+    RTC_CHECK(i >= 0 && i < S.nu + S.ng + S.nc);
+    idx = i < S.nu ? S.us_index[i] : S.gs_index[i - S.nu];
+    RTC_CHECK(idx >= 0 && idx < S.np + S.nu + S.ng + S.nc);
+    const double2* rows = reinterpret_cast<const double2*>(R64[idx].inv);
+    return (kCubes && i - S.nu >= S.ng) ? p64::cube_roots(rows, od, dd, t1, t2) : p64::sphere_roots(rows, od, dd, t1, t2);
+}
+
+// kGlobal == 1 (RTC_OPT_NO_BOUND_FILTER): every shape's exact test, per lane
+template <bool kCubes>
+__device__ __forceinline__ void intersect_mixed(const Streams32& S, const ShadeRec64* __restrict__ R64, p64::V3 od, p64::V3 dd,
+                                                double& best_t, int& best_idx) {
+    planes_mixed(S, R64, od, dd, best_t, best_idx);
+    for (int i = 0; i < S.nu + S.ng + (kCubes ? S.nc : 0); ++i) {
+        int idx; double t1, t2;
+        if (roots_mixed<kCubes>(S, R64, i, od, dd, idx, t1, t2)) p64::take(t1 >= 0.0 ? t1 : t2, idx, best_t, best_idx);
+    }
+    if (best_idx == 0x7fffffff) best_idx = -1;
+}
+
+// kFilter: the solids of one ray by the whole warp — a forward query over [0, nearest hit so far].  best_t / best_idx come
+// in as the planes' result and are warp-uniform throughout: every candidate's root is broadcast and taken by all lanes.
+template <bool kCubes>
+__device__ __forceinline__ void coop_hit(const Streams32& S, const ShadeRec64* __restrict__ R64, const RayQ& Q, p64::V3 od, p64::V3 dd,
+                                         double& best_t, int& best_idx) {
+    const unsigned full = 0xffffffffu;
     // positions beyond the nearest hit found so far cannot hold the hit (an equal t loses or wins by shape index: kept by the margin)
     auto bound_of = [&](double t) { return fmaf(__double2float_ru(t) * Q.len, 1.000002f, Q.E); };
     float hi = bound_of(best_t);
-    auto exact = [&](int i) {
-        const int idx = i < S.nu ? S.us_index[i] : S.gs_index[i - S.nu];
-        const double2* rows = reinterpret_cast<const double2*>(R64[idx].inv);
-        double t1, t2;
-        const bool any = (kCubes && i - S.nu >= S.ng) ? p64::cube_roots(rows, od, dd, t1, t2) : p64::sphere_roots(rows, od, dd, t1, t2);
-        if (any) {
-            p64::take(t1 >= 0.0 ? t1 : t2, idx, best_t, best_idx);
+    warp_query(S, Q, -Q.E, hi, [&](bool c, int i) -> bool {
+        double t = 0.0;
+        int idx = -1;
+        if (c) {
+            int sidx; double t1, t2;
+            if (roots_mixed<kCubes>(S, R64, i, od, dd, sidx, t1, t2)) {
+                const double tt = t1 >= 0.0 ? t1 : t2;
+                if (tt >= 0.0) { t = tt; idx = sidx; }
+            }
+        }
+        unsigned m = __ballot_sync(full, idx >= 0);
+        if (m) {
+            while (m) {
+                const int src = __ffs(m) - 1;
+                m &= m - 1u;
+                p64::take(__shfl_sync(full, t, src), __shfl_sync(full, idx, src), best_t, best_idx);
+            }
             hi = bound_of(best_t);
         }
-    };
-    if (kFilter) sweep_bounds(S, Q, lo, hi, exact);
-    else for (int i = 0; i < S.nu + S.ng + (kCubes ? S.nc : 0); ++i) exact(i);
-    if (best_idx == 0x7fffffff) best_idx = -1;
+        return false;
+    });
 }
 
 // Intersection::compute_refractive (src/shape.rs:115-141) for a hit on a transparent material, list-free as in the
 // parity kernel (parity64.cuh): only entries with t < 0 matter, i.e. shapes that reach behind the ray origin — a second
 // query over (-inf, 0], run twice: pass 0 takes the parity of the negative entries per world_id (u8 ids alias beyond 255
 // shapes), pass 1 keeps the last two containers.
-template <bool kCubes, bool kFilter>
-__device__ __noinline__ void containers_mixed(const Streams32& S, const ShadeRec64* __restrict__ R64, F3 o, F3 d, p64::V3 od, p64::V3 dd,
+template <bool kCubes>
+__device__ __noinline__ void containers_mixed(const Streams32& S, const ShadeRec64* __restrict__ R64, p64::V3 od, p64::V3 dd,
                                               int hit_idx, double& n1, double& n2) {
     unsigned parity[8];
 #pragma unroll
     for (int k = 0; k < 8; ++k) parity[k] = 0u;
     p64::Cont top1, top2;
     top1.idx = -1; top2.idx = -1; top1.t = top2.t = 0.0; top1.ord = top2.ord = 0; top1.id = top2.id = -1;
-    const RayQ Q = make_rayq(S, o, d);
-    const float lo = -__int_as_float(0x7f800000), hi = Q.E;
 #pragma unroll 1
     for (int pass = 0; pass < 2; ++pass) {
         auto entry = [&](double t, int idx, int root) {
@@ -539,15 +621,75 @@ __device__ __noinline__ void containers_mixed(const Streams32& S, const ShadeRec
             double t;
             if (p64::plane_root(reinterpret_cast<const double2*>(R64[idx].inv + 4), od, dd, t) && t < 0.0) entry(t, idx, 0);
         }
-        auto exact = [&](int i) {
-            const int idx = i < S.nu ? S.us_index[i] : S.gs_index[i - S.nu];
-            const double2* rows = reinterpret_cast<const double2*>(R64[idx].inv);
-            double t1, t2;
-            const bool any = (kCubes && i - S.nu >= S.ng) ? p64::cube_roots(rows, od, dd, t1, t2) : p64::sphere_roots(rows, od, dd, t1, t2);
-            if (any) { if (t1 < 0.0) entry(t1, idx, 0); if (t2 < 0.0) entry(t2, idx, 1); }
+        for (int i = 0; i < S.nu + S.ng + (kCubes ? S.nc : 0); ++i) {
+            int idx; double t1, t2;
+            if (roots_mixed<kCubes>(S, R64, i, od, dd, idx, t1, t2)) { if (t1 < 0.0) entry(t1, idx, 0); if (t2 < 0.0) entry(t2, idx, 1); }
+        }
+    }
+    n1 = top1.idx >= 0 ? R64[top1.idx].refractive_index : 1.0;
+    const int hid = R64[hit_idx].world_id & 255;
+    const bool hit_is_container = (parity[hid >> 5] >> (hid & 31)) & 1u;
+    if (hit_is_container) {
+        if (top1.idx >= 0 && top1.id == hid) n2 = top2.idx >= 0 ? R64[top2.idx].refractive_index : 1.0;
+        else n2 = top1.idx >= 0 ? R64[top1.idx].refractive_index : 1.0;
+    } else {
+        n2 = R64[hit_idx].refractive_index;
+    }
+}
+
+// The same by the whole warp for one ray (kFilter): planes one per lane, solids as a backward query; every negative entry
+// is broadcast, the parity words live in the warp's shared memory (lane 0 toggles), the last two containers in
+// warp-uniform registers.
+template <bool kCubes>
+__device__ __forceinline__ void coop_containers(const Streams32& S, const ShadeRec64* __restrict__ R64, const RayQ& Q, p64::V3 od, p64::V3 dd,
+                                                int hit_idx, unsigned* parity, double& n1, double& n2) {
+    const unsigned full = 0xffffffffu;
+    const int lane = threadIdx.x & 31;
+    __syncwarp();
+    if (lane < 8) parity[lane] = 0u;
+    __syncwarp();
+    p64::Cont top1, top2;
+    top1.idx = -1; top2.idx = -1; top1.t = top2.t = 0.0; top1.ord = top2.ord = 0; top1.id = top2.id = -1;
+#pragma unroll 1
+    for (int pass = 0; pass < 2; ++pass) {
+        auto entry = [&](double t, int idx, int root) {     // called with warp-uniform arguments
+            const int id = R64[idx].world_id & 255;
+            if (pass == 0) { if (lane == 0) parity[id >> 5] ^= 1u << (id & 31); }
+            else if ((parity[id >> 5] >> (id & 31)) & 1u) { p64::Cont e; e.t = t; e.ord = 2 * idx + root; e.idx = idx; e.id = id; p64::offer(e, top1, top2); }
         };
-        if (kFilter) sweep_bounds(S, Q, lo, hi, exact);
-        else for (int i = 0; i < S.nu + S.ng + (kCubes ? S.nc : 0); ++i) exact(i);
+        for (int p0 = 0; p0 < S.np; p0 += 32) {
+            double t = 0.0;
+            int idx = 0;
+            bool neg = false;
+            if (p0 + lane < S.np) {
+                idx = S.pl_index[p0 + lane];
+                neg = p64::plane_root(reinterpret_cast<const double2*>(R64[idx].inv + 4), od, dd, t) && t < 0.0;
+            }
+            unsigned m = __ballot_sync(full, neg);
+            while (m) {
+                const int src = __ffs(m) - 1;
+                m &= m - 1u;
+                entry(__shfl_sync(full, t, src), __shfl_sync(full, idx, src), 0);
+            }
+        }
+        float hi = Q.E;
+        warp_query(S, Q, -__int_as_float(0x7f800000), hi, [&](bool c, int i) -> bool {
+            double t1 = 0.0, t2 = 0.0;
+            int idx = 0;
+            bool neg = false;
+            if (c) neg = roots_mixed<kCubes>(S, R64, i, od, dd, idx, t1, t2) && t1 < 0.0;   // t1 <= t2
+            unsigned m = __ballot_sync(full, neg);
+            while (m) {
+                const int src = __ffs(m) - 1;
+                m &= m - 1u;
+                const double a = __shfl_sync(full, t1, src), b = __shfl_sync(full, t2, src);
+                const int is = __shfl_sync(full, idx, src);
+                entry(a, is, 0);
+                if (b < 0.0) entry(b, is, 1);
+            }
+            return false;
+        });
+        __syncwarp();   // pass 0's toggles are visible to every lane before pass 1 reads them
     }
     n1 = top1.idx >= 0 ? R64[top1.idx].refractive_index : 1.0;
     const int hid = R64[hit_idx].world_id & 255;
@@ -645,7 +787,7 @@ __device__ __noinline__ void compute_refractive32_unique(const Streams32& S, con
 #endif
 // kSmem: shading records staged to shared memory; kUnique: world_ids are unique (<= 255 shapes);
 // kGlobal: the intersect streams stay in global memory (read through L1/L2 as warp-uniform loads) —
-// scenes of any size, e.g. the 10k-shape config C4; 2 = with the bounding-sphere filter in front (sweep_bounds).
+// scenes of any size, e.g. the 10k-shape config C4; 2 = with the bounding-sphere hierarchy in front (warp_query).
 // kCubes: the scene has cubes (object-space slab tests behind the general spheres); scenes without them compile none of it
 // kGlobal != 0 is also kRefine: the geometry of the radiance rays in f64 (see intersect_mixed)
 template <bool kSmem, bool kUnique, int kGlobal, bool kCubes>
@@ -666,6 +808,7 @@ render_f32_kernel(DevScene32 sc, CamParams cam, void* __restrict__ out_rgb, uint
     constexpr bool kFilter = kGlobal == 2;
     constexpr bool kRefine = kGlobal != 0;
     const ShadeRec64* __restrict__ R64 = sc.rec64;
+    const WarpSlots W = warp_slots(smem4);   // kFilter kernels: one published ray per lane (kWarpSlotBytes per warp of dynamic shared memory)
     S.bound = sc.bound; S.nb4 = sc.n_bound4; S.cmax = sc.bound_cmax; S.rmax = sc.bound_rmax;
     S.gbound = sc.gbound; S.gcmax = sc.gbound_cmax; S.grmax = sc.gbound_rmax;
     S.sbound = sc.sbound; S.scmax = sc.sbound_cmax; S.srmax = sc.sbound_rmax;
@@ -753,6 +896,7 @@ render_f32_kernel(DevScene32 sc, CamParams cam, void* __restrict__ out_rgb, uint
         // ---------------------------------------------------------------- refill lanes without a ray
         if (!has_ray && sp > 0) {
             --sp;
+            RTC_CHECK(sp >= 0 && sp < kMaxStack);
             if (kRefine) {
                 const double2 a = stk_d0[sp], b = stk_d1[sp], c = stk_d2[sp];
                 const float2 w = stk_w[sp];
@@ -784,6 +928,7 @@ render_f32_kernel(DevScene32 sc, CamParams cam, void* __restrict__ out_rgb, uint
                 if (aa) acc = aa_tot * (1.0f / (float)aa_ntot);
                 // pixel finished: Canvas::write_pixel (src/canvas.rs:43-46)
                 size_t p = (size_t)(cam.dst_full ? py : pr) * cam.hsize + px;
+                RTC_CHECK(px >= 0 && px < (int)cam.hsize && (cam.dst_full ? (py >= 0 && py < (int)cam.vsize) : (pr >= 0 && pr < cam.shard_rows)));
                 if (cam.out_format == RTC_OUT_F64_RGB) {
                     double* o = (double*)out_rgb + 3 * p;
                     o[0] = (double)acc.x; o[1] = (double)acc.y; o[2] = (double)acc.z;
@@ -874,12 +1019,52 @@ render_f32_kernel(DevScene32 sc, CamParams cam, void* __restrict__ out_rgb, uint
         if (kRefine) {
             ro = mk((float)rod.x, (float)rod.y, (float)rod.z);   // f32 roundings of the ray: the filter, the shading
             rd = mk((float)rdd.x, (float)rdd.y, (float)rdd.z);
-            if (has_ray) { intersect_mixed<kCubes, kFilter>(S, R64, ro, rd, rod, rdd, t64, hit); ++n_rays; }   // hit = shape index
+            if (kFilter) {
+                // planes with the ray's own lane; the solids of every ray by the whole warp, one ray at a time (warp_query)
+                double pt = __longlong_as_double(0x7ff0000000000000LL);
+                int pidx = 0x7fffffff;
+                __syncwarp();
+                if (has_ray) {
+                    ++n_rays;
+                    planes_mixed(S, R64, rod, rdd, pt, pidx);
+                    publish_rayq(W, lane, make_rayq(S, ro, rd));
+                    W.d0[lane] = make_double2(rod.x, rod.y); W.d1[lane] = make_double2(rod.z, rdd.x); W.d2[lane] = make_double2(rdd.y, rdd.z);
+                }
+                __syncwarp();
+                unsigned todo = __ballot_sync(full, has_ray);
+                while (todo) {
+                    const int w = __ffs(todo) - 1;
+                    todo &= todo - 1u;
+                    const RayQ Q = load_rayq(W, w);
+                    const double2 a = W.d0[w], b = W.d1[w], c = W.d2[w];
+                    double bt = __shfl_sync(full, pt, w);
+                    int bi = __shfl_sync(full, pidx, w);
+                    coop_hit<kCubes>(S, R64, Q, p64::mk(a.x, a.y, b.x), p64::mk(b.y, c.x, c.y), bt, bi);
+                    if (lane == w) { pt = bt; pidx = bi; }
+                }
+                t64 = pt;
+                hit = pidx == 0x7fffffff ? -1 : pidx;                                                          // hit = shape index
+            } else if (has_ray) { intersect_mixed<kCubes>(S, R64, rod, rdd, t64, hit); ++n_rays; }
         } else {
             if (has_ray) { intersect32<!kUnique, kCubes>(S, ro, rd, t, hit, neg, n_neg); ++n_rays; }            // hit = stream position
         }
         if (has_ray && is_primary && hit >= 0) { if (sub < 4) hitbits |= 1u << sub; ++n_phits; }
         if (hit < 0) has_ray = false;   // World::color_at -> background_color (black), src/shape.rs:708
+        double n1c = 1.0, n2c = 1.0;    // kFilter: compute_refractive of the transparent hits, by the whole warp (the rays' slots are still published)
+        if (kRefine && kFilter) {
+            const bool need = hit >= 0 && R[hit].tr_ri.x != 0.f;
+            unsigned todo = __ballot_sync(full, need);
+            while (todo) {
+                const int w = __ffs(todo) - 1;
+                todo &= todo - 1u;
+                const RayQ Q = load_rayq(W, w);
+                const double2 a = W.d0[w], b = W.d1[w], c = W.d2[w];
+                double n1, n2;
+                coop_containers<kCubes>(S, R64, Q, p64::mk(a.x, a.y, b.x), p64::mk(b.y, c.x, c.y), __shfl_sync(full, hit, w),
+                                        reinterpret_cast<unsigned*>(W.so), n1, n2);
+                if (lane == w) { n1c = n1; n2c = n2; }
+            }
+        }
 
         // ---------------------------------------------------------------- phase B: prepare_computations
         F3 hp = mk(0, 0, 0), hn = mk(0, 1, 0);
@@ -891,6 +1076,7 @@ render_f32_kernel(DevScene32 sc, CamParams cam, void* __restrict__ out_rgb, uint
             // shade_hit's children (:689-699, 729-781): the next ray and the pending refraction ray leave this block in f64;
             // the shadow test and the shading below get f32 roundings (hp with the f32 epsilon, hn, rd).
             hidx = hit;
+            RTC_CHECK(hidx >= 0 && hidx < sc.n_shapes);
             const ShadeRec64& r64 = R64[hidx];
             const ShadeRec32& rec = R[hidx];
             const float4 ds = rec.dif_spec, tr = rec.tr_ri;
@@ -907,7 +1093,10 @@ render_f32_kernel(DevScene32 sc, CamParams cam, void* __restrict__ out_rgb, uint
             }
             p64::V3 normal = p64::normalize(p64::xvec3(r64.invt, ln));
             double n1 = 1.0, n2 = 1.0;
-            if (tr.x != 0.f) containers_mixed<kCubes, kFilter>(S, R64, ro, rd, rod, rdd, hidx, n1, n2);
+            if (tr.x != 0.f) {
+                if (kFilter) { n1 = n1c; n2 = n2c; }
+                else containers_mixed<kCubes>(S, R64, rod, rdd, hidx, n1, n2);
+            }
             if (p64::dot(normal, eyev) < 0.0) normal = p64::neg(normal);
             const p64::V3 over_point = p64::add(point, p64::mul(normal, p64::kEps));
             const double cos_i = p64::dot(eyev, normal);
@@ -960,7 +1149,9 @@ render_f32_kernel(DevScene32 sc, CamParams cam, void* __restrict__ out_rgb, uint
             is_primary = false;
         }
         if (!kRefine && hit >= 0) {
+            RTC_CHECK(hit < S.np + S.nu + S.ng + S.nc);
             hidx = stream_to_shape(S, hit);
+            RTC_CHECK(hidx >= 0 && hidx < sc.n_shapes);
             const ShadeRec32& rec = R[hidx];
             const float4 tr = rec.tr_ri;
             const int geom = __float_as_int(tr.w);
@@ -1014,7 +1205,30 @@ render_f32_kernel(DevScene32 sc, CamParams cam, void* __restrict__ out_rgb, uint
             }
             const bool inside = ((sc.light_inside >> li) & 1) != 0;
             bool shadowed = false;
-            if (hit >= 0) { shadowed = shadow32<kCubes, kFilter>(S, pL, uL, inside, hp, lpos - hp); ++n_rays; }
+            if (kFilter) {
+                // is_shadowed: plane terms with the hit's lane, the solids as an any-hit segment query by the whole warp
+                const F3 sd = lpos - hp;
+                bool todo_me = false;
+                __syncwarp();
+                if (hit >= 0) {
+                    ++n_rays;
+                    shadowed = shadow_planes32(S, pL, hp);
+                    if (!shadowed) {
+                        todo_me = true;
+                        publish_rayq(W, lane, make_rayq(S, hp, sd));
+                        W.so[lane] = make_float4(hp.x, hp.y, hp.z, 0.f); W.sd[lane] = make_float4(sd.x, sd.y, sd.z, 0.f);
+                    }
+                }
+                __syncwarp();
+                unsigned todo = __ballot_sync(full, todo_me);
+                while (todo) {
+                    const int w = __ffs(todo) - 1;
+                    todo &= todo - 1u;
+                    const RayQ Q = load_rayq(W, w);
+                    const bool sh = coop_shadow<kCubes>(S, uL, inside, Q, xyz(W.so[w]), xyz(W.sd[w]));
+                    if (lane == w) shadowed = sh;
+                }
+            } else if (hit >= 0) { shadowed = shadow32<kCubes>(S, pL, uL, inside, hp, lpos - hp); ++n_rays; }
             if (hit >= 0) {
                 const ShadeRec32& rec = R[hidx];
                 const float4 ca = rec.col_amb, ds = rec.dif_spec;
@@ -1113,6 +1327,17 @@ render_f32_kernel(DevScene32 sc, CamParams cam, void* __restrict__ out_rgb, uint
 
 }  // namespace
 
+cudaError_t preload_render_f32() {
+    cudaFuncAttributes at;
+    cudaError_t e = cudaSuccess;
+    auto touch = [&](auto kernel) { if (e == cudaSuccess) e = cudaFuncGetAttributes(&at, kernel); };
+#define RTC_TOUCH32(SM, GL) touch(render_f32_kernel<SM, true, GL, true>); touch(render_f32_kernel<SM, true, GL, false>); \
+                            touch(render_f32_kernel<SM, false, GL, true>); touch(render_f32_kernel<SM, false, GL, false>);
+    RTC_TOUCH32(false, 2) RTC_TOUCH32(false, 1) RTC_TOUCH32(true, 0) RTC_TOUCH32(false, 0)
+#undef RTC_TOUCH32
+    return e;
+}
+
 cudaError_t launch_render_f32(const DevScene32& scene, const CamParams& cam, void* d_rgb, uint8_t* d_hit,
                               Counters* d_counters, unsigned* d_work, cudaStream_t stream) {
     if (cam.shard_rows <= 0) return cudaSuccess;
@@ -1128,7 +1353,7 @@ cudaError_t launch_render_f32(const DevScene32& scene, const CamParams& cam, voi
     const int warps = kThreads / 32;
     const bool small = streams + recs <= 40 * 1024;
     const bool global_streams = !small && streams > 96 * 1024;   // big scenes: streams stay in global memory behind L1/L2
-    const size_t smem = global_streams ? 16 : (small ? streams + recs : streams);
+    const size_t smem = global_streams ? (size_t)(kThreads / 32) * kWarpSlotBytes : (small ? streams + recs : streams);
     auto launch = [&](auto kernel) -> cudaError_t {
         cudaError_t er = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (er != cudaSuccess) return er;

@@ -322,6 +322,7 @@ render_f32_small_kernel(const __grid_constant__ SmallParams P, void* __restrict_
             else {                                            // Canvas::write_pixel (src/canvas.rs:43-46)
                 if (kAA) acc = aa_tot * (1.0f / (float)aa_ntot);
                 size_t p = (size_t)(P.dst_full ? py : pr) * (size_t)P.hsize + (size_t)px;
+                RTC_CHECK(px >= 0 && px < P.hsize && pr >= 0 && pr < P.shard_rows && py >= P.row0);
                 if (kFmt == RTC_OUT_F64_RGB) {
                     double* o = (double*)out_rgb + 3 * p;
                     o[0] = (double)acc.x; o[1] = (double)acc.y; o[2] = (double)acc.z;
@@ -353,6 +354,7 @@ render_f32_small_kernel(const __grid_constant__ SmallParams P, void* __restrict_
                 t = __shfl_sync(full, t, 0);
                 if (t >= (unsigned)P.total_tiles) { exhausted = true; break; }
                 if (P.order) t = P.order[t];                  // heavy tiles first (classify_tiles_small_kernel)
+                RTC_CHECK(t < (unsigned)P.total_tiles);
                 const int ty = (int)(t / (unsigned)P.tiles_x);
                 wtx = ((int)t - ty * P.tiles_x) * kTileX;
                 wty = ty * kTileY;
@@ -376,6 +378,7 @@ render_f32_small_kernel(const __grid_constant__ SmallParams P, void* __restrict_
         if (!has_ray) {
             if (sp > 0) {                                     // next pending refraction ray of this pixel
                 --sp;
+                RTC_CHECK(sp >= 0 && sp < kMaxStack);
                 const float4 a = stk_a[sp], b = stk_b[sp];
                 ro = xyz(a); rw = a.w; rd = xyz(b); remaining = __float_as_int(b.w);
                 primary = false; has_ray = true;
@@ -415,6 +418,7 @@ render_f32_small_kernel(const __grid_constant__ SmallParams P, void* __restrict_
 
         // ------------------------------------------------------------ phase B: prepare_computations (src/shape.rs:75-96,144-152)
         const int hpos = hit ? (int)(key & kMask) : 0;
+        RTC_CHECK(!hit || hpos < P.np || (hpos >= kSmallMaxPlanes && hpos < kSmallMaxPlanes + P.nu));
         const float t = __uint_as_float((key & ~kMask) | ((kMask + 1u) >> 1));   // centre of the truncation interval
         const unsigned rec = rbase + (unsigned)hpos * kRecBytes;
         const float4 tr = lds4(rec + kOffTrRi);
@@ -606,6 +610,17 @@ extern "C" int rtc_debug_read_trace(unsigned long long* dst, int n_words) {
     return (int)cudaMemcpyFromSymbol(dst, g_trace, sizeof(unsigned long long) * (size_t)n_words);
 }
 #endif
+
+cudaError_t preload_render_f32_small() {
+    cudaFuncAttributes at;
+    cudaError_t e = cudaFuncGetAttributes(&at, classify_tiles_small_kernel);
+    auto touch = [&](auto kernel) { if (e == cudaSuccess) e = cudaFuncGetAttributes(&at, kernel); };
+#define RTC_TOUCHS(F) touch(render_f32_small_kernel<F, true, true>); touch(render_f32_small_kernel<F, false, true>); \
+                      touch(render_f32_small_kernel<F, true, false>); touch(render_f32_small_kernel<F, false, false>);
+    RTC_TOUCHS(RTC_OUT_F64_RGB) RTC_TOUCHS(RTC_OUT_F32_RGB) RTC_TOUCHS(RTC_OUT_U8_RGB)
+#undef RTC_TOUCHS
+    return e;
+}
 
 cudaError_t launch_render_f32_small(const SmallParams& P, int out_format, void* d_rgb, uint8_t* d_hit, Counters* d_counters,
                                     unsigned* d_work, cudaStream_t stream) {

@@ -430,6 +430,7 @@ render_f64_kernel(DevScene64 sc, CamParams cam, double* __restrict__ out_f64, fl
             if (idx < 0) {
                 color = mk(0., 0., 0.);  // background_color, src/shape.rs:652
             } else {
+                RTC_CHECK(idx >= 0 && idx < sc.n_shapes);
                 const ShadeRec64& rec = sc.rec[idx];
                 // Intersection::compute_vectors + CachedVectors::new (src/shape.rs:144-152, 75-96)
                 V3 point = add(ro, mul(rd, t));
@@ -520,6 +521,7 @@ render_f64_kernel(DevScene64 sc, CamParams cam, double* __restrict__ out_f64, fl
                         color = surface;
                     }
                 } else {
+                    RTC_CHECK(level >= 0 && level < RTC_MAX_DEPTH);
                     Frame& f = stack[level];
                     f.surface = surface;
                     f.refl = mk(0., 0., 0.);
@@ -618,6 +620,7 @@ render_f64_kernel(DevScene64 sc, CamParams cam, double* __restrict__ out_f64, fl
     const bool writer = in_image && (ss == 1 || (((sx | sy) & 1) == 0));
     if (writer) {
         size_t p = (size_t)(cam.dst_full ? py : pr) * cam.hsize + px;
+        RTC_CHECK(px >= 0 && px < (int)cam.hsize && (cam.dst_full ? (py >= 0 && py < (int)cam.vsize) : (pr >= 0 && pr < cam.shard_rows)));
         if (cam.out_format == RTC_OUT_F64_RGB) {
             out_f64[3 * p + 0] = result.x; out_f64[3 * p + 1] = result.y; out_f64[3 * p + 2] = result.z;
         } else if (cam.out_format == RTC_OUT_F32_RGB) {
@@ -648,6 +651,15 @@ render_f64_kernel(DevScene64 sc, CamParams cam, double* __restrict__ out_f64, fl
 }
 
 }  // namespace
+
+cudaError_t preload_render_f64() {
+    cudaFuncAttributes at;
+    cudaError_t e = cudaSuccess;
+    auto touch = [&](auto kernel) { if (e == cudaSuccess) e = cudaFuncGetAttributes(&at, kernel); };
+    touch(render_f64_kernel<true, true, true>); touch(render_f64_kernel<true, true, false>); touch(render_f64_kernel<true, false, true>); touch(render_f64_kernel<true, false, false>);
+    touch(render_f64_kernel<false, true, true>); touch(render_f64_kernel<false, true, false>); touch(render_f64_kernel<false, false, true>); touch(render_f64_kernel<false, false, false>);
+    return e;
+}
 
 cudaError_t launch_render_f64(const DevScene64& scene, const CamParams& cam, void* d_rgb, uint8_t* d_hit,
                               Counters* d_counters, cudaStream_t stream) {

@@ -992,6 +992,17 @@ int rtc_context_create(const int* device_ids, int n_gpus, rtc_context** out_ctx)
         if (e == cudaSuccess) e = d.counters.ensure(1);
         if (e == cudaSuccess) e = d.work.ensure(8);
         if (e == cudaSuccess) e = cudaMemset(d.work.p, 0, 8 * sizeof(unsigned));
+        if (e == cudaSuccess) e = preload_render_f64();      // no launch of the library ever loads code (rtc_common.h)
+        if (e == cudaSuccess) e = preload_render_f32();
+        if (e == cudaSuccess) e = preload_render_f32_small();
+        if (e == cudaSuccess) {
+            cudaFuncAttributes at;
+            const void* own[] = {(const void*)signal_kernel, (const void*)wait_kernel, (const void*)assemble_rows_kernel<uint4>,
+                                 (const void*)assemble_rows_kernel<uint32_t>, (const void*)assemble_rows_kernel<unsigned char>,
+                                 (const void*)pack_rgba8_kernel<double>, (const void*)pack_rgba8_kernel<float>,
+                                 (const void*)fma_peak_kernel<float>, (const void*)fma_peak_kernel<double>};
+            for (const void* k : own) if (e == cudaSuccess) e = cudaFuncGetAttributes(&at, k);
+        }
         if (e == cudaSuccess) e = d.wait_status.ensure(1);
         if (e == cudaSuccess) e = cudaMemset(d.wait_status.p, 0xff, sizeof(unsigned));
         if (e == cudaSuccess && g > 0) {   // peer stores into the first GPU's frame (rtc_render_device on several GPUs)

@@ -18,6 +18,17 @@
 #include <stdint.h>
 #include "../../include/rtc.h"
 
+// `make checked` builds librtc_b200_checked.so with -DRTC_CHECKED: every index the kernels form into a stream, a record
+// array, a per-lane stack or a frame is asserted in range (a failed device assert prints file:line and stops the kernel).
+// tools/sanitize_run.py runs the whole entry-point matrix on it between guard bands — the stand-in for compute-sanitizer,
+// which this GPU pool refuses to run (profiles/r02_sanitizer.txt).  The product build compiles none of it.
+#ifdef RTC_CHECKED
+#include <assert.h>
+#define RTC_CHECK(c) assert(c)
+#else
+#define RTC_CHECK(c) ((void)0)
+#endif
+
 namespace rtc {
 
 // ---- f64 (parity) layout ----------------------------------------------------------------------
@@ -213,6 +224,14 @@ __host__ __device__ inline int shard_num_rows(int vsize, int tile_rows, int shar
     }
     return rows;
 }
+
+// Loads every kernel of a translation unit on the current device (cudaFuncGetAttributes).  With CUDA's lazy module loading
+// the FIRST launch of a kernel may need a device-wide synchronisation; behind a kernel that spins on a completion flag
+// (rtc_wait_device, the fused wait of rtc_render_device_synced) that launch would block until the wait times out.
+// rtc_context_create calls these once per GPU, so no launch of the library ever loads code.
+cudaError_t preload_render_f64();
+cudaError_t preload_render_f32();
+cudaError_t preload_render_f32_small();
 
 // kernel launchers implemented in the kernel TUs
 cudaError_t launch_render_f64(const DevScene64& scene, const CamParams& cam, void* d_rgb, uint8_t* d_hit,

@@ -2,11 +2,17 @@
 runs (memcheck / racecheck / initcheck, SURVEY.md §5 "race detection").  Frames are tiny so that a sanitizer pass
 takes seconds; each case is also compared with a second render of itself (bit-identical) so that a hazard which
 changes a pixel shows up even when the tool does not flag it.
-usage: compute-sanitizer --tool memcheck python tools/sanitize_run.py [--multi]"""
+usage: compute-sanitizer --tool memcheck python tools/sanitize_run.py [--multi]
+       python tools/sanitize_run.py --checked     (the pool refuses compute-sanitizer: the library built with every index
+                                                   asserted, `make -C raytracer-challenge_b200/csrc checked`, and every device
+                                                   frame between guard bands that must come back untouched)"""
 import os
 import sys
 
-sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+if "--checked" in sys.argv:
+    os.environ["RTC_B200_LIB"] = os.path.join(ROOT, "raytracer-challenge_b200", "csrc", "librtc_b200_checked.so")
 import numpy as np
 import torch
 
@@ -33,6 +39,39 @@ def both(world, cam, **kw):
             assert np.array_equal(a, b) and np.array_equal(ma, mb), ("not reproducible", prec, fmt)
 
 
+def guarded(world, cam, **kw):
+    """rtc_render_device into device frames with a guard band of 4 rows of a sentinel on either side (and behind the hit
+    mask): a store outside the frame shows up as a changed guard byte."""
+    r.upload(world)
+    d = cam.flatten()
+    G = 4
+    for prec in (ffi.PRECISION_F64_PARITY, ffi.PRECISION_F32_FAST):
+        for fmt, dt in ((ffi.OUT_F64_RGB, torch.float64), (ffi.OUT_F32_RGB, torch.float32), (ffi.OUT_U8_RGB, torch.uint8)):
+            for shards in (1, 3):
+                for k in range(shards):
+                    o = rtc.Renderer.make_opts(precision=prec, out_format=fmt, shard_index=k, shard_count=shards, tile_rows=4, **kw)
+                    rows = r.shard_rows(d, o)
+                    buf = torch.full((rows + 2 * G, d.hsize, 3), 77, dtype=dt, device="cuda")
+                    msk = torch.full((rows + 2 * G, d.hsize), 77, dtype=torch.uint8, device="cuda")
+                    r.render_device(d, o, buf[G:].data_ptr(), msk[G:].data_ptr())
+                    torch.cuda.synchronize()
+                    for t in (buf, msk):
+                        assert bool((t[:G] == 77).all()) and bool((t[rows + G:] == 77).all()), ("guard band overwritten", prec, fmt, shards, k)
+    print("guarded ok:", d.hsize, d.vsize, kw, flush=True)
+
+
+if "--checked" in sys.argv:
+    print("library:", ffi.LIB_PATH, flush=True)
+    assert ffi.LIB_PATH.endswith("_checked.so")
+guarded(room, rtc.scenes.reflect_refract_camera(64, 36))
+guarded(room, rtc.scenes.reflect_refract_camera(33, 17, samples=0))
+guarded(room, rtc.scenes.reflect_refract_camera(40, 21, samples=5))
+guarded(room, rtc.scenes.reflect_refract_camera(64, 36), flags=ffi.OPT_F32_GENERAL_KERNEL)
+guarded(two, rtc.scenes.reflect_refract_camera(48, 24))
+guarded(cube_world, cube_cam)
+guarded(big, rtc.scenes.synthetic_camera(48, 27))
+guarded(big, rtc.scenes.synthetic_camera(24, 14), flags=ffi.OPT_NO_BOUND_FILTER)
+guarded(room, rtc.scenes.reflect_refract_camera(1024, 512))   # tile scheduling pre-pass (>= 4096 tiles)
 both(room, rtc.scenes.reflect_refract_camera(64, 36))
 both(room, rtc.scenes.reflect_refract_camera(33, 17, samples=0))
 both(room, rtc.scenes.reflect_refract_camera(40, 20, samples=5))
