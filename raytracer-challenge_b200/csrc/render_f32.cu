@@ -52,6 +52,7 @@ struct Streams32 {
     const float4* bound; int nb4; float cmax, rmax;   // bounding-sphere filter (DevScene32::bound), kFilter kernels only
     const float4* gbound; float gcmax, grmax;         // one bound per eight entries of `bound` (DevScene32::gbound)
     const float4* sbound; float scmax, srmax;         // one bound per 32 groups (DevScene32::sbound)
+    const float4* gbox; const float4* sbox;           // the same two levels as axis-aligned boxes (lo, hi interleaved)
 };
 
 // Cube::intersect_local (src/shape.rs:540-591) in object space: slab test per axis.  A zero direction
@@ -101,7 +102,9 @@ struct RayQ {
     float od;        // o . dh
     float len;       // |d|: position along the ray = t * len
     float E;         // absolute error bound of the positions computed here
-    float margin, gmargin, smargin;
+    float margin;    // of the entry-level sphere test (squared-distance units)
+    F3 inv, c0, c1;  // box levels: position of the ray in the plane x_a = b is fmaf(b, inv_a, c_a); c0 / c1 carry the box's
+                     // lower / upper faces moved outwards by E
 };
 __device__ __forceinline__ RayQ make_rayq(const Streams32& S, F3 o, F3 d) {
     RayQ q;
@@ -110,10 +113,13 @@ __device__ __forceinline__ RayQ make_rayq(const Streams32& S, F3 o, F3 d) {
     q.len = dd * il;
     q.m = mk(o.y * q.dh.z - o.z * q.dh.y, o.z * q.dh.x - o.x * q.dh.z, o.x * q.dh.y - o.y * q.dh.x);
     q.od = dot(o, q.dh);
-    q.E = 3.8e-6f * (fmaxf(fmaxf(S.cmax, S.gcmax), S.scmax) + fabsf(o.x) + fabsf(o.y) + fabsf(o.z));
+    q.E = 3.8e-6f * (S.cmax + S.rmax + fabsf(o.x) + fabsf(o.y) + fabsf(o.z));
     q.margin = fmaf(q.E, 2.f * S.rmax + q.E, 2e-6f * S.rmax * S.rmax);
-    q.gmargin = fmaf(q.E, 2.f * S.grmax + q.E, 2e-6f * S.grmax * S.grmax);
-    q.smargin = fmaf(q.E, 2.f * S.srmax + q.E, 2e-6f * S.srmax * S.srmax);
+    // a direction component of (almost) zero keeps a finite reciprocal: the slab then holds the whole ray or none of it
+    auto inv_of = [](float v) { return rcp(copysignf(fmaxf(fabsf(v), 1e-30f), v)); };
+    q.inv = mk(inv_of(q.dh.x), inv_of(q.dh.y), inv_of(q.dh.z));
+    q.c0 = mk(-(o.x + q.E) * q.inv.x, -(o.y + q.E) * q.inv.y, -(o.z + q.E) * q.inv.z);
+    q.c1 = mk(-(o.x - q.E) * q.inv.x, -(o.y - q.E) * q.inv.y, -(o.z - q.E) * q.inv.z);
     return q;
 }
 // ---- warp-cooperative queries (kFilter kernels) -------------------------------------------------------------------
@@ -121,91 +127,111 @@ __device__ __forceinline__ RayQ make_rayq(const Streams32& S, F3 o, F3 d) {
 // members, and a warp pays for the union (round 1: 12 of 32 lanes busy in the member and exact tests).  Here the warp
 // takes its rays ONE AT A TIME and spends its 32 lanes on the hierarchy instead: lane j tests block j, then group j of
 // the chosen block, then member (j & 7) of four candidate groups at once; the exact tests of a step run on the lanes
-// that found the candidates.  Every bound is loaded once, as one coalesced 512-byte row, and the loop nest is uniform.
-// Blocks are visited NEAREST FIRST: each lane turns its block's entry position max(s - R, 0) into a key
-// (float bits, low 6 bits = block slot), a warp min picks the next block, and the walk stops when that block
-// starts beyond `hi` — for radiance rays the nearest hit so far, which the exact tests keep shrinking.
+// that found the candidates.  Every bound is loaded once, as coalesced rows, and the loop nest is uniform.
+// The two upper levels are axis-aligned boxes (slab test against the query's interval of positions [lo, hi] along the
+// ray), the entries bounding spheres (distance from the ray's line + position, as before).  Blocks are visited NEAREST
+// FIRST: each lane turns the position where the ray enters its block into a key (float bits, low 6 bits = block slot),
+// a warp min picks the next block, and the walk stops when that block starts beyond `hi` — for radiance rays the
+// nearest hit so far, which the exact tests keep shrinking.
 // A ray's query constants travel through shared memory: its lane publishes them, all lanes read them back (broadcast).
 struct WarpSlots {
-    float4* qa; float4* qb; float4* qc;       // RayQ: (dh, od) (m, len) (E, margin, gmargin, smargin)
+    float4* qa; float4* qb; float4* qc;       // RayQ: (dh, od) (m, len) (E, margin, -, -)
+    float4* qd; float4* qe; float4* qf;       // RayQ: inv, c0, c1
     double2* d0; double2* d1; double2* d2;    // the ray in f64: (ox oy) (oz dx) (dy dz)
     float4* so; float4* sd;                   // shadow ray in f32: (o, 0) (d, 0); the containers query keeps its parity words in `so`
+    int* queue;                               // candidate groups of the block being visited
 };
-constexpr int kWarpSlotBytes = 8 * 32 * 16;
+constexpr int kWarpSlotBytes = 12 * 32 * 16;
 __device__ __forceinline__ WarpSlots warp_slots(void* smem_base) {
     WarpSlots W;
     char* base = reinterpret_cast<char*>(smem_base) + (threadIdx.x >> 5) * kWarpSlotBytes;
-    W.qa = reinterpret_cast<float4*>(base); W.qb = W.qa + 32; W.qc = W.qb + 32;
-    W.d0 = reinterpret_cast<double2*>(W.qc + 32); W.d1 = W.d0 + 32; W.d2 = W.d1 + 32;
+    W.qa = reinterpret_cast<float4*>(base); W.qb = W.qa + 32; W.qc = W.qb + 32; W.qd = W.qc + 32; W.qe = W.qd + 32; W.qf = W.qe + 32;
+    W.d0 = reinterpret_cast<double2*>(W.qf + 32); W.d1 = W.d0 + 32; W.d2 = W.d1 + 32;
     W.so = reinterpret_cast<float4*>(W.d2 + 32); W.sd = W.so + 32;
+    W.queue = reinterpret_cast<int*>(W.sd + 32);
     return W;
 }
 __device__ __forceinline__ void publish_rayq(const WarpSlots& W, int lane, const RayQ& q) {
     W.qa[lane] = make_float4(q.dh.x, q.dh.y, q.dh.z, q.od);
     W.qb[lane] = make_float4(q.m.x, q.m.y, q.m.z, q.len);
-    W.qc[lane] = make_float4(q.E, q.margin, q.gmargin, q.smargin);
+    W.qc[lane] = make_float4(q.E, q.margin, 0.f, 0.f);
+    W.qd[lane] = make_float4(q.inv.x, q.inv.y, q.inv.z, 0.f);
+    W.qe[lane] = make_float4(q.c0.x, q.c0.y, q.c0.z, 0.f);
+    W.qf[lane] = make_float4(q.c1.x, q.c1.y, q.c1.z, 0.f);
 }
 __device__ __forceinline__ RayQ load_rayq(const WarpSlots& W, int w) {
-    const float4 a = W.qa[w], b = W.qb[w], c = W.qc[w];
+    const float4 a = W.qa[w], b = W.qb[w], c = W.qc[w], d = W.qd[w], e = W.qe[w], f = W.qf[w];
     RayQ q;
     q.dh = mk(a.x, a.y, a.z); q.od = a.w; q.m = mk(b.x, b.y, b.z); q.len = b.w;
-    q.E = c.x; q.margin = c.y; q.gmargin = c.z; q.smargin = c.w;
+    q.E = c.x; q.margin = c.y;
+    q.inv = mk(d.x, d.y, d.z); q.c0 = mk(e.x, e.y, e.z); q.c1 = mk(f.x, f.y, f.z);
     return q;
 }
 
 // One ray (Q, warp-uniform), all 32 lanes.  [lo, hi]: the positions along the ray the query cares about (rounding margin E
 // included by the caller); `hi` is read again before every test, so `step` may shrink it.  step(c, i) is called by ALL
 // lanes once per member step — c says this lane holds candidate entry i of the bound stream — and returns true
-// (warp-uniform) to end the query.
+// (warp-uniform) to end the query.  `queue`: 32 ints of the warp's shared memory.
 template <typename Step>
-__device__ __forceinline__ void warp_query(const Streams32& S, const RayQ& Q, float lo, float& hi, Step&& step) {
+__device__ __forceinline__ void warp_query(const Streams32& S, const RayQ& Q, float lo, float& hi, int* queue, Step&& step) {
     const unsigned full = 0xffffffffu;
     const int lane = threadIdx.x & 31;
     const F3 dh = Q.dh, m = Q.m;
-    auto test = [&](float4 b, float mg, float& s) -> bool {
+    // entry level: bounding sphere (cx, cy, cz, -R^2) — the ray's line passes within R, and [s - R, s + R] reaches into [lo, hi]
+    auto sphere_test = [&](float4 b) -> bool {
         const float vx = fmaf(-b.z, dh.y, fmaf(b.y, dh.z, -m.x));
         const float vy = fmaf(-b.x, dh.z, fmaf(b.z, dh.x, -m.y));
         const float vz = fmaf(-b.y, dh.x, fmaf(b.x, dh.y, -m.z));
         const float gap = fmaf(vz, vz, fmaf(vy, vy, fmaf(vx, vx, b.w)));
-        s = fmaf(b.z, dh.z, fmaf(b.y, dh.y, fmaf(b.x, dh.x, -Q.od)));
+        const float s = fmaf(b.z, dh.z, fmaf(b.y, dh.y, fmaf(b.x, dh.x, -Q.od)));
         const float q = fmaxf(fmaxf(lo - s, s - hi), 0.f);
-        return !(gap > mg) && !(fmaf(q, q, b.w) > 0.f);   // a NaN never culls; padding entries (w = +inf) never pass
+        return !(gap > Q.margin) && !(fmaf(q, q, b.w) > 0.f);   // a NaN never culls; padding entries (w = +inf) never pass
     };
-    auto block_key = [&](int slot, int blk) -> unsigned {   // entry position of the block, rounded down, | its slot
-        float s;
-        RTC_CHECK(blk >= 0 && blk < ((((S.nb4 + 255) >> 8) + 31) & ~31));
-        const float4 b = S.sbound[blk];
-        if (!test(b, Q.smargin, s)) return 0xffffffffu;
-        const float entry = fmaxf(s - sqrtf(-b.w) - Q.E, 0.f);
-        return (__float_as_uint(entry) & ~63u) | (unsigned)slot;
+    // upper levels: axis-aligned box, faces moved outwards by E — the positions at which the ray is inside all three slabs,
+    // cut to [lo, hi]; returns whether any are left and where they start
+    auto box_test = [&](float4 bl, float4 bh, float& enter) -> bool {
+        const float x0 = fmaf(bl.x, Q.inv.x, Q.c0.x), x1 = fmaf(bh.x, Q.inv.x, Q.c1.x);
+        const float y0 = fmaf(bl.y, Q.inv.y, Q.c0.y), y1 = fmaf(bh.y, Q.inv.y, Q.c1.y);
+        const float z0 = fmaf(bl.z, Q.inv.z, Q.c0.z), z1 = fmaf(bh.z, Q.inv.z, Q.c1.z);
+        enter = fmaxf(fmaxf(fminf(x0, x1), fminf(y0, y1)), fmaxf(fminf(z0, z1), lo));
+        const float leave = fminf(fminf(fmaxf(x0, x1), fmaxf(y0, y1)), fminf(fmaxf(z0, z1), hi));
+        return !(enter > leave);
     };
-    const int n_blocks = (S.nb4 + 255) >> 8;
-    const int n_pad = (n_blocks + 31) & ~31;      // sbound / gbound are padded to multiples of 32 with never-hit entries
+    const int n_groups = S.nb4 >> 3;              // `bound` is padded to whole groups of eight
+    const int n_blocks = (n_groups + 31) >> 5;
+    auto block_key = [&](int slot, int blk) -> unsigned {   // where the ray enters the block, rounded down, | its slot
+        if (blk >= n_blocks) return 0xffffffffu;
+        float enter;
+        if (!box_test(S.sbox[2 * blk], S.sbox[2 * blk + 1], enter)) return 0xffffffffu;
+        return (__float_as_uint(fmaxf(enter, 0.f)) & ~63u) | (unsigned)slot;
+    };
     for (int sb0 = 0; sb0 < n_blocks; sb0 += 64) {
         unsigned k0 = block_key(lane, sb0 + lane);
-        unsigned k1 = sb0 + 32 < n_pad ? block_key(32 + lane, sb0 + 32 + lane) : 0xffffffffu;
+        unsigned k1 = block_key(32 + lane, sb0 + 32 + lane);
         for (;;) {
             const unsigned mine = min(k0, k1);
             const unsigned k = __reduce_min_sync(full, mine);
             if (k == 0xffffffffu) break;
             if (__uint_as_float(k & ~63u) > hi) break;       // every block left starts beyond the interval
             if (mine == k) { if (k0 == k) k0 = 0xffffffffu; else k1 = 0xffffffffu; }
-            const int gb = 32 * (sb0 + (int)(k & 63u));
-            float sg;
-            RTC_CHECK(gb >= 0 && gb + 31 < (((S.nb4 >> 3) + 31) & ~31));
-            unsigned gm = __ballot_sync(full, test(S.gbound[gb + lane], Q.gmargin, sg));
-            while (gm) {
-                // the four lowest candidate groups of the block: lane l tests member (l & 7) of group number (l >> 3)
-                int sel = -1;
-#pragma unroll
-                for (int u = 0; u < 4; ++u) {
-                    if (gm) { const int gpos = __ffs(gm) - 1; gm &= gm - 1u; if ((lane >> 3) == u) sel = gpos; }
-                }
+            const int gidx = 32 * (sb0 + (int)(k & 63u)) + lane;      // lane j <-> group j of the block
+            float ge;
+            RTC_CHECK(gidx >= 0 && gidx < ((n_groups + 31) & ~31));
+            const bool gp = gidx < n_groups && box_test(S.gbox[2 * gidx], S.gbox[2 * gidx + 1], ge);
+            const unsigned gm = __ballot_sync(full, gp);
+            if (gm == 0u) continue;
+            // the candidate groups, compacted into the warp's queue; then four groups per step: lane l tests member (l & 7)
+            const int n_c = __popc(gm);
+            if (gp) queue[__popc(gm & ((1u << lane) - 1u))] = gidx;
+            __syncwarp();
+            for (int s0 = 0; s0 < n_c; s0 += 4) {
+                const int qi = s0 + (lane >> 3);
                 bool c = false;
                 int i = 0;
-                if (sel >= 0) { i = 8 * (gb + sel) + (lane & 7); RTC_CHECK(i >= 0 && i < S.nb4); float sm; c = test(S.bound[i], Q.margin, sm); }
+                if (qi < n_c) { i = 8 * queue[qi] + (lane & 7); RTC_CHECK(i >= 0 && i < S.nb4); c = sphere_test(S.bound[i]); }
                 if (step(c, i)) return;
             }
+            __syncwarp();   // the queue is free again
         }
     }
 }
@@ -511,11 +537,11 @@ __device__ __forceinline__ bool shadow_planes32(const Streams32& S, const float*
 }
 // ... and the solids are an any-hit segment query by the whole warp: [0, |light - p|], over at the first occluder.
 template <bool kCubes>
-__device__ __forceinline__ bool coop_shadow(const Streams32& S, const float* __restrict__ usL, bool light_inside, const RayQ& Q, F3 o, F3 d) {
+__device__ __forceinline__ bool coop_shadow(const Streams32& S, const float* __restrict__ usL, bool light_inside, const RayQ& Q, F3 o, F3 d, int* queue) {
     const float inv_a = rcp(dot(d, d));
     float hi = fmaf(Q.len, 1.000002f, Q.E);
     bool shadowed = false;
-    warp_query(S, Q, -Q.E, hi, [&](bool c, int i) -> bool {
+    warp_query(S, Q, -Q.E, hi, queue, [&](bool c, int i) -> bool {
         bool occ = false;
         if (c) occ = shadow_exact<kCubes>(S, usL, light_inside, i, o, d, inv_a);
         if (__any_sync(0xffffffffu, occ)) { shadowed = true; return true; }
@@ -569,12 +595,12 @@ __device__ __forceinline__ void intersect_mixed(const Streams32& S, const ShadeR
 // in as the planes' result and are warp-uniform throughout: every candidate's root is broadcast and taken by all lanes.
 template <bool kCubes>
 __device__ __forceinline__ void coop_hit(const Streams32& S, const ShadeRec64* __restrict__ R64, const RayQ& Q, p64::V3 od, p64::V3 dd,
-                                         double& best_t, int& best_idx) {
+                                         int* queue, double& best_t, int& best_idx) {
     const unsigned full = 0xffffffffu;
     // positions beyond the nearest hit found so far cannot hold the hit (an equal t loses or wins by shape index: kept by the margin)
     auto bound_of = [&](double t) { return fmaf(__double2float_ru(t) * Q.len, 1.000002f, Q.E); };
     float hi = bound_of(best_t);
-    warp_query(S, Q, -Q.E, hi, [&](bool c, int i) -> bool {
+    warp_query(S, Q, -Q.E, hi, queue, [&](bool c, int i) -> bool {
         double t = 0.0;
         int idx = -1;
         if (c) {
@@ -642,7 +668,7 @@ __device__ __noinline__ void containers_mixed(const Streams32& S, const ShadeRec
 // warp-uniform registers.
 template <bool kCubes>
 __device__ __forceinline__ void coop_containers(const Streams32& S, const ShadeRec64* __restrict__ R64, const RayQ& Q, p64::V3 od, p64::V3 dd,
-                                                int hit_idx, unsigned* parity, double& n1, double& n2) {
+                                                int hit_idx, unsigned* parity, int* queue, double& n1, double& n2) {
     const unsigned full = 0xffffffffu;
     const int lane = threadIdx.x & 31;
     __syncwarp();
@@ -673,7 +699,7 @@ __device__ __forceinline__ void coop_containers(const Streams32& S, const ShadeR
             }
         }
         float hi = Q.E;
-        warp_query(S, Q, -__int_as_float(0x7f800000), hi, [&](bool c, int i) -> bool {
+        warp_query(S, Q, -__int_as_float(0x7f800000), hi, queue, [&](bool c, int i) -> bool {
             double t1 = 0.0, t2 = 0.0;
             int idx = 0;
             bool neg = false;
@@ -812,6 +838,7 @@ render_f32_kernel(DevScene32 sc, CamParams cam, void* __restrict__ out_rgb, uint
     S.bound = sc.bound; S.nb4 = sc.n_bound4; S.cmax = sc.bound_cmax; S.rmax = sc.bound_rmax;
     S.gbound = sc.gbound; S.gcmax = sc.gbound_cmax; S.grmax = sc.gbound_rmax;
     S.sbound = sc.sbound; S.scmax = sc.sbound_cmax; S.srmax = sc.sbound_rmax;
+    S.gbox = sc.gbox; S.sbox = sc.sbox;
     if (kGlobal) {
         S.planes = sc.planes; S.usph = sc.usph; S.gsph = sc.gsph; S.pl_index = sc.pl_index; S.us_index = sc.us_index; S.gs_index = sc.gs_index;
         plL = sc.plL; usL = sc.usL; gset = sc.gset;
@@ -927,7 +954,7 @@ render_f32_kernel(DevScene32 sc, CamParams cam, void* __restrict__ out_rgb, uint
             else {
                 if (aa) acc = aa_tot * (1.0f / (float)aa_ntot);
                 // pixel finished: Canvas::write_pixel (src/canvas.rs:43-46)
-                size_t p = (size_t)(cam.dst_full ? py : pr) * cam.hsize + px;
+                size_t p = (size_t)(cam.dst_full ? py : (cam.shard_count > 1 ? cam.row0 + pr : pr)) * cam.hsize + px;
                 RTC_CHECK(px >= 0 && px < (int)cam.hsize && (cam.dst_full ? (py >= 0 && py < (int)cam.vsize) : (pr >= 0 && pr < cam.shard_rows)));
                 if (cam.out_format == RTC_OUT_F64_RGB) {
                     double* o = (double*)out_rgb + 3 * p;
@@ -969,7 +996,7 @@ render_f32_kernel(DevScene32 sc, CamParams cam, void* __restrict__ out_rgb, uint
                 px = tx * kTileX + (k & (kTileX - 1));
                 pr = ty * kTileY + k / kTileX;
                 if (px < (int)cam.hsize && pr < cam.shard_rows) {
-                    py = cam.row0 + (cam.shard_count > 1 ? shard_row_to_frame_row(pr, cam.tile_rows, cam.shard_index, cam.shard_count) : pr);
+                    py = cam.shard_count > 1 ? shard_row_to_frame_row(cam.row0 + pr, cam.tile_rows, cam.shard_index, cam.shard_count) : cam.row0 + pr;
                     have = true; sub = 0; acc = mk(0, 0, 0); hitbits = 0;
                     aa_tot = mk(0, 0, 0); aa_ntot = n_sub;
                     if (!(px < (int)cam.xlim && py < (int)cam.ylim)) sub = kSubOutside;  // outside the rect: stays black
@@ -1039,7 +1066,7 @@ render_f32_kernel(DevScene32 sc, CamParams cam, void* __restrict__ out_rgb, uint
                     const double2 a = W.d0[w], b = W.d1[w], c = W.d2[w];
                     double bt = __shfl_sync(full, pt, w);
                     int bi = __shfl_sync(full, pidx, w);
-                    coop_hit<kCubes>(S, R64, Q, p64::mk(a.x, a.y, b.x), p64::mk(b.y, c.x, c.y), bt, bi);
+                    coop_hit<kCubes>(S, R64, Q, p64::mk(a.x, a.y, b.x), p64::mk(b.y, c.x, c.y), W.queue, bt, bi);
                     if (lane == w) { pt = bt; pidx = bi; }
                 }
                 t64 = pt;
@@ -1061,7 +1088,7 @@ render_f32_kernel(DevScene32 sc, CamParams cam, void* __restrict__ out_rgb, uint
                 const double2 a = W.d0[w], b = W.d1[w], c = W.d2[w];
                 double n1, n2;
                 coop_containers<kCubes>(S, R64, Q, p64::mk(a.x, a.y, b.x), p64::mk(b.y, c.x, c.y), __shfl_sync(full, hit, w),
-                                        reinterpret_cast<unsigned*>(W.so), n1, n2);
+                                        reinterpret_cast<unsigned*>(W.so), W.queue, n1, n2);
                 if (lane == w) { n1c = n1; n2c = n2; }
             }
         }
@@ -1225,7 +1252,7 @@ render_f32_kernel(DevScene32 sc, CamParams cam, void* __restrict__ out_rgb, uint
                     const int w = __ffs(todo) - 1;
                     todo &= todo - 1u;
                     const RayQ Q = load_rayq(W, w);
-                    const bool sh = coop_shadow<kCubes>(S, uL, inside, Q, xyz(W.so[w]), xyz(W.sd[w]));
+                    const bool sh = coop_shadow<kCubes>(S, uL, inside, Q, xyz(W.so[w]), xyz(W.sd[w]), W.queue);
                     if (lane == w) shadowed = sh;
                 }
             } else if (hit >= 0) { shadowed = shadow32<kCubes>(S, pL, uL, inside, hp, lpos - hp); ++n_rays; }

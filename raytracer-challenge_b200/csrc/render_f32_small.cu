@@ -321,8 +321,8 @@ render_f32_small_kernel(const __grid_constant__ SmallParams P, void* __restrict_
             if (sub + 1 < (kAA ? aa_ntot : n_sub)) ++sub;
             else {                                            // Canvas::write_pixel (src/canvas.rs:43-46)
                 if (kAA) acc = aa_tot * (1.0f / (float)aa_ntot);
-                size_t p = (size_t)(P.dst_full ? py : pr) * (size_t)P.hsize + (size_t)px;
-                RTC_CHECK(px >= 0 && px < P.hsize && pr >= 0 && pr < P.shard_rows && py >= P.row0);
+                size_t p = (size_t)(P.dst_full ? py : (P.shard_count > 1 ? P.row0 + pr : pr)) * (size_t)P.hsize + (size_t)px;
+                RTC_CHECK(px >= 0 && px < P.hsize && pr >= 0 && pr < P.shard_rows && py >= 0);
                 if (kFmt == RTC_OUT_F64_RGB) {
                     double* o = (double*)out_rgb + 3 * p;
                     o[0] = (double)acc.x; o[1] = (double)acc.y; o[2] = (double)acc.z;
@@ -367,7 +367,7 @@ render_f32_small_kernel(const __grid_constant__ SmallParams P, void* __restrict_
                 px = wtx + (k & (kTileX - 1));
                 pr = wty + (k >> 3);
                 if (px < P.hsize && pr < P.shard_rows) {
-                    py = P.row0 + (P.shard_count > 1 ? shard_row_to_frame_row(pr, P.tile_rows, P.shard_index, P.shard_count) : pr);
+                    py = P.shard_count > 1 ? shard_row_to_frame_row(P.row0 + pr, P.tile_rows, P.shard_index, P.shard_count) : P.row0 + pr;
                     have = true; sub = 0; acc = mk(0.f, 0.f, 0.f); hitbits = 0;
                     if (kAA) { aa_tot = mk(0.f, 0.f, 0.f); aa_ntot = n_sub; }
                     if (!(px < P.xlim && py < P.ylim)) sub = kSubOutside;   // outside the rect: stays black
@@ -585,7 +585,7 @@ classify_tiles_small_kernel(const __grid_constant__ SmallParams P, unsigned* __r
         const int ty = t / P.tiles_x, tx = t - ty * P.tiles_x;
         const int px = min(tx * kTileX + kTileX / 2, P.hsize - 1);
         const int pr = min(ty * kTileY + kTileY / 2, P.shard_rows - 1);
-        const int py = P.row0 + (P.shard_count > 1 ? shard_row_to_frame_row(pr, P.tile_rows, P.shard_index, P.shard_count) : pr);
+        const int py = P.shard_count > 1 ? shard_row_to_frame_row(P.row0 + pr, P.tile_rows, P.shard_index, P.shard_count) : P.row0 + pr;
         const float fx = (float)px, fy = (float)py;          // the corner shared by the four centre pixels
         F3 dir = mk(fmaf(P.cam_dx[0], fx, fmaf(P.cam_dy[0], fy, P.cam_d0[0])),
                     fmaf(P.cam_dx[1], fx, fmaf(P.cam_dy[1], fy, P.cam_d0[1])),

@@ -376,7 +376,7 @@ render_f64_kernel(DevScene64 sc, CamParams cam, double* __restrict__ out_f64, fl
     const int px = sx / ss, pr = sy / ss;     // pixel x, compact shard row
     const bool in_image = px < (int)cam.hsize && pr < cam.shard_rows;
     int py = 0;
-    if (in_image) py = cam.row0 + (cam.shard_count > 1 ? shard_row_to_frame_row(pr, cam.tile_rows, cam.shard_index, cam.shard_count) : pr);
+    if (in_image) py = cam.shard_count > 1 ? shard_row_to_frame_row(cam.row0 + pr, cam.tile_rows, cam.shard_index, cam.shard_count) : cam.row0 + pr;
     const bool active = in_image && px < (int)cam.xlim && py < (int)cam.ylim;
 
     V3 result = mk(0., 0., 0.);
@@ -619,7 +619,7 @@ render_f64_kernel(DevScene64 sc, CamParams cam, double* __restrict__ out_f64, fl
 
     const bool writer = in_image && (ss == 1 || (((sx | sy) & 1) == 0));
     if (writer) {
-        size_t p = (size_t)(cam.dst_full ? py : pr) * cam.hsize + px;
+        size_t p = (size_t)(cam.dst_full ? py : (cam.shard_count > 1 ? cam.row0 + pr : pr)) * cam.hsize + px;
         RTC_CHECK(px >= 0 && px < (int)cam.hsize && (cam.dst_full ? (py >= 0 && py < (int)cam.vsize) : (pr >= 0 && pr < cam.shard_rows)));
         if (cam.out_format == RTC_OUT_F64_RGB) {
             out_f64[3 * p + 0] = result.x; out_f64[3 * p + 1] = result.y; out_f64[3 * p + 2] = result.z;

@@ -69,7 +69,7 @@ struct DeviceState {
     DevBuf<float4> pl32, us32, gs32, bound;
     DevBuf<int32_t> sph_index, pl_index, us_index, gs_index, gset;
     DevBuf<float> plL, usL;
-    DevBuf<float4> bound64, gbound, gbound64, sbound, sbound64;
+    DevBuf<float4> bound64, gbound, gbound64, sbound, sbound64, gbox, sbox;
     DevBuf<double> lights64;   // [n_lights][6]
     DevBuf<float4> lights32;   // [n_lights][2]
     DevBuf<ShadeRec64> rec64;
@@ -277,6 +277,7 @@ struct HostScene {
     std::vector<float4> gbound, gbound64; // one bounding sphere per kGroup consecutive entries of bound / bound64
     float gbound_cmax = 0.f, gbound_rmax = 0.f, gbound64_cmax = 0.f, gbound64_rmax = 0.f;
     std::vector<float4> sbound, sbound64; // one bounding sphere per 32 consecutive groups (a block of 256 entries)
+    std::vector<float4> gbox, sbox;       // the two upper levels of `bound` as axis-aligned boxes (lo, hi interleaved; DevScene32::gbox)
     float sbound_cmax = 0.f, sbound_rmax = 0.f, sbound64_cmax = 0.f, sbound64_rmax = 0.f;
     std::vector<ShadeRec64> rec64;
     std::vector<ShadeRec32> rec32;
@@ -423,6 +424,47 @@ bool group_bounds(std::vector<float4>& bound, int group, int pad_out, std::vecto
     while (gbound.size() % (size_t)pad_out) gbound.push_back(never);
     gcmax = (float)(cm * (1.0 + 1e-6)); grmax = (float)(rm * (1.0 + 1e-6));
     return true;
+}
+
+// Axis-aligned boxes around each `group` consecutive bounding spheres (cx, cy, cz, -R^2; w = +inf: padding, ignored), rounded
+// outwards to f32; an empty group gets an inverted box.  Output: lo, hi interleaved, padded to a multiple of pad_out entries.
+void sphere_boxes(const std::vector<float4>& bound, int group, int pad_out, std::vector<float4>& box) {
+    const float inf = std::numeric_limits<float>::infinity();
+    box.clear();
+    for (size_t g = 0; g < bound.size(); g += (size_t)group) {
+        double lo[3] = {1e300, 1e300, 1e300}, hi[3] = {-1e300, -1e300, -1e300};
+        bool any = false;
+        for (size_t k = g; k < std::min(bound.size(), g + (size_t)group); ++k) {
+            const float4& b = bound[k];
+            if (std::isinf(b.w)) continue;
+            const double r = std::sqrt(std::max(0.0, -(double)b.w)), c[3] = {b.x, b.y, b.z};
+            for (int a = 0; a < 3; ++a) { lo[a] = std::min(lo[a], c[a] - r); hi[a] = std::max(hi[a], c[a] + r); }
+            any = true;
+        }
+        if (!any) { box.push_back(make_float4(inf, inf, inf, 0.f)); box.push_back(make_float4(-inf, -inf, -inf, 0.f)); continue; }
+        auto down = [](double v) { float f = (float)v; return (double)f > v ? std::nextafterf(f, -std::numeric_limits<float>::infinity()) : f; };
+        auto up = [](double v) { float f = (float)v; return (double)f < v ? std::nextafterf(f, std::numeric_limits<float>::infinity()) : f; };
+        box.push_back(make_float4(down(lo[0]), down(lo[1]), down(lo[2]), 0.f));
+        box.push_back(make_float4(up(hi[0]), up(hi[1]), up(hi[2]), 0.f));
+    }
+    while ((box.size() / 2) % (size_t)pad_out) { box.push_back(make_float4(inf, inf, inf, 0.f)); box.push_back(make_float4(-inf, -inf, -inf, 0.f)); }
+}
+// boxes around each `group` consecutive boxes
+void box_boxes(const std::vector<float4>& in, int group, int pad_out, std::vector<float4>& box) {
+    const float inf = std::numeric_limits<float>::infinity();
+    box.clear();
+    for (size_t g = 0; g < in.size() / 2; g += (size_t)group) {
+        float lo[3] = {inf, inf, inf}, hi[3] = {-inf, -inf, -inf};
+        for (size_t k = g; k < std::min(in.size() / 2, g + (size_t)group); ++k) {
+            const float4 &l = in[2 * k], &h = in[2 * k + 1];
+            if (l.x > h.x) continue;   // inverted: empty
+            lo[0] = std::min(lo[0], l.x); lo[1] = std::min(lo[1], l.y); lo[2] = std::min(lo[2], l.z);
+            hi[0] = std::max(hi[0], h.x); hi[1] = std::max(hi[1], h.y); hi[2] = std::max(hi[2], h.z);
+        }
+        box.push_back(make_float4(lo[0], lo[1], lo[2], 0.f));
+        box.push_back(make_float4(hi[0], hi[1], hi[2], 0.f));
+    }
+    while ((box.size() / 2) % (size_t)pad_out) { box.push_back(make_float4(inf, inf, inf, 0.f)); box.push_back(make_float4(-inf, -inf, -inf, 0.f)); }
 }
 
 int flatten(const rtc_light* lights, size_t n_lights, const rtc_shape* shapes, size_t n, HostScene& hs) {
@@ -600,6 +642,7 @@ int flatten(const rtc_light* lights, size_t n_lights, const rtc_shape* shapes, s
             // eight entries per group, 32 groups per block (256 entries), padded so that a kernel can read whole blocks
             if (!group_bounds(hs.bound, kGroup, 32, hs.gbound, hs.gbound_cmax, hs.gbound_rmax) ||
                 !group_bounds(hs.gbound, 32, 32, hs.sbound, hs.sbound_cmax, hs.sbound_rmax)) hs.bound.clear();
+            else { sphere_boxes(hs.bound, kGroup, 32, hs.gbox); box_boxes(hs.gbox, 32, 32, hs.sbox); }
         }
     }
 
@@ -1034,7 +1077,7 @@ void rtc_context_destroy(rtc_context* ctx) {
     for (DeviceState& d : ctx->devs) {
         cudaSetDevice(d.dev);
         if (d.stream) cudaStreamSynchronize(d.stream);
-        d.sph64.release(); d.pl64.release(); d.pl32.release(); d.us32.release(); d.gs32.release(); d.us_index.release(); d.gs_index.release(); d.gset.release(); d.plL.release(); d.usL.release(); d.lights64.release(); d.lights32.release(); d.bound64.release(); d.gbound.release(); d.gbound64.release(); d.sbound.release(); d.sbound64.release(); d.bound.release();
+        d.sph64.release(); d.pl64.release(); d.pl32.release(); d.us32.release(); d.gs32.release(); d.us_index.release(); d.gs_index.release(); d.gset.release(); d.plL.release(); d.usL.release(); d.lights64.release(); d.lights32.release(); d.bound64.release(); d.gbound.release(); d.gbound64.release(); d.sbound.release(); d.sbound64.release(); d.bound.release(); d.gbox.release(); d.sbox.release();
         d.sph_index.release(); d.pl_index.release(); d.rec64.release(); d.rec32.release(); d.srec.release();
         d.rgb.release(); d.hit.release(); d.counters.release(); d.work.release(); d.order.release(); d.wait_status.release();
         if (d.ev_k0) cudaEventDestroy(d.ev_k0);
@@ -1086,6 +1129,8 @@ int rtc_scene_upload_lights(rtc_context* ctx, const rtc_light* light, size_t n_l
         CUDA_TRY(upload(d.gbound64, hs.gbound64, d.stream));
         CUDA_TRY(upload(d.sbound, hs.sbound, d.stream));
         CUDA_TRY(upload(d.sbound64, hs.sbound64, d.stream));
+        CUDA_TRY(upload(d.gbox, hs.gbox, d.stream));
+        CUDA_TRY(upload(d.sbox, hs.sbox, d.stream));
         CUDA_TRY(upload(d.sph_index, hs.sph_index, d.stream));
         CUDA_TRY(upload(d.pl_index, hs.pl_index, d.stream));
         CUDA_TRY(upload(d.rec64, hs.rec64, d.stream));
@@ -1117,6 +1162,7 @@ int rtc_scene_upload_lights(rtc_context* ctx, const rtc_light* light, size_t n_l
         d.s32.gbound = d.gbound.p; d.s32.gbound_cmax = hs.gbound_cmax; d.s32.gbound_rmax = hs.gbound_rmax;
         d.s64.sbound = d.sbound64.p; d.s64.sbound_cmax = hs.sbound64_cmax; d.s64.sbound_rmax = hs.sbound64_rmax;
         d.s32.sbound = d.sbound.p; d.s32.sbound_cmax = hs.sbound_cmax; d.s32.sbound_rmax = hs.sbound_rmax;
+        d.s32.gbox = d.gbox.p; d.s32.sbox = d.sbox.p;
         d.s32.bound = d.bound.p; d.s32.n_bound4 = (int)hs.bound.size(); d.s32.bound_cmax = hs.bound_cmax; d.s32.bound_rmax = hs.bound_rmax;
         for (int k = 0; k < 3; ++k) {
             d.s64.light_pos[k] = light->position[k]; d.s64.light_int[k] = light->intensity[k];
@@ -1404,6 +1450,23 @@ int rtc_scene_selfcheck(const rtc_light* lights, size_t n_lights, const rtc_shap
     if (!hs.bound.empty()) {
         out->n_groups_f32 = (int32_t)(hs.bound.size() / kGroup); out->n_blocks_f32 = (int32_t)((hs.bound.size() / kGroup + 31) / 32);
         out->worst_enclosure_f32 = std::max(worst(hs.bound, hs.gbound, kGroup), worst(hs.gbound, hs.sbound, 32));
+        // the box form of the two upper levels: every entry's bounding sphere inside its group's box, every group's box inside its block's
+        double wb = -1.0;
+        for (size_t i = 0; i < hs.bound.size(); ++i) {
+            const float4& c = hs.bound[i];
+            if (std::isinf(c.w)) continue;
+            const float4 &l = hs.gbox[2 * (i / kGroup)], &h = hs.gbox[2 * (i / kGroup) + 1];
+            const double r = std::sqrt(std::max(0.0, -(double)c.w)), p[3] = {c.x, c.y, c.z}, lo[3] = {l.x, l.y, l.z}, hi[3] = {h.x, h.y, h.z};
+            for (int a = 0; a < 3; ++a) wb = std::max(wb, std::max(lo[a] - (p[a] - r), (p[a] + r) - hi[a]) / std::max(r, 1e-300));
+        }
+        for (size_t g = 0; g < hs.gbox.size() / 2; ++g) {
+            const float4 &l = hs.gbox[2 * g], &h = hs.gbox[2 * g + 1];
+            if (l.x > h.x) continue;
+            const float4 &L = hs.sbox[2 * (g / 32)], &H = hs.sbox[2 * (g / 32) + 1];
+            const double over = std::max({(double)L.x - l.x, (double)L.y - l.y, (double)L.z - l.z, (double)h.x - H.x, (double)h.y - H.y, (double)h.z - H.z});
+            wb = std::max(wb, over > 0.0 ? 1.0 : -1.0);
+        }
+        out->worst_enclosure_f32 = std::max(out->worst_enclosure_f32, wb);
     }
     if (!hs.bound64.empty()) {
         out->n_groups_f64 = (int32_t)(hs.bound64.size() / kGroup); out->n_blocks_f64 = (int32_t)((hs.bound64.size() / kGroup + 31) / 32);
@@ -1517,25 +1580,47 @@ int render_shard(rtc_context* ctx, DeviceState& d, const rtc_camera* cam, const 
     if (out_hit_mask) CUDA_TRY(d.hit.ensure((size_t)shard_rows * hsize));
     if (want_counters) CUDA_TRY(cudaMemsetAsync(d.counters.p, 0, sizeof(Counters), d.stream));
     CUDA_TRY(cudaEventRecord(d.ev_k0, d.stream));
-    int rc = launch_on(d, cp, opts->precision, opts->flags, d.rgb.p, out_hit_mask ? d.hit.p : nullptr, want_counters ? d.counters.p : nullptr, d.stream);
-    if (rc != RTC_OK) return rc;
-    CUDA_TRY(cudaEventRecord(d.ev_k1, d.stream));
-    if (want_counters) CUDA_TRY(cudaMemcpyAsync(pinned_counter, d.counters.p, sizeof(Counters), cudaMemcpyDeviceToHost, d.stream));
-    CUDA_TRY(cudaStreamWaitEvent(d.copy_stream, d.ev_k1, 0));
     const int n_tiles = (shard_rows + tile_rows - 1) / tile_rows;
     double deliver_ms = 0.0;
     unsigned char* stage_hit = ctx->pinned_hit ? ctx->pinned_hit + stage_row0 * hsize : nullptr;
+    int rc = RTC_OK;
+    int n_launches = 1;
     if (direct) {
+        // Row bands of whole tiles, one launch each: band b's tiles cross PCIe (pitched 2-D DMA: compact rows -> their frame
+        // rows in the registered caller buffer) while band b+1 renders.  Small-scene frames only: every launch of a big
+        // scene ends in a long tail of deep ray trees.
         const int n_full = shard_rows / tile_rows;                       // only the frame's last tile can be short
         const size_t tile_bytes = (size_t)tile_rows * row_bytes;
-        unsigned char* dst0 = user + (size_t)shard_index * tile_bytes;   // frame row of the shard's tile 0
-        if (n_full > 0)
-            CUDA_TRY(cudaMemcpy2DAsync(dst0, tile_bytes * (size_t)shard_count, d.rgb.p, tile_bytes, tile_bytes, (size_t)n_full, cudaMemcpyDeviceToHost, d.copy_stream));
-        if (n_full < n_tiles) {
-            const int r0 = n_full * tile_rows;
-            const size_t fr = (size_t)shard_row_to_frame_row(r0, tile_rows, shard_index, shard_count);
-            CUDA_TRY(cudaMemcpyAsync(user + fr * row_bytes, d.rgb.p + (size_t)r0 * row_bytes, (size_t)(shard_rows - r0) * row_bytes, cudaMemcpyDeviceToHost, d.copy_stream));
+        const bool small_kernel = opts->precision == RTC_PRECISION_F32_FAST && d.small_ok && !(opts->flags & RTC_OPT_F32_GENERAL_KERNEL);
+        const int want_bands = d.s64.n_shapes > 256 ? 1 : (shard_bytes >= (32u << 20) ? 4 : (shard_bytes >= (8u << 20) ? 2 : 1));
+        const int n_bands = std::max(1, std::min(want_bands, small_kernel || opts->precision == RTC_PRECISION_F64_PARITY ? n_tiles : 1));
+        n_launches = 0;
+        for (int b = 0; b < n_bands; ++b) {
+            const int t0b = (int)((long long)n_tiles * b / n_bands), t1b = (int)((long long)n_tiles * (b + 1) / n_bands);
+            if (t1b <= t0b) continue;
+            const int r0 = t0b * tile_rows, r1 = std::min(shard_rows, t1b * tile_rows);
+            CamParams cb = cp;
+            cb.row0 = r0; cb.shard_rows = r1 - r0;
+            // buffers are passed at their base: the kernels address compact row row0 + r (shard_count > 1) themselves; a
+            // one-shard "shard" (shard_count == 1 never comes here) is not banded this way
+            rc = launch_on(d, cb, opts->precision, opts->flags, d.rgb.p, out_hit_mask ? d.hit.p : nullptr, want_counters ? d.counters.p : nullptr, d.stream);
+            if (rc != RTC_OK) return rc;
+            ++n_launches;
+            CUDA_TRY(cudaEventRecord(d.ev_band[b], d.stream));
+            CUDA_TRY(cudaStreamWaitEvent(d.copy_stream, d.ev_band[b], 0));
+            const int full_hi = std::min(t1b, n_full);
+            if (full_hi > t0b)
+                CUDA_TRY(cudaMemcpy2DAsync(user + ((size_t)t0b * shard_count + shard_index) * tile_bytes, tile_bytes * (size_t)shard_count,
+                                           d.rgb.p + (size_t)t0b * tile_bytes, tile_bytes, tile_bytes, (size_t)(full_hi - t0b), cudaMemcpyDeviceToHost, d.copy_stream));
+            if (t1b > n_full) {   // the frame's last, shorter tile
+                const int rs = n_full * tile_rows;
+                const size_t fr = (size_t)shard_row_to_frame_row(rs, tile_rows, shard_index, shard_count);
+                CUDA_TRY(cudaMemcpyAsync(user + fr * row_bytes, d.rgb.p + (size_t)rs * row_bytes, (size_t)(shard_rows - rs) * row_bytes, cudaMemcpyDeviceToHost, d.copy_stream));
+            }
         }
+        CUDA_TRY(cudaEventRecord(d.ev_k1, d.stream));
+        if (want_counters) CUDA_TRY(cudaMemcpyAsync(pinned_counter, d.counters.p, sizeof(Counters), cudaMemcpyDeviceToHost, d.stream));
+        CUDA_TRY(cudaStreamWaitEvent(d.copy_stream, d.ev_k1, 0));
         if (out_hit_mask) CUDA_TRY(cudaMemcpyAsync(stage_hit, d.hit.p, (size_t)shard_rows * hsize, cudaMemcpyDeviceToHost, d.copy_stream));
         CUDA_TRY(cudaStreamSynchronize(d.copy_stream));
         if (out_hit_mask)
@@ -1544,6 +1629,11 @@ int render_shard(rtc_context* ctx, DeviceState& d, const rtc_camera* cam, const 
                 std::memcpy(out_hit_mask + (size_t)shard_row_to_frame_row(r0, tile_rows, shard_index, shard_count) * hsize, stage_hit + (size_t)r0 * hsize, (size_t)(r1 - r0) * hsize);
             }
     } else {
+        rc = launch_on(d, cp, opts->precision, opts->flags, d.rgb.p, out_hit_mask ? d.hit.p : nullptr, want_counters ? d.counters.p : nullptr, d.stream);
+        if (rc != RTC_OK) return rc;
+        CUDA_TRY(cudaEventRecord(d.ev_k1, d.stream));
+        if (want_counters) CUDA_TRY(cudaMemcpyAsync(pinned_counter, d.counters.p, sizeof(Counters), cudaMemcpyDeviceToHost, d.stream));
+        CUDA_TRY(cudaStreamWaitEvent(d.copy_stream, d.ev_k1, 0));
         unsigned char* staged = ctx->pinned_rgb + stage_row0 * row_bytes;
         const int n_chunks = std::max(1, std::min(n_tiles, shard_bytes >= (4u << 20) ? 4 : 1));
         int chunk_t0[5];
@@ -1578,7 +1668,7 @@ int render_shard(rtc_context* ctx, DeviceState& d, const rtc_camera* cam, const 
     float k_ms = 0.f;
     CUDA_TRY(cudaEventElapsedTime(&k_ms, d.ev_k0, d.ev_k1));
     if (want_counters) { st.rays = pinned_counter->rays; st.primary_hits = pinned_counter->primary_hits; st.shaded_hits = pinned_counter->shaded_hits; st.shadow_rays = pinned_counter->shadow_rays; }
-    st.kernel_launches = 1;
+    st.kernel_launches = (uint64_t)n_launches;
     st.kernel_ms = k_ms;
     st.total_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
     st.d2h_ms = st.total_ms - k_ms;

@@ -122,6 +122,12 @@ struct DevScene32 {
     float gbound_cmax, gbound_rmax;
     const float4* sbound;           // one per 32 consecutive groups (a block of 256 entries), padded to a multiple of 32
     float sbound_cmax, sbound_rmax;
+    // The same two upper levels as axis-aligned boxes (lo, hi interleaved: two float4 per entry; padded to multiples of 32
+    // entries, padding never read as a candidate).  Eight scattered small spheres fill well under 1 % of the sphere around
+    // them and Morton runs are elongated, so boxes turn away several times more rays than the bounding spheres do; the
+    // warp-cooperative queries of the fast kernel test boxes at the block and group level, spheres at the entries.
+    const float4* gbox;             // [2 * groups]
+    const float4* sbox;             // [2 * blocks]
     float light_pos[3];        // light 0
     float light_int[3];
     int n_lights;              // rtc_scene_upload_lights: plL / usL hold n_lights rows; lights 1.. read them from global memory
@@ -187,7 +193,8 @@ struct CamParams {
     int32_t shard_rows;   // rows in this shard's compact buffer
     int32_t out_format;   // RTC_OUT_*
     int32_t dst_full;     // 1: the destination is a full frame (rows at their frame positions), not the compact shard buffer
-    int32_t row0;         // first frame row of this launch (rtc_render's row bands: shard_count == 1, rows [row0, row0 + shard_rows))
+    int32_t row0;         // row bands (one launch each): shard_count == 1: first FRAME row, the launch renders rows [row0, row0 + shard_rows);
+                          // shard_count > 1: first COMPACT row of the shard, the launch renders compact rows [row0, row0 + shard_rows)
 };
 
 struct Counters {

@@ -41,7 +41,8 @@ def test_direct_delivery_into_a_registered_buffer_equals_staged(rtc, renderer, p
 
 
 @pytest.mark.parametrize("precision", [0, 1])
-@pytest.mark.parametrize("count,tile,size", [(2, 4, (200, 117)), (3, 16, (200, 117)), (8, 4, (1920, 1080)), (4, 4, (64, 3))])
+@pytest.mark.parametrize("count,tile,size", [(2, 4, (200, 117)), (3, 16, (200, 117)), (8, 4, (1920, 1080)), (4, 4, (64, 3)),
+                                             (2, 4, (3840, 2160)), (3, 20, (2560, 1441))])   # the last two: several row bands per shard
 def test_shards_deliver_directly_into_one_registered_frame(rtc, renderer, precision, count, tile, size):
     """What N rank processes do with a registered frame in shared host memory: every shard's rows arrive by pitched 2-D
     DMA at their frame rows (the frame's last, shorter tile by a 1-D copy); all shards together are the unsharded frame."""
