@@ -134,46 +134,79 @@ __device__ __forceinline__ RayQ make_rayq(const Streams32& S, F3 o, F3 d) {
 // a warp min picks the next block, and the walk stops when that block starts beyond `hi` — for radiance rays the
 // nearest hit so far, which the exact tests keep shrinking.
 // A ray's query constants travel through shared memory: its lane publishes them, all lanes read them back (broadcast).
-struct WarpSlots {
-    float4* qa; float4* qb; float4* qc;       // RayQ: (dh, od) (m, len) (E, margin, -, -)
-    float4* qd; float4* qe; float4* qf;       // RayQ: inv, c0, c1
-    double2* d0; double2* d1; double2* d2;    // the ray in f64: (ox oy) (oz dx) (dy dz)
-    float4* so; float4* sd;                   // shadow ray in f32: (o, 0) (d, 0); the containers query keeps its parity words in `so`
-    int* queue;                               // candidate groups of the block being visited
-};
-constexpr int kWarpSlotBytes = 12 * 32 * 16;
+// The slots are addressed through explicit 32-bit shared-window addresses: indexing generic pointers made ptxas rebuild
+// the window base inside every divergent region (7 % of the executed instructions in the first version).
+struct WarpSlots { unsigned base; unsigned* parity; };   // byte address of the warp's slab; the containers query's parity words (generic)
+constexpr unsigned kOffQa = 0, kOffQb = 512, kOffQc = 1024, kOffQd = 1536, kOffQe = 2048, kOffQf = 2560;   // RayQ: (dh, od) (m, len) (E, margin, -, -) inv c0 c1
+constexpr unsigned kOffD0 = 3072, kOffD1 = 3584, kOffD2 = 4096;                                          // the ray in f64: (ox oy) (oz dx) (dy dz)
+constexpr unsigned kOffSo = 4608, kOffSd = 5120;                                                          // shadow ray in f32: (o, 0) (d, 0)
+constexpr unsigned kOffQueue = 5632, kOffParity = 5760;                                                   // candidate groups of the block being visited; parity words
+constexpr unsigned kOffKept = 6144;      // the negative-t entries the containers query keeps: kKeptCap x (t : f64, (id, ord) : 2 x s32)
+constexpr int kKeptCap = 64;
+constexpr int kWarpSlotBytes = 6144 + kKeptCap * 16;
+__device__ __forceinline__ float4 slds4(unsigned addr) {
+    float4 v;
+    asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(addr) : "memory");
+    return v;
+}
+__device__ __forceinline__ void ssts4(unsigned addr, float4 v) {
+    asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+}
+__device__ __forceinline__ double2 sldsd2(unsigned addr) {
+    double2 v;
+    asm volatile("ld.shared.v2.f64 {%0, %1}, [%2];" : "=d"(v.x), "=d"(v.y) : "r"(addr) : "memory");
+    return v;
+}
+__device__ __forceinline__ void sstsd2(unsigned addr, double2 v) {
+    asm volatile("st.shared.v2.f64 [%0], {%1, %2};" ::"r"(addr), "d"(v.x), "d"(v.y) : "memory");
+}
+__device__ __forceinline__ int sldsi(unsigned addr) {
+    int v;
+    asm volatile("ld.shared.s32 %0, [%1];" : "=r"(v) : "r"(addr) : "memory");
+    return v;
+}
+__device__ __forceinline__ void sstsi(unsigned addr, int v) { asm volatile("st.shared.s32 [%0], %1;" ::"r"(addr), "r"(v) : "memory"); }
 __device__ __forceinline__ WarpSlots warp_slots(void* smem_base) {
     WarpSlots W;
     char* base = reinterpret_cast<char*>(smem_base) + (threadIdx.x >> 5) * kWarpSlotBytes;
-    W.qa = reinterpret_cast<float4*>(base); W.qb = W.qa + 32; W.qc = W.qb + 32; W.qd = W.qc + 32; W.qe = W.qd + 32; W.qf = W.qe + 32;
-    W.d0 = reinterpret_cast<double2*>(W.qf + 32); W.d1 = W.d0 + 32; W.d2 = W.d1 + 32;
-    W.so = reinterpret_cast<float4*>(W.d2 + 32); W.sd = W.so + 32;
-    W.queue = reinterpret_cast<int*>(W.sd + 32);
+    W.base = (unsigned)__cvta_generic_to_shared(base);
+    W.parity = reinterpret_cast<unsigned*>(base + kOffParity);
     return W;
 }
 __device__ __forceinline__ void publish_rayq(const WarpSlots& W, int lane, const RayQ& q) {
-    W.qa[lane] = make_float4(q.dh.x, q.dh.y, q.dh.z, q.od);
-    W.qb[lane] = make_float4(q.m.x, q.m.y, q.m.z, q.len);
-    W.qc[lane] = make_float4(q.E, q.margin, 0.f, 0.f);
-    W.qd[lane] = make_float4(q.inv.x, q.inv.y, q.inv.z, 0.f);
-    W.qe[lane] = make_float4(q.c0.x, q.c0.y, q.c0.z, 0.f);
-    W.qf[lane] = make_float4(q.c1.x, q.c1.y, q.c1.z, 0.f);
+    const unsigned a = W.base + 16u * (unsigned)lane;
+    ssts4(a + kOffQa, make_float4(q.dh.x, q.dh.y, q.dh.z, q.od));
+    ssts4(a + kOffQb, make_float4(q.m.x, q.m.y, q.m.z, q.len));
+    ssts4(a + kOffQc, make_float4(q.E, q.margin, 0.f, 0.f));
+    ssts4(a + kOffQd, make_float4(q.inv.x, q.inv.y, q.inv.z, 0.f));
+    ssts4(a + kOffQe, make_float4(q.c0.x, q.c0.y, q.c0.z, 0.f));
+    ssts4(a + kOffQf, make_float4(q.c1.x, q.c1.y, q.c1.z, 0.f));
 }
 __device__ __forceinline__ RayQ load_rayq(const WarpSlots& W, int w) {
-    const float4 a = W.qa[w], b = W.qb[w], c = W.qc[w], d = W.qd[w], e = W.qe[w], f = W.qf[w];
+    const unsigned x = W.base + 16u * (unsigned)w;
+    const float4 a = slds4(x + kOffQa), b = slds4(x + kOffQb), c = slds4(x + kOffQc), d = slds4(x + kOffQd), e = slds4(x + kOffQe), f = slds4(x + kOffQf);
     RayQ q;
     q.dh = mk(a.x, a.y, a.z); q.od = a.w; q.m = mk(b.x, b.y, b.z); q.len = b.w;
     q.E = c.x; q.margin = c.y;
     q.inv = mk(d.x, d.y, d.z); q.c0 = mk(e.x, e.y, e.z); q.c1 = mk(f.x, f.y, f.z);
     return q;
 }
+__device__ __forceinline__ void publish_ray64(const WarpSlots& W, int lane, p64::V3 o, p64::V3 d) {
+    const unsigned a = W.base + 16u * (unsigned)lane;
+    sstsd2(a + kOffD0, make_double2(o.x, o.y)); sstsd2(a + kOffD1, make_double2(o.z, d.x)); sstsd2(a + kOffD2, make_double2(d.y, d.z));
+}
+__device__ __forceinline__ void load_ray64(const WarpSlots& W, int w, p64::V3& o, p64::V3& d) {
+    const unsigned x = W.base + 16u * (unsigned)w;
+    const double2 a = sldsd2(x + kOffD0), b = sldsd2(x + kOffD1), c = sldsd2(x + kOffD2);
+    o = p64::mk(a.x, a.y, b.x); d = p64::mk(b.y, c.x, c.y);
+}
 
 // One ray (Q, warp-uniform), all 32 lanes.  [lo, hi]: the positions along the ray the query cares about (rounding margin E
 // included by the caller); `hi` is read again before every test, so `step` may shrink it.  step(c, i) is called by ALL
 // lanes once per member step — c says this lane holds candidate entry i of the bound stream — and returns true
-// (warp-uniform) to end the query.  `queue`: 32 ints of the warp's shared memory.
+// (warp-uniform) to end the query.  `queue`: shared-window address of 32 ints of the warp's slab.
 template <typename Step>
-__device__ __forceinline__ void warp_query(const Streams32& S, const RayQ& Q, float lo, float& hi, int* queue, Step&& step) {
+__device__ __forceinline__ void warp_query(const Streams32& S, const RayQ& Q, float lo, float& hi, unsigned queue, Step&& step) {
     const unsigned full = 0xffffffffu;
     const int lane = threadIdx.x & 31;
     const F3 dh = Q.dh, m = Q.m;
@@ -222,13 +255,13 @@ __device__ __forceinline__ void warp_query(const Streams32& S, const RayQ& Q, fl
             if (gm == 0u) continue;
             // the candidate groups, compacted into the warp's queue; then four groups per step: lane l tests member (l & 7)
             const int n_c = __popc(gm);
-            if (gp) queue[__popc(gm & ((1u << lane) - 1u))] = gidx;
+            if (gp) sstsi(queue + 4u * (unsigned)__popc(gm & ((1u << lane) - 1u)), gidx);
             __syncwarp();
             for (int s0 = 0; s0 < n_c; s0 += 4) {
                 const int qi = s0 + (lane >> 3);
                 bool c = false;
                 int i = 0;
-                if (qi < n_c) { i = 8 * queue[qi] + (lane & 7); RTC_CHECK(i >= 0 && i < S.nb4); c = sphere_test(S.bound[i]); }
+                if (qi < n_c) { i = 8 * sldsi(queue + 4u * (unsigned)qi) + (lane & 7); RTC_CHECK(i >= 0 && i < S.nb4); c = sphere_test(S.bound[i]); }
                 if (step(c, i)) return;
             }
             __syncwarp();   // the queue is free again
@@ -537,7 +570,7 @@ __device__ __forceinline__ bool shadow_planes32(const Streams32& S, const float*
 }
 // ... and the solids are an any-hit segment query by the whole warp: [0, |light - p|], over at the first occluder.
 template <bool kCubes>
-__device__ __forceinline__ bool coop_shadow(const Streams32& S, const float* __restrict__ usL, bool light_inside, const RayQ& Q, F3 o, F3 d, int* queue) {
+__device__ __forceinline__ bool coop_shadow(const Streams32& S, const float* __restrict__ usL, bool light_inside, const RayQ& Q, F3 o, F3 d, unsigned queue) {
     const float inv_a = rcp(dot(d, d));
     float hi = fmaf(Q.len, 1.000002f, Q.E);
     bool shadowed = false;
@@ -595,7 +628,7 @@ __device__ __forceinline__ void intersect_mixed(const Streams32& S, const ShadeR
 // in as the planes' result and are warp-uniform throughout: every candidate's root is broadcast and taken by all lanes.
 template <bool kCubes>
 __device__ __forceinline__ void coop_hit(const Streams32& S, const ShadeRec64* __restrict__ R64, const RayQ& Q, p64::V3 od, p64::V3 dd,
-                                         int* queue, double& best_t, int& best_idx) {
+                                         unsigned queue, double& best_t, int& best_idx) {
     const unsigned full = 0xffffffffu;
     // positions beyond the nearest hit found so far cannot hold the hit (an equal t loses or wins by shape index: kept by the margin)
     auto bound_of = [&](double t) { return fmaf(__double2float_ru(t) * Q.len, 1.000002f, Q.E); };
@@ -668,9 +701,10 @@ __device__ __noinline__ void containers_mixed(const Streams32& S, const ShadeRec
 // warp-uniform registers.
 template <bool kCubes>
 __device__ __forceinline__ void coop_containers(const Streams32& S, const ShadeRec64* __restrict__ R64, const RayQ& Q, p64::V3 od, p64::V3 dd,
-                                                int hit_idx, unsigned* parity, int* queue, double& n1, double& n2) {
+                                                int hit_idx, unsigned* parity, unsigned queue, unsigned kept, double& n1, double& n2) {
     const unsigned full = 0xffffffffu;
     const int lane = threadIdx.x & 31;
+    int n_kept = 0;   // pass 0 also keeps the entries (warp-uniform count): with at most kKeptCap of them pass 1 reads them back instead of querying again
     __syncwarp();
     if (lane < 8) parity[lane] = 0u;
     __syncwarp();
@@ -680,9 +714,23 @@ __device__ __forceinline__ void coop_containers(const Streams32& S, const ShadeR
     for (int pass = 0; pass < 2; ++pass) {
         auto entry = [&](double t, int idx, int root) {     // called with warp-uniform arguments
             const int id = R64[idx].world_id & 255;
-            if (pass == 0) { if (lane == 0) parity[id >> 5] ^= 1u << (id & 31); }
+            if (pass == 0) {
+                if (lane == 0) {
+                    parity[id >> 5] ^= 1u << (id & 31);
+                    if (n_kept < kKeptCap) sstsd2(kept + 16u * (unsigned)n_kept, make_double2(t, __hiloint2double(id, 2 * idx + root)));
+                }
+                ++n_kept;
+            }
             else if ((parity[id >> 5] >> (id & 31)) & 1u) { p64::Cont e; e.t = t; e.ord = 2 * idx + root; e.idx = idx; e.id = id; p64::offer(e, top1, top2); }
         };
+        if (pass == 1 && n_kept <= kKeptCap) {   // the kept entries, in the order pass 0 met them (the container rule is order-free)
+            for (int k = 0; k < n_kept; ++k) {
+                const double2 e = sldsd2(kept + 16u * (unsigned)k);
+                const int ord = __double2loint(e.y), id = __double2hiint(e.y);
+                if ((parity[id >> 5] >> (id & 31)) & 1u) { p64::Cont c; c.t = e.x; c.ord = ord; c.idx = ord >> 1; c.id = id; p64::offer(c, top1, top2); }
+            }
+            break;
+        }
         for (int p0 = 0; p0 < S.np; p0 += 32) {
             double t = 0.0;
             int idx = 0;
@@ -1055,7 +1103,7 @@ render_f32_kernel(DevScene32 sc, CamParams cam, void* __restrict__ out_rgb, uint
                     ++n_rays;
                     planes_mixed(S, R64, rod, rdd, pt, pidx);
                     publish_rayq(W, lane, make_rayq(S, ro, rd));
-                    W.d0[lane] = make_double2(rod.x, rod.y); W.d1[lane] = make_double2(rod.z, rdd.x); W.d2[lane] = make_double2(rdd.y, rdd.z);
+                    publish_ray64(W, lane, rod, rdd);
                 }
                 __syncwarp();
                 unsigned todo = __ballot_sync(full, has_ray);
@@ -1063,10 +1111,11 @@ render_f32_kernel(DevScene32 sc, CamParams cam, void* __restrict__ out_rgb, uint
                     const int w = __ffs(todo) - 1;
                     todo &= todo - 1u;
                     const RayQ Q = load_rayq(W, w);
-                    const double2 a = W.d0[w], b = W.d1[w], c = W.d2[w];
+                    p64::V3 o64, d64;
+                    load_ray64(W, w, o64, d64);
                     double bt = __shfl_sync(full, pt, w);
                     int bi = __shfl_sync(full, pidx, w);
-                    coop_hit<kCubes>(S, R64, Q, p64::mk(a.x, a.y, b.x), p64::mk(b.y, c.x, c.y), W.queue, bt, bi);
+                    coop_hit<kCubes>(S, R64, Q, o64, d64, W.base + kOffQueue, bt, bi);
                     if (lane == w) { pt = bt; pidx = bi; }
                 }
                 t64 = pt;
@@ -1085,10 +1134,10 @@ render_f32_kernel(DevScene32 sc, CamParams cam, void* __restrict__ out_rgb, uint
                 const int w = __ffs(todo) - 1;
                 todo &= todo - 1u;
                 const RayQ Q = load_rayq(W, w);
-                const double2 a = W.d0[w], b = W.d1[w], c = W.d2[w];
+                p64::V3 o64, d64;
+                load_ray64(W, w, o64, d64);
                 double n1, n2;
-                coop_containers<kCubes>(S, R64, Q, p64::mk(a.x, a.y, b.x), p64::mk(b.y, c.x, c.y), __shfl_sync(full, hit, w),
-                                        reinterpret_cast<unsigned*>(W.so), W.queue, n1, n2);
+                coop_containers<kCubes>(S, R64, Q, o64, d64, __shfl_sync(full, hit, w), W.parity, W.base + kOffQueue, W.base + kOffKept, n1, n2);
                 if (lane == w) { n1c = n1; n2c = n2; }
             }
         }
@@ -1243,7 +1292,8 @@ render_f32_kernel(DevScene32 sc, CamParams cam, void* __restrict__ out_rgb, uint
                     if (!shadowed) {
                         todo_me = true;
                         publish_rayq(W, lane, make_rayq(S, hp, sd));
-                        W.so[lane] = make_float4(hp.x, hp.y, hp.z, 0.f); W.sd[lane] = make_float4(sd.x, sd.y, sd.z, 0.f);
+                        ssts4(W.base + kOffSo + 16u * (unsigned)lane, make_float4(hp.x, hp.y, hp.z, 0.f));
+                        ssts4(W.base + kOffSd + 16u * (unsigned)lane, make_float4(sd.x, sd.y, sd.z, 0.f));
                     }
                 }
                 __syncwarp();
@@ -1252,7 +1302,8 @@ render_f32_kernel(DevScene32 sc, CamParams cam, void* __restrict__ out_rgb, uint
                     const int w = __ffs(todo) - 1;
                     todo &= todo - 1u;
                     const RayQ Q = load_rayq(W, w);
-                    const bool sh = coop_shadow<kCubes>(S, uL, inside, Q, xyz(W.so[w]), xyz(W.sd[w]), W.queue);
+                    const bool sh = coop_shadow<kCubes>(S, uL, inside, Q, xyz(slds4(W.base + kOffSo + 16u * (unsigned)w)),
+                                                        xyz(slds4(W.base + kOffSd + 16u * (unsigned)w)), W.base + kOffQueue);
                     if (lane == w) shadowed = sh;
                 }
             } else if (hit >= 0) { shadowed = shadow32<kCubes>(S, pL, uL, inside, hp, lpos - hp); ++n_rays; }

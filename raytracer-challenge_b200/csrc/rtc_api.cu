@@ -355,36 +355,43 @@ bool bounding_sphere(const double* inv, double unit_radius, double c[3], double&
 // The intersect streams of a scene are read front to back by every ray (brute force, World::intersect
 // src/shape.rs:677-683), so their order is free as long as the index arrays follow: hit selection takes the smallest t
 // (ties: the parity kernel compares shape indices, the fast kernels take the first in stream order — equal f32 roots of
-// different shapes are not a case the tolerance cares about).  Streams with >= kSortMin entries are put in Morton order
-// of the shapes' centres, so that kGroup consecutive entries are neighbours in space and one bounding sphere around
+// different shapes are not a case the tolerance cares about).  Streams with >= kSortMin entries are put in a spatial order
+// of the shapes' centres (spatial_order), so that kGroup consecutive entries are neighbours in space and one bounding sphere around
 // them (DevScene32::gbound / DevScene64::gbound) lets a ray skip all of them with one nine-FFMA line-distance test.
 constexpr size_t kSortMin = 64;
 constexpr int kGroup = 8;
 
-std::vector<int> morton_order(const std::vector<std::array<double, 3>>& c) {
+std::vector<int> spatial_order(const std::vector<std::array<double, 3>>& c) {
+    // Recursive median split along the longest extent of the centres (a k-d order).  Splits fall on multiples of the
+    // block size (256 entries) while a node is larger than a block, and on multiples of the group size (8) below, so
+    // that every block and every group of the stream is one compact subtree: its bounding box is near-cubic, where runs
+    // of a Morton curve are elongated and jump (simulated on C4: 5.4 instead of 11.5 candidate groups per ray;
+    // measured: C4 4K fast mode 142 -> 109 ms, parity mode 177 -> 72 ms).
     const size_t n = c.size();
     std::vector<int> perm(n);
     for (size_t i = 0; i < n; ++i) perm[i] = (int)i;
     if (n < kSortMin) return perm;
-    double lo[3] = {1e300, 1e300, 1e300}, hi[3] = {-1e300, -1e300, -1e300};
     for (const auto& p : c)
-        for (int k = 0; k < 3; ++k) { if (!std::isfinite(p[k])) return perm; lo[k] = std::min(lo[k], p[k]); hi[k] = std::max(hi[k], p[k]); }
-    std::vector<uint32_t> code(n);
-    auto spread = [](uint32_t v) {   // 10 bits -> every third bit
-        v &= 1023u;
-        v = (v | (v << 16)) & 0x030000FFu; v = (v | (v << 8)) & 0x0300F00Fu;
-        v = (v | (v << 4)) & 0x030C30C3u; v = (v | (v << 2)) & 0x09249249u;
-        return v;
-    };
-    for (size_t i = 0; i < n; ++i) {
-        uint32_t q[3];
-        for (int k = 0; k < 3; ++k) {
-            const double ext = hi[k] - lo[k];
-            q[k] = ext > 0.0 ? (uint32_t)std::min(1023.0, (c[i][k] - lo[k]) / ext * 1024.0) : 0u;
-        }
-        code[i] = spread(q[0]) | (spread(q[1]) << 1) | (spread(q[2]) << 2);
+        for (int k = 0; k < 3; ++k) if (!std::isfinite(p[k])) return perm;
+    struct Node { size_t b, e; };
+    std::vector<Node> stack{{0, n}};
+    while (!stack.empty()) {
+        const Node nd = stack.back();
+        stack.pop_back();
+        const size_t len = nd.e - nd.b;
+        if (len <= (size_t)kGroup) continue;
+        double lo[3] = {1e300, 1e300, 1e300}, hi[3] = {-1e300, -1e300, -1e300};
+        for (size_t i = nd.b; i < nd.e; ++i)
+            for (int k = 0; k < 3; ++k) { lo[k] = std::min(lo[k], c[perm[i]][k]); hi[k] = std::max(hi[k], c[perm[i]][k]); }
+        int ax = 0;
+        for (int k = 1; k < 3; ++k) if (hi[k] - lo[k] > hi[ax] - lo[ax]) ax = k;
+        std::sort(perm.begin() + (long)nd.b, perm.begin() + (long)nd.e, [&](int x, int y) { return c[x][ax] < c[y][ax] || (c[x][ax] == c[y][ax] && x < y); });
+        const size_t unit = len > 256 ? 256 : (size_t)kGroup;
+        size_t half = ((len / 2 + unit - 1) / unit) * unit;     // a multiple of the unit at or just above the median
+        if (half >= len) half = (len - 1) / unit * unit;        // (len > unit: both sides stay non-empty)
+        stack.push_back({nd.b, nd.b + half});
+        stack.push_back({nd.b + half, nd.e});
     }
-    std::stable_sort(perm.begin(), perm.end(), [&](int a, int b) { return code[a] < code[b]; });
     return perm;
 }
 template <typename T>
@@ -573,7 +580,7 @@ int flatten(const rtc_light* lights, size_t n_lights, const rtc_shape* shapes, s
         q.tr_ri = make_float4((float)s.transparency, (float)s.refractive_index, __int_as_float_host(s.pattern_kind),
                               __int_as_float_host(geom));
     }
-    // big scenes: Morton order per stream (see morton_order)
+    // big scenes: spatial (k-d) order per stream (see spatial_order)
     {
         auto centres_of = [&](const std::vector<int32_t>& index, double unit_radius) {
             std::vector<std::array<double, 3>> c(index.size());
@@ -586,19 +593,19 @@ int flatten(const rtc_light* lights, size_t n_lights, const rtc_shape* shapes, s
         if (hs.us_index.size() >= kSortMin) {
             std::vector<std::array<double, 3>> c(hs.us32.size());
             for (size_t k = 0; k < c.size(); ++k) c[k] = {hs.us32[k].x, hs.us32[k].y, hs.us32[k].z};
-            const std::vector<int> perm = morton_order(c);
+            const std::vector<int> perm = spatial_order(c);
             apply_perm(hs.us32, perm, 1); apply_perm(hs.us_index, perm, 1);
         }
         if (hs.gs_index.size() >= kSortMin) {
-            const std::vector<int> perm = morton_order(centres_of(hs.gs_index, 1.0));
+            const std::vector<int> perm = spatial_order(centres_of(hs.gs_index, 1.0));
             apply_perm(hs.gs32, perm, 3); apply_perm(hs.gs_index, perm, 1);
         }
         if (hs.cub_index.size() >= kSortMin) {
-            const std::vector<int> perm = morton_order(centres_of(hs.cub_index, std::sqrt(3.0)));
+            const std::vector<int> perm = spatial_order(centres_of(hs.cub_index, std::sqrt(3.0)));
             apply_perm(hs.cb32, perm, 3); apply_perm(hs.cub64, perm, 6); apply_perm(hs.cub_index, perm, 1);
         }
         if (hs.sph_index.size() >= kSortMin) {
-            const std::vector<int> perm = morton_order(centres_of(hs.sph_index, 1.0));
+            const std::vector<int> perm = spatial_order(centres_of(hs.sph_index, 1.0));
             apply_perm(hs.sph64, perm, 6); apply_perm(hs.sph_index, perm, 1);
         }
     }
