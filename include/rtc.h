@@ -221,6 +221,24 @@ int rtc_scene_upload(rtc_context* ctx, const rtc_light* light, const rtc_shape* 
 int rtc_scene_upload_lights(rtc_context* ctx, const rtc_light* lights, size_t n_lights, const rtc_shape* shapes,
                             size_t n_shapes);
 
+/* rtc_render_device without any allocation.  No counterpart in the reference; added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * rtc_render_device may grow the context's tile-order buffer (cudaMalloc) on the first frame of a size; this variant of
+ * the small-scene fast kernel keeps its scratch — the tile counter words and the tile hand-out order — in a static device
+ * array of the library (4 MiB + 256 B, held by every GPU that loads the library until the process exits) and calls no
+ * cudaMalloc, cudaFree or allocating library routine.  Inputs and outputs are the caller's, as in rtc_render_device
+ * (same opts, shards and RTC_OPT_DST_FULL_FRAME included; the frame is bit-identical to rtc_render_device's).
+ * Limits: RTC_PRECISION_F32_FAST on a scene that fits the small-scene form (<= 16 planes, <= 48 similarity-transformed
+ * spheres, one light, light outside every sphere) on a one-GPU context, else RTC_ERR_UNSUPPORTED; at most
+ * RTC_NOALLOC_MAX_TILES tiles of 8x4 pixels per call (7680x4320 fits), else RTC_ERR_UNSUPPORTED with the counts in
+ * rtc_last_error(); `stream` is required and nothing is synchronised; no work counters.
+ * Every call on a GPU shares the one array (whatever the context): calls that overlap on that GPU race — order them on
+ * one stream or with events.  The array keeps the last call's contents; the call clears the words that must start at
+ * zero on `stream` before the launch and rewrites every order word it reads. */
+#define RTC_NOALLOC_MAX_TILES (1 << 20)
+int rtc_render_device_noalloc(rtc_context* ctx, const rtc_camera* cam, const rtc_render_opts* opts, void* d_out_rgb,
+                              uint8_t* d_out_hit_mask, void* stream);
+
 /* Long-lived caller frames (the Canvas a renderer reuses per GIF frame, src/lua.rs:34-41; a frame in memory shared by
  * one process per GPU): register the buffer once (cudaHostRegister: page-locked and visible to every GPU of the machine)
  * and rtc_render delivers finished rows into it by DMA — no staging copy and no pass by host threads; each GPU writes

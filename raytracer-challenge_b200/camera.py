@@ -124,6 +124,11 @@ class Renderer:
             self._ctx, C.byref(cam_desc), C.byref(opts), C.c_void_p(d_rgb), C.c_void_p(d_mask) if d_mask else None, C.c_void_p(stream),
             C.c_void_p(wait_flag) if wait_flag else None, wait_value, C.c_void_p(done_flag) if done_flag else None, done_value))
 
+    def render_device_noalloc(self, cam_desc, opts, d_rgb, stream, d_mask=None):
+        """rtc_render_device_noalloc: the small-scene fast kernel with its scratch in a static device array — no cudaMalloc."""
+        ffi.check(self._lib.rtc_render_device_noalloc(self._ctx, C.byref(cam_desc), C.byref(opts), C.c_void_p(d_rgb),
+                                                      C.c_void_p(d_mask) if d_mask else None, C.c_void_p(stream)))
+
     def assemble_device(self, cam_desc, opts, d_gathered, shard_stride_rows, elem_kind, d_frame, stream=None):
         ffi.check(self._lib.rtc_assemble_device(
             self._ctx, C.byref(cam_desc), C.byref(opts), C.c_void_p(d_gathered), shard_stride_rows,

@@ -622,6 +622,46 @@ cudaError_t preload_render_f32_small() {
     return e;
 }
 
+// ---- rtc_render_device_noalloc: scratch in a static device array --------------------------------------------------------
+// Words 0..7: the persistent kernel's work counters (tiles handed out, blocks done, heavy / light tile counts); words
+// 64.. : the tile hand-out order written by classify_tiles_small_kernel (one word per tile, all total_tiles of them
+// rewritten by every call that uses them).  Every GPU that loads the library holds the array until the process exits; every
+// call on a GPU shares it, so calls that overlap on that GPU race (include/rtc.h).  In host code the NAME of the array is
+// a host-side stand-in, not a device address: the address a kernel may be given comes from cudaGetSymbolAddress, taken once
+// per device with that device current.
+static __device__ __align__(256) unsigned g_noalloc_scratch[64 + kNoAllocMaxTiles];
+static unsigned* g_noalloc_ptr[64] = {};   // by device ordinal
+
+cudaError_t noalloc_setup_current_device() {
+    int dev = -1;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return e;
+    if (dev < 0 || dev >= 64) return cudaErrorInvalidDevice;
+    if (g_noalloc_ptr[dev]) return cudaSuccess;
+    unsigned* ptr = nullptr;
+    e = cudaGetSymbolAddress((void**)&ptr, g_noalloc_scratch);
+    if (e != cudaSuccess) return e;
+    if (!ptr) return cudaErrorInvalidSymbol;
+    g_noalloc_ptr[dev] = ptr;
+    return cudaSuccess;
+}
+
+// Same kernels, same launch shape as launch_render_f32_small; nothing here allocates.  The counter words are cleared on
+// the stream first: the array keeps the last call's contents, and a call that was cut short would have left them non-zero.
+cudaError_t launch_render_f32_small_noalloc(SmallParams P, bool tile_order, int out_format, void* d_rgb, uint8_t* d_hit, cudaStream_t stream) {
+    if (P.total_tiles > kNoAllocMaxTiles) return cudaErrorInvalidValue;
+    int dev = -1;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return e;
+    if (dev < 0 || dev >= 64) return cudaErrorInvalidDevice;
+    if (!g_noalloc_ptr[dev] && (e = noalloc_setup_current_device()) != cudaSuccess) return e;
+    unsigned* scratch = g_noalloc_ptr[dev];
+    e = cudaMemsetAsync(scratch, 0, 64 * sizeof(unsigned), stream);
+    if (e != cudaSuccess) return e;
+    P.order = tile_order ? scratch + 64 : nullptr;
+    return launch_render_f32_small(P, out_format, d_rgb, d_hit, nullptr, scratch, stream);
+}
+
 cudaError_t launch_render_f32_small(const SmallParams& P, int out_format, void* d_rgb, uint8_t* d_hit, Counters* d_counters,
                                     unsigned* d_work, cudaStream_t stream) {
     if (P.shard_rows <= 0) return cudaSuccess;

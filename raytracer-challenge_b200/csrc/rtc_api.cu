@@ -1053,6 +1053,7 @@ int rtc_context_create(const int* device_ids, int n_gpus, rtc_context** out_ctx)
                                  (const void*)fma_peak_kernel<float>, (const void*)fma_peak_kernel<double>};
             for (const void* k : own) if (e == cudaSuccess) e = cudaFuncGetAttributes(&at, k);
         }
+        if (e == cudaSuccess) e = noalloc_setup_current_device();   // rtc_render_device_noalloc's static scratch: its address on this device
         if (e == cudaSuccess) e = d.wait_status.ensure(1);
         if (e == cudaSuccess) e = cudaMemset(d.wait_status.p, 0xff, sizeof(unsigned));
         if (e == cudaSuccess && g > 0) {   // peer stores into the first GPU's frame (rtc_render_device on several GPUs)
@@ -1390,6 +1391,33 @@ int rtc_render_device_synced(rtc_context* ctx, const rtc_camera* cam, const rtc_
     cp.dst_full = (opts->flags & RTC_OPT_DST_FULL_FRAME) ? 1 : 0;
     SyncSpec sy{(const unsigned*)d_wait_flag, wait_value, (unsigned*)d_done_flag, done_value, (unsigned long long)(ctx->wait_timeout_s * 1e9)};
     return launch_on(d, cp, opts->precision, opts->flags, d_out_rgb, d_out_hit_mask, nullptr, (cudaStream_t)stream, &sy);
+}
+
+int rtc_render_device_noalloc(rtc_context* ctx, const rtc_camera* cam, const rtc_render_opts* opts, void* d_out_rgb, uint8_t* d_out_hit_mask,
+                              void* stream) {
+    if (!ctx || !d_out_rgb || !stream) return fail(RTC_ERR_INVALID_ARG, "rtc_render_device_noalloc: null argument (a stream is required)");
+    int rc = validate_opts(cam, opts);
+    if (rc != RTC_OK) return rc;
+    if (!ctx->has_scene) return fail(RTC_ERR_NO_SCENE, "rtc_render_device_noalloc before rtc_scene_upload");
+    if (ctx->devs.size() != 1) return fail(RTC_ERR_UNSUPPORTED, "rtc_render_device_noalloc: one-GPU contexts only");
+    DeviceState& d = ctx->devs[0];
+    if (opts->precision != RTC_PRECISION_F32_FAST || !d.small_ok || (opts->flags & RTC_OPT_F32_GENERAL_KERNEL))
+        return fail(RTC_ERR_UNSUPPORTED, "rtc_render_device_noalloc: only the small-scene fast kernel has a variant without allocations "
+                                         "(RTC_PRECISION_F32_FAST, a scene that fits its constant-bank form: <= 16 planes, <= 48 similarity-transformed spheres, one light)");
+    CUDA_TRY(cudaSetDevice(d.dev));
+    CamParams cp = make_cam(cam, opts, opts->shard_index, opts->shard_count, opts->tile_rows);
+    cp.dst_full = (opts->flags & RTC_OPT_DST_FULL_FRAME) ? 1 : 0;
+    if (cp.shard_rows <= 0) return RTC_OK;
+    SmallParams P = d.small;
+    fill_small_camera(P, cp);
+    P.wait_flag = nullptr; P.done_flag = nullptr; P.wait_status = d.wait_status.p; P.wait_value = P.done_value = 0u; P.wait_timeout_ns = 0ull;
+    if (P.total_tiles > kNoAllocMaxTiles)
+        return fail(RTC_ERR_UNSUPPORTED, "rtc_render_device_noalloc: the frame has " + std::to_string(P.total_tiles) + " tiles of 8x4 pixels, the static scratch holds " +
+                                             std::to_string(kNoAllocMaxTiles) + " (RTC_NOALLOC_MAX_TILES; 7680x4320 fits)");
+    const bool tile_order = P.max_depth > 0 && P.n_glass != 0 && P.total_tiles >= 4096 && !(opts->flags & RTC_OPT_LINEAR_TILE_ORDER);
+    cudaError_t e = launch_render_f32_small_noalloc(P, tile_order, cp.out_format, d_out_rgb, d_out_hit_mask, (cudaStream_t)stream);
+    if (e != cudaSuccess) return fail(RTC_ERR_CUDA, std::string("rtc_render_device_noalloc: ") + cudaGetErrorString(e));
+    return RTC_OK;
 }
 
 int rtc_register_host_buffer(rtc_context* ctx, void* ptr, size_t bytes) {

@@ -240,6 +240,12 @@ cudaError_t preload_render_f64();
 cudaError_t preload_render_f32();
 cudaError_t preload_render_f32_small();
 
+// rtc_render_device_noalloc (include/rtc.h): the small-scene fast kernel with its scratch — the tile counter words and the
+// tile hand-out order — in a static device array of render_f32_small.cu instead of cudaMalloc'd buffers.
+constexpr int kNoAllocMaxTiles = 1 << 20;            // 8x4-pixel tiles: covers 7680x4320 (1,036,800 tiles); 4 MiB + 256 B per GPU
+cudaError_t noalloc_setup_current_device();          // cudaGetSymbolAddress of the array for the CURRENT device (once per device)
+cudaError_t launch_render_f32_small_noalloc(SmallParams P, bool tile_order, int out_format, void* d_rgb, uint8_t* d_hit, cudaStream_t stream);
+
 // kernel launchers implemented in the kernel TUs
 cudaError_t launch_render_f64(const DevScene64& scene, const CamParams& cam, void* d_rgb, uint8_t* d_hit,
                               Counters* d_counters, cudaStream_t stream);

@@ -25,6 +25,7 @@ OPT_LINEAR_TILE_ORDER = 4
 OPT_NO_BOUND_FILTER = 8
 OPT_DELIVER_DIRECT = 16
 OPT_DELIVER_STAGED = 32
+NOALLOC_MAX_TILES = 1 << 20   # RTC_NOALLOC_MAX_TILES
 IPC_HANDLE_BYTES = 64
 
 
@@ -98,6 +99,7 @@ EXPORTS = [
     ("rtc_wait_result", C.c_int, [C.c_void_p, C.c_void_p, C.POINTER(C.c_int)]),
     ("rtc_render_device_synced", C.c_int, [C.c_void_p, C.POINTER(RtcCamera), C.POINTER(RtcRenderOpts), C.c_void_p, C.c_void_p, C.c_void_p,
                                            C.c_void_p, C.c_uint32, C.c_void_p, C.c_uint32]),
+    ("rtc_render_device_noalloc", C.c_int, [C.c_void_p, C.POINTER(RtcCamera), C.POINTER(RtcRenderOpts), C.c_void_p, C.c_void_p, C.c_void_p]),
     ("rtc_register_host_buffer", C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t]),
     ("rtc_unregister_host_buffer", C.c_int, [C.c_void_p, C.c_void_p]),
     ("rtc_pack_rgba8_device", C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_size_t, C.c_float, C.c_void_p, C.c_void_p]),
