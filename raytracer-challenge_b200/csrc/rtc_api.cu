@@ -206,6 +206,7 @@ struct rtc_context {
     Counters* pinned_counters = nullptr;  // one per device
     unsigned* pinned_status = nullptr;    // rtc_wait_result reads the wait status word through this
     std::vector<std::pair<unsigned char*, size_t>> registered;   // rtc_register_host_buffer ranges
+    std::vector<bool> registered_owned;                          // false: the range was already page-locked by another owner (not ours to unregister)
     double wait_timeout_s = 60.0;
 };
 
@@ -1102,7 +1103,7 @@ void rtc_context_destroy(rtc_context* ctx) {
     if (ctx->pinned_hit) cudaFreeHost(ctx->pinned_hit);
     if (ctx->pinned_counters) cudaFreeHost(ctx->pinned_counters);
     if (ctx->pinned_status) cudaFreeHost(ctx->pinned_status);
-    for (auto& r : ctx->registered) cudaHostUnregister(r.first);
+    for (size_t i = 0; i < ctx->registered.size(); ++i) if (ctx->registered_owned[i]) cudaHostUnregister(ctx->registered[i].first);
     delete ctx->pool;
     delete ctx;
 }
@@ -1426,9 +1427,21 @@ int rtc_register_host_buffer(rtc_context* ctx, void* ptr, size_t bytes) {
         if (r.first == (unsigned char*)ptr) return r.second >= bytes ? RTC_OK : fail(RTC_ERR_INVALID_ARG, "rtc_register_host_buffer: already registered with a smaller size");
     CUDA_TRY(cudaSetDevice(ctx->devs[0].dev));
     cudaError_t e = cudaHostRegister(ptr, bytes, cudaHostRegisterPortable);
-    if (e == cudaErrorHostMemoryAlreadyRegistered) { cudaGetLastError(); return fail(RTC_ERR_INVALID_ARG, "rtc_register_host_buffer: the range overlaps memory another owner registered"); }
-    if (e != cudaSuccess) { cudaGetLastError(); return fail(RTC_ERR_CUDA, std::string("cudaHostRegister: ") + cudaGetErrorString(e)); }
+    bool owned = true;
+    if (e == cudaErrorHostMemoryAlreadyRegistered) {
+        // Page-locked already — by another context of this process or by the caller (cudaHostRegister / cudaMallocHost).  That
+        // is all the direct delivery needs when the whole range is: check both ends, and leave the registration to its owner.
+        cudaGetLastError();
+        cudaPointerAttributes a0, a1;
+        if (cudaPointerGetAttributes(&a0, ptr) != cudaSuccess || cudaPointerGetAttributes(&a1, (unsigned char*)ptr + bytes - 1) != cudaSuccess ||
+            a0.type != cudaMemoryTypeHost || a1.type != cudaMemoryTypeHost) {
+            cudaGetLastError();
+            return fail(RTC_ERR_INVALID_ARG, "rtc_register_host_buffer: the range overlaps memory another owner registered only in part");
+        }
+        owned = false;
+    } else if (e != cudaSuccess) { cudaGetLastError(); return fail(RTC_ERR_CUDA, std::string("cudaHostRegister: ") + cudaGetErrorString(e)); }
     ctx->registered.emplace_back((unsigned char*)ptr, bytes);
+    ctx->registered_owned.push_back(owned);
     return RTC_OK;
 }
 
@@ -1437,8 +1450,9 @@ int rtc_unregister_host_buffer(rtc_context* ctx, void* ptr) {
     for (size_t i = 0; i < ctx->registered.size(); ++i)
         if (ctx->registered[i].first == (unsigned char*)ptr) {
             for (DeviceState& d : ctx->devs) { cudaSetDevice(d.dev); cudaStreamSynchronize(d.stream); cudaStreamSynchronize(d.copy_stream); }
-            CUDA_TRY(cudaHostUnregister(ptr));
+            if (ctx->registered_owned[i]) CUDA_TRY(cudaHostUnregister(ptr));
             ctx->registered.erase(ctx->registered.begin() + (long)i);
+            ctx->registered_owned.erase(ctx->registered_owned.begin() + (long)i);
             return RTC_OK;
         }
     return fail(RTC_ERR_INVALID_ARG, "rtc_unregister_host_buffer: not a registered buffer");

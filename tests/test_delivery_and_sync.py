@@ -68,6 +68,28 @@ def test_shards_deliver_directly_into_one_registered_frame(rtc, renderer, precis
         renderer.unregister_host_buffer(frame)
 
 
+def test_a_buffer_another_context_registered_can_be_registered_again(rtc, renderer):
+    """Two contexts of one process deliver into the same long-lived frame (bench.py: a rank's own context and the one-process
+    several-GPU context): the second registration finds the range page-locked, uses it, and leaves the registration to its owner."""
+    world, d = _room(rtc, 320, 180)
+    renderer.upload(world)
+    other = rtc.Renderer([0])
+    other.upload(world)
+    buf = np.full((180, 320, 3), -1.0)
+    renderer.register_host_buffer(buf)
+    other.register_host_buffer(buf)
+    o = rtc.Renderer.make_opts(precision=1, flags=rtc.ffi.OPT_DELIVER_DIRECT)
+    want, _, _ = renderer.render(d, rtc.Renderer.make_opts(precision=1))
+    other.render(d, o, out=buf, want_mask=False, want_stats=False)
+    assert np.array_equal(buf, want)
+    other.unregister_host_buffer(buf)          # not the owner: the range stays page-locked
+    buf[:] = -1.0
+    renderer.render(d, o, out=buf, want_mask=False, want_stats=False)
+    assert np.array_equal(buf, want)
+    renderer.unregister_host_buffer(buf)
+    other.close()
+
+
 def test_direct_delivery_needs_a_registered_buffer(rtc, renderer):
     world, d = _room(rtc, 64, 32)
     renderer.upload(world)
