@@ -42,37 +42,13 @@ FLOP_PER_SHADED_HIT = 150
 # Executed-instruction figures of the timed kernel from the kept `ncu --set full` capture (a number measured under a
 # profiler is never a bench value: these describe the kernel, the timings above are CUDA events).  Refreshed per round.
 HW_PROFILE = {
-    "c3": {"source": "profiles/r01_ncu_f32_small_1p25ms.txt", "fma_pipe_pct": 43.7, "alu_pipe_pct": 37.9, "issue_active_pct": 84.7,
-           "lanes_per_instruction": 28.45, "registers": 74, "dram_bytes_per_launch": 64.56e6,
-           "dram_note": "63.3 MB written + 1.2 MB read per 4K launch; the frame is 99.5 MB, the rest was still in the 126 MB L2 when the kernel ended"},
+    "c3": {"source": "profiles/r02_ncu_f32_small_c3.txt", "fma_pipe_pct": 41.9, "alu_pipe_pct": 41.0, "issue_active_pct": 83.8,
+           "lanes_per_instruction": 28.41, "registers": 74, "dram_bytes_per_launch": 61.38e6,
+           "dram_note": "60.2 MB written + 1.1 MB read per 4K launch; the frame is 99.5 MB, the rest was still in the 126 MB L2 when the kernel ended"},
+    "c4": {"source": "profiles/r02_ncu_f64_c4_960x540.txt (the parity kernel, which fast mode takes for this scene; a 960x540 frame)",
+           "fp64_pipe_pct": 7.8, "fma_pipe_pct": 20.6, "alu_pipe_pct": 19.0, "issue_active_pct": 45.1, "lanes_per_instruction": 7.95,
+           "registers": 128, "dram_bytes_per_launch": None},
 }
-FP32_FORMULA_PEAK = 148 * 128 * 2 * 1.965e9 / 1e12  # TFLOP/s, non-tensor, at clocks.max.sm
-
-
-class ClockSampler:
-    """nvidia-smi clocks / throttle reasons DURING the timed region (B200_PROFILING.md recipe)."""
-    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
-         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
-
-    def __init__(self, gpu_index=0):
-        self.rows, self.proc, self.gpu = [], None, gpu_index
-
-    def start(self):
-        try:
-            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
-                                          "-lms", "100", "-i", str(self.gpu)], stdout=subprocess.PIPE, text=True)
-            self.t = threading.Thread(target=self._read, daemon=True)
-            self.t.start()
-        except Exception:
-            self.proc = None
-
-    def _read(self):
-        for line in self.proc.stdout:
-            self.rows.append((time.time(), [c.strip() for c in line.split(",")]))
-
-    def stop(self, t0, t1):
-        if not self.proc:
-            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
         time.sleep(0.15)
         self.proc.terminate()
         rows = [r for t, r in self.rows if t0 - 0.05 <= t <= t1 + 0.15 and len(r) >= 9] or [r for _, r in self.rows if len(r) >= 9]
@@ -270,8 +246,9 @@ def run_gpu(args):
             if self.sf.mode == "nccl":
                 self.sf.exchange(lambda g, f: r.assemble_device(camd, self.opts, g.data_ptr(), self.sf.stride_rows, self.fmt, f.data_ptr(), stream))
             else:
-                self.sf.exchange(stream=stream)   # completion flags over NVLink: no collective (pixels are already in rank 0's frame)
-                self.sf.release(stream)           # rank 0 has no consumer here: the frame is free again at once
+                # completion flags over NVLink: no collective (pixels are already in rank 0's frame); rank 0 has no consumer here, so
+                # its wait kernel frees the frame for the next one itself (back-pressure flag)
+                self.sf.exchange(stream=stream, release=True)
 
     def timed(fn, steps, warmup):
         for _ in range(warmup):
@@ -504,7 +481,9 @@ def run_gpu(args):
                          "peak_source": "FFMA micro-benchmark on this GPU in this run (rtc_measure_peak_tflops)",
                          "peak_formula": FP32_FORMULA_PEAK, "frac_of_formula": None if c4 else achieved / FP32_FORMULA_PEAK,
                          "algorithmic_gflop_per_frame": flops / 1e9, "kernel_ms": kernel_ms,
-                         "kernel": "render_f32_kernel<kRefine> (f32 hierarchy + shading, f64 ray geometry)" if c4 else "render_f32_small_kernel",
+                         "kernel": "render_f64_kernel: fast mode sends scenes whose streams exceed shared memory to the parity kernel, the fastest kernel "
+                                   "that meets the fast-mode tolerance there (the mixed-precision form of the general f32 kernel: RTC_OPT_F32_GENERAL_KERNEL)"
+                                   if c4 else "render_f32_small_kernel",
                          "hbm_gbs_measured_peak": peaks.get("hbm_gbs"),
                          "hbm_gbs_achieved_frame_write": W * H * 12 * my_share / (kernel_ms * 1e-3) / 1e9},
             "f64": {"ms_per_frame": float(ms64.mean()), "mrays_per_s": rays / (float(ms64.mean()) * 1e-3) / 1e6,
@@ -527,15 +506,15 @@ def run_gpu(args):
             # kernels of this library inside the timed region, all ranks: rank 0 runs the tile scheduling pre-pass + the render
             # kernel (+ the flag wait and the 'consumed' flag store when N > 1); every other rank ONE launch: its render kernel
             # waits for the back-pressure flag and stores its completion flag itself
-            "gpu_launches": args.steps * (2 if N == 1 else 4 + (N - 1)),
-            "gpu_launches_per_step": {"rank0": ["classify_tiles_small_kernel", "render_f32_small_kernel"] + (["wait_kernel", "signal_kernel"] if N > 1 else []),
+            "gpu_launches": args.steps * (2 if N == 1 else 3 + (N - 1)),
+            "gpu_launches_per_step": {"rank0": ["classify_tiles_small_kernel", "render_f32_small_kernel"] + (["wait_kernel"] if N > 1 else []),
                                       "other_ranks": ["render_f32_small_kernel"] if N > 1 else []},
             "clocks": clocks,
         }
         if c4:
-            line["gpu_launches"] = args.steps * (1 if N == 1 else 3 + 3 * (N - 1))
-            line["gpu_launches_per_step"] = {"rank0": ["render_f32_kernel"] + (["wait_kernel", "signal_kernel"] if N > 1 else []),
-                                             "other_ranks": ["wait_kernel", "render_f32_kernel", "signal_kernel"] if N > 1 else []}
+            line["gpu_launches"] = args.steps * (1 if N == 1 else 2 + 3 * (N - 1))
+            line["gpu_launches_per_step"] = {"rank0": ["render_f64_kernel"] + (["wait_kernel"] if N > 1 else []),
+                                             "other_ranks": ["wait_kernel", "render_f64_kernel", "signal_kernel"] if N > 1 else []}
         line.update(extra)
         if single is not None:
             line["e2e_single_process"] = single

@@ -150,8 +150,10 @@ typedef struct rtc_render_opts {
  * With a peer-mapped frame of another GPU (rtc_ipc_open) this is the fused render + gather:
  * finished pixels travel over NVLink as the kernel produces them, no collective afterwards. */
 #define RTC_OPT_DST_FULL_FRAME 1
-/* f32 fast mode: use the general kernel (shared-memory streams, any shape count) even when the
- * scene fits the constant-bank small-scene kernel.  For testing one against the other. */
+/* f32 fast mode: use the general f32 kernel even when the library would choose another one — the constant-bank small-scene
+ * kernel for scenes that fit it, the parity kernel for scenes whose streams exceed shared memory (10^3+ shapes: it is the
+ * fastest kernel that meets the fast-mode tolerance there; the general kernel then runs its mixed-precision form: f32
+ * hierarchy and shading, geometry of the radiance rays in f64).  For testing and measuring one against the other. */
 #define RTC_OPT_F32_GENERAL_KERNEL 2
 /* f32 small-scene kernel: hand tiles out in linear order instead of "tiles that see a transparent
  * surface first" (the scheduling pre-pass).  Same image either way; for measuring the difference. */
@@ -306,6 +308,11 @@ int rtc_ipc_close(rtc_context* ctx, void* d_ptr, uint64_t offset);
  * the producers wait for it before they overwrite the frame (raytracer-challenge_b200/sharded.py). */
 int rtc_signal_device(rtc_context* ctx, void* d_flag, uint32_t value, void* stream);
 int rtc_wait_device(rtc_context* ctx, const void* d_flags, int n, uint32_t value, void* stream);
+/* rtc_wait_device and, in the same kernel, rtc_signal_device(d_then_flag, then_value) once every flag has arrived (not after a
+ * timeout): a rank 0 without a consumer of its own between frames releases the frame ("consumed") without a second launch.
+ * 1 <= n <= 1024. */
+int rtc_wait_signal_device(rtc_context* ctx, const void* d_flags, int n, uint32_t value, void* d_then_flag, uint32_t then_value,
+                           void* stream);
 int rtc_set_wait_timeout(rtc_context* ctx, double seconds);
 int rtc_wait_result(rtc_context* ctx, void* stream, int* first_missing);
 

@@ -171,6 +171,10 @@ class Renderer:
     def wait_device(self, d_flags, n, value, stream=None):
         ffi.check(self._lib.rtc_wait_device(self._ctx, C.c_void_p(d_flags), n, value, C.c_void_p(stream) if stream else None))
 
+    def wait_signal_device(self, d_flags, n, value, d_then_flag, then_value, stream=None):
+        ffi.check(self._lib.rtc_wait_signal_device(self._ctx, C.c_void_p(d_flags), n, value, C.c_void_p(d_then_flag), then_value,
+                                                   C.c_void_p(stream) if stream else None))
+
     def set_wait_timeout(self, seconds):
         ffi.check(self._lib.rtc_set_wait_timeout(self._ctx, C.c_double(seconds)))
 

@@ -1416,6 +1416,15 @@ cudaError_t preload_render_f32() {
     return e;
 }
 
+static size_t f32_stream_bytes(const DevScene32& scene) {
+    const int n_obj = scene.n_gsph + scene.n_cube;
+    return (size_t)(scene.n_planes + scene.n_usph + 3 * n_obj) * 16 + (size_t)(scene.n_planes + scene.n_usph + n_obj) * 4 +
+           (size_t)(scene.n_planes + scene.n_usph) * 4 + 16 * 4 + 16;
+}
+bool f32_streams_are_global(const DevScene32& scene) {
+    return f32_stream_bytes(scene) + (size_t)scene.n_shapes * sizeof(ShadeRec32) > 40 * 1024 && f32_stream_bytes(scene) > 96 * 1024;
+}
+
 cudaError_t launch_render_f32(const DevScene32& scene, const CamParams& cam, void* d_rgb, uint8_t* d_hit,
                               Counters* d_counters, unsigned* d_work, cudaStream_t stream) {
     if (cam.shard_rows <= 0) return cudaSuccess;

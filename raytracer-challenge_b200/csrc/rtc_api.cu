@@ -836,19 +836,31 @@ __global__ void signal_kernel(unsigned* flag, unsigned value) {
 // A wait that runs out of time records which flag is missing (1 + its index, the smallest one wins) and returns: the
 // stream goes on, the CUDA context stays usable (a trap would poison it: every buffer and the scene of the waiting
 // process lost), and the host learns about it from rtc_wait_result.
-__global__ void wait_kernel(const unsigned* flags, int n, unsigned value, unsigned long long timeout_ns, unsigned* status) {
+// then_flag (rtc_wait_signal_device, one block): once every flag has arrived, then_value is release-stored to it by the same
+// kernel — "frame consumed" for a rank 0 that has no consumer of its own between frames, without a second launch.
+__global__ void wait_kernel(const unsigned* flags, int n, unsigned value, unsigned long long timeout_ns, unsigned* status,
+                            unsigned* then_flag = nullptr, unsigned then_value = 0u) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n) return;
-    unsigned long long t0;
-    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
-    for (;;) {
-        unsigned v;
-        asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(flags + i) : "memory");
-        if ((int)(v - value) >= 0) break;
-        unsigned long long t1;
-        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
-        if (t1 - t0 > timeout_ns) { atomicMin(status, (unsigned)i + 1u); break; }
-        __nanosleep(200);
+    bool arrived = true;
+    if (i < n) {
+        unsigned long long t0;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+        for (;;) {
+            unsigned v;
+            asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(flags + i) : "memory");
+            if ((int)(v - value) >= 0) break;
+            unsigned long long t1;
+            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
+            if (t1 - t0 > timeout_ns) { atomicMin(status, (unsigned)i + 1u); arrived = false; break; }
+            __nanosleep(200);
+        }
+    }
+    if (then_flag) {   // (single block)
+        const int all = __syncthreads_and(arrived ? 1 : 0);
+        if (threadIdx.x == 0 && all) {
+            __threadfence_system();
+            asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(then_flag), "r"(then_value) : "memory");
+        }
     }
 }
 
@@ -967,7 +979,13 @@ int launch_on(DeviceState& d, const CamParams& cp, int precision, int flags, voi
     if (sync && !fused && sync->wait_flag) {   // kernels without the fused form: the flag kernels around the launch
         wait_kernel<<<1, 32, 0, st>>>(sync->wait_flag, 1, sync->wait_value, sync->timeout_ns, d.wait_status.p);
     }
-    if (precision == RTC_PRECISION_F64_PARITY) {
+    // Fast mode promises the tolerance, not a data type: on scenes whose streams do not fit shared memory (10^3+ shapes) the
+    // fastest kernel that meets it is the parity kernel with its per-lane three-level walk (C4 4K: 71 ms, and exact) — the
+    // mixed-precision kRefine form of the general f32 kernel needs 109 ms (profiles/r02_experiments.txt) and stays reachable
+    // through RTC_OPT_F32_GENERAL_KERNEL.  The parity kernel converts to the requested output format itself.
+    const bool big_to_parity = precision == RTC_PRECISION_F32_FAST && !(flags & RTC_OPT_F32_GENERAL_KERNEL) && !d.small_ok &&
+                               d.s64.n_bound4 > 0 && f32_streams_are_global(d.s32);
+    if (precision == RTC_PRECISION_F64_PARITY || big_to_parity) {
         DevScene64 s64 = d.s64;
         if (flags & RTC_OPT_NO_BOUND_FILTER) s64.n_bound4 = 0;
         e = launch_render_f64(s64, cp, d_rgb, d_hit, d_counters, st);
@@ -1354,6 +1372,17 @@ int rtc_wait_device(rtc_context* ctx, const void* d_flags, int n, uint32_t value
     cudaStream_t st = stream ? (cudaStream_t)stream : d.stream;
     const unsigned long long timeout_ns = (unsigned long long)(ctx->wait_timeout_s * 1e9);
     wait_kernel<<<(n + 31) / 32, 32, 0, st>>>((const unsigned*)d_flags, n, value, timeout_ns, d.wait_status.p);
+    CUDA_TRY(cudaGetLastError());
+    return RTC_OK;
+}
+
+int rtc_wait_signal_device(rtc_context* ctx, const void* d_flags, int n, uint32_t value, void* d_then_flag, uint32_t then_value, void* stream) {
+    if (!ctx || !d_flags || !d_then_flag || n < 1 || n > 1024) return fail(RTC_ERR_INVALID_ARG, "rtc_wait_signal_device: bad argument (1 <= n <= 1024)");
+    DeviceState& d = ctx->devs[0];
+    CUDA_TRY(cudaSetDevice(d.dev));
+    cudaStream_t st = stream ? (cudaStream_t)stream : d.stream;
+    const unsigned long long timeout_ns = (unsigned long long)(ctx->wait_timeout_s * 1e9);
+    wait_kernel<<<1, (n + 31) / 32 * 32, 0, st>>>((const unsigned*)d_flags, n, value, timeout_ns, d.wait_status.p, (unsigned*)d_then_flag, then_value);
     CUDA_TRY(cudaGetLastError());
     return RTC_OK;
 }

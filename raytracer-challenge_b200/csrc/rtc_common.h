@@ -252,6 +252,10 @@ cudaError_t launch_render_f64(const DevScene64& scene, const CamParams& cam, voi
 cudaError_t launch_render_f32(const DevScene32& scene, const CamParams& cam, void* d_rgb, uint8_t* d_hit,
                               Counters* d_counters, unsigned* d_work, cudaStream_t stream);
 
+// true: the scene's fast-mode streams exceed shared memory (the general f32 kernel would run its kRefine form: streams in
+// global memory, geometry of the radiance rays in f64).  rtc_api.cu's dispatch sends such scenes to the parity kernel instead.
+bool f32_streams_are_global(const DevScene32& scene);
+
 cudaError_t launch_render_f32_small(const SmallParams& P, int out_format, void* d_rgb, uint8_t* d_hit, Counters* d_counters,
                                     unsigned* d_work, cudaStream_t stream);
 

@@ -95,6 +95,7 @@ EXPORTS = [
     ("rtc_ipc_close", C.c_int, [C.c_void_p, C.c_void_p, C.c_uint64]),
     ("rtc_signal_device", C.c_int, [C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p]),
     ("rtc_wait_device", C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_uint32, C.c_void_p]),
+    ("rtc_wait_signal_device", C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_uint32, C.c_void_p, C.c_uint32, C.c_void_p]),
     ("rtc_set_wait_timeout", C.c_int, [C.c_void_p, C.c_double]),
     ("rtc_wait_result", C.c_int, [C.c_void_p, C.c_void_p, C.POINTER(C.c_int)]),
     ("rtc_render_device_synced", C.c_int, [C.c_void_p, C.POINTER(RtcCamera), C.POINTER(RtcRenderOpts), C.c_void_p, C.c_void_p, C.c_void_p,

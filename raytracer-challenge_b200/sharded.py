@@ -161,10 +161,12 @@ class ShardedFrame:
         if self.world > 1 and self.mode == "p2p" and self.signal == "flags" and self.rank == 0:
             self._renderer.signal_device(self.flags.data_ptr(), self.seq, stream)
 
-    def exchange(self, assemble=None, stream=None):
+    def exchange(self, assemble=None, stream=None, release=False):
         """The exchange step after every rank's render call was enqueued.  Returns the frame on
         rank 0 (None elsewhere).  ``assemble(gathered, frame)`` de-interleaves on the device
-        (rtc_assemble_device); without it the torch index form is used (CPU tensors)."""
+        (rtc_assemble_device); without it the torch index form is used (CPU tensors).  release=True (p2p with flags): rank 0
+        has no consumer to wait for and frees the frame for the next one in the same launch — otherwise call release()
+        after the consumer."""
         if self.world == 1:
             return self.frame
         if self.mode == "nccl":
@@ -180,7 +182,10 @@ class ShardedFrame:
         if self.signal == "flags":
             self.seq += 1
             if self.rank == 0:
-                self._renderer.wait_device(self.flags.data_ptr() + 4, self.world - 1, self.seq, stream)
+                if release:   # no consumer of our own between frames: wait and "frame consumed" in one launch
+                    self._renderer.wait_signal_device(self.flags.data_ptr() + 4, self.world - 1, self.seq, self.flags.data_ptr(), self.seq, stream)
+                else:
+                    self._renderer.wait_device(self.flags.data_ptr() + 4, self.world - 1, self.seq, stream)
                 return self.frame
             if not getattr(self, "_fused", False):   # the render call was not render(): store the flag behind it
                 self._renderer.signal_device(self.remote_flags + 4 * self.rank, self.seq, stream)

@@ -200,6 +200,24 @@ def test_render_device_synced_waits_for_the_consumer_and_signals(rtc, renderer, 
     assert int(words[1]) == 10
 
 
+def test_wait_signal_device_releases_only_when_every_flag_arrived(rtc):
+    import torch
+    f = rtc.ffi
+    r = rtc.Renderer([0])
+    r.set_wait_timeout(0.05)
+    words = torch.zeros(64, dtype=torch.int32, device="cuda")
+    words[1:4] = 4
+    torch.cuda.synchronize()
+    r.wait_signal_device(words.data_ptr() + 4, 3, 4, words.data_ptr(), 4)
+    r.wait_result()
+    assert int(words[0]) == 4
+    r.wait_signal_device(words.data_ptr() + 4, 5, 4, words.data_ptr(), 9)    # flags 3 and 4 never arrive: no release
+    with pytest.raises(f.RtcError) as e:
+        r.wait_result()
+    assert e.value.code == f.RTC_ERR_TIMEOUT and int(words[0]) == 4
+    r.close()
+
+
 def test_a_wait_that_times_out_is_reported_and_the_context_survives(rtc, orc):
     """A rank that never signals: rtc_wait_device gives up after the context's timeout, rtc_wait_result names the missing
     flag with RTC_ERR_TIMEOUT, and the context renders on (round 1 trapped: every buffer of the process was lost)."""

@@ -517,17 +517,25 @@ def _lattice_check(rtc, orc, renderer, flat, cam, step, n_random, f32_min_ok, de
     assert np.array_equal(hit.reshape(-1)[idx], want_hit)
     err = np.abs(got.reshape(-1, 3)[idx] - want).max()
     assert err <= TOL64, f"max |delta| = {err}"
-    got32, hit32, st32 = renderer.render(d, rtc.Renderer.make_opts(precision=rtc.ffi.PRECISION_F32_FAST, max_depth=depth, out_format=rtc.ffi.OUT_F32_RGB))
-    q_got = orc.quantize_u8(got32.reshape(-1, 3)[idx].astype(np.float64)).astype(int)
+    # fast mode twice on big scenes: the library's own choice (scenes whose streams exceed shared memory go to the parity
+    # kernel: the fastest kernel that meets the tolerance) and the general f32 kernel forced (its mixed-precision kRefine form)
+    big = flat[2] > 4000
     q_want = orc.quantize_u8(want).astype(int)
-    ok = (np.abs(q_got - q_want).max(axis=1) <= 1).mean()
-    mm = int((hit32.reshape(-1)[idx] != want_hit).sum())
+    for f32_flags in ((0, rtc.ffi.OPT_F32_GENERAL_KERNEL) if big else (0,)):
+        got32, hit32, st32 = renderer.render(d, rtc.Renderer.make_opts(precision=rtc.ffi.PRECISION_F32_FAST, max_depth=depth, out_format=rtc.ffi.OUT_F32_RGB,
+                                                                       flags=f32_flags))
+        q_got = orc.quantize_u8(got32.reshape(-1, 3)[idx].astype(np.float64)).astype(int)
+        ok = (np.abs(q_got - q_want).max(axis=1) <= 1).mean()
+        mm = int((hit32.reshape(-1)[idx] != want_hit).sum())
+        if f32_flags == 0 and big:
+            assert ok >= f32_min_ok and mm == 0 and st32.rays == st.rays, (ok, mm)
     assert mm == 0 if f32_mask_exact else mm <= 1e-3 * idx.size, f"f32 hit mask differs from the oracle's on {mm} of {idx.size} lattice pixels"
     if ok < f32_min_ok:   # say where it fails before failing: the fraction per recursion depth limit
         per_depth = {}
         for dd in range(0, depth):
             w_d, _, _ = orc.OracleWorld(flat=flat).render(cam, max_depth=dd, threads=NCPU, pixels=idx)
-            g_d, _, _ = renderer.render(d, rtc.Renderer.make_opts(precision=rtc.ffi.PRECISION_F32_FAST, max_depth=dd, out_format=rtc.ffi.OUT_F32_RGB))
+            g_d, _, _ = renderer.render(d, rtc.Renderer.make_opts(precision=rtc.ffi.PRECISION_F32_FAST, max_depth=dd, out_format=rtc.ffi.OUT_F32_RGB,
+                                                                  flags=rtc.ffi.OPT_F32_GENERAL_KERNEL if big else 0))
             qd = orc.quantize_u8(g_d.reshape(-1, 3)[idx].astype(np.float64)).astype(int)
             per_depth[dd] = float((np.abs(qd - orc.quantize_u8(w_d).astype(int)).max(axis=1) <= 1).mean())
         raise AssertionError(f"f32: only {ok:.5f} of lattice pixels within 1/255 at depth {depth}; by depth limit: {per_depth}")
@@ -581,10 +589,10 @@ def _big_mixed_world(rtc):
 
 
 def test_bounding_sphere_filter_changes_nothing(rtc, renderer, c4_flat):
-    """Scenes whose streams stay in global memory run the exact shape tests behind a bounding-sphere filter
-    (render_f32.cu sweep_bounds).  The filter is conservative: the frame, the hit mask and the ray counters are
-    those of the plain brute-force loops (RTC_OPT_NO_BOUND_FILTER), bit for bit — spheres, affine spheres,
-    cubes, needle-shaped ellipsoids, aliased world_ids."""
+    """Scenes whose streams stay in global memory run the exact shape tests of the general f32 kernel (forced here: by
+    default such scenes go to the parity kernel) behind a box / sphere hierarchy (render_f32.cu warp_query).  The
+    hierarchy is conservative: the frame, the hit mask and the ray counters are those of the plain brute-force loops
+    (RTC_OPT_NO_BOUND_FILTER), bit for bit — spheres, affine spheres, cubes, needle-shaped ellipsoids, aliased world_ids."""
     import torch
     ffi = rtc.ffi
     for flat, cam in ((c4_flat, rtc.scenes.synthetic_camera(640, 360)),
@@ -592,7 +600,7 @@ def test_bounding_sphere_filter_changes_nothing(rtc, renderer, c4_flat):
         renderer.upload_flat(*flat)
         d = cam.flatten()
         out = []
-        for flags in (0, ffi.OPT_NO_BOUND_FILTER):
+        for flags in (ffi.OPT_F32_GENERAL_KERNEL, ffi.OPT_F32_GENERAL_KERNEL | ffi.OPT_NO_BOUND_FILTER):
             buf = torch.empty((d.vsize, d.hsize, 3), dtype=torch.float32, device="cuda")
             hit = torch.empty((d.vsize, d.hsize), dtype=torch.uint8, device="cuda")
             st = ffi.RtcStats()

@@ -25,7 +25,8 @@ room = rtc.scenes.reflect_refract_scene()
 two = rtc.scenes.reflect_refract_scene()
 two.add_light(rtc.Light(rtc.Color(0.3, 0.5, 0.9), (3.5, 3.0, -3.0)))
 cube_world, cube_cam = rtc.scenes.cube_scene(7, hsize=48, vsize=32)
-big = rtc.scenes.synthetic_scene(n_spheres=1500, seed=0xB200)   # > 255 shapes: aliased ids, global-memory streams + filter
+mid = rtc.scenes.synthetic_scene(n_spheres=1500, seed=0xB200)   # > 255 shapes: aliased ids, the shared-memory streams of the general kernels
+big = rtc.scenes.synthetic_scene(n_spheres=7000, seed=0xB200)   # streams beyond 96 KB: global-memory streams, the hierarchy queries (kRefine kernels)
 
 
 def both(world, cam, **kw):
@@ -69,7 +70,10 @@ guarded(room, rtc.scenes.reflect_refract_camera(40, 21, samples=5))
 guarded(room, rtc.scenes.reflect_refract_camera(64, 36), flags=ffi.OPT_F32_GENERAL_KERNEL)
 guarded(two, rtc.scenes.reflect_refract_camera(48, 24))
 guarded(cube_world, cube_cam)
+guarded(mid, rtc.scenes.synthetic_camera(48, 27))
 guarded(big, rtc.scenes.synthetic_camera(48, 27))
+guarded(big, rtc.scenes.synthetic_camera(48, 27), flags=ffi.OPT_F32_GENERAL_KERNEL)   # the kRefine form of the general f32 kernel (default: parity kernel)
+guarded(big, rtc.scenes.synthetic_camera(7, 5), flags=ffi.OPT_F32_GENERAL_KERNEL)     # fewer rays than a warp has lanes
 guarded(big, rtc.scenes.synthetic_camera(24, 14), flags=ffi.OPT_NO_BOUND_FILTER)
 guarded(room, rtc.scenes.reflect_refract_camera(1024, 512))   # tile scheduling pre-pass (>= 4096 tiles)
 both(room, rtc.scenes.reflect_refract_camera(64, 36))
@@ -78,7 +82,9 @@ both(room, rtc.scenes.reflect_refract_camera(40, 20, samples=5))
 both(room, rtc.scenes.reflect_refract_camera(64, 36), flags=ffi.OPT_F32_GENERAL_KERNEL)
 both(two, rtc.scenes.reflect_refract_camera(48, 24))
 both(cube_world, cube_cam)
+both(mid, rtc.scenes.synthetic_camera(48, 27))
 both(big, rtc.scenes.synthetic_camera(48, 27))
+both(big, rtc.scenes.synthetic_camera(48, 27), flags=ffi.OPT_F32_GENERAL_KERNEL)
 both(big, rtc.scenes.synthetic_camera(32, 18), flags=ffi.OPT_NO_BOUND_FILTER)
 # a 4K-sized tile count takes the tile scheduling pre-pass (classify_tiles_small_kernel): one larger frame
 r.upload(room)
