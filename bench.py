@@ -383,7 +383,7 @@ def run_gpu(args):
     # gather, no collective on the data path.  The frame is registered (rtc_register_host_buffer), so the library may deliver
     # by DMA straight into it; h2d / d2h bytes are per rank.
     from rtc_b200.sharded import SharedHostFrame
-    shared = SharedHostFrame(W, H, rank, N)
+    shared = SharedHostFrame(W, H, rank, N, numa_interleave=args.numa_interleave)
     host = shared.array
     shared.register(r)
 
@@ -412,12 +412,14 @@ def run_gpu(args):
         o2.flags |= fl
         return o2
 
-    # fast mode, the library's own delivery choice: N = 1 stages f32 over the one PCIe link and widens on the host (half the
-    # bytes); N > 1 DMA-writes f64 rows straight into the registered frame (no host pass)
+    # fast mode, the library's own delivery choice: N = 1 mixes — most row bands cross the one PCIe link as f32 and are widened
+    # by the host threads, the last few go as f64 by DMA straight into the frame, so that link and host threads finish together;
+    # N > 1 DMA-writes f64 rows straight into the registered frame (no host pass)
     e2e_t = e2e_run(oe, e2e_steps)
     e2e_ms = float(e2e_t.mean()) * 1e3
     direct_default = N > 1
-    d2h = my_rows * W * 3 * (8 if direct_default else 4)
+    delivery = r.delivery_info()          # bytes the last frame moved device -> host on this rank, bands and bands sent direct
+    d2h = delivery["d2h_bytes"]
     e2e_frame_ok = None
     if N > 1 and rank == 0:
         ref = torch.empty((H, W, 3), dtype=torch.float32, device=dev)
@@ -429,6 +431,7 @@ def run_gpu(args):
         e2e_frame_ok = bool(np.array_equal(host, ref_host))
     # the other delivery for comparison, and parity mode end to end (direct: 24 B/pixel cross PCIe either way)
     alt_t = e2e_run(with_flags(oe, ffi.OPT_DELIVER_STAGED if direct_default else ffi.OPT_DELIVER_DIRECT), max(1, e2e_steps // 2))
+    staged_t = e2e_run(with_flags(oe, ffi.OPT_DELIVER_STAGED), max(1, e2e_steps // 2)) if N == 1 else None
     e64_t = e2e_run(oe64, max(1, min(e2e_steps, 3)))
     frames = {}
     if N == 1:
@@ -522,14 +525,19 @@ def run_gpu(args):
             "e2e": {"value": rays / (e2e_ms * 1e-3) / 1e6, "unit": "Mrays/s", "ms_per_frame": e2e_ms, "h2d_bytes_per_step": int(h2d),
                     "d2h_bytes_per_step": int(d2h), "steps": e2e_steps,
                     "ms_per_frame_min": float(e2e_t.min()) * 1e3, "ms_per_frame_median": float(e2e_t.median()) * 1e3,
-                    "pcie_gbs_per_link": d2h / (e2e_ms * 1e-3) / 1e9,
-                    "path": "rtc_scene_upload + rtc_render (f32 fast, F64_RGB Canvas layout) into a registered host buffer: the frame crosses PCIe "
-                            "as f32 (half the bytes over the one link) and host threads widen it into the Canvas" if N == 1 else
+                    "pcie_gbs_per_link": d2h / (e2e_ms * 1e-3) / 1e9, "frame_pages": shared.numa,
+                    "row_bands": delivery["bands"], "row_bands_direct": delivery["bands_direct"],
+                    "path": "rtc_scene_upload + rtc_render (f32 fast, F64_RGB Canvas layout) into a registered host buffer, mixed delivery: the first "
+                            "row bands cross PCIe as f32 (half the bytes over the one link) and host threads widen them into the Canvas, the last "
+                            "row_bands_direct bands are written as f64 by the kernel and go by DMA straight into the Canvas (link and host threads side "
+                            "by side; the split follows the previous frame's timing; the frame does not depend on it)" if N == 1 else
                             "every rank: rtc_scene_upload + rtc_render of its shard (interleaved row tiles) into ONE registered f64 Canvas frame in host memory "
                             "shared by the rank processes — pitched DMA of f64 rows over the rank's own PCIe link, no staging, no host pass, no gather; "
                             "bytes are per rank; time = max over ranks per step",
                     "other_delivery": {"ms_per_frame": float(alt_t.mean()) * 1e3,
-                                       "path": "forced direct f64 DMA" if N == 1 else "staged: f32 over PCIe + widening by the rank's host threads (round 1's path)"}},
+                                       "path": "forced direct f64 DMA" if N == 1 else "staged: f32 over PCIe + widening by the rank's host threads (round 1's path)"},
+                    "staged_delivery": None if staged_t is None else {"ms_per_frame": float(staged_t.mean()) * 1e3,
+                                                                      "path": "all bands f32 over PCIe + widening by host threads (round 1's path)"}},
             # kernels of this library inside the timed region, all ranks: rank 0 runs the tile scheduling pre-pass + the render
             # kernel (+ the flag wait and the 'consumed' flag store when N > 1); every other rank ONE launch: its render kernel
             # waits for the back-pressure flag and stores its completion flag itself
@@ -576,6 +584,8 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--tile-rows", type=int, default=4, help="rows per interleaved tile (multi-GPU sharding)")
+    ap.add_argument("--numa-interleave", action="store_true",
+                    help="spread the pages of the shared host frame over the machine's memory nodes (mbind) instead of first touch by rank 0")
     ap.add_argument("--workload", default="c3", choices=["c3", "c4", "c5"],
                     help="c3 (default): the metric's 4K frame; c4: BASELINE.json configs[3], 10k random spheres + planes at 4K; "
                          "c5: configs[4], 7680x4320 with the deterministic 2x2 supersample")

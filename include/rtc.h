@@ -163,11 +163,15 @@ typedef struct rtc_render_opts {
  * sphere first.  Same image, hit mask and counters either way (the filter is conservative); for checking that. */
 #define RTC_OPT_NO_BOUND_FILTER 8
 /* rtc_render: deliver by DMA straight into the caller's buffer in out_format (no pinned staging, no host pass).  Needs
- * the buffer registered (rtc_register_host_buffer), else RTC_ERR_INVALID_ARG.  Without this flag the library chooses:
- * registered buffers get the direct delivery except for the one case where staging wins — a whole fast-mode frame on one
- * GPU into an F64_RGB Canvas, which crosses PCIe as f32 (half the bytes) and is widened by host threads. */
+ * the buffer registered (rtc_register_host_buffer), else RTC_ERR_INVALID_ARG.  Without a delivery flag the library chooses:
+ * registered buffers get the direct delivery except for a whole fast-mode frame on one GPU into an F64_RGB Canvas, where
+ * the one link is the limit: most of that frame crosses PCIe as f32 (half the bytes) and is widened by host threads, and
+ * the last few row bands are written as f64 by the kernel and go by DMA straight into the buffer, so that link and host
+ * threads finish together (how many bands follows the previous frame's timing; f32 -> f64 is exact on either side, the
+ * frame does not depend on the split). */
 #define RTC_OPT_DELIVER_DIRECT 16
-/* rtc_render: never deliver directly (measure the staged path with a registered buffer). */
+/* rtc_render: never deliver directly (measure the staged path with a registered buffer).  Both delivery flags together:
+ * the mixed delivery above with a fixed split (half the bands each way) — for tests. */
 #define RTC_OPT_DELIVER_STAGED 32
 
 #define RTC_MAX_DEPTH 8
@@ -248,6 +252,12 @@ int rtc_render_device_noalloc(rtc_context* ctx, const rtc_camera* cam, const rtc
  * Unregister before freeing the memory.  Replaces nothing in the reference (Canvas.pixels is a Vec, src/canvas.rs:17-22). */
 int rtc_register_host_buffer(rtc_context* ctx, void* ptr, size_t bytes);
 int rtc_unregister_host_buffer(rtc_context* ctx, void* ptr);
+
+/* What the last rtc_render on this context moved over PCIe and how: bytes copied device -> host for the frame (all GPUs
+ * of the context), the row bands (kernel launches) it was rendered in, and how many of those went by DMA straight into the
+ * caller's buffer (0: all staged; == bands: all direct; between: the mixed delivery of RTC_OPT_DELIVER_DIRECT's comment).
+ * Any pointer may be null.  Measurement support for the bench line's d2h_bytes_per_step; no counterpart in the reference. */
+int rtc_delivery_info(rtc_context* ctx, uint64_t* d2h_bytes, int* bands, int* bands_direct);
 
 /* Camera::render / render_async (src/camera.rs:116-160): renders the uploaded scene into the
  * caller's HOST buffers.  out_rgb: hsize*vsize*3 elements of opts->out_format, row-major

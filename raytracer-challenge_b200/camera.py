@@ -193,6 +193,12 @@ class Renderer:
     def unregister_host_buffer(self, array):
         ffi.check(self._lib.rtc_unregister_host_buffer(self._ctx, array.ctypes.data_as(C.c_void_p)))
 
+    def delivery_info(self):
+        """rtc_delivery_info: {"d2h_bytes", "bands", "bands_direct"} of the last render() on this context."""
+        b, n, k = C.c_uint64(0), C.c_int(0), C.c_int(0)
+        ffi.check(self._lib.rtc_delivery_info(self._ctx, C.byref(b), C.byref(n), C.byref(k)))
+        return {"d2h_bytes": int(b.value), "bands": int(n.value), "bands_direct": int(k.value)}
+
     def shard_rows(self, cam_desc, opts):
         return self._lib.rtc_shard_rows(C.byref(cam_desc), C.byref(opts))
 

@@ -58,12 +58,14 @@ struct DevBuf {
     }
 };
 
+constexpr int kMaxBands = 16;   // row bands of one rtc_render frame (launches whose copies overlap the next launch)
+
 struct DeviceState {
     int dev = 0;
     cudaStream_t stream = nullptr;
     cudaStream_t copy_stream = nullptr;   // D2H of finished bands while later bands render
-    cudaEvent_t ev_k0 = nullptr, ev_k1 = nullptr, ev_c1 = nullptr;
-    cudaEvent_t ev_band[8] = {}, ev_copy[8] = {};
+    cudaEvent_t ev_k0 = nullptr, ev_k1 = nullptr, ev_c0 = nullptr, ev_c1 = nullptr;   // timing events: kernels, copies of a frame
+    cudaEvent_t ev_band[kMaxBands] = {}, ev_copy[kMaxBands] = {};
     // scene
     DevBuf<double2> sph64, pl64;
     DevBuf<float4> pl32, us32, gs32, bound;
@@ -81,6 +83,7 @@ struct DeviceState {
     DevScene32 s32{};
     // frame
     DevBuf<unsigned char> rgb;
+    DevBuf<unsigned char> rgb_wide;   // f64 rows of the bands a mixed delivery sends by DMA straight into the caller's frame
     DevBuf<unsigned char> hit;
     DevBuf<Counters> counters;
     DevBuf<unsigned> work;  // tile counter of the persistent f32 kernel (+ blocks done, heavy / light tile counts)
@@ -208,6 +211,9 @@ struct rtc_context {
     std::vector<std::pair<unsigned char*, size_t>> registered;   // rtc_register_host_buffer ranges
     std::vector<bool> registered_owned;                          // false: the range was already page-locked by another owner (not ours to unregister)
     double wait_timeout_s = 60.0;
+    uint64_t last_d2h_bytes = 0;   // rtc_delivery_info: what the last rtc_render moved over PCIe, and how
+    int last_bands = 0, last_bands_direct = 0;
+    int mix_direct_bands = 2;   // mixed delivery (rtc_render, one GPU): bands of eight that go by f64 DMA; follows the host's speed
 };
 
 namespace {
@@ -1052,9 +1058,10 @@ int rtc_context_create(const int* device_ids, int n_gpus, rtc_context** out_ctx)
         if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&d.stream, cudaStreamNonBlocking);
         if (e == cudaSuccess) e = cudaEventCreate(&d.ev_k0);
         if (e == cudaSuccess) e = cudaEventCreate(&d.ev_k1);
+        if (e == cudaSuccess) e = cudaEventCreate(&d.ev_c0);
         if (e == cudaSuccess) e = cudaEventCreate(&d.ev_c1);
         if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&d.copy_stream, cudaStreamNonBlocking);
-        for (int b = 0; b < 8 && e == cudaSuccess; ++b) {
+        for (int b = 0; b < kMaxBands && e == cudaSuccess; ++b) {
             e = cudaEventCreateWithFlags(&d.ev_band[b], cudaEventDisableTiming);
             if (e == cudaSuccess) e = cudaEventCreateWithFlags(&d.ev_copy[b], cudaEventDisableTiming);
         }
@@ -1106,11 +1113,12 @@ void rtc_context_destroy(rtc_context* ctx) {
         if (d.stream) cudaStreamSynchronize(d.stream);
         d.sph64.release(); d.pl64.release(); d.pl32.release(); d.us32.release(); d.gs32.release(); d.us_index.release(); d.gs_index.release(); d.gset.release(); d.plL.release(); d.usL.release(); d.lights64.release(); d.lights32.release(); d.bound64.release(); d.gbound.release(); d.gbound64.release(); d.sbound.release(); d.sbound64.release(); d.bound.release(); d.gbox.release(); d.sbox.release();
         d.sph_index.release(); d.pl_index.release(); d.rec64.release(); d.rec32.release(); d.srec.release();
-        d.rgb.release(); d.hit.release(); d.counters.release(); d.work.release(); d.order.release(); d.wait_status.release();
+        d.rgb.release(); d.rgb_wide.release(); d.hit.release(); d.counters.release(); d.work.release(); d.order.release(); d.wait_status.release();
         if (d.ev_k0) cudaEventDestroy(d.ev_k0);
         if (d.ev_k1) cudaEventDestroy(d.ev_k1);
+        if (d.ev_c0) cudaEventDestroy(d.ev_c0);
         if (d.ev_c1) cudaEventDestroy(d.ev_c1);
-        for (int b = 0; b < 8; ++b) {
+        for (int b = 0; b < kMaxBands; ++b) {
             if (d.ev_band[b]) cudaEventDestroy(d.ev_band[b]);
             if (d.ev_copy[b]) cudaEventDestroy(d.ev_copy[b]);
         }
@@ -1807,6 +1815,8 @@ extern "C" int rtc_render(rtc_context* ctx, const rtc_camera* cam, const rtc_ren
                           ctx->pool, stats != nullptr, &ctx->pinned_counters[0], st);
         if (rc != RTC_OK) return rc;
         st.total_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+        ctx->last_d2h_bytes = (uint64_t)shard_num_rows((int)cam->vsize, tile_rows, opts->shard_index, opts->shard_count) * row_bytes;
+        ctx->last_bands = (int)st.kernel_launches; ctx->last_bands_direct = direct ? ctx->last_bands : 0;
         if (stats) *stats = st;
         return RTC_OK;
     }
@@ -1822,7 +1832,7 @@ extern "C" int rtc_render(rtc_context* ctx, const rtc_camera* cam, const rtc_ren
         //    left after the last kernel is the copy and delivery of a sixteenth of the frame.
         DeviceState& d = ctx->devs[0];
         CUDA_TRY(cudaSetDevice(d.dev));
-        static const int kPlanEq8[] = {1, 1, 1, 1, 1, 1, 1, 1}, kPlanF64[] = {6, 5, 3, 1, 1}, kPlanMid[] = {1, 2, 1}, kPlanOne[] = {1};
+        static const int kPlanEq8[] = {1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1}, kPlanF64[] = {6, 5, 3, 1, 1}, kPlanMid[] = {1, 2, 1}, kPlanOne[] = {1};
         const int* plan = kPlanOne; int n_plan = 1, plan_sum = 1;
         if (frame_bytes >= (32u << 20)) {
             // kernel-bound frames: parity mode, and fast mode outside the small-scene kernel (every launch has its own
@@ -1831,8 +1841,11 @@ extern "C" int rtc_render(rtc_context* ctx, const rtc_camera* cam, const rtc_ren
             if (d.s64.n_shapes > 256) { plan = kPlanOne; n_plan = 1; plan_sum = 1; }   // tens of ms of kernel, ms-long tails: one launch, then the copy
             else if (kernel_bound) { plan = kPlanF64; n_plan = 5; plan_sum = 16; }
             else { plan = kPlanEq8; n_plan = 8; plan_sum = 8; }
+#ifdef RTC_PROBE_KNOBS   // `make probe`: measurement build only (tools/e2e_mix_probe.py); the product library reads no environment
+            if (plan == kPlanEq8 && getenv("RTC_MIX_BANDS")) { n_plan = plan_sum = std::max(1, std::min(kMaxBands, atoi(getenv("RTC_MIX_BANDS")))); }
+#endif
         } else if (frame_bytes >= (4u << 20)) { plan = kPlanMid; n_plan = 3; plan_sum = 4; }
-        int band_r0[9];
+        int band_r0[kMaxBands + 1];
         int n_bands = 0;
         {
             int acc = 0, prev = 0;
@@ -1843,37 +1856,81 @@ extern "C" int rtc_render(rtc_context* ctx, const rtc_camera* cam, const rtc_ren
             }
             band_r0[n_bands] = (int)cam->vsize;
         }
+        // Mixed delivery (a fast-mode F64_RGB frame into a REGISTERED buffer): the first bands cross PCIe as f32 and are
+        // widened by the host threads, the last k_wide bands are written as f64 by the kernel and go by DMA straight into
+        // the caller's frame — the link and the host threads work side by side instead of the slower of the two setting
+        // the frame time.  f32 -> f64 is exact on either side, so the frame does not depend on k_wide.  Chosen per frame
+        // from how the previous frame ended (host threads still widening after the last byte had landed: one band more
+        // goes by DMA; DMA still running after the host had finished: one band fewer), or half the bands when both
+        // delivery flags are set (tests).
+        const bool mix_forced = registered && f32_wins && (opts->flags & RTC_OPT_DELIVER_DIRECT) && (opts->flags & RTC_OPT_DELIVER_STAGED);
+        const bool mix_auto = registered && f32_wins && !direct && !(opts->flags & (RTC_OPT_DELIVER_DIRECT | RTC_OPT_DELIVER_STAGED)) && plan == kPlanEq8;
+        int k_wide = mix_forced ? n_bands / 2 : (mix_auto ? std::min(ctx->mix_direct_bands, n_bands / 2) : 0);
+#ifdef RTC_PROBE_KNOBS
+        if (mix_auto && getenv("RTC_MIX_K")) k_wide = std::max(0, std::min(n_bands - 1, atoi(getenv("RTC_MIX_K"))));
+#endif
+        const size_t wide_row_bytes = row_elems * 8;
         CUDA_TRY(d.rgb.ensure(frame_bytes));
+        if (k_wide) CUDA_TRY(d.rgb_wide.ensure(wide_row_bytes * cam->vsize));
         if (out_hit_mask) CUDA_TRY(d.hit.ensure(mask_bytes));
         CUDA_TRY(cudaMemsetAsync(d.counters.p, 0, sizeof(Counters), d.stream));
         CUDA_TRY(cudaEventRecord(d.ev_k0, d.stream));
         for (int b = 0; b < n_bands; ++b) {
             const int r0 = band_r0[b], r1 = band_r0[b + 1];
-            CamParams cp = make_cam(cam, &dopts, 0, 1, 16);
+            const bool wide = b >= n_bands - k_wide;
+            rtc_render_opts bopts = dopts;
+            if (wide) bopts.out_format = RTC_OUT_F64_RGB;
+            CamParams cp = make_cam(cam, &bopts, 0, 1, 16);
             cp.dst_full = 1; cp.row0 = r0; cp.shard_rows = r1 - r0;
             // work counters only when the caller asked for stats: the plain kernel instantiation carries no book-keeping
-            rc = launch_on(d, cp, opts->precision, opts->flags, d.rgb.p, out_hit_mask ? d.hit.p : nullptr, stats ? d.counters.p : nullptr, d.stream);
+            rc = launch_on(d, cp, opts->precision, opts->flags, wide ? d.rgb_wide.p : d.rgb.p, out_hit_mask ? d.hit.p : nullptr, stats ? d.counters.p : nullptr, d.stream);
             if (rc != RTC_OK) return rc;
             CUDA_TRY(cudaEventRecord(d.ev_band[b], d.stream));
             CUDA_TRY(cudaStreamWaitEvent(d.copy_stream, d.ev_band[b], 0));
-            // direct: the band goes straight to its rows of the caller's (registered) frame
+            // direct (and the wide bands of a mixed delivery): the band goes straight to its rows of the caller's (registered) frame
+            if (wide)
+                CUDA_TRY(cudaMemcpyAsync(user + (size_t)r0 * wide_row_bytes, d.rgb_wide.p + (size_t)r0 * wide_row_bytes, (size_t)(r1 - r0) * wide_row_bytes,
+                                         cudaMemcpyDeviceToHost, d.copy_stream));
+            else
             CUDA_TRY(cudaMemcpyAsync((direct ? user : ctx->pinned_rgb) + (size_t)r0 * row_bytes, d.rgb.p + (size_t)r0 * row_bytes, (size_t)(r1 - r0) * row_bytes,
                                      cudaMemcpyDeviceToHost, d.copy_stream));
             if (out_hit_mask)
                 CUDA_TRY(cudaMemcpyAsync(ctx->pinned_hit + (size_t)r0 * cam->hsize, d.hit.p + (size_t)r0 * cam->hsize, (size_t)(r1 - r0) * cam->hsize,
                                          cudaMemcpyDeviceToHost, d.copy_stream));
             CUDA_TRY(cudaEventRecord(d.ev_copy[b], d.copy_stream));
+            if (mix_auto && b == 0) CUDA_TRY(cudaEventRecord(d.ev_c0, d.copy_stream));
         }
+        if (mix_auto) CUDA_TRY(cudaEventRecord(d.ev_c1, d.copy_stream));
         CUDA_TRY(cudaEventRecord(d.ev_k1, d.stream));
         CUDA_TRY(cudaMemcpyAsync(&ctx->pinned_counters[0], d.counters.p, sizeof(Counters), cudaMemcpyDeviceToHost, d.stream));
         double deliver_ms = 0.0;
+        auto first_landed = std::chrono::steady_clock::now(), host_done = first_landed;
         for (int b = 0; b < n_bands; ++b) {
             const int r0 = band_r0[b], r1 = band_r0[b + 1];
+            const bool wide = b >= n_bands - k_wide;
             CUDA_TRY(cudaEventSynchronize(d.ev_copy[b]));
             auto h0 = std::chrono::steady_clock::now();
-            if (!direct) host_deliver(ctx, user + (size_t)r0 * row_elems * out_elem, ctx->pinned_rgb + (size_t)r0 * row_bytes, (size_t)(r1 - r0) * row_elems, dev_elem, out_elem);
+            if (b == 0) first_landed = h0;
+            if (!direct && !wide) host_deliver(ctx, user + (size_t)r0 * row_elems * out_elem, ctx->pinned_rgb + (size_t)r0 * row_bytes, (size_t)(r1 - r0) * row_elems, dev_elem, out_elem);
             if (out_hit_mask) std::memcpy(out_hit_mask + (size_t)r0 * cam->hsize, ctx->pinned_hit + (size_t)r0 * cam->hsize, (size_t)(r1 - r0) * cam->hsize);
-            deliver_ms += std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - h0).count();
+            auto h1 = std::chrono::steady_clock::now();
+            if (!wide) host_done = h1;
+            deliver_ms += std::chrono::duration<double, std::milli>(h1 - h0).count();
+        }
+        if (mix_auto) {
+            // how long after the frame's last byte had landed the host threads finished their last band (negative: before)
+            float dma_ms = 0.f;
+            CUDA_TRY(cudaEventSynchronize(d.ev_c1));
+            CUDA_TRY(cudaEventElapsedTime(&dma_ms, d.ev_c0, d.ev_c1));
+            const double lag_ms = std::chrono::duration<double, std::milli>(host_done - first_landed).count() - (double)dma_ms;
+            const double band_ms = (double)dma_ms / (double)(n_bands + k_wide - 1);   // one f32 band over the link
+#ifdef RTC_PROBE_KNOBS
+            if (getenv("RTC_MIX_TRACE"))
+                fprintf(stderr, "mix: bands %d wide %d  first copy -> last copy %.3f ms  first landed -> host done %.3f ms  lag %.3f  deliver %.3f\n", n_bands, k_wide,
+                        dma_ms, std::chrono::duration<double, std::milli>(host_done - first_landed).count(), lag_ms, deliver_ms);
+#endif
+            if (lag_ms > 1.6 * band_ms && ctx->mix_direct_bands < n_bands / 2) ++ctx->mix_direct_bands;
+            else if (lag_ms < -1.6 * band_ms && ctx->mix_direct_bands > 0) --ctx->mix_direct_bands;
         }
         CUDA_TRY(cudaStreamSynchronize(d.stream));
         float k_ms = 0.f;
@@ -1885,6 +1942,8 @@ extern "C" int rtc_render(rtc_context* ctx, const rtc_camera* cam, const rtc_ren
         st.total_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
         st.d2h_ms = st.total_ms - k_ms;   // whatever was not hidden behind the kernel: PCIe + host delivery
         st.gather_ms = deliver_ms;
+        ctx->last_bands = n_bands; ctx->last_bands_direct = direct ? n_bands : k_wide;
+        ctx->last_d2h_bytes = (uint64_t)band_r0[n_bands - k_wide] * row_bytes + (uint64_t)((int)cam->vsize - band_r0[n_bands - k_wide]) * (k_wide ? wide_row_bytes : row_bytes);
         if (stats) *stats = st;
         return RTC_OK;
     }
@@ -1916,6 +1975,16 @@ extern "C" int rtc_render(rtc_context* ctx, const rtc_camera* cam, const rtc_ren
         st.kernel_launches += gst[g].kernel_launches;
     }
     st.total_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+    ctx->last_d2h_bytes = (uint64_t)cam->vsize * row_bytes;
+    ctx->last_bands = (int)st.kernel_launches; ctx->last_bands_direct = direct ? ctx->last_bands : 0;
     if (stats) *stats = st;
+    return RTC_OK;
+}
+
+extern "C" int rtc_delivery_info(rtc_context* ctx, uint64_t* d2h_bytes, int* bands, int* bands_direct) {
+    if (!ctx) return fail(RTC_ERR_INVALID_ARG, "rtc_delivery_info: null context");
+    if (d2h_bytes) *d2h_bytes = ctx->last_d2h_bytes;
+    if (bands) *bands = ctx->last_bands;
+    if (bands_direct) *bands_direct = ctx->last_bands_direct;
     return RTC_OK;
 }

@@ -103,6 +103,7 @@ EXPORTS = [
     ("rtc_render_device_noalloc", C.c_int, [C.c_void_p, C.POINTER(RtcCamera), C.POINTER(RtcRenderOpts), C.c_void_p, C.c_void_p, C.c_void_p]),
     ("rtc_register_host_buffer", C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t]),
     ("rtc_unregister_host_buffer", C.c_int, [C.c_void_p, C.c_void_p]),
+    ("rtc_delivery_info", C.c_int, [C.c_void_p, C.POINTER(C.c_uint64), C.POINTER(C.c_int), C.POINTER(C.c_int)]),
     ("rtc_pack_rgba8_device", C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_size_t, C.c_float, C.c_void_p, C.c_void_p]),
     ("rtc_download_frame", C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_uint32, C.c_uint32, C.c_int, C.c_void_p, C.c_void_p]),
     ("rtc_measure_peak_tflops", C.c_int, [C.c_void_p, C.c_int, C.POINTER(C.c_double)]),

@@ -198,16 +198,45 @@ class ShardedFrame:
         return self.frame if self.rank == 0 else None
 
 
+def _mbind_interleave(addr, nbytes):
+    """Spread the pages of a not-yet-touched mapping round-robin over the machine's memory nodes (mbind(2),
+    MPOL_INTERLEAVE; for a shared-memory segment the policy belongs to the segment, so it holds for every process that
+    maps it).  Eight GPUs hang off two sockets: a frame whose pages all sit on the socket of the thread that touched them
+    first makes half the GPUs' DMA cross the socket link.  Returns a word for the bench line; never raises."""
+    import ctypes
+    try:
+        nodes = []
+        for part in open("/sys/devices/system/node/has_memory").read().strip().split(","):
+            lo, _, hi = part.partition("-")
+            nodes += list(range(int(lo), int(hi or lo) + 1))
+        if len(nodes) < 2:
+            return "one memory node: nothing to interleave"
+        mask = (ctypes.c_ulong * 16)()
+        for n in nodes:
+            mask[n // 64] |= 1 << (n % 64)
+        libc = ctypes.CDLL(None, use_errno=True)
+        page = 4096
+        start = addr & ~(page - 1)
+        length = (addr + nbytes - start + page - 1) & ~(page - 1)
+        rc = libc.syscall(237, ctypes.c_void_p(start), ctypes.c_ulong(length), 3, mask, ctypes.c_ulong(16 * 64), 0)   # SYS_mbind (x86-64), MPOL_INTERLEAVE
+        if rc != 0:
+            return "mbind refused (errno %d): first touch by rank 0" % ctypes.get_errno()
+        return "pages interleaved over %d memory nodes" % len(nodes)
+    except Exception as e:   # no /sys node files, not x86-64, ...
+        return "interleave unavailable (%s): first touch by rank 0" % type(e).__name__
+
+
 class SharedHostFrame:
     """One Canvas frame (hsize x vsize x 3, f64 by default) in host memory that all rank processes of a node map:
     POSIX shared memory created by rank 0, its name broadcast over the process group.  Every rank's ``rtc_render`` with
     ``shard_index = rank, shard_count = world`` fills in the rows of its shard (include/rtc.h, rtc_render_opts) — its
     own PCIe link, its own host threads, no gather and no collective on the data path.  ``array`` is the numpy view."""
 
-    def __init__(self, hsize, vsize, rank, world, dtype="float64"):
+    def __init__(self, hsize, vsize, rank, world, dtype="float64", numa_interleave=False):
         import numpy as np
         from multiprocessing import shared_memory
         self.rank, self.world = rank, world
+        self.numa = "first touch by rank 0"
         nbytes = int(hsize) * int(vsize) * 3 * np.dtype(dtype).itemsize
         name = [None]
         if rank == 0:
@@ -224,6 +253,8 @@ class SharedHostFrame:
                 pass
         self.array = np.ndarray((vsize, hsize, 3), dtype=dtype, buffer=self._shm.buf)
         self._registered_with = None
+        if numa_interleave and rank == 0:
+            self.numa = _mbind_interleave(self.array.ctypes.data, nbytes)
 
     def register(self, renderer):
         """rtc_register_host_buffer on this process's mapping of the segment: this rank's rtc_render then delivers its

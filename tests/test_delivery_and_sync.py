@@ -40,6 +40,30 @@ def test_direct_delivery_into_a_registered_buffer_equals_staged(rtc, renderer, p
             renderer.unregister_host_buffer(buf)
 
 
+@pytest.mark.parametrize("size", [(1024, 516), (3840, 2160), (3840, 2161)])
+def test_mixed_delivery_of_a_fast_frame_equals_staged(rtc, renderer, size):
+    """A fast-mode frame into a registered F64_RGB Canvas buffer on one GPU: the first row bands cross PCIe as f32 and are
+    widened by host threads, the last ones are written as f64 by the kernel and DMA-ed straight into the buffer.  Either
+    way every value is the kernel's f32 widened exactly, so the frame is the staged frame bit for bit — with the split
+    fixed at half the bands (both delivery flags) and with the library's own choice over several frames in a row (the
+    split follows the previous frame's timing)."""
+    f = rtc.ffi
+    world, d = _room(rtc, *size)
+    renderer.upload(world)
+    want, want_hit, st = renderer.render(d, rtc.Renderer.make_opts(precision=1))          # unregistered: staged
+    buf = np.full((size[1], size[0], 3), 7.0)
+    renderer.register_host_buffer(buf)
+    try:
+        got, hit, st2 = renderer.render(d, rtc.Renderer.make_opts(precision=1, flags=f.OPT_DELIVER_DIRECT | f.OPT_DELIVER_STAGED), out=buf)
+        assert np.array_equal(buf, want) and np.array_equal(hit, want_hit) and st2.rays == st.rays
+        for _ in range(5):
+            buf[:] = 7.0
+            got, hit, st2 = renderer.render(d, rtc.Renderer.make_opts(precision=1), out=buf)
+            assert np.array_equal(buf, want) and np.array_equal(hit, want_hit) and st2.rays == st.rays
+    finally:
+        renderer.unregister_host_buffer(buf)
+
+
 @pytest.mark.parametrize("precision", [0, 1])
 @pytest.mark.parametrize("count,tile,size", [(2, 4, (200, 117)), (3, 16, (200, 117)), (8, 4, (1920, 1080)), (4, 4, (64, 3)),
                                              (2, 4, (3840, 2160)), (3, 20, (2560, 1441))])   # the last two: several row bands per shard
