@@ -1,0 +1,6 @@
+#!/bin/bash
+# plane screens in the parity kernel: whole GPU suite (bit-exactness), then kernel times of every config
+mkdir -p gpurun_out/c13; O=gpurun_out/c13
+timeout 2400 python -m pytest tests -m gpu -x -q > $O/pytest_gpu.txt 2>&1; echo "rc=$?" >> $O/pytest_gpu.txt
+tail -8 $O/pytest_gpu.txt
+timeout 300 python tools/perf_configs.py > $O/perf_configs.txt 2>&1; cat $O/perf_configs.txt
