@@ -37,8 +37,14 @@ struct Streams {  // intersect streams, in shared memory when they fit, else glo
 struct Neg { double t; int ord; int pad; };
 constexpr int kNegCap = 48;
 // kGroups: two-level filter (streams in global memory: big scenes, Morton order); otherwise entries four at a time
-template <bool kCollect, bool kCubes, bool kGroups>
-__device__ __noinline__ void intersect_world(const Streams& S, V3 o, V3 d, double& best_t, int& best_idx, Neg* neg, int& n_neg) {
+// kMode 0 / 1: kCollect fixed at compile time (two copies of the search in a kernel, one per ray kind); kMode 2: kCollect is
+// the run-time argument — ONE copy serves radiance and shadow rays.  The kernel is bound by instruction fetch as much as by
+// anything (5.7 k instructions, `no_instruction` 1.3 stall cycles per issue): sharing the copy takes 6 KB off the hot loop
+// and the room frames from 7.39 to 7.12 ms (C2 2.21 -> 2.10, C4 71.9 -> 69.9); the kExt kernels (resample pass, several
+// lights) are at their register limit and lose 2-3 % to the extra live flag, so they keep the two copies.
+template <int kMode, bool kCubes, bool kGroups>
+__device__ __noinline__ void intersect_world_impl(const Streams& S, V3 o, V3 d, double& best_t, int& best_idx, Neg* neg, int& n_neg, const bool collect) {
+    const bool kCollect = kMode == 2 ? collect : kMode == 1;
     best_t = __longlong_as_double(0x7ff0000000000000LL);
     best_idx = 0x7fffffff;
     if (kCollect) n_neg = 0;
@@ -172,6 +178,10 @@ __device__ __noinline__ void intersect_world(const Streams& S, V3 o, V3 d, doubl
     }
     if (best_idx == 0x7fffffff) best_idx = -1;
 }
+template <bool kCollect, bool kCubes, bool kGroups, bool kOneCopy>
+__device__ __forceinline__ void intersect_world(const Streams& S, V3 o, V3 d, double& best_t, int& best_idx, Neg* neg, int& n_neg) {
+    intersect_world_impl<kOneCopy ? 2 : (kCollect ? 1 : 0), kCubes, kGroups>(S, o, d, best_t, best_idx, neg, n_neg, kCollect);
+}
 
 // Intersection::compute_refractive (src/shape.rs:115-141) without materialising the list: see parity64.cuh (Cont, offer).
 template <bool kCubes>
@@ -250,6 +260,30 @@ __device__ __noinline__ void compute_refractive(const Streams& S, const DevScene
 
 // The same from the entries intersect_world<true> kept for this ray.
 __device__ __noinline__ void compute_refractive_kept(const DevScene64& sc, int hit_idx, const Neg* neg, int n_neg, double& n1, double& n2) {
+    if (sc.ids_unique) {
+        // Unique world_ids (every scene of at most 256 shapes): an id is toggled once per negative entry of ITS shape, so a
+        // shape is a container iff exactly one of its entries is negative.  A sphere or cube with both roots negative was
+        // kept as two consecutive entries: skipped as a pair — no parity words (a dynamically indexed local array).
+        Cont top1, top2;
+        top1.idx = -1; top2.idx = -1; top1.t = top2.t = 0.0; top1.ord = top2.ord = 0; top1.id = top2.id = -1;
+        bool hit_is_container = false;
+        for (int k = 0; k < n_neg; ++k) {
+            const int idx = neg[k].ord >> 1;
+            if (k + 1 < n_neg && (neg[k + 1].ord >> 1) == idx) { ++k; continue; }
+            if (idx == hit_idx) hit_is_container = true;
+            Cont e; e.t = neg[k].t; e.ord = neg[k].ord; e.idx = idx; e.id = idx;
+            if (top1.idx < 0 || later(e, top1)) { top2 = top1; top1 = e; }
+            else if (top2.idx < 0 || later(e, top2)) top2 = e;
+        }
+        n1 = top1.idx >= 0 ? sc.rec[top1.idx].refractive_index : 1.0;
+        if (hit_is_container) {
+            if (top1.idx == hit_idx) n2 = top2.idx >= 0 ? sc.rec[top2.idx].refractive_index : 1.0;
+            else n2 = n1;
+        } else {
+            n2 = sc.rec[hit_idx].refractive_index;
+        }
+        return;
+    }
     unsigned parity[8];
 #pragma unroll
     for (int k = 0; k < 8; ++k) parity[k] = 0u;
@@ -275,15 +309,24 @@ __device__ __noinline__ void compute_refractive_kept(const DevScene64& sc, int h
     }
 }
 
+// `n % 2.0 == 0.0` (Rust's % on f64 is fmod) for an INTEGER-VALUED n — a floor(), or a sum of floor()s
+// (src/material.rs:97-103,163-170,198-205) — without the ~170-instruction fmod routine: the remainder is 0 iff n is even,
+// n * 0.5 is exact, and it is an integer iff n is even (from 2^53 on every double is an even integer and its half an
+// integer).  fmod(+-inf) and fmod(NaN) are NaN, which never equals 0: the magnitude test and the NaN compare keep that.
+__device__ __forceinline__ bool even_int(double n) {
+    const double h = n * 0.5;
+    return h == floor(h) && fabs(n) <= 1.7976931348623157e308;
+}
+
 // Pattern::pattern_at for the six patterns (src/material.rs:67-69,97-103,133-135,163-170,198-205,233-241)
 __device__ __forceinline__ V3 pattern_at(const ShadeRec64& r, V3 p) {
     V3 a = mk(r.pat_a[0], r.pat_a[1], r.pat_a[2]), b = mk(r.pat_b[0], r.pat_b[1], r.pat_b[2]);
     switch (r.pattern_kind) {
         case RTC_PATTERN_TEST: return p;
-        case RTC_PATTERN_STRIPE: return fmod(floor(p.x), 2.0) == 0. ? a : b;
+        case RTC_PATTERN_STRIPE: return even_int(floor(p.x)) ? a : b;
         case RTC_PATTERN_GRADIENT: return add(a, mul(sub(b, a), p.x - floor(p.x)));
-        case RTC_PATTERN_RING: return fmod(floor(sqrt(p.x * p.x + p.y * p.y)), 2.0) == 0.0 ? a : b;
-        case RTC_PATTERN_CHECKER: return fmod(floor(p.x) + floor(p.y) + floor(p.z), 2.0) == 0.0 ? a : b;
+        case RTC_PATTERN_RING: return even_int(floor(sqrt(p.x * p.x + p.y * p.y))) ? a : b;
+        case RTC_PATTERN_CHECKER: return even_int(floor(p.x) + floor(p.y) + floor(p.z)) ? a : b;
         default: /* GRID: a = base, b = grid lines */
             return (fabs(p.x - floor(p.x)) < 0.01 || fabs(p.z - floor(p.z)) < 0.01) ? b : a;
     }
@@ -425,7 +468,7 @@ render_f64_kernel(DevScene64 sc, CamParams cam, double* __restrict__ out_f64, fl
             bool descended = false;
             double t; int idx;
             ++n_rays;
-            intersect_world<true, kCubes, !kInSmem>(S, ro, rd, t, idx, kept, n_neg);
+            intersect_world<true, kCubes, !kInSmem, !kExt>(S, ro, rd, t, idx, kept, n_neg);
             if (first) { primary_hit = idx >= 0; first = false; }
             if (idx < 0) {
                 color = mk(0., 0., 0.);  // background_color, src/shape.rs:652
@@ -471,7 +514,7 @@ render_f64_kernel(DevScene64 sc, CamParams cam, double* __restrict__ out_f64, fl
                     V3 sdir = normalize(v);
                     double st; int sidx;
                     ++n_rays; ++n_shadow;
-                    intersect_world<false, kCubes, !kInSmem>(S, over_point, sdir, st, sidx, kept, n_shadow_neg);
+                    intersect_world<false, kCubes, !kInSmem, !kExt>(S, over_point, sdir, st, sidx, kept, n_shadow_neg);
                     bool shadowed = sidx >= 0 && st < distance;
                     V3 term = lighting(rec, lpos, lint, over_point, eyev, normal, shadowed);
                     surface = li == 0 ? term : add(surface, term);

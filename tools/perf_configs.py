@@ -1,4 +1,4 @@
-"""Kernel timings of the other BASELINE.json configs through rtc_render_device on one GPU:
+"""(RTC_B200_LIB selects a kernel-variant library for A/B runs.)  Kernel timings of the BASELINE.json configs through rtc_render_device on one GPU:
 C2 (1920x1080 room), C4 (10k shapes, 4K), C5 (8K, 2x2 supersample).  usage: python tools/perf_configs.py"""
 import os, sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
@@ -10,7 +10,8 @@ room = rtc.scenes.reflect_refract_scene().flatten()
 c4 = rtc.scenes.synthetic_scene().flatten()
 two = rtc.scenes.reflect_refract_scene()
 two.add_light(rtc.Light(rtc.Color(0.3, 0.5, 0.9), (3.5, 3.0, -3.0)))
-cases = [("C3 room 3840x2160 samples=4", room, rtc.scenes.reflect_refract_camera(3840, 2160, samples=4), 3),   # resample pass
+cases = [("C3 room 3840x2160", room, rtc.scenes.reflect_refract_camera(3840, 2160), 5),
+         ("C3 room 3840x2160 samples=4", room, rtc.scenes.reflect_refract_camera(3840, 2160, samples=4), 3),   # resample pass
          ("C5 room 7680x4320 samples=4", room, rtc.scenes.reflect_refract_camera(7680, 4320, samples=4), 2),
          ("C3 room 3840x2160 2 lights", (two.flatten_lights(), two.flatten()[1], two.flatten()[2]), rtc.scenes.reflect_refract_camera(3840, 2160), 3),
          ("C2 room 1920x1080", room, rtc.scenes.reflect_refract_camera(1920, 1080), 5),
