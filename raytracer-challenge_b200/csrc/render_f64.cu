@@ -383,7 +383,14 @@ template <bool kInSmem, bool kCubes, bool kExt>
 #ifndef RTC_F64_MIN_BLOCKS
 #define RTC_F64_MIN_BLOCKS 4
 #endif
-__global__ void __launch_bounds__(kThreads, RTC_F64_MIN_BLOCKS)
+#ifndef RTC_F64_MIN_BLOCKS_GLOBAL
+#define RTC_F64_MIN_BLOCKS_GLOBAL 8
+#endif
+// Blocks per SM.  Streams in shared memory (the room scenes): the kernel waits for its own FP64 chains and for instruction
+// fetch, and 4 blocks at 128 registers beat 5 / 6 blocks at 96 / 80 registers with spills (C3 4K 6.69 / 6.71 / 6.83 ms).
+// Streams in global memory (big scenes): it waits for the hierarchy's loads, and more resident warps pay for the
+// spills (C4 4K 69.7 / 65.3 / 61.1 / 58.0 / 56.2 / 62.9 / 74.4 ms at 4 / 5 / 6 / 7 / 8 / 10 / 12 blocks: 8 blocks, 64 registers).
+__global__ void __launch_bounds__(kThreads, kInSmem ? RTC_F64_MIN_BLOCKS : RTC_F64_MIN_BLOCKS_GLOBAL)
 render_f64_kernel(DevScene64 sc, CamParams cam, double* __restrict__ out_f64, float* __restrict__ out_f32,
                   uint8_t* __restrict__ out_u8, uint8_t* __restrict__ out_hit, Counters* __restrict__ counters) {
     extern __shared__ double2 smem[];
@@ -728,7 +735,12 @@ cudaError_t launch_render_f64(const DevScene64& scene, const CamParams& cam, voi
         if (resample) return cubes ? launch(render_f64_kernel<kS, true, true>, bytes) : launch(render_f64_kernel<kS, false, true>, bytes);
         return cubes ? launch(render_f64_kernel<kS, true, false>, bytes) : launch(render_f64_kernel<kS, false, false>, bytes);
     };
-    if (smem <= 200 * 1024) e = pick(std::true_type{}, smem);
+    // Streams in shared memory + the flat search (four bounding spheres per trip) for small scenes; from ~64 spheres / cubes on
+    // the hierarchical search over streams in global memory wins, and by a growing factor (1920x1080, n random spheres, flat /
+    // hierarchical: n = 48 1.9 / 2.3 ms, 64 2.2 / 2.2, 100 2.8 / 2.2, 400 8.5 / 3.3, 1500 99.6 / 6.2: the flat search is
+    // linear in n and large streams leave room for one block per SM; profiles/r02_mid_scenes.txt).  Same frames either way.
+    const bool in_smem = scene.n_spheres + scene.n_cubes <= 64 && smem <= 48 * 1024;
+    if (in_smem) e = pick(std::true_type{}, smem);
     else e = pick(std::false_type{}, 0);
     if (e != cudaSuccess) return e;
     return cudaGetLastError();

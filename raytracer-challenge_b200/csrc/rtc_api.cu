@@ -985,12 +985,15 @@ int launch_on(DeviceState& d, const CamParams& cp, int precision, int flags, voi
     if (sync && !fused && sync->wait_flag) {   // kernels without the fused form: the flag kernels around the launch
         wait_kernel<<<1, 32, 0, st>>>(sync->wait_flag, 1, sync->wait_value, sync->timeout_ns, d.wait_status.p);
     }
-    // Fast mode promises the tolerance, not a data type: on scenes whose streams do not fit shared memory (10^3+ shapes) the
-    // fastest kernel that meets it is the parity kernel with its per-lane three-level walk (C4 4K: 71 ms, and exact) — the
-    // mixed-precision kRefine form of the general f32 kernel needs 109 ms (profiles/r02_experiments.txt) and stays reachable
-    // through RTC_OPT_F32_GENERAL_KERNEL.  The parity kernel converts to the requested output format itself.
+    // Fast mode promises the tolerance, not a data type.  Beyond ~128 shapes the fastest kernel that meets it is the parity
+    // kernel in its hierarchical form (per-lane three-level walk over the k-d ordered streams, 8 blocks per SM), and it is
+    // exact: the general f32 kernel tests every bounding sphere of a stream held in shared memory, linear in the scene
+    // (1920x1080, n random spheres, general f32 kernel / parity kernel: n = 100 1.9 / 2.2 ms, 150 2.9 / 2.2, 400 7.4 / 3.3,
+    // 1500 29 / 6.2, 3000 96 / 8.7; profiles/r02_mid_scenes.txt), and on streams too large for shared memory its
+    // mixed-precision kRefine form needs 109 ms where the parity kernel needs 56 (C4 4K; profiles/r02_experiments.txt).
+    // Both stay reachable through RTC_OPT_F32_GENERAL_KERNEL.  The parity kernel converts to the requested output format.
     const bool big_to_parity = precision == RTC_PRECISION_F32_FAST && !(flags & RTC_OPT_F32_GENERAL_KERNEL) && !d.small_ok &&
-                               d.s64.n_bound4 > 0 && f32_streams_are_global(d.s32);
+                               d.s64.n_bound4 > 0 && (f32_streams_are_global(d.s32) || d.s64.n_shapes > 128);
     if (precision == RTC_PRECISION_F64_PARITY || big_to_parity) {
         DevScene64 s64 = d.s64;
         if (flags & RTC_OPT_NO_BOUND_FILTER) s64.n_bound4 = 0;

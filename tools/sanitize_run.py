@@ -71,6 +71,7 @@ guarded(room, rtc.scenes.reflect_refract_camera(64, 36), flags=ffi.OPT_F32_GENER
 guarded(two, rtc.scenes.reflect_refract_camera(48, 24))
 guarded(cube_world, cube_cam)
 guarded(mid, rtc.scenes.synthetic_camera(48, 27))
+guarded(mid, rtc.scenes.synthetic_camera(48, 27), flags=ffi.OPT_F32_GENERAL_KERNEL)   # the general f32 kernel with 1500 shapes in shared memory (default: parity kernel)
 guarded(big, rtc.scenes.synthetic_camera(48, 27))
 guarded(big, rtc.scenes.synthetic_camera(48, 27), flags=ffi.OPT_F32_GENERAL_KERNEL)   # the kRefine form of the general f32 kernel (default: parity kernel)
 guarded(big, rtc.scenes.synthetic_camera(7, 5), flags=ffi.OPT_F32_GENERAL_KERNEL)     # fewer rays than a warp has lanes
@@ -83,6 +84,7 @@ both(room, rtc.scenes.reflect_refract_camera(64, 36), flags=ffi.OPT_F32_GENERAL_
 both(two, rtc.scenes.reflect_refract_camera(48, 24))
 both(cube_world, cube_cam)
 both(mid, rtc.scenes.synthetic_camera(48, 27))
+both(mid, rtc.scenes.synthetic_camera(48, 27), flags=ffi.OPT_F32_GENERAL_KERNEL)
 both(big, rtc.scenes.synthetic_camera(48, 27))
 both(big, rtc.scenes.synthetic_camera(48, 27), flags=ffi.OPT_F32_GENERAL_KERNEL)
 both(big, rtc.scenes.synthetic_camera(32, 18), flags=ffi.OPT_NO_BOUND_FILTER)
