@@ -120,6 +120,9 @@ __device__ __forceinline__ unsigned intersect_small(const SmallParams& P, F3 o, 
         best = min(best, min(sphere_key<kSmallMaxPlanes + 2 * g>(P.usph[2 * g], o, d, mask_reg),
                              sphere_key<kSmallMaxPlanes + 2 * g + 1>(P.usph[2 * g + 1], o, d, mask_reg)));
     });
+    // an odd count's last shape: the last slot of its array (a padded pair would cost a whole second test per ray)
+    if (P.np_odd) best = min(best, plane_key<kSmallMaxPlanes - 1>(P.planes[kSmallMaxPlanes - 1], o, d, mask_reg));
+    if (P.nu_odd) best = min(best, sphere_key<kSmallMaxPlanes + kSmallMaxUsph - 1>(P.usph[kSmallMaxUsph - 1], o, d, mask_reg));
     return best;
 }
 
@@ -150,6 +153,15 @@ __device__ __forceinline__ bool shadow_small(const SmallParams& P, F3 o, F3 d) {
         }
         g = fminf(g, fminf(fm[0], fm[1]));
     });
+    if (P.np_odd) g = fminf(g, row4(P.splanes[kSmallMaxPlanes - 1], o));
+    if (P.nu_odd) {
+        const float4 sp = P.usph_s[kSmallMaxUsph - 1];
+        F3 L = mk(o.x - sp.x, o.y - sp.y, o.z - sp.z);
+        float f0 = fmaf(L.z, L.z, fmaf(L.y, L.y, fmaf(L.x, L.x, -sp.w)));
+        float b2 = dot(d2, L);
+        float tc = __saturatef(b2 * nhia);
+        g = fminf(g, fmaf(tc, fmaf(a, tc, b2), f0));
+    }
     return g <= 0.f;
 }
 
@@ -195,6 +207,8 @@ __device__ __forceinline__ Top2 containers_small(const SmallParams& P, F3 o, F3 
         t = offer2(t, sphere_back_key<kSmallMaxPlanes + 2 * g>(P.usph[2 * g], o, d, mask_reg),
                    sphere_back_key<kSmallMaxPlanes + 2 * g + 1>(P.usph[2 * g + 1], o, d, mask_reg));
     });
+    if (P.np_odd) t = offer2(t, plane_back_key<kSmallMaxPlanes - 1>(P.planes_d[kSmallMaxPlanes - 1], o, d, mask_reg), 0xffffffffu);
+    if (P.nu_odd) t = offer2(t, sphere_back_key<kSmallMaxPlanes + kSmallMaxUsph - 1>(P.usph[kSmallMaxUsph - 1], o, d, mask_reg), 0xffffffffu);
     return t;
 }
 
@@ -249,8 +263,10 @@ render_f32_small_kernel(const __grid_constant__ SmallParams P, void* __restrict_
     {   // stage the shading records (indexed by stream position): coalesced 16-byte loads
         constexpr int kRec4 = (int)(sizeof(SmallRec32) / 16);
         const float4* g_rec = reinterpret_cast<const float4*>(P.rec);
-        for (int i = threadIdx.x; i < kRec4 * P.np; i += kThreads) smem4[i] = g_rec[i];
-        for (int i = threadIdx.x; i < kRec4 * P.nu; i += kThreads) smem4[kRec4 * kSmallMaxPlanes + i] = g_rec[kRec4 * kSmallMaxPlanes + i];
+        for (int i = threadIdx.x; i < kRec4 * 2 * P.npg; i += kThreads) smem4[i] = g_rec[i];
+        for (int i = threadIdx.x; i < kRec4 * 2 * P.nug; i += kThreads) smem4[kRec4 * kSmallMaxPlanes + i] = g_rec[kRec4 * kSmallMaxPlanes + i];
+        if (P.np_odd) for (int i = threadIdx.x; i < kRec4; i += kThreads) smem4[kRec4 * (kSmallMaxPlanes - 1) + i] = g_rec[kRec4 * (kSmallMaxPlanes - 1) + i];
+        if (P.nu_odd) for (int i = threadIdx.x; i < kRec4; i += kThreads) smem4[kRec4 * (kSmallMaxShapes - 1) + i] = g_rec[kRec4 * (kSmallMaxShapes - 1) + i];
         if (P.wait_flag && threadIdx.x == 0) {   // back-pressure: the destination frame is free once the consumer says so
             unsigned long long t0, t1;
             asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
@@ -418,7 +434,8 @@ render_f32_small_kernel(const __grid_constant__ SmallParams P, void* __restrict_
 
         // ------------------------------------------------------------ phase B: prepare_computations (src/shape.rs:75-96,144-152)
         const int hpos = hit ? (int)(key & kMask) : 0;
-        RTC_CHECK(!hit || hpos < P.np || (hpos >= kSmallMaxPlanes && hpos < kSmallMaxPlanes + P.nu));
+        RTC_CHECK(!hit || hpos < 2 * P.npg || (P.np_odd && hpos == kSmallMaxPlanes - 1) || (hpos >= kSmallMaxPlanes && hpos < kSmallMaxPlanes + 2 * P.nug) ||
+                  (P.nu_odd && hpos == kSmallMaxShapes - 1));
         const float t = __uint_as_float((key & ~kMask) | ((kMask + 1u) >> 1));   // centre of the truncation interval
         const unsigned rec = rbase + (unsigned)hpos * kRecBytes;
         const float4 tr = lds4(rec + kOffTrRi);
@@ -669,7 +686,7 @@ cudaError_t launch_render_f32_small(const SmallParams& P, int out_format, void* 
     int dev = 0, sms = 0;
     cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-    const size_t smem = (size_t)(kSmallMaxPlanes + P.nu) * sizeof(SmallRec32) + 16;
+    const size_t smem = (size_t)(P.nu_odd ? kSmallMaxShapes : kSmallMaxPlanes + P.nu) * sizeof(SmallRec32) + 16;   // records by stream position
     const int warps = kThreads / 32;
     if (P.order) classify_tiles_small_kernel<<<(P.total_tiles + kThreads - 1) / kThreads, kThreads, 0, stream>>>(P, d_work);
     auto launch = [&](auto kernel) -> cudaError_t {

@@ -724,7 +724,10 @@ int flatten(const rtc_light* lights, size_t n_lights, const rtc_shape* shapes, s
         for (int k = 0; k < kSmallMaxPlanes; ++k) sp.planes[k] = sp.planes_d[k] = sp.splanes[k] = make_float4(0.f, 0.f, 0.f, 1.f);
         for (int k = 0; k < kSmallMaxUsph; ++k) sp.usph[k] = sp.usph_s[k] = make_float4(0.f, 0.f, 0.f, -1.f);
         hs.srec.assign(kSmallMaxShapes, SmallRec32{});
-        sp.np = np; sp.nu = nu; sp.npg = (np + 1) / 2; sp.nug = (nu + 1) / 2;
+        sp.np = np; sp.nu = nu; sp.npg = np / 2; sp.nug = nu / 2; sp.np_odd = np & 1; sp.nu_odd = nu & 1;
+        // stream position of plane k / sphere k: an odd count's last shape goes to the last slot (SmallParams::np_odd)
+        auto plane_slot = [&](int k) { return (k == np - 1 && (np & 1)) ? kSmallMaxPlanes - 1 : k; };
+        auto sphere_slot = [&](int k) { return (k == nu - 1 && (nu & 1)) ? kSmallMaxUsph - 1 : k; };
         int n_glass = 0;
         auto fill_common = [&](SmallRec32& r, const rtc_shape& s, const ShadeRec32& q) {
             r.col_amb = q.col_amb; r.dif_spec = q.dif_spec;
@@ -736,14 +739,15 @@ int flatten(const rtc_light* lights, size_t n_lights, const rtc_shape* shapes, s
         for (int k = 0; k < np; ++k) {
             const int i = hs.pl_index[k];
             const float4 pl = hs.pl32[k];
-            sp.planes[k] = sp.planes_d[k] = pl;
+            const int slot = plane_slot(k);
+            sp.planes[slot] = sp.planes_d[slot] = pl;
             // f(1) = n.light + w: fold it into the coefficients so that the shadow test is splane.(o,1) <= 0
             const double f1 = shapes[i].inv[4] * lp[0] + shapes[i].inv[5] * lp[1] + shapes[i].inv[6] * lp[2] + shapes[i].inv[7];
             const double sc = f1 / (std::fabs(f1) > 0.0 ? std::fabs(f1) : 1.0);   // sign only: keeps the magnitudes of the plane
-            sp.splanes[k] = make_float4((float)(shapes[i].inv[4] * sc), (float)(shapes[i].inv[5] * sc), (float)(shapes[i].inv[6] * sc),
-                                        (float)(shapes[i].inv[7] * sc));
-            if (f1 == 0.0) sp.splanes[k] = make_float4(0.f, 0.f, 0.f, 1.f);   // the light lies in the plane: it never shadows (see plL above)
-            SmallRec32& r = hs.srec[k];
+            sp.splanes[slot] = make_float4((float)(shapes[i].inv[4] * sc), (float)(shapes[i].inv[5] * sc), (float)(shapes[i].inv[6] * sc),
+                                           (float)(shapes[i].inv[7] * sc));
+            if (f1 == 0.0) sp.splanes[slot] = make_float4(0.f, 0.f, 0.f, 1.f);   // the light lies in the plane: it never shadows (see plL above)
+            SmallRec32& r = hs.srec[slot];
             const float4 g0 = hs.rec32[i].g0;
             r.nrm = make_float4(g0.x, g0.y, g0.z, 0.f);
             fill_common(r, shapes[i], hs.rec32[i]);
@@ -751,8 +755,9 @@ int flatten(const rtc_light* lights, size_t n_lights, const rtc_shape* shapes, s
         }
         for (int k = 0; k < nu; ++k) {
             const int i = hs.us_index[k];
-            sp.usph[k] = sp.usph_s[k] = hs.us32[k];
-            SmallRec32& r = hs.srec[kSmallMaxPlanes + k];
+            const int slot = sphere_slot(k);
+            sp.usph[slot] = sp.usph_s[slot] = hs.us32[k];
+            SmallRec32& r = hs.srec[kSmallMaxPlanes + slot];
             const float4 g0 = hs.rec32[i].g0;   // (c, 1/r)
             r.nrm = make_float4(-g0.x * g0.w, -g0.y * g0.w, -g0.z * g0.w, g0.w);
             fill_common(r, shapes[i], hs.rec32[i]);

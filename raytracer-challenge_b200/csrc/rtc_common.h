@@ -158,7 +158,9 @@ struct SmallParams {
     float4 usph[kSmallMaxUsph];        // (cx, cy, cz, r^2); padding (0,0,0,-1): never hit
     float4 usph_s[kSmallMaxUsph];      // same again (the shadow loop's copy)
     float4 glass[kSmallMaxGlass];      // the spheres with refractive_index != 1
-    int npg, nug;                      // plane / sphere groups of two
+    int npg, nug;                      // FULL plane / sphere groups of two: the streams' positions [0, 2 npg) and [0, 2 nug)
+    int np_odd, nu_odd;                // an odd count's last shape sits in the LAST slot of its array (position kSmallMaxPlanes - 1 /
+                                       // kSmallMaxUsph - 1: a compile-time position like every other) and is tested on its own
     int np, nu;
     int n_glass;                       // -1: fast n1/n2 test unavailable (a glass plane, or more than 8 glass spheres)
     int n_extra;                       // antialiasing_samples when >= 2 (resample passes, src/camera.rs:84-92), else 0
