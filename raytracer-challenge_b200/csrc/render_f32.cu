@@ -1416,13 +1416,19 @@ cudaError_t preload_render_f32() {
     return e;
 }
 
+// Beyond this many shapes the general kernel runs in its kRefine form (hierarchy queries in f32, the radiance rays' geometry
+// in f64) even when its streams would fit shared memory: an all-f32 path drifts on dense sphere fields — every bounce
+// amplifies the hit point's rounding — and falls under the 99.9 % bar (1500 random spheres: 99.79 % of the pixels within
+// 1/255; tests/test_gpu_parity.py::test_fast_mode_dispatch_by_scene_size).  Fast mode's default for such scenes is the
+// parity kernel (rtc_api.cu, launch_on); this is what RTC_OPT_F32_GENERAL_KERNEL gets.
+constexpr int kRefineFromShapes = 128;
 static size_t f32_stream_bytes(const DevScene32& scene) {
     const int n_obj = scene.n_gsph + scene.n_cube;
     return (size_t)(scene.n_planes + scene.n_usph + 3 * n_obj) * 16 + (size_t)(scene.n_planes + scene.n_usph + n_obj) * 4 +
            (size_t)(scene.n_planes + scene.n_usph) * 4 + 16 * 4 + 16;
 }
 bool f32_streams_are_global(const DevScene32& scene) {
-    return f32_stream_bytes(scene) + (size_t)scene.n_shapes * sizeof(ShadeRec32) > 40 * 1024 && f32_stream_bytes(scene) > 96 * 1024;
+    return f32_stream_bytes(scene) + (size_t)scene.n_shapes * sizeof(ShadeRec32) > 40 * 1024 && (f32_stream_bytes(scene) > 96 * 1024 || scene.n_shapes > kRefineFromShapes);
 }
 
 cudaError_t launch_render_f32(const DevScene32& scene, const CamParams& cam, void* d_rgb, uint8_t* d_hit,
@@ -1439,7 +1445,7 @@ cudaError_t launch_render_f32(const DevScene32& scene, const CamParams& cam, voi
     const int tiles = ((cam.hsize + kTileX - 1) / kTileX) * ((cam.shard_rows + kTileY - 1) / kTileY);
     const int warps = kThreads / 32;
     const bool small = streams + recs <= 40 * 1024;
-    const bool global_streams = !small && streams > 96 * 1024;   // big scenes: streams stay in global memory behind L1/L2
+    const bool global_streams = !small && (streams > 96 * 1024 || scene.n_shapes > kRefineFromShapes);   // big scenes: streams stay in global memory behind L1/L2
     const size_t smem = global_streams ? (size_t)(kThreads / 32) * kWarpSlotBytes : (small ? streams + recs : streams);
     auto launch = [&](auto kernel) -> cudaError_t {
         cudaError_t er = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);

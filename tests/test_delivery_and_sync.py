@@ -64,6 +64,32 @@ def test_mixed_delivery_of_a_fast_frame_equals_staged(rtc, renderer, size):
         renderer.unregister_host_buffer(buf)
 
 
+def test_delivery_info_reports_what_the_last_render_moved(rtc, renderer):
+    """rtc_delivery_info: bytes copied device -> host, row bands and bands sent by DMA straight into the caller's buffer, for the
+    staged, the direct and the mixed delivery of one fast-mode frame into an F64_RGB buffer."""
+    f = rtc.ffi
+    w, h = 1024, 516
+    world, d = _room(rtc, w, h)
+    renderer.upload(world)
+    buf = np.zeros((h, w, 3))
+    renderer.render(d, rtc.Renderer.make_opts(precision=1), out=buf, want_mask=False)              # not registered: staged, f32 over PCIe
+    info = renderer.delivery_info()
+    assert info["d2h_bytes"] == w * h * 3 * 4 and info["bands_direct"] == 0 and info["bands"] >= 1
+    renderer.register_host_buffer(buf)
+    try:
+        renderer.render(d, rtc.Renderer.make_opts(precision=1, flags=f.OPT_DELIVER_DIRECT), out=buf, want_mask=False)
+        info = renderer.delivery_info()
+        assert info["d2h_bytes"] == w * h * 3 * 8 and info["bands_direct"] == info["bands"] >= 1
+        renderer.render(d, rtc.Renderer.make_opts(precision=1, flags=f.OPT_DELIVER_DIRECT | f.OPT_DELIVER_STAGED), out=buf, want_mask=False)
+        info = renderer.delivery_info()
+        assert 0 < info["bands_direct"] < info["bands"] and w * h * 3 * 4 < info["d2h_bytes"] < w * h * 3 * 8
+        renderer.render(d, rtc.Renderer.make_opts(precision=0), out=buf, want_mask=False)          # parity mode, registered: direct
+        info = renderer.delivery_info()
+        assert info["d2h_bytes"] == w * h * 3 * 8 and info["bands_direct"] == info["bands"]
+    finally:
+        renderer.unregister_host_buffer(buf)
+
+
 @pytest.mark.parametrize("precision", [0, 1])
 @pytest.mark.parametrize("count,tile,size", [(2, 4, (200, 117)), (3, 16, (200, 117)), (8, 4, (1920, 1080)), (4, 4, (64, 3)),
                                              (2, 4, (3840, 2160)), (3, 20, (2560, 1441))])   # the last two: several row bands per shard

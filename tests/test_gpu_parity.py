@@ -666,3 +666,26 @@ def test_c5_8k_supersampled_lattice(rtc, orc, renderer):
     cam = rtc.scenes.reflect_refract_camera(7680, 4320, samples=0)
     st, st32, ok = _lattice_check(rtc, orc, renderer, world.flatten(), cam, step=32, n_random=2048, f32_min_ok=0.999)
     assert st.primary_hits == 7680 * 4320 * 4
+
+
+@pytest.mark.parametrize("n_spheres", [100, 200, 1500])
+def test_fast_mode_dispatch_by_scene_size(rtc, renderer, n_spheres):
+    """Fast mode promises the tolerance, not a data type: beyond 128 shapes the library runs the parity kernel in its
+    hierarchical form (faster there than the general f32 kernel, and exact), so the fast frame IS the parity frame; up to
+    128 shapes, and with RTC_OPT_F32_GENERAL_KERNEL at any size, the general f32 kernel renders it — within 1/255 of the
+    parity frame on >= 99.9 % of the pixels, hit mask identical."""
+    f = rtc.ffi
+    renderer.upload_flat(*rtc.scenes.synthetic_scene(n_spheres=n_spheres, seed=0xB200).flatten())
+    d = rtc.scenes.synthetic_camera(192, 108).flatten()
+    want, want_hit, st = renderer.render(d, rtc.Renderer.make_opts(precision=f.PRECISION_F64_PARITY))
+    fast, fast_hit, st1 = renderer.render(d, rtc.Renderer.make_opts(precision=f.PRECISION_F32_FAST))
+    gen, gen_hit, st2 = renderer.render(d, rtc.Renderer.make_opts(precision=f.PRECISION_F32_FAST, flags=f.OPT_F32_GENERAL_KERNEL))
+    if n_spheres + 8 > 128:
+        # (a fast-mode frame crosses PCIe as f32 and is widened on the host: the parity kernel's colours rounded to f32)
+        assert np.array_equal(fast, want.astype(np.float32).astype(np.float64)) and np.array_equal(fast_hit, want_hit) and st1.rays == st.rays
+    for img, hit in ((fast, fast_hit), (gen, gen_hit)):
+        q = np.clip(np.rint(np.clip(img, 0.0, 1.0) * 255.0), 0, 255).astype(int)
+        qw = np.clip(np.rint(np.clip(want, 0.0, 1.0) * 255.0), 0, 255).astype(int)
+        ok = (np.abs(q - qw).max(axis=2) <= 1).mean()
+        assert ok >= 0.999, f"{n_spheres} spheres: only {ok:.5f} of the pixels within 1/255 of the parity frame"
+        assert np.array_equal(hit, want_hit)
