@@ -42,12 +42,12 @@ FLOP_PER_SHADED_HIT = 150
 # Executed-instruction figures of the timed kernel from the kept `ncu --set full` capture (a number measured under a
 # profiler is never a bench value: these describe the kernel, the timings above are CUDA events).  Refreshed per round.
 HW_PROFILE = {
-    "c3": {"source": "profiles/r02_ncu_f32_small_c3.txt", "fma_pipe_pct": 41.9, "alu_pipe_pct": 41.0, "issue_active_pct": 83.8,
-           "lanes_per_instruction": 28.41, "registers": 74, "dram_bytes_per_launch": 61.38e6,
-           "dram_note": "60.2 MB written + 1.1 MB read per 4K launch; the frame is 99.5 MB, the rest was still in the 126 MB L2 when the kernel ended"},
+    "c3": {"source": "profiles/r02_ncu_f32_small_c3.txt", "fma_pipe_pct": 42.1, "alu_pipe_pct": 42.6, "issue_active_pct": 86.9,
+           "lanes_per_instruction": 28.53, "registers": 72, "dram_bytes_per_launch": 66.83e6,
+           "dram_note": "65.7 MB written + 1.2 MB read per 4K launch; the frame is 99.5 MB, the rest was still in the 126 MB L2 when the kernel ended"},
     "c4": {"source": "profiles/r02_ncu_f64_c4_960x540.txt (the parity kernel, which fast mode takes for this scene; a 960x540 frame)",
-           "fp64_pipe_pct": 7.8, "fma_pipe_pct": 20.6, "alu_pipe_pct": 19.0, "issue_active_pct": 45.1, "lanes_per_instruction": 7.95,
-           "registers": 128, "dram_bytes_per_launch": None},
+           "fp64_pipe_pct": 9.0, "fma_pipe_pct": 23.7, "alu_pipe_pct": 21.7, "issue_active_pct": 54.0, "lanes_per_instruction": 8.02,
+           "registers": 64, "dram_bytes_per_launch": None},
 }
 FP32_FORMULA_PEAK = 148 * 128 * 2 * 1.965e9 / 1e12  # TFLOP/s, non-tensor, at clocks.max.sm
 

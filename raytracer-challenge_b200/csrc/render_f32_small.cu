@@ -244,8 +244,14 @@ __device__ unsigned long long g_trace[16384 * 4];
 __device__ __forceinline__ unsigned long long gtime() { unsigned long long t; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t)); return t; }
 #endif
 
+// Blocks per SM (128 threads each).  Measured after the odd-slot change, C3 4K / 4K with samples = 4: 5 blocks 1.261 ms, 6
+// blocks (74 registers) 1.268 / 6.03, 7 blocks (71 registers, no spills) 1.214 / 5.91, 8 blocks (64 registers, 36 B of
+// spills) 1.217 / 5.78: 7 for the plain frame, 8 for the resample-pass kernels.
 #ifndef RTC_F32S_MIN_BLOCKS
-#define RTC_F32S_MIN_BLOCKS 6
+#define RTC_F32S_MIN_BLOCKS 7
+#endif
+#ifndef RTC_F32S_MIN_BLOCKS_AA
+#define RTC_F32S_MIN_BLOCKS_AA 8
 #endif
 
 // kAux: the launch wants the work counters and/or the hit mask; without them (the plain frame) the
@@ -255,7 +261,7 @@ __device__ __forceinline__ unsigned long long gtime() { unsigned long long t; as
 // with `samples` more at counter-based offsets (include/rtc.h); rays carry weight 1 and the sum is divided at the end.
 // Frames with samples 0 / 1 run the kAA = false code, unchanged.
 template <int kFmt, bool kAux, bool kAA>
-__global__ void __launch_bounds__(kThreads, RTC_F32S_MIN_BLOCKS)
+__global__ void __launch_bounds__(kThreads, kAA ? RTC_F32S_MIN_BLOCKS_AA : RTC_F32S_MIN_BLOCKS)
 render_f32_small_kernel(const __grid_constant__ SmallParams P, void* __restrict__ out_rgb, uint8_t* __restrict__ out_hit,
                         Counters* __restrict__ counters, unsigned* __restrict__ work) {
     extern __shared__ float4 smem4[];
