@@ -208,7 +208,10 @@ int rtc_device_count(void);
  * counter, so a render enqueued on a second stream (or rtc_render beside a user-stream rtc_render_device)
  * must be ordered after the previous one by the caller (an event or a synchronise).  Different contexts may be
  * used concurrently (Camera::render takes &self,
- * &World and both are Sync: src/shape.rs:17, src/material.rs:33). */
+ * &World and both are Sync: src/shape.rs:17, src/material.rs:33).
+ * The host threads that deliver staged frames (rtc_render) are created with the first render: one per hardware thread, or
+ * the number in the environment variable RTC_B200_HOST_THREADS, read once at that point — the library's only environment
+ * variable (a deployment knob like OMP_NUM_THREADS; nothing on a render call's path reads the environment). */
 int rtc_context_create(const int* device_ids, int n_gpus, rtc_context** out_ctx);
 void rtc_context_destroy(rtc_context* ctx);
 

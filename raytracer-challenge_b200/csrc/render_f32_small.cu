@@ -240,7 +240,7 @@ constexpr unsigned kOffNrm = 0, kOffColAmb = 16, kOffDifSpec = 32, kOffTrRi = 48
 static_assert(sizeof(SmallRec32) == 144, "SmallRec32 layout");
 
 #ifdef RTC_F32S_TRACE   // diagnostic build only (tools/trace_tail.py): per-warp start / tiles-exhausted / end times
-__device__ unsigned long long g_trace[16384 * 4];
+__device__ unsigned long long g_trace[16384 * 6];   // per warp: t0, t_exhausted, t_end, iterations | per warp: last tile, its hand-out rank
 __device__ __forceinline__ unsigned long long gtime() { unsigned long long t; asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t)); return t; }
 #endif
 
@@ -319,7 +319,7 @@ render_f32_small_kernel(const __grid_constant__ SmallParams P, void* __restrict_
 #ifdef RTC_F32S_TRACE
     const unsigned long long tr_t0 = gtime();
     unsigned long long tr_t1 = 0;
-    unsigned tr_iters = 0, tr_tail_iters = 0;
+    unsigned tr_iters = 0, tr_tail_iters = 0, tr_last_tile = 0, tr_last_rank = 0;
 #endif
 
     for (;;) {
@@ -375,7 +375,13 @@ render_f32_small_kernel(const __grid_constant__ SmallParams P, void* __restrict_
                 if (lane == 0) t = atomicAdd(work, 1u);
                 t = __shfl_sync(full, t, 0);
                 if (t >= (unsigned)P.total_tiles) { exhausted = true; break; }
+#ifdef RTC_F32S_TRACE
+                tr_last_rank = t;
+#endif
                 if (P.order) t = P.order[t];                  // heavy tiles first (classify_tiles_small_kernel)
+#ifdef RTC_F32S_TRACE
+                tr_last_tile = t;
+#endif
                 RTC_CHECK(t < (unsigned)P.total_tiles);
                 const int ty = (int)(t / (unsigned)P.tiles_x);
                 wtx = ((int)t - ty * P.tiles_x) * kTileX;
@@ -559,7 +565,8 @@ render_f32_small_kernel(const __grid_constant__ SmallParams P, void* __restrict_
 #ifdef RTC_F32S_TRACE
     if (lane == 0) {
         const unsigned w = blockIdx.x * (kThreads / 32) + (threadIdx.x >> 5);
-        if (w < 16384) { g_trace[4 * w] = tr_t0; g_trace[4 * w + 1] = tr_t1; g_trace[4 * w + 2] = gtime(); g_trace[4 * w + 3] = ((unsigned long long)tr_iters << 32) | tr_tail_iters; }
+        if (w < 16384) { g_trace[4 * w] = tr_t0; g_trace[4 * w + 1] = tr_t1; g_trace[4 * w + 2] = gtime(); g_trace[4 * w + 3] = ((unsigned long long)tr_iters << 32) | tr_tail_iters;
+                         g_trace[4 * 16384 + 2 * w] = tr_last_tile; g_trace[4 * 16384 + 2 * w + 1] = tr_last_rank; }
     }
 #endif
     // The tile counter resets itself: the last block to finish zeroes work[0] (tiles handed out) and

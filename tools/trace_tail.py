@@ -21,12 +21,14 @@ opts = rtc.Renderer.make_opts(precision=1, out_format=ffi.OUT_F32_RGB, shard_ind
 for rep in range(3):
     st = ffi.RtcStats()
     r.render_device(cam, opts, buf.data_ptr(), None, None, st)
-warps = 148 * 6 * 4
-raw = np.zeros(warps * 4, dtype=np.uint64)
+warps = 148 * 8 * 4   # upper bound of resident warps (7 blocks of 4 warps per SM)
+raw = np.zeros(16384 * 6, dtype=np.uint64)
 rc = lib.rtc_debug_read_trace(raw.ctypes.data_as(ctypes.c_void_p), ctypes.c_int(raw.size))
 assert rc == 0, rc
-t = raw.reshape(warps, 4)
-t = t[t[:, 0] > 0]
+t = raw[:16384 * 4].reshape(16384, 4)
+last = raw[16384 * 4:].reshape(16384, 2)
+ran = t[:, 0] > 0
+t, last = t[ran], last[ran]
 t0, t1, t2 = t[:, 0].astype(np.int64), t[:, 1].astype(np.int64), t[:, 2].astype(np.int64)
 iters, tail = (t[:, 3] >> np.uint64(32)).astype(np.int64), (t[:, 3] & np.uint64(0xffffffff)).astype(np.int64)
 base = t0.min()
@@ -41,3 +43,14 @@ tail_us = (t2 - np.where(seen, t1, t2)) / 1e3
 print(f"time after exhaustion per warp: mean {tail_us.mean():.1f} p90 {np.percentile(tail_us, 90):.1f} max {tail_us.max():.1f} us;  us/iter in tail {tail_us.sum() / max(tail.sum(), 1):.2f}")
 hist, edges = np.histogram(us(t2), bins=12)
 print("end-time histogram (us):", " ".join(f"{edges[i]:.0f}:{hist[i]}" for i in range(len(hist))))
+
+# the warps that end last: which tile did they fetch last, when was it handed out, what does its centre pixel see?
+tiles_x = (3840 + 7) // 8
+rows = [r_ for r_ in range(2160) if (r_ // tile) % n == 0] if n > 1 else list(range(2160))
+order_ = np.argsort(-t2)[:16]
+print("latest warps: end us | iterations after exhaustion | last tile (tx, ty) -> frame pixel of its corner | hand-out rank of", int(st.kernel_launches), "launch(es)")
+for w in order_:
+    tid, rk = int(last[w, 0]), int(last[w, 1])
+    ty_, tx_ = divmod(tid, tiles_x)
+    fy = rows[min(ty_ * 4, len(rows) - 1)]
+    print(f"  {us(t2[w]):7.1f} | {int(tail[w]):3d} | tile ({tx_:3d},{ty_:3d}) -> pixel ({tx_ * 8:4d},{fy:4d}) | rank {rk}")
