@@ -29,6 +29,12 @@ struct Streams {  // intersect streams, in shared memory when they fit, else glo
     const float4* gbound; float gcmax, grmax;               // one per eight entries of `bound` (DevScene64::gbound), padded to a multiple of 32
     const float4* sbound; float scmax, srmax;               // one per 32 groups (DevScene64::sbound), padded to a multiple of 32
 };
+// The block's copy, written once by thread 0: the searches below are out-of-line functions, and a Streams built in the
+// kernel's registers would reach them through a reference, i.e. through the thread's local memory (every field a local load
+// on every call; ncu counted 130 local loads per loop iteration before this).
+__shared__ Streams g_streams;
+// Result of a search, returned in registers (reference parameters of an out-of-line function live in local memory too).
+struct Found { double t; int idx; int n_neg; };
 
 // kCollect (radiance rays): the list entries with t < 0 that the loops come across are kept in `neg`
 // (t, 2 * shape index + root): they are all Intersection::compute_refractive looks at, so a transparent
@@ -43,11 +49,12 @@ constexpr int kNegCap = 48;
 // and the room frames from 7.39 to 7.12 ms (C2 2.21 -> 2.10, C4 71.9 -> 69.9); the kExt kernels (resample pass, several
 // lights) are at their register limit and lose 2-3 % to the extra live flag, so they keep the two copies.
 template <int kMode, bool kCubes, bool kGroups>
-__device__ __noinline__ void intersect_world_impl(const Streams& S, V3 o, V3 d, double& best_t, int& best_idx, Neg* neg, int& n_neg, const bool collect) {
+__device__ __noinline__ Found intersect_world_impl(V3 o, V3 d, Neg* neg, const bool collect) {
+    const Streams& S = g_streams;
     const bool kCollect = kMode == 2 ? collect : kMode == 1;
-    best_t = __longlong_as_double(0x7ff0000000000000LL);
-    best_idx = 0x7fffffff;
-    if (kCollect) n_neg = 0;
+    double best_t = __longlong_as_double(0x7ff0000000000000LL);
+    int best_idx = 0x7fffffff;
+    int n_neg = 0;
     auto keep = [&](double t, int ord) { if (n_neg < kNegCap) { neg[n_neg].t = t; neg[n_neg].ord = ord; } ++n_neg; };
 #pragma unroll kUnroll
     for (int i = 0; i < S.np; ++i) {
@@ -177,16 +184,21 @@ __device__ __noinline__ void intersect_world_impl(const Streams& S, V3 o, V3 d, 
         }
     }
     if (best_idx == 0x7fffffff) best_idx = -1;
+    Found f; f.t = best_t; f.idx = best_idx; f.n_neg = n_neg;
+    return f;
 }
 template <bool kCollect, bool kCubes, bool kGroups, bool kOneCopy>
-__device__ __forceinline__ void intersect_world(const Streams& S, V3 o, V3 d, double& best_t, int& best_idx, Neg* neg, int& n_neg) {
-    intersect_world_impl<kOneCopy ? 2 : (kCollect ? 1 : 0), kCubes, kGroups>(S, o, d, best_t, best_idx, neg, n_neg, kCollect);
+__device__ __forceinline__ void intersect_world(V3 o, V3 d, double& best_t, int& best_idx, Neg* neg, int& n_neg) {
+    const Found f = intersect_world_impl<kOneCopy ? 2 : (kCollect ? 1 : 0), kCubes, kGroups>(o, d, neg, kCollect);
+    best_t = f.t; best_idx = f.idx;
+    if (kCollect) n_neg = f.n_neg;
 }
 
 // Intersection::compute_refractive (src/shape.rs:115-141) without materialising the list: see parity64.cuh (Cont, offer).
 template <bool kCubes>
-__device__ __noinline__ void compute_refractive(const Streams& S, const DevScene64& sc, V3 o, V3 d, int hit_idx,
+__device__ __noinline__ void compute_refractive(const DevScene64& sc, V3 o, V3 d, int hit_idx,
                                                 double& n1, double& n2) {
+    const Streams& S = g_streams;
     unsigned parity[8];
 #pragma unroll
     for (int k = 0; k < 8; ++k) parity[k] = 0u;
@@ -259,7 +271,9 @@ __device__ __noinline__ void compute_refractive(const Streams& S, const DevScene
 }
 
 // The same from the entries intersect_world<true> kept for this ray.
-__device__ __noinline__ void compute_refractive_kept(const DevScene64& sc, int hit_idx, const Neg* neg, int n_neg, double& n1, double& n2) {
+struct N12 { double n1, n2; };
+__device__ __noinline__ N12 compute_refractive_kept(const DevScene64& sc, int hit_idx, const Neg* neg, int n_neg) {
+    double n1, n2;
     if (sc.ids_unique) {
         // Unique world_ids (every scene of at most 256 shapes): an id is toggled once per negative entry of ITS shape, so a
         // shape is a container iff exactly one of its entries is negative.  A sphere or cube with both roots negative was
@@ -282,7 +296,8 @@ __device__ __noinline__ void compute_refractive_kept(const DevScene64& sc, int h
         } else {
             n2 = sc.rec[hit_idx].refractive_index;
         }
-        return;
+        N12 r; r.n1 = n1; r.n2 = n2;
+        return r;
     }
     unsigned parity[8];
 #pragma unroll
@@ -307,6 +322,8 @@ __device__ __noinline__ void compute_refractive_kept(const DevScene64& sc, int h
     } else {
         n2 = sc.rec[hit_idx].refractive_index;
     }
+    N12 r; r.n1 = n1; r.n2 = n2;
+    return r;
 }
 
 // `n % 2.0 == 0.0` (Rust's % on f64 is fmod) for an INTEGER-VALUED n — a floor(), or a sum of floor()s
@@ -391,7 +408,7 @@ template <bool kInSmem, bool kCubes, bool kExt>
 // Streams in global memory (big scenes): it waits for the hierarchy's loads, and more resident warps pay for the
 // spills (C4 4K 69.7 / 65.3 / 61.1 / 58.0 / 56.2 / 62.9 / 74.4 ms at 4 / 5 / 6 / 7 / 8 / 10 / 12 blocks: 8 blocks, 64 registers).
 __global__ void __launch_bounds__(kThreads, kInSmem ? RTC_F64_MIN_BLOCKS : RTC_F64_MIN_BLOCKS_GLOBAL)
-render_f64_kernel(DevScene64 sc, CamParams cam, double* __restrict__ out_f64, float* __restrict__ out_f32,
+render_f64_kernel(const __grid_constant__ DevScene64 sc, const __grid_constant__ CamParams cam, double* __restrict__ out_f64, float* __restrict__ out_f32,
                   uint8_t* __restrict__ out_u8, uint8_t* __restrict__ out_hit, Counters* __restrict__ counters) {
     extern __shared__ double2 smem[];
     Streams S;
@@ -419,6 +436,8 @@ render_f64_kernel(DevScene64 sc, CamParams cam, double* __restrict__ out_f64, fl
     }
     S.nb4 = sc.n_bound4; S.cmax = sc.bound_cmax; S.rmax = sc.bound_rmax; S.gcmax = sc.gbound_cmax; S.grmax = sc.gbound_rmax;
     S.sbound = sc.sbound; S.scmax = sc.sbound_cmax; S.srmax = sc.sbound_rmax;
+    if (threadIdx.x == 0) g_streams = S;   // (the staged data is already visible: the barrier above; this one publishes the struct)
+    __syncthreads();
 
     const int ss = cam.samples == 1 ? 1 : 2;  // samples per pixel edge
     int sx, sy;
@@ -475,7 +494,7 @@ render_f64_kernel(DevScene64 sc, CamParams cam, double* __restrict__ out_f64, fl
             bool descended = false;
             double t; int idx;
             ++n_rays;
-            intersect_world<true, kCubes, !kInSmem, !kExt>(S, ro, rd, t, idx, kept, n_neg);
+            intersect_world<true, kCubes, !kInSmem, !kExt>(ro, rd, t, idx, kept, n_neg);
             if (first) { primary_hit = idx >= 0; first = false; }
             if (idx < 0) {
                 color = mk(0., 0., 0.);  // background_color, src/shape.rs:652
@@ -497,8 +516,8 @@ render_f64_kernel(DevScene64 sc, CamParams cam, double* __restrict__ out_f64, fl
                 V3 normal = normalize(xvec3(rec.invt, ln));
                 double n1 = 1.0, n2 = 1.0;
                 if (rec.transparency != 0.0) {
-                    if (n_neg <= kNegCap) compute_refractive_kept(sc, idx, kept, n_neg, n1, n2);
-                    else compute_refractive<kCubes>(S, sc, ro, rd, idx, n1, n2);   // more entries than were kept: the two passes
+                    if (n_neg <= kNegCap) { const N12 r = compute_refractive_kept(sc, idx, kept, n_neg); n1 = r.n1; n2 = r.n2; }
+                    else compute_refractive<kCubes>(sc, ro, rd, idx, n1, n2);   // more entries than were kept: the two passes
                 }
                 bool inside = dot(normal, eyev) < 0.0;
                 if (inside) normal = neg(normal);
@@ -521,7 +540,7 @@ render_f64_kernel(DevScene64 sc, CamParams cam, double* __restrict__ out_f64, fl
                     V3 sdir = normalize(v);
                     double st; int sidx;
                     ++n_rays; ++n_shadow;
-                    intersect_world<false, kCubes, !kInSmem, !kExt>(S, over_point, sdir, st, sidx, kept, n_shadow_neg);
+                    intersect_world<false, kCubes, !kInSmem, !kExt>(over_point, sdir, st, sidx, kept, n_shadow_neg);
                     bool shadowed = sidx >= 0 && st < distance;
                     V3 term = lighting(rec, lpos, lint, over_point, eyev, normal, shadowed);
                     surface = li == 0 ? term : add(surface, term);
