@@ -29,6 +29,9 @@ struct Streams {  // intersect streams, in shared memory when they fit, else glo
     const float4* gbound; float gcmax, grmax;               // one per eight entries of `bound` (DevScene64::gbound), padded to a multiple of 32
     const float4* sbound; float scmax, srmax;               // one per 32 groups (DevScene64::sbound), padded to a multiple of 32
 };
+#ifndef RTC_F64_ONE_COPY
+#define RTC_F64_ONE_COPY(ext) true   // one copy of the search for both ray kinds in every kernel (see intersect_world_impl)
+#endif
 // The block's copy, written once by thread 0: the searches below are out-of-line functions, and a Streams built in the
 // kernel's registers would reach them through a reference, i.e. through the thread's local memory (every field a local load
 // on every call; ncu counted 130 local loads per loop iteration before this).
@@ -45,9 +48,10 @@ constexpr int kNegCap = 48;
 // kGroups: two-level filter (streams in global memory: big scenes, Morton order); otherwise entries four at a time
 // kMode 0 / 1: kCollect fixed at compile time (two copies of the search in a kernel, one per ray kind); kMode 2: kCollect is
 // the run-time argument — ONE copy serves radiance and shadow rays.  The kernel is bound by instruction fetch as much as by
-// anything (5.7 k instructions, `no_instruction` 1.3 stall cycles per issue): sharing the copy takes 6 KB off the hot loop
-// and the room frames from 7.39 to 7.12 ms (C2 2.21 -> 2.10, C4 71.9 -> 69.9); the kExt kernels (resample pass, several
-// lights) are at their register limit and lose 2-3 % to the extra live flag, so they keep the two copies.
+// anything (5.7 k instructions, `no_instruction` 1.3 stall cycles per issue at the time): sharing the copy took 6 KB off the
+// hot loop and the room frames from 7.39 to 7.12 ms (C2 2.21 -> 2.10, C4 71.9 -> 69.9).  The kExt kernels (resample pass,
+// several lights) first lost 2-3 % to the extra live flag; once the streams' descriptor had moved to shared memory they
+// gain too (samples = 4: 33.2 -> 32.2 ms, two lights 10.0 -> 9.7), so every kernel uses mode 2 (RTC_F64_ONE_COPY).
 template <int kMode, bool kCubes, bool kGroups>
 __device__ __noinline__ Found intersect_world_impl(V3 o, V3 d, Neg* neg, const bool collect) {
     const Streams& S = g_streams;
@@ -494,7 +498,7 @@ render_f64_kernel(const __grid_constant__ DevScene64 sc, const __grid_constant__
             bool descended = false;
             double t; int idx;
             ++n_rays;
-            intersect_world<true, kCubes, !kInSmem, !kExt>(ro, rd, t, idx, kept, n_neg);
+            intersect_world<true, kCubes, !kInSmem, RTC_F64_ONE_COPY(kExt)>(ro, rd, t, idx, kept, n_neg);
             if (first) { primary_hit = idx >= 0; first = false; }
             if (idx < 0) {
                 color = mk(0., 0., 0.);  // background_color, src/shape.rs:652
@@ -540,7 +544,7 @@ render_f64_kernel(const __grid_constant__ DevScene64 sc, const __grid_constant__
                     V3 sdir = normalize(v);
                     double st; int sidx;
                     ++n_rays; ++n_shadow;
-                    intersect_world<false, kCubes, !kInSmem, !kExt>(over_point, sdir, st, sidx, kept, n_shadow_neg);
+                    intersect_world<false, kCubes, !kInSmem, RTC_F64_ONE_COPY(kExt)>(over_point, sdir, st, sidx, kept, n_shadow_neg);
                     bool shadowed = sidx >= 0 && st < distance;
                     V3 term = lighting(rec, lpos, lint, over_point, eyev, normal, shadowed);
                     surface = li == 0 ? term : add(surface, term);
