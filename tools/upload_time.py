@@ -1,0 +1,12 @@
+import sys, time
+sys.path.insert(0, "/root/repo")
+import numpy as np, torch
+import rtc_b200 as rtc
+r = rtc.Renderer([0])
+flat = rtc.scenes.reflect_refract_scene().flatten()
+for _ in range(5): r.upload_flat(*flat)
+ts = []
+for _ in range(200):
+    a = time.perf_counter(); r.upload_flat(*flat); ts.append(time.perf_counter() - a)
+ts.sort()
+print("rtc_scene_upload (13 shapes): min %.1f us median %.1f us p90 %.1f us" % (ts[0] * 1e6, ts[100] * 1e6, ts[180] * 1e6))
