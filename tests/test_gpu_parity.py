@@ -689,3 +689,32 @@ def test_fast_mode_dispatch_by_scene_size(rtc, renderer, n_spheres):
         ok = (np.abs(q - qw).max(axis=2) <= 1).mean()
         assert ok >= 0.999, f"{n_spheres} spheres: only {ok:.5f} of the pixels within 1/255 of the parity frame"
         assert np.array_equal(hit, want_hit)
+
+
+@pytest.mark.parametrize("n_planes,n_spheres", [(1, 0), (0, 1), (1, 1), (2, 1), (1, 2), (3, 3), (3, 4), (2, 5), (5, 8), (15, 47), (16, 48)])
+def test_small_scene_kernel_odd_and_even_shape_counts(rtc, orc, renderer, n_planes, n_spheres):
+    """The small-scene kernel tests shapes in pairs and an odd count's last shape on its own, from the last slot of its
+    constant-bank array (render_f32_small.cu): every parity of plane / sphere counts, up to the kernel's limits of 16 planes
+    and 48 spheres, against the oracle — with glass and mirrors among the last shapes, which are the ones that move."""
+    rnd = random.Random(1000 * n_planes + n_spheres)
+    w = rtc.World(rtc.Light(rtc.Color(1, 1, 1), (-3.0, 9.0, -8.0)))
+    for k in range(n_planes):
+        m = rtc.Material(color=rtc.Color(rnd.random(), rnd.random(), rnd.random()), specular=0.3,
+                         reflectiveness=0.4 if k == n_planes - 1 else 0.0)
+        if k % 3 == 0:
+            t = rtc.Matrix.identity().translation(0, -1.0 - 0.3 * k, 0)
+        elif k % 3 == 1:
+            t = rtc.Matrix.identity().rotation_x(math.pi / 2).translation(0, 0, 14.0 + k)
+        else:
+            t = rtc.Matrix.identity().rotation_z(math.pi / 2).translation(-9.0 - k, 0, 0)
+        w.add_shape(rtc.Plane(t, m))
+    for k in range(n_spheres):
+        r = rnd.uniform(0.35, 0.9)
+        last = k == n_spheres - 1
+        m = rtc.Material(color=rtc.Color(rnd.random(), rnd.random(), rnd.random()), diffuse=0.7, specular=0.4,
+                         reflectiveness=0.6 if last else 0.0, transparency=0.8 if last else 0.0, refractive_index=1.5 if last else 1.0)
+        pos = (0.0, 0.6, 2.0) if last else (rnd.uniform(-6, 6), rnd.uniform(-0.5, 4), rnd.uniform(3, 11))
+        w.add_shape(rtc.Sphere(rtc.Matrix.identity().scaling(r, r, r).translation(*pos), m))
+    cam = rtc.Camera.new_with_transform(160, 100, 1.0, rtc.Matrix.make_view_transform((0, 1.5, -7.0), (0, 0.8, 3), (0, 1, 0)))
+    for general in (False, True):
+        _check32(rtc, orc, renderer, w, cam, general=general, min_ok=0.998, mask_tol=2e-3)
