@@ -213,7 +213,8 @@ struct rtc_context {
     double wait_timeout_s = 60.0;
     uint64_t last_d2h_bytes = 0;   // rtc_delivery_info: what the last rtc_render moved over PCIe, and how
     int last_bands = 0, last_bands_direct = 0;
-    int mix_direct_bands = 2;   // mixed delivery (rtc_render, one GPU): bands of eight that go by f64 DMA; follows the host's speed
+    double mix_lag_ms = 0.0;    // running mean of (host threads done) - (last byte landed) of the mixed delivery
+    int mix_direct_bands = 1;   // mixed delivery (rtc_render, one GPU): how many of the last row bands go by f64 DMA; follows the host's speed
 };
 
 namespace {
@@ -1834,13 +1835,15 @@ extern "C" int rtc_render(rtc_context* ctx, const rtc_camera* cam, const rtc_ren
         // [row0, row0 + rows) written at their frame positions).  Band b's D2H runs on the copy stream
         // while band b+1 renders, and (staged) the host delivers band b while band b+1 crosses PCIe.
         //  * fast mode is copy- and delivery-bound (99.5 MB at ~56 GB/s and a ~1.8 ms host widening against a
-        //    1.25 ms kernel): eight equal bands keep all three stages busy (measured 2.5 ms; small-large-small
-        //    bands 3.2 ms, because a large band is delivered only after its whole copy);
+        //    1.2 ms kernel): eight equal bands keep all three stages busy (measured 2.5 ms; small-large-small
+        //    bands 3.2 ms, because a large band is delivered only after its whole copy); into a registered buffer:
+        //    nine bands, the first and the last half as high, and the mixed delivery;
         //  * parity mode is kernel-bound: few large bands first (every launch has its own tail), and what is
         //    left after the last kernel is the copy and delivery of a sixteenth of the frame.
         DeviceState& d = ctx->devs[0];
         CUDA_TRY(cudaSetDevice(d.dev));
-        static const int kPlanEq8[] = {1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1}, kPlanF64[] = {6, 5, 3, 1, 1}, kPlanMid[] = {1, 2, 1}, kPlanOne[] = {1};
+        static const int kPlanEq8[] = {1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1, 1}, kPlanF64[] = {6, 5, 3, 1, 1}, kPlanMid[] = {1, 2, 1}, kPlanOne[] = {1},
+                         kPlanMix9[] = {1, 2, 2, 2, 2, 2, 2, 2, 1};
         const int* plan = kPlanOne; int n_plan = 1, plan_sum = 1;
         if (frame_bytes >= (32u << 20)) {
             // kernel-bound frames: parity mode, and fast mode outside the small-scene kernel (every launch has its own
@@ -1848,11 +1851,28 @@ extern "C" int rtc_render(rtc_context* ctx, const rtc_camera* cam, const rtc_ren
             const bool kernel_bound = opts->precision == RTC_PRECISION_F64_PARITY || !d.small_ok || (opts->flags & RTC_OPT_F32_GENERAL_KERNEL);
             if (d.s64.n_shapes > 256) { plan = kPlanOne; n_plan = 1; plan_sum = 1; }   // tens of ms of kernel, ms-long tails: one launch, then the copy
             else if (kernel_bound) { plan = kPlanF64; n_plan = 5; plan_sum = 16; }
+            else if (registered && f32_wins && !(opts->flags & (RTC_OPT_DELIVER_DIRECT | RTC_OPT_DELIVER_STAGED))) {
+                // mixed delivery (below): a short first band starts the copies after a sixteenth of the kernel work instead of an
+                // eighth, a short last band is what goes by DMA first; 2.44 -> 2.34 ms against eight equal bands
+                // (profiles/r02_e2e_mix_probe.txt: seven plans x four splits)
+                plan = kPlanMix9; n_plan = 9; plan_sum = 16;
+            }
             else { plan = kPlanEq8; n_plan = 8; plan_sum = 8; }
 #ifdef RTC_PROBE_KNOBS   // `make probe`: measurement build only (tools/e2e_mix_probe.py); the product library reads no environment
             if (plan == kPlanEq8 && getenv("RTC_MIX_BANDS")) { n_plan = plan_sum = std::max(1, std::min(kMaxBands, atoi(getenv("RTC_MIX_BANDS")))); }
+            static int probe_plan[kMaxBands];
+            if (plan == kPlanEq8 && getenv("RTC_MIX_PLAN")) {   // e.g. "1,2,2,2,2,2,2,2,1": band heights in sixteenths or whatever they sum to
+                n_plan = 0; plan_sum = 0;
+                for (const char* c = getenv("RTC_MIX_PLAN"); *c && n_plan < kMaxBands;) {
+                    probe_plan[n_plan] = std::max(1, atoi(c)); plan_sum += probe_plan[n_plan++];
+                    while (*c && *c != ',') ++c;
+                    if (*c == ',') ++c;
+                }
+                plan = probe_plan;
+            }
 #endif
         } else if (frame_bytes >= (4u << 20)) { plan = kPlanMid; n_plan = 3; plan_sum = 4; }
+        const bool mix_plan = plan != kPlanOne && plan != kPlanMid && plan != kPlanF64;   // the copy- and delivery-bound plan of a big fast-mode frame
         int band_r0[kMaxBands + 1];
         int n_bands = 0;
         {
@@ -1872,7 +1892,7 @@ extern "C" int rtc_render(rtc_context* ctx, const rtc_camera* cam, const rtc_ren
         // goes by DMA; DMA still running after the host had finished: one band fewer), or half the bands when both
         // delivery flags are set (tests).
         const bool mix_forced = registered && f32_wins && (opts->flags & RTC_OPT_DELIVER_DIRECT) && (opts->flags & RTC_OPT_DELIVER_STAGED);
-        const bool mix_auto = registered && f32_wins && !direct && !(opts->flags & (RTC_OPT_DELIVER_DIRECT | RTC_OPT_DELIVER_STAGED)) && plan == kPlanEq8;
+        const bool mix_auto = registered && f32_wins && !direct && !(opts->flags & (RTC_OPT_DELIVER_DIRECT | RTC_OPT_DELIVER_STAGED)) && mix_plan;
         int k_wide = mix_forced ? n_bands / 2 : (mix_auto ? std::min(ctx->mix_direct_bands, n_bands / 2) : 0);
 #ifdef RTC_PROBE_KNOBS
         if (mix_auto && getenv("RTC_MIX_K")) k_wide = std::max(0, std::min(n_bands - 1, atoi(getenv("RTC_MIX_K"))));
@@ -1931,14 +1951,16 @@ extern "C" int rtc_render(rtc_context* ctx, const rtc_camera* cam, const rtc_ren
             CUDA_TRY(cudaEventSynchronize(d.ev_c1));
             CUDA_TRY(cudaEventElapsedTime(&dma_ms, d.ev_c0, d.ev_c1));
             const double lag_ms = std::chrono::duration<double, std::milli>(host_done - first_landed).count() - (double)dma_ms;
-            const double band_ms = (double)dma_ms / (double)(n_bands + k_wide - 1);   // one f32 band over the link
+            const double band_ms = (double)dma_ms / 8.0;   // about an eighth of the frame over the link
 #ifdef RTC_PROBE_KNOBS
             if (getenv("RTC_MIX_TRACE"))
                 fprintf(stderr, "mix: bands %d wide %d  first copy -> last copy %.3f ms  first landed -> host done %.3f ms  lag %.3f  deliver %.3f\n", n_bands, k_wide,
                         dma_ms, std::chrono::duration<double, std::milli>(host_done - first_landed).count(), lag_ms, deliver_ms);
 #endif
-            if (lag_ms > 1.6 * band_ms && ctx->mix_direct_bands < n_bands / 2) ++ctx->mix_direct_bands;
-            else if (lag_ms < -1.6 * band_ms && ctx->mix_direct_bands > 0) --ctx->mix_direct_bands;
+            // single frames are noisy (0.2 ... 0.8 ms at the same split): follow a running mean, and move one band at a time
+            ctx->mix_lag_ms = 0.7 * ctx->mix_lag_ms + 0.3 * lag_ms;
+            if (ctx->mix_lag_ms > 2.5 * band_ms && ctx->mix_direct_bands < n_bands / 2) { ++ctx->mix_direct_bands; ctx->mix_lag_ms = 0.0; }
+            else if (ctx->mix_lag_ms < -1.5 * band_ms && ctx->mix_direct_bands > 0) { --ctx->mix_direct_bands; ctx->mix_lag_ms = 0.0; }
         }
         CUDA_TRY(cudaStreamSynchronize(d.stream));
         float k_ms = 0.f;

@@ -35,10 +35,13 @@ def run(n=12):
     return ts[0] * 1e3, ts[len(ts) // 2] * 1e3
 
 
+os.environ["RTC_MIX_TRACE"] = "1"
+print("adaptive, the library's own plan:", run(20), r.delivery_info(), flush=True)
+del os.environ["RTC_MIX_TRACE"]
 want = None
-for bands in (8, 16, 12):
+for bands in (8,):
     os.environ["RTC_MIX_BANDS"] = str(bands)
-    for k in range(0, bands // 2 + 2):
+    for k in range(0, 3):
         os.environ["RTC_MIX_K"] = str(k)
         lo, med = run()
         if want is None:
@@ -46,6 +49,12 @@ for bands in (8, 16, 12):
         ok = np.array_equal(host, want)
         print(f"bands {bands:2d}  direct {k:2d}  min {lo:6.3f}  median {med:6.3f} ms  {r.delivery_info()}  frame identical: {ok}", flush=True)
 del os.environ["RTC_MIX_K"]
-os.environ["RTC_MIX_BANDS"] = "8"
-os.environ["RTC_MIX_TRACE"] = "1"
-print("adaptive, 8 bands:", run(6), r.delivery_info(), flush=True)
+del os.environ["RTC_MIX_BANDS"]
+for plan in ("1,1,1,1,1,1,1,1", "1,2,2,2,2,2,2,2,1", "1,1,2,2,2,2,2,2,1,1", "1,3,3,3,3,2,1", "1,2,3,3,3,2,1,1", "2,3,3,3,3,1,1", "1,2,2,2,2,2,2,1,1,1"):
+    os.environ["RTC_MIX_PLAN"] = plan
+    for k in (0, 1, 2, 3):
+        os.environ["RTC_MIX_K"] = str(k)
+        lo, med = run()
+        print(f"plan {plan:24s} direct bands {k}  min {lo:6.3f}  median {med:6.3f} ms  {r.delivery_info()}  frame identical: {np.array_equal(host, want)}", flush=True)
+del os.environ["RTC_MIX_K"]
+del os.environ["RTC_MIX_PLAN"]
