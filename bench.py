@@ -432,7 +432,6 @@ def run_gpu(args):
     # the other delivery for comparison, and parity mode end to end (direct: 24 B/pixel cross PCIe either way)
     alt_t = e2e_run(with_flags(oe, ffi.OPT_DELIVER_STAGED if direct_default else ffi.OPT_DELIVER_DIRECT), max(1, e2e_steps // 2))
     staged_t = e2e_run(with_flags(oe, ffi.OPT_DELIVER_STAGED), max(1, e2e_steps // 2)) if N == 1 else None
-    direct_t = e2e_run(with_flags(oe, ffi.OPT_DELIVER_DIRECT), max(1, e2e_steps // 2)) if N > 1 else None
     e64_t = e2e_run(oe64, max(1, min(e2e_steps, 3)))
     frames = {}
     if N == 1:
@@ -533,16 +532,12 @@ def run_gpu(args):
                             "row_bands_direct bands are written as f64 by the kernel and go by DMA straight into the Canvas (link and host threads side "
                             "by side; the split follows the previous frame's timing; the frame does not depend on it)" if N == 1 else
                             "every rank: rtc_scene_upload + rtc_render of its shard (interleaved row tiles) into ONE registered f64 Canvas frame in host memory "
-                            "shared by the rank processes, no gather; mixed delivery per rank: the shard's first row bands cross PCIe as f32 and the rank's "
-                            "host threads widen them into their frame rows, the last row_bands_direct bands go as f64 by pitched DMA straight to their frame "
-                            "rows (the host's aggregate DMA rate bounds an all-direct delivery, the host threads an all-staged one); bytes are per rank; "
-                            "time = max over ranks per step",
+                            "shared by the rank processes — pitched DMA of f64 rows over the rank's own PCIe link, no staging, no host pass, no gather; "
+                            "bytes are per rank; time = max over ranks per step",
                     "other_delivery": {"ms_per_frame": float(alt_t.mean()) * 1e3,
                                        "path": "forced direct f64 DMA" if N == 1 else "staged: f32 over PCIe + widening by the rank's host threads (round 1's path)"},
                     "staged_delivery": None if staged_t is None else {"ms_per_frame": float(staged_t.mean()) * 1e3,
-                                                                      "path": "all bands f32 over PCIe + widening by host threads (round 1's path)"},
-                    "direct_delivery": None if direct_t is None else {"ms_per_frame": float(direct_t.mean()) * 1e3,
-                                                                      "path": "all tiles as f64 by pitched DMA, no host pass"}},
+                                                                      "path": "all bands f32 over PCIe + widening by host threads (round 1's path)"}},
             # kernels of this library inside the timed region, all ranks: rank 0 runs the tile scheduling pre-pass + the render
             # kernel (+ the flag wait and the 'consumed' flag store when N > 1); every other rank ONE launch: its render kernel
             # waits for the back-pressure flag and stores its completion flag itself

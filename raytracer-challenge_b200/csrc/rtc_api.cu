@@ -213,8 +213,6 @@ struct rtc_context {
     double wait_timeout_s = 60.0;
     uint64_t last_d2h_bytes = 0;   // rtc_delivery_info: what the last rtc_render moved over PCIe, and how
     int last_bands = 0, last_bands_direct = 0;
-    double mix_shard_lag_ms = 0.0;   // the same pair for a shard of a frame (one process per GPU, render_shard_mixed)
-    int mix_shard_direct_bands = 2;
     double mix_lag_ms = 0.0;    // running mean of (host threads done) - (last byte landed) of the mixed delivery
     int mix_direct_bands = 1;   // mixed delivery (rtc_render, one GPU): how many of the last row bands go by f64 DMA; follows the host's speed
 };
@@ -1773,124 +1771,6 @@ int render_shard(rtc_context* ctx, DeviceState& d, const rtc_camera* cam, const 
     return RTC_OK;
 }
 
-// One shard of a fast-mode frame into a REGISTERED F64_RGB frame, one process per GPU: the mixed delivery of the one-GPU
-// path (rtc_render below) for a shard.  With N GPUs on one host the aggregate DMA rate into host memory is what bounds
-// direct delivery (71 / 74 / 95 GB/s at N = 2 / 4 / 8 on the box measured: 2.8 / 2.7 / 2.0 ms for 199 MB), while the
-// rank's host threads sit idle; staged delivery moves half the bytes but is bound by those threads.  So the shard is
-// rendered as row bands of whole tiles; the first bands are written as f32, cross PCIe into pinned staging and are
-// widened into their frame rows by the rank's threads, the last k bands are written as f64 and go by pitched DMA straight
-// to their frame rows.  k follows a running mean of (host threads done) - (last byte landed), like the one-GPU path.
-int render_shard_mixed(rtc_context* ctx, DeviceState& d, const rtc_camera* cam, const rtc_render_opts* opts, int shard_index, int shard_count,
-                       int tile_rows, unsigned char* user, uint8_t* out_hit_mask, HostPool* pool, bool want_counters, Counters* pinned_counter,
-                       rtc_stats& st) {
-    auto t0 = std::chrono::steady_clock::now();
-    CUDA_TRY(cudaSetDevice(d.dev));
-    const size_t row_elems = (size_t)cam->hsize * 3, row32 = row_elems * 4, row64 = row_elems * 8, hsize = cam->hsize;
-    rtc_render_opts o32 = *opts, o64 = *opts;
-    o32.out_format = RTC_OUT_F32_RGB; o64.out_format = RTC_OUT_F64_RGB;
-    const CamParams cp32 = make_cam(cam, &o32, shard_index, shard_count, tile_rows), cp64 = make_cam(cam, &o64, shard_index, shard_count, tile_rows);
-    const int shard_rows = cp32.shard_rows;
-    if (shard_rows <= 0) return RTC_OK;
-    const int n_tiles = (shard_rows + tile_rows - 1) / tile_rows, n_full = shard_rows / tile_rows;
-    const size_t shard32 = (size_t)shard_rows * row32;
-    const int n_bands = std::max(1, std::min(n_tiles, shard32 >= (24u << 20) ? 8 : (shard32 >= (6u << 20) ? 4 : 2)));
-    const int k_wide = std::min(std::max(ctx->mix_shard_direct_bands, 0), n_bands);
-    CUDA_TRY(d.rgb.ensure(shard32));
-    if (k_wide) CUDA_TRY(d.rgb_wide.ensure((size_t)shard_rows * row64));
-    if (out_hit_mask) CUDA_TRY(d.hit.ensure((size_t)shard_rows * hsize));
-    if (want_counters) CUDA_TRY(cudaMemsetAsync(d.counters.p, 0, sizeof(Counters), d.stream));
-    CUDA_TRY(cudaEventRecord(d.ev_k0, d.stream));
-    int band_t0[kMaxBands + 1];
-    for (int b = 0; b <= n_bands; ++b) band_t0[b] = (int)((long long)n_tiles * b / n_bands);
-    unsigned char* staged = ctx->pinned_rgb;
-    unsigned char* stage_hit = ctx->pinned_hit;
-    const size_t tile64 = (size_t)tile_rows * row64;
-    int rc = RTC_OK, n_launches = 0;
-    for (int b = 0; b < n_bands; ++b) {
-        const int t0b = band_t0[b], t1b = band_t0[b + 1];
-        if (t1b <= t0b) continue;
-        const bool wide = b >= n_bands - k_wide;
-        const int r0 = t0b * tile_rows, r1 = std::min(shard_rows, t1b * tile_rows);
-        CamParams cb = wide ? cp64 : cp32;
-        cb.row0 = r0; cb.shard_rows = r1 - r0;
-        rc = launch_on(d, cb, opts->precision, opts->flags, wide ? d.rgb_wide.p : d.rgb.p, out_hit_mask ? d.hit.p : nullptr, want_counters ? d.counters.p : nullptr, d.stream);
-        if (rc != RTC_OK) return rc;
-        ++n_launches;
-        CUDA_TRY(cudaEventRecord(d.ev_band[b], d.stream));
-        CUDA_TRY(cudaStreamWaitEvent(d.copy_stream, d.ev_band[b], 0));
-        if (wide) {
-            const int full_hi = std::min(t1b, n_full);
-            if (full_hi > t0b)
-                CUDA_TRY(cudaMemcpy2DAsync(user + ((size_t)t0b * shard_count + shard_index) * tile64, tile64 * (size_t)shard_count, d.rgb_wide.p + (size_t)t0b * tile64, tile64,
-                                           tile64, (size_t)(full_hi - t0b), cudaMemcpyDeviceToHost, d.copy_stream));
-            if (t1b > n_full) {   // the frame's last, shorter tile
-                const int rs = n_full * tile_rows;
-                const size_t fr = (size_t)shard_row_to_frame_row(rs, tile_rows, shard_index, shard_count);
-                CUDA_TRY(cudaMemcpyAsync(user + fr * row64, d.rgb_wide.p + (size_t)rs * row64, (size_t)(shard_rows - rs) * row64, cudaMemcpyDeviceToHost, d.copy_stream));
-            }
-        } else {
-            CUDA_TRY(cudaMemcpyAsync(staged + (size_t)r0 * row32, d.rgb.p + (size_t)r0 * row32, (size_t)(r1 - r0) * row32, cudaMemcpyDeviceToHost, d.copy_stream));
-        }
-        CUDA_TRY(cudaEventRecord(d.ev_copy[b], d.copy_stream));
-        if (b == 0) CUDA_TRY(cudaEventRecord(d.ev_c0, d.copy_stream));
-    }
-    CUDA_TRY(cudaEventRecord(d.ev_c1, d.copy_stream));
-    CUDA_TRY(cudaEventRecord(d.ev_k1, d.stream));
-    if (want_counters) CUDA_TRY(cudaMemcpyAsync(pinned_counter, d.counters.p, sizeof(Counters), cudaMemcpyDeviceToHost, d.stream));
-    CUDA_TRY(cudaStreamWaitEvent(d.copy_stream, d.ev_k1, 0));
-    if (out_hit_mask) CUDA_TRY(cudaMemcpyAsync(stage_hit, d.hit.p, (size_t)shard_rows * hsize, cudaMemcpyDeviceToHost, d.copy_stream));
-    double deliver_ms = 0.0;
-    auto first_landed = std::chrono::steady_clock::now(), host_done = first_landed;
-    for (int b = 0; b < n_bands; ++b) {
-        const int t0b = band_t0[b], t1b = band_t0[b + 1];
-        if (t1b <= t0b) continue;
-        const bool wide = b >= n_bands - k_wide;
-        CUDA_TRY(cudaEventSynchronize(d.ev_copy[b]));
-        auto h0 = std::chrono::steady_clock::now();
-        if (b == 0) first_landed = h0;
-        if (wide) continue;
-        auto task = [=](int i) {   // one tile: compact rows [r0, r1) of the staging -> its frame rows, widened
-            const int r0 = (t0b + i) * tile_rows, r1 = std::min(shard_rows, r0 + tile_rows);
-            const size_t fr = (size_t)shard_row_to_frame_row(r0, tile_rows, shard_index, shard_count);
-            rtc_host_widen_f32_f64(reinterpret_cast<double*>(user) + fr * row_elems, reinterpret_cast<const float*>(staged) + (size_t)r0 * row_elems, (size_t)(r1 - r0) * row_elems);
-        };
-        const int n_b = t1b - t0b;
-        if (pool && n_b > 1) pool->parallel_for(n_b, task);
-        else for (int i = 0; i < n_b; ++i) task(i);
-        host_done = std::chrono::steady_clock::now();
-        deliver_ms += std::chrono::duration<double, std::milli>(host_done - h0).count();
-    }
-    CUDA_TRY(cudaStreamSynchronize(d.copy_stream));
-    if (out_hit_mask)
-        for (int t = 0; t < n_tiles; ++t) {
-            const int r0 = t * tile_rows, r1 = std::min(shard_rows, r0 + tile_rows);
-            std::memcpy(out_hit_mask + (size_t)shard_row_to_frame_row(r0, tile_rows, shard_index, shard_count) * hsize, stage_hit + (size_t)r0 * hsize, (size_t)(r1 - r0) * hsize);
-        }
-    if (n_bands > 1 && !(opts->flags & (RTC_OPT_DELIVER_DIRECT | RTC_OPT_DELIVER_STAGED))) {
-        float dma_ms = 0.f;
-        CUDA_TRY(cudaEventElapsedTime(&dma_ms, d.ev_c0, d.ev_c1));
-        const double lag_ms = std::chrono::duration<double, std::milli>(host_done - first_landed).count() - (double)dma_ms;
-        const double band_ms = std::max(0.02, (double)dma_ms / (double)n_bands);
-        ctx->mix_shard_lag_ms = 0.7 * ctx->mix_shard_lag_ms + 0.3 * lag_ms;
-        if (ctx->mix_shard_lag_ms > 1.5 * band_ms && ctx->mix_shard_direct_bands < n_bands) { ++ctx->mix_shard_direct_bands; ctx->mix_shard_lag_ms = 0.0; }
-        else if (ctx->mix_shard_lag_ms < -1.5 * band_ms && ctx->mix_shard_direct_bands > 0) { --ctx->mix_shard_direct_bands; ctx->mix_shard_lag_ms = 0.0; }
-    }
-    CUDA_TRY(cudaStreamSynchronize(d.stream));
-    float k_ms = 0.f;
-    CUDA_TRY(cudaEventElapsedTime(&k_ms, d.ev_k0, d.ev_k1));
-    if (want_counters) { st.rays = pinned_counter->rays; st.primary_hits = pinned_counter->primary_hits; st.shaded_hits = pinned_counter->shaded_hits; st.shadow_rays = pinned_counter->shadow_rays; }
-    st.kernel_launches = (uint64_t)n_launches;
-    st.kernel_ms = k_ms;
-    st.total_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
-    st.d2h_ms = st.total_ms - k_ms;
-    st.gather_ms = deliver_ms;
-    int wide_rows = 0;
-    for (int b = n_bands - k_wide; b < n_bands; ++b) wide_rows += std::min(shard_rows, band_t0[b + 1] * tile_rows) - band_t0[b] * tile_rows;
-    ctx->last_bands = n_launches; ctx->last_bands_direct = k_wide;
-    ctx->last_d2h_bytes = (uint64_t)(shard_rows - wide_rows) * row32 + (uint64_t)wide_rows * row64;
-    return RTC_OK;
-}
-
 }  // namespace
 
 extern "C" int rtc_render(rtc_context* ctx, const rtc_camera* cam, const rtc_render_opts* opts, void* out_rgb,
@@ -1912,10 +1792,7 @@ extern "C" int rtc_render(rtc_context* ctx, const rtc_camera* cam, const rtc_ren
     if ((opts->flags & RTC_OPT_DELIVER_DIRECT) && !registered)
         return fail(RTC_ERR_INVALID_ARG, "rtc_render: RTC_OPT_DELIVER_DIRECT needs a buffer registered with rtc_register_host_buffer");
     const bool f32_wins = !sharded && opts->precision == RTC_PRECISION_F32_FAST && opts->out_format == RTC_OUT_F64_RGB;
-    // a shard of a fast-mode F64_RGB frame, one process per GPU, registered frame, no delivery flag: the mixed delivery of a shard
-    const bool shard_mixed = G == 1 && opts->shard_count > 1 && registered && opts->precision == RTC_PRECISION_F32_FAST && opts->out_format == RTC_OUT_F64_RGB &&
-                             !(opts->flags & (RTC_OPT_DELIVER_DIRECT | RTC_OPT_DELIVER_STAGED));
-    const bool direct = registered && !shard_mixed && !(opts->flags & RTC_OPT_DELIVER_STAGED) && ((opts->flags & RTC_OPT_DELIVER_DIRECT) || !f32_wins);
+    const bool direct = registered && !(opts->flags & RTC_OPT_DELIVER_STAGED) && ((opts->flags & RTC_OPT_DELIVER_DIRECT) || !f32_wins);
     // Staged fast mode computes in f32: an F64_RGB (Canvas.pixels) request is produced as f32 on the device,
     // crosses PCIe as f32 and is widened on the host (exact), halving the bytes of the dominant copy.
     const int dev_fmt = (!direct && opts->precision == RTC_PRECISION_F32_FAST && opts->out_format == RTC_OUT_F64_RGB) ? RTC_OUT_F32_RGB : opts->out_format;
@@ -1943,14 +1820,6 @@ extern "C" int rtc_render(rtc_context* ctx, const rtc_camera* cam, const rtc_ren
         // rank processes share — and this call fills in the rows of its shard only.  Every GPU delivers its rows over its
         // own PCIe link (and, staged, by its own host threads): no gather step, no collective.
         const int tile_rows = opts->tile_rows > 0 ? opts->tile_rows : 16;
-        if (shard_mixed) {
-            rc = render_shard_mixed(ctx, ctx->devs[0], cam, opts, opts->shard_index, opts->shard_count, tile_rows, user, out_hit_mask, ctx->pool, stats != nullptr,
-                                    &ctx->pinned_counters[0], st);
-            if (rc != RTC_OK) return rc;
-            st.total_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
-            if (stats) *stats = st;
-            return RTC_OK;
-        }
         rc = render_shard(ctx, ctx->devs[0], cam, opts, dev_fmt, direct, opts->shard_index, opts->shard_count, tile_rows, user, out_hit_mask, 0,
                           ctx->pool, stats != nullptr, &ctx->pinned_counters[0], st);
         if (rc != RTC_OK) return rc;
