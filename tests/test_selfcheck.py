@@ -51,3 +51,35 @@ def test_argument_checks(rtc):
     assert L.rtc_scene_selfcheck(C.byref(light), 0, shapes, n, C.byref(out)) == rtc.ffi.RTC_ERR_INVALID_ARG
     assert L.rtc_scene_selfcheck(C.byref(light), 1, shapes, n, None) == rtc.ffi.RTC_ERR_INVALID_ARG
     assert L.rtc_scene_selfcheck(C.byref(light), 1, shapes, n, C.byref(out)) == 0 and out.n_uniform_spheres == 2
+
+
+@pytest.mark.parametrize("n_spheres", [70, 300, 2500])
+def test_kd_order_keeps_every_level_enclosed_and_the_streams_permutations(rtc, n_spheres):
+    """The k-d order of big scenes (rtc_api.cu, spatial_order: nth_element per node, leaves sorted) through the host-only
+    self-check: the streams are permutations of the input shapes, the stream is in spatial order, and every group /
+    block bound encloses the level below it (worst enclosure slack <= 0 up to rounding) — for sizes around the sort
+    threshold (64), one block (256) and many blocks."""
+    import ctypes as C
+    f = rtc.ffi
+    light, shapes, n = rtc.scenes.synthetic_scene(n_spheres=n_spheres, seed=7).flatten()
+    out = f.RtcSelfcheck()
+    f.check(f.lib().rtc_scene_selfcheck(C.byref(light), 1, shapes, n, C.byref(out)))
+    assert out.streams_are_permutations == 1 and out.morton_sorted == 1
+    assert out.n_uniform_spheres + out.n_general_spheres == n_spheres and out.n_planes == 8
+    assert out.n_groups_f64 == (n_spheres + 7) // 8 and out.n_blocks_f64 == (out.n_groups_f64 + 31) // 32
+    assert out.worst_enclosure_f32 <= 1e-6 and out.worst_enclosure_f64 <= 1e-4
+
+
+def test_shared_host_frame_single_rank_and_numa_option(rtc):
+    """SharedHostFrame on one rank (no process group needed): a POSIX shared-memory Canvas frame; the NUMA option never
+    raises — it reports what it did (one memory node here: nothing to interleave)."""
+    import numpy as np
+    from rtc_b200.sharded import SharedHostFrame, _mbind_interleave
+    for opt in (False, True):
+        fr = SharedHostFrame(48, 20, 0, 1, numa_interleave=opt)
+        assert fr.array.shape == (20, 48, 3) and fr.array.dtype == np.float64 and isinstance(fr.numa, str)
+        fr.array[:] = 1.5
+        assert float(fr.array.sum()) == 1.5 * 20 * 48 * 3
+        fr.close()
+    buf = np.zeros(1 << 16)
+    assert isinstance(_mbind_interleave(buf.ctypes.data, buf.nbytes), str)
