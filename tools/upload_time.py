@@ -1,5 +1,7 @@
-import sys, time
-sys.path.insert(0, "/root/repo")
+"""Host + device latency of rtc_scene_upload for the room scene (13 shapes): the part of every end-to-end step that is not the
+render call.  usage: python tools/upload_time.py"""
+import os, sys, time
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import numpy as np, torch
 import rtc_b200 as rtc
 r = rtc.Renderer([0])
