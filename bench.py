@@ -539,11 +539,13 @@ def run_gpu(args):
                     "staged_delivery": None if staged_t is None else {"ms_per_frame": float(staged_t.mean()) * 1e3,
                                                                       "path": "all bands f32 over PCIe + widening by host threads (round 1's path)"}},
             # kernels of this library inside the timed region, all ranks: rank 0 runs the tile scheduling pre-pass + the render
-            # kernel (+ the flag wait and the 'consumed' flag store when N > 1); every other rank ONE launch: its render kernel
-            # waits for the back-pressure flag and stores its completion flag itself
-            "gpu_launches": args.steps * (2 if N == 1 else 3 + (N - 1)),
+            # kernel (+ the flag wait and the 'consumed' flag store when N > 1); every other rank: its render kernel, which waits for
+            # the back-pressure flag and stores its completion flag itself (up to four GPUs preceded by the tile pre-pass: heavy tiles
+            # first; beyond that a linear order keeps the pixel stream into rank 0's NVLink ingress even)
+            "gpu_launches": args.steps * (2 if N == 1 else 3 + (N - 1) * (2 if N <= 4 else 1)),
             "gpu_launches_per_step": {"rank0": ["classify_tiles_small_kernel", "render_f32_small_kernel"] + (["wait_kernel"] if N > 1 else []),
-                                      "other_ranks": ["render_f32_small_kernel"] if N > 1 else []},
+                                      "other_ranks": ([] if N == 1 else ["render_f32_small_kernel"] if N > 4 else
+                                                      ["classify_tiles_small_kernel", "render_f32_small_kernel"])},
             "clocks": clocks,
         }
         if c4:

@@ -1261,7 +1261,7 @@ int rtc_render_device(rtc_context* ctx, const rtc_camera* cam, const rtc_render_
             CamParams cp = make_cam(cam, opts, g, G, tile_rows);
             cp.dst_full = 1;
             if (g == 0) CUDA_TRY(cudaEventRecord(d.ev_k0, s0));
-            rc = launch_on(dg, cp, opts->precision, opts->flags | (g > 0 ? RTC_OPT_LINEAR_TILE_ORDER : 0), d_out_rgb, d_out_hit_mask,
+            rc = launch_on(dg, cp, opts->precision, opts->flags | (g > 0 && G > 4 ? RTC_OPT_LINEAR_TILE_ORDER : 0)   /* more than four GPUs: an even pixel stream into the first GPU's NVLink ingress */, d_out_rgb, d_out_hit_mask,
                            counters ? dg.counters.p : nullptr, sg);
             if (rc != RTC_OK) return rc;
             if (counters) CUDA_TRY(cudaMemcpyAsync(&ctx->pinned_counters[g], dg.counters.p, sizeof(Counters), cudaMemcpyDeviceToHost, sg));

@@ -125,9 +125,11 @@ class ShardedFrame:
         flags = kw.pop("flags", 0)
         if self.world > 1 and self.mode == "p2p":
             flags |= ffi.OPT_DST_FULL_FRAME
-            if self.rank != 0:
-                # peer stores: keep the pixel stream over NVLink even in time (the heavy-tiles-first order
-                # ends with a burst of cheap pixels that saturates rank 0's ingress; measured +27 us at N=8)
+            if self.rank != 0 and self.world > 4:
+                # peer stores from MORE than four GPUs: keep the pixel stream over NVLink even in time (87 MB per 4K frame into
+                # rank 0's 900 GB/s ingress is 97 us of a 150 us kernel at N = 8, and the heavy-tiles-first order ends with a
+                # burst of cheap pixels over that limit: +27 us).  Up to four GPUs the link has room and the heavy-first order
+                # is the faster kernel (a 1/2 shard 0.625 -> 0.601 ms, a 1/4 shard 0.332 -> 0.316; profiles/r02_tail_trace.txt).
                 flags |= ffi.OPT_LINEAR_TILE_ORDER
         return make_opts(out_format=self.out_format, shard_index=self.rank, shard_count=self.world,
                          tile_rows=self.tile_rows, flags=flags, **kw)
