@@ -151,9 +151,9 @@ typedef struct rtc_render_opts {
  * finished pixels travel over NVLink as the kernel produces them, no collective afterwards. */
 #define RTC_OPT_DST_FULL_FRAME 1
 /* f32 fast mode: use the general f32 kernel even when the library would choose another one — the constant-bank small-scene
- * kernel for scenes that fit it, the parity kernel for scenes whose streams exceed shared memory (10^3+ shapes: it is the
- * fastest kernel that meets the fast-mode tolerance there; the general kernel then runs its mixed-precision form: f32
- * hierarchy and shading, geometry of the radiance rays in f64).  For testing and measuring one against the other. */
+ * kernel for scenes that fit it, the parity kernel for scenes of more than 128 shapes (it is the fastest kernel that meets
+ * the fast-mode tolerance there, and exact; the general kernel then runs its mixed-precision form: f32 hierarchy and
+ * shading, geometry of the radiance rays in f64).  For testing and measuring one against the other. */
 #define RTC_OPT_F32_GENERAL_KERNEL 2
 /* f32 small-scene kernel: hand tiles out in linear order instead of "tiles that see a transparent
  * surface first" (the scheduling pre-pass).  Same image either way; for measuring the difference. */
