@@ -217,7 +217,11 @@ void rtc_context_destroy(rtc_context* ctx);
 
 /* Scene flattening pass: takes World.shapes in add_shape order (src/shape.rs:661-667) and
  * World.light, and packs them into structure-of-arrays device buffers on every GPU of the
- * context.  Replaces what World::intersect (src/shape.rs:677-683) reads per ray. */
+ * context.  Replaces what World::intersect (src/shape.rs:677-683) reads per ray.  `light` and `shapes` are not referenced
+ * after the call returns.  On a one-GPU context the arrays travel as one pinned blob and the call returns without
+ * waiting for the copy: every later call of this library on the context is ordered behind it (on the context's own stream
+ * by stream order, on a caller's stream by an event wait the library inserts).  Uploading a new scene while a render of
+ * the old one is still in flight on another stream is the caller's to order, as it always was. */
 int rtc_scene_upload(rtc_context* ctx, const rtc_light* light, const rtc_shape* shapes, size_t n_shapes);
 
 /* Same flattening pass for a world with several point lights — the "FIXME -- multiple lights" of World::shade_hit

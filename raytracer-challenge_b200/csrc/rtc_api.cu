@@ -88,6 +88,9 @@ struct DeviceState {
     DevBuf<Counters> counters;
     DevBuf<unsigned> work;  // tile counter of the persistent f32 kernel (+ blocks done, heavy / light tile counts)
     DevBuf<unsigned> order; // tile hand-out order of the small-scene kernel
+    DevBuf<unsigned char> upload_arena;   // device copy of rtc_context::pinned_upload, scattered to the scene buffers by one kernel
+    cudaEvent_t upload_done = nullptr;    // recorded on `stream` behind that kernel: the blob may be packed again, and launches on
+                                          // OTHER streams (rtc_render_device with a caller's stream) wait for it before they read the scene
     DevBuf<unsigned> wait_status;   // rtc_wait_device: 0, or 1 + index of the first flag that did not arrive in time
     bool peer_to_first = false;     // this GPU can store into the context's first GPU (rtc_render_device on several GPUs)
 };
@@ -208,6 +211,8 @@ struct rtc_context {
     size_t pinned_hit_cap = 0;
     Counters* pinned_counters = nullptr;  // one per device
     unsigned* pinned_status = nullptr;    // rtc_wait_result reads the wait status word through this
+    unsigned char* pinned_upload = nullptr;   // rtc_scene_upload on a one-GPU context: table + all scene arrays, one H2D copy
+    size_t pinned_upload_cap = 0;
     std::vector<std::pair<unsigned char*, size_t>> registered;   // rtc_register_host_buffer ranges
     std::vector<bool> registered_owned;                          // false: the range was already page-locked by another owner (not ours to unregister)
     double wait_timeout_s = 60.0;
@@ -787,6 +792,38 @@ cudaError_t upload(DevBuf<T>& b, const std::vector<T>& v, cudaStream_t st) {
     return cudaMemcpyAsync(b.p, v.data(), v.size() * sizeof(T), cudaMemcpyHostToDevice, st);
 }
 
+// rtc_scene_upload on a one-GPU context: the ~20 scene arrays of a small scene are ~10 KB in all, and 20 separate copies
+// (each finished before the call returns: the host vectors die) were 60 us on the critical path of every end-to-end step.
+// They travel as ONE pinned blob — a table of (destination, offset, bytes) followed by the arrays — and one kernel scatters
+// the blob to the scene buffers; the call returns without waiting (the blob is the context's, packed again only after
+// upload_done).  All arrays are 4-byte granular and the offsets 256-byte aligned.
+struct ScatterEntry { unsigned long long dst, off, bytes; };
+__global__ void scatter_upload_kernel(const unsigned char* __restrict__ blob, int n) {
+    const ScatterEntry* tab = reinterpret_cast<const ScatterEntry*>(blob);
+    for (int e = blockIdx.y; e < n; e += gridDim.y) {
+        const ScatterEntry t = tab[e];
+        const uint4* s = reinterpret_cast<const uint4*>(blob + t.off);
+        uint4* d = reinterpret_cast<uint4*>(t.dst);
+        const size_t n16 = t.bytes / 16;
+        for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n16; i += (size_t)gridDim.x * blockDim.x) d[i] = s[i];
+        const size_t tail4 = (t.bytes - n16 * 16) / 4;
+        if (blockIdx.x == 0 && threadIdx.x < tail4)
+            reinterpret_cast<unsigned*>(t.dst)[n16 * 4 + threadIdx.x] = reinterpret_cast<const unsigned*>(blob + t.off)[n16 * 4 + threadIdx.x];
+    }
+}
+struct UploadBatch {
+    struct Item { void* dst; const void* src; size_t bytes; };
+    std::vector<Item> items;
+    cudaError_t err = cudaSuccess;
+    template <typename T>
+    void add(DevBuf<T>& b, const std::vector<T>& v) {
+        static_assert(sizeof(T) % 4 == 0, "4-byte granular arrays");
+        if (err != cudaSuccess) return;
+        err = b.ensure(v.size());
+        if (err == cudaSuccess && !v.empty()) items.push_back({b.p, v.data(), v.size() * sizeof(T)});
+    }
+};
+
 }  // namespace
 
 // ---- de-interleave kernel (rtc_assemble_device) --------------------------------------------------
@@ -993,6 +1030,8 @@ struct SyncSpec {
 int launch_on(DeviceState& d, const CamParams& cp, int precision, int flags, void* d_rgb, uint8_t* d_hit, Counters* d_counters,
               cudaStream_t st, const SyncSpec* sync = nullptr) {
     cudaError_t e;
+    if (st != d.stream && d.upload_done && (e = cudaStreamWaitEvent(st, d.upload_done, 0)) != cudaSuccess)   // rtc_scene_upload no longer waits
+        return fail(RTC_ERR_CUDA, std::string("stream order behind the scene upload: ") + cudaGetErrorString(e));
     const bool fused = sync && precision == RTC_PRECISION_F32_FAST && d.small_ok && !(flags & RTC_OPT_F32_GENERAL_KERNEL);
     if (sync && !fused && sync->wait_flag) {   // kernels without the fused form: the flag kernels around the launch
         wait_kernel<<<1, 32, 0, st>>>(sync->wait_flag, 1, sync->wait_value, sync->timeout_ns, d.wait_status.p);
@@ -1086,6 +1125,7 @@ int rtc_context_create(const int* device_ids, int n_gpus, rtc_context** out_ctx)
         if (e == cudaSuccess) e = preload_render_f64();      // no launch of the library ever loads code (rtc_common.h)
         if (e == cudaSuccess) e = preload_render_f32();
         if (e == cudaSuccess) e = preload_render_f32_small();
+        if (e == cudaSuccess) { cudaFuncAttributes at; e = cudaFuncGetAttributes(&at, scatter_upload_kernel); }
         if (e == cudaSuccess) {
             cudaFuncAttributes at;
             const void* own[] = {(const void*)signal_kernel, (const void*)wait_kernel, (const void*)assemble_rows_kernel<uint4>,
@@ -1128,10 +1168,11 @@ void rtc_context_destroy(rtc_context* ctx) {
         if (d.stream) cudaStreamSynchronize(d.stream);
         d.sph64.release(); d.pl64.release(); d.pl32.release(); d.us32.release(); d.gs32.release(); d.us_index.release(); d.gs_index.release(); d.gset.release(); d.plL.release(); d.usL.release(); d.lights64.release(); d.lights32.release(); d.bound64.release(); d.gbound.release(); d.gbound64.release(); d.sbound.release(); d.sbound64.release(); d.bound.release(); d.gbox.release(); d.sbox.release();
         d.sph_index.release(); d.pl_index.release(); d.rec64.release(); d.rec32.release(); d.srec.release();
-        d.rgb.release(); d.rgb_wide.release(); d.hit.release(); d.counters.release(); d.work.release(); d.order.release(); d.wait_status.release();
+        d.rgb.release(); d.rgb_wide.release(); d.hit.release(); d.counters.release(); d.work.release(); d.order.release(); d.wait_status.release(); d.upload_arena.release();
         if (d.ev_k0) cudaEventDestroy(d.ev_k0);
         if (d.ev_k1) cudaEventDestroy(d.ev_k1);
         if (d.ev_c0) cudaEventDestroy(d.ev_c0);
+        if (d.upload_done) cudaEventDestroy(d.upload_done);
         if (d.ev_c1) cudaEventDestroy(d.ev_c1);
         for (int b = 0; b < kMaxBands; ++b) {
             if (d.ev_band[b]) cudaEventDestroy(d.ev_band[b]);
@@ -1141,6 +1182,7 @@ void rtc_context_destroy(rtc_context* ctx) {
         if (d.stream) cudaStreamDestroy(d.stream);
     }
     if (ctx->pinned_rgb) cudaFreeHost(ctx->pinned_rgb);
+    if (ctx->pinned_upload) cudaFreeHost(ctx->pinned_upload);
     if (ctx->pinned_hit) cudaFreeHost(ctx->pinned_hit);
     if (ctx->pinned_counters) cudaFreeHost(ctx->pinned_counters);
     if (ctx->pinned_status) cudaFreeHost(ctx->pinned_status);
@@ -1161,33 +1203,64 @@ int rtc_scene_upload_lights(rtc_context* ctx, const rtc_light* light, size_t n_l
     if (rc != RTC_OK) return rc;
     for (DeviceState& d : ctx->devs) {
         CUDA_TRY(cudaSetDevice(d.dev));
-        CUDA_TRY(upload(d.sph64, hs.sph64, d.stream));
-        CUDA_TRY(upload(d.pl64, hs.pl64, d.stream));
-        CUDA_TRY(upload(d.pl32, hs.pl32, d.stream));
-        CUDA_TRY(upload(d.us32, hs.us32, d.stream));
-        CUDA_TRY(upload(d.gs32, hs.gs32, d.stream));
-        CUDA_TRY(upload(d.us_index, hs.us_index, d.stream));
-        CUDA_TRY(upload(d.gs_index, hs.gs_index, d.stream));
-        CUDA_TRY(upload(d.gset, hs.gset, d.stream));
-        CUDA_TRY(upload(d.plL, hs.plL, d.stream));
-        CUDA_TRY(upload(d.usL, hs.usL, d.stream));
-        CUDA_TRY(upload(d.lights64, hs.lights64, d.stream));
-        CUDA_TRY(upload(d.lights32, hs.lights32, d.stream));
-        CUDA_TRY(upload(d.bound, hs.bound, d.stream));
-        CUDA_TRY(upload(d.bound64, hs.bound64, d.stream));
-        CUDA_TRY(upload(d.gbound, hs.gbound, d.stream));
-        CUDA_TRY(upload(d.gbound64, hs.gbound64, d.stream));
-        CUDA_TRY(upload(d.sbound, hs.sbound, d.stream));
-        CUDA_TRY(upload(d.sbound64, hs.sbound64, d.stream));
-        CUDA_TRY(upload(d.gbox, hs.gbox, d.stream));
-        CUDA_TRY(upload(d.sbox, hs.sbox, d.stream));
-        CUDA_TRY(upload(d.sph_index, hs.sph_index, d.stream));
-        CUDA_TRY(upload(d.pl_index, hs.pl_index, d.stream));
-        CUDA_TRY(upload(d.rec64, hs.rec64, d.stream));
-        CUDA_TRY(upload(d.rec32, hs.rec32, d.stream));
+        const bool batched = ctx->devs.size() == 1;   // several GPUs: the plain copies (every device needs its own table)
+        UploadBatch batch;
+        if (batched) {
+            batch.add(d.sph64, hs.sph64);
+            batch.add(d.pl64, hs.pl64);
+            batch.add(d.pl32, hs.pl32);
+            batch.add(d.us32, hs.us32);
+            batch.add(d.gs32, hs.gs32);
+            batch.add(d.us_index, hs.us_index);
+            batch.add(d.gs_index, hs.gs_index);
+            batch.add(d.gset, hs.gset);
+            batch.add(d.plL, hs.plL);
+            batch.add(d.usL, hs.usL);
+            batch.add(d.lights64, hs.lights64);
+            batch.add(d.lights32, hs.lights32);
+            batch.add(d.bound, hs.bound);
+            batch.add(d.bound64, hs.bound64);
+            batch.add(d.gbound, hs.gbound);
+            batch.add(d.gbound64, hs.gbound64);
+            batch.add(d.sbound, hs.sbound);
+            batch.add(d.sbound64, hs.sbound64);
+            batch.add(d.gbox, hs.gbox);
+            batch.add(d.sbox, hs.sbox);
+            batch.add(d.sph_index, hs.sph_index);
+            batch.add(d.pl_index, hs.pl_index);
+            batch.add(d.rec64, hs.rec64);
+            batch.add(d.rec32, hs.rec32);
+            if (hs.small_ok) batch.add(d.srec, hs.srec);
+            CUDA_TRY(batch.err);
+        } else {
+            CUDA_TRY(upload(d.sph64, hs.sph64, d.stream));
+            CUDA_TRY(upload(d.pl64, hs.pl64, d.stream));
+            CUDA_TRY(upload(d.pl32, hs.pl32, d.stream));
+            CUDA_TRY(upload(d.us32, hs.us32, d.stream));
+            CUDA_TRY(upload(d.gs32, hs.gs32, d.stream));
+            CUDA_TRY(upload(d.us_index, hs.us_index, d.stream));
+            CUDA_TRY(upload(d.gs_index, hs.gs_index, d.stream));
+            CUDA_TRY(upload(d.gset, hs.gset, d.stream));
+            CUDA_TRY(upload(d.plL, hs.plL, d.stream));
+            CUDA_TRY(upload(d.usL, hs.usL, d.stream));
+            CUDA_TRY(upload(d.lights64, hs.lights64, d.stream));
+            CUDA_TRY(upload(d.lights32, hs.lights32, d.stream));
+            CUDA_TRY(upload(d.bound, hs.bound, d.stream));
+            CUDA_TRY(upload(d.bound64, hs.bound64, d.stream));
+            CUDA_TRY(upload(d.gbound, hs.gbound, d.stream));
+            CUDA_TRY(upload(d.gbound64, hs.gbound64, d.stream));
+            CUDA_TRY(upload(d.sbound, hs.sbound, d.stream));
+            CUDA_TRY(upload(d.sbound64, hs.sbound64, d.stream));
+            CUDA_TRY(upload(d.gbox, hs.gbox, d.stream));
+            CUDA_TRY(upload(d.sbox, hs.sbox, d.stream));
+            CUDA_TRY(upload(d.sph_index, hs.sph_index, d.stream));
+            CUDA_TRY(upload(d.pl_index, hs.pl_index, d.stream));
+            CUDA_TRY(upload(d.rec64, hs.rec64, d.stream));
+            CUDA_TRY(upload(d.rec32, hs.rec32, d.stream));
+            if (hs.small_ok) CUDA_TRY(upload(d.srec, hs.srec, d.stream));
+        }
         d.small_ok = hs.small_ok;
         if (hs.small_ok) {
-            CUDA_TRY(upload(d.srec, hs.srec, d.stream));
             d.small = hs.small;
             d.small.rec = d.srec.p;
         }
@@ -1218,8 +1291,33 @@ int rtc_scene_upload_lights(rtc_context* ctx, const rtc_light* light, size_t n_l
             d.s64.light_pos[k] = light->position[k]; d.s64.light_int[k] = light->intensity[k];
             d.s32.light_pos[k] = (float)light->position[k]; d.s32.light_int[k] = (float)light->intensity[k];
         }
-        // the host vectors die at return: finish the copies now
-        CUDA_TRY(cudaStreamSynchronize(d.stream));
+        if (batched) {
+            size_t total = (batch.items.size() * sizeof(ScatterEntry) + 255) / 256 * 256, max_bytes = 0;
+            std::vector<ScatterEntry> table;
+            for (const auto& it : batch.items) { table.push_back({(unsigned long long)(uintptr_t)it.dst, (unsigned long long)total, (unsigned long long)it.bytes}); total += (it.bytes + 255) / 256 * 256; max_bytes = std::max(max_bytes, it.bytes); }
+            if (!d.upload_done) CUDA_TRY(cudaEventCreateWithFlags(&d.upload_done, cudaEventDisableTiming));
+            else CUDA_TRY(cudaEventSynchronize(d.upload_done));          // the previous upload's copy has left the blob
+            if (total > ctx->pinned_upload_cap) {
+                if (ctx->pinned_upload) cudaFreeHost(ctx->pinned_upload);
+                ctx->pinned_upload = nullptr; ctx->pinned_upload_cap = 0;
+                CUDA_TRY(cudaMallocHost((void**)&ctx->pinned_upload, total));
+                ctx->pinned_upload_cap = total;
+            }
+            CUDA_TRY(d.upload_arena.ensure(total));
+            if (!table.empty()) {
+                std::memcpy(ctx->pinned_upload, table.data(), table.size() * sizeof(ScatterEntry));
+                for (size_t k = 0; k < batch.items.size(); ++k) std::memcpy(ctx->pinned_upload + table[k].off, batch.items[k].src, batch.items[k].bytes);
+                CUDA_TRY(cudaMemcpyAsync(d.upload_arena.p, ctx->pinned_upload, total, cudaMemcpyHostToDevice, d.stream));
+                const unsigned gx = (unsigned)std::max<size_t>(1, std::min<size_t>(64, (max_bytes / 16 + 255) / 256));
+                scatter_upload_kernel<<<dim3(gx, (unsigned)std::min<size_t>(table.size(), 64)), 256, 0, d.stream>>>(d.upload_arena.p, (int)table.size());
+                CUDA_TRY(cudaGetLastError());
+            }
+            CUDA_TRY(cudaEventRecord(d.upload_done, d.stream));
+            // no wait: the blob is the context's, and everything that reads the scene is ordered behind d.stream
+        } else {
+            // the host vectors die at return: finish the copies now
+            CUDA_TRY(cudaStreamSynchronize(d.stream));
+        }
     }
     ctx->has_scene = true;
     return RTC_OK;
@@ -1468,6 +1566,7 @@ int rtc_render_device_noalloc(rtc_context* ctx, const rtc_camera* cam, const rtc
         return fail(RTC_ERR_UNSUPPORTED, "rtc_render_device_noalloc: the frame has " + std::to_string(P.total_tiles) + " tiles of 8x4 pixels, the static scratch holds " +
                                              std::to_string(kNoAllocMaxTiles) + " (RTC_NOALLOC_MAX_TILES; 7680x4320 fits)");
     const bool tile_order = P.max_depth > 0 && P.n_glass != 0 && P.total_tiles >= 4096 && !(opts->flags & RTC_OPT_LINEAR_TILE_ORDER);
+    if ((cudaStream_t)stream != d.stream && d.upload_done) CUDA_TRY(cudaStreamWaitEvent((cudaStream_t)stream, d.upload_done, 0));   // the scene upload does not wait
     cudaError_t e = launch_render_f32_small_noalloc(P, tile_order, cp.out_format, d_out_rgb, d_out_hit_mask, (cudaStream_t)stream);
     if (e != cudaSuccess) return fail(RTC_ERR_CUDA, std::string("rtc_render_device_noalloc: ") + cudaGetErrorString(e));
     return RTC_OK;
